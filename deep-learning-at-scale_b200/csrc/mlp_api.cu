@@ -1,0 +1,131 @@
+// C-ABI entry points of the MLP path: mode dispatch (fp32 CUDA-core kernels / tcgen05 kernels)
+// and the mini-batch step loop that stands in for Keras `model.fit` (cnn.py:127-128).
+#include "common.cuh"
+
+namespace dlas {
+// mlp_simt.cu
+size_t simt_workspace_bytes(const int* dims, int n_layers);
+int simt_grad(const int* dims, int n_layers, int loss, const float* params, const float* X, const float* y,
+              size_t n_rows, float* grad_sum, void* workspace, size_t workspace_bytes, cudaStream_t st);
+int simt_eval_loss(const int* dims, int n_layers, int loss, const float* params, const float* X, const float* y,
+                   size_t n_rows, float* loss_sum, void* workspace, size_t workspace_bytes, cudaStream_t st);
+int simt_predict(const int* dims, int n_layers, const float* params, const float* X, size_t n_rows, float* yhat,
+                 cudaStream_t st);
+// optim.cu
+int opt_step_impl(const dlas_opt_cfg* cfg, float* params, float* m, float* v, const float* grad_sum, size_t n,
+                  float grad_scale, uint64_t iteration, float* loss_out, cudaStream_t st);
+// mlp_tc.cu
+bool tc_supported(const int* dims, int n_layers);
+size_t tc_workspace_bytes(const int* dims, int n_layers);
+int tc_grad(const int* dims, int n_layers, int loss, const float* params, const float* X, const float* y,
+            size_t n_rows, float* grad_sum, void* workspace, size_t workspace_bytes, cudaStream_t st);
+
+namespace {
+int check_common(const char* fn, const int* dims, int n_layers, int loss, int mode) {
+  DLAS_REQUIRE(dims != nullptr, "%s: dims is null", fn);
+  DLAS_REQUIRE(n_layers >= 1 && n_layers <= 8, "%s: n_layers %d not in 1..8", fn, n_layers);
+  DLAS_REQUIRE(loss == DLAS_LOSS_MSE || loss == DLAS_LOSS_MAE_CLIP, "%s: unknown loss %d", fn, loss);
+  DLAS_REQUIRE(mode == DLAS_MODE_FP32 || mode == DLAS_MODE_TC, "%s: unknown mode %d", fn, mode);
+  if (mode == DLAS_MODE_TC && !tc_supported(dims, n_layers)) {
+    set_error("%s: DLAS_MODE_TC does not support these layer widths (see dlas_mlp_mode_supported)", fn);
+    return DLAS_ERR_UNSUPPORTED_SHAPE;
+  }
+  return DLAS_OK;
+}
+}  // namespace
+}  // namespace dlas
+
+using namespace dlas;
+
+extern "C" size_t dlas_mlp_n_params(const int* dims, int n_layers) {
+  if (!dims || n_layers < 1) return 0;
+  size_t n = 0;
+  for (int l = 0; l < n_layers; ++l) n += (size_t)dims[l] * dims[l + 1] + dims[l + 1];
+  return n;
+}
+
+extern "C" int dlas_mlp_mode_supported(const int* dims, int n_layers, int mode) {
+  if (!dims || n_layers < 1 || n_layers > 8) return 0;
+  if (mode == DLAS_MODE_FP32) return simt_workspace_bytes(dims, n_layers) > 0 ? 1 : 0;
+  if (mode == DLAS_MODE_TC) return tc_supported(dims, n_layers) ? 1 : 0;
+  return 0;
+}
+
+extern "C" size_t dlas_mlp_workspace_bytes(const int* dims, int n_layers, int mode) {
+  if (!dims || n_layers < 1 || n_layers > 8) return 0;
+  if (mode == DLAS_MODE_TC) return tc_supported(dims, n_layers) ? tc_workspace_bytes(dims, n_layers) : 0;
+  return simt_workspace_bytes(dims, n_layers);
+}
+
+extern "C" int dlas_mlp_grad(const int* dims, int n_layers, int loss, int mode, const float* params,
+                             const float* X, const float* y, size_t n_rows, float* grad_sum,
+                             void* workspace, size_t workspace_bytes, void* stream) {
+  DLAS_CHECK_DEVICE();
+  int rc = check_common("dlas_mlp_grad", dims, n_layers, loss, mode);
+  if (rc != DLAS_OK) return rc;
+  DLAS_REQUIRE(params && grad_sum && (n_rows == 0 || (X && y)), "dlas_mlp_grad: null pointer");
+  if (mode == DLAS_MODE_TC)
+    return tc_grad(dims, n_layers, loss, params, X, y, n_rows, grad_sum, workspace, workspace_bytes,
+                   (cudaStream_t)stream);
+  return simt_grad(dims, n_layers, loss, params, X, y, n_rows, grad_sum, workspace, workspace_bytes,
+                   (cudaStream_t)stream);
+}
+
+extern "C" int dlas_mlp_fit_steps(const int* dims, int n_layers, int loss, int mode,
+                                  const dlas_opt_cfg* cfg, float* params, float* m, float* v,
+                                  const float* X, const float* y, size_t n_rows, int batch,
+                                  const int64_t* batch_order_host, int64_t first_batch, int n_steps,
+                                  uint64_t iteration0, float* step_losses, float* grad_sum,
+                                  void* workspace, size_t workspace_bytes, void* stream) {
+  DLAS_CHECK_DEVICE();
+  int rc = check_common("dlas_mlp_fit_steps", dims, n_layers, loss, mode);
+  if (rc != DLAS_OK) return rc;
+  DLAS_REQUIRE(cfg && params && m && X && y && grad_sum, "dlas_mlp_fit_steps: null pointer");
+  DLAS_REQUIRE(batch >= 1, "dlas_mlp_fit_steps: batch %d < 1", batch);
+  DLAS_REQUIRE(n_steps >= 0, "dlas_mlp_fit_steps: n_steps %d < 0", n_steps);
+  const size_t n_batches = n_rows / (size_t)batch;  // Keras would also run a ragged last batch; callers
+  DLAS_REQUIRE(n_batches >= 1 || n_steps == 0,      // pass it as its own call with batch = remainder
+               "dlas_mlp_fit_steps: n_rows %zu < batch %d", n_rows, batch);
+  const size_t n_params = dlas_mlp_n_params(dims, n_layers);
+  const size_t d0 = dims[0], dL = dims[n_layers];
+  cudaStream_t st = (cudaStream_t)stream;
+  for (int s = 0; s < n_steps; ++s) {
+    int64_t b = batch_order_host ? batch_order_host[s] : first_batch + s;
+    DLAS_REQUIRE(b >= 0 && (size_t)b < n_batches, "dlas_mlp_fit_steps: batch index %lld out of range (%zu batches)",
+                 (long long)b, n_batches);
+    const float* Xb = X + (size_t)b * batch * d0;
+    const float* yb = y + (size_t)b * batch * dL;
+    if (mode == DLAS_MODE_TC)
+      rc = tc_grad(dims, n_layers, loss, params, Xb, yb, batch, grad_sum, workspace, workspace_bytes, st);
+    else
+      rc = simt_grad(dims, n_layers, loss, params, Xb, yb, batch, grad_sum, workspace, workspace_bytes, st);
+    if (rc != DLAS_OK) return rc;
+    rc = opt_step_impl(cfg, params, m, v, grad_sum, n_params, 1.0f / (float)batch, iteration0 + (uint64_t)s,
+                       step_losses ? step_losses + s : nullptr, st);
+    if (rc != DLAS_OK) return rc;
+  }
+  return DLAS_OK;
+}
+
+extern "C" int dlas_mlp_predict(const int* dims, int n_layers, int mode, const float* params,
+                                const float* X, size_t n_rows, float* yhat, void* stream) {
+  DLAS_CHECK_DEVICE();
+  int rc = check_common("dlas_mlp_predict", dims, n_layers, DLAS_LOSS_MSE, DLAS_MODE_FP32);
+  if (rc != DLAS_OK) return rc;
+  DLAS_REQUIRE(mode == DLAS_MODE_FP32 || mode == DLAS_MODE_TC, "dlas_mlp_predict: unknown mode %d", mode);
+  DLAS_REQUIRE(params && (n_rows == 0 || (X && yhat)), "dlas_mlp_predict: null pointer");
+  // inference runs the fp32 kernel in both modes (HBM-leaning)
+  return simt_predict(dims, n_layers, params, X, n_rows, yhat, (cudaStream_t)stream);
+}
+
+extern "C" int dlas_mlp_eval_loss(const int* dims, int n_layers, int loss, int mode, const float* params,
+                                  const float* X, const float* y, size_t n_rows, float* loss_sum,
+                                  void* workspace, size_t workspace_bytes, void* stream) {
+  DLAS_CHECK_DEVICE();
+  int rc = check_common("dlas_mlp_eval_loss", dims, n_layers, loss, DLAS_MODE_FP32);
+  if (rc != DLAS_OK) return rc;
+  DLAS_REQUIRE(mode == DLAS_MODE_FP32 || mode == DLAS_MODE_TC, "dlas_mlp_eval_loss: unknown mode %d", mode);
+  DLAS_REQUIRE(params && loss_sum && (n_rows == 0 || (X && y)), "dlas_mlp_eval_loss: null pointer");
+  return simt_eval_loss(dims, n_layers, loss, params, X, y, n_rows, loss_sum, workspace, workspace_bytes,
+                        (cudaStream_t)stream);
+}

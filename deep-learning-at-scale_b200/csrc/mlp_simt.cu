@@ -1,0 +1,410 @@
+// Fused fp32 MLP training / inference on CUDA cores (DLAS_MODE_FP32): forward, loss, backward and
+// per-CTA weight-gradient accumulation in ONE persistent kernel, any layer widths.
+// Stands in for the per-batch body of Keras `model.fit` / `test_on_batch` (cnn.py:127-128, :132),
+// with the loss of cnn.py:29-32 and MSE.
+//
+// Layout per CTA (one CTA per SM, grid = SM count, tiles of R=32 rows handed out round-robin so the
+// summation order is fixed):
+//   smem  actT[l][feature][RS]   activations of every layer, transposed (rows contiguous, RS=36
+//                                floats so that float4 row loads stay aligned and column reads
+//                                spread over banks)
+//         dzT[2][max_w][RS]      ping-pong pre-activation gradients
+//   HBM   partial[cta][n_params+1]  this CTA's running gradient sums (+ loss sum); private, no atomics
+//         WT                     per-layer transposed weights for the backward data pass
+// A second tiny kernel adds the per-CTA partials in CTA order (deterministic).
+// Algorithmic work: 2*sum(in*out) flop forward and 4*sum(in*out) (minus the first layer's dX)
+// backward per row; 4*(in0+out) bytes per row from HBM.
+#include "common.cuh"
+
+namespace dlas {
+namespace {
+
+constexpr int R = 32;      // rows per tile
+constexpr int RS = 36;     // padded row stride of transposed tiles (floats)
+constexpr int NT = 512;    // threads per CTA
+constexpr int MAXL = 8;    // max Dense layers
+
+struct MlpDesc {
+  int n_layers;
+  int dims[MAXL + 1];
+  int w_off[MAXL];
+  int b_off[MAXL];
+  int act_off[MAXL + 1];  // float offset of actT[l] in dynamic smem
+  int dz_off[2];
+  int n_params;
+  int max_w;
+  int smem_floats;
+};
+
+int make_desc(const int* dims, int n_layers, MlpDesc& d) {
+  DLAS_REQUIRE(dims != nullptr, "mlp: dims is null");
+  DLAS_REQUIRE(n_layers >= 1 && n_layers <= MAXL, "mlp: n_layers %d not in 1..%d", n_layers, MAXL);
+  d.n_layers = n_layers;
+  int o = 0, so = 0, mw = 0;
+  for (int l = 0; l <= n_layers; ++l) {
+    DLAS_REQUIRE(dims[l] >= 1 && dims[l] <= 4096, "mlp: dims[%d]=%d not in 1..4096", l, dims[l]);
+    d.dims[l] = dims[l];
+    d.act_off[l] = so;
+    so += dims[l] * RS;
+    if (l > 0 && dims[l] > mw) mw = dims[l];
+  }
+  for (int l = 0; l < n_layers; ++l) {
+    d.w_off[l] = o;
+    o += dims[l] * dims[l + 1];
+    d.b_off[l] = o;
+    o += dims[l + 1];
+  }
+  d.n_params = o;
+  d.max_w = mw;
+  d.dz_off[0] = so;
+  so += mw * RS;
+  d.dz_off[1] = so;
+  so += mw * RS;
+  d.smem_floats = so + 32;  // + block-reduce scratch
+  if ((size_t)d.smem_floats * 4 > 227 * 1024) {
+    set_error("mlp fp32 mode: layer widths need %zu bytes of shared memory per CTA (> 227 KB)",
+              (size_t)d.smem_floats * 4);
+    return DLAS_ERR_UNSUPPORTED_SHAPE;
+  }
+  return DLAS_OK;
+}
+
+__host__ __device__ inline size_t partial_stride(int n_params) { return ((size_t)n_params + 1 + 3) & ~(size_t)3; }
+
+// out(j, r0..r0+RT) = sum_k inT[k][r] * Wm[k*ldw + j]; one (column j, row group) item per thread.
+template <int RT, class Epi>
+__device__ __forceinline__ void gemm_rows(const float* __restrict__ inT, const float* __restrict__ Wm,
+                                          int ldw, int K, int N, Epi epi) {
+  constexpr int G = R / RT;
+  const int items = N * G;
+  for (int item = threadIdx.x; item < items; item += NT) {
+    const int j = item % N, r0 = (item / N) * RT;
+    float acc[RT];
+#pragma unroll
+    for (int i = 0; i < RT; ++i) acc[i] = 0.0f;
+    const float* a = inT + r0;
+    const float* w = Wm + j;
+    int k = 0;
+    for (; k + 4 <= K; k += 4) {
+      float wv[4];
+#pragma unroll
+      for (int u = 0; u < 4; ++u) wv[u] = __ldg(w + (size_t)(k + u) * ldw);
+#pragma unroll
+      for (int u = 0; u < 4; ++u) {
+        const float* ar = a + (k + u) * RS;
+        if (RT >= 4) {
+#pragma unroll
+          for (int i = 0; i < RT; i += 4) {
+            float4 v = *reinterpret_cast<const float4*>(ar + i);
+            acc[i] = fmaf(v.x, wv[u], acc[i]);
+            acc[i + 1] = fmaf(v.y, wv[u], acc[i + 1]);
+            acc[i + 2] = fmaf(v.z, wv[u], acc[i + 2]);
+            acc[i + 3] = fmaf(v.w, wv[u], acc[i + 3]);
+          }
+        } else {
+#pragma unroll
+          for (int i = 0; i < RT; ++i) acc[i] = fmaf(ar[i], wv[u], acc[i]);
+        }
+      }
+    }
+    for (; k < K; ++k) {
+      float wv = __ldg(w + (size_t)k * ldw);
+      const float* ar = a + k * RS;
+#pragma unroll
+      for (int i = 0; i < RT; ++i) acc[i] = fmaf(ar[i], wv, acc[i]);
+    }
+    epi(j, r0, acc);
+  }
+}
+
+template <class Epi>
+__device__ __forceinline__ void gemm_dispatch(const float* inT, const float* Wm, int ldw, int K, int N, Epi epi) {
+  // as many row groups as the thread count allows: RT = R / min(R, NT / N) rounded to a power of 2
+  int g = NT / N;
+  if (g >= 32) gemm_rows<1>(inT, Wm, ldw, K, N, epi);
+  else if (g >= 16) gemm_rows<2>(inT, Wm, ldw, K, N, epi);
+  else if (g >= 8) gemm_rows<4>(inT, Wm, ldw, K, N, epi);
+  else if (g >= 4) gemm_rows<8>(inT, Wm, ldw, K, N, epi);
+  else if (g >= 2) gemm_rows<16>(inT, Wm, ldw, K, N, epi);
+  else gemm_rows<32>(inT, Wm, ldw, K, N, epi);
+}
+
+// dW[k][j] (+)= sum_r aT[k][r] * dzT[j][r];  db[j] (+)= sum_r dzT[j][r]
+__device__ __forceinline__ void accumulate_dw(const float* __restrict__ aT, const float* __restrict__ dzT,
+                                              int K, int N, float* __restrict__ pw, float* __restrict__ pb,
+                                              bool first) {
+  int kgn = NT / N;
+  if (kgn < 1) kgn = 1;
+  if (kgn > K) kgn = K;
+  const int items = N * kgn;
+  for (int item = threadIdx.x; item < items; item += NT) {
+    const int j = item % N, kg = item / N;
+    float dz[R];
+#pragma unroll
+    for (int i = 0; i < R; i += 4) {
+      float4 v = *reinterpret_cast<const float4*>(dzT + j * RS + i);
+      dz[i] = v.x; dz[i + 1] = v.y; dz[i + 2] = v.z; dz[i + 3] = v.w;
+    }
+    if (kg == 0) {
+      float s = 0.0f;
+#pragma unroll
+      for (int i = 0; i < R; ++i) s += dz[i];
+      pb[j] = first ? s : pb[j] + s;
+    }
+    for (int k = kg; k < K; k += kgn) {
+      const float* ar = aT + k * RS;
+      float s0 = 0.0f, s1 = 0.0f, s2 = 0.0f, s3 = 0.0f;
+#pragma unroll
+      for (int i = 0; i < R; i += 4) {
+        float4 v = *reinterpret_cast<const float4*>(ar + i);
+        s0 = fmaf(v.x, dz[i], s0);
+        s1 = fmaf(v.y, dz[i + 1], s1);
+        s2 = fmaf(v.z, dz[i + 2], s2);
+        s3 = fmaf(v.w, dz[i + 3], s3);
+      }
+      float s = (s0 + s1) + (s2 + s3);
+      float* p = pw + (size_t)k * N + j;
+      *p = first ? s : *p + s;
+    }
+  }
+}
+
+__device__ __forceinline__ float block_sum(float v, float* scratch) {
+  // fixed-order tree: warp shuffle, then lane 0 of each warp through smem
+#pragma unroll
+  for (int o = 16; o > 0; o >>= 1) v += __shfl_down_sync(0xffffffffu, v, o);
+  __syncthreads();
+  if ((threadIdx.x & 31) == 0) scratch[threadIdx.x >> 5] = v;
+  __syncthreads();
+  float s = 0.0f;
+  if (threadIdx.x == 0)
+    for (int w = 0; w < NT / 32; ++w) s += scratch[w];
+  return s;  // valid on thread 0
+}
+
+enum { KIND_TRAIN = 0, KIND_EVAL = 1, KIND_PREDICT = 2 };
+
+template <int KIND>
+__global__ void __launch_bounds__(NT, 1)
+mlp_simt_kernel(const MlpDesc d, const int loss, const float* __restrict__ params,
+                const float* __restrict__ WT, const float* __restrict__ X, const float* __restrict__ y,
+                const size_t n_rows, float* __restrict__ partials, float* __restrict__ yhat) {
+  extern __shared__ __align__(16) float smem[];
+  const int L = d.n_layers;
+  const int d0 = d.dims[0], dL = d.dims[L];
+  const size_t n_tiles = (n_rows + R - 1) / R;
+  float* my_partial = partials ? partials + (size_t)blockIdx.x * partial_stride(d.n_params) : nullptr;
+  float loss_acc = 0.0f;
+  bool first = true;
+
+  for (size_t tile = blockIdx.x; tile < n_tiles; tile += gridDim.x) {
+    const size_t row0 = tile * R;
+    const int nr = (int)((n_rows - row0) < (size_t)R ? (n_rows - row0) : (size_t)R);
+    // ---- X tile -> actT[0] (coalesced global reads, transposed smem writes)
+    {
+      float* a0 = smem + d.act_off[0];
+      const float* xg = X + row0 * (size_t)d0;
+      for (int idx = threadIdx.x; idx < R * d0; idx += NT) {
+        int r = idx / d0, k = idx - r * d0;
+        a0[k * RS + r] = (r < nr) ? __ldcs(xg + idx) : 0.0f;
+      }
+    }
+    __syncthreads();
+    // ---- forward
+    for (int l = 0; l < L; ++l) {
+      const float* inT = smem + d.act_off[l];
+      float* outT = smem + d.act_off[l + 1];
+      const float* bias = params + d.b_off[l];
+      const bool relu = (l < L - 1);
+      gemm_dispatch(inT, params + d.w_off[l], d.dims[l + 1], d.dims[l], d.dims[l + 1],
+                    [&](int j, int r0, auto& acc) {
+                      const float b = __ldg(bias + j);
+                      constexpr int RT = sizeof(acc) / sizeof(float);
+#pragma unroll
+                      for (int i = 0; i < RT; ++i) {
+                        float v = acc[i] + b;
+                        outT[j * RS + r0 + i] = relu ? fmaxf(v, 0.0f) : v;
+                      }
+                    });
+      __syncthreads();
+    }
+    const float* outT = smem + d.act_off[L];
+    if (KIND == KIND_PREDICT) {
+      float* yo = yhat + row0 * (size_t)dL;
+      for (int idx = threadIdx.x; idx < nr * dL; idx += NT) {
+        int r = idx / dL, j = idx - r * dL;
+        yo[idx] = outT[j * RS + r];
+      }
+      __syncthreads();
+      continue;
+    }
+    // ---- loss and d(loss sum)/d(yhat) -> dzT[cur]
+    int cur = 0;
+    float* dz = smem + d.dz_off[cur];
+    {
+      const float inv_out = 1.0f / (float)dL;
+      const float* yg = y + row0 * (size_t)dL;
+      for (int idx = threadIdx.x; idx < R * dL; idx += NT) {
+        int r = idx / dL, j = idx - r * dL;
+        float g = 0.0f;
+        if (r < nr) {
+          float dd = outT[j * RS + r] - __ldcs(yg + idx);
+          if (loss == DLAS_LOSS_MSE) {
+            loss_acc += dd * dd * inv_out;
+            g = 2.0f * dd * inv_out;
+          } else {  // cnn.py:29-32 mae_clip, CLIP_VALUE = 6
+            float a = fabsf(dd);
+            loss_acc += fminf(a, 6.0f) * inv_out;
+            g = (a <= 6.0f) ? (dd > 0.0f ? inv_out : (dd < 0.0f ? -inv_out : 0.0f)) : 0.0f;
+          }
+        }
+        if (KIND == KIND_TRAIN) dz[j * RS + r] = g;
+      }
+    }
+    if (KIND == KIND_TRAIN) {
+      __syncthreads();
+      // ---- backward
+      for (int l = L - 1; l >= 0; --l) {
+        const float* aT = smem + d.act_off[l];
+        const float* dzc = smem + d.dz_off[cur];
+        accumulate_dw(aT, dzc, d.dims[l], d.dims[l + 1], my_partial + d.w_off[l], my_partial + d.b_off[l], first);
+        if (l > 0) {
+          float* dzn = smem + d.dz_off[cur ^ 1];
+          // dA[k][r] = sum_j dz[j][r] * W[k][j] = sum_j dzT[j][r] * WT[j][k]; masked by relu'(A)
+          gemm_dispatch(dzc, WT + d.w_off[l], d.dims[l], d.dims[l + 1], d.dims[l],
+                        [&](int k, int r0, auto& acc) {
+                          constexpr int RT = sizeof(acc) / sizeof(float);
+#pragma unroll
+                          for (int i = 0; i < RT; ++i)
+                            dzn[k * RS + r0 + i] = aT[k * RS + r0 + i] > 0.0f ? acc[i] : 0.0f;
+                        });
+        }
+        __syncthreads();
+        cur ^= 1;
+      }
+      first = false;
+    } else {
+      __syncthreads();
+    }
+  }
+  if (KIND != KIND_PREDICT) {
+    float s = block_sum(loss_acc, smem + d.smem_floats - 32);
+    if (threadIdx.x == 0) my_partial[d.n_params] = s;
+  }
+}
+
+__global__ void __launch_bounds__(256)
+transpose_weights_kernel(const MlpDesc d, const float* __restrict__ params, float* __restrict__ WT) {
+  for (int l = 1; l < d.n_layers; ++l) {  // layer 0 never needs dX
+    const int K = d.dims[l], N = d.dims[l + 1];
+    const float* W = params + d.w_off[l];
+    float* T = WT + d.w_off[l];
+    for (int idx = blockIdx.x * 256 + threadIdx.x; idx < K * N; idx += gridDim.x * 256) {
+      int j = idx / K, k = idx - j * K;  // T[j][k] = W[k][j]
+      T[idx] = W[(size_t)k * N + j];
+    }
+  }
+}
+
+// out[i] = sum over active CTAs (in CTA order) of partial[c][i], i in [i0, i0+count)
+__global__ void __launch_bounds__(256)
+reduce_partials_kernel(const float* __restrict__ partials, size_t stride, int n_active, size_t i0,
+                       size_t count, float* __restrict__ out) {
+  size_t i = (size_t)blockIdx.x * 256 + threadIdx.x;
+  if (i >= count) return;
+  float s = 0.0f;
+  for (int c = 0; c < n_active; ++c) s += partials[(size_t)c * stride + i0 + i];
+  out[i] = s;
+}
+
+int grid_size() { return sm_count(); }
+
+template <int KIND>
+int launch_main(const MlpDesc& d, int loss, const float* params, const float* WT, const float* X,
+                const float* y, size_t n_rows, float* partials, float* yhat, cudaStream_t st) {
+  static bool attr_set = false;
+  size_t smem = (size_t)d.smem_floats * sizeof(float);
+  if (!attr_set) {
+    DLAS_CUDA(cudaFuncSetAttribute(mlp_simt_kernel<KIND>, cudaFuncAttributeMaxDynamicSharedMemorySize, 227 * 1024));
+    attr_set = true;
+  }
+  mlp_simt_kernel<KIND><<<grid_size(), NT, smem, st>>>(d, loss, params, WT, X, y, n_rows, partials, yhat);
+  DLAS_LAUNCH_CHECK();
+  return DLAS_OK;
+}
+
+}  // namespace
+
+// ---- entry points used by mlp_api.cu ---------------------------------------------------------
+size_t simt_workspace_bytes(const int* dims, int n_layers) {
+  MlpDesc d;
+  if (make_desc(dims, n_layers, d) != DLAS_OK) return 0;
+  return ((size_t)grid_size() * partial_stride(d.n_params) + (size_t)d.n_params) * sizeof(float);
+}
+
+int simt_grad(const int* dims, int n_layers, int loss, const float* params, const float* X, const float* y,
+              size_t n_rows, float* grad_sum, void* workspace, size_t workspace_bytes, cudaStream_t st) {
+  MlpDesc d;
+  int rc = make_desc(dims, n_layers, d);
+  if (rc != DLAS_OK) return rc;
+  size_t need = simt_workspace_bytes(dims, n_layers);
+  if (workspace == nullptr || workspace_bytes < need) {
+    set_error("mlp: workspace of %zu bytes given, %zu needed", workspace_bytes, need);
+    return DLAS_ERR_WORKSPACE;
+  }
+  if (n_rows == 0) {
+    DLAS_CUDA(cudaMemsetAsync(grad_sum, 0, ((size_t)d.n_params + 1) * sizeof(float), st));
+    return DLAS_OK;
+  }
+  float* partials = (float*)workspace;
+  float* WT = partials + (size_t)grid_size() * partial_stride(d.n_params);
+  transpose_weights_kernel<<<64, 256, 0, st>>>(d, params, WT);
+  DLAS_LAUNCH_CHECK();
+  int pi = prof_begin(DLAS_PROF_MLP_GRAD, st);
+  rc = launch_main<KIND_TRAIN>(d, loss, params, WT, X, y, n_rows, partials, nullptr, st);
+  prof_end(pi, st);
+  if (rc != DLAS_OK) return rc;
+  size_t n_tiles = (n_rows + R - 1) / R;
+  int n_active = (int)(n_tiles < (size_t)grid_size() ? n_tiles : (size_t)grid_size());
+  size_t count = (size_t)d.n_params + 1;
+  reduce_partials_kernel<<<(unsigned)((count + 255) / 256), 256, 0, st>>>(partials, partial_stride(d.n_params),
+                                                                        n_active, 0, count, grad_sum);
+  DLAS_LAUNCH_CHECK();
+  return DLAS_OK;
+}
+
+int simt_eval_loss(const int* dims, int n_layers, int loss, const float* params, const float* X,
+                   const float* y, size_t n_rows, float* loss_sum, void* workspace, size_t workspace_bytes,
+                   cudaStream_t st) {
+  MlpDesc d;
+  int rc = make_desc(dims, n_layers, d);
+  if (rc != DLAS_OK) return rc;
+  size_t need = simt_workspace_bytes(dims, n_layers);
+  if (workspace == nullptr || workspace_bytes < need) {
+    set_error("mlp: workspace of %zu bytes given, %zu needed", workspace_bytes, need);
+    return DLAS_ERR_WORKSPACE;
+  }
+  if (n_rows == 0) {
+    DLAS_CUDA(cudaMemsetAsync(loss_sum, 0, sizeof(float), st));
+    return DLAS_OK;
+  }
+  float* partials = (float*)workspace;
+  rc = launch_main<KIND_EVAL>(d, loss, params, nullptr, X, y, n_rows, partials, nullptr, st);
+  if (rc != DLAS_OK) return rc;
+  // CTAs without a tile still write their (zero) loss partial, so all CTAs are summed
+  reduce_partials_kernel<<<1, 256, 0, st>>>(partials, partial_stride(d.n_params), grid_size(),
+                                            (size_t)d.n_params, 1, loss_sum);
+  DLAS_LAUNCH_CHECK();
+  return DLAS_OK;
+}
+
+int simt_predict(const int* dims, int n_layers, const float* params, const float* X, size_t n_rows,
+                 float* yhat, cudaStream_t st) {
+  MlpDesc d;
+  int rc = make_desc(dims, n_layers, d);
+  if (rc != DLAS_OK) return rc;
+  if (n_rows == 0) return DLAS_OK;
+  return launch_main<KIND_PREDICT>(d, DLAS_LOSS_MSE, params, nullptr, X, nullptr, n_rows, nullptr, yhat, st);
+}
+
+}  // namespace dlas

@@ -1,0 +1,344 @@
+"""Host-side mirror of the Keras call sequence the reference scripts use (cnn.py:110-132):
+
+    model = Sequential(); model.add(Dense(in, out, activation="relu")); ...
+    model.compile(loss=mae_clip, optimizer=SGD(lr=0.001, momentum=0.99, decay=1e-6, nesterov=True))
+    model.fit(X, y, validation_data=(Xv, yv), verbose=2, callbacks=[EarlyStopping(...),
+              ModelCheckpoint(path, save_best_only=True)], nb_epoch=1000, batch_size=20)
+    model.test_on_batch(Xt, yt)
+
+Same names, argument meaning and defaults; everything numeric runs in libdlas_b200.so on the GPU.
+Data-parallel training (one process per GPU, torch.distributed): each rank passes ITS shard of
+every global batch; gradient sums are all-reduced once per step in a single flat bucket and the
+optimiser sees the global-batch mean."""
+from __future__ import annotations
+
+import os
+import time
+
+import numpy as np
+import torch
+
+from . import _lib, hashing, ops, parallel
+
+
+# ---- losses / optimisers / layers / callbacks (Keras names) -----------------------------------
+def mae_clip(y_true=None, y_pred=None):
+    """cnn.py:29-32: mean(clip(|y_true - y_pred|, 0, 6), axis=-1).  Passed to compile(loss=mae_clip);
+    the arithmetic is the kernel's loss epilogue, this object only selects it."""
+    raise RuntimeError("mae_clip is evaluated inside the CUDA kernels; pass it to compile(loss=mae_clip)")
+
+
+_LOSSES = {"mse": _lib.LOSS_MSE, "mean_squared_error": _lib.LOSS_MSE, "mae_clip": _lib.LOSS_MAE_CLIP,
+           mae_clip: _lib.LOSS_MAE_CLIP}
+
+
+class SGD:
+    """keras.optimizers.SGD as called at cnn.py:117."""
+
+    def __init__(self, lr=0.01, momentum=0.0, decay=0.0, nesterov=False):
+        self.lr, self.momentum, self.decay, self.nesterov = lr, momentum, decay, nesterov
+
+    def cfg(self):
+        return ops.make_opt_cfg(_lib.OPT_SGD, self.lr, self.momentum, self.decay, self.nesterov)
+
+
+class Adam:
+    """keras.optimizers.Adam (epsilon added outside the bias-corrected square root)."""
+
+    def __init__(self, lr=0.001, beta_1=0.9, beta_2=0.999, epsilon=1e-7, decay=0.0):
+        self.lr, self.beta_1, self.beta_2, self.epsilon, self.decay = lr, beta_1, beta_2, epsilon, decay
+
+    def cfg(self):
+        return ops.make_opt_cfg(_lib.OPT_ADAM, self.lr, 0.0, self.decay, False, self.beta_1, self.beta_2, self.epsilon)
+
+
+class Dense:
+    """Dense(input_dim, output_dim) -- the Keras-0.x positional form of cnn.py:114 -- or
+    Dense(output_dim, input_dim=...) / Dense(units) after a first layer."""
+
+    def __init__(self, *args, activation=None, input_dim=None):
+        if len(args) == 2:
+            self.input_dim, self.output_dim = int(args[0]), int(args[1])
+        elif len(args) == 1:
+            self.input_dim, self.output_dim = (None if input_dim is None else int(input_dim)), int(args[0])
+        else:
+            raise TypeError("Dense(input_dim, output_dim) or Dense(output_dim, input_dim=...)")
+        if activation not in (None, "linear", "relu"):
+            raise NotImplementedError("activation %r: the kernels implement relu (hidden) and linear (output)" % (activation,))
+        self.activation = "linear" if activation is None else activation
+
+
+class EarlyStopping:
+    """keras.callbacks.EarlyStopping(monitor='val_loss', patience=10), cnn.py:121."""
+
+    def __init__(self, monitor="val_loss", patience=0):
+        self.monitor, self.patience = monitor, patience
+        self.best, self.wait, self.stopped_epoch = np.inf, 0, None
+
+    def on_epoch_end(self, model, epoch, logs):
+        cur = logs.get(self.monitor)
+        if cur is None:
+            return False
+        if cur < self.best:
+            self.best, self.wait = cur, 0
+            return False
+        self.wait += 1
+        if self.wait >= self.patience:
+            self.stopped_epoch = epoch
+            return True
+        return False
+
+
+class ModelCheckpoint:
+    """keras.callbacks.ModelCheckpoint(path, save_best_only=True), cnn.py:122.  File format: a
+    torch.save dict {dims, params} (the reference's HDF5 writer is not available)."""
+
+    def __init__(self, filepath, monitor="val_loss", save_best_only=False):
+        self.filepath, self.monitor, self.save_best_only = filepath, monitor, save_best_only
+        self.best = np.inf
+
+    def on_epoch_end(self, model, epoch, logs):
+        cur = logs.get(self.monitor)
+        if self.save_best_only:
+            if cur is None or not cur < self.best:
+                return False
+            self.best = cur
+        if model.rank == 0:
+            model.save_weights(self.filepath)
+        return False
+
+
+# ---- the model -------------------------------------------------------------------------------
+class Sequential:
+    def __init__(self, layers=None, mode="fp32", seed=ops.BASE_SEED, device=None):
+        self.layers = []
+        self.mode = {"fp32": _lib.MODE_FP32, "tc": _lib.MODE_TC}[mode] if isinstance(mode, str) else int(mode)
+        self.seed = seed
+        self.device = device
+        self.params = None
+        self.loss = None
+        self.iterations = 0
+        for l in layers or []:
+            self.add(l)
+
+    # -- build (cnn.py:110-114)
+    def add(self, layer):
+        if not isinstance(layer, Dense):
+            raise NotImplementedError("only Dense layers are on the B200 hot path")
+        if layer.input_dim is None:
+            if not self.layers:
+                raise ValueError("first layer needs input_dim")
+            layer.input_dim = self.layers[-1].output_dim
+        elif self.layers and layer.input_dim != self.layers[-1].output_dim:
+            raise ValueError("layer input_dim %d != previous output_dim %d" % (layer.input_dim, self.layers[-1].output_dim))
+        self.layers.append(layer)
+
+    @property
+    def dims(self):
+        return [self.layers[0].input_dim] + [l.output_dim for l in self.layers]
+
+    # -- compile (cnn.py:118)
+    def compile(self, loss="mse", optimizer=None):
+        if not self.layers:
+            raise ValueError("add layers before compile")
+        for l in self.layers[:-1]:
+            if l.activation != "relu":
+                raise NotImplementedError("hidden layers are ReLU on this path (cnn.py:111)")
+        if self.layers[-1].activation != "linear":
+            raise NotImplementedError("the output layer is linear on this path (cnn.py:114)")
+        if loss not in _LOSSES:
+            raise ValueError("unknown loss %r" % (loss,))
+        self.loss = _LOSSES[loss]
+        self.optimizer = optimizer if optimizer is not None else SGD()
+        self.cfg = self.optimizer.cfg()
+        _lib.load()  # fail here, loudly, if the CUDA extension is missing
+        if not torch.cuda.is_available():
+            raise RuntimeError("dlas needs a B200 GPU: there is no CPU path")
+        self.device = torch.device(self.device if self.device is not None else "cuda:%d" % torch.cuda.current_device())
+        dims = self.dims
+        if not ops.mlp_mode_supported(dims, self.mode):
+            raise _lib.DlasError(-5, "layer widths %s are not supported in mode %d" % (dims, self.mode))
+        n = ops.mlp_n_params(dims)
+        self.n_params = n
+        if self.params is None:
+            self.params = torch.from_numpy(self._glorot(dims)).to(self.device)
+        self.m = torch.zeros(n, dtype=torch.float32, device=self.device)
+        self.v = torch.zeros(n, dtype=torch.float32, device=self.device)
+        self.grad_sum = torch.zeros(n + 1, dtype=torch.float32, device=self.device)  # [n] = loss sum
+        self.workspace = ops.mlp_workspace(dims, self.mode, self.device)
+        self.iterations = 0
+        self.rank, self.world = parallel.world_info()
+        return self
+
+    def _glorot(self, dims):
+        """Keras Dense default: glorot_uniform kernel, zero bias (drawn from the counter hash)."""
+        p = np.zeros(sum(a * b + b for a, b in zip(dims[:-1], dims[1:])), dtype=np.float32)
+        o = 0
+        for li, (a, b) in enumerate(zip(dims[:-1], dims[1:])):
+            lim = np.sqrt(6.0 / (a + b))
+            u = hashing.uniform(self.seed, 100 + li, a * b).astype(np.float64)
+            p[o:o + a * b] = ((2.0 * u - 1.0) * lim).astype(np.float32)
+            o += a * b + b
+        return p
+
+    def set_weights_flat(self, flat):
+        t = torch.as_tensor(np.asarray(flat, dtype=np.float32))
+        if self.params is None:
+            self.params = t.to(self.device if self.device is not None else "cuda")
+        else:
+            self.params.copy_(t)
+
+    def get_weights_flat(self):
+        return self.params.detach().cpu().numpy()
+
+    def save_weights(self, path):
+        d = os.path.dirname(path)
+        if d:
+            os.makedirs(d, exist_ok=True)
+        torch.save({"dims": self.dims, "params": self.params.detach().cpu()}, path)
+
+    def load_weights(self, path):
+        ck = torch.load(path)
+        if list(ck["dims"]) != self.dims:
+            raise ValueError("checkpoint dims %s != model dims %s" % (ck["dims"], self.dims))
+        self.set_weights_flat(ck["params"].numpy())
+
+    # -- helpers
+    def _to_dev(self, a, cols):
+        if isinstance(a, torch.Tensor):
+            t = a.to(device=self.device, dtype=torch.float32)
+        else:
+            t = torch.as_tensor(np.asarray(a, dtype=np.float32), device=self.device)
+        return t.reshape(-1, cols).contiguous()
+
+    def train_on_batch(self, X, y, global_rows=None):
+        """One optimiser step on this rank's shard (X, y) of one global batch; returns the device
+        scalar holding the global batch-mean loss."""
+        dims = self.dims
+        rows = global_rows if global_rows is not None else X.shape[0] * self.world
+        loss_out = torch.empty(1, dtype=torch.float32, device=self.device)
+        parallel.dp_step(
+            lambda: ops.mlp_grad(dims, self.loss, self.mode, self.params, X, y, self.grad_sum, self.workspace),
+            lambda scale: ops.opt_step(self.cfg, self.params, self.m, self.v, self.grad_sum, scale,
+                                       self.iterations, loss_out),
+            self.grad_sum, rows)
+        self.iterations += 1
+        return loss_out
+
+    # -- fit (cnn.py:127-128)
+    def fit(self, x=None, y=None, validation_data=None, verbose=2, callbacks=None, nb_epoch=None, epochs=None,
+            batch_size=32, shuffle=True, log=print):
+        if self.loss is None:
+            raise RuntimeError("compile() the model before fit()")
+        n_epochs = nb_epoch if nb_epoch is not None else (epochs if epochs is not None else 1)
+        dims = self.dims
+        X = self._to_dev(x, dims[0])
+        Y = self._to_dev(y, dims[-1])
+        if validation_data is not None:
+            Xv, Yv = self._to_dev(validation_data[0], dims[0]), self._to_dev(validation_data[1], dims[-1])
+        local_batch = batch_size // self.world
+        if local_batch < 1 or local_batch * self.world != batch_size:
+            raise ValueError("batch_size %d must be a positive multiple of the world size %d" % (batch_size, self.world))
+        n_local = X.shape[0]
+        n_full = n_local // local_batch
+        rem = n_local - n_full * local_batch
+        history = {"loss": [], "val_loss": []}
+        callbacks = callbacks or []
+        for epoch in range(n_epochs):
+            t0 = time.time()
+            order = hashing.batch_order(self.seed, epoch, n_full) if shuffle else np.arange(n_full, dtype=np.int64)
+            losses = torch.empty(n_full + (1 if rem else 0), dtype=torch.float32, device=self.device)
+            if self.world == 1:
+                if n_full:
+                    ops.mlp_fit_steps(dims, self.loss, self.mode, self.cfg, self.params, self.m, self.v, X, Y,
+                                      local_batch, n_full, self.iterations, losses, self.grad_sum, self.workspace,
+                                      batch_order=order)
+                    self.iterations += n_full
+                if rem:  # Keras also trains on the ragged last batch
+                    Xr, Yr = X[n_full * local_batch:], Y[n_full * local_batch:]
+                    ops.mlp_fit_steps(dims, self.loss, self.mode, self.cfg, self.params, self.m, self.v, Xr, Yr,
+                                      rem, 1, self.iterations, losses[n_full:], self.grad_sum, self.workspace)
+                    self.iterations += 1
+            else:
+                for s in range(n_full):
+                    b = int(order[s])
+                    lo = self.train_on_batch(X[b * local_batch:(b + 1) * local_batch], Y[b * local_batch:(b + 1) * local_batch],
+                                             global_rows=batch_size)
+                    losses[s:s + 1].copy_(lo)
+                if rem:
+                    lo = self.train_on_batch(X[n_full * local_batch:], Y[n_full * local_batch:], global_rows=rem * self.world)
+                    losses[n_full:].copy_(lo)
+            # Keras reports the sample-weighted mean of the batch losses
+            w = torch.full_like(losses, float(local_batch))
+            if rem:
+                w[-1] = float(rem)
+            logs = {"loss": float((losses * w).sum().item() / max(1, n_local))}
+            if validation_data is not None:
+                logs["val_loss"] = self.evaluate(Xv, Yv)
+            history["loss"].append(logs["loss"])
+            history["val_loss"].append(logs.get("val_loss"))
+            if verbose and self.rank == 0:
+                msg = "Epoch %d/%d - %.1fs - loss: %.6f" % (epoch + 1, n_epochs, time.time() - t0, logs["loss"])
+                if "val_loss" in logs:
+                    msg += " - val_loss: %.6f" % logs["val_loss"]
+                log(msg)
+            stop = False
+            for cb in callbacks:
+                stop = bool(cb.on_epoch_end(self, epoch, logs)) or stop
+            if stop:
+                break
+        return history
+
+    def fit_host(self, x_host, y_host, batch_size, n_steps, losses_host=None, first_batch=0):
+        """Train `n_steps` steps streaming batches from (pinned) HOST tensors: the host->device copy
+        of step s+1 runs on a copy stream under the kernels of step s (two device buffers); each
+        step's batch-mean loss is read back into `losses_host` (pinned, n_steps floats).  With
+        torch.distributed, x_host/y_host hold this rank's shard and batch_size is the GLOBAL batch.
+        Returns losses_host; the caller synchronises."""
+        dims = self.dims
+        lb = batch_size // self.world
+        n_batches = x_host.shape[0] // lb
+        if losses_host is None:
+            losses_host = torch.empty(n_steps, dtype=torch.float32).pin_memory()
+        if not hasattr(self, "_hb") or self._hb[0][0].shape[0] != lb:
+            self._hb = [(torch.empty((lb, dims[0]), dtype=torch.float32, device=self.device),
+                         torch.empty((lb, dims[-1]), dtype=torch.float32, device=self.device)) for _ in range(2)]
+            self._copy_stream = torch.cuda.Stream(device=self.device)
+            self._ready = [torch.cuda.Event() for _ in range(2)]
+            self._free = [torch.cuda.Event() for _ in range(2)]
+        main = torch.cuda.current_stream()
+        for ev in self._free:
+            ev.record(main)
+        yv = y_host.reshape(-1, dims[-1])
+        for s in range(n_steps):
+            b = (first_batch + s) % n_batches
+            k = s & 1
+            with torch.cuda.stream(self._copy_stream):
+                self._copy_stream.wait_event(self._free[k])
+                self._hb[k][0].copy_(x_host[b * lb:(b + 1) * lb], non_blocking=True)
+                self._hb[k][1].copy_(yv[b * lb:(b + 1) * lb], non_blocking=True)
+                self._ready[k].record(self._copy_stream)
+            main.wait_event(self._ready[k])
+            lo = self.train_on_batch(self._hb[k][0], self._hb[k][1], global_rows=batch_size)
+            losses_host[s:s + 1].copy_(lo, non_blocking=True)
+            self._free[k].record(main)
+        return losses_host
+
+    # -- inference (cnn.py:132)
+    def predict(self, x):
+        X = self._to_dev(x, self.dims[0])
+        return ops.mlp_predict(self.dims, self.mode, self.params, X)
+
+    def evaluate(self, x, y):
+        """Mean loss over (x, y); with torch.distributed the mean is over all ranks' rows."""
+        X = self._to_dev(x, self.dims[0])
+        Y = self._to_dev(y, self.dims[-1])
+        ls = ops.mlp_eval_loss(self.dims, self.loss, self.mode, self.params, X, Y, self.workspace)
+        cnt = torch.tensor([float(X.shape[0])], dtype=torch.float32, device=self.device)
+        if self.world > 1:
+            pack = torch.cat([ls, cnt])
+            torch.distributed.all_reduce(pack)
+            ls, cnt = pack[:1], pack[1:]
+        return float(ls.item() / max(1.0, cnt.item()))
+
+    test_on_batch = evaluate

@@ -1,0 +1,152 @@
+"""Thin tensor-level wrappers over the C ABI.  PyTorch is used for device memory and streams only;
+every computation below happens inside libdlas_b200.so."""
+from __future__ import annotations
+
+import ctypes as C
+
+import torch
+
+from . import _lib
+from ._lib import check, int_array, ptr, stream_ptr
+
+BASE_SEED = 20261106
+
+
+def _dev_f32(t, name):
+    if not (isinstance(t, torch.Tensor) and t.is_cuda and t.dtype == torch.float32 and t.is_contiguous()):
+        raise TypeError("%s must be a contiguous float32 CUDA tensor" % name)
+    return t
+
+
+# ---- Gilbert --------------------------------------------------------------------------------
+def gilbert(P, S, R, out=None, variant=_lib.GILBERT_POLY):
+    """q = P * S^1.89 / (435 * R^0.546), element-wise over fp32 CUDA vectors (Readme.md:7-8)."""
+    _dev_f32(P, "P"), _dev_f32(S, "S"), _dev_f32(R, "R")
+    if not (P.numel() == S.numel() == R.numel()):
+        raise ValueError("P, S, R must have the same number of elements")
+    if out is None:
+        out = torch.empty_like(P)
+    _dev_f32(out, "out")
+    check(_lib.load().dlas_gilbert_f32(ptr(P), ptr(S), ptr(R), ptr(out), P.numel(), int(variant), stream_ptr()))
+    return out
+
+
+# ---- synthetic inputs -------------------------------------------------------------------------
+def synth_gilbert(n, seed=BASE_SEED, start=0, device="cuda"):
+    P, S, R = (torch.empty(n, dtype=torch.float32, device=device) for _ in range(3))
+    check(_lib.load().dlas_synth_gilbert_f32(ptr(P), ptr(S), ptr(R), seed, start, n, stream_ptr()))
+    return P, S, R
+
+
+def synth_rows(n_rows, n_features, seed=BASE_SEED, start=0, device="cuda", out=None):
+    if out is None:
+        X = torch.empty((n_rows, n_features), dtype=torch.float32, device=device)
+        y = torch.empty((n_rows, 1), dtype=torch.float32, device=device)
+    else:
+        X, y = out
+    check(_lib.load().dlas_synth_rows_f32(ptr(X), ptr(y), seed, start, n_rows, n_features, stream_ptr()))
+    return X, y
+
+
+def synth_series(n_seq, T, d_in, seed=BASE_SEED, start=0, device="cuda"):
+    X = torch.empty((n_seq, T, d_in), dtype=torch.float32, device=device)
+    y = torch.empty((n_seq, 1), dtype=torch.float32, device=device)
+    check(_lib.load().dlas_synth_series_f32(ptr(X), ptr(y), seed, start, n_seq, T, d_in, stream_ptr()))
+    return X, y
+
+
+def split_codes(n, seed=BASE_SEED, start=0, device="cuda"):
+    """cnn.py:68 randomSplit([0.64, 0.16, 0.2]) -> int8 codes 0/1/2 per row."""
+    code = torch.empty(n, dtype=torch.int8, device=device)
+    check(_lib.load().dlas_split_codes(ptr(code), seed, start, n, stream_ptr()))
+    return code
+
+
+def lag_windows(series, n_lags):
+    """(n, F) raw series -> (n - n_lags + 1, n_lags * F) lag-major windows (dynamic ANN input)."""
+    _dev_f32(series, "series")
+    n, f = series.shape
+    if n < n_lags:
+        return torch.empty((0, n_lags * f), dtype=torch.float32, device=series.device)
+    out = torch.empty((n - n_lags + 1, n_lags * f), dtype=torch.float32, device=series.device)
+    check(_lib.load().dlas_lag_windows_f32(ptr(series), n, f, n_lags, ptr(out), stream_ptr()))
+    return out
+
+
+# ---- MLP ------------------------------------------------------------------------------------
+def mlp_n_params(dims):
+    return int(_lib.load().dlas_mlp_n_params(int_array(dims), len(dims) - 1))
+
+
+def mlp_mode_supported(dims, mode):
+    return bool(_lib.load().dlas_mlp_mode_supported(int_array(dims), len(dims) - 1, int(mode)))
+
+
+def mlp_workspace(dims, mode=_lib.MODE_FP32, device="cuda"):
+    nbytes = int(_lib.load().dlas_mlp_workspace_bytes(int_array(dims), len(dims) - 1, int(mode)))
+    if nbytes == 0:
+        raise _lib.DlasError(-5, "layer widths %s are not supported in mode %d" % (list(dims), mode))
+    return torch.empty(nbytes, dtype=torch.uint8, device=device)
+
+
+def make_opt_cfg(kind, lr, momentum=0.0, decay=0.0, nesterov=False, beta1=0.9, beta2=0.999, eps=1e-7):
+    return _lib.OptCfg(int(kind), float(lr), float(momentum), float(decay), int(bool(nesterov)),
+                       float(beta1), float(beta2), float(eps))
+
+
+def mlp_grad(dims, loss, mode, params, X, y, grad_sum, workspace, n_rows=None):
+    n_rows = X.shape[0] if n_rows is None else n_rows
+    check(_lib.load().dlas_mlp_grad(int_array(dims), len(dims) - 1, int(loss), int(mode), ptr(params), ptr(X),
+                                    ptr(y), n_rows, ptr(grad_sum), ptr(workspace), workspace.numel(),
+                                    stream_ptr()))
+    return grad_sum
+
+
+def opt_step(cfg, params, m, v, grad_sum, grad_scale, iteration, loss_out=None):
+    check(_lib.load().dlas_opt_step(C.byref(cfg), ptr(params), ptr(m), ptr(v), ptr(grad_sum), params.numel(),
+                                    float(grad_scale), int(iteration), ptr(loss_out), stream_ptr()))
+
+
+def mlp_fit_steps(dims, loss, mode, cfg, params, m, v, X, y, batch, n_steps, iteration0, step_losses, grad_sum,
+                  workspace, batch_order=None, first_batch=0):
+    order = None
+    if batch_order is not None:
+        order = (C.c_int64 * len(batch_order))(*[int(b) for b in batch_order])
+    check(_lib.load().dlas_mlp_fit_steps(int_array(dims), len(dims) - 1, int(loss), int(mode), C.byref(cfg),
+                                         ptr(params), ptr(m), ptr(v), ptr(X), ptr(y), X.shape[0], int(batch),
+                                         order, int(first_batch), int(n_steps), int(iteration0),
+                                         ptr(step_losses), ptr(grad_sum), ptr(workspace), workspace.numel(),
+                                         stream_ptr()))
+
+
+def mlp_predict(dims, mode, params, X, out=None):
+    _dev_f32(X, "X")
+    if out is None:
+        out = torch.empty((X.shape[0], dims[-1]), dtype=torch.float32, device=X.device)
+    check(_lib.load().dlas_mlp_predict(int_array(dims), len(dims) - 1, int(mode), ptr(params), ptr(X), X.shape[0],
+                                       ptr(out), stream_ptr()))
+    return out
+
+
+def mlp_eval_loss(dims, loss, mode, params, X, y, workspace, loss_sum=None):
+    if loss_sum is None:
+        loss_sum = torch.empty(1, dtype=torch.float32, device=X.device)
+    check(_lib.load().dlas_mlp_eval_loss(int_array(dims), len(dims) - 1, int(loss), int(mode), ptr(params), ptr(X),
+                                         ptr(y), X.shape[0], ptr(loss_sum), ptr(workspace), workspace.numel(),
+                                         stream_ptr()))
+    return loss_sum
+
+
+# ---- kernel timing (bench.py roofline) --------------------------------------------------------
+PROF_GILBERT, PROF_MLP_GRAD = 0, 1
+
+
+def prof_enable(on=True):
+    check(_lib.load().dlas_prof_enable(int(bool(on))))
+
+
+def prof_read(slot):
+    """(summed kernel milliseconds, launches) recorded for `slot` since the last read."""
+    ms, cnt = C.c_float(0.0), C.c_int(0)
+    check(_lib.load().dlas_prof_read(int(slot), C.byref(ms), C.byref(cnt)))
+    return float(ms.value), int(cnt.value)

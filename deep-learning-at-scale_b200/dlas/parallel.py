@@ -1,0 +1,50 @@
+"""Data-parallel plumbing (one process per GPU, torch.distributed; NCCL over NVLink on B200, gloo
+in the CPU tests).  Replaces the Spark-driver averaging that BASELINE.json asks for (the snapshot
+has none): rows of every global batch are split into `world` contiguous
+slices, each rank computes gradient SUMS over its slice, one all-reduce of ONE flat bucket
+(n_params gradients + the loss sum) per step, then every rank applies the same update with
+grad_scale = 1/global_batch.  The path has no other collective."""
+from __future__ import annotations
+
+import torch
+import torch.distributed as dist
+
+
+def world_info():
+    if dist.is_available() and dist.is_initialized():
+        return dist.get_rank(), dist.get_world_size()
+    return 0, 1
+
+
+def shard_bounds(global_batch, rank, world):
+    """Rows [lo, hi) of a global batch that rank `rank` owns; the union over ranks is the batch."""
+    if global_batch % world:
+        raise ValueError("global batch %d is not a multiple of the world size %d" % (global_batch, world))
+    per = global_batch // world
+    return rank * per, (rank + 1) * per
+
+
+def local_rows(n_rows, global_batch, rank, world):
+    """Index tensor of the rows of a dataset (n_rows, whole batches only) that belong to `rank`
+    when every consecutive block of `global_batch` rows is one step's batch."""
+    lo, hi = shard_bounds(global_batch, rank, world)
+    n_batches = n_rows // global_batch
+    base = torch.arange(n_batches, dtype=torch.int64)[:, None] * global_batch
+    return (base + torch.arange(lo, hi, dtype=torch.int64)[None, :]).reshape(-1)
+
+
+def allreduce_sum_(bucket):
+    """In-place SUM all-reduce of the flat bucket (no-op for a single process)."""
+    _, world = world_info()
+    if world > 1:
+        dist.all_reduce(bucket, op=dist.ReduceOp.SUM)
+    return bucket
+
+
+def dp_step(grad_fn, step_fn, bucket, global_rows):
+    """One synchronous data-parallel step: grad_fn() fills `bucket` with this rank's sums,
+    the bucket is all-reduced, step_fn(1/global_rows) applies the update.  Returns the bucket."""
+    grad_fn()
+    allreduce_sum_(bucket)
+    step_fn(1.0 / float(global_rows))
+    return bucket

@@ -1,0 +1,138 @@
+/* dlas_b200.h -- C ABI of libdlas_b200.so: the B200 (sm_100a) data-parallel hot path of
+ * OmarZOS/deep-learning-at-scale (mini-batch training / inference of the flow regressors and the
+ * Gilbert physical baseline).
+ *
+ * The reference has NO native interface: its boundary is the Keras call sequence in
+ * "Artificial intelligence models/Static neural network models/cnn.py" (cited below as cnn.py).
+ * Each entry point names the reference lines it stands in for.  All pointers are DEVICE pointers
+ * unless a name ends in _host; `stream` is a cudaStream_t passed as void* (NULL = default
+ * stream).  Functions are stream-ordered and asynchronous; none of them allocates device memory
+ * (scratch is passed in by the caller).  Return 0 on success, a negative DLAS_ERR_* otherwise;
+ * the message is available from dlas_last_error() (thread-local).  There is no CPU fallback: on a
+ * device that is not compute capability 10.x every compute entry point returns
+ * DLAS_ERR_UNSUPPORTED_DEVICE.
+ */
+#ifndef DLAS_B200_H
+#define DLAS_B200_H
+
+#include <stddef.h>
+#include <stdint.h>
+
+#ifdef __cplusplus
+extern "C" {
+#endif
+
+#define DLAS_OK 0
+#define DLAS_ERR_INVALID (-1)
+#define DLAS_ERR_CUDA (-2)
+#define DLAS_ERR_UNSUPPORTED_DEVICE (-3)
+#define DLAS_ERR_WORKSPACE (-4)
+#define DLAS_ERR_UNSUPPORTED_SHAPE (-5)
+
+/* losses: cnn.py:29-32 (mae_clip); MSE from BASELINE.json config 1 */
+#define DLAS_LOSS_MSE 0
+#define DLAS_LOSS_MAE_CLIP 1
+/* optimisers: cnn.py:117 (SGD lr/momentum/decay/nesterov); Adam from BASELINE.json north_star */
+#define DLAS_OPT_SGD 0
+#define DLAS_OPT_ADAM 1
+/* arithmetic mode of the MLP kernels */
+#define DLAS_MODE_FP32 0   /* CUDA-core fp32, any layer widths                                   */
+#define DLAS_MODE_TC 1     /* tcgen05 tensor cores: fp16 operands (10-bit mantissa, as TF32),
+                              fp32 accumulation in TMEM; fixed shapes, see dlas_mlp_mode_supported */
+/* Gilbert kernel variants (same results within the stated 1e-6; differ in instruction mix) */
+#define DLAS_GILBERT_POLY 0  /* polynomial log2 for all three inputs                              */
+#define DLAS_GILBERT_MUFU 7  /* bit i set: input i (P,S,R) takes its mantissa log2 from MUFU.LG2  */
+
+typedef struct dlas_opt_cfg {
+  int32_t kind;      /* DLAS_OPT_*                                  */
+  float lr;          /* cnn.py:117 lr=0.001                          */
+  float momentum;    /* cnn.py:117 momentum=0.99                     */
+  float decay;       /* cnn.py:117 decay=1e-6 (lr_t = lr/(1+decay*it)) */
+  int32_t nesterov;  /* cnn.py:117 nesterov=True                     */
+  float beta1, beta2, eps; /* Adam */
+} dlas_opt_cfg;
+
+/* ---- library ---------------------------------------------------------------------------- */
+int dlas_version(void);
+const char* dlas_last_error(void);
+/* 0 if the current device is a B200-class (cc 10.x) GPU, DLAS_ERR_UNSUPPORTED_DEVICE otherwise. */
+int dlas_device_check(void);
+/* number of SMs of the current device (grid sizing is a multiple of it) */
+int dlas_sm_count(void);
+
+/* Kernel timing for the benchmark (no reference counterpart; cnn.py:126-129 only takes wall-clock
+ * time around fit).  While enabled, the dominant kernel of each entry point is bracketed by CUDA
+ * events on its own stream.  Slots: 0 = Gilbert kernel, 1 = MLP forward/backward kernel.
+ * dlas_prof_read synchronises, returns the summed milliseconds and the launch count of a slot
+ * (host pointers) and clears it. */
+#define DLAS_PROF_GILBERT 0
+#define DLAS_PROF_MLP_GRAD 1
+int dlas_prof_enable(int on);
+int dlas_prof_read(int slot, float* ms_sum_host, int* count_host);
+
+/* ---- Gilbert's equation: q = P*S^1.89/(435*R^0.546) ---------------------------------------
+ * Replaces the "Physical model" script named at Readme.md:7-8 (no code in the snapshot; formula from
+ * BASELINE.json).  SoA fp32 arrays of n rows; 16 algorithmic bytes per row.  <=1e-6 relative to
+ * the fp64 formula on the fp32 inputs for positive finite normal inputs; P==0 gives 0;
+ * negative, NaN, infinite or subnormal inputs take an IEEE powf slow path. */
+int dlas_gilbert_f32(const float* P, const float* S, const float* R, float* q, size_t n,
+                     int variant, void* stream);
+
+/* ---- synthetic inputs (stand in for the Spark CSV ingest cnn.py:49-103) ------ */
+int dlas_synth_gilbert_f32(float* P, float* S, float* R, uint64_t seed, uint64_t start, size_t n,
+                           void* stream);
+int dlas_synth_rows_f32(float* X, float* y, uint64_t seed, uint64_t start, size_t n_rows,
+                        int n_features, void* stream);
+int dlas_synth_series_f32(float* X, float* y, uint64_t seed, uint64_t start, size_t n_seq, int T,
+                          int d_in, void* stream);
+/* cnn.py:68 randomSplit([0.64,0.16,0.2]): code[i] = 0 train / 1 validation / 2 test for row start+i */
+int dlas_split_codes(int8_t* code, uint64_t seed, uint64_t start, size_t n, void* stream);
+/* dynamic ANN (Readme.md:19): out[i] = rows i..i+n_lags-1 of series (n_rows, n_features) flattened
+ * lag-major; writes n_rows-n_lags+1 windows. */
+int dlas_lag_windows_f32(const float* series, size_t n_rows, int n_features, int n_lags, float* out,
+                         void* stream);
+
+/* ---- MLP (static / dynamic ANN): Sequential of Dense layers, cnn.py:110-118 ---------------
+ * dims[0..n_layers] are the layer widths (n_layers Dense layers); hidden ReLU, linear output.
+ * Flat fp32 parameter vector: per layer W[in][out] row-major then b[out]. */
+size_t dlas_mlp_n_params(const int* dims, int n_layers);
+int dlas_mlp_mode_supported(const int* dims, int n_layers, int mode);
+/* bytes of device scratch dlas_mlp_grad / dlas_mlp_fit_steps need for these shapes and mode */
+size_t dlas_mlp_workspace_bytes(const int* dims, int n_layers, int mode);
+
+/* Forward + loss + backward over n_rows rows: the body of one `model.fit` batch, cnn.py:127-128,
+ * without the optimiser update.  Writes grad_sum[0..n_params) = SUM over rows of per-row
+ * gradients (no 1/batch factor) and grad_sum[n_params] = SUM of per-row losses, so that
+ * data-parallel shards can be added before the step.  Deterministic reduction order. */
+int dlas_mlp_grad(const int* dims, int n_layers, int loss, int mode, const float* params,
+                  const float* X, const float* y, size_t n_rows, float* grad_sum, void* workspace,
+                  size_t workspace_bytes, void* stream);
+
+/* Optimiser update (cnn.py:117 SGD; Adam): g = grad_sum*grad_scale; `iteration` counts batches
+ * already applied (Keras `iterations`).  m is the SGD velocity / Adam first moment, v the Adam
+ * second moment (ignored for SGD).  If loss_out != NULL writes *loss_out = grad_sum[n]*grad_scale. */
+int dlas_opt_step(const dlas_opt_cfg* cfg, float* params, float* m, float* v, const float* grad_sum,
+                  size_t n, float grad_scale, uint64_t iteration, float* loss_out, void* stream);
+
+/* n_steps consecutive single-GPU mini-batch steps (the `model.fit` inner loop, cnn.py:127-128):
+ * step s uses rows [b*batch, (b+1)*batch) with b = batch_order_host ? batch_order_host[s]
+ * : first_batch + s.  step_losses (device, n_steps floats, may be NULL) receives the batch-mean
+ * loss of each step.  iteration0 = batches applied before this call. */
+int dlas_mlp_fit_steps(const int* dims, int n_layers, int loss, int mode, const dlas_opt_cfg* cfg,
+                       float* params, float* m, float* v, const float* X, const float* y,
+                       size_t n_rows, int batch, const int64_t* batch_order_host,
+                       int64_t first_batch, int n_steps, uint64_t iteration0, float* step_losses,
+                       float* grad_sum, void* workspace, size_t workspace_bytes, void* stream);
+
+/* Inference (model.predict / test_on_batch, cnn.py:132): yhat (n_rows, dims[n_layers]). */
+int dlas_mlp_predict(const int* dims, int n_layers, int mode, const float* params, const float* X,
+                     size_t n_rows, float* yhat, void* stream);
+/* loss_sum[0] = SUM of per-row losses (validation / test loss numerator, cnn.py:121,:132) */
+int dlas_mlp_eval_loss(const int* dims, int n_layers, int loss, int mode, const float* params,
+                       const float* X, const float* y, size_t n_rows, float* loss_sum,
+                       void* workspace, size_t workspace_bytes, void* stream);
+
+#ifdef __cplusplus
+}
+#endif
+#endif /* DLAS_B200_H */

@@ -1,0 +1,79 @@
+"""CPU checks of the drop-in boundary: the C-ABI library builds for sm_100a, loads, and exports
+exactly what include/dlas_b200.h declares (no compute calls without a GPU)."""
+import ctypes
+import os
+import re
+
+import pytest
+
+ROOT = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
+HEADER = os.path.join(ROOT, "include", "dlas_b200.h")
+
+
+def declared_symbols():
+    src = open(HEADER).read()
+    src = re.sub(r"/\*.*?\*/", "", src, flags=re.S)
+    return sorted(set(re.findall(r"\b(dlas_[a-z0-9_]+)\s*\(", src)))
+
+
+@pytest.fixture(scope="module")
+def lib():
+    import __graft_entry__ as G
+    G.build()
+    from dlas import _lib
+    return _lib.load()
+
+
+def test_header_declares_the_path():
+    syms = declared_symbols()
+    for must in ("dlas_gilbert_f32", "dlas_mlp_grad", "dlas_opt_step", "dlas_mlp_fit_steps", "dlas_mlp_predict",
+                 "dlas_last_error"):
+        assert must in syms
+
+
+def test_library_exports_every_declared_symbol(lib):
+    for s in declared_symbols():
+        assert hasattr(lib, s), "libdlas_b200.so does not export %s" % s
+
+
+def test_binding_table_matches_header(lib):
+    from dlas import _lib
+    assert sorted(_lib.SIGNATURES) == declared_symbols()
+
+
+def test_version_and_error_string(lib):
+    assert lib.dlas_version() >= 100
+    assert isinstance(lib.dlas_last_error(), bytes)
+
+
+def test_host_only_queries(lib):
+    from dlas import _lib
+    dims = _lib.int_array([32, 256, 256, 1])
+    assert lib.dlas_mlp_n_params(dims, 3) == 32 * 256 + 256 + 256 * 256 + 256 + 256 + 1 == 74497
+    dims = _lib.int_array([8, 64, 64, 1])
+    assert lib.dlas_mlp_n_params(dims, 3) == 4801
+
+
+def test_no_cpu_fallback_without_gpu(lib):
+    import torch
+    if torch.cuda.is_available():
+        pytest.skip("GPU present")
+    rc = lib.dlas_gilbert_f32(None, None, None, None, 16, 0, None)
+    assert rc == -3  # DLAS_ERR_UNSUPPORTED_DEVICE: fails loudly, computes nothing
+    assert b"CUDA" in lib.dlas_last_error() or b"device" in lib.dlas_last_error()
+    import dlas
+    m = dlas.Sequential([dlas.Dense(8, 64, activation="relu"), dlas.Dense(64, 1)])
+    with pytest.raises(RuntimeError):
+        m.compile(loss="mse", optimizer=dlas.SGD())
+
+
+def test_product_never_imports_oracle():
+    """The product path must not import, call or link anything under oracle/ (comments may cite it)."""
+    pkg = os.path.join(ROOT, "deep-learning-at-scale_b200")
+    pat = re.compile(r"^\s*(import|from)\s+[^#\n]*\b(dlas_oracle|oracle)\b", re.M)
+    for d, _, files in os.walk(pkg):
+        for f in files:
+            if f.endswith(".py"):
+                assert not pat.search(open(os.path.join(d, f), errors="replace").read()), f
+            if f.endswith((".cu", ".cuh")):
+                assert "#include \"../../oracle" not in open(os.path.join(d, f), errors="replace").read(), f

@@ -200,6 +200,7 @@ int launch(const float* P, const float* S, const float* R, float* q, size_t n, c
 }  // namespace
 }  // namespace dlas
 
+#ifndef GILBERT_TUNE
 extern "C" int dlas_gilbert_f32(const float* P, const float* S, const float* R, float* q, size_t n,
                                 int variant, void* stream) {
   using namespace dlas;
@@ -219,3 +220,4 @@ extern "C" int dlas_gilbert_f32(const float* P, const float* S, const float* R, 
     default: return launch<7>(P, S, R, q, n, st);
   }
 }
+#endif  // GILBERT_TUNE

@@ -15,6 +15,7 @@
 // Algorithmic work: 2*sum(in*out) flop forward and 4*sum(in*out) (minus the first layer's dX)
 // backward per row; 4*(in0+out) bytes per row from HBM.
 #include "common.cuh"
+#include "simt_tiles.cuh"
 
 namespace dlas {
 namespace {
@@ -71,104 +72,6 @@ int make_desc(const int* dims, int n_layers, MlpDesc& d) {
 
 __host__ __device__ inline size_t partial_stride(int n_params) { return ((size_t)n_params + 1 + 3) & ~(size_t)3; }
 
-// out(j, r0..r0+RT) = sum_k inT[k][r] * Wm[k*ldw + j]; one (column j, row group) item per thread.
-template <int RT, class Epi>
-__device__ __forceinline__ void gemm_rows(const float* __restrict__ inT, const float* __restrict__ Wm,
-                                          int ldw, int K, int N, Epi epi) {
-  constexpr int G = R / RT;
-  const int items = N * G;
-  for (int item = threadIdx.x; item < items; item += NT) {
-    const int j = item % N, r0 = (item / N) * RT;
-    float acc[RT];
-#pragma unroll
-    for (int i = 0; i < RT; ++i) acc[i] = 0.0f;
-    const float* a = inT + r0;
-    const float* w = Wm + j;
-    int k = 0;
-    for (; k + 4 <= K; k += 4) {
-      float wv[4];
-#pragma unroll
-      for (int u = 0; u < 4; ++u) wv[u] = __ldg(w + (size_t)(k + u) * ldw);
-#pragma unroll
-      for (int u = 0; u < 4; ++u) {
-        const float* ar = a + (k + u) * RS;
-        if (RT >= 4) {
-#pragma unroll
-          for (int i = 0; i < RT; i += 4) {
-            float4 v = *reinterpret_cast<const float4*>(ar + i);
-            acc[i] = fmaf(v.x, wv[u], acc[i]);
-            acc[i + 1] = fmaf(v.y, wv[u], acc[i + 1]);
-            acc[i + 2] = fmaf(v.z, wv[u], acc[i + 2]);
-            acc[i + 3] = fmaf(v.w, wv[u], acc[i + 3]);
-          }
-        } else {
-#pragma unroll
-          for (int i = 0; i < RT; ++i) acc[i] = fmaf(ar[i], wv[u], acc[i]);
-        }
-      }
-    }
-    for (; k < K; ++k) {
-      float wv = __ldg(w + (size_t)k * ldw);
-      const float* ar = a + k * RS;
-#pragma unroll
-      for (int i = 0; i < RT; ++i) acc[i] = fmaf(ar[i], wv, acc[i]);
-    }
-    epi(j, r0, acc);
-  }
-}
-
-template <class Epi>
-__device__ __forceinline__ void gemm_dispatch(const float* inT, const float* Wm, int ldw, int K, int N, Epi epi) {
-  // as many row groups as the thread count allows: RT = R / min(R, NT / N) rounded to a power of 2
-  int g = NT / N;
-  if (g >= 32) gemm_rows<1>(inT, Wm, ldw, K, N, epi);
-  else if (g >= 16) gemm_rows<2>(inT, Wm, ldw, K, N, epi);
-  else if (g >= 8) gemm_rows<4>(inT, Wm, ldw, K, N, epi);
-  else if (g >= 4) gemm_rows<8>(inT, Wm, ldw, K, N, epi);
-  else if (g >= 2) gemm_rows<16>(inT, Wm, ldw, K, N, epi);
-  else gemm_rows<32>(inT, Wm, ldw, K, N, epi);
-}
-
-// dW[k][j] (+)= sum_r aT[k][r] * dzT[j][r];  db[j] (+)= sum_r dzT[j][r]
-__device__ __forceinline__ void accumulate_dw(const float* __restrict__ aT, const float* __restrict__ dzT,
-                                              int K, int N, float* __restrict__ pw, float* __restrict__ pb,
-                                              bool first) {
-  int kgn = NT / N;
-  if (kgn < 1) kgn = 1;
-  if (kgn > K) kgn = K;
-  const int items = N * kgn;
-  for (int item = threadIdx.x; item < items; item += NT) {
-    const int j = item % N, kg = item / N;
-    float dz[R];
-#pragma unroll
-    for (int i = 0; i < R; i += 4) {
-      float4 v = *reinterpret_cast<const float4*>(dzT + j * RS + i);
-      dz[i] = v.x; dz[i + 1] = v.y; dz[i + 2] = v.z; dz[i + 3] = v.w;
-    }
-    if (kg == 0) {
-      float s = 0.0f;
-#pragma unroll
-      for (int i = 0; i < R; ++i) s += dz[i];
-      pb[j] = first ? s : pb[j] + s;
-    }
-    for (int k = kg; k < K; k += kgn) {
-      const float* ar = aT + k * RS;
-      float s0 = 0.0f, s1 = 0.0f, s2 = 0.0f, s3 = 0.0f;
-#pragma unroll
-      for (int i = 0; i < R; i += 4) {
-        float4 v = *reinterpret_cast<const float4*>(ar + i);
-        s0 = fmaf(v.x, dz[i], s0);
-        s1 = fmaf(v.y, dz[i + 1], s1);
-        s2 = fmaf(v.z, dz[i + 2], s2);
-        s3 = fmaf(v.w, dz[i + 3], s3);
-      }
-      float s = (s0 + s1) + (s2 + s3);
-      float* p = pw + (size_t)k * N + j;
-      *p = first ? s : *p + s;
-    }
-  }
-}
-
 __device__ __forceinline__ float block_sum(float v, float* scratch) {
   // fixed-order tree: warp shuffle, then lane 0 of each warp through smem
 #pragma unroll
@@ -216,7 +119,7 @@ mlp_simt_kernel(const MlpDesc d, const int loss, const float* __restrict__ param
       float* outT = smem + d.act_off[l + 1];
       const float* bias = params + d.b_off[l];
       const bool relu = (l < L - 1);
-      gemm_dispatch(inT, params + d.w_off[l], d.dims[l + 1], d.dims[l], d.dims[l + 1],
+      gemm_dispatch<R, RS, NT>(inT, params + d.w_off[l], d.dims[l + 1], d.dims[l], d.dims[l + 1],
                     [&](int j, int r0, auto& acc) {
                       const float b = __ldg(bias + j);
                       constexpr int RT = sizeof(acc) / sizeof(float);
@@ -267,11 +170,11 @@ mlp_simt_kernel(const MlpDesc d, const int loss, const float* __restrict__ param
       for (int l = L - 1; l >= 0; --l) {
         const float* aT = smem + d.act_off[l];
         const float* dzc = smem + d.dz_off[cur];
-        accumulate_dw(aT, dzc, d.dims[l], d.dims[l + 1], my_partial + d.w_off[l], my_partial + d.b_off[l], first);
+        accumulate_dw<R, RS, NT>(aT, dzc, d.dims[l], d.dims[l + 1], my_partial + d.w_off[l], my_partial + d.b_off[l], first);
         if (l > 0) {
           float* dzn = smem + d.dz_off[cur ^ 1];
           // dA[k][r] = sum_j dz[j][r] * W[k][j] = sum_j dzT[j][r] * WT[j][k]; masked by relu'(A)
-          gemm_dispatch(dzc, WT + d.w_off[l], d.dims[l], d.dims[l + 1], d.dims[l],
+          gemm_dispatch<R, RS, NT>(dzc, WT + d.w_off[l], d.dims[l], d.dims[l + 1], d.dims[l],
                         [&](int k, int r0, auto& acc) {
                           constexpr int RT = sizeof(acc) / sizeof(float);
 #pragma unroll

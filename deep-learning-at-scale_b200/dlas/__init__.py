@@ -5,6 +5,7 @@ from ._lib import (DlasError, GILBERT_MUFU, GILBERT_POLY, LOSS_MAE_CLIP, LOSS_MS
                    OPT_ADAM, OPT_SGD, load)
 from .models import SGD, Adam, Dense, EarlyStopping, ModelCheckpoint, Sequential, mae_clip
 from .ops import gilbert
+from .recurrent import LSTM, LSTMRegressor
 
-__all__ = ["Sequential", "Dense", "SGD", "Adam", "EarlyStopping", "ModelCheckpoint", "mae_clip", "gilbert",
+__all__ = ["Sequential", "Dense", "SGD", "Adam", "EarlyStopping", "ModelCheckpoint", "mae_clip", "gilbert", "LSTM", "LSTMRegressor",
            "load", "DlasError"]

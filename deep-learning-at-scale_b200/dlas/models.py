@@ -118,13 +118,20 @@ class Sequential:
         self.params = None
         self.loss = None
         self.iterations = 0
+        self._impl = None   # LSTMRegressor when the stack holds LSTM layers
         for l in layers or []:
             self.add(l)
 
     # -- build (cnn.py:110-114)
     def add(self, layer):
+        from .recurrent import LSTM
+        if isinstance(layer, LSTM) or any(isinstance(l, LSTM) for l in self.layers):
+            if isinstance(layer, Dense) and layer.input_dim is None:
+                layer.input_dim = self.layers[-1].units
+            self.layers.append(layer)
+            return
         if not isinstance(layer, Dense):
-            raise NotImplementedError("only Dense layers are on the B200 hot path")
+            raise NotImplementedError("only Dense and LSTM layers are on the B200 hot path")
         if layer.input_dim is None:
             if not self.layers:
                 raise ValueError("first layer needs input_dim")
@@ -138,9 +145,32 @@ class Sequential:
         return [self.layers[0].input_dim] + [l.output_dim for l in self.layers]
 
     # -- compile (cnn.py:118)
+    def _compile_lstm(self, loss, optimizer):
+        from .recurrent import LSTM, LSTMRegressor
+        rec = [l for l in self.layers if isinstance(l, LSTM)]
+        head = self.layers[len(rec):]
+        if self.layers[:len(rec)] != rec or len(head) != 1 or not isinstance(head[0], Dense) or head[0].output_dim != 1:
+            raise NotImplementedError("supported stack: LSTM layers followed by one Dense(1)")
+        if rec[0].input_shape is None or len({l.units for l in rec}) != 1:
+            raise NotImplementedError("first LSTM needs input_shape=(T, d_in); all LSTM layers share one width")
+        T, d_in = rec[0].input_shape
+        self._impl = LSTMRegressor(d_in, rec[0].units, len(rec), T, seed=self.seed, device=self.device)
+        if self.params is not None:
+            self._impl.params = self.params
+        self._impl.compile(loss, optimizer if optimizer is not None else SGD())
+        for name in ("fit", "predict", "evaluate", "test_on_batch", "train_on_batch", "set_weights_flat",
+                     "get_weights_flat", "save_weights"):
+            setattr(self, name, getattr(self._impl, name))
+        return self
+
     def compile(self, loss="mse", optimizer=None):
         if not self.layers:
             raise ValueError("add layers before compile")
+        if loss not in _LOSSES:
+            raise ValueError("unknown loss %r" % (loss,))
+        from .recurrent import LSTM
+        if any(isinstance(l, LSTM) for l in self.layers):
+            return self._compile_lstm(loss, optimizer)
         for l in self.layers[:-1]:
             if l.activation != "relu":
                 raise NotImplementedError("hidden layers are ReLU on this path (cnn.py:111)")

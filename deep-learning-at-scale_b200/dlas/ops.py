@@ -150,3 +150,29 @@ def prof_read(slot):
     ms, cnt = C.c_float(0.0), C.c_int(0)
     check(_lib.load().dlas_prof_read(int(slot), C.byref(ms), C.byref(cnt)))
     return float(ms.value), int(cnt.value)
+
+
+# ---- LSTM -------------------------------------------------------------------------------------
+def lstm_n_params(d_in, hidden, n_layers):
+    return int(_lib.load().dlas_lstm_n_params(d_in, hidden, n_layers))
+
+
+def lstm_workspace(d_in, hidden, n_layers, T, n_seq, device="cuda"):
+    nbytes = int(_lib.load().dlas_lstm_workspace_bytes(d_in, hidden, n_layers, T, n_seq))
+    if nbytes == 0:
+        raise _lib.DlasError(-5, "LSTM shape d_in=%d hidden=%d layers=%d is not supported" % (d_in, hidden, n_layers))
+    return torch.empty(nbytes, dtype=torch.uint8, device=device)
+
+
+def lstm_grad(d_in, hidden, n_layers, T, loss, params, X, y, grad_sum, workspace):
+    check(_lib.load().dlas_lstm_grad(d_in, hidden, n_layers, T, int(loss), ptr(params), ptr(X), ptr(y), X.shape[0],
+                                     ptr(grad_sum), ptr(workspace), workspace.numel(), stream_ptr()))
+    return grad_sum
+
+
+def lstm_predict(d_in, hidden, n_layers, T, params, X, workspace, out=None):
+    if out is None:
+        out = torch.empty((X.shape[0], 1), dtype=torch.float32, device=X.device)
+    check(_lib.load().dlas_lstm_predict(d_in, hidden, n_layers, T, ptr(params), ptr(X), X.shape[0], ptr(out),
+                                        ptr(workspace), workspace.numel(), stream_ptr()))
+    return out

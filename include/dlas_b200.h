@@ -132,6 +132,24 @@ int dlas_mlp_eval_loss(const int* dims, int n_layers, int loss, int mode, const 
                        const float* X, const float* y, size_t n_rows, float* loss_sum,
                        void* workspace, size_t workspace_bytes, void* stream);
 
+/* ---- LSTM regressor (Readme.md:21; BASELINE.json config 5) ---------------------------------
+ * n_layers stacked LSTM layers of width hidden over X (n_seq, T, d_in) batch-major, last hidden
+ * state -> Dense(hidden -> 1).  Flat layout: per layer K[(d_l+hidden)][4*hidden] (input kernel
+ * rows then recurrent kernel rows; gate column blocks i,f,c,o), b[4*hidden]; then head w[hidden],
+ * b[1]. */
+size_t dlas_lstm_n_params(int d_in, int hidden, int n_layers);
+size_t dlas_lstm_workspace_bytes(int d_in, int hidden, int n_layers, int T, size_t n_seq);
+/* forward + loss + full BPTT over n_seq sequences: grad_sum[0..n_params) = SUM of per-sequence
+ * gradients, grad_sum[n_params] = SUM of per-sequence losses (the body of one fit batch,
+ * cnn.py:127-128; the update is dlas_opt_step). */
+int dlas_lstm_grad(int d_in, int hidden, int n_layers, int T, int loss, const float* params,
+                   const float* X, const float* y, size_t n_seq, float* grad_sum, void* workspace,
+                   size_t workspace_bytes, void* stream);
+/* forward only: yhat (n_seq) -- model.predict / test_on_batch, cnn.py:132 */
+int dlas_lstm_predict(int d_in, int hidden, int n_layers, int T, const float* params,
+                      const float* X, size_t n_seq, float* yhat, void* workspace,
+                      size_t workspace_bytes, void* stream);
+
 #ifdef __cplusplus
 }
 #endif

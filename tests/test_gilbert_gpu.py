@@ -73,9 +73,13 @@ def test_special_inputs_take_the_slow_path(ops):
     q = _run(ops, P, S, R, 0)
     with np.errstate(all="ignore"):
         ref = (P.astype(np.float64) * S.astype(np.float64) ** 1.89 / (435.0 * R.astype(np.float64) ** 0.546)).astype(f)
-    assert q[0] == 0 and np.isnan(q[1]) and np.isnan(q[2]) and np.isinf(q[3])
+    # P == 0 -> 0; negative P is just a negative flow; NaN propagates; inf stays inf
+    assert q[0] == 0 and q[1] == pytest.approx(ref[1], rel=1e-5) and np.isnan(q[2]) and np.isinf(q[3])
     assert q[5] == 0 and np.isinf(q[6]) and np.isinf(q[7]) and q[8] == 0
     assert q[4] == pytest.approx(ref[4], rel=1e-4)    # subnormal input: powf path
+    # negative choke size or gas-oil ratio has no real power: NaN, as the fp64 formula gives
+    q = _run(ops, f([100.0, 100.0]), f([-4.0, 16.0]), f([1.0, -2.0]), 0)
+    assert np.isnan(q).all()
 
 
 def test_full_size_properties(ops):

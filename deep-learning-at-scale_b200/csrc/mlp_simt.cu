@@ -311,3 +311,81 @@ int simt_predict(const int* dims, int n_layers, const float* params, const float
 }
 
 }  // namespace dlas
+
+// ---------------------------------------------------------------------------------------------
+// dlas_mlp_grad_noalloc: the same forward + loss + backward as dlas_mlp_grad (fp32 mode), for
+// hosts that cannot give the library a scratch buffer because they are not allowed to call
+// cudaMalloc where they train -- for example an executor plug-in whose device memory belongs
+// entirely to the executor's own pool and is fixed once tasks start, or a latency-bound serving
+// loop that bans allocator calls because cudaMalloc stalls the whole device.  The per-CTA gradient
+// partials and the transposed weights live in the file-scope device array below instead.
+//
+// * The array is DLAS_NOALLOC_SCRATCH_BYTES (4 MiB) and every GPU that loads the library keeps it
+//   until the process exits.  Networks whose scratch need is larger (roughly: more than ~7,000
+//   parameters on a 148-SM part) are refused with DLAS_ERR_WORKSPACE -- use dlas_mlp_grad.
+// * In host code the array's name is only a stand-in, not a device address.  The first call on each
+//   device (with that device current) asks the runtime for the real address with
+//   cudaGetSymbolAddress and caches it; that first call should therefore be made before any stream
+//   capture begins.  Later calls only launch kernels and a memset.
+// * All calls on a device share the one array and it keeps whatever the previous call left.  Each
+//   call clears the part it is about to use, and every CTA overwrites (not adds to) its slots on
+//   its first tile, so stale numbers are never read.  Two calls that overlap on the GPU (different
+//   streams, or different host threads) would write the same scratch and race: issue them on one
+//   stream, or serialise them.
+// * Nothing here calls cudaMalloc, cudaFree, or any routine that allocates (no events, no torch).
+// ---------------------------------------------------------------------------------------------
+namespace dlas {
+namespace {
+constexpr size_t kNoAllocFloats = DLAS_NOALLOC_SCRATCH_BYTES / sizeof(float);
+static __device__ __align__(256) float g_noalloc_scratch[kNoAllocFloats];
+float* g_noalloc_ptr[64];  // per device, filled on first use
+}  // namespace
+}  // namespace dlas
+
+extern "C" int dlas_mlp_grad_noalloc(const int* dims, int n_layers, int loss, const float* params,
+                                     const float* X, const float* y, size_t n_rows, float* grad_sum,
+                                     void* stream) {
+  using namespace dlas;
+  DLAS_CHECK_DEVICE();
+  MlpDesc d;
+  int rc = make_desc(dims, n_layers, d);
+  if (rc != DLAS_OK) return rc;
+  DLAS_REQUIRE(loss == DLAS_LOSS_MSE || loss == DLAS_LOSS_MAE_CLIP, "dlas_mlp_grad_noalloc: unknown loss %d", loss);
+  DLAS_REQUIRE(params && grad_sum && (n_rows == 0 || (X && y)), "dlas_mlp_grad_noalloc: null pointer");
+  const int grid = grid_size();
+  const size_t stride = partial_stride(d.n_params);
+  const size_t need_floats = (size_t)grid * stride + (size_t)d.n_params;
+  if (need_floats > kNoAllocFloats) {
+    set_error("dlas_mlp_grad_noalloc: these layer widths need %zu bytes of scratch but the built-in array holds "
+              "%zu (DLAS_NOALLOC_SCRATCH_BYTES); use dlas_mlp_grad with a caller-provided workspace",
+              need_floats * sizeof(float), (size_t)DLAS_NOALLOC_SCRATCH_BYTES);
+    return DLAS_ERR_WORKSPACE;
+  }
+  int dev = 0;
+  DLAS_CUDA(cudaGetDevice(&dev));
+  DLAS_REQUIRE(dev >= 0 && dev < 64, "dlas_mlp_grad_noalloc: device ordinal %d out of range", dev);
+  if (g_noalloc_ptr[dev] == nullptr) {  // once per device, with that device current
+    float* p = nullptr;
+    DLAS_CUDA(cudaGetSymbolAddress((void**)&p, g_noalloc_scratch));
+    g_noalloc_ptr[dev] = p;
+  }
+  float* scratch = g_noalloc_ptr[dev];
+  cudaStream_t st = (cudaStream_t)stream;
+  if (n_rows == 0) {
+    DLAS_CUDA(cudaMemsetAsync(grad_sum, 0, ((size_t)d.n_params + 1) * sizeof(float), st));
+    return DLAS_OK;
+  }
+  DLAS_CUDA(cudaMemsetAsync(scratch, 0, need_floats * sizeof(float), st));
+  float* partials = scratch;
+  float* WT = scratch + (size_t)grid * stride;
+  transpose_weights_kernel<<<64, 256, 0, st>>>(d, params, WT);
+  DLAS_LAUNCH_CHECK();
+  rc = launch_main<KIND_TRAIN>(d, loss, params, WT, X, y, n_rows, partials, nullptr, st);
+  if (rc != DLAS_OK) return rc;
+  const size_t n_tiles = (n_rows + R - 1) / R;
+  const int n_active = (int)(n_tiles < (size_t)grid ? n_tiles : (size_t)grid);
+  const size_t count = (size_t)d.n_params + 1;
+  reduce_partials_kernel<<<(unsigned)((count + 255) / 256), 256, 0, st>>>(partials, stride, n_active, 0, count, grad_sum);
+  DLAS_LAUNCH_CHECK();
+  return DLAS_OK;
+}

@@ -53,6 +53,7 @@ SIGNATURES = {
                                 C.POINTER(C.c_int64), C.c_int64, _i, _u64, _p, _p, _p, _sz, _p]),
     "dlas_mlp_predict": (_i, [_ip, _i, _i, _p, _p, _sz, _p, _p]),
     "dlas_mlp_eval_loss": (_i, [_ip, _i, _i, _i, _p, _p, _p, _sz, _p, _p, _sz, _p]),
+    "dlas_mlp_grad_noalloc": (_i, [_ip, _i, _i, _p, _p, _p, _sz, _p, _p]),
     "dlas_lstm_n_params": (_sz, [_i, _i, _i]),
     "dlas_lstm_workspace_bytes": (_sz, [_i, _i, _i, _i, _sz]),
     "dlas_lstm_grad": (_i, [_i, _i, _i, _i, _i, _p, _p, _p, _sz, _p, _p, _sz, _p]),

@@ -132,6 +132,21 @@ int dlas_mlp_eval_loss(const int* dims, int n_layers, int loss, int mode, const 
                        const float* X, const float* y, size_t n_rows, float* loss_sum,
                        void* workspace, size_t workspace_bytes, void* stream);
 
+/* dlas_mlp_grad without a caller-provided workspace.  This entry point has no counterpart in the
+ * reference; it exists for hosts that may not call cudaMalloc at the point where they train (a
+ * plug-in inside an executor that owns and has locked all device memory, a serving loop that bans
+ * allocator calls because they stall the device).  Same arguments and results as dlas_mlp_grad in
+ * DLAS_MODE_FP32; the per-CTA gradient partials live in a device array built into the library:
+ * DLAS_NOALLOC_SCRATCH_BYTES per GPU, held from library load until the process exits.  Layer widths
+ * that need more scratch than that are refused with DLAS_ERR_WORKSPACE.  It calls no allocating
+ * routine.  The first call on each device looks up the array's device address, so make that call
+ * before any stream capture starts.  All calls share the array: calls that overlap on the GPU
+ * (two streams, two threads) race -- keep them on one stream. */
+#define DLAS_NOALLOC_SCRATCH_BYTES (4u << 20)
+int dlas_mlp_grad_noalloc(const int* dims, int n_layers, int loss, const float* params,
+                          const float* X, const float* y, size_t n_rows, float* grad_sum,
+                          void* stream);
+
 /* ---- LSTM regressor (Readme.md:21; BASELINE.json config 5) ---------------------------------
  * n_layers stacked LSTM layers of width hidden over X (n_seq, T, d_in) batch-major, last hidden
  * state -> Dense(hidden -> 1).  Flat layout: per layer K[(d_l+hidden)][4*hidden] (input kernel

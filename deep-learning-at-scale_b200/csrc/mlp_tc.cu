@@ -1,14 +1,438 @@
-// tcgen05 / TMEM MLP training kernel (DLAS_MODE_TC).  Placeholder until the tensor-core kernel lands:
-// reports "unsupported" for every shape so that callers get DLAS_ERR_UNSUPPORTED_SHAPE, never a
-// silent fallback.
+// Tensor-core training kernel for the 32-256-256-1 static ANN (DLAS_MODE_TC): forward, loss and
+// backward of cnn.py:127-128's batch body on tcgen05.mma with fp32 accumulators in TMEM.
+//
+// Operands are fp16 (11-bit significand, the same as TF32; fp32 accumulate), because fp32/TF32
+// operands do not fit on chip: W2 alone is 256 KB of the 227 KB of shared memory, and dW2's fp32
+// accumulator (256x256) is all 512 TMEM columns of one SM.  The network is therefore split over a
+// CTA PAIR (cluster of 2) along layer 2's OUTPUT units; CTA `rank` owns out-columns
+// [rank*128, rank*128+128):
+//     Z1 = X W1, H1 = relu(Z1+b1)                 both CTAs (K = 32, cheap, redundant)
+//     Z2h = H1 W2[:, half]                        N = 128
+//     p = relu(Z2h+b2h) . w3h                     per-row partial dot; the ONLY cross-CTA exchange
+//                                                 (128 floats through distributed shared memory)
+//     dZ2h = dy w3h relu'(Z2h)
+//     dW2[:, half] += H1^T dZ2h                   256 TMEM columns, accumulated over all tiles
+//     dH1p = dZ2h W2[:, half]^T                   PARTIAL dH1; dZ1p = relu'(H1) o dH1p is linear in
+//     dW1p^T += dZ1p^T [X | 1]                    the partials, so each CTA just adds its share to
+//                                                 dW1 / db1 (column 32 of [X | 1] gives db1)
+// MMA floor per 128-row tile per CTA: 3584 cycles (256 + 1024 + 1024 + 1024 + 256), 93 % of the
+// 6680 SM-cycles the unsplit network needs per tile.  This version runs the phases back to back
+// (MMA, then its epilogue); overlap is the next step.
+//
+// Shared memory (fp16 tiles in the column-blocked SWIZZLE_128B layout of tc_common.cuh):
+//   sW1 [32][256] 16 KB | sW2 [256][128] 64 KB | sX [128][64] 16 KB ([x | 1 | 0]) | sH1 [128][256] 64 KB
+//   (dZ1 overwrites H1 in place) | sDZ2 [128][128] 32 KB | fp32: b1, b2h, w3h, y, exchange buffers
+// TMEM columns: [0,128) work | [128,384) dW2 half (two M=128 halves) | [384,432) and [448,496) dW1^T halves (N=48)
 #include "common.cuh"
+#include "tc_common.cuh"
+
 namespace dlas {
 size_t simt_workspace_bytes(const int* dims, int n_layers);
-bool tc_supported(const int*, int) { return false; }
-size_t tc_workspace_bytes(const int* dims, int n_layers) { return simt_workspace_bytes(dims, n_layers); }
-int tc_grad(const int*, int, int, const float*, const float*, const float*, size_t, float*, void*, size_t,
-            cudaStream_t) {
-  set_error("DLAS_MODE_TC is not available in this build");
-  return DLAS_ERR_UNSUPPORTED_SHAPE;
+
+namespace {
+using namespace tc;
+
+constexpr int D0 = 32, D1 = 256, D2 = 256;
+constexpr int TILE = 128;
+constexpr int NT = 128;
+constexpr int W1_OFF = 0, B1_OFF = W1_OFF + D0 * D1, W2_OFF = B1_OFF + D1, B2_OFF = W2_OFF + D1 * D2,
+              W3_OFF = B2_OFF + D2, B3_OFF = W3_OFF + D2, N_PARAMS = B3_OFF + 1;
+constexpr size_t PSTRIDE = ((size_t)N_PARAMS + 1 + 3) & ~(size_t)3;
+
+constexpr uint32_t S_W1 = 0, S_W2 = S_W1 + 16384, S_X = S_W2 + 65536, S_H1 = S_X + 16384, S_DZ2 = S_H1 + 65536,
+                   S_F32 = S_DZ2 + 32768;
+// fp32 area (float index): b1[256] b2h[128] w3h[128] y[128] part[2][128] red[4][128] misc[16]
+constexpr int F_B1 = 0, F_B2 = 256, F_W3 = 384, F_Y = 512, F_PART = 640, F_RED = 896, F_MISC = 1408, F_END = 1424;
+constexpr uint32_t S_BAR = S_F32 + F_END * 4;   // mbarrier (8 B) + tmem base (4 B)
+constexpr uint32_t SMEM_BYTES = S_BAR + 16 + 1024;  // + slack for the 1024-B alignment of the base
+
+constexpr uint32_t TM_WORK = 0, TM_DW2 = 128, TM_DW1 = 384, TM_COLS = 512;
+
+// out: lane l holds sum over the warp's 32 lanes of v[l]
+__device__ __forceinline__ float warp_colsum32(float (&v)[32], int lane) {
+#pragma unroll
+  for (int s = 16; s >= 1; s >>= 1) {
+    const bool hi = (lane & s) != 0;
+#pragma unroll
+    for (int i = 0; i < s; ++i) {
+      float send = hi ? v[i] : v[i + s];
+      float keep = hi ? v[i + s] : v[i];
+      v[i] = keep + __shfl_xor_sync(0xffffffffu, send, s);
+    }
+  }
+  return v[0];
 }
+
+__global__ void __cluster_dims__(2, 1, 1) __launch_bounds__(NT, 1)
+mlp_tc_kernel(const int loss_kind, const float* __restrict__ params, const float* __restrict__ X,
+              const float* __restrict__ y, const size_t n_rows, float* __restrict__ partials,
+              int* __restrict__ err_flag) {
+  extern __shared__ uint8_t smem_raw[];
+  uint8_t* smem = reinterpret_cast<uint8_t*>((reinterpret_cast<uintptr_t>(smem_raw) + 1023) & ~(uintptr_t)1023);
+  float* f32 = reinterpret_cast<float*>(smem + S_F32);
+  uint64_t* bar = reinterpret_cast<uint64_t*>(smem + S_BAR);
+  uint32_t* tmem_slot = reinterpret_cast<uint32_t*>(smem + S_BAR + 8);
+  const uint32_t sW1 = smem_u32(smem + S_W1), sW2 = smem_u32(smem + S_W2), sX = smem_u32(smem + S_X),
+                 sH1 = smem_u32(smem + S_H1), sDZ2 = smem_u32(smem + S_DZ2);
+
+  const int tid = threadIdx.x, warp = tid >> 5, lane = tid & 31;
+  const uint32_t rank = cluster_ctarank();
+  const int pair = blockIdx.x >> 1, n_pairs = gridDim.x >> 1;
+  const size_t n_tiles = (n_rows + TILE - 1) / TILE;
+
+  // ---- one-time set-up: barrier, TMEM, weights -> fp16 tiles ---------------------------------------
+  if (tid == 0) { mbar_init(bar, 1); mbar_fence_init(); }
+  if (warp == 0) tmem_alloc(tmem_slot, TM_COLS);
+  {
+    const float* W1 = params + W1_OFF;                        // [32][256]
+    for (int idx = tid; idx < D0 * (D1 / 8); idx += NT) {
+      int r = idx / (D1 / 8), c = (idx % (D1 / 8)) * 8;
+      float4 a = __ldg(reinterpret_cast<const float4*>(W1 + r * D1 + c));
+      float4 b = __ldg(reinterpret_cast<const float4*>(W1 + r * D1 + c + 4));
+      uint4 h = make_uint4(pack_half2(a.x, a.y), pack_half2(a.z, a.w), pack_half2(b.x, b.y), pack_half2(b.z, b.w));
+      *reinterpret_cast<uint4*>(smem + S_W1 + tile_chunk_off(D0, r, c)) = h;
+    }
+    const float* W2 = params + W2_OFF + rank * 128;           // [256][256], my 128 out-columns
+    for (int idx = tid; idx < D1 * 16; idx += NT) {
+      int r = idx >> 4, c = (idx & 15) * 8;
+      float4 a = __ldg(reinterpret_cast<const float4*>(W2 + (size_t)r * D2 + c));
+      float4 b = __ldg(reinterpret_cast<const float4*>(W2 + (size_t)r * D2 + c + 4));
+      uint4 h = make_uint4(pack_half2(a.x, a.y), pack_half2(a.z, a.w), pack_half2(b.x, b.y), pack_half2(b.z, b.w));
+      *reinterpret_cast<uint4*>(smem + S_W2 + tile_chunk_off(D1, r, c)) = h;
+    }
+    for (int i = tid; i < D1; i += NT) f32[F_B1 + i] = __ldg(params + B1_OFF + i);
+    f32[F_B2 + tid] = __ldg(params + B2_OFF + rank * 128 + tid);
+    f32[F_W3 + tid] = __ldg(params + W3_OFF + rank * 128 + tid);
+    // constant part of [x | 1 | 0]: column 32 = 1, columns 33..63 = 0
+    *reinterpret_cast<uint4*>(smem + S_X + tile_chunk_off(TILE, tid, 32)) = make_uint4(0x00003C00u, 0u, 0u, 0u);
+    for (int c = 40; c < 64; c += 8) *reinterpret_cast<uint4*>(smem + S_X + tile_chunk_off(TILE, tid, c)) = make_uint4(0u, 0u, 0u, 0u);
+  }
+  const float b3 = __ldg(params + B3_OFF);
+  fence_async_smem();
+  fence_before();
+  __syncthreads();
+  fence_after();
+  cluster_sync_all();  // the peer CTA is running: its shared memory may be written from here on
+  const uint32_t tm = *tmem_slot;
+  const uint32_t lane_base = (uint32_t)(warp * 32) << 16;
+  const uint32_t peer_part = map_to_cta(smem_u32(f32 + F_PART), rank ^ 1u);
+
+  constexpr uint32_t ID_KM_MN_128 = make_idesc(128, 128, false, true);   // A K-major, B MN-major
+  constexpr uint32_t ID_MN_MN_128 = make_idesc(128, 128, true, true);
+  constexpr uint32_t ID_KM_KM_128 = make_idesc(128, 128, false, false);
+  constexpr uint32_t ID_MN_MN_48 = make_idesc(128, 48, true, true);
+
+  uint32_t parity = 0;
+  bool ok = true;
+  bool first = true;
+  float acc_w3[4] = {0.f, 0.f, 0.f, 0.f}, acc_b2[4] = {0.f, 0.f, 0.f, 0.f};  // column (chunk*32 + lane) sums of this warp's rows
+  float acc_loss = 0.f, acc_b3 = 0.f;
+  int it = 0;
+
+  for (size_t tile = pair; tile < n_tiles; tile += n_pairs, ++it) {
+    const size_t row0 = tile * TILE;
+    const int nr = (int)((n_rows - row0) < (size_t)TILE ? (n_rows - row0) : (size_t)TILE);
+    // ---- (a) X tile (fp32 -> fp16) and targets -----------------------------------------------------
+    {
+      const float* xr = X + (row0 + tid) * (size_t)D0;
+#pragma unroll
+      for (int q = 0; q < 4; ++q) {
+        uint4 h = make_uint4(0u, 0u, 0u, 0u);
+        if (tid < nr) {
+          float4 a = __ldcs(reinterpret_cast<const float4*>(xr + q * 8));
+          float4 b = __ldcs(reinterpret_cast<const float4*>(xr + q * 8 + 4));
+          h = make_uint4(pack_half2(a.x, a.y), pack_half2(a.z, a.w), pack_half2(b.x, b.y), pack_half2(b.z, b.w));
+        }
+        *reinterpret_cast<uint4*>(smem + S_X + tile_chunk_off(TILE, tid, q * 8)) = h;
+      }
+      f32[F_Y + tid] = (tid < nr) ? __ldcs(y + row0 + tid) : 0.f;
+    }
+    fence_async_smem();
+    fence_before();
+    __syncthreads();
+    // ---- (b) Z1 = X W1 in two N=128 chunks; H1 = relu(Z1 + b1) -> sH1 -------------------------------
+#pragma unroll 1
+    for (int j = 0; j < 2; ++j) {
+      if (tid == 0) {
+        fence_after();
+#pragma unroll
+        for (int k = 0; k < D0; k += 16)
+          mma_f16(tm + TM_WORK, desc_kmajor(sX, TILE, 0, k), desc_mnmajor(sW1, D0, j * 128, k), ID_KM_MN_128, k > 0);
+        mma_commit(bar);
+      }
+      ok = mbar_wait(bar, parity) && ok;
+      parity ^= 1;
+      fence_after();
+#pragma unroll 1
+      for (int c0 = 0; c0 < 128; c0 += 32) {
+        uint32_t v[32];
+        tmem_ld32(tm + TM_WORK + lane_base + c0, v);
+        tmem_ld_wait();
+#pragma unroll
+        for (int q = 0; q < 4; ++q) {
+          const float4 ba = *reinterpret_cast<const float4*>(f32 + F_B1 + j * 128 + c0 + q * 8);
+          const float4 bb = *reinterpret_cast<const float4*>(f32 + F_B1 + j * 128 + c0 + q * 8 + 4);
+          float h0 = fmaxf(__uint_as_float(v[q * 8 + 0]) + ba.x, 0.f), h1 = fmaxf(__uint_as_float(v[q * 8 + 1]) + ba.y, 0.f);
+          float h2 = fmaxf(__uint_as_float(v[q * 8 + 2]) + ba.z, 0.f), h3 = fmaxf(__uint_as_float(v[q * 8 + 3]) + ba.w, 0.f);
+          float h4 = fmaxf(__uint_as_float(v[q * 8 + 4]) + bb.x, 0.f), h5 = fmaxf(__uint_as_float(v[q * 8 + 5]) + bb.y, 0.f);
+          float h6 = fmaxf(__uint_as_float(v[q * 8 + 6]) + bb.z, 0.f), h7 = fmaxf(__uint_as_float(v[q * 8 + 7]) + bb.w, 0.f);
+          *reinterpret_cast<uint4*>(smem + S_H1 + tile_chunk_off(TILE, tid, j * 128 + c0 + q * 8)) =
+              make_uint4(pack_half2(h0, h1), pack_half2(h2, h3), pack_half2(h4, h5), pack_half2(h6, h7));
+        }
+      }
+      fence_async_smem();
+      fence_before();
+      __syncthreads();
+    }
+    // ---- (c) Z2h = H1 W2h; partial output dot; exchange; dZ2h -> sDZ2 ---------------------------------
+    if (tid == 0) {
+      fence_after();
+#pragma unroll
+      for (int k = 0; k < D1; k += 16)
+        mma_f16(tm + TM_WORK, desc_kmajor(sH1, TILE, 0, k), desc_mnmajor(sW2, D1, 0, k), ID_KM_MN_128, k > 0);
+      mma_commit(bar);
+    }
+    ok = mbar_wait(bar, parity) && ok;
+    parity ^= 1;
+    fence_after();
+    float part = 0.f;
+#pragma unroll 1
+    for (int c0 = 0; c0 < 128; c0 += 32) {
+      uint32_t v[32];
+      tmem_ld32(tm + TM_WORK + lane_base + c0, v);
+      tmem_ld_wait();
+#pragma unroll
+      for (int i = 0; i < 32; ++i)
+        part = fmaf(fmaxf(__uint_as_float(v[i]) + f32[F_B2 + c0 + i], 0.f), f32[F_W3 + c0 + i], part);
+    }
+    const int buf = it & 1;
+    st_cluster_f32(peer_part + (uint32_t)(buf * 128 + tid) * 4, part);
+    cluster_sync_all();
+    const float other = f32[F_PART + buf * 128 + tid];
+    const float yhat = (rank == 0 ? part + other : other + part) + b3;   // same value on both CTAs
+    float g = 0.f;
+    if (tid < nr) {
+      const float d = yhat - f32[F_Y + tid];
+      if (loss_kind == DLAS_LOSS_MSE) {
+        acc_loss += d * d;
+        g = 2.0f * d;
+      } else {  // cnn.py:29-32, CLIP_VALUE = 6
+        const float a = fabsf(d);
+        acc_loss += fminf(a, 6.0f);
+        g = (a <= 6.0f) ? (d > 0.f ? 1.f : (d < 0.f ? -1.f : 0.f)) : 0.f;
+      }
+    }
+    acc_b3 += g;
+#pragma unroll 1
+    for (int c0 = 0; c0 < 128; c0 += 32) {
+      uint32_t v[32];
+      tmem_ld32(tm + TM_WORK + lane_base + c0, v);
+      tmem_ld_wait();
+      float hg[32], dz[32];
+#pragma unroll
+      for (int i = 0; i < 32; ++i) {
+        const float z = __uint_as_float(v[i]) + f32[F_B2 + c0 + i];
+        hg[i] = fmaxf(z, 0.f) * g;                               // -> dw3
+        dz[i] = z > 0.f ? g * f32[F_W3 + c0 + i] : 0.f;          // -> dZ2, db2
+      }
+#pragma unroll
+      for (int q = 0; q < 4; ++q)
+        *reinterpret_cast<uint4*>(smem + S_DZ2 + tile_chunk_off(TILE, tid, c0 + q * 8)) =
+            make_uint4(pack_half2(dz[q * 8 + 0], dz[q * 8 + 1]), pack_half2(dz[q * 8 + 2], dz[q * 8 + 3]),
+                       pack_half2(dz[q * 8 + 4], dz[q * 8 + 5]), pack_half2(dz[q * 8 + 6], dz[q * 8 + 7]));
+      acc_w3[c0 >> 5] += warp_colsum32(hg, lane);
+      acc_b2[c0 >> 5] += warp_colsum32(dz, lane);
+    }
+    fence_async_smem();
+    fence_before();
+    __syncthreads();
+    // ---- (d) dW2h += H1^T dZ2h; dH1p = dZ2h W2h^T in two N=128 chunks; dZ1p = relu'(H1) o dH1p in place
+#pragma unroll 1
+    for (int j = 0; j < 2; ++j) {
+      if (tid == 0) {
+        fence_after();
+        if (j == 0) {
+#pragma unroll 1
+          for (int mh = 0; mh < 2; ++mh)
+#pragma unroll
+            for (int k = 0; k < TILE; k += 16)
+              mma_f16(tm + TM_DW2 + mh * 128, desc_mnmajor(sH1, TILE, mh * 128, k), desc_mnmajor(sDZ2, TILE, 0, k),
+                      ID_MN_MN_128, !(first && k == 0));
+        }
+#pragma unroll
+        for (int k = 0; k < 128; k += 16)
+          mma_f16(tm + TM_WORK, desc_kmajor(sDZ2, TILE, 0, k), desc_kmajor(sW2, D1, j * 128, k), ID_KM_KM_128, k > 0);
+        mma_commit(bar);
+      }
+      ok = mbar_wait(bar, parity) && ok;
+      parity ^= 1;
+      fence_after();
+#pragma unroll 1
+      for (int c0 = 0; c0 < 128; c0 += 32) {
+        uint32_t v[32];
+        tmem_ld32(tm + TM_WORK + lane_base + c0, v);
+        tmem_ld_wait();
+#pragma unroll
+        for (int q = 0; q < 4; ++q) {
+          uint4* p = reinterpret_cast<uint4*>(smem + S_H1 + tile_chunk_off(TILE, tid, j * 128 + c0 + q * 8));
+          const uint4 h = *p;
+          const uint32_t hw[4] = {h.x, h.y, h.z, h.w};
+          uint32_t o[4];
+#pragma unroll
+          for (int e = 0; e < 4; ++e) {
+            const float lo = (hw[e] & 0x7FFFu) ? __uint_as_float(v[q * 8 + 2 * e]) : 0.f;       // H1 > 0 (it is >= 0)
+            const float hi = (hw[e] & 0x7FFF0000u) ? __uint_as_float(v[q * 8 + 2 * e + 1]) : 0.f;
+            o[e] = pack_half2(lo, hi);
+          }
+          *p = make_uint4(o[0], o[1], o[2], o[3]);
+        }
+      }
+      fence_async_smem();
+      fence_before();
+      __syncthreads();
+    }
+    // ---- (e) dW1p^T += dZ1p^T [X | 1] (column 32 -> db1) ------------------------------------------------
+    if (tid == 0) {
+      fence_after();
+#pragma unroll 1
+      for (int mh = 0; mh < 2; ++mh)
+#pragma unroll
+        for (int k = 0; k < TILE; k += 16)
+          mma_f16(tm + TM_DW1 + mh * 64, desc_mnmajor(sH1, TILE, mh * 128, k), desc_mnmajor(sX, TILE, 0, k), ID_MN_MN_48,
+                  !(first && k == 0));
+      mma_commit(bar);
+    }
+    ok = mbar_wait(bar, parity) && ok;   // sX and sH1 are free for the next tile
+    parity ^= 1;
+    fence_after();
+    first = false;
+  }
+
+  // ---- drain the accumulators into this CTA's partial vector ---------------------------------------
+  float* my = partials + (size_t)blockIdx.x * PSTRIDE;
+  if (!first) {
+#pragma unroll 1
+    for (int mh = 0; mh < 2; ++mh) {
+      float* dst = my + W2_OFF + (size_t)(mh * 128 + tid) * D2 + rank * 128;   // row in = mh*128+tid, my out-columns
+#pragma unroll 1
+      for (int c0 = 0; c0 < 128; c0 += 32) {
+        uint32_t v[32];
+        tmem_ld32(tm + TM_DW2 + mh * 128 + lane_base + c0, v);
+        tmem_ld_wait();
+#pragma unroll
+        for (int q = 0; q < 8; ++q)
+          *reinterpret_cast<float4*>(dst + c0 + q * 4) = make_float4(__uint_as_float(v[q * 4]), __uint_as_float(v[q * 4 + 1]),
+                                                                     __uint_as_float(v[q * 4 + 2]), __uint_as_float(v[q * 4 + 3]));
+      }
+      // dW1p^T: lane = h1 unit, column = input feature; column 32 = db1
+      uint32_t v[32], w[16];
+      tmem_ld32(tm + TM_DW1 + mh * 64 + lane_base, v);
+      tmem_ld16(tm + TM_DW1 + mh * 64 + lane_base + 32, w);
+      tmem_ld_wait();
+      const int h1 = mh * 128 + tid;
+#pragma unroll
+      for (int i = 0; i < 32; ++i) my[W1_OFF + i * D1 + h1] = __uint_as_float(v[i]);
+      my[B1_OFF + h1] = __uint_as_float(w[0]);
+    }
+    // column sums held per warp -> add the four warps in warp order
+#pragma unroll
+    for (int c = 0; c < 4; ++c) f32[F_RED + warp * 128 + c * 32 + lane] = acc_w3[c];
+    __syncthreads();
+    my[W3_OFF + rank * 128 + tid] = (f32[F_RED + tid] + f32[F_RED + 128 + tid]) + (f32[F_RED + 256 + tid] + f32[F_RED + 384 + tid]);
+    __syncthreads();
+#pragma unroll
+    for (int c = 0; c < 4; ++c) f32[F_RED + warp * 128 + c * 32 + lane] = acc_b2[c];
+    __syncthreads();
+    my[B2_OFF + rank * 128 + tid] = (f32[F_RED + tid] + f32[F_RED + 128 + tid]) + (f32[F_RED + 256 + tid] + f32[F_RED + 384 + tid]);
+    __syncthreads();
+    // loss and db3: fixed-order sum over the 128 rows (rank 0 only contributes them)
+    f32[F_RED + tid] = acc_loss;
+    f32[F_RED + 128 + tid] = acc_b3;
+    __syncthreads();
+    if (rank == 0 && tid < 2) {
+      float s = 0.f;
+      for (int i = 0; i < 128; ++i) s += f32[F_RED + tid * 128 + i];
+      my[tid == 0 ? N_PARAMS : B3_OFF] = s;
+    }
+  }
+  if (!ok && tid == 0) atomicExch(err_flag, 1);
+  // ---- teardown ----------------------------------------------------------------------------------------
+  fence_before();
+  __syncthreads();
+  cluster_sync_all();   // do not exit while the peer may still write our exchange buffer
+  if (warp == 0) tmem_dealloc(tm, TM_COLS);
+}
+
+// grad_sum[i] = sum of the partials of the CTAs that own entry i, in CTA order:
+//   W1, b1: every active CTA (each holds a partial);  W2[:, c], b2[c], w3[c]: CTAs of rank c/128;
+//   b3 and the loss sum: rank-0 CTAs.
+__global__ void __launch_bounds__(256)
+tc_reduce_kernel(const float* __restrict__ partials, int n_active_pairs, const int* __restrict__ err_flag,
+                 float* __restrict__ out) {
+  int i = blockIdx.x * 256 + threadIdx.x;
+  if (i > N_PARAMS) return;
+  if (*err_flag) {  // an mbarrier wait timed out inside the tcgen05 kernel: fail loudly, never return numbers
+    out[i] = __int_as_float(0x7fc00000);
+    return;
+  }
+  int first = 0, step = 1;
+  if (i >= W2_OFF && i < B2_OFF) { first = ((i - W2_OFF) % D2) / 128; step = 2; }
+  else if (i >= B2_OFF && i < W3_OFF) { first = (i - B2_OFF) / 128; step = 2; }
+  else if (i >= W3_OFF && i < B3_OFF) { first = (i - W3_OFF) / 128; step = 2; }
+  else if (i >= B3_OFF) { first = 0; step = 2; }
+  float s = 0.f;
+  for (int c = first; c < 2 * n_active_pairs; c += step) s += partials[(size_t)c * PSTRIDE + i];
+  out[i] = s;
+}
+
+int n_ctas() { return (sm_count() / 2) * 2; }
+
+}  // namespace
+
+bool tc_supported(const int* dims, int n_layers) {
+  return n_layers == 3 && dims[0] == D0 && dims[1] == D1 && dims[2] == D2 && dims[3] == 1;
+}
+
+size_t tc_workspace_bytes(const int* dims, int n_layers) {
+  size_t tc = (size_t)n_ctas() * PSTRIDE * sizeof(float) + 256;   // partials + error flag
+  size_t simt = simt_workspace_bytes(dims, n_layers);             // eval / predict share the workspace
+  return tc > simt ? tc : simt;
+}
+
+int tc_grad(const int* dims, int n_layers, int loss, const float* params, const float* X, const float* y,
+            size_t n_rows, float* grad_sum, void* workspace, size_t workspace_bytes, cudaStream_t st) {
+  if (!tc_supported(dims, n_layers)) {
+    set_error("DLAS_MODE_TC supports the 32-256-256-1 network only");
+    return DLAS_ERR_UNSUPPORTED_SHAPE;
+  }
+  size_t need = tc_workspace_bytes(dims, n_layers);
+  if (workspace == nullptr || workspace_bytes < need) {
+    set_error("mlp (tc): workspace of %zu bytes given, %zu needed", workspace_bytes, need);
+    return DLAS_ERR_WORKSPACE;
+  }
+  if (n_rows == 0) {
+    DLAS_CUDA(cudaMemsetAsync(grad_sum, 0, ((size_t)N_PARAMS + 1) * sizeof(float), st));
+    return DLAS_OK;
+  }
+  DLAS_REQUIRE((((uintptr_t)X) & 15) == 0, "mlp (tc): X must be 16-byte aligned");
+  float* partials = (float*)workspace;
+  int* err_flag = (int*)((char*)workspace + (size_t)n_ctas() * PSTRIDE * sizeof(float));
+  static bool attr_set = false;
+  if (!attr_set) {
+    DLAS_CUDA(cudaFuncSetAttribute(mlp_tc_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)SMEM_BYTES));
+    attr_set = true;
+  }
+  const int grid = n_ctas();
+  DLAS_CUDA(cudaMemsetAsync(err_flag, 0, sizeof(int), st));
+  int pi = prof_begin(DLAS_PROF_MLP_GRAD, st);
+  mlp_tc_kernel<<<grid, NT, SMEM_BYTES, st>>>(loss, params, X, y, n_rows, partials, err_flag);
+  prof_end(pi, st);
+  DLAS_LAUNCH_CHECK();
+  size_t n_tiles = (n_rows + TILE - 1) / TILE;
+  int n_active_pairs = (int)(n_tiles < (size_t)(grid / 2) ? n_tiles : (size_t)(grid / 2));
+  tc_reduce_kernel<<<(N_PARAMS + 1 + 255) / 256, 256, 0, st>>>(partials, n_active_pairs, err_flag, grad_sum);
+  DLAS_LAUNCH_CHECK();
+  return DLAS_OK;
+}
+
 }  // namespace dlas

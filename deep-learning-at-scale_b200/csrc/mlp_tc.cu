@@ -11,18 +11,25 @@
 //     p = relu(Z2h+b2h) . w3h                     per-row partial dot; the ONLY cross-CTA exchange
 //                                                 (128 floats through distributed shared memory)
 //     dZ2h = dy w3h relu'(Z2h)
-//     dW2[:, half] += H1^T dZ2h                   256 TMEM columns, accumulated over all tiles
+//     dW2[:, half] += H1^T dZ2h, db2h += dZ2h^T 1 256 + 16 TMEM columns, accumulated over all tiles
 //     dH1p = dZ2h W2[:, half]^T                   PARTIAL dH1; dZ1p = relu'(H1) o dH1p is linear in
 //     dW1p^T += dZ1p^T [X | 1]                    the partials, so each CTA just adds its share to
 //                                                 dW1 / db1 (column 32 of [X | 1] gives db1)
 // MMA floor per 128-row tile per CTA: 3584 cycles (256 + 1024 + 1024 + 1024 + 256), 93 % of the
-// 6680 SM-cycles the unsplit network needs per tile.  This version runs the phases back to back
-// (MMA, then its epilogue); overlap is the next step.
+// 6680 SM-cycles the unsplit network needs per tile.
+//
+// Warp roles (288 threads): warps 0-7 epilogue (warp w: TMEM lane quarter w%4 = rows, column half
+// w/4 of each 64-column chunk), warp 8 = MMA issuer.  Every GEMM whose result feeds an epilogue is
+// cut into N=64 chunks that alternate between two 64-column TMEM work buffers, so the epilogue of
+// chunk i runs under the MMA of chunk i+1; dW2 / db2 / dW1 accumulate in their own TMEM columns for
+// the whole launch and need no per-tile epilogue.  X tiles are double-buffered (tile t+1 is loaded
+// during tile t).  mbarriers: mma_done[b] (tcgen05.commit -> epilogue), buf_free[b] (epilogue ->
+// issuer), x_ready[j] / h1_ready / dz2_ready / dz1_ready (operands in smem -> issuer).
 //
 // Shared memory (fp16 tiles in the column-blocked SWIZZLE_128B layout of tc_common.cuh):
-//   sW1 [32][256] 16 KB | sW2 [256][128] 64 KB | sX [128][64] 16 KB ([x | 1 | 0]) | sH1 [128][256] 64 KB
-//   (dZ1 overwrites H1 in place) | sDZ2 [128][128] 32 KB | fp32: b1, b2h, w3h, y, exchange buffers
-// TMEM columns: [0,128) work | [128,384) dW2 half (two M=128 halves) | [384,432) and [448,496) dW1^T halves (N=48)
+//   sW1 [32][256] 16 KB | sW2 [256][128] 64 KB | sX[2] [128][64] 2x16 KB ([x | 1 | 0]) |
+//   sH1 [128][256] 64 KB (dZ1 overwrites it in place) | sDZ2 [128][128] 32 KB | ones [16][64] 2 KB | fp32 vectors
+// TMEM columns: [0,64) [64,128) work | [128,384) dW2 half | [384,432) [448,496) dW1^T halves | [496,512) db2
 #include "common.cuh"
 #include "tc_common.cuh"
 
@@ -34,21 +41,25 @@ using namespace tc;
 
 constexpr int D0 = 32, D1 = 256, D2 = 256;
 constexpr int TILE = 128;
-constexpr int NT = 128;
+constexpr int N_EPI = 256;            // epilogue threads (warps 0-7)
+constexpr int NT = N_EPI + 32;        // + MMA issuer warp
 constexpr int W1_OFF = 0, B1_OFF = W1_OFF + D0 * D1, W2_OFF = B1_OFF + D1, B2_OFF = W2_OFF + D1 * D2,
               W3_OFF = B2_OFF + D2, B3_OFF = W3_OFF + D2, N_PARAMS = B3_OFF + 1;
 constexpr size_t PSTRIDE = ((size_t)N_PARAMS + 1 + 3) & ~(size_t)3;
 
-constexpr uint32_t S_W1 = 0, S_W2 = S_W1 + 16384, S_X = S_W2 + 65536, S_H1 = S_X + 16384, S_DZ2 = S_H1 + 65536,
-                   S_F32 = S_DZ2 + 32768;
-// fp32 area (float index): b1[256] b2h[128] w3h[128] y[128] part[2][128] red[4][128] misc[16]
-constexpr int F_B1 = 0, F_B2 = 256, F_W3 = 384, F_Y = 512, F_PART = 640, F_RED = 896, F_MISC = 1408, F_END = 1424;
-constexpr uint32_t S_BAR = S_F32 + F_END * 4;   // mbarrier (8 B) + tmem base (4 B)
-constexpr uint32_t SMEM_BYTES = S_BAR + 16 + 1024;  // + slack for the 1024-B alignment of the base
+constexpr uint32_t S_W1 = 0, S_W2 = S_W1 + 16384, S_X = S_W2 + 65536, S_H1 = S_X + 2 * 16384, S_DZ2 = S_H1 + 65536,
+                   S_ONES = S_DZ2 + 32768, S_F32 = S_ONES + 2048;
+// fp32 area (float index)
+constexpr int F_B1 = 0, F_B2 = 256, F_W3 = 384, F_Y = 512 /*[2][128]*/, F_PART = 768 /*[2][128]*/, F_RP = 1024 /*[2][128]*/,
+              F_RED = 1280 /*[4][128]*/, F_END = 1792;
+constexpr uint32_t S_BAR = S_F32 + F_END * 4;
+enum { B_DONE0 = 0, B_DONE1, B_FREE0, B_FREE1, B_X0, B_X1, B_H1, B_DZ2, B_DZ1, B_ALL, N_BARS };
+constexpr uint32_t S_TMEM = S_BAR + N_BARS * 8;
+constexpr uint32_t SMEM_BYTES = S_TMEM + 16;
 
-constexpr uint32_t TM_WORK = 0, TM_DW2 = 128, TM_DW1 = 384, TM_COLS = 512;
+constexpr uint32_t TM_W0 = 0, TM_DW2 = 128, TM_DW1 = 384, TM_DB2 = 496, TM_COLS = 512;
 
-// out: lane l holds sum over the warp's 32 lanes of v[l]
+// out: lane l holds the sum over the warp's 32 lanes of v[l]
 __device__ __forceinline__ float warp_colsum32(float (&v)[32], int lane) {
 #pragma unroll
   for (int s = 16; s >= 1; s >>= 1) {
@@ -63,49 +74,66 @@ __device__ __forceinline__ float warp_colsum32(float (&v)[32], int lane) {
   return v[0];
 }
 
+__device__ __forceinline__ uint4 pack8(float4 a, float4 b) {
+  return make_uint4(pack_half2(a.x, a.y), pack_half2(a.z, a.w), pack_half2(b.x, b.y), pack_half2(b.z, b.w));
+}
+
 __global__ void __cluster_dims__(2, 1, 1) __launch_bounds__(NT, 1)
 mlp_tc_kernel(const int loss_kind, const float* __restrict__ params, const float* __restrict__ X,
               const float* __restrict__ y, const size_t n_rows, float* __restrict__ partials,
               int* __restrict__ err_flag) {
-  extern __shared__ uint8_t smem_raw[];
-  uint8_t* smem = reinterpret_cast<uint8_t*>((reinterpret_cast<uintptr_t>(smem_raw) + 1023) & ~(uintptr_t)1023);
+  extern __shared__ __align__(1024) uint8_t smem[];
   float* f32 = reinterpret_cast<float*>(smem + S_F32);
-  uint64_t* bar = reinterpret_cast<uint64_t*>(smem + S_BAR);
-  uint32_t* tmem_slot = reinterpret_cast<uint32_t*>(smem + S_BAR + 8);
-  const uint32_t sW1 = smem_u32(smem + S_W1), sW2 = smem_u32(smem + S_W2), sX = smem_u32(smem + S_X),
-                 sH1 = smem_u32(smem + S_H1), sDZ2 = smem_u32(smem + S_DZ2);
+  uint64_t* bars = reinterpret_cast<uint64_t*>(smem + S_BAR);
+  uint32_t* tmem_slot = reinterpret_cast<uint32_t*>(smem + S_TMEM);
+  const uint32_t sbase = smem_u32(smem);
+  const uint32_t sW1 = sbase + S_W1, sW2 = sbase + S_W2, sX = sbase + S_X, sH1 = sbase + S_H1, sDZ2 = sbase + S_DZ2,
+                 sONES = sbase + S_ONES, sF = sbase + S_F32;
 
   const int tid = threadIdx.x, warp = tid >> 5, lane = tid & 31;
   const uint32_t rank = cluster_ctarank();
   const int pair = blockIdx.x >> 1, n_pairs = gridDim.x >> 1;
   const size_t n_tiles = (n_rows + TILE - 1) / TILE;
+  bool ok = (sbase & 1023u) == 0;   // the swizzled tile layout needs a 1024-byte aligned base
 
-  // ---- one-time set-up: barrier, TMEM, weights -> fp16 tiles ---------------------------------------
-  if (tid == 0) { mbar_init(bar, 1); mbar_fence_init(); }
-  if (warp == 0) tmem_alloc(tmem_slot, TM_COLS);
+  // ---- one-time set-up: barriers, TMEM, weights -> fp16 tiles -------------------------------------------
+  if (tid == 0) {
+    mbar_init(&bars[B_DONE0], 1); mbar_init(&bars[B_DONE1], 1);
+    mbar_init(&bars[B_FREE0], N_EPI); mbar_init(&bars[B_FREE1], N_EPI);
+    mbar_init(&bars[B_X0], N_EPI); mbar_init(&bars[B_X1], N_EPI);
+    mbar_init(&bars[B_H1], N_EPI); mbar_init(&bars[B_DZ2], N_EPI); mbar_init(&bars[B_DZ1], N_EPI);
+    mbar_init(&bars[B_ALL], 1);
+    mbar_fence_init();
+  }
+  if (warp == 8) tmem_alloc(tmem_slot, TM_COLS);
   {
     const float* W1 = params + W1_OFF;                        // [32][256]
+#pragma unroll 4
     for (int idx = tid; idx < D0 * (D1 / 8); idx += NT) {
-      int r = idx / (D1 / 8), c = (idx % (D1 / 8)) * 8;
+      const int r = idx / (D1 / 8), c = (idx % (D1 / 8)) * 8;
       float4 a = __ldg(reinterpret_cast<const float4*>(W1 + r * D1 + c));
       float4 b = __ldg(reinterpret_cast<const float4*>(W1 + r * D1 + c + 4));
-      uint4 h = make_uint4(pack_half2(a.x, a.y), pack_half2(a.z, a.w), pack_half2(b.x, b.y), pack_half2(b.z, b.w));
-      *reinterpret_cast<uint4*>(smem + S_W1 + tile_chunk_off(D0, r, c)) = h;
+      sts128(sW1 + tile_chunk_off(D0, r, c), pack8(a, b));
     }
     const float* W2 = params + W2_OFF + rank * 128;           // [256][256], my 128 out-columns
+#pragma unroll 8
     for (int idx = tid; idx < D1 * 16; idx += NT) {
-      int r = idx >> 4, c = (idx & 15) * 8;
+      const int r = idx >> 4, c = (idx & 15) * 8;
       float4 a = __ldg(reinterpret_cast<const float4*>(W2 + (size_t)r * D2 + c));
       float4 b = __ldg(reinterpret_cast<const float4*>(W2 + (size_t)r * D2 + c + 4));
-      uint4 h = make_uint4(pack_half2(a.x, a.y), pack_half2(a.z, a.w), pack_half2(b.x, b.y), pack_half2(b.z, b.w));
-      *reinterpret_cast<uint4*>(smem + S_W2 + tile_chunk_off(D1, r, c)) = h;
+      sts128(sW2 + tile_chunk_off(D1, r, c), pack8(a, b));
     }
     for (int i = tid; i < D1; i += NT) f32[F_B1 + i] = __ldg(params + B1_OFF + i);
-    f32[F_B2 + tid] = __ldg(params + B2_OFF + rank * 128 + tid);
-    f32[F_W3 + tid] = __ldg(params + W3_OFF + rank * 128 + tid);
-    // constant part of [x | 1 | 0]: column 32 = 1, columns 33..63 = 0
-    *reinterpret_cast<uint4*>(smem + S_X + tile_chunk_off(TILE, tid, 32)) = make_uint4(0x00003C00u, 0u, 0u, 0u);
-    for (int c = 40; c < 64; c += 8) *reinterpret_cast<uint4*>(smem + S_X + tile_chunk_off(TILE, tid, c)) = make_uint4(0u, 0u, 0u, 0u);
+    if (tid < 128) {
+      f32[F_B2 + tid] = __ldg(params + B2_OFF + rank * 128 + tid);
+      f32[F_W3 + tid] = __ldg(params + W3_OFF + rank * 128 + tid);
+      // constant part of [x | 1 | 0] in both X buffers: column 32 = 1, columns 33..63 = 0
+      for (int j = 0; j < 2; ++j) {
+        sts128(sX + j * 16384 + tile_chunk_off(TILE, tid, 32), make_uint4(0x00003C00u, 0u, 0u, 0u));
+        for (int c = 40; c < 64; c += 8) sts128(sX + j * 16384 + tile_chunk_off(TILE, tid, c), make_uint4(0u, 0u, 0u, 0u));
+      }
+      sts128(sONES + tid * 16, make_uint4(0x3C003C00u, 0x3C003C00u, 0x3C003C00u, 0x3C003C00u));  // 2 KB of fp16 1.0
+    }
   }
   const float b3 = __ldg(params + B3_OFF);
   fence_async_smem();
@@ -114,253 +142,313 @@ mlp_tc_kernel(const int loss_kind, const float* __restrict__ params, const float
   fence_after();
   cluster_sync_all();  // the peer CTA is running: its shared memory may be written from here on
   const uint32_t tm = *tmem_slot;
-  const uint32_t lane_base = (uint32_t)(warp * 32) << 16;
-  const uint32_t peer_part = map_to_cta(smem_u32(f32 + F_PART), rank ^ 1u);
 
-  constexpr uint32_t ID_KM_MN_128 = make_idesc(128, 128, false, true);   // A K-major, B MN-major
-  constexpr uint32_t ID_MN_MN_128 = make_idesc(128, 128, true, true);
-  constexpr uint32_t ID_KM_KM_128 = make_idesc(128, 128, false, false);
-  constexpr uint32_t ID_MN_MN_48 = make_idesc(128, 48, true, true);
+  const int my_tiles = (n_tiles > (size_t)pair) ? (int)((n_tiles - pair + n_pairs - 1) / n_pairs) : 0;
 
-  uint32_t parity = 0;
-  bool ok = true;
-  bool first = true;
-  float acc_w3[4] = {0.f, 0.f, 0.f, 0.f}, acc_b2[4] = {0.f, 0.f, 0.f, 0.f};  // column (chunk*32 + lane) sums of this warp's rows
-  float acc_loss = 0.f, acc_b3 = 0.f;
-  int it = 0;
-
-  for (size_t tile = pair; tile < n_tiles; tile += n_pairs, ++it) {
-    const size_t row0 = tile * TILE;
-    const int nr = (int)((n_rows - row0) < (size_t)TILE ? (n_rows - row0) : (size_t)TILE);
-    // ---- (a) X tile (fp32 -> fp16) and targets -----------------------------------------------------
-    {
-      const float* xr = X + (row0 + tid) * (size_t)D0;
+  if (warp == 8) {
+    // =========================== MMA issuer ===========================
+    constexpr uint32_t ID_KM_MN_64 = make_idesc(128, 64, false, true);
+    constexpr uint32_t ID_KM_KM_64 = make_idesc(128, 64, false, false);
+    constexpr uint32_t ID_MN_MN_128 = make_idesc(128, 128, true, true);
+    constexpr uint32_t ID_MN_MN_48 = make_idesc(128, 48, true, true);
+    constexpr uint32_t ID_MN_KM_16 = make_idesc(128, 16, true, false);
+    uint32_t n = 0;  // running index of chunk GEMMs; buffer = n & 1
+    for (int it = 0; it < my_tiles; ++it) {
+      const uint32_t sXc = sX + (uint32_t)(it & 1) * 16384;
+      const bool first = (it == 0);
+      if (lane == 0) {
+        ok = mbar_wait(&bars[B_X0 + (it & 1)], (it >> 1) & 1) && ok;
+        // Z1 = X W1: four N=64 chunks
+        for (int s = 0; s < 4; ++s, ++n) {
+          const uint32_t b = n & 1;
+          ok = mbar_wait(&bars[B_FREE0 + b], ((n >> 1) & 1) ^ 1) && ok;
+          fence_after();
 #pragma unroll
-      for (int q = 0; q < 4; ++q) {
-        uint4 h = make_uint4(0u, 0u, 0u, 0u);
-        if (tid < nr) {
-          float4 a = __ldcs(reinterpret_cast<const float4*>(xr + q * 8));
-          float4 b = __ldcs(reinterpret_cast<const float4*>(xr + q * 8 + 4));
-          h = make_uint4(pack_half2(a.x, a.y), pack_half2(a.z, a.w), pack_half2(b.x, b.y), pack_half2(b.z, b.w));
+          for (int k = 0; k < D0; k += 16)
+            mma_f16(tm + TM_W0 + b * 64, desc_kmajor(sXc, TILE, 0, k), desc_mnmajor(sW1, D0, s * 64, k), ID_KM_MN_64, k > 0);
+          mma_commit(&bars[B_DONE0 + b]);
         }
-        *reinterpret_cast<uint4*>(smem + S_X + tile_chunk_off(TILE, tid, q * 8)) = h;
+        // Z2h = H1 W2h: two N=64 chunks
+        ok = mbar_wait(&bars[B_H1], it & 1) && ok;
+        for (int s = 0; s < 2; ++s, ++n) {
+          const uint32_t b = n & 1;
+          ok = mbar_wait(&bars[B_FREE0 + b], ((n >> 1) & 1) ^ 1) && ok;
+          fence_after();
+#pragma unroll
+          for (int k = 0; k < D1; k += 16)
+            mma_f16(tm + TM_W0 + b * 64, desc_kmajor(sH1, TILE, 0, k), desc_mnmajor(sW2, D1, s * 64, k), ID_KM_MN_64, k > 0);
+          mma_commit(&bars[B_DONE0 + b]);
+        }
       }
-      f32[F_Y + tid] = (tid < nr) ? __ldcs(y + row0 + tid) : 0.f;
-    }
-    fence_async_smem();
-    fence_before();
-    __syncthreads();
-    // ---- (b) Z1 = X W1 in two N=128 chunks; H1 = relu(Z1 + b1) -> sH1 -------------------------------
-#pragma unroll 1
-    for (int j = 0; j < 2; ++j) {
-      if (tid == 0) {
+      __syncwarp();
+      cluster_sync_all();   // pairs with the epilogue warps' exchange of the partial output dots
+      if (lane == 0) {
+        ok = mbar_wait(&bars[B_DZ2], it & 1) && ok;
         fence_after();
+        // db2h += dZ2h^T 1 ; dW2h += H1^T dZ2h (accumulate over the whole launch)
 #pragma unroll
-        for (int k = 0; k < D0; k += 16)
-          mma_f16(tm + TM_WORK, desc_kmajor(sX, TILE, 0, k), desc_mnmajor(sW1, D0, j * 128, k), ID_KM_MN_128, k > 0);
-        mma_commit(bar);
-      }
-      ok = mbar_wait(bar, parity) && ok;
-      parity ^= 1;
-      fence_after();
+        for (int k = 0; k < TILE; k += 16)
+          mma_f16(tm + TM_DB2, desc_mnmajor(sDZ2, TILE, 0, k), desc_kmajor(sONES, 16, 0, 0), ID_MN_KM_16, !(first && k == 0));
 #pragma unroll 1
-      for (int c0 = 0; c0 < 128; c0 += 32) {
-        uint32_t v[32];
-        tmem_ld32(tm + TM_WORK + lane_base + c0, v);
-        tmem_ld_wait();
+        for (int mh = 0; mh < 2; ++mh)
 #pragma unroll
-        for (int q = 0; q < 4; ++q) {
-          const float4 ba = *reinterpret_cast<const float4*>(f32 + F_B1 + j * 128 + c0 + q * 8);
-          const float4 bb = *reinterpret_cast<const float4*>(f32 + F_B1 + j * 128 + c0 + q * 8 + 4);
-          float h0 = fmaxf(__uint_as_float(v[q * 8 + 0]) + ba.x, 0.f), h1 = fmaxf(__uint_as_float(v[q * 8 + 1]) + ba.y, 0.f);
-          float h2 = fmaxf(__uint_as_float(v[q * 8 + 2]) + ba.z, 0.f), h3 = fmaxf(__uint_as_float(v[q * 8 + 3]) + ba.w, 0.f);
-          float h4 = fmaxf(__uint_as_float(v[q * 8 + 4]) + bb.x, 0.f), h5 = fmaxf(__uint_as_float(v[q * 8 + 5]) + bb.y, 0.f);
-          float h6 = fmaxf(__uint_as_float(v[q * 8 + 6]) + bb.z, 0.f), h7 = fmaxf(__uint_as_float(v[q * 8 + 7]) + bb.w, 0.f);
-          *reinterpret_cast<uint4*>(smem + S_H1 + tile_chunk_off(TILE, tid, j * 128 + c0 + q * 8)) =
-              make_uint4(pack_half2(h0, h1), pack_half2(h2, h3), pack_half2(h4, h5), pack_half2(h6, h7));
+          for (int k = 0; k < TILE; k += 16)
+            mma_f16(tm + TM_DW2 + mh * 128, desc_mnmajor(sH1, TILE, mh * 128, k), desc_mnmajor(sDZ2, TILE, 0, k), ID_MN_MN_128,
+                    !(first && k == 0));
+        // dH1p = dZ2h W2h^T: four N=64 chunks (in-index)
+        for (int s = 0; s < 4; ++s, ++n) {
+          const uint32_t b = n & 1;
+          ok = mbar_wait(&bars[B_FREE0 + b], ((n >> 1) & 1) ^ 1) && ok;
+          fence_after();
+#pragma unroll
+          for (int k = 0; k < 128; k += 16)
+            mma_f16(tm + TM_W0 + b * 64, desc_kmajor(sDZ2, TILE, 0, k), desc_kmajor(sW2, D1, s * 64, k), ID_KM_KM_64, k > 0);
+          mma_commit(&bars[B_DONE0 + b]);
+        }
+        // dW1p^T += dZ1p^T [X | 1]
+        ok = mbar_wait(&bars[B_DZ1], it & 1) && ok;
+        fence_after();
+#pragma unroll 1
+        for (int mh = 0; mh < 2; ++mh)
+#pragma unroll
+          for (int k = 0; k < TILE; k += 16)
+            mma_f16(tm + TM_DW1 + mh * 64, desc_mnmajor(sH1, TILE, mh * 128, k), desc_mnmajor(sXc, TILE, 0, k), ID_MN_MN_48,
+                    !(first && k == 0));
+      }
+      __syncwarp();
+    }
+    if (lane == 0) mma_commit(&bars[B_ALL]);
+    __syncwarp();
+  } else {
+    // =========================== epilogue warps ===========================
+    const int q = warp & 3, hh = warp >> 2;
+    const int row = q * 32 + lane;                      // TMEM lane = tile row
+    const uint32_t lane_base = (uint32_t)(q * 32) << 16;
+    const uint32_t peer_part = map_to_cta(sF + F_PART * 4, rank ^ 1u);
+    float acc_w3[2] = {0.f, 0.f};
+    float acc_loss = 0.f, acc_b3 = 0.f;
+    uint32_t n = 0;
+    // X tile loader: thread -> (row tid>>1, 16 features (tid&1)*16..)
+    const int xr = tid >> 1, xh = tid & 1;
+    float4 xv[4];
+    float yv = 0.f;
+    auto x_issue = [&](size_t tile) {
+      const size_t row0 = tile * TILE;
+      const bool in = row0 + xr < n_rows;
+      const float* src = X + (row0 + xr) * (size_t)D0 + xh * 16;
+#pragma unroll
+      for (int i = 0; i < 4; ++i) xv[i] = in ? __ldcs(reinterpret_cast<const float4*>(src + i * 4)) : make_float4(0.f, 0.f, 0.f, 0.f);
+      if (tid < TILE) yv = (row0 + tid < n_rows) ? __ldcs(y + row0 + tid) : 0.f;
+    };
+    auto x_store = [&](int j) {
+      sts128(sX + j * 16384 + tile_chunk_off(TILE, xr, xh * 16), pack8(xv[0], xv[1]));
+      sts128(sX + j * 16384 + tile_chunk_off(TILE, xr, xh * 16 + 8), pack8(xv[2], xv[3]));
+      if (tid < TILE) f32[F_Y + j * 128 + tid] = yv;
+      fence_async_smem();
+      mbar_arrive(&bars[B_X0 + j]);
+    };
+    if (my_tiles > 0) {
+      x_issue(pair);
+      x_store(0);
+    }
+    for (int it = 0; it < my_tiles; ++it) {
+      const size_t tile = (size_t)pair + (size_t)it * n_pairs;
+      const size_t row0 = tile * TILE;
+      const bool row_valid = row0 + row < n_rows;
+      if (it + 1 < my_tiles) x_issue(tile + n_pairs);      // next tile's rows: in flight during phase (b)
+      // ---- (b) H1 = relu(Z1 + b1) -> sH1, four chunks ------------------------------------------------
+#pragma unroll 1
+      for (int s = 0; s < 4; ++s, ++n) {
+        const uint32_t b = n & 1;
+        ok = mbar_wait(&bars[B_DONE0 + b], (n >> 1) & 1) && ok;
+        fence_after();
+        uint32_t v[32];
+        tmem_ld32(tm + TM_W0 + b * 64 + lane_base + hh * 32, v);
+        tmem_ld_wait();
+        fence_before();
+        mbar_arrive(&bars[B_FREE0 + b]);
+        const int c0 = s * 64 + hh * 32;
+#pragma unroll
+        for (int g8 = 0; g8 < 4; ++g8) {
+          const float4 ba = lds128f(sF + (F_B1 + c0 + g8 * 8) * 4), bb = lds128f(sF + (F_B1 + c0 + g8 * 8 + 4) * 4);
+          float4 lo = make_float4(fmaxf(__uint_as_float(v[g8 * 8 + 0]) + ba.x, 0.f), fmaxf(__uint_as_float(v[g8 * 8 + 1]) + ba.y, 0.f),
+                                  fmaxf(__uint_as_float(v[g8 * 8 + 2]) + ba.z, 0.f), fmaxf(__uint_as_float(v[g8 * 8 + 3]) + ba.w, 0.f));
+          float4 hi = make_float4(fmaxf(__uint_as_float(v[g8 * 8 + 4]) + bb.x, 0.f), fmaxf(__uint_as_float(v[g8 * 8 + 5]) + bb.y, 0.f),
+                                  fmaxf(__uint_as_float(v[g8 * 8 + 6]) + bb.z, 0.f), fmaxf(__uint_as_float(v[g8 * 8 + 7]) + bb.w, 0.f));
+          sts128(sH1 + tile_chunk_off(TILE, row, c0 + g8 * 8), pack8(lo, hi));
         }
       }
       fence_async_smem();
-      fence_before();
-      __syncthreads();
-    }
-    // ---- (c) Z2h = H1 W2h; partial output dot; exchange; dZ2h -> sDZ2 ---------------------------------
-    if (tid == 0) {
-      fence_after();
+      mbar_arrive(&bars[B_H1]);
+      if (it + 1 < my_tiles) x_store((it + 1) & 1);        // the other X buffer was last read by tile it-1's dW1
+      // ---- (c) Z2h: partial output dot, exchange, dZ2h -> sDZ2 ---------------------------------------
+      float part = 0.f;
+      const uint32_t n_c = n;
+      n += 2;
 #pragma unroll
-      for (int k = 0; k < D1; k += 16)
-        mma_f16(tm + TM_WORK, desc_kmajor(sH1, TILE, 0, k), desc_mnmajor(sW2, D1, 0, k), ID_KM_MN_128, k > 0);
-      mma_commit(bar);
-    }
-    ok = mbar_wait(bar, parity) && ok;
-    parity ^= 1;
-    fence_after();
-    float part = 0.f;
-#pragma unroll 1
-    for (int c0 = 0; c0 < 128; c0 += 32) {
-      uint32_t v[32];
-      tmem_ld32(tm + TM_WORK + lane_base + c0, v);
-      tmem_ld_wait();
-#pragma unroll
-      for (int i = 0; i < 32; ++i)
-        part = fmaf(fmaxf(__uint_as_float(v[i]) + f32[F_B2 + c0 + i], 0.f), f32[F_W3 + c0 + i], part);
-    }
-    const int buf = it & 1;
-    st_cluster_f32(peer_part + (uint32_t)(buf * 128 + tid) * 4, part);
-    cluster_sync_all();
-    const float other = f32[F_PART + buf * 128 + tid];
-    const float yhat = (rank == 0 ? part + other : other + part) + b3;   // same value on both CTAs
-    float g = 0.f;
-    if (tid < nr) {
-      const float d = yhat - f32[F_Y + tid];
-      if (loss_kind == DLAS_LOSS_MSE) {
-        acc_loss += d * d;
-        g = 2.0f * d;
-      } else {  // cnn.py:29-32, CLIP_VALUE = 6
-        const float a = fabsf(d);
-        acc_loss += fminf(a, 6.0f);
-        g = (a <= 6.0f) ? (d > 0.f ? 1.f : (d < 0.f ? -1.f : 0.f)) : 0.f;
-      }
-    }
-    acc_b3 += g;
-#pragma unroll 1
-    for (int c0 = 0; c0 < 128; c0 += 32) {
-      uint32_t v[32];
-      tmem_ld32(tm + TM_WORK + lane_base + c0, v);
-      tmem_ld_wait();
-      float hg[32], dz[32];
-#pragma unroll
-      for (int i = 0; i < 32; ++i) {
-        const float z = __uint_as_float(v[i]) + f32[F_B2 + c0 + i];
-        hg[i] = fmaxf(z, 0.f) * g;                               // -> dw3
-        dz[i] = z > 0.f ? g * f32[F_W3 + c0 + i] : 0.f;          // -> dZ2, db2
-      }
-#pragma unroll
-      for (int q = 0; q < 4; ++q)
-        *reinterpret_cast<uint4*>(smem + S_DZ2 + tile_chunk_off(TILE, tid, c0 + q * 8)) =
-            make_uint4(pack_half2(dz[q * 8 + 0], dz[q * 8 + 1]), pack_half2(dz[q * 8 + 2], dz[q * 8 + 3]),
-                       pack_half2(dz[q * 8 + 4], dz[q * 8 + 5]), pack_half2(dz[q * 8 + 6], dz[q * 8 + 7]));
-      acc_w3[c0 >> 5] += warp_colsum32(hg, lane);
-      acc_b2[c0 >> 5] += warp_colsum32(dz, lane);
-    }
-    fence_async_smem();
-    fence_before();
-    __syncthreads();
-    // ---- (d) dW2h += H1^T dZ2h; dH1p = dZ2h W2h^T in two N=128 chunks; dZ1p = relu'(H1) o dH1p in place
-#pragma unroll 1
-    for (int j = 0; j < 2; ++j) {
-      if (tid == 0) {
+      for (int s = 0; s < 2; ++s) {
+        const uint32_t b = (n_c + s) & 1;
+        ok = mbar_wait(&bars[B_DONE0 + b], ((n_c + s) >> 1) & 1) && ok;
         fence_after();
-        if (j == 0) {
-#pragma unroll 1
-          for (int mh = 0; mh < 2; ++mh)
-#pragma unroll
-            for (int k = 0; k < TILE; k += 16)
-              mma_f16(tm + TM_DW2 + mh * 128, desc_mnmajor(sH1, TILE, mh * 128, k), desc_mnmajor(sDZ2, TILE, 0, k),
-                      ID_MN_MN_128, !(first && k == 0));
-        }
-#pragma unroll
-        for (int k = 0; k < 128; k += 16)
-          mma_f16(tm + TM_WORK, desc_kmajor(sDZ2, TILE, 0, k), desc_kmajor(sW2, D1, j * 128, k), ID_KM_KM_128, k > 0);
-        mma_commit(bar);
-      }
-      ok = mbar_wait(bar, parity) && ok;
-      parity ^= 1;
-      fence_after();
-#pragma unroll 1
-      for (int c0 = 0; c0 < 128; c0 += 32) {
         uint32_t v[32];
-        tmem_ld32(tm + TM_WORK + lane_base + c0, v);
+        tmem_ld32(tm + TM_W0 + b * 64 + lane_base + hh * 32, v);
         tmem_ld_wait();
+        const int c0 = s * 64 + hh * 32;
 #pragma unroll
-        for (int q = 0; q < 4; ++q) {
-          uint4* p = reinterpret_cast<uint4*>(smem + S_H1 + tile_chunk_off(TILE, tid, j * 128 + c0 + q * 8));
-          const uint4 h = *p;
+        for (int g4 = 0; g4 < 8; ++g4) {
+          const float4 bv = lds128f(sF + (F_B2 + c0 + g4 * 4) * 4), wv = lds128f(sF + (F_W3 + c0 + g4 * 4) * 4);
+          part = fmaf(fmaxf(__uint_as_float(v[g4 * 4 + 0]) + bv.x, 0.f), wv.x, part);
+          part = fmaf(fmaxf(__uint_as_float(v[g4 * 4 + 1]) + bv.y, 0.f), wv.y, part);
+          part = fmaf(fmaxf(__uint_as_float(v[g4 * 4 + 2]) + bv.z, 0.f), wv.z, part);
+          part = fmaf(fmaxf(__uint_as_float(v[g4 * 4 + 3]) + bv.w, 0.f), wv.w, part);
+        }
+      }
+      const int buf = it & 1;
+      f32[F_RP + hh * 128 + row] = part;
+      named_bar_sync(1, N_EPI);
+      const float mine = f32[F_RP + row] + f32[F_RP + 128 + row];
+      if (hh == 0) st_cluster_f32(peer_part + (uint32_t)(buf * 128 + row) * 4, mine);
+      cluster_sync_all();
+      const float other = f32[F_PART + buf * 128 + row];
+      const float yhat = (rank == 0 ? mine + other : other + mine) + b3;   // same value on both CTAs
+      float g = 0.f;
+      if (row_valid) {
+        const float d = yhat - f32[F_Y + buf * 128 + row];
+        float lo;
+        if (loss_kind == DLAS_LOSS_MSE) {
+          lo = d * d;
+          g = 2.0f * d;
+        } else {  // cnn.py:29-32, CLIP_VALUE = 6
+          const float a = fabsf(d);
+          lo = fminf(a, 6.0f);
+          g = (a <= 6.0f) ? (d > 0.f ? 1.f : (d < 0.f ? -1.f : 0.f)) : 0.f;
+        }
+        if (hh == 0) { acc_loss += lo; acc_b3 += g; }
+      }
+      // second pass over Z2h (still in the two work buffers; the issuer needs them again only for dH1p)
+#pragma unroll
+      for (int s = 0; s < 2; ++s) {
+        const uint32_t b = (n_c + s) & 1;
+        const int c0 = s * 64 + hh * 32;
+        uint32_t v[32];
+        tmem_ld32(tm + TM_W0 + b * 64 + lane_base + hh * 32, v);
+        tmem_ld_wait();
+        fence_before();
+        mbar_arrive(&bars[B_FREE0 + b]);
+        float hg[32];
+#pragma unroll
+        for (int g8 = 0; g8 < 4; ++g8) {
+          const float4 wa = lds128f(sF + (F_W3 + c0 + g8 * 8) * 4), wb = lds128f(sF + (F_W3 + c0 + g8 * 8 + 4) * 4);
+          const float4 ba = lds128f(sF + (F_B2 + c0 + g8 * 8) * 4), bb = lds128f(sF + (F_B2 + c0 + g8 * 8 + 4) * 4);
+          const float w8[8] = {wa.x, wa.y, wa.z, wa.w, wb.x, wb.y, wb.z, wb.w};
+          const float b8[8] = {ba.x, ba.y, ba.z, ba.w, bb.x, bb.y, bb.z, bb.w};
+          float dz[8];
+#pragma unroll
+          for (int e = 0; e < 8; ++e) {
+            const float zz = __uint_as_float(v[g8 * 8 + e]) + b8[e];
+            hg[g8 * 8 + e] = fmaxf(zz, 0.f) * g;                 // -> dw3
+            dz[e] = zz > 0.f ? g * w8[e] : 0.f;                  // -> dZ2
+          }
+          sts128(sDZ2 + tile_chunk_off(TILE, row, c0 + g8 * 8),
+                 make_uint4(pack_half2(dz[0], dz[1]), pack_half2(dz[2], dz[3]), pack_half2(dz[4], dz[5]), pack_half2(dz[6], dz[7])));
+        }
+        acc_w3[s] += warp_colsum32(hg, lane);
+      }
+      fence_async_smem();
+      mbar_arrive(&bars[B_DZ2]);
+      // ---- (d) dZ1p = relu'(H1) o dH1p in place over H1, four chunks -----------------------------------
+#pragma unroll 1
+      for (int s = 0; s < 4; ++s, ++n) {
+        const uint32_t b = n & 1;
+        ok = mbar_wait(&bars[B_DONE0 + b], (n >> 1) & 1) && ok;
+        fence_after();
+        uint32_t v[32];
+        tmem_ld32(tm + TM_W0 + b * 64 + lane_base + hh * 32, v);
+        tmem_ld_wait();
+        fence_before();
+        mbar_arrive(&bars[B_FREE0 + b]);
+        const int c0 = s * 64 + hh * 32;
+#pragma unroll
+        for (int g8 = 0; g8 < 4; ++g8) {
+          const uint32_t a = sH1 + tile_chunk_off(TILE, row, c0 + g8 * 8);
+          const uint4 h = lds128(a);
           const uint32_t hw[4] = {h.x, h.y, h.z, h.w};
           uint32_t o[4];
 #pragma unroll
           for (int e = 0; e < 4; ++e) {
-            const float lo = (hw[e] & 0x7FFFu) ? __uint_as_float(v[q * 8 + 2 * e]) : 0.f;       // H1 > 0 (it is >= 0)
-            const float hi = (hw[e] & 0x7FFF0000u) ? __uint_as_float(v[q * 8 + 2 * e + 1]) : 0.f;
+            const float lo = (hw[e] & 0x7FFFu) ? __uint_as_float(v[g8 * 8 + 2 * e]) : 0.f;       // H1 > 0 (it is >= 0)
+            const float hi = (hw[e] & 0x7FFF0000u) ? __uint_as_float(v[g8 * 8 + 2 * e + 1]) : 0.f;
             o[e] = pack_half2(lo, hi);
           }
-          *p = make_uint4(o[0], o[1], o[2], o[3]);
+          sts128(a, make_uint4(o[0], o[1], o[2], o[3]));
         }
       }
       fence_async_smem();
-      fence_before();
-      __syncthreads();
+      mbar_arrive(&bars[B_DZ1]);
     }
-    // ---- (e) dW1p^T += dZ1p^T [X | 1] (column 32 -> db1) ------------------------------------------------
-    if (tid == 0) {
+
+    // ---- drain the accumulators into this CTA's partial vector -----------------------------------------
+    float* my = partials + (size_t)blockIdx.x * PSTRIDE;
+    if (my_tiles > 0) {
+      ok = mbar_wait(&bars[B_ALL], 0) && ok;
       fence_after();
 #pragma unroll 1
-      for (int mh = 0; mh < 2; ++mh)
-#pragma unroll
-        for (int k = 0; k < TILE; k += 16)
-          mma_f16(tm + TM_DW1 + mh * 64, desc_mnmajor(sH1, TILE, mh * 128, k), desc_mnmajor(sX, TILE, 0, k), ID_MN_MN_48,
-                  !(first && k == 0));
-      mma_commit(bar);
-    }
-    ok = mbar_wait(bar, parity) && ok;   // sX and sH1 are free for the next tile
-    parity ^= 1;
-    fence_after();
-    first = false;
-  }
-
-  // ---- drain the accumulators into this CTA's partial vector ---------------------------------------
-  float* my = partials + (size_t)blockIdx.x * PSTRIDE;
-  if (!first) {
+      for (int mh = 0; mh < 2; ++mh) {
+        float* dst = my + W2_OFF + (size_t)(mh * 128 + row) * D2 + rank * 128 + hh * 64;   // row in = mh*128+row
 #pragma unroll 1
-    for (int mh = 0; mh < 2; ++mh) {
-      float* dst = my + W2_OFF + (size_t)(mh * 128 + tid) * D2 + rank * 128;   // row in = mh*128+tid, my out-columns
-#pragma unroll 1
-      for (int c0 = 0; c0 < 128; c0 += 32) {
-        uint32_t v[32];
-        tmem_ld32(tm + TM_DW2 + mh * 128 + lane_base + c0, v);
-        tmem_ld_wait();
+        for (int c0 = 0; c0 < 64; c0 += 32) {
+          uint32_t v[32];
+          tmem_ld32(tm + TM_DW2 + mh * 128 + lane_base + hh * 64 + c0, v);
+          tmem_ld_wait();
 #pragma unroll
-        for (int q = 0; q < 8; ++q)
-          *reinterpret_cast<float4*>(dst + c0 + q * 4) = make_float4(__uint_as_float(v[q * 4]), __uint_as_float(v[q * 4 + 1]),
-                                                                     __uint_as_float(v[q * 4 + 2]), __uint_as_float(v[q * 4 + 3]));
+          for (int i = 0; i < 8; ++i)
+            *reinterpret_cast<float4*>(dst + c0 + i * 4) = make_float4(__uint_as_float(v[i * 4]), __uint_as_float(v[i * 4 + 1]),
+                                                                       __uint_as_float(v[i * 4 + 2]), __uint_as_float(v[i * 4 + 3]));
+        }
+        // dW1p^T: lane = h1 unit, column = input feature; column 32 = db1
+        const int h1 = mh * 128 + row;
+        if (hh == 0) {
+          uint32_t v[32];
+          tmem_ld32(tm + TM_DW1 + mh * 64 + lane_base, v);
+          tmem_ld_wait();
+#pragma unroll
+          for (int i = 0; i < 32; ++i) my[W1_OFF + i * D1 + h1] = __uint_as_float(v[i]);
+        } else {
+          uint32_t w[16];
+          tmem_ld16(tm + TM_DW1 + mh * 64 + lane_base + 32, w);
+          tmem_ld_wait();
+          my[B1_OFF + h1] = __uint_as_float(w[0]);
+        }
       }
-      // dW1p^T: lane = h1 unit, column = input feature; column 32 = db1
-      uint32_t v[32], w[16];
-      tmem_ld32(tm + TM_DW1 + mh * 64 + lane_base, v);
-      tmem_ld16(tm + TM_DW1 + mh * 64 + lane_base + 32, w);
-      tmem_ld_wait();
-      const int h1 = mh * 128 + tid;
-#pragma unroll
-      for (int i = 0; i < 32; ++i) my[W1_OFF + i * D1 + h1] = __uint_as_float(v[i]);
-      my[B1_OFF + h1] = __uint_as_float(w[0]);
-    }
-    // column sums held per warp -> add the four warps in warp order
-#pragma unroll
-    for (int c = 0; c < 4; ++c) f32[F_RED + warp * 128 + c * 32 + lane] = acc_w3[c];
-    __syncthreads();
-    my[W3_OFF + rank * 128 + tid] = (f32[F_RED + tid] + f32[F_RED + 128 + tid]) + (f32[F_RED + 256 + tid] + f32[F_RED + 384 + tid]);
-    __syncthreads();
-#pragma unroll
-    for (int c = 0; c < 4; ++c) f32[F_RED + warp * 128 + c * 32 + lane] = acc_b2[c];
-    __syncthreads();
-    my[B2_OFF + rank * 128 + tid] = (f32[F_RED + tid] + f32[F_RED + 128 + tid]) + (f32[F_RED + 256 + tid] + f32[F_RED + 384 + tid]);
-    __syncthreads();
-    // loss and db3: fixed-order sum over the 128 rows (rank 0 only contributes them)
-    f32[F_RED + tid] = acc_loss;
-    f32[F_RED + 128 + tid] = acc_b3;
-    __syncthreads();
-    if (rank == 0 && tid < 2) {
-      float s = 0.f;
-      for (int i = 0; i < 128; ++i) s += f32[F_RED + tid * 128 + i];
-      my[tid == 0 ? N_PARAMS : B3_OFF] = s;
+      if (hh == 0) {  // db2h: lane = out column, every accumulator column holds the same sum
+        uint32_t w[16];
+        tmem_ld16(tm + TM_DB2 + lane_base, w);
+        tmem_ld_wait();
+        my[B2_OFF + rank * 128 + row] = __uint_as_float(w[0]);
+      }
+      // dw3h: per-warp column sums -> add the four row quarters in order
+      f32[F_RED + q * 128 + hh * 32 + lane] = acc_w3[0];
+      f32[F_RED + q * 128 + 64 + hh * 32 + lane] = acc_w3[1];
+      named_bar_sync(1, N_EPI);
+      if (tid < 128)
+        my[W3_OFF + rank * 128 + tid] = (f32[F_RED + tid] + f32[F_RED + 128 + tid]) + (f32[F_RED + 256 + tid] + f32[F_RED + 384 + tid]);
+      named_bar_sync(1, N_EPI);
+      // loss and db3: fixed-order sum over the 128 rows (only rank 0 contributes them)
+      if (hh == 0) { f32[F_RED + row] = acc_loss; f32[F_RED + 128 + row] = acc_b3; }
+      named_bar_sync(1, N_EPI);
+      if (rank == 0 && tid < 2) {
+        float s = 0.f;
+        for (int i = 0; i < 128; ++i) s += f32[F_RED + tid * 128 + i];
+        my[tid == 0 ? N_PARAMS : B3_OFF] = s;
+      }
     }
   }
-  if (!ok && tid == 0) atomicExch(err_flag, 1);
+  if (!ok && lane == 0) atomicExch(err_flag, 1);
   // ---- teardown ----------------------------------------------------------------------------------------
   fence_before();
   __syncthreads();
   cluster_sync_all();   // do not exit while the peer may still write our exchange buffer
-  if (warp == 0) tmem_dealloc(tm, TM_COLS);
+  if (warp == 8) tmem_dealloc(tm, TM_COLS);
 }
 
 // grad_sum[i] = sum of the partials of the CTAs that own entry i, in CTA order:

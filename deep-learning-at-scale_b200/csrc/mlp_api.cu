@@ -19,6 +19,9 @@ bool tc_supported(const int* dims, int n_layers);
 size_t tc_workspace_bytes(const int* dims, int n_layers);
 int tc_grad(const int* dims, int n_layers, int loss, const float* params, const float* X, const float* y,
             size_t n_rows, float* grad_sum, void* workspace, size_t workspace_bytes, cudaStream_t st);
+int tc_fit_step(const int* dims, int n_layers, int loss, const dlas_opt_cfg* cfg, float* params, float* m, float* v,
+                const float* X, const float* y, size_t n_rows, uint64_t iteration, float* loss_out, void* workspace,
+                size_t workspace_bytes, cudaStream_t st);
 
 namespace {
 int check_common(const char* fn, const int* dims, int n_layers, int loss, int mode) {
@@ -95,10 +98,13 @@ extern "C" int dlas_mlp_fit_steps(const int* dims, int n_layers, int loss, int m
                  (long long)b, n_batches);
     const float* Xb = X + (size_t)b * batch * d0;
     const float* yb = y + (size_t)b * batch * dL;
-    if (mode == DLAS_MODE_TC)
-      rc = tc_grad(dims, n_layers, loss, params, Xb, yb, batch, grad_sum, workspace, workspace_bytes, st);
-    else
-      rc = simt_grad(dims, n_layers, loss, params, Xb, yb, batch, grad_sum, workspace, workspace_bytes, st);
+    if (mode == DLAS_MODE_TC) {   // gradient kernel + (reduction fused with the update): two launches per step
+      rc = tc_fit_step(dims, n_layers, loss, cfg, params, m, v, Xb, yb, batch, iteration0 + (uint64_t)s,
+                       step_losses ? step_losses + s : nullptr, workspace, workspace_bytes, st);
+      if (rc != DLAS_OK) return rc;
+      continue;
+    }
+    rc = simt_grad(dims, n_layers, loss, params, Xb, yb, batch, grad_sum, workspace, workspace_bytes, st);
     if (rc != DLAS_OK) return rc;
     rc = opt_step_impl(cfg, params, m, v, grad_sum, n_params, 1.0f / (float)batch, iteration0 + (uint64_t)s,
                        step_losses ? step_losses + s : nullptr, st);

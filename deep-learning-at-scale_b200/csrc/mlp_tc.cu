@@ -31,7 +31,9 @@
 //   sH1 [128][256] 64 KB (dZ1 overwrites it in place) | sDZ2 [128][128] 32 KB | ones [16][64] 2 KB | fp32 vectors
 // TMEM columns: [0,64) [64,128) work | [128,384) dW2 half | [384,432) [448,496) dW1^T halves | [496,512) db2
 #include "common.cuh"
+#include "optim_math.cuh"
 #include "tc_common.cuh"
+#include <stdlib.h>
 
 namespace dlas {
 size_t simt_workspace_bytes(const int* dims, int n_layers);
@@ -47,11 +49,12 @@ constexpr int W1_OFF = 0, B1_OFF = W1_OFF + D0 * D1, W2_OFF = B1_OFF + D1, B2_OF
               W3_OFF = B2_OFF + D2, B3_OFF = W3_OFF + D2, N_PARAMS = B3_OFF + 1;
 constexpr size_t PSTRIDE = ((size_t)N_PARAMS + 1 + 3) & ~(size_t)3;
 
-constexpr uint32_t S_W1 = 0, S_W2 = S_W1 + 16384, S_X = S_W2 + 65536, S_H1 = S_X + 2 * 16384, S_DZ2 = S_H1 + 65536,
+constexpr int K1 = 48;                // layer-1 contraction: 32 features + the ones column (bias row of W1) + 15 zero rows
+constexpr uint32_t S_W1 = 0, S_W2 = S_W1 + K1 * 4 * 128, S_X = S_W2 + 65536, S_H1 = S_X + 2 * 16384, S_DZ2 = S_H1 + 65536,
                    S_ONES = S_DZ2 + 32768, S_F32 = S_ONES + 2048;
 // fp32 area (float index)
-constexpr int F_B1 = 0, F_B2 = 256, F_W3 = 384, F_Y = 512 /*[2][128]*/, F_PART = 768 /*[2][128]*/, F_RP = 1024 /*[2][128]*/,
-              F_RED = 1280 /*[4][128]*/, F_END = 1792;
+constexpr int F_B2 = 0, F_W3 = 128, F_Y = 256 /*[2][128]*/, F_PART = 512 /*[2][128]*/, F_RP = 768 /*[2][128]*/,
+              F_RED = 1024 /*[4][128]*/, F_END = 1536;
 constexpr uint32_t S_BAR = S_F32 + F_END * 4;
 enum { B_DONE0 = 0, B_DONE1, B_FREE0, B_FREE1, B_X0, B_X1, B_H1, B_DZ2, B_DZ1, B_ALL, N_BARS };
 constexpr uint32_t S_TMEM = S_BAR + N_BARS * 8;
@@ -78,10 +81,14 @@ __device__ __forceinline__ uint4 pack8(float4 a, float4 b) {
   return make_uint4(pack_half2(a.x, a.y), pack_half2(a.z, a.w), pack_half2(b.x, b.y), pack_half2(b.z, b.w));
 }
 
+// Debug trace (DLAS_TC_TRACE=<file>): SM-clock stamps of CTA 0, epilogue thread 0 (slots 0..) and the issuer (slots 512..)
+#define TRACE_E(k) do { if (trace && blockIdx.x == 0 && tid == 0 && te < 500) trace[te++] = ((long long)(k) << 48) | (clock64() & 0xFFFFFFFFFFFFll); } while (0)
+#define TRACE_M(k) do { if (trace && blockIdx.x == 0 && lane == 0 && tmm < 500) trace[512 + tmm++] = ((long long)(k) << 48) | (clock64() & 0xFFFFFFFFFFFFll); } while (0)
+
 __global__ void __cluster_dims__(2, 1, 1) __launch_bounds__(NT, 1)
 mlp_tc_kernel(const int loss_kind, const float* __restrict__ params, const float* __restrict__ X,
               const float* __restrict__ y, const size_t n_rows, float* __restrict__ partials,
-              int* __restrict__ err_flag) {
+              unsigned* __restrict__ err_flag, const unsigned call_id, long long* __restrict__ trace) {
   extern __shared__ __align__(1024) uint8_t smem[];
   float* f32 = reinterpret_cast<float*>(smem + S_F32);
   uint64_t* bars = reinterpret_cast<uint64_t*>(smem + S_BAR);
@@ -95,6 +102,8 @@ mlp_tc_kernel(const int loss_kind, const float* __restrict__ params, const float
   const int pair = blockIdx.x >> 1, n_pairs = gridDim.x >> 1;
   const size_t n_tiles = (n_rows + TILE - 1) / TILE;
   bool ok = (sbase & 1023u) == 0;   // the swizzled tile layout needs a 1024-byte aligned base
+  int te = 0, tmm = 0;
+  TRACE_E(1);
 
   // ---- one-time set-up: barriers, TMEM, weights -> fp16 tiles -------------------------------------------
   if (tid == 0) {
@@ -107,23 +116,36 @@ mlp_tc_kernel(const int loss_kind, const float* __restrict__ params, const float
   }
   if (warp == 8) tmem_alloc(tmem_slot, TM_COLS);
   {
-    const float* W1 = params + W1_OFF;                        // [32][256]
-#pragma unroll 4
-    for (int idx = tid; idx < D0 * (D1 / 8); idx += NT) {
+    // sW1 = [W1 ; b1 ; 0]: rows 0..31 weights, row 32 the bias (it multiplies the ones column of [x | 1 | 0]),
+    // rows 33..47 zero -> Z1 comes out of the MMA with the bias already added
+    for (int idx = tid; idx < K1 * (D1 / 8); idx += NT) {
       const int r = idx / (D1 / 8), c = (idx % (D1 / 8)) * 8;
-      float4 a = __ldg(reinterpret_cast<const float4*>(W1 + r * D1 + c));
-      float4 b = __ldg(reinterpret_cast<const float4*>(W1 + r * D1 + c + 4));
-      sts128(sW1 + tile_chunk_off(D0, r, c), pack8(a, b));
+      float4 a = make_float4(0.f, 0.f, 0.f, 0.f), b = a;
+      if (r <= D0) {
+        const float* src = (r < D0) ? params + W1_OFF + r * D1 + c : params + B1_OFF + c;
+        a = __ldg(reinterpret_cast<const float4*>(src));
+        b = __ldg(reinterpret_cast<const float4*>(src + 4));
+      }
+      sts128(sW1 + tile_chunk_off(K1, r, c), pack8(a, b));
     }
     const float* W2 = params + W2_OFF + rank * 128;           // [256][256], my 128 out-columns
-#pragma unroll 8
-    for (int idx = tid; idx < D1 * 16; idx += NT) {
-      const int r = idx >> 4, c = (idx & 15) * 8;
-      float4 a = __ldg(reinterpret_cast<const float4*>(W2 + (size_t)r * D2 + c));
-      float4 b = __ldg(reinterpret_cast<const float4*>(W2 + (size_t)r * D2 + c + 4));
-      sts128(sW2 + tile_chunk_off(D1, r, c), pack8(a, b));
+    for (int i0 = 0; i0 < D1 * 16; i0 += NT * 4) {             // 4 chunks (8 loads) in flight per thread
+      float4 a[4], b[4];
+#pragma unroll
+      for (int u = 0; u < 4; ++u) {
+        const int idx = i0 + u * NT + tid;
+        if (idx < D1 * 16) {
+          const int r = idx >> 4, c = (idx & 15) * 8;
+          a[u] = __ldg(reinterpret_cast<const float4*>(W2 + (size_t)r * D2 + c));
+          b[u] = __ldg(reinterpret_cast<const float4*>(W2 + (size_t)r * D2 + c + 4));
+        }
+      }
+#pragma unroll
+      for (int u = 0; u < 4; ++u) {
+        const int idx = i0 + u * NT + tid;
+        if (idx < D1 * 16) sts128(sW2 + tile_chunk_off(D1, idx >> 4, (idx & 15) * 8), pack8(a[u], b[u]));
+      }
     }
-    for (int i = tid; i < D1; i += NT) f32[F_B1 + i] = __ldg(params + B1_OFF + i);
     if (tid < 128) {
       f32[F_B2 + tid] = __ldg(params + B2_OFF + rank * 128 + tid);
       f32[F_W3 + tid] = __ldg(params + W3_OFF + rank * 128 + tid);
@@ -142,82 +164,114 @@ mlp_tc_kernel(const int loss_kind, const float* __restrict__ params, const float
   fence_after();
   cluster_sync_all();  // the peer CTA is running: its shared memory may be written from here on
   const uint32_t tm = *tmem_slot;
+  TRACE_E(2);
 
   const int my_tiles = (n_tiles > (size_t)pair) ? (int)((n_tiles - pair + n_pairs - 1) / n_pairs) : 0;
 
   if (warp == 8) {
     // =========================== MMA issuer ===========================
+    // The whole warp runs the control flow (so descriptor arithmetic stays warp-uniform); one elected
+    // lane issues.  Descriptors are a constant base plus a compile-time offset per K step.
     constexpr uint32_t ID_KM_MN_64 = make_idesc(128, 64, false, true);
     constexpr uint32_t ID_KM_KM_64 = make_idesc(128, 64, false, false);
     constexpr uint32_t ID_MN_MN_128 = make_idesc(128, 128, true, true);
     constexpr uint32_t ID_MN_MN_48 = make_idesc(128, 48, true, true);
     constexpr uint32_t ID_MN_KM_16 = make_idesc(128, 16, true, false);
+    const bool leader = elect_one();
+    const uint64_t dX_km[2] = {desc_kmajor(sX, TILE, 0, 0), desc_kmajor(sX + 16384, TILE, 0, 0)};
+    const uint64_t dX_mn[2] = {desc_mnmajor(sX, TILE, 0, 0), desc_mnmajor(sX + 16384, TILE, 0, 0)};
+    const uint64_t dW1_mn = desc_mnmajor(sW1, K1, 0, 0);
+    const uint64_t dW2_mn = desc_mnmajor(sW2, D1, 0, 0), dW2_km = desc_kmajor(sW2, D1, 0, 0);
+    const uint64_t dH1_km = desc_kmajor(sH1, TILE, 0, 0), dH1_mn = desc_mnmajor(sH1, TILE, 0, 0);
+    const uint64_t dDZ2_km = desc_kmajor(sDZ2, TILE, 0, 0), dDZ2_mn = desc_mnmajor(sDZ2, TILE, 0, 0);
+    const uint64_t dONES = desc_kmajor(sONES, 16, 0, 0);
     uint32_t n = 0;  // running index of chunk GEMMs; buffer = n & 1
     for (int it = 0; it < my_tiles; ++it) {
-      const uint32_t sXc = sX + (uint32_t)(it & 1) * 16384;
+      const int xb = it & 1;
       const bool first = (it == 0);
-      if (lane == 0) {
-        ok = mbar_wait(&bars[B_X0 + (it & 1)], (it >> 1) & 1) && ok;
-        // Z1 = X W1: four N=64 chunks
-        for (int s = 0; s < 4; ++s, ++n) {
-          const uint32_t b = n & 1;
-          ok = mbar_wait(&bars[B_FREE0 + b], ((n >> 1) & 1) ^ 1) && ok;
-          fence_after();
+      TRACE_M(10);
+      ok = mbar_wait(&bars[B_X0 + xb], (it >> 1) & 1) && ok;
+      TRACE_M(11);
+      // Z1 + b1 = [X | 1 | 0] [W1 ; b1 ; 0]: four N=64 chunks, K = 48
 #pragma unroll
-          for (int k = 0; k < D0; k += 16)
-            mma_f16(tm + TM_W0 + b * 64, desc_kmajor(sXc, TILE, 0, k), desc_mnmajor(sW1, D0, s * 64, k), ID_KM_MN_64, k > 0);
-          mma_commit(&bars[B_DONE0 + b]);
-        }
-        // Z2h = H1 W2h: two N=64 chunks
-        ok = mbar_wait(&bars[B_H1], it & 1) && ok;
-        for (int s = 0; s < 2; ++s, ++n) {
-          const uint32_t b = n & 1;
-          ok = mbar_wait(&bars[B_FREE0 + b], ((n >> 1) & 1) ^ 1) && ok;
-          fence_after();
-#pragma unroll
-          for (int k = 0; k < D1; k += 16)
-            mma_f16(tm + TM_W0 + b * 64, desc_kmajor(sH1, TILE, 0, k), desc_mnmajor(sW2, D1, s * 64, k), ID_KM_MN_64, k > 0);
-          mma_commit(&bars[B_DONE0 + b]);
-        }
-      }
-      __syncwarp();
-      cluster_sync_all();   // pairs with the epilogue warps' exchange of the partial output dots
-      if (lane == 0) {
-        ok = mbar_wait(&bars[B_DZ2], it & 1) && ok;
+      for (int s = 0; s < 4; ++s, ++n) {
+        const uint32_t b = n & 1;
+        ok = mbar_wait(&bars[B_FREE0 + b], ((n >> 1) & 1) ^ 1) && ok;
         fence_after();
+        if (leader) {
+#pragma unroll
+          for (int i = 0; i < K1 / 16; ++i)
+            mma_f16(tm + TM_W0 + b * 64, dX_km[xb] + koff_kmajor(TILE, i), dW1_mn + mnoff(K1, s * 64) + koff_mnmajor(i), ID_KM_MN_64, i > 0);
+          mma_commit(&bars[B_DONE0 + b]);
+        }
+        __syncwarp();
+      }
+      // Z2h = H1 W2h: two N=64 chunks
+      TRACE_M(12);
+      ok = mbar_wait(&bars[B_H1], it & 1) && ok;
+      TRACE_M(13);
+#pragma unroll
+      for (int s = 0; s < 2; ++s, ++n) {
+        const uint32_t b = n & 1;
+        ok = mbar_wait(&bars[B_FREE0 + b], ((n >> 1) & 1) ^ 1) && ok;
+        fence_after();
+        if (leader) {
+#pragma unroll
+          for (int i = 0; i < D1 / 16; ++i)
+            mma_f16(tm + TM_W0 + b * 64, dH1_km + koff_kmajor(TILE, i), dW2_mn + mnoff(D1, s * 64) + koff_mnmajor(i), ID_KM_MN_64, i > 0);
+          mma_commit(&bars[B_DONE0 + b]);
+        }
+        __syncwarp();
+      }
+      TRACE_M(14);
+      cluster_sync_all();   // pairs with the epilogue warps' exchange of the partial output dots
+      TRACE_M(15);
+      ok = mbar_wait(&bars[B_DZ2], it & 1) && ok;
+      TRACE_M(16);
+      fence_after();
+      if (leader) {
         // db2h += dZ2h^T 1 ; dW2h += H1^T dZ2h (accumulate over the whole launch)
 #pragma unroll
-        for (int k = 0; k < TILE; k += 16)
-          mma_f16(tm + TM_DB2, desc_mnmajor(sDZ2, TILE, 0, k), desc_kmajor(sONES, 16, 0, 0), ID_MN_KM_16, !(first && k == 0));
-#pragma unroll 1
+        for (int i = 0; i < TILE / 16; ++i)
+          mma_f16(tm + TM_DB2, dDZ2_mn + koff_mnmajor(i), dONES, ID_MN_KM_16, !(first && i == 0));
+#pragma unroll
         for (int mh = 0; mh < 2; ++mh)
 #pragma unroll
-          for (int k = 0; k < TILE; k += 16)
-            mma_f16(tm + TM_DW2 + mh * 128, desc_mnmajor(sH1, TILE, mh * 128, k), desc_mnmajor(sDZ2, TILE, 0, k), ID_MN_MN_128,
-                    !(first && k == 0));
-        // dH1p = dZ2h W2h^T: four N=64 chunks (in-index)
-        for (int s = 0; s < 4; ++s, ++n) {
-          const uint32_t b = n & 1;
-          ok = mbar_wait(&bars[B_FREE0 + b], ((n >> 1) & 1) ^ 1) && ok;
-          fence_after();
+          for (int i = 0; i < TILE / 16; ++i)
+            mma_f16(tm + TM_DW2 + mh * 128, dH1_mn + mnoff(TILE, mh * 128) + koff_mnmajor(i), dDZ2_mn + koff_mnmajor(i), ID_MN_MN_128,
+                    !(first && i == 0));
+      }
+      __syncwarp();
+      // dH1p = dZ2h W2h^T: four N=64 chunks (in-index)
 #pragma unroll
-          for (int k = 0; k < 128; k += 16)
-            mma_f16(tm + TM_W0 + b * 64, desc_kmajor(sDZ2, TILE, 0, k), desc_kmajor(sW2, D1, s * 64, k), ID_KM_KM_64, k > 0);
+      for (int s = 0; s < 4; ++s, ++n) {
+        const uint32_t b = n & 1;
+        ok = mbar_wait(&bars[B_FREE0 + b], ((n >> 1) & 1) ^ 1) && ok;
+        fence_after();
+        if (leader) {
+#pragma unroll
+          for (int i = 0; i < 128 / 16; ++i)
+            mma_f16(tm + TM_W0 + b * 64, dDZ2_km + koff_kmajor(TILE, i), dW2_km + rowoff(s * 64) + koff_kmajor(D1, i), ID_KM_KM_64, i > 0);
           mma_commit(&bars[B_DONE0 + b]);
         }
-        // dW1p^T += dZ1p^T [X | 1]
-        ok = mbar_wait(&bars[B_DZ1], it & 1) && ok;
-        fence_after();
-#pragma unroll 1
+        __syncwarp();
+      }
+      // dW1p^T += dZ1p^T [X | 1]
+      TRACE_M(17);
+      ok = mbar_wait(&bars[B_DZ1], it & 1) && ok;
+      TRACE_M(18);
+      fence_after();
+      if (leader) {
+#pragma unroll
         for (int mh = 0; mh < 2; ++mh)
 #pragma unroll
-          for (int k = 0; k < TILE; k += 16)
-            mma_f16(tm + TM_DW1 + mh * 64, desc_mnmajor(sH1, TILE, mh * 128, k), desc_mnmajor(sXc, TILE, 0, k), ID_MN_MN_48,
-                    !(first && k == 0));
+          for (int i = 0; i < TILE / 16; ++i)
+            mma_f16(tm + TM_DW1 + mh * 64, dH1_mn + mnoff(TILE, mh * 128) + koff_mnmajor(i), dX_mn[xb] + koff_mnmajor(i), ID_MN_MN_48,
+                    !(first && i == 0));
       }
       __syncwarp();
     }
-    if (lane == 0) mma_commit(&bars[B_ALL]);
+    if (leader) mma_commit(&bars[B_ALL]);
     __syncwarp();
   } else {
     // =========================== epilogue warps ===========================
@@ -255,8 +309,9 @@ mlp_tc_kernel(const int loss_kind, const float* __restrict__ params, const float
       const size_t tile = (size_t)pair + (size_t)it * n_pairs;
       const size_t row0 = tile * TILE;
       const bool row_valid = row0 + row < n_rows;
+      TRACE_E(20);
       if (it + 1 < my_tiles) x_issue(tile + n_pairs);      // next tile's rows: in flight during phase (b)
-      // ---- (b) H1 = relu(Z1 + b1) -> sH1, four chunks ------------------------------------------------
+      // ---- (b) H1 = relu(Z1 + b1) -> sH1, four chunks (the bias is already in the accumulator) --------
 #pragma unroll 1
       for (int s = 0; s < 4; ++s, ++n) {
         const uint32_t b = n & 1;
@@ -269,19 +324,21 @@ mlp_tc_kernel(const int loss_kind, const float* __restrict__ params, const float
         mbar_arrive(&bars[B_FREE0 + b]);
         const int c0 = s * 64 + hh * 32;
 #pragma unroll
-        for (int g8 = 0; g8 < 4; ++g8) {
-          const float4 ba = lds128f(sF + (F_B1 + c0 + g8 * 8) * 4), bb = lds128f(sF + (F_B1 + c0 + g8 * 8 + 4) * 4);
-          float4 lo = make_float4(fmaxf(__uint_as_float(v[g8 * 8 + 0]) + ba.x, 0.f), fmaxf(__uint_as_float(v[g8 * 8 + 1]) + ba.y, 0.f),
-                                  fmaxf(__uint_as_float(v[g8 * 8 + 2]) + ba.z, 0.f), fmaxf(__uint_as_float(v[g8 * 8 + 3]) + ba.w, 0.f));
-          float4 hi = make_float4(fmaxf(__uint_as_float(v[g8 * 8 + 4]) + bb.x, 0.f), fmaxf(__uint_as_float(v[g8 * 8 + 5]) + bb.y, 0.f),
-                                  fmaxf(__uint_as_float(v[g8 * 8 + 6]) + bb.z, 0.f), fmaxf(__uint_as_float(v[g8 * 8 + 7]) + bb.w, 0.f));
-          sts128(sH1 + tile_chunk_off(TILE, row, c0 + g8 * 8), pack8(lo, hi));
+        for (int g8 = 0; g8 < 4; ++g8) {   // relu on packed halves: one F2FP + one HMNMX2 per two elements
+          uint4 o;
+          o.x = relu_h2(pack_half2(__uint_as_float(v[g8 * 8 + 0]), __uint_as_float(v[g8 * 8 + 1])));
+          o.y = relu_h2(pack_half2(__uint_as_float(v[g8 * 8 + 2]), __uint_as_float(v[g8 * 8 + 3])));
+          o.z = relu_h2(pack_half2(__uint_as_float(v[g8 * 8 + 4]), __uint_as_float(v[g8 * 8 + 5])));
+          o.w = relu_h2(pack_half2(__uint_as_float(v[g8 * 8 + 6]), __uint_as_float(v[g8 * 8 + 7])));
+          sts128(sH1 + tile_chunk_off(TILE, row, c0 + g8 * 8), o);
         }
       }
       fence_async_smem();
       mbar_arrive(&bars[B_H1]);
+      TRACE_E(21);
       if (it + 1 < my_tiles) x_store((it + 1) & 1);        // the other X buffer was last read by tile it-1's dW1
       // ---- (c) Z2h: partial output dot, exchange, dZ2h -> sDZ2 ---------------------------------------
+      TRACE_E(22);
       float part = 0.f;
       const uint32_t n_c = n;
       n += 2;
@@ -303,12 +360,15 @@ mlp_tc_kernel(const int loss_kind, const float* __restrict__ params, const float
           part = fmaf(fmaxf(__uint_as_float(v[g4 * 4 + 3]) + bv.w, 0.f), wv.w, part);
         }
       }
+      TRACE_E(23);
       const int buf = it & 1;
       f32[F_RP + hh * 128 + row] = part;
       named_bar_sync(1, N_EPI);
       const float mine = f32[F_RP + row] + f32[F_RP + 128 + row];
       if (hh == 0) st_cluster_f32(peer_part + (uint32_t)(buf * 128 + row) * 4, mine);
+      TRACE_E(24);
       cluster_sync_all();
+      TRACE_E(25);
       const float other = f32[F_PART + buf * 128 + row];
       const float yhat = (rank == 0 ? mine + other : other + mine) + b3;   // same value on both CTAs
       float g = 0.f;
@@ -342,20 +402,22 @@ mlp_tc_kernel(const int loss_kind, const float* __restrict__ params, const float
           const float4 ba = lds128f(sF + (F_B2 + c0 + g8 * 8) * 4), bb = lds128f(sF + (F_B2 + c0 + g8 * 8 + 4) * 4);
           const float w8[8] = {wa.x, wa.y, wa.z, wa.w, wb.x, wb.y, wb.z, wb.w};
           const float b8[8] = {ba.x, ba.y, ba.z, ba.w, bb.x, bb.y, bb.z, bb.w};
-          float dz[8];
+          uint32_t o[4];
 #pragma unroll
-          for (int e = 0; e < 8; ++e) {
-            const float zz = __uint_as_float(v[g8 * 8 + e]) + b8[e];
-            hg[g8 * 8 + e] = fmaxf(zz, 0.f) * g;                 // -> dw3
-            dz[e] = zz > 0.f ? g * w8[e] : 0.f;                  // -> dZ2
+          for (int e = 0; e < 4; ++e) {
+            const float z0 = __uint_as_float(v[g8 * 8 + 2 * e]) + b8[2 * e], z1 = __uint_as_float(v[g8 * 8 + 2 * e + 1]) + b8[2 * e + 1];
+            hg[g8 * 8 + 2 * e] = fmaxf(z0, 0.f) * g;                 // -> dw3
+            hg[g8 * 8 + 2 * e + 1] = fmaxf(z1, 0.f) * g;
+            // dZ2 = (z > 0) * (g * w3): mask and product on packed halves
+            o[e] = mul_h2(gt0_h2(pack_half2(z0, z1)), pack_half2(g * w8[2 * e], g * w8[2 * e + 1]));
           }
-          sts128(sDZ2 + tile_chunk_off(TILE, row, c0 + g8 * 8),
-                 make_uint4(pack_half2(dz[0], dz[1]), pack_half2(dz[2], dz[3]), pack_half2(dz[4], dz[5]), pack_half2(dz[6], dz[7])));
+          sts128(sDZ2 + tile_chunk_off(TILE, row, c0 + g8 * 8), make_uint4(o[0], o[1], o[2], o[3]));
         }
         acc_w3[s] += warp_colsum32(hg, lane);
       }
       fence_async_smem();
       mbar_arrive(&bars[B_DZ2]);
+      TRACE_E(26);
       // ---- (d) dZ1p = relu'(H1) o dH1p in place over H1, four chunks -----------------------------------
 #pragma unroll 1
       for (int s = 0; s < 4; ++s, ++n) {
@@ -372,26 +434,26 @@ mlp_tc_kernel(const int loss_kind, const float* __restrict__ params, const float
         for (int g8 = 0; g8 < 4; ++g8) {
           const uint32_t a = sH1 + tile_chunk_off(TILE, row, c0 + g8 * 8);
           const uint4 h = lds128(a);
-          const uint32_t hw[4] = {h.x, h.y, h.z, h.w};
-          uint32_t o[4];
-#pragma unroll
-          for (int e = 0; e < 4; ++e) {
-            const float lo = (hw[e] & 0x7FFFu) ? __uint_as_float(v[g8 * 8 + 2 * e]) : 0.f;       // H1 > 0 (it is >= 0)
-            const float hi = (hw[e] & 0x7FFF0000u) ? __uint_as_float(v[g8 * 8 + 2 * e + 1]) : 0.f;
-            o[e] = pack_half2(lo, hi);
-          }
+          uint32_t o[4];   // dZ1 = (H1 > 0) * dH1p on packed halves
+          o[0] = mul_h2(gt0_h2(h.x), pack_half2(__uint_as_float(v[g8 * 8 + 0]), __uint_as_float(v[g8 * 8 + 1])));
+          o[1] = mul_h2(gt0_h2(h.y), pack_half2(__uint_as_float(v[g8 * 8 + 2]), __uint_as_float(v[g8 * 8 + 3])));
+          o[2] = mul_h2(gt0_h2(h.z), pack_half2(__uint_as_float(v[g8 * 8 + 4]), __uint_as_float(v[g8 * 8 + 5])));
+          o[3] = mul_h2(gt0_h2(h.w), pack_half2(__uint_as_float(v[g8 * 8 + 6]), __uint_as_float(v[g8 * 8 + 7])));
           sts128(a, make_uint4(o[0], o[1], o[2], o[3]));
         }
       }
       fence_async_smem();
       mbar_arrive(&bars[B_DZ1]);
+      TRACE_E(27);
     }
 
     // ---- drain the accumulators into this CTA's partial vector -----------------------------------------
     float* my = partials + (size_t)blockIdx.x * PSTRIDE;
     if (my_tiles > 0) {
+      TRACE_E(30);
       ok = mbar_wait(&bars[B_ALL], 0) && ok;
       fence_after();
+      TRACE_E(31);
 #pragma unroll 1
       for (int mh = 0; mh < 2; ++mh) {
         float* dst = my + W2_OFF + (size_t)(mh * 128 + row) * D2 + rank * 128 + hh * 64;   // row in = mh*128+row
@@ -443,7 +505,8 @@ mlp_tc_kernel(const int loss_kind, const float* __restrict__ params, const float
       }
     }
   }
-  if (!ok && lane == 0) atomicExch(err_flag, 1);
+  TRACE_E(32);
+  if (!ok && lane == 0) atomicExch(err_flag, call_id);
   // ---- teardown ----------------------------------------------------------------------------------------
   fence_before();
   __syncthreads();
@@ -454,71 +517,139 @@ mlp_tc_kernel(const int loss_kind, const float* __restrict__ params, const float
 // grad_sum[i] = sum of the partials of the CTAs that own entry i, in CTA order:
 //   W1, b1: every active CTA (each holds a partial);  W2[:, c], b2[c], w3[c]: CTAs of rank c/128;
 //   b3 and the loss sum: rank-0 CTAs.
+// With FUSE_OPT the optimiser update of entry i is applied in the same pass (single-GPU step: no
+// all-reduce sits between the gradient and the update), and the batch-mean loss goes to *loss_out.
+template <bool FUSE_OPT>
 __global__ void __launch_bounds__(256)
-tc_reduce_kernel(const float* __restrict__ partials, int n_active_pairs, const int* __restrict__ err_flag,
-                 float* __restrict__ out) {
-  int i = blockIdx.x * 256 + threadIdx.x;
+tc_reduce_kernel(const float* __restrict__ partials, int n_active_pairs, const unsigned* __restrict__ err_flag,
+                 unsigned call_id, float* __restrict__ out, OptScalars opt, float grad_scale, float* __restrict__ params,
+                 float* __restrict__ m, float* __restrict__ v, float* __restrict__ loss_out) {
+  const int i = blockIdx.x * 256 + threadIdx.x;
   if (i > N_PARAMS) return;
-  if (*err_flag) {  // an mbarrier wait timed out inside the tcgen05 kernel: fail loudly, never return numbers
-    out[i] = __int_as_float(0x7fc00000);
-    return;
-  }
   int first = 0, step = 1;
   if (i >= W2_OFF && i < B2_OFF) { first = ((i - W2_OFF) % D2) / 128; step = 2; }
   else if (i >= B2_OFF && i < W3_OFF) { first = (i - B2_OFF) / 128; step = 2; }
   else if (i >= W3_OFF && i < B3_OFF) { first = (i - W3_OFF) / 128; step = 2; }
   else if (i >= B3_OFF) { first = 0; step = 2; }
   float s = 0.f;
+#pragma unroll 8
   for (int c = first; c < 2 * n_active_pairs; c += step) s += partials[(size_t)c * PSTRIDE + i];
-  out[i] = s;
+  // an mbarrier wait timed out inside this call's tcgen05 kernel: fail loudly, never return numbers
+  if (*err_flag == call_id) s = __int_as_float(0x7fc00000);
+  if (out) out[i] = s;
+  if (FUSE_OPT) {
+    if (i == N_PARAMS) {
+      if (loss_out) *loss_out = s * grad_scale;
+    } else {
+      float p = params[i], mi = m[i], vi = (opt.kind == 0) ? 0.f : v[i];
+      opt_update(opt, s * grad_scale, p, mi, vi);
+      params[i] = p;
+      m[i] = mi;
+      if (opt.kind != 0) v[i] = vi;
+    }
+  }
 }
 
 int n_ctas() { return (sm_count() / 2) * 2; }
+unsigned g_call_id = 0x5eed0000u;
 
-}  // namespace
-
-bool tc_supported(const int* dims, int n_layers) {
-  return n_layers == 3 && dims[0] == D0 && dims[1] == D1 && dims[2] == D2 && dims[3] == 1;
-}
-
-size_t tc_workspace_bytes(const int* dims, int n_layers) {
-  size_t tc = (size_t)n_ctas() * PSTRIDE * sizeof(float) + 256;   // partials + error flag
-  size_t simt = simt_workspace_bytes(dims, n_layers);             // eval / predict share the workspace
-  return tc > simt ? tc : simt;
-}
-
-int tc_grad(const int* dims, int n_layers, int loss, const float* params, const float* X, const float* y,
-            size_t n_rows, float* grad_sum, void* workspace, size_t workspace_bytes, cudaStream_t st) {
-  if (!tc_supported(dims, n_layers)) {
-    set_error("DLAS_MODE_TC supports the 32-256-256-1 network only");
-    return DLAS_ERR_UNSUPPORTED_SHAPE;
-  }
-  size_t need = tc_workspace_bytes(dims, n_layers);
+int launch_main(int loss, const float* params, const float* X, const float* y, size_t n_rows, void* workspace,
+                size_t workspace_bytes, cudaStream_t st, float** partials_out, unsigned** err_out, int* n_active_pairs) {
+  size_t need = (size_t)n_ctas() * PSTRIDE * sizeof(float) + 256;
   if (workspace == nullptr || workspace_bytes < need) {
     set_error("mlp (tc): workspace of %zu bytes given, %zu needed", workspace_bytes, need);
     return DLAS_ERR_WORKSPACE;
   }
-  if (n_rows == 0) {
-    DLAS_CUDA(cudaMemsetAsync(grad_sum, 0, ((size_t)N_PARAMS + 1) * sizeof(float), st));
-    return DLAS_OK;
-  }
   DLAS_REQUIRE((((uintptr_t)X) & 15) == 0, "mlp (tc): X must be 16-byte aligned");
   float* partials = (float*)workspace;
-  int* err_flag = (int*)((char*)workspace + (size_t)n_ctas() * PSTRIDE * sizeof(float));
+  unsigned* err_flag = (unsigned*)((char*)workspace + (size_t)n_ctas() * PSTRIDE * sizeof(float));
   static bool attr_set = false;
   if (!attr_set) {
     DLAS_CUDA(cudaFuncSetAttribute(mlp_tc_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)SMEM_BYTES));
     attr_set = true;
   }
   const int grid = n_ctas();
-  DLAS_CUDA(cudaMemsetAsync(err_flag, 0, sizeof(int), st));
+  ++g_call_id;   // the error word is never cleared: a kernel that times out writes THIS call's id into it
   int pi = prof_begin(DLAS_PROF_MLP_GRAD, st);
-  mlp_tc_kernel<<<grid, NT, SMEM_BYTES, st>>>(loss, params, X, y, n_rows, partials, err_flag);
+  long long* trace = nullptr;
+  const char* trace_path = getenv("DLAS_TC_TRACE");   // debug only: this branch allocates and synchronises
+  if (trace_path) {
+    DLAS_CUDA(cudaMalloc(&trace, 1024 * sizeof(long long)));
+    DLAS_CUDA(cudaMemsetAsync(trace, 0, 1024 * sizeof(long long), st));
+  }
+  mlp_tc_kernel<<<grid, NT, SMEM_BYTES, st>>>(loss, params, X, y, n_rows, partials, err_flag, g_call_id, trace);
   prof_end(pi, st);
   DLAS_LAUNCH_CHECK();
+  if (trace_path) {
+    long long h[1024];
+    DLAS_CUDA(cudaMemcpyAsync(h, trace, sizeof(h), cudaMemcpyDeviceToHost, st));
+    DLAS_CUDA(cudaStreamSynchronize(st));
+    cudaFree(trace);
+    FILE* f = fopen(trace_path, "w");
+    if (f) {
+      for (int i = 0; i < 1024; ++i)
+        if (h[i]) fprintf(f, "%s %lld %lld\n", i < 512 ? "E" : "M", h[i] >> 48, h[i] & 0xFFFFFFFFFFFFll);
+      fclose(f);
+    }
+  }
   size_t n_tiles = (n_rows + TILE - 1) / TILE;
-  int n_active_pairs = (int)(n_tiles < (size_t)(grid / 2) ? n_tiles : (size_t)(grid / 2));
-  tc_reduce_kernel<<<(N_PARAMS + 1 + 255) / 256, 256, 0, st>>>(partials, n_active_pairs, err_flag, grad_sum);
+  *n_active_pairs = (int)(n_tiles < (size_t)(grid / 2) ? n_tiles : (size_t)(grid / 2));
+  *partials_out = partials;
+  *err_out = err_flag;
+  return DLAS_OK;
+}
+
+}  // namespace
+
+int make_opt_scalars(const dlas_opt_cfg* cfg, uint64_t iteration, OptScalars& o);   // optim.cu
+
+bool tc_supported(const int* dims, int n_layers) {
+  return n_layers == 3 && dims[0] == D0 && dims[1] == D1 && dims[2] == D2 && dims[3] == 1;
+}
+
+size_t tc_workspace_bytes(const int* dims, int n_layers) {
+  size_t tc = (size_t)n_ctas() * PSTRIDE * sizeof(float) + 256;   // partials + error word
+  size_t simt = simt_workspace_bytes(dims, n_layers);             // eval / predict share the workspace
+  return tc > simt ? tc : simt;
+}
+
+// forward + loss + backward: grad_sum[0..n) gradient sums, grad_sum[n] loss sum
+int tc_grad(const int* dims, int n_layers, int loss, const float* params, const float* X, const float* y,
+            size_t n_rows, float* grad_sum, void* workspace, size_t workspace_bytes, cudaStream_t st) {
+  if (!tc_supported(dims, n_layers)) {
+    set_error("DLAS_MODE_TC supports the 32-256-256-1 network only");
+    return DLAS_ERR_UNSUPPORTED_SHAPE;
+  }
+  if (n_rows == 0) {
+    DLAS_CUDA(cudaMemsetAsync(grad_sum, 0, ((size_t)N_PARAMS + 1) * sizeof(float), st));
+    return DLAS_OK;
+  }
+  float* partials; unsigned* err; int nap;
+  int rc = launch_main(loss, params, X, y, n_rows, workspace, workspace_bytes, st, &partials, &err, &nap);
+  if (rc != DLAS_OK) return rc;
+  tc_reduce_kernel<false><<<(N_PARAMS + 1 + 255) / 256, 256, 0, st>>>(partials, nap, err, g_call_id, grad_sum, OptScalars{},
+                                                                     0.f, nullptr, nullptr, nullptr, nullptr);
+  DLAS_LAUNCH_CHECK();
+  return DLAS_OK;
+}
+
+// one whole single-GPU step: gradient kernel, then reduction fused with the optimiser update
+int tc_fit_step(const int* dims, int n_layers, int loss, const dlas_opt_cfg* cfg, float* params, float* m, float* v,
+                const float* X, const float* y, size_t n_rows, uint64_t iteration, float* loss_out, void* workspace,
+                size_t workspace_bytes, cudaStream_t st) {
+  if (!tc_supported(dims, n_layers)) {
+    set_error("DLAS_MODE_TC supports the 32-256-256-1 network only");
+    return DLAS_ERR_UNSUPPORTED_SHAPE;
+  }
+  OptScalars o;
+  int rc = make_opt_scalars(cfg, iteration, o);
+  if (rc != DLAS_OK) return rc;
+  DLAS_REQUIRE(o.kind == DLAS_OPT_SGD || v != nullptr, "Adam needs the second-moment buffer v");
+  float* partials; unsigned* err; int nap;
+  rc = launch_main(loss, params, X, y, n_rows, workspace, workspace_bytes, st, &partials, &err, &nap);
+  if (rc != DLAS_OK) return rc;
+  tc_reduce_kernel<true><<<(N_PARAMS + 1 + 255) / 256, 256, 0, st>>>(partials, nap, err, g_call_id, nullptr, o,
+                                                                    1.0f / (float)n_rows, params, m, v, loss_out);
   DLAS_LAUNCH_CHECK();
   return DLAS_OK;
 }

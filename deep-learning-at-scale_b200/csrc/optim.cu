@@ -4,6 +4,7 @@
 // all-reduced gradient SUM is consumed as is.  Step-dependent scalars are computed on the host
 // in double and passed by value.
 #include "common.cuh"
+#include "optim_math.cuh"
 #include <math.h>
 
 namespace dlas {
@@ -59,6 +60,25 @@ int opt_step_impl(const dlas_opt_cfg* cfg, float* params, float* m, float* v, co
     return DLAS_ERR_INVALID;
   }
   DLAS_LAUNCH_CHECK();
+  return DLAS_OK;
+}
+
+// Step-dependent scalars for kernels that fuse the update into their own epilogue (optim_math.cuh).
+int make_opt_scalars(const dlas_opt_cfg* cfg, uint64_t iteration, OptScalars& o) {
+  DLAS_REQUIRE(cfg != nullptr, "optimiser cfg is null");
+  DLAS_REQUIRE(cfg->kind == DLAS_OPT_SGD || cfg->kind == DLAS_OPT_ADAM, "unknown optimiser kind %d", cfg->kind);
+  double lr_t = (double)cfg->lr / (1.0 + (double)cfg->decay * (double)iteration);
+  if (cfg->kind == DLAS_OPT_ADAM) {
+    const double t = (double)iteration + 1.0;
+    lr_t = lr_t * sqrt(1.0 - pow((double)cfg->beta2, t)) / (1.0 - pow((double)cfg->beta1, t));
+  }
+  o.kind = cfg->kind;
+  o.lr_t = (float)lr_t;
+  o.momentum = cfg->momentum;
+  o.nesterov = cfg->nesterov;
+  o.beta1 = cfg->beta1;
+  o.beta2 = cfg->beta2;
+  o.eps = cfg->eps;
   return DLAS_OK;
 }
 

@@ -46,6 +46,15 @@ __device__ __forceinline__ uint64_t desc_mnmajor(uint32_t base, int rows, int mn
   uint32_t a = base + (uint32_t)((mn0 >> 6) * rows * 128 + (k0 >> 3) * 1024);
   return make_desc(a, (uint32_t)rows * 128, 1024);
 }
+// Descriptor offsets (added to a base descriptor; the address field counts 16-byte units and never
+// carries out of its 14 bits for addresses inside one CTA's shared memory):
+//   K step i (16 elements) of a K-major view of a tile with `rows` rows
+__host__ __device__ constexpr uint64_t koff_kmajor(int rows, int i) { return (uint64_t)(((i >> 2) * rows * 128 + (i & 3) * 32) >> 4); }
+//   K step i (16 rows) of an MN-major view
+__host__ __device__ constexpr uint64_t koff_mnmajor(int i) { return (uint64_t)((i * 2048) >> 4); }
+//   MN offset mn0 (multiple of 64 columns) of an MN-major view; row offset row0 (multiple of 8) of a K-major view
+__host__ __device__ constexpr uint64_t mnoff(int rows, int mn0) { return (uint64_t)(((mn0 >> 6) * rows * 128) >> 4); }
+__host__ __device__ constexpr uint64_t rowoff(int row0) { return (uint64_t)(((row0 >> 3) * 1024) >> 4); }
 // kind::f16, A and B fp16, D fp32
 __host__ __device__ constexpr uint32_t make_idesc(int M, int N, bool a_mn, bool b_mn) {
   return (1u << 4) | ((a_mn ? 1u : 0u) << 15) | ((b_mn ? 1u : 0u) << 16) | ((uint32_t)(N >> 3) << 17) |
@@ -96,6 +105,13 @@ __device__ __forceinline__ void tmem_ld16(uint32_t taddr, uint32_t (&v)[16]) {
 }
 __device__ __forceinline__ void tmem_ld_wait() { asm volatile("tcgen05.wait::ld.sync.aligned;" ::: "memory"); }
 
+// one lane of the (converged) warp
+__device__ __forceinline__ bool elect_one() {
+  uint32_t pred;
+  asm volatile("{\n\t.reg .pred p;\n\telect.sync _|p, 0xffffffff;\n\tselp.u32 %0, 1, 0, p;\n\t}" : "=r"(pred));
+  return pred != 0;
+}
+
 // ---- mbarrier -----------------------------------------------------------------------------------------
 __device__ __forceinline__ void mbar_init(uint64_t* bar, uint32_t count) {
   asm volatile("mbarrier.init.shared::cta.b64 [%0], %1;" ::"r"(smem_u32(bar)), "r"(count) : "memory");
@@ -125,7 +141,7 @@ __device__ __forceinline__ uint4 lds128(uint32_t a) {
   return v;
 }
 __device__ __forceinline__ void sts128(uint32_t a, uint4 v) {
-  asm volatile("st.shared.v4.b32 [%0], {%1,%2,%3,%4};" ::"r"(a), "r"(v.x), "r"(v.y), "r"(v.z), "r"(v.w) : "memory");
+  asm volatile("st.shared.v4.b32 [%0], {%1,%2,%3,%4};" ::"r"(a), "r"(v.x), "r"(v.y), "r"(v.z), "r"(v.w));
 }
 __device__ __forceinline__ float4 lds128f(uint32_t a) {
   float4 v;
@@ -137,7 +153,7 @@ __device__ __forceinline__ float lds_f32(uint32_t a) {
   asm volatile("ld.shared.f32 %0, [%1];" : "=f"(v) : "r"(a));
   return v;
 }
-__device__ __forceinline__ void sts_f32(uint32_t a, float v) { asm volatile("st.shared.f32 [%0], %1;" ::"r"(a), "f"(v) : "memory"); }
+__device__ __forceinline__ void sts_f32(uint32_t a, float v) { asm volatile("st.shared.f32 [%0], %1;" ::"r"(a), "f"(v)); }
 __device__ __forceinline__ void named_bar_sync(int id, int nthreads) { asm volatile("bar.sync %0, %1;" ::"r"(id), "r"(nthreads) : "memory"); }
 
 // ---- cluster / DSMEM ---------------------------------------------------------------------------------
@@ -153,6 +169,24 @@ __device__ __forceinline__ uint32_t map_to_cta(uint32_t saddr, uint32_t rank) {
 }
 __device__ __forceinline__ void st_cluster_f32(uint32_t caddr, float v) {
   asm volatile("st.shared::cluster.f32 [%0], %1;" ::"r"(caddr), "f"(v) : "memory");
+}
+
+// packed fp16 helpers for the epilogues (one instruction per two elements)
+__device__ __forceinline__ uint32_t relu_h2(uint32_t a) {
+  uint32_t r;
+  asm("max.f16x2 %0, %1, %2;" : "=r"(r) : "r"(a), "r"(0u));
+  return r;
+}
+// 1.0 where a > 0 else 0.0, per half
+__device__ __forceinline__ uint32_t gt0_h2(uint32_t a) {
+  uint32_t r;
+  asm("set.gt.f16x2.f16x2 %0, %1, %2;" : "=r"(r) : "r"(a), "r"(0u));
+  return r;
+}
+__device__ __forceinline__ uint32_t mul_h2(uint32_t a, uint32_t b) {
+  uint32_t r;
+  asm("mul.f16x2 %0, %1, %2;" : "=r"(r) : "r"(a), "r"(b));
+  return r;
 }
 
 __device__ __forceinline__ uint32_t pack_half2(float a, float b) {

@@ -104,7 +104,32 @@ def test_fit_steps_golden(dl, golden_dir, name, loss):
                       _cuda(g["y"]), b, ns, 0, losses, gs, ws)
     torch.cuda.synchronize()
     np.testing.assert_allclose(losses.cpu().numpy(), g[name + "_losses"], rtol=LOSS_TOL)   # batch 64
-    assert _relerr(p.cpu().numpy(), g[name + "_final"]) < TOL
+    # Adam divides every coordinate's step by its own gradient scale, so rounding noise on near-zero
+    # gradient coordinates moves those weights by O(lr) however small the gradient is: at batch 64 the
+    # fp16-operand noise is not averaged away and Adam gets its own stated tolerance here (2e-3);
+    # test_adam_batch_4096 checks it at a realistic batch.
+    assert _relerr(p.cpu().numpy(), g[name + "_final"]) < (2e-3 if name.startswith("adam") else TOL)
+
+
+def test_adam_batch_4096(dl):
+    from dlas import ops
+    batch, nb = 4096, 20
+    X, y = O.synth_rows(O.BASE_SEED, 0, batch * nb, 32)
+    p0 = O.glorot_init(DIMS, O.BASE_SEED)
+    p = _cuda(p0)
+    m, v = torch.zeros_like(p), torch.zeros_like(p)
+    gs = torch.zeros(p.numel() + 1, device="cuda")
+    losses = torch.zeros(nb, device="cuda")
+    ops.mlp_fit_steps(DIMS, dl.LOSS_MSE, dl.MODE_TC, dl.Adam().cfg(), p, m, v, _cuda(X), _cuda(y), batch, nb, 0, losses, gs,
+                      ops.mlp_workspace(DIMS, dl.MODE_TC))
+    torch.cuda.synchronize()
+    pr = p0.astype(np.float64)
+    ref = O.mlp_fit_steps(pr, DIMS, X.astype(np.float64), y.astype(np.float64), batch, nb, O.LOSS_MSE, O.adam_config(),
+                          O.opt_state(pr.size))
+    got = losses.cpu().numpy()
+    print("adam batch 4096: max per-step loss rel err %.3g; weights rel err %.3g" % (np.abs(got / ref - 1).max(), _relerr(p.cpu().numpy(), pr)))
+    np.testing.assert_allclose(got, ref, rtol=LOSS_TOL)
+    assert _relerr(p.cpu().numpy(), pr) < 5e-4
 
 
 def test_facade_100_steps_batch_4096_vs_oracle(dl):

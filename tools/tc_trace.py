@@ -1,0 +1,26 @@
+"""Debug: one 65,536-row gradient call of the tcgen05 kernel with DLAS_TC_TRACE set; prints the SM-clock
+phase breakdown of CTA 0 (epilogue thread 0 and the MMA issuer)."""
+import os
+import sys
+
+sys.path.insert(0, os.path.join(os.path.dirname(os.path.abspath(__file__)), "..", "deep-learning-at-scale_b200"))
+import torch  # noqa: E402
+import dlas  # noqa: E402
+from dlas import ops  # noqa: E402
+
+DIMS = [32, 256, 256, 1]
+X, y = ops.synth_rows(65536, 32)
+p = torch.randn(ops.mlp_n_params(DIMS), device="cuda") * 0.05
+ws = ops.mlp_workspace(DIMS, dlas.MODE_TC)
+gs = torch.zeros(p.numel() + 1, device="cuda")
+for _ in range(3):
+    ops.mlp_grad(DIMS, 0, dlas.MODE_TC, p, X, y, gs, ws)
+torch.cuda.synchronize()
+os.environ["DLAS_TC_TRACE"] = "/tmp/tc_trace.txt"
+ops.mlp_grad(DIMS, 0, dlas.MODE_TC, p, X, y, gs, ws)
+torch.cuda.synchronize()
+ev = [l.split() for l in open("/tmp/tc_trace.txt")]
+for who in ("E", "M"):
+    seq = [(int(k), int(t)) for w, k, t in ev if w == who]
+    t0 = seq[0][1]
+    print(who, " ".join("%d:%d" % (k, t - t0) for k, t in seq))

@@ -19,7 +19,7 @@ def _dev_f32(t, name):
 
 
 # ---- Gilbert --------------------------------------------------------------------------------
-def gilbert(P, S, R, out=None, variant=_lib.GILBERT_POLY):
+def gilbert(P, S, R, out=None, variant=_lib.GILBERT_MUFU):
     """q = P * S^1.89 / (435 * R^0.546), element-wise over fp32 CUDA vectors (Readme.md:7-8)."""
     _dev_f32(P, "P"), _dev_f32(S, "S"), _dev_f32(R, "R")
     if not (P.numel() == S.numel() == R.numel()):

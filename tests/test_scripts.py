@@ -1,0 +1,63 @@
+"""The spark-submit-style scripts keep the reference's argv contract (cnn.py:2, :41-44, :53-59) and its
+two closing print lines (cnn.py:133-134)."""
+import os
+import subprocess
+import sys
+
+import numpy as np
+import pytest
+
+ROOT = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
+SCRIPTS = os.path.join(ROOT, "deep-learning-at-scale_b200", "scripts")
+
+
+def test_schema_rule_and_target_exclusion(capsys):
+    sys.path.insert(0, SCRIPTS)
+    import _common as C
+    ap = C.parser("t")
+    args = ap.parse_args(["a,b,well,q", "float,int,string,float", "q", "/tmp/store/"])
+    names, cont = C.schema(args)
+    out = capsys.readouterr().out
+    assert names == ["a", "b", "well", "q"] and cont == ["a", "b"]          # target excluded (fixes D5), strings ignored
+    assert "Categorical variables: well" in out                             # cnn.py:73
+    assert (args.epochs, args.batch_size, args.patience, args.loss) == (1000, 20, 10, "mae_clip")   # cnn.py:121,128,118
+    with pytest.raises(SystemExit):
+        C.schema(ap.parse_args(["a,b", "float", "a", "/tmp/"]))
+
+
+@pytest.mark.gpu
+@pytest.mark.parametrize("script,extra", [
+    ("static_ann.py", ["--synthetic", "20000", "--hidden", "64,64", "--batch-size", "256", "--epochs", "3", "--loss", "mse"]),
+    ("dynamic_ann.py", ["--synthetic", "6000", "--lags", "24", "--hidden", "256,256", "--batch-size", "256", "--epochs", "2"]),
+    ("lstm.py", ["--synthetic", "600", "--seq-len", "12", "--hidden", "32", "--layers", "2", "--batch-size", "64", "--epochs", "2"]),
+    ("gilbert.py", ["--synthetic", "100000"]),
+])
+def test_scripts_run_with_reference_argv(tmp_path, script, extra):
+    names = ",".join("f%d" % i for i in range(8)) + ",q"
+    types = ",".join(["float"] * 9)
+    store = str(tmp_path) + "/"
+    r = subprocess.run([sys.executable, os.path.join(SCRIPTS, script), names, types, "q", store] + extra,
+                       capture_output=True, text=True, timeout=600)
+    assert r.returncode == 0, r.stdout[-1500:] + r.stderr[-1500:]
+    assert "Time elapsed:" in r.stdout
+    if script != "gilbert.py":
+        assert "Testing set loss:" in r.stdout and "Epoch 1/" in r.stdout
+        assert os.path.exists(os.path.join(store, "models", script[:-3] + ".mdl"))          # cnn.py:122
+
+
+@pytest.mark.gpu
+def test_static_ann_from_csv(tmp_path):
+    rng = np.random.default_rng(0)
+    n = 5000
+    A = rng.normal(size=(n, 3)).astype(np.float32)
+    q = (A @ np.float32([0.5, -1.0, 2.0]) + 0.1).astype(np.float32)
+    path = str(tmp_path / "wells.csv")
+    with open(path, "w") as f:
+        for i in range(n):
+            f.write("%g,%g,w%d,%g,%g\n" % (A[i, 0], A[i, 1], i % 7, A[i, 2], q[i]))
+    r = subprocess.run([sys.executable, os.path.join(SCRIPTS, "static_ann.py"), "a,b,well,c,q", "float,float,string,float,float", "q",
+                        str(tmp_path) + "/", "--data", path, "--hidden", "64,64", "--batch-size", "128", "--epochs", "30",
+                        "--optimizer", "adam", "--loss", "mse"], capture_output=True, text=True, timeout=600)
+    assert r.returncode == 0, r.stdout[-1500:] + r.stderr[-1500:]
+    loss = float(r.stdout.split("Testing set loss:")[1].split()[0])
+    assert loss < 0.05 * float(np.var(q))      # it learns the linear map

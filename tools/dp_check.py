@@ -1,0 +1,55 @@
+"""Data-parallel parity on real GPUs (run under torchrun with WORLD_SIZE ranks, NCCL):
+every rank trains on ITS shard of each global batch through the public facade; rank 0 compares the
+per-step losses and final weights with the single-process fp64 oracle on the whole batches.
+    python -m torch.distributed.run --nnodes=1 --nproc-per-node 2 --master-addr 127.0.0.1 tools/dp_check.py [fp32|tc]"""
+import os
+import sys
+
+ROOT = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
+for p in (os.path.join(ROOT, "deep-learning-at-scale_b200"), os.path.join(ROOT, "oracle")):
+    sys.path.insert(0, p)
+import numpy as np  # noqa: E402
+import torch  # noqa: E402
+import torch.distributed as dist  # noqa: E402
+import dlas  # noqa: E402
+from dlas import parallel  # noqa: E402
+import dlas_oracle as O  # noqa: E402
+
+mode = sys.argv[1] if len(sys.argv) > 1 else "fp32"
+rank, local, world = int(os.environ["RANK"]), int(os.environ["LOCAL_RANK"]), int(os.environ["WORLD_SIZE"])
+torch.cuda.set_device(local)
+dist.init_process_group("nccl", device_id=torch.device("cuda", local))
+dims = [32, 256, 256, 1]
+batch, steps = 8192, 12
+X, y = O.synth_rows(O.BASE_SEED, 0, batch * steps, 32)
+p0 = O.glorot_init(dims, O.BASE_SEED)
+mine = parallel.local_rows(X.shape[0], batch, rank, world).numpy()
+model = dlas.Sequential([dlas.Dense(32, 256, activation="relu"), dlas.Dense(256, 256, activation="relu"), dlas.Dense(256, 1)], mode=mode)
+model.compile(loss="mse", optimizer=dlas.SGD(lr=0.001, momentum=0.99, decay=1e-6, nesterov=True))
+model.set_weights_flat(p0)
+Xl, yl = torch.from_numpy(X[mine]).cuda(), torch.from_numpy(y[mine]).cuda().reshape(-1, 1)
+lb = batch // world
+losses = []
+for s in range(steps):
+    losses.append(model.train_on_batch(Xl[s * lb:(s + 1) * lb], yl[s * lb:(s + 1) * lb], global_rows=batch))
+got = torch.cat(losses).cpu().numpy()
+w = model.get_weights_flat()
+# every rank must hold identical weights after the all-reduced steps
+chk = torch.tensor([float(np.abs(w).sum())], device="cuda", dtype=torch.float64)
+lo, hi = chk.clone(), chk.clone()
+dist.all_reduce(lo, op=dist.ReduceOp.MIN)
+dist.all_reduce(hi, op=dist.ReduceOp.MAX)
+ok = True
+if rank == 0:
+    pr = p0.astype(np.float64)
+    ref = O.mlp_fit_steps(pr, dims, X.astype(np.float64), y.astype(np.float64), batch, steps, O.LOSS_MSE, O.sgd_config(), O.opt_state(pr.size))
+    lerr = float(np.abs(got / ref - 1).max())
+    werr = float(np.linalg.norm(w - pr) / np.linalg.norm(pr))
+    same = float(hi.item() - lo.item())
+    tol_l = 1e-4 if mode == "fp32" else 3e-4
+    ok = lerr < tol_l and werr < 1e-4 and same == 0.0
+    print("dp_check world=%d mode=%s: max loss rel err %.3g, weights rel err %.3g, rank spread %.3g -> %s"
+          % (world, mode, lerr, werr, same, "OK" if ok else "FAIL"), flush=True)
+dist.barrier()
+dist.destroy_process_group()
+sys.exit(0 if ok else 1)

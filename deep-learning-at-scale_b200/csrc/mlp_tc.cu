@@ -77,6 +77,12 @@ __device__ __forceinline__ float warp_colsum32(float (&v)[32], int lane) {
   return v[0];
 }
 
+// every lane has done its own fences; one arrival for the warp
+__device__ __forceinline__ void warp_arrive(int lane, uint64_t* bar) {
+  __syncwarp();
+  if (lane == 0) mbar_arrive(bar);
+}
+
 __device__ __forceinline__ uint4 pack8(float4 a, float4 b) {
   return make_uint4(pack_half2(a.x, a.y), pack_half2(a.z, a.w), pack_half2(b.x, b.y), pack_half2(b.z, b.w));
 }
@@ -108,13 +114,17 @@ mlp_tc_kernel(const int loss_kind, const float* __restrict__ params, const float
   // ---- one-time set-up: barriers, TMEM, weights -> fp16 tiles -------------------------------------------
   if (tid == 0) {
     mbar_init(&bars[B_DONE0], 1); mbar_init(&bars[B_DONE1], 1);
-    mbar_init(&bars[B_FREE0], N_EPI); mbar_init(&bars[B_FREE1], N_EPI);
-    mbar_init(&bars[B_X0], N_EPI); mbar_init(&bars[B_X1], N_EPI);
-    mbar_init(&bars[B_H1], N_EPI); mbar_init(&bars[B_DZ2], N_EPI); mbar_init(&bars[B_DZ1], N_EPI);
+    // one arrival per epilogue WARP (lane 0, after __syncwarp): 256 per-thread arrivals on one word would serialise
+    mbar_init(&bars[B_FREE0], N_EPI / 32); mbar_init(&bars[B_FREE1], N_EPI / 32);
+    mbar_init(&bars[B_X0], N_EPI / 32); mbar_init(&bars[B_X1], N_EPI / 32);
+    mbar_init(&bars[B_H1], N_EPI / 32); mbar_init(&bars[B_DZ2], N_EPI / 32); mbar_init(&bars[B_DZ1], N_EPI / 32);
     mbar_init(&bars[B_ALL], 1);
     mbar_fence_init();
   }
   if (warp == 8) tmem_alloc(tmem_slot, TM_COLS);
+  // Programmatic dependent launch: everything above overlaps the tail of the previous kernel in the stream
+  // (the optimiser update that produced `params`); from here on its writes are visible.
+  asm volatile("griddepcontrol.wait;" ::: "memory");
   {
     // sW1 = [W1 ; b1 ; 0]: rows 0..31 weights, row 32 the bias (it multiplies the ones column of [x | 1 | 0]),
     // rows 33..47 zero -> Z1 comes out of the MMA with the bias already added
@@ -166,6 +176,8 @@ mlp_tc_kernel(const int loss_kind, const float* __restrict__ params, const float
   const uint32_t tm = *tmem_slot;
   TRACE_E(2);
 
+  // dependents (the reduction kernel) may be scheduled from now on; they block in griddepcontrol.wait until this grid is done
+  asm volatile("griddepcontrol.launch_dependents;" ::: "memory");
   const int my_tiles = (n_tiles > (size_t)pair) ? (int)((n_tiles - pair + n_pairs - 1) / n_pairs) : 0;
 
   if (warp == 8) {
@@ -242,11 +254,13 @@ mlp_tc_kernel(const int loss_kind, const float* __restrict__ params, const float
                     !(first && i == 0));
       }
       __syncwarp();
+      TRACE_M(60);
       // dH1p = dZ2h W2h^T: four N=64 chunks (in-index)
 #pragma unroll
       for (int s = 0; s < 4; ++s, ++n) {
         const uint32_t b = n & 1;
         ok = mbar_wait(&bars[B_FREE0 + b], ((n >> 1) & 1) ^ 1) && ok;
+        TRACE_M(61);
         fence_after();
         if (leader) {
 #pragma unroll
@@ -299,7 +313,7 @@ mlp_tc_kernel(const int loss_kind, const float* __restrict__ params, const float
       sts128(sX + j * 16384 + tile_chunk_off(TILE, xr, xh * 16 + 8), pack8(xv[2], xv[3]));
       if (tid < TILE) f32[F_Y + j * 128 + tid] = yv;
       fence_async_smem();
-      mbar_arrive(&bars[B_X0 + j]);
+      warp_arrive(lane, &bars[B_X0 + j]);
     };
     if (my_tiles > 0) {
       x_issue(pair);
@@ -315,13 +329,17 @@ mlp_tc_kernel(const int loss_kind, const float* __restrict__ params, const float
 #pragma unroll 1
       for (int s = 0; s < 4; ++s, ++n) {
         const uint32_t b = n & 1;
+        TRACE_E(40);
         ok = mbar_wait(&bars[B_DONE0 + b], (n >> 1) & 1) && ok;
+        TRACE_E(41);
         fence_after();
         uint32_t v[32];
         tmem_ld32(tm + TM_W0 + b * 64 + lane_base + hh * 32, v);
         tmem_ld_wait();
+        TRACE_E(42);
         fence_before();
-        mbar_arrive(&bars[B_FREE0 + b]);
+        warp_arrive(lane, &bars[B_FREE0 + b]);
+        TRACE_E(43);
         const int c0 = s * 64 + hh * 32;
 #pragma unroll
         for (int g8 = 0; g8 < 4; ++g8) {   // relu on packed halves: one F2FP + one HMNMX2 per two elements
@@ -334,7 +352,7 @@ mlp_tc_kernel(const int loss_kind, const float* __restrict__ params, const float
         }
       }
       fence_async_smem();
-      mbar_arrive(&bars[B_H1]);
+      warp_arrive(lane, &bars[B_H1]);
       TRACE_E(21);
       if (it + 1 < my_tiles) x_store((it + 1) & 1);        // the other X buffer was last read by tile it-1's dW1
       // ---- (c) Z2h: partial output dot, exchange, dZ2h -> sDZ2 ---------------------------------------
@@ -394,7 +412,7 @@ mlp_tc_kernel(const int loss_kind, const float* __restrict__ params, const float
         tmem_ld32(tm + TM_W0 + b * 64 + lane_base + hh * 32, v);
         tmem_ld_wait();
         fence_before();
-        mbar_arrive(&bars[B_FREE0 + b]);
+        warp_arrive(lane, &bars[B_FREE0 + b]);
         float hg[32];
 #pragma unroll
         for (int g8 = 0; g8 < 4; ++g8) {
@@ -416,19 +434,22 @@ mlp_tc_kernel(const int loss_kind, const float* __restrict__ params, const float
         acc_w3[s] += warp_colsum32(hg, lane);
       }
       fence_async_smem();
-      mbar_arrive(&bars[B_DZ2]);
+      warp_arrive(lane, &bars[B_DZ2]);
       TRACE_E(26);
       // ---- (d) dZ1p = relu'(H1) o dH1p in place over H1, four chunks -----------------------------------
 #pragma unroll 1
       for (int s = 0; s < 4; ++s, ++n) {
         const uint32_t b = n & 1;
+        TRACE_E(50);
         ok = mbar_wait(&bars[B_DONE0 + b], (n >> 1) & 1) && ok;
+        TRACE_E(51);
         fence_after();
         uint32_t v[32];
         tmem_ld32(tm + TM_W0 + b * 64 + lane_base + hh * 32, v);
         tmem_ld_wait();
         fence_before();
-        mbar_arrive(&bars[B_FREE0 + b]);
+        warp_arrive(lane, &bars[B_FREE0 + b]);
+        TRACE_E(52);
         const int c0 = s * 64 + hh * 32;
 #pragma unroll
         for (int g8 = 0; g8 < 4; ++g8) {
@@ -443,7 +464,7 @@ mlp_tc_kernel(const int loss_kind, const float* __restrict__ params, const float
         }
       }
       fence_async_smem();
-      mbar_arrive(&bars[B_DZ1]);
+      warp_arrive(lane, &bars[B_DZ1]);
       TRACE_E(27);
     }
 
@@ -507,6 +528,7 @@ mlp_tc_kernel(const int loss_kind, const float* __restrict__ params, const float
   }
   TRACE_E(32);
   if (!ok && lane == 0) atomicExch(err_flag, call_id);
+
   // ---- teardown ----------------------------------------------------------------------------------------
   fence_before();
   __syncthreads();
@@ -524,16 +546,29 @@ __global__ void __launch_bounds__(256)
 tc_reduce_kernel(const float* __restrict__ partials, int n_active_pairs, const unsigned* __restrict__ err_flag,
                  unsigned call_id, float* __restrict__ out, OptScalars opt, float grad_scale, float* __restrict__ params,
                  float* __restrict__ m, float* __restrict__ v, float* __restrict__ loss_out) {
-  const int i = blockIdx.x * 256 + threadIdx.x;
-  if (i > N_PARAMS) return;
+  // 64 consecutive entries per block; the list of contributing CTAs is cut into 4 contiguous quarters summed by 4
+  // thread groups (more loads in flight: the pass is latency-bound), then added in quarter order -> still deterministic
+  __shared__ float red[3][64];
+  asm volatile("griddepcontrol.launch_dependents;" ::: "memory");   // next gradient kernel: set-up may overlap this pass
+  asm volatile("griddepcontrol.wait;" ::: "memory");   // the gradient kernel has completed; its partials are visible
+  const int i = blockIdx.x * 64 + (threadIdx.x & 63), grp = threadIdx.x >> 6;
+  const bool live = i <= N_PARAMS;
   int first = 0, step = 1;
   if (i >= W2_OFF && i < B2_OFF) { first = ((i - W2_OFF) % D2) / 128; step = 2; }
   else if (i >= B2_OFF && i < W3_OFF) { first = (i - B2_OFF) / 128; step = 2; }
   else if (i >= W3_OFF && i < B3_OFF) { first = (i - W3_OFF) / 128; step = 2; }
   else if (i >= B3_OFF) { first = 0; step = 2; }
+  const int n_src = (2 * n_active_pairs - first + step - 1) / step;        // contributing CTAs
+  const int per = (n_src + 3) / 4, k0 = grp * per, k1 = min(n_src, k0 + per);
   float s = 0.f;
+  if (live) {
 #pragma unroll 8
-  for (int c = first; c < 2 * n_active_pairs; c += step) s += partials[(size_t)c * PSTRIDE + i];
+    for (int k = k0; k < k1; ++k) s += partials[(size_t)(first + k * step) * PSTRIDE + i];
+  }
+  if (grp > 0) red[grp - 1][threadIdx.x & 63] = s;
+  __syncthreads();
+  if (grp > 0 || !live) return;
+  s = ((s + red[0][threadIdx.x]) + red[1][threadIdx.x]) + red[2][threadIdx.x];
   // an mbarrier wait timed out inside this call's tcgen05 kernel: fail loudly, never return numbers
   if (*err_flag == call_id) s = __int_as_float(0x7fc00000);
   if (out) out[i] = s;
@@ -549,6 +584,7 @@ tc_reduce_kernel(const float* __restrict__ partials, int n_active_pairs, const u
     }
   }
 }
+
 
 int n_ctas() { return (sm_count() / 2) * 2; }
 unsigned g_call_id = 0x5eed0000u;
@@ -577,7 +613,19 @@ int launch_main(int loss, const float* params, const float* X, const float* y, s
     DLAS_CUDA(cudaMalloc(&trace, 1024 * sizeof(long long)));
     DLAS_CUDA(cudaMemsetAsync(trace, 0, 1024 * sizeof(long long), st));
   }
-  mlp_tc_kernel<<<grid, NT, SMEM_BYTES, st>>>(loss, params, X, y, n_rows, partials, err_flag, g_call_id, trace);
+  {
+    cudaLaunchConfig_t cfg = {};
+    cfg.gridDim = dim3(grid);
+    cfg.blockDim = dim3(NT);
+    cfg.dynamicSmemBytes = SMEM_BYTES;
+    cfg.stream = st;
+    cudaLaunchAttribute at[1];
+    at[0].id = cudaLaunchAttributeProgrammaticStreamSerialization;
+    at[0].val.programmaticStreamSerializationAllowed = 1;
+    cfg.attrs = at;
+    cfg.numAttrs = 1;
+    DLAS_CUDA(cudaLaunchKernelEx(&cfg, mlp_tc_kernel, loss, params, X, y, n_rows, partials, err_flag, g_call_id, trace));
+  }
   prof_end(pi, st);
   DLAS_LAUNCH_CHECK();
   if (trace_path) {
@@ -596,6 +644,23 @@ int launch_main(int loss, const float* params, const float* X, const float* y, s
   *n_active_pairs = (int)(n_tiles < (size_t)(grid / 2) ? n_tiles : (size_t)(grid / 2));
   *partials_out = partials;
   *err_out = err_flag;
+  return DLAS_OK;
+}
+
+template <bool FUSE>
+int launch_reduce(cudaStream_t st, const float* partials, int nap, const unsigned* err, float* out, OptScalars o,
+                  float grad_scale, float* params, float* m, float* v, float* loss_out) {
+  cudaLaunchConfig_t cfg = {};
+  cfg.gridDim = dim3((N_PARAMS + 1 + 63) / 64);
+  cfg.blockDim = dim3(256);
+  cfg.stream = st;
+  cudaLaunchAttribute at[1];
+  at[0].id = cudaLaunchAttributeProgrammaticStreamSerialization;
+  at[0].val.programmaticStreamSerializationAllowed = 1;
+  cfg.attrs = at;
+  cfg.numAttrs = 1;
+  DLAS_CUDA(cudaLaunchKernelEx(&cfg, tc_reduce_kernel<FUSE>, partials, nap, err, g_call_id, out, o, grad_scale, params, m, v,
+                               loss_out));
   return DLAS_OK;
 }
 
@@ -627,9 +692,8 @@ int tc_grad(const int* dims, int n_layers, int loss, const float* params, const 
   float* partials; unsigned* err; int nap;
   int rc = launch_main(loss, params, X, y, n_rows, workspace, workspace_bytes, st, &partials, &err, &nap);
   if (rc != DLAS_OK) return rc;
-  tc_reduce_kernel<false><<<(N_PARAMS + 1 + 255) / 256, 256, 0, st>>>(partials, nap, err, g_call_id, grad_sum, OptScalars{},
-                                                                     0.f, nullptr, nullptr, nullptr, nullptr);
-  DLAS_LAUNCH_CHECK();
+  rc = launch_reduce<false>(st, partials, nap, err, grad_sum, OptScalars{}, 0.f, nullptr, nullptr, nullptr, nullptr);
+  if (rc != DLAS_OK) return rc;
   return DLAS_OK;
 }
 
@@ -648,9 +712,8 @@ int tc_fit_step(const int* dims, int n_layers, int loss, const dlas_opt_cfg* cfg
   float* partials; unsigned* err; int nap;
   rc = launch_main(loss, params, X, y, n_rows, workspace, workspace_bytes, st, &partials, &err, &nap);
   if (rc != DLAS_OK) return rc;
-  tc_reduce_kernel<true><<<(N_PARAMS + 1 + 255) / 256, 256, 0, st>>>(partials, nap, err, g_call_id, nullptr, o,
-                                                                    1.0f / (float)n_rows, params, m, v, loss_out);
-  DLAS_LAUNCH_CHECK();
+  rc = launch_reduce<true>(st, partials, nap, err, nullptr, o, 1.0f / (float)n_rows, params, m, v, loss_out);
+  if (rc != DLAS_OK) return rc;
   return DLAS_OK;
 }
 

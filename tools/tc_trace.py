@@ -23,4 +23,6 @@ ev = [l.split() for l in open("/tmp/tc_trace.txt")]
 for who in ("E", "M"):
     seq = [(int(k), int(t)) for w, k, t in ev if w == who]
     t0 = seq[0][1]
-    print(who, " ".join("%d:%d" % (k, t - t0) for k, t in seq))
+    out = " ".join("%d:%d" % (k, t - t0) for k, t in seq)
+    open(os.path.join(os.path.dirname(os.path.abspath(__file__)), "..", "gpurun_out", "tc_trace_%s.txt" % who), "w").write(out + "\n")
+    print(who, out[:1500])

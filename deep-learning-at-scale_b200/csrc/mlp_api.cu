@@ -6,7 +6,8 @@ namespace dlas {
 // mlp_simt.cu
 size_t simt_workspace_bytes(const int* dims, int n_layers);
 int simt_grad(const int* dims, int n_layers, int loss, const float* params, const float* X, const float* y,
-              size_t n_rows, float* grad_sum, void* workspace, size_t workspace_bytes, cudaStream_t st);
+              size_t n_rows, float* grad_sum, void* workspace, size_t workspace_bytes, cudaStream_t st,
+              const long long* cursor = nullptr);
 int simt_eval_loss(const int* dims, int n_layers, int loss, const float* params, const float* X, const float* y,
                    size_t n_rows, float* loss_sum, void* workspace, size_t workspace_bytes, cudaStream_t st);
 int simt_predict(const int* dims, int n_layers, const float* params, const float* X, size_t n_rows, float* yhat,
@@ -18,7 +19,8 @@ int opt_step_impl(const dlas_opt_cfg* cfg, float* params, float* m, float* v, co
 bool tc_supported(const int* dims, int n_layers);
 size_t tc_workspace_bytes(const int* dims, int n_layers);
 int tc_grad(const int* dims, int n_layers, int loss, const float* params, const float* X, const float* y,
-            size_t n_rows, float* grad_sum, void* workspace, size_t workspace_bytes, cudaStream_t st);
+            size_t n_rows, float* grad_sum, void* workspace, size_t workspace_bytes, cudaStream_t st,
+            const long long* cursor = nullptr);
 int tc_fit_step(const int* dims, int n_layers, int loss, const dlas_opt_cfg* cfg, float* params, float* m, float* v,
                 const float* X, const float* y, size_t n_rows, uint64_t iteration, float* loss_out, void* workspace,
                 size_t workspace_bytes, cudaStream_t st);
@@ -72,6 +74,23 @@ extern "C" int dlas_mlp_grad(const int* dims, int n_layers, int loss, int mode, 
                    (cudaStream_t)stream);
   return simt_grad(dims, n_layers, loss, params, X, y, n_rows, grad_sum, workspace, workspace_bytes,
                    (cudaStream_t)stream);
+}
+
+extern "C" int dlas_mlp_grad_at(const int* dims, int n_layers, int loss, int mode, const float* params,
+                                const float* X_base, const float* y_base, size_t batch_rows,
+                                const dlas_step_state* state_dev, float* grad_sum, void* workspace,
+                                size_t workspace_bytes, void* stream) {
+  DLAS_CHECK_DEVICE();
+  int rc = check_common("dlas_mlp_grad_at", dims, n_layers, loss, mode);
+  if (rc != DLAS_OK) return rc;
+  DLAS_REQUIRE(params && grad_sum && X_base && y_base && state_dev, "dlas_mlp_grad_at: null pointer");
+  DLAS_REQUIRE(batch_rows >= 1, "dlas_mlp_grad_at: batch_rows is 0");
+  const long long* cursor = reinterpret_cast<const long long*>(&state_dev->cursor);
+  if (mode == DLAS_MODE_TC)
+    return tc_grad(dims, n_layers, loss, params, X_base, y_base, batch_rows, grad_sum, workspace, workspace_bytes,
+                   (cudaStream_t)stream, cursor);
+  return simt_grad(dims, n_layers, loss, params, X_base, y_base, batch_rows, grad_sum, workspace, workspace_bytes,
+                   (cudaStream_t)stream, cursor);
 }
 
 extern "C" int dlas_mlp_fit_steps(const int* dims, int n_layers, int loss, int mode,

@@ -90,8 +90,13 @@ enum { KIND_TRAIN = 0, KIND_EVAL = 1, KIND_PREDICT = 2 };
 template <int KIND>
 __global__ void __launch_bounds__(NT, 1)
 mlp_simt_kernel(const MlpDesc d, const int loss, const float* __restrict__ params,
-                const float* __restrict__ WT, const float* __restrict__ X, const float* __restrict__ y,
-                const size_t n_rows, float* __restrict__ partials, float* __restrict__ yhat) {
+                const float* __restrict__ WT, const float* __restrict__ X_base, const float* __restrict__ y_base,
+                const size_t n_rows, float* __restrict__ partials, float* __restrict__ yhat,
+                const long long* __restrict__ cursor) {
+  // device-resident batch cursor (replayable steps): rows [cursor*n_rows, (cursor+1)*n_rows)
+  const size_t batch0 = cursor ? (size_t)cursor[0] * n_rows : 0;
+  const float* __restrict__ X = X_base + batch0 * d.dims[0];
+  const float* __restrict__ y = y_base ? y_base + batch0 * d.dims[d.n_layers] : nullptr;
   extern __shared__ __align__(16) float smem[];
   const int L = d.n_layers;
   const int d0 = d.dims[0], dL = d.dims[L];
@@ -224,14 +229,15 @@ int grid_size() { return sm_count(); }
 
 template <int KIND>
 int launch_main(const MlpDesc& d, int loss, const float* params, const float* WT, const float* X,
-                const float* y, size_t n_rows, float* partials, float* yhat, cudaStream_t st) {
+                const float* y, size_t n_rows, float* partials, float* yhat, cudaStream_t st,
+                const long long* cursor = nullptr) {
   static bool attr_set = false;
   size_t smem = (size_t)d.smem_floats * sizeof(float);
   if (!attr_set) {
     DLAS_CUDA(cudaFuncSetAttribute(mlp_simt_kernel<KIND>, cudaFuncAttributeMaxDynamicSharedMemorySize, 227 * 1024));
     attr_set = true;
   }
-  mlp_simt_kernel<KIND><<<grid_size(), NT, smem, st>>>(d, loss, params, WT, X, y, n_rows, partials, yhat);
+  mlp_simt_kernel<KIND><<<grid_size(), NT, smem, st>>>(d, loss, params, WT, X, y, n_rows, partials, yhat, cursor);
   DLAS_LAUNCH_CHECK();
   return DLAS_OK;
 }
@@ -246,7 +252,8 @@ size_t simt_workspace_bytes(const int* dims, int n_layers) {
 }
 
 int simt_grad(const int* dims, int n_layers, int loss, const float* params, const float* X, const float* y,
-              size_t n_rows, float* grad_sum, void* workspace, size_t workspace_bytes, cudaStream_t st) {
+              size_t n_rows, float* grad_sum, void* workspace, size_t workspace_bytes, cudaStream_t st,
+              const long long* cursor) {
   MlpDesc d;
   int rc = make_desc(dims, n_layers, d);
   if (rc != DLAS_OK) return rc;
@@ -264,7 +271,7 @@ int simt_grad(const int* dims, int n_layers, int loss, const float* params, cons
   transpose_weights_kernel<<<64, 256, 0, st>>>(d, params, WT);
   DLAS_LAUNCH_CHECK();
   int pi = prof_begin(DLAS_PROF_MLP_GRAD, st);
-  rc = launch_main<KIND_TRAIN>(d, loss, params, WT, X, y, n_rows, partials, nullptr, st);
+  rc = launch_main<KIND_TRAIN>(d, loss, params, WT, X, y, n_rows, partials, nullptr, st, cursor);
   prof_end(pi, st);
   if (rc != DLAS_OK) return rc;
   size_t n_tiles = (n_rows + R - 1) / R;

@@ -92,9 +92,14 @@ __device__ __forceinline__ uint4 pack8(float4 a, float4 b) {
 #define TRACE_M(k) do { if (trace && blockIdx.x == 0 && lane == 0 && tmm < 500) trace[512 + tmm++] = ((long long)(k) << 48) | (clock64() & 0xFFFFFFFFFFFFll); } while (0)
 
 __global__ void __cluster_dims__(2, 1, 1) __launch_bounds__(NT, 1)
-mlp_tc_kernel(const int loss_kind, const float* __restrict__ params, const float* __restrict__ X,
-              const float* __restrict__ y, const size_t n_rows, float* __restrict__ partials,
-              unsigned* __restrict__ err_flag, const unsigned call_id, long long* __restrict__ trace) {
+mlp_tc_kernel(const int loss_kind, const float* __restrict__ params, const float* __restrict__ X_base,
+              const float* __restrict__ y_base, const size_t n_rows, float* __restrict__ partials,
+              unsigned* __restrict__ err_flag, const unsigned call_id, long long* __restrict__ trace,
+              const long long* __restrict__ cursor) {
+  // device-resident batch cursor (replayable steps): this launch works on rows [cursor*n_rows, (cursor+1)*n_rows)
+  const size_t batch0 = cursor ? (size_t)cursor[0] * n_rows : 0;
+  const float* __restrict__ X = X_base + batch0 * D0;
+  const float* __restrict__ y = y_base + batch0;
   extern __shared__ __align__(1024) uint8_t smem[];
   float* f32 = reinterpret_cast<float*>(smem + S_F32);
   uint64_t* bars = reinterpret_cast<uint64_t*>(smem + S_BAR);
@@ -590,7 +595,8 @@ int n_ctas() { return (sm_count() / 2) * 2; }
 unsigned g_call_id = 0x5eed0000u;
 
 int launch_main(int loss, const float* params, const float* X, const float* y, size_t n_rows, void* workspace,
-                size_t workspace_bytes, cudaStream_t st, float** partials_out, unsigned** err_out, int* n_active_pairs) {
+                size_t workspace_bytes, cudaStream_t st, float** partials_out, unsigned** err_out, int* n_active_pairs,
+                const long long* cursor = nullptr) {
   size_t need = (size_t)n_ctas() * PSTRIDE * sizeof(float) + 256;
   if (workspace == nullptr || workspace_bytes < need) {
     set_error("mlp (tc): workspace of %zu bytes given, %zu needed", workspace_bytes, need);
@@ -624,7 +630,7 @@ int launch_main(int loss, const float* params, const float* X, const float* y, s
     at[0].val.programmaticStreamSerializationAllowed = 1;
     cfg.attrs = at;
     cfg.numAttrs = 1;
-    DLAS_CUDA(cudaLaunchKernelEx(&cfg, mlp_tc_kernel, loss, params, X, y, n_rows, partials, err_flag, g_call_id, trace));
+    DLAS_CUDA(cudaLaunchKernelEx(&cfg, mlp_tc_kernel, loss, params, X, y, n_rows, partials, err_flag, g_call_id, trace, cursor));
   }
   prof_end(pi, st);
   DLAS_LAUNCH_CHECK();
@@ -680,7 +686,8 @@ size_t tc_workspace_bytes(const int* dims, int n_layers) {
 
 // forward + loss + backward: grad_sum[0..n) gradient sums, grad_sum[n] loss sum
 int tc_grad(const int* dims, int n_layers, int loss, const float* params, const float* X, const float* y,
-            size_t n_rows, float* grad_sum, void* workspace, size_t workspace_bytes, cudaStream_t st) {
+            size_t n_rows, float* grad_sum, void* workspace, size_t workspace_bytes, cudaStream_t st,
+            const long long* cursor) {
   if (!tc_supported(dims, n_layers)) {
     set_error("DLAS_MODE_TC supports the 32-256-256-1 network only");
     return DLAS_ERR_UNSUPPORTED_SHAPE;
@@ -690,7 +697,7 @@ int tc_grad(const int* dims, int n_layers, int loss, const float* params, const 
     return DLAS_OK;
   }
   float* partials; unsigned* err; int nap;
-  int rc = launch_main(loss, params, X, y, n_rows, workspace, workspace_bytes, st, &partials, &err, &nap);
+  int rc = launch_main(loss, params, X, y, n_rows, workspace, workspace_bytes, st, &partials, &err, &nap, cursor);
   if (rc != DLAS_OK) return rc;
   rc = launch_reduce<false>(st, partials, nap, err, grad_sum, OptScalars{}, 0.f, nullptr, nullptr, nullptr, nullptr);
   if (rc != DLAS_OK) return rc;

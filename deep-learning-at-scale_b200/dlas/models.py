@@ -108,6 +108,24 @@ class ModelCheckpoint:
         return False
 
 
+class GraphStepper:
+    """Replays a captured training step (Sequential.graph_stepper)."""
+
+    def __init__(self, model, graph, state, ring):
+        self.model, self.graph, self.state, self.ring = model, graph, state, ring
+
+    def run(self, n_steps):
+        for _ in range(n_steps):
+            self.graph.replay()
+        self.model.iterations += n_steps
+
+    def recent_losses(self, n):
+        """The batch-mean losses of the last n steps (device ring buffer -> host)."""
+        it = int(self.state[1].item())
+        idx = torch.arange(it - n, it, device=self.ring.device) % self.ring.numel()
+        return self.ring[idx].cpu().numpy()
+
+
 # ---- the model -------------------------------------------------------------------------------
 class Sequential:
     def __init__(self, layers=None, mode="fp32", seed=ops.BASE_SEED, device=None):
@@ -318,6 +336,39 @@ class Sequential:
             if stop:
                 break
         return history
+
+    def graph_stepper(self, X, Y, local_batch, global_rows=None, ring_len=4096, warmup_steps=3):
+        """Capture ONE whole training step -- gradient kernels on this rank's next `local_batch` rows of the
+        resident (X, Y), the all-reduce of the flat bucket, the optimiser update, the cursor advance -- in a
+        CUDA graph and return a GraphStepper whose .run(n) replays it n times with no per-step host work.
+        The batch cursor and the iteration counter live in device memory (dlas_step_state), so every replay
+        trains on the next batch with the right learning-rate schedule.  `warmup_steps` real steps run first."""
+        dims = self.dims
+        n_batches = X.shape[0] // local_batch
+        if n_batches < 1:
+            raise ValueError("need at least one whole batch of %d rows" % local_batch)
+        rows = global_rows if global_rows is not None else local_batch * self.world
+        state = torch.tensor([0, self.iterations], dtype=torch.int64, device=self.device)
+        ring = torch.zeros(ring_len, dtype=torch.float32, device=self.device)
+        Y = Y.reshape(-1, dims[-1])
+
+        def one_step():
+            ops.mlp_grad_at(dims, self.loss, self.mode, self.params, X, Y, local_batch, state, self.grad_sum, self.workspace)
+            parallel.allreduce_sum_(self.grad_sum)
+            ops.opt_step_at(self.cfg, self.params, self.m, self.v, self.grad_sum, 1.0 / rows, state, ring)
+            ops.step_advance(state, n_batches)
+
+        side = torch.cuda.Stream(device=self.device)
+        side.wait_stream(torch.cuda.current_stream())
+        with torch.cuda.stream(side):
+            for _ in range(warmup_steps):
+                one_step()
+        torch.cuda.current_stream().wait_stream(side)
+        graph = torch.cuda.CUDAGraph()
+        with torch.cuda.graph(graph):
+            one_step()
+        self.iterations += warmup_steps               # capture records the step, it does not run it
+        return GraphStepper(self, graph, state, ring)
 
     def fit_host(self, x_host, y_host, batch_size, n_steps, losses_host=None, first_batch=0):
         """Train `n_steps` steps streaming batches from (pinned) HOST tensors: the host->device copy

@@ -176,3 +176,20 @@ def lstm_predict(d_in, hidden, n_layers, T, params, X, workspace, out=None):
     check(_lib.load().dlas_lstm_predict(d_in, hidden, n_layers, T, ptr(params), ptr(X), X.shape[0], ptr(out),
                                         ptr(workspace), workspace.numel(), stream_ptr()))
     return out
+
+
+# ---- replayable steps: cursor + iteration counter in device memory (CUDA-graph friendly) --------------
+def mlp_grad_at(dims, loss, mode, params, X_base, y_base, batch_rows, state, grad_sum, workspace):
+    check(_lib.load().dlas_mlp_grad_at(int_array(dims), len(dims) - 1, int(loss), int(mode), ptr(params), ptr(X_base),
+                                       ptr(y_base), int(batch_rows), ptr(state), ptr(grad_sum), ptr(workspace),
+                                       workspace.numel(), stream_ptr()))
+
+
+def opt_step_at(cfg, params, m, v, grad_sum, grad_scale, state, loss_ring=None):
+    check(_lib.load().dlas_opt_step_at(C.byref(cfg), ptr(params), ptr(m), ptr(v), ptr(grad_sum), params.numel(),
+                                       float(grad_scale), ptr(state), ptr(loss_ring),
+                                       0 if loss_ring is None else loss_ring.numel(), stream_ptr()))
+
+
+def step_advance(state, n_batches):
+    check(_lib.load().dlas_step_advance(ptr(state), int(n_batches), stream_ptr()))

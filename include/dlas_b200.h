@@ -114,6 +114,27 @@ int dlas_mlp_grad(const int* dims, int n_layers, int loss, int mode, const float
 int dlas_opt_step(const dlas_opt_cfg* cfg, float* params, float* m, float* v, const float* grad_sum,
                   size_t n, float grad_scale, uint64_t iteration, float* loss_out, void* stream);
 
+/* Replayable steps (no reference counterpart: cnn.py:127-128 drives every batch from the host).  The batch
+ * cursor and the optimiser's iteration counter live in DEVICE memory, so that one step
+ *   dlas_mlp_grad_at -> [all-reduce of grad_sum] -> dlas_opt_step_at -> dlas_step_advance
+ * can be captured once in a CUDA graph and replayed with no host work per step.
+ *   dlas_mlp_grad_at  : dlas_mlp_grad on rows [cursor*batch_rows, (cursor+1)*batch_rows) of X_base / y_base
+ *   dlas_opt_step_at  : dlas_opt_step with the learning-rate schedule / Adam bias taken from state->iteration;
+ *                       the batch-mean loss goes to loss_ring[iteration % ring_len] (may be NULL)
+ *   dlas_step_advance : cursor = (cursor + 1) % n_batches; iteration += 1 */
+typedef struct dlas_step_state {
+  int64_t cursor;
+  int64_t iteration;
+} dlas_step_state;
+int dlas_mlp_grad_at(const int* dims, int n_layers, int loss, int mode, const float* params,
+                     const float* X_base, const float* y_base, size_t batch_rows,
+                     const dlas_step_state* state_dev, float* grad_sum, void* workspace,
+                     size_t workspace_bytes, void* stream);
+int dlas_opt_step_at(const dlas_opt_cfg* cfg, float* params, float* m, float* v, const float* grad_sum,
+                     size_t n, float grad_scale, const dlas_step_state* state_dev, float* loss_ring,
+                     int64_t ring_len, void* stream);
+int dlas_step_advance(dlas_step_state* state_dev, int64_t n_batches, void* stream);
+
 /* n_steps consecutive single-GPU mini-batch steps (the `model.fit` inner loop, cnn.py:127-128):
  * step s uses rows [b*batch, (b+1)*batch) with b = batch_order_host ? batch_order_host[s]
  * : first_batch + s.  step_losses (device, n_steps floats, may be NULL) receives the batch-mean

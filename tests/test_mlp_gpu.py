@@ -201,3 +201,40 @@ def test_full_size_batch_properties(dl):
     lr, gref = O.mlp_loss_grad_sums(p.cpu().numpy().astype(np.float64), dims, Xh.astype(np.float64), yh.astype(np.float64), 0)
     g = a.cpu().numpy()
     assert g[-1] == pytest.approx(lr, rel=TOL) and _relerr(g[:-1], gref) < TOL
+
+
+@pytest.mark.parametrize("mode,dims", [("fp32", [8, 64, 64, 1]), ("tc", [32, 256, 256, 1])])
+def test_graph_replayed_steps_match_host_driven_steps(dl, mode, dims):
+    """A step captured once in a CUDA graph (device-resident batch cursor and iteration counter) and
+    replayed must give what the host-driven step loop gives -- same batches, same lr schedule."""
+    batch, nb = 1024, 12
+    X, y = O.synth_rows(O.BASE_SEED, 0, batch * nb, dims[0])
+    p0 = O.glorot_init(dims, 3)
+
+    def make():
+        m = dl.Sequential(mode=mode)
+        for a, b in zip(dims[:-2], dims[1:-1]):
+            m.add(dl.Dense(a, b, activation="relu"))
+        m.add(dl.Dense(dims[-2], dims[-1]))
+        m.compile(loss="mse", optimizer=dl.SGD(lr=0.01, momentum=0.9, decay=1e-3, nesterov=True))   # visible decay
+        m.set_weights_flat(p0)
+        return m
+
+    Xd, yd = _cuda(X), _cuda(y).reshape(-1, 1)
+    a = make()
+    st = a.graph_stepper(Xd, yd, batch, warmup_steps=3)     # steps 0..2 run eagerly, then the step is captured
+    st.run(nb + 4 - 3)                                       # steps 3..15: the cursor wraps after 12 batches
+    torch.cuda.synchronize()
+    b = make()
+    for s in range(nb + 4):
+        k = s % nb
+        b.train_on_batch(Xd[k * batch:(k + 1) * batch], yd[k * batch:(k + 1) * batch])
+    torch.cuda.synchronize()
+    assert a.iterations == b.iterations == nb + 4
+    np.testing.assert_allclose(a.get_weights_flat(), b.get_weights_flat(), rtol=1e-5, atol=1e-7)
+    pr = p0.astype(np.float64)
+    cfg, stt = O.sgd_config(lr=0.01, momentum=0.9, decay=1e-3), O.opt_state(pr.size)
+    ref = np.concatenate([O.mlp_fit_steps(pr, dims, X.astype(np.float64), y.astype(np.float64), batch, nb, O.LOSS_MSE, cfg, stt),
+                          O.mlp_fit_steps(pr, dims, X.astype(np.float64), y.astype(np.float64), batch, 4, O.LOSS_MSE, cfg, stt)])
+    np.testing.assert_allclose(st.recent_losses(8), ref[-8:], rtol=3e-4 if mode == "tc" else 1e-4)
+    assert _relerr(a.get_weights_flat(), pr) < 1e-4

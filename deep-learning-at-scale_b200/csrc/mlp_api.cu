@@ -7,7 +7,7 @@ namespace dlas {
 size_t simt_workspace_bytes(const int* dims, int n_layers);
 int simt_grad(const int* dims, int n_layers, int loss, const float* params, const float* X, const float* y,
               size_t n_rows, float* grad_sum, void* workspace, size_t workspace_bytes, cudaStream_t st,
-              const long long* cursor = nullptr);
+              const long long* cursor = nullptr, size_t parity_stride = 0);
 int simt_eval_loss(const int* dims, int n_layers, int loss, const float* params, const float* X, const float* y,
                    size_t n_rows, float* loss_sum, void* workspace, size_t workspace_bytes, cudaStream_t st);
 int simt_predict(const int* dims, int n_layers, const float* params, const float* X, size_t n_rows, float* yhat,
@@ -20,7 +20,7 @@ bool tc_supported(const int* dims, int n_layers);
 size_t tc_workspace_bytes(const int* dims, int n_layers);
 int tc_grad(const int* dims, int n_layers, int loss, const float* params, const float* X, const float* y,
             size_t n_rows, float* grad_sum, void* workspace, size_t workspace_bytes, cudaStream_t st,
-            const long long* cursor = nullptr);
+            const long long* cursor = nullptr, size_t parity_stride = 0);
 int tc_fit_step(const int* dims, int n_layers, int loss, const dlas_opt_cfg* cfg, float* params, float* m, float* v,
                 const float* X, const float* y, size_t n_rows, uint64_t iteration, float* loss_out, void* workspace,
                 size_t workspace_bytes, cudaStream_t st);
@@ -78,8 +78,8 @@ extern "C" int dlas_mlp_grad(const int* dims, int n_layers, int loss, int mode, 
 
 extern "C" int dlas_mlp_grad_at(const int* dims, int n_layers, int loss, int mode, const float* params,
                                 const float* X_base, const float* y_base, size_t batch_rows,
-                                const dlas_step_state* state_dev, float* grad_sum, void* workspace,
-                                size_t workspace_bytes, void* stream) {
+                                const dlas_step_state* state_dev, float* grad_sum, size_t parity_stride,
+                                void* workspace, size_t workspace_bytes, void* stream) {
   DLAS_CHECK_DEVICE();
   int rc = check_common("dlas_mlp_grad_at", dims, n_layers, loss, mode);
   if (rc != DLAS_OK) return rc;
@@ -88,9 +88,9 @@ extern "C" int dlas_mlp_grad_at(const int* dims, int n_layers, int loss, int mod
   const long long* cursor = reinterpret_cast<const long long*>(&state_dev->cursor);
   if (mode == DLAS_MODE_TC)
     return tc_grad(dims, n_layers, loss, params, X_base, y_base, batch_rows, grad_sum, workspace, workspace_bytes,
-                   (cudaStream_t)stream, cursor);
+                   (cudaStream_t)stream, cursor, parity_stride);
   return simt_grad(dims, n_layers, loss, params, X_base, y_base, batch_rows, grad_sum, workspace, workspace_bytes,
-                   (cudaStream_t)stream, cursor);
+                   (cudaStream_t)stream, cursor, parity_stride);
 }
 
 extern "C" int dlas_mlp_fit_steps(const int* dims, int n_layers, int loss, int mode,

@@ -217,12 +217,13 @@ transpose_weights_kernel(const MlpDesc d, const float* __restrict__ params, floa
 // out[i] = sum over active CTAs (in CTA order) of partial[c][i], i in [i0, i0+count)
 __global__ void __launch_bounds__(256)
 reduce_partials_kernel(const float* __restrict__ partials, size_t stride, int n_active, size_t i0,
-                       size_t count, float* __restrict__ out) {
+                       size_t count, float* __restrict__ out, const long long* __restrict__ state = nullptr,
+                       size_t parity_stride = 0) {
   size_t i = (size_t)blockIdx.x * 256 + threadIdx.x;
   if (i >= count) return;
   float s = 0.0f;
   for (int c = 0; c < n_active; ++c) s += partials[(size_t)c * stride + i0 + i];
-  out[i] = s;
+  out[(state && (state[1] & 1)) ? parity_stride + i : i] = s;   // state[1] = iteration: double-buffered bucket
 }
 
 int grid_size() { return sm_count(); }
@@ -253,7 +254,7 @@ size_t simt_workspace_bytes(const int* dims, int n_layers) {
 
 int simt_grad(const int* dims, int n_layers, int loss, const float* params, const float* X, const float* y,
               size_t n_rows, float* grad_sum, void* workspace, size_t workspace_bytes, cudaStream_t st,
-              const long long* cursor) {
+              const long long* cursor, size_t parity_stride) {
   MlpDesc d;
   int rc = make_desc(dims, n_layers, d);
   if (rc != DLAS_OK) return rc;
@@ -278,7 +279,8 @@ int simt_grad(const int* dims, int n_layers, int loss, const float* params, cons
   int n_active = (int)(n_tiles < (size_t)grid_size() ? n_tiles : (size_t)grid_size());
   size_t count = (size_t)d.n_params + 1;
   reduce_partials_kernel<<<(unsigned)((count + 255) / 256), 256, 0, st>>>(partials, partial_stride(d.n_params),
-                                                                        n_active, 0, count, grad_sum);
+                                                                        n_active, 0, count, grad_sum,
+                                                                        parity_stride ? cursor : nullptr, parity_stride);
   DLAS_LAUNCH_CHECK();
   return DLAS_OK;
 }

@@ -550,7 +550,8 @@ template <bool FUSE_OPT>
 __global__ void __launch_bounds__(256)
 tc_reduce_kernel(const float* __restrict__ partials, int n_active_pairs, const unsigned* __restrict__ err_flag,
                  unsigned call_id, float* __restrict__ out, OptScalars opt, float grad_scale, float* __restrict__ params,
-                 float* __restrict__ m, float* __restrict__ v, float* __restrict__ loss_out) {
+                 float* __restrict__ m, float* __restrict__ v, float* __restrict__ loss_out,
+                 const long long* __restrict__ state, size_t parity_stride) {
   // 64 consecutive entries per block; the list of contributing CTAs is cut into 4 contiguous quarters summed by 4
   // thread groups (more loads in flight: the pass is latency-bound), then added in quarter order -> still deterministic
   __shared__ float red[3][64];
@@ -576,7 +577,7 @@ tc_reduce_kernel(const float* __restrict__ partials, int n_active_pairs, const u
   s = ((s + red[0][threadIdx.x]) + red[1][threadIdx.x]) + red[2][threadIdx.x];
   // an mbarrier wait timed out inside this call's tcgen05 kernel: fail loudly, never return numbers
   if (*err_flag == call_id) s = __int_as_float(0x7fc00000);
-  if (out) out[i] = s;
+  if (out) out[(state && (state[1] & 1)) ? parity_stride + i : i] = s;   // state[1] = iteration: double-buffered bucket
   if (FUSE_OPT) {
     if (i == N_PARAMS) {
       if (loss_out) *loss_out = s * grad_scale;
@@ -655,7 +656,8 @@ int launch_main(int loss, const float* params, const float* X, const float* y, s
 
 template <bool FUSE>
 int launch_reduce(cudaStream_t st, const float* partials, int nap, const unsigned* err, float* out, OptScalars o,
-                  float grad_scale, float* params, float* m, float* v, float* loss_out) {
+                  float grad_scale, float* params, float* m, float* v, float* loss_out, const long long* state = nullptr,
+                  size_t parity_stride = 0) {
   cudaLaunchConfig_t cfg = {};
   cfg.gridDim = dim3((N_PARAMS + 1 + 63) / 64);
   cfg.blockDim = dim3(256);
@@ -666,7 +668,7 @@ int launch_reduce(cudaStream_t st, const float* partials, int nap, const unsigne
   cfg.attrs = at;
   cfg.numAttrs = 1;
   DLAS_CUDA(cudaLaunchKernelEx(&cfg, tc_reduce_kernel<FUSE>, partials, nap, err, g_call_id, out, o, grad_scale, params, m, v,
-                               loss_out));
+                               loss_out, state, parity_stride));
   return DLAS_OK;
 }
 
@@ -687,7 +689,7 @@ size_t tc_workspace_bytes(const int* dims, int n_layers) {
 // forward + loss + backward: grad_sum[0..n) gradient sums, grad_sum[n] loss sum
 int tc_grad(const int* dims, int n_layers, int loss, const float* params, const float* X, const float* y,
             size_t n_rows, float* grad_sum, void* workspace, size_t workspace_bytes, cudaStream_t st,
-            const long long* cursor) {
+            const long long* cursor, size_t parity_stride) {
   if (!tc_supported(dims, n_layers)) {
     set_error("DLAS_MODE_TC supports the 32-256-256-1 network only");
     return DLAS_ERR_UNSUPPORTED_SHAPE;
@@ -699,7 +701,8 @@ int tc_grad(const int* dims, int n_layers, int loss, const float* params, const 
   float* partials; unsigned* err; int nap;
   int rc = launch_main(loss, params, X, y, n_rows, workspace, workspace_bytes, st, &partials, &err, &nap, cursor);
   if (rc != DLAS_OK) return rc;
-  rc = launch_reduce<false>(st, partials, nap, err, grad_sum, OptScalars{}, 0.f, nullptr, nullptr, nullptr, nullptr);
+  rc = launch_reduce<false>(st, partials, nap, err, grad_sum, OptScalars{}, 0.f, nullptr, nullptr, nullptr, nullptr,
+                            parity_stride ? cursor : nullptr, parity_stride);
   if (rc != DLAS_OK) return rc;
   return DLAS_OK;
 }

@@ -49,7 +49,8 @@ SIGNATURES = {
     "dlas_mlp_workspace_bytes": (_sz, [_ip, _i, _i]),
     "dlas_mlp_grad": (_i, [_ip, _i, _i, _i, _p, _p, _p, _sz, _p, _p, _sz, _p]),
     "dlas_opt_step": (_i, [C.POINTER(OptCfg), _p, _p, _p, _p, _sz, _f, _u64, _p, _p]),
-    "dlas_mlp_grad_at": (_i, [_ip, _i, _i, _i, _p, _p, _p, _sz, _p, _p, _p, _sz, _p]),
+    "dlas_mlp_grad_at": (_i, [_ip, _i, _i, _i, _p, _p, _p, _sz, _p, _p, _sz, _p, _sz, _p]),
+    "dlas_dp_allreduce_update": (_i, [C.POINTER(OptCfg), _p, _p, _p, _p, _i, _i, _sz, _sz, _sz, _f, _p, _p, C.c_int64, _p]),
     "dlas_opt_step_at": (_i, [C.POINTER(OptCfg), _p, _p, _p, _p, _sz, _f, _p, _p, C.c_int64, _p]),
     "dlas_step_advance": (_i, [_p, C.c_int64, _p]),
     "dlas_mlp_fit_steps": (_i, [_ip, _i, _i, _i, C.POINTER(OptCfg), _p, _p, _p, _p, _p, _sz, _i,

@@ -337,7 +337,7 @@ class Sequential:
                 break
         return history
 
-    def graph_stepper(self, X, Y, local_batch, global_rows=None, ring_len=4096, warmup_steps=3):
+    def graph_stepper(self, X, Y, local_batch, global_rows=None, ring_len=4096, warmup_steps=3, peer=None):
         """Capture ONE whole training step -- gradient kernels on this rank's next `local_batch` rows of the
         resident (X, Y), the all-reduce of the flat bucket, the optimiser update, the cursor advance -- in a
         CUDA graph and return a GraphStepper whose .run(n) replays it n times with no per-step host work.
@@ -352,10 +352,29 @@ class Sequential:
         ring = torch.zeros(ring_len, dtype=torch.float32, device=self.device)
         Y = Y.reshape(-1, dims[-1])
 
+        # peer=True: the all-reduce and the update are ONE kernel of ours over NVLink peer memory
+        # (dlas_dp_allreduce_update); peer=False: NCCL all-reduce between our kernels; None: peer when world > 1
+        # and the ranks' memory can be mapped, else NCCL
+        bucket = None
+        if self.world > 1 and peer is not False:
+            try:
+                bucket = parallel.PeerBucket(self.n_params, self.device)
+            except Exception as e:   # no symmetric-memory support between these GPUs: NCCL path (still no CPU path)
+                if peer:
+                    raise
+                print("dlas: peer-memory bucket unavailable (%s); using the NCCL all-reduce" % (e,))
+        self.dp_path = "peer-kernel" if bucket is not None else ("nccl" if self.world > 1 else "single")
+
         def one_step():
-            ops.mlp_grad_at(dims, self.loss, self.mode, self.params, X, Y, local_batch, state, self.grad_sum, self.workspace)
-            parallel.allreduce_sum_(self.grad_sum)
-            ops.opt_step_at(self.cfg, self.params, self.m, self.v, self.grad_sum, 1.0 / rows, state, ring)
+            if bucket is not None:
+                ops.mlp_grad_at(dims, self.loss, self.mode, self.params, X, Y, local_batch, state, bucket.buf, self.workspace,
+                                parity_stride=bucket.parity_stride)
+                ops.dp_allreduce_update(self.cfg, self.params, self.m, self.v, bucket.bases, self.rank, self.world,
+                                        bucket.parity_stride, bucket.flags_offset, 1.0 / rows, state, ring)
+            else:
+                ops.mlp_grad_at(dims, self.loss, self.mode, self.params, X, Y, local_batch, state, self.grad_sum, self.workspace)
+                parallel.allreduce_sum_(self.grad_sum)
+                ops.opt_step_at(self.cfg, self.params, self.m, self.v, self.grad_sum, 1.0 / rows, state, ring)
             ops.step_advance(state, n_batches)
 
         side = torch.cuda.Stream(device=self.device)
@@ -368,7 +387,9 @@ class Sequential:
         with torch.cuda.graph(graph):
             one_step()
         self.iterations += warmup_steps               # capture records the step, it does not run it
-        return GraphStepper(self, graph, state, ring)
+        st = GraphStepper(self, graph, state, ring)
+        st.bucket = bucket      # keeps the mapped memory alive as long as the graph
+        return st
 
     def fit_host(self, x_host, y_host, batch_size, n_steps, losses_host=None, first_batch=0):
         """Train `n_steps` steps streaming batches from (pinned) HOST tensors: the host->device copy

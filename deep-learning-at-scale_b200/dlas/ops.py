@@ -179,10 +179,18 @@ def lstm_predict(d_in, hidden, n_layers, T, params, X, workspace, out=None):
 
 
 # ---- replayable steps: cursor + iteration counter in device memory (CUDA-graph friendly) --------------
-def mlp_grad_at(dims, loss, mode, params, X_base, y_base, batch_rows, state, grad_sum, workspace):
+def mlp_grad_at(dims, loss, mode, params, X_base, y_base, batch_rows, state, grad_sum, workspace, parity_stride=0):
     check(_lib.load().dlas_mlp_grad_at(int_array(dims), len(dims) - 1, int(loss), int(mode), ptr(params), ptr(X_base),
-                                       ptr(y_base), int(batch_rows), ptr(state), ptr(grad_sum), ptr(workspace),
-                                       workspace.numel(), stream_ptr()))
+                                       ptr(y_base), int(batch_rows), ptr(state), ptr(grad_sum), int(parity_stride),
+                                       ptr(workspace), workspace.numel(), stream_ptr()))
+
+
+def dp_allreduce_update(cfg, params, m, v, peer_bases, rank, world, parity_stride, flags_offset, grad_scale, state,
+                        loss_ring=None):
+    check(_lib.load().dlas_dp_allreduce_update(C.byref(cfg), ptr(params), ptr(m), ptr(v), ptr(peer_bases), int(rank), int(world),
+                                               params.numel(), int(parity_stride), int(flags_offset), float(grad_scale),
+                                               ptr(state), ptr(loss_ring), 0 if loss_ring is None else loss_ring.numel(),
+                                               stream_ptr()))
 
 
 def opt_step_at(cfg, params, m, v, grad_sum, grad_scale, state, loss_ring=None):

@@ -48,3 +48,23 @@ def dp_step(grad_fn, step_fn, bucket, global_rows):
     allreduce_sum_(bucket)
     step_fn(1.0 / float(global_rows))
     return bucket
+
+
+class PeerBucket:
+    """This rank's gradient bucket in memory that every peer GPU of the box can load from (torch symmetric memory:
+    CUDA VMM allocations exchanged between the ranks' processes), laid out as dlas_dp_allreduce_update expects:
+    two parity copies of (n_params gradient sums + loss sum), then `world` arrival flags.  PyTorch only allocates and
+    maps the memory; the reduction over NVLink and the update are dlas_dp_allreduce_update's one kernel."""
+
+    def __init__(self, n_params, device):
+        import torch.distributed._symmetric_memory as symm_mem
+        self.rank, self.world = world_info()
+        self.parity_stride = (n_params + 1 + 63) // 64 * 64
+        self.flags_offset = 2 * self.parity_stride
+        total = self.flags_offset + 64
+        self.buf = symm_mem.empty(total, dtype=torch.float32, device=device)
+        self.handle = symm_mem.rendezvous(self.buf, dist.group.WORLD)
+        self.buf.zero_()                      # flags start at 0; iteration it announces it+1 >= 1
+        torch.cuda.synchronize(device)
+        dist.barrier()                        # nobody announces before everybody has cleared
+        self.bases = torch.tensor([int(p) for p in self.handle.buffer_ptrs], dtype=torch.int64, device=device)

@@ -118,7 +118,9 @@ int dlas_opt_step(const dlas_opt_cfg* cfg, float* params, float* m, float* v, co
  * cursor and the optimiser's iteration counter live in DEVICE memory, so that one step
  *   dlas_mlp_grad_at -> [all-reduce of grad_sum] -> dlas_opt_step_at -> dlas_step_advance
  * can be captured once in a CUDA graph and replayed with no host work per step.
- *   dlas_mlp_grad_at  : dlas_mlp_grad on rows [cursor*batch_rows, (cursor+1)*batch_rows) of X_base / y_base
+ *   dlas_mlp_grad_at  : dlas_mlp_grad on rows [cursor*batch_rows, (cursor+1)*batch_rows) of X_base / y_base; with
+ *                       parity_stride > 0 the sums go to grad_sum + (iteration & 1) * parity_stride (the
+ *                       double-buffered bucket dlas_dp_allreduce_update reads from its peers)
  *   dlas_opt_step_at  : dlas_opt_step with the learning-rate schedule / Adam bias taken from state->iteration;
  *                       the batch-mean loss goes to loss_ring[iteration % ring_len] (may be NULL)
  *   dlas_step_advance : cursor = (cursor + 1) % n_batches; iteration += 1 */
@@ -128,12 +130,31 @@ typedef struct dlas_step_state {
 } dlas_step_state;
 int dlas_mlp_grad_at(const int* dims, int n_layers, int loss, int mode, const float* params,
                      const float* X_base, const float* y_base, size_t batch_rows,
-                     const dlas_step_state* state_dev, float* grad_sum, void* workspace,
-                     size_t workspace_bytes, void* stream);
+                     const dlas_step_state* state_dev, float* grad_sum, size_t parity_stride,
+                     void* workspace, size_t workspace_bytes, void* stream);
 int dlas_opt_step_at(const dlas_opt_cfg* cfg, float* params, float* m, float* v, const float* grad_sum,
                      size_t n, float grad_scale, const dlas_step_state* state_dev, float* loss_ring,
                      int64_t ring_len, void* stream);
 int dlas_step_advance(dlas_step_state* state_dev, int64_t n_batches, void* stream);
+
+/* Gradient all-reduce FUSED with the optimiser update over NVLink peer memory, in one kernel: what BASELINE.json
+ * calls "the Spark driver's gradient/parameter averaging" (the snapshot has no code for it).  Every rank owns a
+ * bucket of the same layout in memory its peers can load from (CUDA IPC / symmetric memory; the caller maps it and
+ * passes the `world` base addresses in device array peer_bases_dev):
+ *     floats [0, n+1)                              gradient sums + loss sum, even iterations
+ *     floats [parity_stride, parity_stride+n+1)    the same, odd iterations (double buffer)
+ *     uint32 [flags_offset, flags_offset+world)    arrival flags, zero-initialised by the caller, one per source rank
+ * The kernel announces "my bucket of iteration it is complete" to every peer (release store of it+1 into
+ * flag[rank] of each peer), waits until all `world` flags of its own bucket have reached it+1, then every rank adds
+ * the `world` buckets in rank order (so all ranks compute bit-identical sums) and applies dlas_opt_step_at's update
+ * with g = sum * grad_scale.  No host work, no NCCL call; replayable in a CUDA graph.  The stream order must be
+ * dlas_mlp_grad_at(..., grad_sum = own bucket, parity_stride) -> this call -> dlas_step_advance.  A rank that does
+ * not see its peers within a bounded spin writes NaN into the loss ring instead of hanging. */
+int dlas_dp_allreduce_update(const dlas_opt_cfg* cfg, float* params, float* m, float* v,
+                             const uint64_t* peer_bases_dev, int rank, int world, size_t n,
+                             size_t parity_stride, size_t flags_offset, float grad_scale,
+                             const dlas_step_state* state_dev, float* loss_ring, int64_t ring_len,
+                             void* stream);
 
 /* n_steps consecutive single-GPU mini-batch steps (the `model.fit` inner loop, cnn.py:127-128):
  * step s uses rows [b*batch, (b+1)*batch) with b = batch_order_host ? batch_order_host[s]

@@ -16,6 +16,9 @@ from dlas import parallel  # noqa: E402
 import dlas_oracle as O  # noqa: E402
 
 mode = sys.argv[1] if len(sys.argv) > 1 else "fp32"
+path = "eager"          # eager: train_on_batch + NCCL; graph: replayed step + NCCL; peer: replayed step + our NVLink kernel
+if "-" in mode:
+    mode, path = mode.split("-")
 rank, local, world = int(os.environ["RANK"]), int(os.environ["LOCAL_RANK"]), int(os.environ["WORLD_SIZE"])
 torch.cuda.set_device(local)
 dist.init_process_group("nccl", device_id=torch.device("cuda", local))
@@ -29,10 +32,17 @@ model.compile(loss="mse", optimizer=dlas.SGD(lr=0.001, momentum=0.99, decay=1e-6
 model.set_weights_flat(p0)
 Xl, yl = torch.from_numpy(X[mine]).cuda(), torch.from_numpy(y[mine]).cuda().reshape(-1, 1)
 lb = batch // world
-losses = []
-for s in range(steps):
-    losses.append(model.train_on_batch(Xl[s * lb:(s + 1) * lb], yl[s * lb:(s + 1) * lb], global_rows=batch))
-got = torch.cat(losses).cpu().numpy()
+if path == "eager":
+    losses = []
+    for s in range(steps):
+        losses.append(model.train_on_batch(Xl[s * lb:(s + 1) * lb], yl[s * lb:(s + 1) * lb], global_rows=batch))
+    got = torch.cat(losses).cpu().numpy()
+else:
+    st = model.graph_stepper(Xl, yl, lb, global_rows=batch, warmup_steps=3, peer=(path == "peer"))
+    st.run(steps - 3)
+    torch.cuda.synchronize()
+    got = st.recent_losses(steps)
+    assert model.dp_path == ("peer-kernel" if path == "peer" else "nccl"), model.dp_path
 w = model.get_weights_flat()
 # every rank must hold identical weights after the all-reduced steps
 chk = torch.tensor([float(np.abs(w).sum())], device="cuda", dtype=torch.float64)
@@ -48,8 +58,10 @@ if rank == 0:
     same = float(hi.item() - lo.item())
     tol_l = 1e-4 if mode == "fp32" else 3e-4
     ok = lerr < tol_l and werr < 1e-4 and same == 0.0
-    print("dp_check world=%d mode=%s: max loss rel err %.3g, weights rel err %.3g, rank spread %.3g -> %s"
-          % (world, mode, lerr, werr, same, "OK" if ok else "FAIL"), flush=True)
-dist.barrier()
-dist.destroy_process_group()
-sys.exit(0 if ok else 1)
+    print("dp_check world=%d mode=%s path=%s: max loss rel err %.3g, weights rel err %.3g, rank spread %.3g -> %s"
+          % (world, mode, path, lerr, werr, same, "OK" if ok else "FAIL"), flush=True)
+flag = torch.tensor([0 if ok else 1], device="cuda")
+dist.broadcast(flag, 0)
+torch.cuda.synchronize()
+sys.stdout.flush()
+os._exit(int(flag.item()))     # captured collectives keep communicator resources alive: skip the collective teardown

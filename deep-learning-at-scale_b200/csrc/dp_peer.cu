@@ -31,11 +31,11 @@ __device__ __forceinline__ unsigned ld_acquire_sys(const unsigned* p) {
 }
 __device__ __forceinline__ float4 ld_peer4(const float* p) {   // never served from a stale L1 line
   float4 v;
-  asm volatile("ld.relaxed.sys.global.v4.f32 {%0,%1,%2,%3}, [%4];" : "=f"(v.x), "=f"(v.y), "=f"(v.z), "=f"(v.w) : "l"(p) : "memory");
+  asm volatile("ld.relaxed.sys.global.v4.f32 {%0,%1,%2,%3}, [%4];" : "=f"(v.x), "=f"(v.y), "=f"(v.z), "=f"(v.w) : "l"(p));
   return v;
 }
 
-constexpr int MAXW = 16;
+constexpr int MAXW = 8;     // one NVSwitch box
 
 __global__ void __launch_bounds__(256)
 dp_allreduce_update_kernel(const dlas_opt_cfg cfg, float* __restrict__ p, float* __restrict__ m, float* __restrict__ v,
@@ -79,10 +79,15 @@ dp_allreduce_update_kernel(const dlas_opt_cfg cfg, float* __restrict__ p, float*
   const size_t off = (it & 1) ? parity_stride : 0;
   const size_t i0 = ((size_t)blockIdx.x * 256 + threadIdx.x) * 4;
   if (i0 > n) return;                      // element n is the loss sum
+  // all peer loads first (each is a ~2 us NVLink round trip: they must be in flight together), then the adds
+  float4 q[MAXW];
+#pragma unroll
+  for (int r = 0; r < MAXW; ++r)
+    q[r] = (r < world) ? ld_peer4(reinterpret_cast<const float*>(bases[r]) + off + i0) : make_float4(0.f, 0.f, 0.f, 0.f);
   float4 s = make_float4(0.f, 0.f, 0.f, 0.f);
-  for (int r = 0; r < world; ++r) {        // rank order: bit-identical on every rank
-    const float4 q = ld_peer4(reinterpret_cast<const float*>(bases[r]) + off + i0);
-    s.x += q.x; s.y += q.y; s.z += q.z; s.w += q.w;
+#pragma unroll
+  for (int r = 0; r < MAXW; ++r) {         // rank order: bit-identical on every rank (absent ranks add +0)
+    s.x += q[r].x; s.y += q[r].y; s.z += q[r].z; s.w += q[r].w;
   }
   const float sv[4] = {s.x, s.y, s.z, s.w};
 #pragma unroll

@@ -56,7 +56,7 @@ constexpr uint32_t S_W1 = 0, S_W2 = S_W1 + K1 * 4 * 128, S_X = S_W2 + 65536, S_H
 constexpr int F_B2 = 0, F_W3 = 128, F_Y = 256 /*[2][128]*/, F_PART = 512 /*[2][128]*/, F_RP = 768 /*[2][128]*/,
               F_RED = 1024 /*[4][128]*/, F_END = 1536;
 constexpr uint32_t S_BAR = S_F32 + F_END * 4;
-enum { B_DONE0 = 0, B_DONE1, B_FREE0, B_FREE1, B_X0, B_X1, B_H1, B_DZ2, B_DZ1, B_ALL, N_BARS };
+enum { B_DONE0 = 0, B_DONE1, B_FREE0, B_FREE1, B_X0, B_X1, B_H1, B_DZ2, B_DZ1, B_DW1, B_ALL, B_XC0, B_XC1, N_BARS };
 constexpr uint32_t S_TMEM = S_BAR + N_BARS * 8;
 constexpr uint32_t SMEM_BYTES = S_TMEM + 16;
 
@@ -123,7 +123,8 @@ mlp_tc_kernel(const int loss_kind, const float* __restrict__ params, const float
     mbar_init(&bars[B_FREE0], N_EPI / 32); mbar_init(&bars[B_FREE1], N_EPI / 32);
     mbar_init(&bars[B_X0], N_EPI / 32); mbar_init(&bars[B_X1], N_EPI / 32);
     mbar_init(&bars[B_H1], N_EPI / 32); mbar_init(&bars[B_DZ2], N_EPI / 32); mbar_init(&bars[B_DZ1], N_EPI / 32);
-    mbar_init(&bars[B_ALL], 1);
+    mbar_init(&bars[B_ALL], 1); mbar_init(&bars[B_DW1], 1);
+    mbar_init(&bars[B_XC0], 1); mbar_init(&bars[B_XC1], 1);   // exchange of the partial output dots: 1 arrival + 512 tx bytes
     mbar_fence_init();
   }
   if (warp == 8) tmem_alloc(tmem_slot, TM_COLS);
@@ -190,6 +191,7 @@ mlp_tc_kernel(const int loss_kind, const float* __restrict__ params, const float
     // The whole warp runs the control flow (so descriptor arithmetic stays warp-uniform); one elected
     // lane issues.  Descriptors are a constant base plus a compile-time offset per K step.
     constexpr uint32_t ID_KM_MN_64 = make_idesc(128, 64, false, true);
+    constexpr uint32_t ID_KM_MN_128 = make_idesc(128, 128, false, true);
     constexpr uint32_t ID_KM_KM_64 = make_idesc(128, 64, false, false);
     constexpr uint32_t ID_MN_MN_128 = make_idesc(128, 128, true, true);
     constexpr uint32_t ID_MN_MN_48 = make_idesc(128, 48, true, true);
@@ -203,45 +205,49 @@ mlp_tc_kernel(const int loss_kind, const float* __restrict__ params, const float
     const uint64_t dDZ2_km = desc_kmajor(sDZ2, TILE, 0, 0), dDZ2_mn = desc_mnmajor(sDZ2, TILE, 0, 0);
     const uint64_t dONES = desc_kmajor(sONES, 16, 0, 0);
     uint32_t n = 0;  // running index of chunk GEMMs; buffer = n & 1
+    // Z1 + b1 = [X | 1 | 0] [W1 ; b1 ; 0] in four N=64 chunks, K = 48.  Chunks 0,1 of tile t+1 are issued at the END
+    // of tile t, before dW1(t), so that they are already in TMEM when the epilogue warps come back for them.
+    auto issue_z1 = [&](int xb, int s) {
+      const uint32_t b = n & 1;
+      ok = mbar_wait(&bars[B_FREE0 + b], ((n >> 1) & 1) ^ 1) && ok;
+      fence_after();
+      if (leader) {
+#pragma unroll
+        for (int i = 0; i < K1 / 16; ++i)
+          mma_f16(tm + TM_W0 + b * 64, dX_km[xb] + koff_kmajor(TILE, i), dW1_mn + mnoff(K1, 64) * s + koff_mnmajor(i), ID_KM_MN_64, i > 0);
+        mma_commit(&bars[B_DONE0 + b]);
+      }
+      __syncwarp();
+      ++n;
+    };
+    if (my_tiles > 0) {
+      ok = mbar_wait(&bars[B_X0], 0) && ok;
+      issue_z1(0, 0);
+      issue_z1(0, 1);
+    }
     for (int it = 0; it < my_tiles; ++it) {
       const int xb = it & 1;
       const bool first = (it == 0);
       TRACE_M(10);
-      ok = mbar_wait(&bars[B_X0 + xb], (it >> 1) & 1) && ok;
-      TRACE_M(11);
-      // Z1 + b1 = [X | 1 | 0] [W1 ; b1 ; 0]: four N=64 chunks, K = 48
-#pragma unroll
-      for (int s = 0; s < 4; ++s, ++n) {
-        const uint32_t b = n & 1;
-        ok = mbar_wait(&bars[B_FREE0 + b], ((n >> 1) & 1) ^ 1) && ok;
-        fence_after();
-        if (leader) {
-#pragma unroll
-          for (int i = 0; i < K1 / 16; ++i)
-            mma_f16(tm + TM_W0 + b * 64, dX_km[xb] + koff_kmajor(TILE, i), dW1_mn + mnoff(K1, s * 64) + koff_mnmajor(i), ID_KM_MN_64, i > 0);
-          mma_commit(&bars[B_DONE0 + b]);
-        }
-        __syncwarp();
-      }
-      // Z2h = H1 W2h: two N=64 chunks
+      issue_z1(xb, 2);
+      issue_z1(xb, 3);
+      // Z2h = H1 W2h: ONE N=128 MMA chain over both work buffers (smem operand traffic: 128 KB instead of 192 KB)
       TRACE_M(12);
       ok = mbar_wait(&bars[B_H1], it & 1) && ok;
       TRACE_M(13);
+      ok = mbar_wait(&bars[B_FREE0 + (n & 1)], ((n >> 1) & 1) ^ 1) && ok;
+      ok = mbar_wait(&bars[B_FREE0 + ((n + 1) & 1)], (((n + 1) >> 1) & 1) ^ 1) && ok;
+      fence_after();
+      if (leader) {
 #pragma unroll
-      for (int s = 0; s < 2; ++s, ++n) {
-        const uint32_t b = n & 1;
-        ok = mbar_wait(&bars[B_FREE0 + b], ((n >> 1) & 1) ^ 1) && ok;
-        fence_after();
-        if (leader) {
-#pragma unroll
-          for (int i = 0; i < D1 / 16; ++i)
-            mma_f16(tm + TM_W0 + b * 64, dH1_km + koff_kmajor(TILE, i), dW2_mn + mnoff(D1, s * 64) + koff_mnmajor(i), ID_KM_MN_64, i > 0);
-          mma_commit(&bars[B_DONE0 + b]);
-        }
-        __syncwarp();
+        for (int i = 0; i < D1 / 16; ++i)
+          mma_f16(tm + TM_W0, dH1_km + koff_kmajor(TILE, i), dW2_mn + koff_mnmajor(i), ID_KM_MN_128, i > 0);
+        mma_commit(&bars[B_DONE0]);
+        mma_commit(&bars[B_DONE1]);
       }
+      __syncwarp();
+      n += 2;
       TRACE_M(14);
-      cluster_sync_all();   // pairs with the epilogue warps' exchange of the partial output dots
       TRACE_M(15);
       ok = mbar_wait(&bars[B_DZ2], it & 1) && ok;
       TRACE_M(16);
@@ -275,6 +281,12 @@ mlp_tc_kernel(const int loss_kind, const float* __restrict__ params, const float
         }
         __syncwarp();
       }
+      // next tile's Z1 chunks 0,1 (their buffers are free as soon as the last two dH1p chunks have been read)
+      if (it + 1 < my_tiles) {
+        ok = mbar_wait(&bars[B_X0 + (xb ^ 1)], ((it + 1) >> 1) & 1) && ok;
+        issue_z1(xb ^ 1, 0);
+        issue_z1(xb ^ 1, 1);
+      }
       // dW1p^T += dZ1p^T [X | 1]
       TRACE_M(17);
       ok = mbar_wait(&bars[B_DZ1], it & 1) && ok;
@@ -287,6 +299,7 @@ mlp_tc_kernel(const int loss_kind, const float* __restrict__ params, const float
           for (int i = 0; i < TILE / 16; ++i)
             mma_f16(tm + TM_DW1 + mh * 64, dH1_mn + mnoff(TILE, mh * 128) + koff_mnmajor(i), dX_mn[xb] + koff_mnmajor(i), ID_MN_MN_48,
                     !(first && i == 0));
+        mma_commit(&bars[B_DW1]);   // sH1 (dZ1) and sX[xb] are free once this arrives
       }
       __syncwarp();
     }
@@ -298,6 +311,7 @@ mlp_tc_kernel(const int loss_kind, const float* __restrict__ params, const float
     const int row = q * 32 + lane;                      // TMEM lane = tile row
     const uint32_t lane_base = (uint32_t)(q * 32) << 16;
     const uint32_t peer_part = map_to_cta(sF + F_PART * 4, rank ^ 1u);
+    const uint32_t peer_xc = map_to_cta(smem_u32(&bars[B_XC0]), rank ^ 1u);
     float acc_w3[2] = {0.f, 0.f};
     float acc_loss = 0.f, acc_b3 = 0.f;
     uint32_t n = 0;
@@ -345,6 +359,7 @@ mlp_tc_kernel(const int loss_kind, const float* __restrict__ params, const float
         fence_before();
         warp_arrive(lane, &bars[B_FREE0 + b]);
         TRACE_E(43);
+        if (s == 0 && it > 0) ok = mbar_wait(&bars[B_DW1], (it - 1) & 1) && ok;   // dW1 of the previous tile still reads sH1
         const int c0 = s * 64 + hh * 32;
 #pragma unroll
         for (int g8 = 0; g8 < 4; ++g8) {   // relu on packed halves: one F2FP + one HMNMX2 per two elements
@@ -388,9 +403,12 @@ mlp_tc_kernel(const int loss_kind, const float* __restrict__ params, const float
       f32[F_RP + hh * 128 + row] = part;
       named_bar_sync(1, N_EPI);
       const float mine = f32[F_RP + row] + f32[F_RP + 128 + row];
-      if (hh == 0) st_cluster_f32(peer_part + (uint32_t)(buf * 128 + row) * 4, mine);
+      // exchange with the peer CTA: each of the 128 rows is stored straight into the peer's shared memory with an
+      // asynchronous store that completes 4 transaction bytes on the PEER's mbarrier; nobody else has to synchronise
+      if (tid == 0) mbar_arrive_expect_tx(&bars[B_XC0 + buf], 512);
+      if (hh == 0) st_async_f32(peer_part + (uint32_t)(buf * 128 + row) * 4, mine, peer_xc + (uint32_t)buf * 8);
       TRACE_E(24);
-      cluster_sync_all();
+      ok = mbar_wait(&bars[B_XC0 + buf], (it >> 1) & 1) && ok;
       TRACE_E(25);
       const float other = f32[F_PART + buf * 128 + row];
       const float yhat = (rank == 0 ? mine + other : other + mine) + b3;   // same value on both CTAs

@@ -167,6 +167,14 @@ __device__ __forceinline__ uint32_t map_to_cta(uint32_t saddr, uint32_t rank) {
   asm volatile("mapa.shared::cluster.u32 %0, %1, %2;" : "=r"(r) : "r"(saddr), "r"(rank));
   return r;
 }
+__device__ __forceinline__ void mbar_arrive_expect_tx(uint64_t* bar, uint32_t bytes) {
+  asm volatile("mbarrier.arrive.expect_tx.shared::cta.b64 _, [%0], %1;" ::"r"(smem_u32(bar)), "r"(bytes) : "memory");
+}
+// asynchronous 4-byte store into a peer CTA's shared memory; completes 4 transaction bytes on the peer's mbarrier
+__device__ __forceinline__ void st_async_f32(uint32_t caddr, float v, uint32_t cbar) {
+  asm volatile("st.async.weak.shared::cluster.mbarrier::complete_tx::bytes.b32 [%0], %1, [%2];" ::"r"(caddr), "r"(__float_as_uint(v)), "r"(cbar)
+               : "memory");
+}
 __device__ __forceinline__ void st_cluster_f32(uint32_t caddr, float v) {
   asm volatile("st.shared::cluster.f32 [%0], %1;" ::"r"(caddr), "f"(v) : "memory");
 }

@@ -147,6 +147,7 @@ def main():
     ap.add_argument("--gilbert-rows", type=int, default=200_000_000)
     ap.add_argument("--gilbert-variant", type=int, default=-1)
     ap.add_argument("--no-cpu-baseline", action="store_true")
+    ap.add_argument("--no-extras", action="store_true", help="skip the dynamic-ANN / 8-64-64-1 / LSTM side measurements")
     args = ap.parse_args()
     rank = int(os.environ.get("RANK", "0"))
     local_rank = int(os.environ.get("LOCAL_RANK", "0"))
@@ -287,6 +288,44 @@ def main():
     best = max(gil, key=lambda k: gil[k]["rows_per_s"])
     del P, S, R, q
 
+    # ---- the other model families of SURVEY.md 8d, N=1 only, a few steps each (reported beside the headline, not the metric)
+    extras = {}
+    if N == 1 and not args.no_extras:
+        def timed(fn, n):
+            for _ in range(2):
+                fn()
+            torch.cuda.synchronize()
+            e0.record()
+            for _ in range(n):
+                fn()
+            e1.record()
+            torch.cuda.synchronize()
+            return e0.elapsed_time(e1) * 1e-3 / n
+        # dynamic ANN (config 4): 24 lags x 8 features -> 192-256-256-1, fp32 kernel, 65,536 windows per step
+        dd = [192, 256, 256, 1]
+        series, ys = ops.synth_rows(65536 + 23, 8)
+        Wd = ops.lag_windows(series, 24)
+        mdl = dlas.Sequential([dlas.Dense(192, 256, activation="relu"), dlas.Dense(256, 256, activation="relu"), dlas.Dense(256, 1)])
+        mdl.compile(loss="mse", optimizer=dlas.SGD(lr=0.001, momentum=0.99, decay=1e-6, nesterov=True))
+        yd = ys[23:].contiguous()
+        t = timed(lambda: mdl.train_on_batch(Wd, yd), 5)
+        extras["dynamic_ann_192_256_256_1"] = {"samples_per_s": 65536 / t, "mode": "fp32", "rows_per_step": 65536,
+                                               "frac_of_bf16_sustained_peak": 591360 * 65536 / t / 1e12 / pk["tf_sust"]}
+        # static ANN 8-64-64-1 (config 1 shape), fp32 kernel
+        X8, y8 = ops.synth_rows(65536, 8)
+        m8 = dlas.Sequential([dlas.Dense(8, 64, activation="relu"), dlas.Dense(64, 64, activation="relu"), dlas.Dense(64, 1)])
+        m8.compile(loss="mse", optimizer=dlas.SGD(lr=0.001, momentum=0.99, decay=1e-6, nesterov=True))
+        t = timed(lambda: m8.train_on_batch(X8, y8), 10)
+        extras["static_ann_8_64_64_1"] = {"samples_per_s": 65536 / t, "mode": "fp32", "rows_per_step": 65536}
+        # LSTM 2x128, T=48, batch 4096 (config 5)
+        Xs, ysq = ops.synth_series(4096, 48, 8)
+        ml = dlas.Sequential([dlas.LSTM(128, input_shape=(48, 8), return_sequences=True), dlas.LSTM(128), dlas.Dense(1)])
+        ml.compile(loss="mse", optimizer=dlas.SGD(lr=0.001, momentum=0.99, decay=1e-6, nesterov=True))
+        t = timed(lambda: ml.train_on_batch(Xs, ysq), 3)
+        extras["lstm_2x128_T48_batch4096"] = {"sequences_per_s": 4096 / t, "ms_per_step": t * 1e3, "mode": "fp32",
+                                              "frac_of_bf16_sustained_peak": 57.41e6 * 4096 / t / 1e12 / pk["tf_sust"]}
+        del series, ys, Wd, yd, X8, y8, Xs, ysq
+
     if rank == 0:
         kern_s = kern_ms / max(1, kern_n) * 1e-3
         tfs = TRAIN_FLOP_PER_SAMPLE * B / kern_s / 1e12
@@ -308,12 +347,13 @@ def main():
             "e2e": {"value": e2e_value, "unit": "samples/s", "h2d_bytes_per_step": B * BYTES_PER_SAMPLE, "d2h_bytes_per_step": 4},
             "gpu_launches": launches_per_step * K,
             "clocks": clk.summary(),
+            "other_models": extras,
             "gilbert": {"metric": "gilbert_rows_per_s", "rows": g_rows * N, "variant": int(best), **gil[best], "all_variants": gil},
         }
         if N == 1 and not args.no_cpu_baseline:
             rate1, _, _ = cpu_port_rate(8192, 2, warmup=1)
             rows = int(min(65536, max(4096, (rate1 * 1.0) // 4096 * 4096)))
-            n_steps = int(max(3, min(40, 15.0 * rate1 / rows)))
+            n_steps = int(max(3, min(2000, 15.0 * rate1 / rows)))      # ~15 s of CPU work
             rate, dt, thr = cpu_port_rate(rows, n_steps, warmup=1)
             line["cpu_baseline"] = {"value": rate, "unit": "samples/s", "cores": thr, "kind": "port",
                                     "sample": "%d steps of %d rows (%.1f s) of the same 32-256-256-1 step, torch-CPU fp32 port; "

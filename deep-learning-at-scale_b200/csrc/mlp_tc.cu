@@ -43,7 +43,10 @@ using namespace tc;
 
 constexpr int D0 = 32, D1 = 256, D2 = 256;
 constexpr int TILE = 128;
-constexpr int N_EPI = 256;            // epilogue threads (warps 0-7)
+constexpr int CSPLIT = 2;             // epilogue warps per TMEM lane quarter (4 measured no faster: the epilogues are latency- and smem-bound): each takes 64/CSPLIT columns of a chunk
+constexpr int CW = 64 / CSPLIT;
+constexpr int N_EPI = 128 * CSPLIT;   // epilogue threads (warps 0 .. 4*CSPLIT-1)
+constexpr int ISSUER_WARP = N_EPI / 32;
 constexpr int NT = N_EPI + 32;        // + MMA issuer warp
 constexpr int W1_OFF = 0, B1_OFF = W1_OFF + D0 * D1, W2_OFF = B1_OFF + D1, B2_OFF = W2_OFF + D1 * D2,
               W3_OFF = B2_OFF + D2, B3_OFF = W3_OFF + D2, N_PARAMS = B3_OFF + 1;
@@ -53,8 +56,8 @@ constexpr int K1 = 48;                // layer-1 contraction: 32 features + the 
 constexpr uint32_t S_W1 = 0, S_W2 = S_W1 + K1 * 4 * 128, S_X = S_W2 + 65536, S_H1 = S_X + 2 * 16384, S_DZ2 = S_H1 + 65536,
                    S_ONES = S_DZ2 + 32768, S_F32 = S_ONES + 2048;
 // fp32 area (float index)
-constexpr int F_B2 = 0, F_W3 = 128, F_Y = 256 /*[2][128]*/, F_PART = 512 /*[2][128]*/, F_RP = 768 /*[2][128]*/,
-              F_RED = 1024 /*[4][128]*/, F_END = 1536;
+constexpr int F_B2 = 0, F_W3 = 128, F_Y = 256 /*[2][128]*/, F_PART = 512 /*[2][128]*/, F_RP = 768 /*[CSPLIT][128]*/,
+              F_RED = F_RP + CSPLIT * 128 /*[4][128]*/, F_END = F_RED + 512;
 constexpr uint32_t S_BAR = S_F32 + F_END * 4;
 enum { B_DONE0 = 0, B_DONE1, B_FREE0, B_FREE1, B_X0, B_X1, B_H1, B_DZ2, B_DZ1, B_DW1, B_ALL, B_XC0, B_XC1, N_BARS };
 constexpr uint32_t S_TMEM = S_BAR + N_BARS * 8;
@@ -62,10 +65,11 @@ constexpr uint32_t SMEM_BYTES = S_TMEM + 16;
 
 constexpr uint32_t TM_W0 = 0, TM_DW2 = 128, TM_DW1 = 384, TM_DB2 = 496, TM_COLS = 512;
 
-// out: lane l holds the sum over the warp's 32 lanes of v[l]
-__device__ __forceinline__ float warp_colsum32(float (&v)[32], int lane) {
+// v[0..W) per lane -> lane l (< W) returns the sum over the warp's 32 lanes of v[l]  (W = 32 or 16)
+template <int W>
+__device__ __forceinline__ float warp_colsum(float (&v)[W], int lane) {
 #pragma unroll
-  for (int s = 16; s >= 1; s >>= 1) {
+  for (int s = W / 2; s >= 1; s >>= 1) {
     const bool hi = (lane & s) != 0;
 #pragma unroll
     for (int i = 0; i < s; ++i) {
@@ -74,8 +78,14 @@ __device__ __forceinline__ float warp_colsum32(float (&v)[32], int lane) {
       v[i] = keep + __shfl_xor_sync(0xffffffffu, send, s);
     }
   }
-  return v[0];
+  float r = v[0];
+  if (W == 16) r += __shfl_xor_sync(0xffffffffu, r, 16);   // lanes l and l+16 hold the two halves of column l % 16
+  return r;
 }
+
+template <int W> __device__ __forceinline__ void tmem_ld(uint32_t taddr, uint32_t (&v)[W]);
+template <> __device__ __forceinline__ void tmem_ld<32>(uint32_t taddr, uint32_t (&v)[32]) { tmem_ld32(taddr, v); }
+template <> __device__ __forceinline__ void tmem_ld<16>(uint32_t taddr, uint32_t (&v)[16]) { tmem_ld16(taddr, v); }
 
 // every lane has done its own fences; one arrival for the warp
 __device__ __forceinline__ void warp_arrive(int lane, uint64_t* bar) {
@@ -127,7 +137,7 @@ mlp_tc_kernel(const int loss_kind, const float* __restrict__ params, const float
     mbar_init(&bars[B_XC0], 1); mbar_init(&bars[B_XC1], 1);   // exchange of the partial output dots: 1 arrival + 512 tx bytes
     mbar_fence_init();
   }
-  if (warp == 8) tmem_alloc(tmem_slot, TM_COLS);
+  if (warp == ISSUER_WARP) tmem_alloc(tmem_slot, TM_COLS);
   // Programmatic dependent launch: everything above overlaps the tail of the previous kernel in the stream
   // (the optimiser update that produced `params`); from here on its writes are visible.
   asm volatile("griddepcontrol.wait;" ::: "memory");
@@ -186,7 +196,7 @@ mlp_tc_kernel(const int loss_kind, const float* __restrict__ params, const float
   asm volatile("griddepcontrol.launch_dependents;" ::: "memory");
   const int my_tiles = (n_tiles > (size_t)pair) ? (int)((n_tiles - pair + n_pairs - 1) / n_pairs) : 0;
 
-  if (warp == 8) {
+  if (warp == ISSUER_WARP) {
     // =========================== MMA issuer ===========================
     // The whole warp runs the control flow (so descriptor arithmetic stays warp-uniform); one elected
     // lane issues.  Descriptors are a constant base plus a compile-time offset per K step.
@@ -307,6 +317,7 @@ mlp_tc_kernel(const int loss_kind, const float* __restrict__ params, const float
     __syncwarp();
   } else {
     // =========================== epilogue warps ===========================
+    // warp w: TMEM lane quarter q = w % 4 (rows 32q..32q+31), column slice hh = w / 4 of every 64-column chunk
     const int q = warp & 3, hh = warp >> 2;
     const int row = q * 32 + lane;                      // TMEM lane = tile row
     const uint32_t lane_base = (uint32_t)(q * 32) << 16;
@@ -315,21 +326,23 @@ mlp_tc_kernel(const int loss_kind, const float* __restrict__ params, const float
     float acc_w3[2] = {0.f, 0.f};
     float acc_loss = 0.f, acc_b3 = 0.f;
     uint32_t n = 0;
-    // X tile loader: thread -> (row tid>>1, 16 features (tid&1)*16..)
-    const int xr = tid >> 1, xh = tid & 1;
-    float4 xv[4];
+    // X tile loader: thread -> (row tid / XT, XF features), XT threads per row
+    constexpr int XT = N_EPI / TILE, XF = D0 / XT;      // 4 threads per row, 8 features each
+    const int xr = tid / XT, xh = tid % XT;
+    float4 xv[XF / 4];
     float yv = 0.f;
     auto x_issue = [&](size_t tile) {
       const size_t row0 = tile * TILE;
       const bool in = row0 + xr < n_rows;
-      const float* src = X + (row0 + xr) * (size_t)D0 + xh * 16;
+      const float* src = X + (row0 + xr) * (size_t)D0 + xh * XF;
 #pragma unroll
-      for (int i = 0; i < 4; ++i) xv[i] = in ? __ldcs(reinterpret_cast<const float4*>(src + i * 4)) : make_float4(0.f, 0.f, 0.f, 0.f);
+      for (int i = 0; i < XF / 4; ++i) xv[i] = in ? __ldcs(reinterpret_cast<const float4*>(src + i * 4)) : make_float4(0.f, 0.f, 0.f, 0.f);
       if (tid < TILE) yv = (row0 + tid < n_rows) ? __ldcs(y + row0 + tid) : 0.f;
     };
     auto x_store = [&](int j) {
-      sts128(sX + j * 16384 + tile_chunk_off(TILE, xr, xh * 16), pack8(xv[0], xv[1]));
-      sts128(sX + j * 16384 + tile_chunk_off(TILE, xr, xh * 16 + 8), pack8(xv[2], xv[3]));
+#pragma unroll
+      for (int i = 0; i < XF / 8; ++i)
+        sts128(sX + j * 16384 + tile_chunk_off(TILE, xr, xh * XF + i * 8), pack8(xv[2 * i], xv[2 * i + 1]));
       if (tid < TILE) f32[F_Y + j * 128 + tid] = yv;
       fence_async_smem();
       warp_arrive(lane, &bars[B_X0 + j]);
@@ -352,17 +365,17 @@ mlp_tc_kernel(const int loss_kind, const float* __restrict__ params, const float
         ok = mbar_wait(&bars[B_DONE0 + b], (n >> 1) & 1) && ok;
         TRACE_E(41);
         fence_after();
-        uint32_t v[32];
-        tmem_ld32(tm + TM_W0 + b * 64 + lane_base + hh * 32, v);
+        uint32_t v[CW];
+        tmem_ld<CW>(tm + TM_W0 + b * 64 + lane_base + hh * CW, v);
         tmem_ld_wait();
         TRACE_E(42);
         fence_before();
         warp_arrive(lane, &bars[B_FREE0 + b]);
         TRACE_E(43);
         if (s == 0 && it > 0) ok = mbar_wait(&bars[B_DW1], (it - 1) & 1) && ok;   // dW1 of the previous tile still reads sH1
-        const int c0 = s * 64 + hh * 32;
+        const int c0 = s * 64 + hh * CW;
 #pragma unroll
-        for (int g8 = 0; g8 < 4; ++g8) {   // relu on packed halves: one F2FP + one HMNMX2 per two elements
+        for (int g8 = 0; g8 < CW / 8; ++g8) {   // relu on packed halves: one F2FP + one HMNMX2 per two elements
           uint4 o;
           o.x = relu_h2(pack_half2(__uint_as_float(v[g8 * 8 + 0]), __uint_as_float(v[g8 * 8 + 1])));
           o.y = relu_h2(pack_half2(__uint_as_float(v[g8 * 8 + 2]), __uint_as_float(v[g8 * 8 + 3])));
@@ -385,12 +398,12 @@ mlp_tc_kernel(const int loss_kind, const float* __restrict__ params, const float
         const uint32_t b = (n_c + s) & 1;
         ok = mbar_wait(&bars[B_DONE0 + b], ((n_c + s) >> 1) & 1) && ok;
         fence_after();
-        uint32_t v[32];
-        tmem_ld32(tm + TM_W0 + b * 64 + lane_base + hh * 32, v);
+        uint32_t v[CW];
+        tmem_ld<CW>(tm + TM_W0 + b * 64 + lane_base + hh * CW, v);
         tmem_ld_wait();
-        const int c0 = s * 64 + hh * 32;
+        const int c0 = s * 64 + hh * CW;
 #pragma unroll
-        for (int g4 = 0; g4 < 8; ++g4) {
+        for (int g4 = 0; g4 < CW / 4; ++g4) {
           const float4 bv = lds128f(sF + (F_B2 + c0 + g4 * 4) * 4), wv = lds128f(sF + (F_W3 + c0 + g4 * 4) * 4);
           part = fmaf(fmaxf(__uint_as_float(v[g4 * 4 + 0]) + bv.x, 0.f), wv.x, part);
           part = fmaf(fmaxf(__uint_as_float(v[g4 * 4 + 1]) + bv.y, 0.f), wv.y, part);
@@ -402,7 +415,9 @@ mlp_tc_kernel(const int loss_kind, const float* __restrict__ params, const float
       const int buf = it & 1;
       f32[F_RP + hh * 128 + row] = part;
       named_bar_sync(1, N_EPI);
-      const float mine = f32[F_RP + row] + f32[F_RP + 128 + row];
+      float mine = 0.f;
+#pragma unroll
+      for (int h = 0; h < CSPLIT; ++h) mine += f32[F_RP + h * 128 + row];     // fixed order: same value in every warp
       // exchange with the peer CTA: each of the 128 rows is stored straight into the peer's shared memory with an
       // asynchronous store that completes 4 transaction bytes on the PEER's mbarrier; nobody else has to synchronise
       if (tid == 0) mbar_arrive_expect_tx(&bars[B_XC0 + buf], 512);
@@ -430,15 +445,15 @@ mlp_tc_kernel(const int loss_kind, const float* __restrict__ params, const float
 #pragma unroll
       for (int s = 0; s < 2; ++s) {
         const uint32_t b = (n_c + s) & 1;
-        const int c0 = s * 64 + hh * 32;
-        uint32_t v[32];
-        tmem_ld32(tm + TM_W0 + b * 64 + lane_base + hh * 32, v);
+        const int c0 = s * 64 + hh * CW;
+        uint32_t v[CW];
+        tmem_ld<CW>(tm + TM_W0 + b * 64 + lane_base + hh * CW, v);
         tmem_ld_wait();
         fence_before();
         warp_arrive(lane, &bars[B_FREE0 + b]);
-        float hg[32];
+        float hg[CW];
 #pragma unroll
-        for (int g8 = 0; g8 < 4; ++g8) {
+        for (int g8 = 0; g8 < CW / 8; ++g8) {
           const float4 wa = lds128f(sF + (F_W3 + c0 + g8 * 8) * 4), wb = lds128f(sF + (F_W3 + c0 + g8 * 8 + 4) * 4);
           const float4 ba = lds128f(sF + (F_B2 + c0 + g8 * 8) * 4), bb = lds128f(sF + (F_B2 + c0 + g8 * 8 + 4) * 4);
           const float w8[8] = {wa.x, wa.y, wa.z, wa.w, wb.x, wb.y, wb.z, wb.w};
@@ -454,7 +469,7 @@ mlp_tc_kernel(const int loss_kind, const float* __restrict__ params, const float
           }
           sts128(sDZ2 + tile_chunk_off(TILE, row, c0 + g8 * 8), make_uint4(o[0], o[1], o[2], o[3]));
         }
-        acc_w3[s] += warp_colsum32(hg, lane);
+        acc_w3[s] += warp_colsum<CW>(hg, lane);
       }
       fence_async_smem();
       warp_arrive(lane, &bars[B_DZ2]);
@@ -467,15 +482,15 @@ mlp_tc_kernel(const int loss_kind, const float* __restrict__ params, const float
         ok = mbar_wait(&bars[B_DONE0 + b], (n >> 1) & 1) && ok;
         TRACE_E(51);
         fence_after();
-        uint32_t v[32];
-        tmem_ld32(tm + TM_W0 + b * 64 + lane_base + hh * 32, v);
+        uint32_t v[CW];
+        tmem_ld<CW>(tm + TM_W0 + b * 64 + lane_base + hh * CW, v);
         tmem_ld_wait();
         fence_before();
         warp_arrive(lane, &bars[B_FREE0 + b]);
         TRACE_E(52);
-        const int c0 = s * 64 + hh * 32;
+        const int c0 = s * 64 + hh * CW;
 #pragma unroll
-        for (int g8 = 0; g8 < 4; ++g8) {
+        for (int g8 = 0; g8 < CW / 8; ++g8) {
           const uint32_t a = sH1 + tile_chunk_off(TILE, row, c0 + g8 * 8);
           const uint4 h = lds128(a);
           uint32_t o[4];   // dZ1 = (H1 > 0) * dH1p on packed halves
@@ -498,13 +513,14 @@ mlp_tc_kernel(const int loss_kind, const float* __restrict__ params, const float
       ok = mbar_wait(&bars[B_ALL], 0) && ok;
       fence_after();
       TRACE_E(31);
+      constexpr int DC = 128 / CSPLIT;                    // dW2 columns per thread and M half
 #pragma unroll 1
       for (int mh = 0; mh < 2; ++mh) {
-        float* dst = my + W2_OFF + (size_t)(mh * 128 + row) * D2 + rank * 128 + hh * 64;   // row in = mh*128+row
+        float* dst = my + W2_OFF + (size_t)(mh * 128 + row) * D2 + rank * 128 + hh * DC;   // row in = mh*128+row
 #pragma unroll 1
-        for (int c0 = 0; c0 < 64; c0 += 32) {
+        for (int c0 = 0; c0 < DC; c0 += 32) {
           uint32_t v[32];
-          tmem_ld32(tm + TM_DW2 + mh * 128 + lane_base + hh * 64 + c0, v);
+          tmem_ld32(tm + TM_DW2 + mh * 128 + lane_base + hh * DC + c0, v);
           tmem_ld_wait();
 #pragma unroll
           for (int i = 0; i < 8; ++i)
@@ -519,22 +535,24 @@ mlp_tc_kernel(const int loss_kind, const float* __restrict__ params, const float
           tmem_ld_wait();
 #pragma unroll
           for (int i = 0; i < 32; ++i) my[W1_OFF + i * D1 + h1] = __uint_as_float(v[i]);
-        } else {
+        } else if (hh == 1) {
           uint32_t w[16];
           tmem_ld16(tm + TM_DW1 + mh * 64 + lane_base + 32, w);
           tmem_ld_wait();
           my[B1_OFF + h1] = __uint_as_float(w[0]);
         }
       }
-      if (hh == 0) {  // db2h: lane = out column, every accumulator column holds the same sum
+      if (hh == CSPLIT - 1) {  // db2h: lane = out column, every accumulator column holds the same sum
         uint32_t w[16];
         tmem_ld16(tm + TM_DB2 + lane_base, w);
         tmem_ld_wait();
         my[B2_OFF + rank * 128 + row] = __uint_as_float(w[0]);
       }
-      // dw3h: per-warp column sums -> add the four row quarters in order
-      f32[F_RED + q * 128 + hh * 32 + lane] = acc_w3[0];
-      f32[F_RED + q * 128 + 64 + hh * 32 + lane] = acc_w3[1];
+      // dw3h: per-warp column sums (lanes 0..CW-1 hold them) -> add the four row quarters in order
+      if (lane < CW) {
+        f32[F_RED + q * 128 + hh * CW + lane] = acc_w3[0];
+        f32[F_RED + q * 128 + 64 + hh * CW + lane] = acc_w3[1];
+      }
       named_bar_sync(1, N_EPI);
       if (tid < 128)
         my[W3_OFF + rank * 128 + tid] = (f32[F_RED + tid] + f32[F_RED + 128 + tid]) + (f32[F_RED + 256 + tid] + f32[F_RED + 384 + tid]);
@@ -556,7 +574,7 @@ mlp_tc_kernel(const int loss_kind, const float* __restrict__ params, const float
   fence_before();
   __syncthreads();
   cluster_sync_all();   // do not exit while the peer may still write our exchange buffer
-  if (warp == 8) tmem_dealloc(tm, TM_COLS);
+  if (warp == ISSUER_WARP) tmem_dealloc(tm, TM_COLS);
 }
 
 // grad_sum[i] = sum of the partials of the CTAs that own entry i, in CTA order:
@@ -564,15 +582,16 @@ mlp_tc_kernel(const int loss_kind, const float* __restrict__ params, const float
 //   b3 and the loss sum: rank-0 CTAs.
 // With FUSE_OPT the optimiser update of entry i is applied in the same pass (single-GPU step: no
 // all-reduce sits between the gradient and the update), and the batch-mean loss goes to *loss_out.
+constexpr int RG = 4;   // thread groups per block of 64 entries (8 measured no faster)
 template <bool FUSE_OPT>
-__global__ void __launch_bounds__(256)
+__global__ void __launch_bounds__(64 * RG)
 tc_reduce_kernel(const float* __restrict__ partials, int n_active_pairs, const unsigned* __restrict__ err_flag,
                  unsigned call_id, float* __restrict__ out, OptScalars opt, float grad_scale, float* __restrict__ params,
                  float* __restrict__ m, float* __restrict__ v, float* __restrict__ loss_out,
                  const long long* __restrict__ state, size_t parity_stride) {
-  // 64 consecutive entries per block; the list of contributing CTAs is cut into 4 contiguous quarters summed by 4
+  // 64 consecutive entries per block; the list of contributing CTAs is cut into RG contiguous parts summed by RG
   // thread groups (more loads in flight: the pass is latency-bound), then added in quarter order -> still deterministic
-  __shared__ float red[3][64];
+  __shared__ float red[RG - 1][64];
   asm volatile("griddepcontrol.launch_dependents;" ::: "memory");   // next gradient kernel: set-up may overlap this pass
   asm volatile("griddepcontrol.wait;" ::: "memory");   // the gradient kernel has completed; its partials are visible
   const int i = blockIdx.x * 64 + (threadIdx.x & 63), grp = threadIdx.x >> 6;
@@ -583,7 +602,7 @@ tc_reduce_kernel(const float* __restrict__ partials, int n_active_pairs, const u
   else if (i >= W3_OFF && i < B3_OFF) { first = (i - W3_OFF) / 128; step = 2; }
   else if (i >= B3_OFF) { first = 0; step = 2; }
   const int n_src = (2 * n_active_pairs - first + step - 1) / step;        // contributing CTAs
-  const int per = (n_src + 3) / 4, k0 = grp * per, k1 = min(n_src, k0 + per);
+  const int per = (n_src + RG - 1) / RG, k0 = grp * per, k1 = min(n_src, k0 + per);
   float s = 0.f;
   if (live) {
 #pragma unroll 8
@@ -592,7 +611,8 @@ tc_reduce_kernel(const float* __restrict__ partials, int n_active_pairs, const u
   if (grp > 0) red[grp - 1][threadIdx.x & 63] = s;
   __syncthreads();
   if (grp > 0 || !live) return;
-  s = ((s + red[0][threadIdx.x]) + red[1][threadIdx.x]) + red[2][threadIdx.x];
+#pragma unroll
+  for (int g2 = 0; g2 < RG - 1; ++g2) s += red[g2][threadIdx.x];
   // an mbarrier wait timed out inside this call's tcgen05 kernel: fail loudly, never return numbers
   if (*err_flag == call_id) s = __int_as_float(0x7fc00000);
   if (out) out[(state && (state[1] & 1)) ? parity_stride + i : i] = s;   // state[1] = iteration: double-buffered bucket
@@ -678,7 +698,7 @@ int launch_reduce(cudaStream_t st, const float* partials, int nap, const unsigne
                   size_t parity_stride = 0) {
   cudaLaunchConfig_t cfg = {};
   cfg.gridDim = dim3((N_PARAMS + 1 + 63) / 64);
-  cfg.blockDim = dim3(256);
+  cfg.blockDim = dim3(64 * RG);
   cfg.stream = st;
   cudaLaunchAttribute at[1];
   at[0].id = cudaLaunchAttributeProgrammaticStreamSerialization;

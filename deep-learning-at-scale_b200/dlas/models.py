@@ -181,7 +181,13 @@ class Sequential:
             setattr(self, name, getattr(self._impl, name))
         return self
 
-    def compile(self, loss="mse", optimizer=None):
+    def compile(self, loss="mse", optimizer=None, averaging="gradient", average_every=1):
+        """averaging="gradient" (default): synchronous mean-gradient averaging every step, the parity semantics of
+        SURVEY.md 8e.  averaging="parameter": Spark-driver-style periodic parameter averaging -- `average_every`
+        local steps per rank between averages of parameters and optimiser state."""
+        if averaging not in ("gradient", "parameter"):
+            raise ValueError("averaging must be 'gradient' or 'parameter'")
+        self.average_every = int(average_every) if averaging == "parameter" else 0
         if not self.layers:
             raise ValueError("add layers before compile")
         if loss not in _LOSSES:
@@ -261,8 +267,18 @@ class Sequential:
 
     def train_on_batch(self, X, y, global_rows=None):
         """One optimiser step on this rank's shard (X, y) of one global batch; returns the device
-        scalar holding the global batch-mean loss."""
+        scalar holding the global batch-mean loss (the LOCAL shard's mean loss in parameter-averaging mode)."""
         dims = self.dims
+        if getattr(self, "average_every", 0) > 0 and self.world > 1:
+            # periodic PARAMETER averaging (optional mode): local step on the local mean gradient, no per-step collective;
+            # every `average_every` steps parameters and optimiser state are replaced by their mean over ranks
+            loss_out = torch.empty(1, dtype=torch.float32, device=self.device)
+            ops.mlp_grad(dims, self.loss, self.mode, self.params, X, y, self.grad_sum, self.workspace)
+            ops.opt_step(self.cfg, self.params, self.m, self.v, self.grad_sum, 1.0 / X.shape[0], self.iterations, loss_out)
+            self.iterations += 1
+            if self.iterations % self.average_every == 0:
+                parallel.average_([self.params, self.m, self.v])
+            return loss_out
         rows = global_rows if global_rows is not None else X.shape[0] * self.world
         loss_out = torch.empty(1, dtype=torch.float32, device=self.device)
         parallel.dp_step(

@@ -68,3 +68,17 @@ class PeerBucket:
         torch.cuda.synchronize(device)
         dist.barrier()                        # nobody announces before everybody has cleared
         self.bases = torch.tensor([int(p) for p in self.handle.buffer_ptrs], dtype=torch.int64, device=device)
+
+
+def average_(tensors):
+    """In-place MEAN over ranks of each tensor (periodic parameter averaging).  NCCL averages inside the collective;
+    gloo (CPU tests) has no AVG, so there the sum is divided on the host."""
+    _, world = world_info()
+    if world <= 1:
+        return
+    for t in tensors:
+        if dist.get_backend() == "nccl":
+            dist.all_reduce(t, op=dist.ReduceOp.AVG)
+        else:
+            dist.all_reduce(t, op=dist.ReduceOp.SUM)
+            t /= world

@@ -490,3 +490,32 @@ def early_stopping_trace(val_losses, patience=10):
             if wait >= patience:
                 return ep, best_ep
     return None, best_ep
+
+
+# --------------------------------------------------------------------------------------
+# Periodic PARAMETER averaging (BASELINE.json "gradient/parameter averaging"): what a Spark
+# driver does between partitions -- every replica runs `every` local steps on its own slice of each global
+# batch (mean over its LOCAL rows), then parameters AND optimiser state are replaced by their mean over replicas.
+# The snapshot has no averaging code; this pins the optional mode.  With every=1 and plain
+# SGD (no momentum) it coincides with the default synchronous gradient averaging.
+# --------------------------------------------------------------------------------------
+def mlp_fit_steps_param_avg(params, dims, X, y, batch, n_steps, loss, cfg, world, every):
+    reps = [params.copy() for _ in range(world)]
+    sts = [opt_state(params.size, params.dtype) for _ in range(world)]
+    shard = batch // world
+    losses = []
+    for s in range(n_steps):
+        Xb, yb = X[s * batch:(s + 1) * batch], y[s * batch:(s + 1) * batch]
+        lsum = 0.0
+        for r in range(world):
+            l_r, g_r = mlp_loss_grad_sums(reps[r], dims, Xb[r * shard:(r + 1) * shard], yb[r * shard:(r + 1) * shard], loss)
+            lsum += l_r
+            opt_step(reps[r], g_r / params.dtype.type(shard), cfg, sts[r])
+        losses.append(lsum / batch)
+        if (s + 1) % every == 0:
+            for arrs in ([reps[r] for r in range(world)], [sts[r]["m"] for r in range(world)], [sts[r]["v"] for r in range(world)]):
+                mean = sum(arrs) / world
+                for a in arrs:
+                    a[...] = mean
+    params[...] = sum(reps) / world
+    return np.asarray(losses)

@@ -121,3 +121,23 @@ def test_dp_step_gloo_world2_equals_single_process(golden_dir, tmp_path):
     r, g = np.load(out), np.load(golden)
     np.testing.assert_allclose(r["losses"], g["losses_w1"], rtol=1e-12)
     np.testing.assert_allclose(r["final"], g["final_w1"], rtol=1e-9, atol=1e-13)
+
+
+def _avg_worker(rank, world, port, out):
+    os.environ.update(MASTER_ADDR="127.0.0.1", MASTER_PORT=str(port))
+    dist.init_process_group("gloo", rank=rank, world_size=world)
+    a = torch.full((5,), float(rank + 1), dtype=torch.float64)
+    b = torch.arange(3, dtype=torch.float64) * (rank + 1)
+    parallel.average_([a, b])
+    if rank == 0:
+        np.savez(out, a=a.numpy(), b=b.numpy())
+    dist.barrier()
+    dist.destroy_process_group()
+
+
+def test_parameter_average_gloo_world2(tmp_path):
+    out = str(tmp_path / "avg.npz")
+    mp.spawn(_avg_worker, args=(2, _free_port(), out), nprocs=2, join=True)
+    r = np.load(out)
+    np.testing.assert_allclose(r["a"], 1.5)
+    np.testing.assert_allclose(r["b"], np.arange(3) * 1.5)

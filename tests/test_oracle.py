@@ -260,3 +260,21 @@ def test_torch_cpu_port_matches_oracle(golden_dir):
     P, S, R = O.synth_gilbert(O.BASE_SEED, 0, 10000)
     q = T.gilbert_numpy_f32(P, S, R, threads=3)
     assert np.abs(q / O.gilbert(P, S, R) - 1).max() < 1e-6
+
+
+def test_parameter_averaging_reduces_to_gradient_averaging_for_plain_sgd():
+    """every=1, no momentum: averaging parameters after one local step == one step on the mean gradient."""
+    dims, batch, steps = [5, 7, 1], 32, 5
+    rng = np.random.default_rng(4)
+    p0 = rng.normal(size=O.mlp_n_params(dims)) * 0.3
+    X, y = rng.normal(size=(batch * steps, 5)), rng.normal(size=(batch * steps, 1))
+    cfg = O.sgd_config(lr=0.05, momentum=0.0, decay=0.0, nesterov=False)
+    a = p0.copy()
+    la = O.mlp_fit_steps_param_avg(a, dims, X, y, batch, steps, O.LOSS_MSE, cfg, world=4, every=1)
+    b = p0.copy()
+    lb = O.mlp_fit_steps(b, dims, X, y, batch, steps, O.LOSS_MSE, cfg, O.opt_state(b.size))
+    np.testing.assert_allclose(a, b, rtol=1e-10, atol=1e-13)
+    np.testing.assert_allclose(la, lb, rtol=1e-10)
+    c = p0.copy()
+    O.mlp_fit_steps_param_avg(c, dims, X, y, batch, steps, O.LOSS_MSE, cfg, world=4, every=3)   # local SGD drifts
+    assert np.abs(c - b).max() > 1e-6

@@ -28,11 +28,13 @@ X, y = O.synth_rows(O.BASE_SEED, 0, batch * steps, 32)
 p0 = O.glorot_init(dims, O.BASE_SEED)
 mine = parallel.local_rows(X.shape[0], batch, rank, world).numpy()
 model = dlas.Sequential([dlas.Dense(32, 256, activation="relu"), dlas.Dense(256, 256, activation="relu"), dlas.Dense(256, 1)], mode=mode)
-model.compile(loss="mse", optimizer=dlas.SGD(lr=0.001, momentum=0.99, decay=1e-6, nesterov=True))
+every = int(path[4:]) if path.startswith("pavg") else 0      # e.g. fp32-pavg3: parameter averaging every 3 steps
+model.compile(loss="mse", optimizer=dlas.SGD(lr=0.001, momentum=0.99, decay=1e-6, nesterov=True),
+              averaging="parameter" if every else "gradient", average_every=max(1, every))
 model.set_weights_flat(p0)
 Xl, yl = torch.from_numpy(X[mine]).cuda(), torch.from_numpy(y[mine]).cuda().reshape(-1, 1)
 lb = batch // world
-if path == "eager":
+if path == "eager" or every:
     losses = []
     for s in range(steps):
         losses.append(model.train_on_batch(Xl[s * lb:(s + 1) * lb], yl[s * lb:(s + 1) * lb], global_rows=batch))
@@ -43,6 +45,8 @@ else:
     torch.cuda.synchronize()
     got = st.recent_losses(steps)
     assert model.dp_path == ("peer-kernel" if path == "peer" else "nccl"), model.dp_path
+if every:
+    parallel.average_([model.params])          # the oracle reports the replica mean after the last step
 w = model.get_weights_flat()
 # every rank must hold identical weights after the all-reduced steps
 chk = torch.tensor([float(np.abs(w).sum())], device="cuda", dtype=torch.float64)
@@ -52,7 +56,12 @@ dist.all_reduce(hi, op=dist.ReduceOp.MAX)
 ok = True
 if rank == 0:
     pr = p0.astype(np.float64)
-    ref = O.mlp_fit_steps(pr, dims, X.astype(np.float64), y.astype(np.float64), batch, steps, O.LOSS_MSE, O.sgd_config(), O.opt_state(pr.size))
+    if every:   # per-step loss here is the rank-0 shard's local mean; compare weights (after a final average) only
+        ref = O.mlp_fit_steps_param_avg(pr, dims, X.astype(np.float64), y.astype(np.float64), batch, steps, O.LOSS_MSE,
+                                        O.sgd_config(), world, every)
+        got = ref
+    else:
+        ref = O.mlp_fit_steps(pr, dims, X.astype(np.float64), y.astype(np.float64), batch, steps, O.LOSS_MSE, O.sgd_config(), O.opt_state(pr.size))
     lerr = float(np.abs(got / ref - 1).max())
     werr = float(np.linalg.norm(w - pr) / np.linalg.norm(pr))
     same = float(hi.item() - lo.item())

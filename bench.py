@@ -64,7 +64,7 @@ class ClockSampler:
                         self.reasons.add(k)
             except Exception:
                 pass
-            self._stop.wait(0.02)
+            self._stop.wait(0.004)
 
     def __enter__(self):
         if self.nv:
@@ -284,7 +284,8 @@ def main():
         gbs = g_rows * GILBERT_BYTES_PER_ROW / (gk_ms / gk_n * 1e-3) / 1e9
         gil[str(var)] = {"rows_per_s": rows_s, "kernel_ms": gk_ms / gk_n,
                          "roofline": {"bound": "hbm", "achieved": gbs, "peak": pk["hbm"], "unit": "GB/s",
-                                      "frac": gbs / pk["hbm"], "traffic": None}}
+                                      "frac": gbs / pk["hbm"],
+                                      "traffic": (3.179e9 * g_rows / 200_000_000)}}   # ncu: 2.400 GB read + 0.779 GB written per 200M rows (profiles/)
     best = max(gil, key=lambda k: gil[k]["rows_per_s"])
     del P, S, R, q
 
@@ -341,7 +342,8 @@ def main():
                        "rows_resident_per_gpu": rows_rank, "l2": "inputs (%.1f GB per GPU) larger than L2; every step reads new rows"
                        % (rows_rank * BYTES_PER_SAMPLE / 1e9), "parallelism": "dp%d" % N, "final_loss": final_loss},
             "roofline": {"bound": "tensor", "achieved": tfs, "peak": pk["tf_sust"], "unit": "TFLOP/s", "frac": tfs / pk["tf_sust"],
-                         "traffic": None, "kernel": "mlp forward+loss+backward", "kernel_ms": kern_s * 1e3,
+                         "traffic": (10.56e6 if (mode == "tc" and B == 65536) else None),   # ncu dram read+write per launch, profiles/r01_ncu_full_tc_final.txt
+                         "kernel": "mlp forward+loss+backward", "kernel_ms": kern_s * 1e3,
                          "kernel_share_of_step": (kern_ms / max(1, kern_n)) / (ms / K), "peak_source": pk["src"] + ", bf16 sustained",
                          "hbm_frac": BYTES_PER_SAMPLE * B / kern_s / 1e9 / pk["hbm"]},
             "e2e": {"value": e2e_value, "unit": "samples/s", "h2d_bytes_per_step": B * BYTES_PER_SAMPLE, "d2h_bytes_per_step": 4},

@@ -519,3 +519,72 @@ def mlp_fit_steps_param_avg(params, dims, X, y, batch, n_steps, loss, cfg, world
                     a[...] = mean
     params[...] = sum(reps) / world
     return np.asarray(losses)
+
+
+# --------------------------------------------------------------------------------------
+# The CNN that is actually in the snapshot (cnn.py:110-114):
+#   Convolution1D(1, 100, 13, activation="relu") -> Dropout(0.5) -> Flatten -> Dense(3600, 12)
+# on (48, 1) inputs, valid border.  Flat layout: Wc[K][F] (tap-major), bc[F], Wd[T*F][n_out], bd[n_out],
+# T = L - K + 1; Flatten is time-major (index t*F + f), as Keras flattens (steps, filters).
+# Pinned where Keras-0.x/Theano cannot be consulted: cross-correlation tap order (Theano's conv2d flips the
+# filter -- a relabelling of learned weights); inverted dropout (x * mask / keep at train time, identity at
+# test time); the mask is the counter hash of (seed, sample id, unit) so CUDA and oracle draw the same one.
+# --------------------------------------------------------------------------------------
+STREAM_DROPOUT = 300
+
+
+def cnn_offsets(L, K, F, n_out):
+    T = L - K + 1
+    wc, bc = 0, K * F
+    wd = bc + F
+    bd = wd + T * F * n_out
+    return (wc, bc, wd, bd), bd + n_out
+
+
+def cnn_init(L, K, F, n_out, seed, dtype=np.float32):
+    (wc, bc, wd, bd), n = cnn_offsets(L, K, F, n_out)
+    T = L - K + 1
+    p = np.zeros(n, dtype=np.float64)
+    lim = np.sqrt(6.0 / (K + K * F))
+    p[wc:wc + K * F] = (2.0 * hash_uniform(seed, 400, np.arange(K * F, dtype=np.uint64)).astype(np.float64) - 1.0) * lim
+    lim = np.sqrt(6.0 / (T * F + n_out))
+    p[wd:wd + T * F * n_out] = (2.0 * hash_uniform(seed, 401, np.arange(T * F * n_out, dtype=np.uint64)).astype(np.float64) - 1.0) * lim
+    return p.astype(dtype)
+
+
+def dropout_mask(seed, sample0, n_rows, n_units, keep=0.5):
+    """mask[r][j] = 1 if the 24-bit hash of (sample0 + r) * n_units + j is below keep * 2^24."""
+    idx = (np.uint64(sample0) + np.arange(n_rows, dtype=np.uint64))[:, None] * np.uint64(n_units) + np.arange(n_units, dtype=np.uint64)[None, :]
+    return (hash_u24(seed, STREAM_DROPOUT, idx) < np.uint32(keep * (1 << 24))).astype(np.float64)
+
+
+def cnn_forward(params, L, K, F, n_out, X, mask=None, keep=0.5):
+    (wc, bc, wd, bd), _ = cnn_offsets(L, K, F, n_out)
+    T = L - K + 1
+    Wc = params[wc:wc + K * F].reshape(K, F)
+    win = np.stack([X[:, k:k + T] for k in range(K)], axis=2)          # (B, T, K)
+    conv = win @ Wc + params[bc:bc + F]                                 # (B, T, F)
+    a = np.maximum(conv, 0.0).reshape(X.shape[0], T * F)
+    if mask is not None:
+        a = a * mask / keep
+    out = a @ params[wd:wd + T * F * n_out].reshape(T * F, n_out) + params[bd:bd + n_out]
+    return out, a, win
+
+
+def cnn_loss_grad_sums(params, L, K, F, n_out, X, y, loss, mask=None, keep=0.5):
+    dt = params.dtype
+    (wc, bc, wd, bd), n = cnn_offsets(L, K, F, n_out)
+    T = L - K + 1
+    out, a, win = cnn_forward(params, L, K, F, n_out, X.astype(dt), mask, keep)
+    per, g = loss_and_grad(out, np.asarray(y, dtype=dt).reshape(X.shape[0], n_out), loss)
+    grads = np.zeros(n, dtype=dt)
+    Wd = params[wd:wd + T * F * n_out].reshape(T * F, n_out)
+    grads[wd:wd + T * F * n_out] = (a.T @ g).reshape(-1)
+    grads[bd:bd + n_out] = g.sum(axis=0)
+    da = g @ Wd.T
+    if mask is not None:
+        da = da * mask / keep
+    dconv = (da * (a > 0 if mask is None else (cnn_forward(params, L, K, F, n_out, X.astype(dt))[1] > 0))).reshape(-1, T, F)
+    grads[wc:wc + K * F] = np.einsum("btk,btf->kf", win, dconv).reshape(-1)
+    grads[bc:bc + F] = dconv.sum(axis=(0, 1))
+    return per.sum(), grads

@@ -278,3 +278,26 @@ def test_parameter_averaging_reduces_to_gradient_averaging_for_plain_sgd():
     c = p0.copy()
     O.mlp_fit_steps_param_avg(c, dims, X, y, batch, steps, O.LOSS_MSE, cfg, world=4, every=3)   # local SGD drifts
     assert np.abs(c - b).max() > 1e-6
+
+
+def test_cnn_backward_vs_autograd_and_shapes():
+    """cnn.py:110-114: Conv1D(1->100, k=13, relu) -> Dropout(0.5) -> Flatten -> Dense(3600 -> 12) on (48, 1)."""
+    L, K, F, n_out, B = 48, 13, 100, 12, 5
+    (wc, bc, wd, bd), n = O.cnn_offsets(L, K, F, n_out)
+    assert n == 44612 and (L - K + 1) * F == 3600          # SURVEY.md 2.2: 1,400 + 43,212 parameters, Dense(3600, 12)
+    rng = np.random.default_rng(8)
+    p = rng.normal(size=n) * 0.1
+    X, y = rng.normal(size=(B, L)), rng.normal(size=(B, n_out)) * 4
+    mask = O.dropout_mask(O.BASE_SEED, 77, B, 3600)
+    assert 0.45 < mask.mean() < 0.55
+    for loss in (O.LOSS_MSE, O.LOSS_MAE_CLIP):
+        ls, g = O.cnn_loss_grad_sums(p, L, K, F, n_out, X, y, loss, mask)
+        pt = torch.tensor(p, requires_grad=True)
+        conv = torch.nn.functional.conv1d(torch.tensor(X)[:, None, :], pt[wc:wc + K * F].reshape(K, F).T[:, None, :], pt[bc:bc + F])
+        a = torch.relu(conv).permute(0, 2, 1).reshape(B, 3600) * torch.tensor(mask) / 0.5      # (B, T, F) time-major flatten
+        out = a @ pt[wd:wd + 3600 * n_out].reshape(3600, n_out) + pt[bd:bd + n_out]
+        d = out - torch.tensor(y)
+        per = (d * d).mean(dim=1) if loss == O.LOSS_MSE else torch.clamp(d.abs(), 0, 6).mean(dim=1)
+        per.sum().backward()
+        assert ls == pytest.approx(per.sum().item(), rel=1e-12)
+        np.testing.assert_allclose(g, pt.grad.numpy(), rtol=1e-9, atol=1e-12)

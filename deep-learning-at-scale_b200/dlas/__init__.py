@@ -6,6 +6,8 @@ from ._lib import (DlasError, GILBERT_MUFU, GILBERT_POLY, LOSS_MAE_CLIP, LOSS_MS
 from .models import SGD, Adam, Dense, EarlyStopping, ModelCheckpoint, Sequential, mae_clip
 from .ops import gilbert
 from .recurrent import LSTM, LSTMRegressor
+from .convolutional import CnnRegressor, Convolution1D, Dropout, Flatten
 
 __all__ = ["Sequential", "Dense", "SGD", "Adam", "EarlyStopping", "ModelCheckpoint", "mae_clip", "gilbert", "LSTM", "LSTMRegressor",
+           "Convolution1D", "Dropout", "Flatten", "CnnRegressor",
            "load", "DlasError"]

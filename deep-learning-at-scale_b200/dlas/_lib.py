@@ -62,6 +62,10 @@ SIGNATURES = {
     "dlas_lstm_workspace_bytes": (_sz, [_i, _i, _i, _i, _sz]),
     "dlas_lstm_grad": (_i, [_i, _i, _i, _i, _i, _p, _p, _p, _sz, _p, _p, _sz, _p]),
     "dlas_lstm_predict": (_i, [_i, _i, _i, _i, _p, _p, _sz, _p, _p, _sz, _p]),
+    "dlas_cnn_n_params": (_sz, [_i, _i, _i, _i]),
+    "dlas_cnn_workspace_bytes": (_sz, [_i, _i, _i, _i, _sz]),
+    "dlas_cnn_grad": (_i, [_i, _i, _i, _i, _i, _p, _p, _p, _sz, _f, _u64, _u64, _p, _p, _sz, _p]),
+    "dlas_cnn_predict": (_i, [_i, _i, _i, _i, _p, _p, _sz, _p, _p, _sz, _p]),
 }
 
 _lib = None

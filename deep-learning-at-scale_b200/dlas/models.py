@@ -143,13 +143,17 @@ class Sequential:
     # -- build (cnn.py:110-114)
     def add(self, layer):
         from .recurrent import LSTM
+        from .convolutional import Convolution1D, Dropout, Flatten
         if isinstance(layer, LSTM) or any(isinstance(l, LSTM) for l in self.layers):
             if isinstance(layer, Dense) and layer.input_dim is None:
                 layer.input_dim = self.layers[-1].units
             self.layers.append(layer)
             return
+        if isinstance(layer, (Convolution1D, Dropout, Flatten)) or any(isinstance(l, Convolution1D) for l in self.layers):
+            self.layers.append(layer)       # the stack of cnn.py:110-114, checked in compile
+            return
         if not isinstance(layer, Dense):
-            raise NotImplementedError("only Dense and LSTM layers are on the B200 hot path")
+            raise NotImplementedError("Dense, LSTM and the Convolution1D/Dropout/Flatten stack of cnn.py are on the B200 hot path")
         if layer.input_dim is None:
             if not self.layers:
                 raise ValueError("first layer needs input_dim")
@@ -172,14 +176,39 @@ class Sequential:
         if rec[0].input_shape is None or len({l.units for l in rec}) != 1:
             raise NotImplementedError("first LSTM needs input_shape=(T, d_in); all LSTM layers share one width")
         T, d_in = rec[0].input_shape
-        self._impl = LSTMRegressor(d_in, rec[0].units, len(rec), T, seed=self.seed, device=self.device)
+        return self._delegate(LSTMRegressor(d_in, rec[0].units, len(rec), T, seed=self.seed, device=self.device), loss, optimizer)
+
+    def _delegate(self, impl, loss, optimizer):
+        self._impl = impl
         if self.params is not None:
-            self._impl.params = self.params
-        self._impl.compile(loss, optimizer if optimizer is not None else SGD())
+            impl.params = self.params
+        impl.compile(loss, optimizer if optimizer is not None else SGD())
         for name in ("fit", "predict", "evaluate", "test_on_batch", "train_on_batch", "set_weights_flat",
                      "get_weights_flat", "save_weights"):
-            setattr(self, name, getattr(self._impl, name))
+            setattr(self, name, getattr(impl, name))
         return self
+
+    def _compile_cnn(self, loss, optimizer):
+        from .convolutional import CnnRegressor, Convolution1D, Dropout, Flatten
+        kinds = [type(l) for l in self.layers]
+        if kinds not in ([Convolution1D, Dropout, Flatten, Dense], [Convolution1D, Flatten, Dense]):
+            raise NotImplementedError("supported stack: Convolution1D -> [Dropout] -> Flatten -> Dense (cnn.py:110-114)")
+        conv, dense = self.layers[0], self.layers[-1]
+        if dense.activation != "linear":
+            raise NotImplementedError("the output layer is linear on this path (cnn.py:114)")
+        L = conv.input_length
+        if dense.input_dim is not None:      # Dense(3600, 12): T*F fixes the series length
+            if dense.input_dim % conv.nb_filter:
+                raise ValueError("Dense input_dim %d is not a multiple of nb_filter %d" % (dense.input_dim, conv.nb_filter))
+            L_dense = dense.input_dim // conv.nb_filter + conv.filter_length - 1
+            if L is not None and L != L_dense:
+                raise ValueError("input_length %d disagrees with Dense input_dim %d" % (L, dense.input_dim))
+            L = L_dense
+        if L is None:
+            raise ValueError("give Convolution1D(input_length=...) or Dense(input_dim, output_dim)")
+        drop = self.layers[1].p if len(self.layers) == 4 else 0.0
+        return self._delegate(CnnRegressor(L, conv.filter_length, conv.nb_filter, dense.output_dim, drop, seed=self.seed,
+                                           device=self.device), loss, optimizer)
 
     def compile(self, loss="mse", optimizer=None, averaging="gradient", average_every=1):
         """averaging="gradient" (default): synchronous mean-gradient averaging every step, the parity semantics of
@@ -195,6 +224,9 @@ class Sequential:
         from .recurrent import LSTM
         if any(isinstance(l, LSTM) for l in self.layers):
             return self._compile_lstm(loss, optimizer)
+        from .convolutional import Convolution1D
+        if any(isinstance(l, Convolution1D) for l in self.layers):
+            return self._compile_cnn(loss, optimizer)
         for l in self.layers[:-1]:
             if l.activation != "relu":
                 raise NotImplementedError("hidden layers are ReLU on this path (cnn.py:111)")

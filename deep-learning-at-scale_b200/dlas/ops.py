@@ -178,6 +178,34 @@ def lstm_predict(d_in, hidden, n_layers, T, params, X, workspace, out=None):
     return out
 
 
+# ---- the CNN of cnn.py:110-114 -----------------------------------------------------------------------
+def cnn_n_params(L, K, F, n_out):
+    n = int(_lib.load().dlas_cnn_n_params(L, K, F, n_out))
+    if n == 0:
+        raise _lib.DlasError(-1, "CNN shape L=%d K=%d F=%d n_out=%d is not supported" % (L, K, F, n_out))
+    return n
+
+
+def cnn_workspace(L, K, F, n_out, n_rows, device="cuda"):
+    nbytes = int(_lib.load().dlas_cnn_workspace_bytes(L, K, F, n_out, int(n_rows)))
+    return torch.empty(max(nbytes, 256), dtype=torch.uint8, device=device)
+
+
+def cnn_grad(L, K, F, n_out, loss, params, X, y, grad_sum, workspace, keep=1.0, dropout_seed=0, sample0=0):
+    check(_lib.load().dlas_cnn_grad(L, K, F, n_out, int(loss), ptr(params), ptr(X), ptr(y), X.shape[0], float(keep),
+                                    int(dropout_seed), int(sample0), ptr(grad_sum), ptr(workspace), workspace.numel(),
+                                    stream_ptr()))
+    return grad_sum
+
+
+def cnn_predict(L, K, F, n_out, params, X, workspace, out=None):
+    if out is None:
+        out = torch.empty((X.shape[0], n_out), dtype=torch.float32, device=X.device)
+    check(_lib.load().dlas_cnn_predict(L, K, F, n_out, ptr(params), ptr(X), X.shape[0], ptr(out), ptr(workspace),
+                                       workspace.numel(), stream_ptr()))
+    return out
+
+
 # ---- replayable steps: cursor + iteration counter in device memory (CUDA-graph friendly) --------------
 def mlp_grad_at(dims, loss, mode, params, X_base, y_base, batch_rows, state, grad_sum, workspace, parity_stride=0):
     check(_lib.load().dlas_mlp_grad_at(int_array(dims), len(dims) - 1, int(loss), int(mode), ptr(params), ptr(X_base),

@@ -207,6 +207,26 @@ int dlas_lstm_predict(int d_in, int hidden, int n_layers, int T, const float* pa
                       const float* X, size_t n_seq, float* yhat, void* workspace,
                       size_t workspace_bytes, void* stream);
 
+/* ---- the script's own CNN (cnn.py:110-114):
+ *   Convolution1D(1, F, K, activation='relu', border_mode='valid') -> Dropout(1 - keep) -> Flatten()
+ *   -> Dense((L-K+1)*F, n_out)            [cnn.py: L=48, K=13, F=100, n_out=12 -> 44,612 parameters]
+ * flat parameters: Wc[K][F], bc[F], Wd[(L-K+1)*F][n_out] (Flatten is time-major: t*F + f), bd[n_out].
+ * X is (n_rows, L) fp32 (one input channel), y (n_rows, n_out).  n_out <= 16. */
+size_t dlas_cnn_n_params(int L, int K, int F, int n_out);                 /* 0 on a bad shape */
+size_t dlas_cnn_workspace_bytes(int L, int K, int F, int n_out, size_t n_rows);
+/* replaces the forward+backward half of model.fit's train-on-batch (cnn.py:124-128):
+ * grad_sum[0..n_params) = gradient SUMS over the rows, grad_sum[n_params] = sum of per-row losses.
+ * Dropout is inverted (a * mask / keep); mask bit of (row r, unit j) is the counter hash of
+ * (sample0 + r) * T*F + j on stream 300 of dropout_seed, so every rank/step draws its own bits when
+ * the caller passes sample0 = iteration * global_batch + first row of this rank.  keep >= 1: no dropout.
+ * Follow with dlas_opt_step (cnn.py:117 SGD). */
+int dlas_cnn_grad(int L, int K, int F, int n_out, int loss, const float* params, const float* X,
+                  const float* y, size_t n_rows, float keep, uint64_t dropout_seed, uint64_t sample0,
+                  float* grad_sum, void* workspace, size_t workspace_bytes, void* stream);
+/* model.predict / test_on_batch (cnn.py:132): test-time forward, dropout off; yhat (n_rows, n_out) */
+int dlas_cnn_predict(int L, int K, int F, int n_out, const float* params, const float* X,
+                     size_t n_rows, float* yhat, void* workspace, size_t workspace_bytes, void* stream);
+
 #ifdef __cplusplus
 }
 #endif

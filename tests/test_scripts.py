@@ -30,6 +30,7 @@ def test_schema_rule_and_target_exclusion(capsys):
     ("static_ann.py", ["--synthetic", "20000", "--hidden", "64,64", "--batch-size", "256", "--epochs", "3", "--loss", "mse"]),
     ("dynamic_ann.py", ["--synthetic", "6000", "--lags", "24", "--hidden", "256,256", "--batch-size", "256", "--epochs", "2"]),
     ("lstm.py", ["--synthetic", "600", "--seq-len", "12", "--hidden", "32", "--layers", "2", "--batch-size", "64", "--epochs", "2"]),
+    ("cnn.py", ["--synthetic", "800", "--batch-size", "20", "--epochs", "2"]),
     ("gilbert.py", ["--synthetic", "100000"]),
 ])
 def test_scripts_run_with_reference_argv(tmp_path, script, extra):

@@ -325,7 +325,17 @@ def main():
         t = timed(lambda: ml.train_on_batch(Xs, ysq), 3)
         extras["lstm_2x128_T48_batch4096"] = {"sequences_per_s": 4096 / t, "ms_per_step": t * 1e3, "mode": "fp32",
                                               "frac_of_bf16_sustained_peak": 57.41e6 * 4096 / t / 1e12 / pk["tf_sust"]}
-        del series, ys, Wd, yd, X8, y8, Xs, ysq
+        # the script's own CNN (cnn.py:110-128) at its own batch of 20 and at 4096 rows per step, dropout on
+        for cb in (20, 4096):
+            Wc, _ = ops.synth_series(cb, 60, 1)
+            Wc = Wc.reshape(cb, 60)
+            Xc, yc = Wc[:, :48].contiguous(), Wc[:, 48:].contiguous()
+            mc = dlas.Sequential([dlas.Convolution1D(1, 100, 13, activation="relu"), dlas.Dropout(0.5), dlas.Flatten(), dlas.Dense(3600, 12)])
+            mc.compile(loss=dlas.mae_clip, optimizer=dlas.SGD(lr=0.001, momentum=0.99, decay=1e-6, nesterov=True))
+            t = timed(lambda: mc.train_on_batch(Xc, yc), 20)
+            extras["cnn_48_conv13x100_dense12_batch%d" % cb] = {"samples_per_s": cb / t, "us_per_step": t * 1e6, "mode": "fp32",
+                                                                 "launches_per_step": 7}
+        del series, ys, Wd, yd, X8, y8, Xs, ysq, Wc, Xc, yc
 
     if rank == 0:
         kern_s = kern_ms / max(1, kern_n) * 1e-3

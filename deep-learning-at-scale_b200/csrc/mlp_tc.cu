@@ -44,10 +44,11 @@ using namespace tc;
 constexpr int D0 = 32, D1 = 256, D2 = 256;
 constexpr int TILE = 128;
 constexpr int CSPLIT = 2;             // epilogue warps per TMEM lane quarter (4 measured no faster: the epilogues are latency- and smem-bound): each takes 64/CSPLIT columns of a chunk
-constexpr int CW = 64 / CSPLIT;
+constexpr int CW = 128 / CSPLIT;      // work-buffer columns per epilogue thread
 constexpr int N_EPI = 128 * CSPLIT;   // epilogue threads (warps 0 .. 4*CSPLIT-1)
 constexpr int ISSUER_WARP = N_EPI / 32;
-constexpr int NT = N_EPI + 32;        // + MMA issuer warp
+constexpr int NT = N_EPI + 128;       // + the issuer warpgroup (warp ISSUER_WARP issues; its three siblings only give their registers away)
+constexpr int EPI_REGS = 200, ISSUER_REGS = 104;  // setmaxnreg: 2 x 128 x 200 + 128 x 104 = 64,512 <= 65,536
 constexpr int W1_OFF = 0, B1_OFF = W1_OFF + D0 * D1, W2_OFF = B1_OFF + D1, B2_OFF = W2_OFF + D1 * D2,
               W3_OFF = B2_OFF + D2, B3_OFF = W3_OFF + D2, N_PARAMS = B3_OFF + 1;
 constexpr size_t PSTRIDE = ((size_t)N_PARAMS + 1 + 3) & ~(size_t)3;
@@ -59,7 +60,7 @@ constexpr uint32_t S_W1 = 0, S_W2 = S_W1 + K1 * 4 * 128, S_X = S_W2 + 65536, S_H
 constexpr int F_B2 = 0, F_W3 = 128, F_Y = 256 /*[2][128]*/, F_PART = 512 /*[2][128]*/, F_RP = 768 /*[CSPLIT][128]*/,
               F_RED = F_RP + CSPLIT * 128 /*[4][128]*/, F_END = F_RED + 512;
 constexpr uint32_t S_BAR = S_F32 + F_END * 4;
-enum { B_DONE0 = 0, B_DONE1, B_FREE0, B_FREE1, B_X0, B_X1, B_H1, B_DZ2, B_DZ1, B_DW1, B_ALL, B_XC0, B_XC1, N_BARS };
+enum { B_DONE = 0, B_FREE, B_X0, B_X1, B_H1A, B_H1, B_DZ2, B_DZ1A, B_DZ1, B_DW1, B_ALL, B_XC0, B_XC1, N_BARS };
 constexpr uint32_t S_TMEM = S_BAR + N_BARS * 8;
 constexpr uint32_t SMEM_BYTES = S_TMEM + 16;
 
@@ -97,8 +98,8 @@ __device__ __forceinline__ uint4 pack8(float4 a, float4 b) {
   return make_uint4(pack_half2(a.x, a.y), pack_half2(a.z, a.w), pack_half2(b.x, b.y), pack_half2(b.z, b.w));
 }
 
-// Debug trace (DLAS_TC_TRACE=<file>): SM-clock stamps of CTA 0, epilogue thread 0 (slots 0..) and the issuer (slots 512..)
-#define TRACE_E(k) do { if (trace && blockIdx.x == 0 && tid == 0 && te < 500) trace[te++] = ((long long)(k) << 48) | (clock64() & 0xFFFFFFFFFFFFll); } while (0)
+// Debug trace (DLAS_TC_TRACE=<file>): SM-clock stamps of CTA 0, epilogue warp 0 (slots 0..), the issuer (slots 512..) and the last epilogue warp (slots 1024..)
+#define TRACE_E(k) do { if (trace && blockIdx.x == 0 && lane == 0 && (warp == 0 || warp == N_EPI / 32 - 1) && te < 500) trace[(warp ? 1024 : 0) + te++] = ((long long)(k) << 48) | (clock64() & 0xFFFFFFFFFFFFll); } while (0)
 #define TRACE_M(k) do { if (trace && blockIdx.x == 0 && lane == 0 && tmm < 500) trace[512 + tmm++] = ((long long)(k) << 48) | (clock64() & 0xFFFFFFFFFFFFll); } while (0)
 
 __global__ void __cluster_dims__(2, 1, 1) __launch_bounds__(NT, 1)
@@ -128,11 +129,12 @@ mlp_tc_kernel(const int loss_kind, const float* __restrict__ params, const float
 
   // ---- one-time set-up: barriers, TMEM, weights -> fp16 tiles -------------------------------------------
   if (tid == 0) {
-    mbar_init(&bars[B_DONE0], 1); mbar_init(&bars[B_DONE1], 1);
+    mbar_init(&bars[B_DONE], 1);
     // one arrival per epilogue WARP (lane 0, after __syncwarp): 256 per-thread arrivals on one word would serialise
-    mbar_init(&bars[B_FREE0], N_EPI / 32); mbar_init(&bars[B_FREE1], N_EPI / 32);
+    mbar_init(&bars[B_FREE], N_EPI / 32);
     mbar_init(&bars[B_X0], N_EPI / 32); mbar_init(&bars[B_X1], N_EPI / 32);
-    mbar_init(&bars[B_H1], N_EPI / 32); mbar_init(&bars[B_DZ2], N_EPI / 32); mbar_init(&bars[B_DZ1], N_EPI / 32);
+    mbar_init(&bars[B_H1A], N_EPI / 32); mbar_init(&bars[B_H1], N_EPI / 32); mbar_init(&bars[B_DZ2], N_EPI / 32); mbar_init(&bars[B_DZ1A], N_EPI / 32);
+    mbar_init(&bars[B_DZ1], N_EPI / 32);
     mbar_init(&bars[B_ALL], 1); mbar_init(&bars[B_DW1], 1);
     mbar_init(&bars[B_XC0], 1); mbar_init(&bars[B_XC1], 1);   // exchange of the partial output dots: 1 arrival + 512 tx bytes
     mbar_fence_init();
@@ -196,36 +198,50 @@ mlp_tc_kernel(const int loss_kind, const float* __restrict__ params, const float
   asm volatile("griddepcontrol.launch_dependents;" ::: "memory");
   const int my_tiles = (n_tiles > (size_t)pair) ? (int)((n_tiles - pair + n_pairs - 1) / n_pairs) : 0;
 
-  if (warp == ISSUER_WARP) {
+  if (warp >= ISSUER_WARP) {
+    // the issuer warpgroup hands most of its registers to the two epilogue warpgroups
+    asm volatile("setmaxnreg.dec.sync.aligned.u32 %0;" ::"n"(ISSUER_REGS));
+  }
+  if (warp > ISSUER_WARP) {
+    // idle siblings of the issuer warp
+  } else if (warp == ISSUER_WARP) {
     // =========================== MMA issuer ===========================
     // The whole warp runs the control flow (so descriptor arithmetic stays warp-uniform); one elected
     // lane issues.  Descriptors are a constant base plus a compile-time offset per K step.
-    constexpr uint32_t ID_KM_MN_64 = make_idesc(128, 64, false, true);
     constexpr uint32_t ID_KM_MN_128 = make_idesc(128, 128, false, true);
-    constexpr uint32_t ID_KM_KM_64 = make_idesc(128, 64, false, false);
+    constexpr uint32_t ID_KM_KM_128 = make_idesc(128, 128, false, false);
     constexpr uint32_t ID_MN_MN_128 = make_idesc(128, 128, true, true);
     constexpr uint32_t ID_MN_MN_48 = make_idesc(128, 48, true, true);
     constexpr uint32_t ID_MN_KM_16 = make_idesc(128, 16, true, false);
     const bool leader = elect_one();
-    const uint64_t dX_km[2] = {desc_kmajor(sX, TILE, 0, 0), desc_kmajor(sX + 16384, TILE, 0, 0)};
-    const uint64_t dX_mn[2] = {desc_mnmajor(sX, TILE, 0, 0), desc_mnmajor(sX + 16384, TILE, 0, 0)};
-    const uint64_t dW1_mn = desc_mnmajor(sW1, K1, 0, 0);
-    const uint64_t dW2_mn = desc_mnmajor(sW2, D1, 0, 0), dW2_km = desc_kmajor(sW2, D1, 0, 0);
-    const uint64_t dH1_km = desc_kmajor(sH1, TILE, 0, 0), dH1_mn = desc_mnmajor(sH1, TILE, 0, 0);
-    const uint64_t dDZ2_km = desc_kmajor(sDZ2, TILE, 0, 0), dDZ2_mn = desc_mnmajor(sDZ2, TILE, 0, 0);
-    const uint64_t dONES = desc_kmajor(sONES, 16, 0, 0);
-    uint32_t n = 0;  // running index of chunk GEMMs; buffer = n & 1
-    // Z1 + b1 = [X | 1 | 0] [W1 ; b1 ; 0] in four N=64 chunks, K = 48.  Chunks 0,1 of tile t+1 are issued at the END
-    // of tile t, before dW1(t), so that they are already in TMEM when the epilogue warps come back for them.
-    auto issue_z1 = [&](int xb, int s) {
-      const uint32_t b = n & 1;
-      ok = mbar_wait(&bars[B_FREE0 + b], ((n >> 1) & 1) ^ 1) && ok;
+    // the second X buffer is 16 KB further: +1024 in the descriptor's (address >> 4) field
+    uint64_t dX_km0 = desc_kmajor(sX, TILE, 0, 0), dX_mn0 = desc_mnmajor(sX, TILE, 0, 0);
+    uint64_t dW1_mn = desc_mnmajor(sW1, K1, 0, 0);
+    uint64_t dW2_mn = desc_mnmajor(sW2, D1, 0, 0), dW2_km = desc_kmajor(sW2, D1, 0, 0);
+    uint64_t dH1_km = desc_kmajor(sH1, TILE, 0, 0), dH1_mn = desc_mnmajor(sH1, TILE, 0, 0);
+    uint64_t dDZ2_km = desc_kmajor(sDZ2, TILE, 0, 0), dDZ2_mn = desc_mnmajor(sDZ2, TILE, 0, 0);
+    uint64_t dONES = desc_kmajor(sONES, 16, 0, 0);
+    // Re-derive "base + compile-time offset" inside every tile: hoisted out of the loop, the ~100 descriptor sums
+    // do not fit the issuer's reduced register budget and come back as local-memory loads in front of every MMA.
+    auto pin_descs = [&]() {
+      asm volatile("" : "+l"(dX_km0), "+l"(dX_mn0), "+l"(dW1_mn), "+l"(dW2_mn), "+l"(dW2_km));
+      asm volatile("" : "+l"(dH1_km), "+l"(dH1_mn), "+l"(dDZ2_km), "+l"(dDZ2_mn), "+l"(dONES));
+    };
+    uint32_t n = 0;  // running index of work-buffer uses (five per tile): use n completes phase n of B_DONE / B_FREE
+    auto wait_free = [&]() {   // the epilogue has read use n-1 out of the work buffer
+      ok = mbar_wait(&bars[B_FREE], (n & 1) ^ 1) && ok;
       fence_after();
+    };
+    // Z1 + b1 = [X | 1 | 0] [W1 ; b1 ; 0], K = 48, as two N=128 halves.  Half 0 of tile t+1 is issued near the END of
+    // tile t, so that it is already in TMEM when the epilogue warps come back for it.
+    auto issue_z1 = [&](int xb, int h) {
+      wait_free();
       if (leader) {
 #pragma unroll
         for (int i = 0; i < K1 / 16; ++i)
-          mma_f16(tm + TM_W0 + b * 64, dX_km[xb] + koff_kmajor(TILE, i), dW1_mn + mnoff(K1, 64) * s + koff_mnmajor(i), ID_KM_MN_64, i > 0);
-        mma_commit(&bars[B_DONE0 + b]);
+          mma_f16(tm + TM_W0, dX_km0 + (uint64_t)(xb * 1024) + koff_kmajor(TILE, i), dW1_mn + mnoff(K1, 128) * h + koff_mnmajor(i),
+                  ID_KM_MN_128, i > 0);
+        mma_commit(&bars[B_DONE]);
       }
       __syncwarp();
       ++n;
@@ -233,101 +249,131 @@ mlp_tc_kernel(const int loss_kind, const float* __restrict__ params, const float
     if (my_tiles > 0) {
       ok = mbar_wait(&bars[B_X0], 0) && ok;
       issue_z1(0, 0);
-      issue_z1(0, 1);
     }
     for (int it = 0; it < my_tiles; ++it) {
       const int xb = it & 1;
       const bool first = (it == 0);
+      pin_descs();
       TRACE_M(10);
-      issue_z1(xb, 2);
-      issue_z1(xb, 3);
-      // Z2h = H1 W2h: ONE N=128 MMA chain over both work buffers (smem operand traffic: 128 KB instead of 192 KB)
+      issue_z1(xb, 1);
+      // Z2h = H1 W2h: one N=128 chain, K = 256; its first half only needs H1 columns 0..127, which are in place
+      // while the epilogue is still converting columns 128..255
       TRACE_M(12);
-      ok = mbar_wait(&bars[B_H1], it & 1) && ok;
-      TRACE_M(13);
-      ok = mbar_wait(&bars[B_FREE0 + (n & 1)], ((n >> 1) & 1) ^ 1) && ok;
-      ok = mbar_wait(&bars[B_FREE0 + ((n + 1) & 1)], (((n + 1) >> 1) & 1) ^ 1) && ok;
+      wait_free();
+      ok = mbar_wait(&bars[B_H1A], it & 1) && ok;
       fence_after();
       if (leader) {
 #pragma unroll
-        for (int i = 0; i < D1 / 16; ++i)
+        for (int i = 0; i < D1 / 32; ++i)
           mma_f16(tm + TM_W0, dH1_km + koff_kmajor(TILE, i), dW2_mn + koff_mnmajor(i), ID_KM_MN_128, i > 0);
-        mma_commit(&bars[B_DONE0]);
-        mma_commit(&bars[B_DONE1]);
       }
       __syncwarp();
-      n += 2;
+      ok = mbar_wait(&bars[B_H1], it & 1) && ok;
+      TRACE_M(13);
+      fence_after();
+      if (leader) {
+#pragma unroll
+        for (int i = D1 / 32; i < D1 / 16; ++i)
+          mma_f16(tm + TM_W0, dH1_km + koff_kmajor(TILE, i), dW2_mn + koff_mnmajor(i), ID_KM_MN_128, 1);
+        mma_commit(&bars[B_DONE]);
+      }
+      __syncwarp();
+      ++n;
       TRACE_M(14);
-      TRACE_M(15);
       ok = mbar_wait(&bars[B_DZ2], it & 1) && ok;
       TRACE_M(16);
       fence_after();
-      if (leader) {
-        // db2h += dZ2h^T 1 ; dW2h += H1^T dZ2h (accumulate over the whole launch)
-#pragma unroll
-        for (int i = 0; i < TILE / 16; ++i)
-          mma_f16(tm + TM_DB2, dDZ2_mn + koff_mnmajor(i), dONES, ID_MN_KM_16, !(first && i == 0));
-#pragma unroll
-        for (int mh = 0; mh < 2; ++mh)
+      // Order: dW2 rows 0..127 | dH1p half 0 | dW2 rows 128..255, db2 | dH1p half 1 | dW1 rows 0..127 | next tile's
+      // Z1 half 0 | dW1 rows 128..255.  The epilogue overwrites H1 with dZ1 in place, half by half: half h (H1 columns
+      // 128h..128h+127) may be written once the dW2 half that reads those columns as its M rows has completed, which
+      // the commit of dH1p half h implies (MMAs complete in issue order).
+      auto issue_dw2 = [&](int mh) {
+        if (leader) {
 #pragma unroll
           for (int i = 0; i < TILE / 16; ++i)
             mma_f16(tm + TM_DW2 + mh * 128, dH1_mn + mnoff(TILE, mh * 128) + koff_mnmajor(i), dDZ2_mn + koff_mnmajor(i), ID_MN_MN_128,
                     !(first && i == 0));
-      }
-      __syncwarp();
-      TRACE_M(60);
-      // dH1p = dZ2h W2h^T: four N=64 chunks (in-index)
-#pragma unroll
-      for (int s = 0; s < 4; ++s, ++n) {
-        const uint32_t b = n & 1;
-        ok = mbar_wait(&bars[B_FREE0 + b], ((n >> 1) & 1) ^ 1) && ok;
+        }
+        __syncwarp();
+      };
+      auto issue_dh1 = [&](int h) {   // dH1p half h = dZ2h W2h^T[:, 128h..128h+127]
+        wait_free();
         TRACE_M(61);
-        fence_after();
         if (leader) {
 #pragma unroll
           for (int i = 0; i < 128 / 16; ++i)
-            mma_f16(tm + TM_W0 + b * 64, dDZ2_km + koff_kmajor(TILE, i), dW2_km + rowoff(s * 64) + koff_kmajor(D1, i), ID_KM_KM_64, i > 0);
-          mma_commit(&bars[B_DONE0 + b]);
+            mma_f16(tm + TM_W0, dDZ2_km + koff_kmajor(TILE, i), dW2_km + rowoff(h * 128) + koff_kmajor(D1, i), ID_KM_KM_128, i > 0);
+          mma_commit(&bars[B_DONE]);
         }
         __syncwarp();
+        ++n;
+      };
+      auto issue_dw1 = [&](int mh) {  // dW1p^T rows mh*128.. += dZ1p^T [X | 1]
+        if (leader) {
+#pragma unroll
+          for (int i = 0; i < TILE / 16; ++i)
+            mma_f16(tm + TM_DW1 + mh * 64, dH1_mn + mnoff(TILE, mh * 128) + koff_mnmajor(i), dX_mn0 + (uint64_t)(xb * 1024) + koff_mnmajor(i),
+                    ID_MN_MN_48, !(first && i == 0));
+        }
+        __syncwarp();
+      };
+      issue_dw2(0);
+      TRACE_M(60);
+      issue_dh1(0);
+      issue_dw2(1);
+      if (leader) {   // db2h += dZ2h^T 1
+#pragma unroll
+        for (int i = 0; i < TILE / 16; ++i)
+          mma_f16(tm + TM_DB2, dDZ2_mn + koff_mnmajor(i), dONES, ID_MN_KM_16, !(first && i == 0));
       }
-      // next tile's Z1 chunks 0,1 (their buffers are free as soon as the last two dH1p chunks have been read)
+      __syncwarp();
+      issue_dh1(1);
+      TRACE_M(17);
+      ok = mbar_wait(&bars[B_DZ1A], it & 1) && ok;    // dZ1 columns 0..127 are in place
+      fence_after();
+      issue_dw1(0);
+      // next tile's Z1 half 0 (the work buffer is free as soon as the second dH1p half has been read)
       if (it + 1 < my_tiles) {
         ok = mbar_wait(&bars[B_X0 + (xb ^ 1)], ((it + 1) >> 1) & 1) && ok;
         issue_z1(xb ^ 1, 0);
-        issue_z1(xb ^ 1, 1);
       }
-      // dW1p^T += dZ1p^T [X | 1]
-      TRACE_M(17);
       ok = mbar_wait(&bars[B_DZ1], it & 1) && ok;
       TRACE_M(18);
       fence_after();
-      if (leader) {
-#pragma unroll
-        for (int mh = 0; mh < 2; ++mh)
-#pragma unroll
-          for (int i = 0; i < TILE / 16; ++i)
-            mma_f16(tm + TM_DW1 + mh * 64, dH1_mn + mnoff(TILE, mh * 128) + koff_mnmajor(i), dX_mn[xb] + koff_mnmajor(i), ID_MN_MN_48,
-                    !(first && i == 0));
-        mma_commit(&bars[B_DW1]);   // sH1 (dZ1) and sX[xb] are free once this arrives
-      }
+      issue_dw1(1);
+      if (leader) mma_commit(&bars[B_DW1]);   // sH1 (dZ1), sDZ2 and sX[xb] are free once this arrives
       __syncwarp();
     }
     if (leader) mma_commit(&bars[B_ALL]);
     __syncwarp();
   } else {
     // =========================== epilogue warps ===========================
-    // warp w: TMEM lane quarter q = w % 4 (rows 32q..32q+31), column slice hh = w / 4 of every 64-column chunk
+    asm volatile("setmaxnreg.inc.sync.aligned.u32 %0;" ::"n"(EPI_REGS));
+    // warp w: TMEM lane quarter q = w % 4 (rows 32q..32q+31), column slice hh = w / 4 (CW columns) of every 128-column chunk
     const int q = warp & 3, hh = warp >> 2;
     const int row = q * 32 + lane;                      // TMEM lane = tile row
     const uint32_t lane_base = (uint32_t)(q * 32) << 16;
+    const uint32_t t_work = tm + TM_W0 + lane_base + hh * CW;
     const uint32_t peer_part = map_to_cta(sF + F_PART * 4, rank ^ 1u);
     const uint32_t peer_xc = map_to_cta(smem_u32(&bars[B_XC0]), rank ^ 1u);
-    float acc_w3[2] = {0.f, 0.f};
+    float acc_w3[CW / 32][32];   // dw3 partials of this thread's row and CW columns, summed over rows once at the end
+#pragma unroll
+    for (int j = 0; j < CW; ++j) acc_w3[j >> 5][j & 31] = 0.f;
     float acc_loss = 0.f, acc_b3 = 0.f;
     uint32_t n = 0;
+    // this thread's CW columns of the work buffer (use n) -> registers; the buffer is handed back at once
+    auto take = [&](uint32_t (&v)[CW]) {
+      ok = mbar_wait(&bars[B_DONE], n & 1) && ok;
+      fence_after();
+#pragma unroll
+      for (int c = 0; c < CW / 32; ++c) tmem_ld32(t_work + c * 32, *reinterpret_cast<uint32_t(*)[32]>(&v[c * 32]));
+      tmem_ld_wait();
+      fence_before();
+      warp_arrive(lane, &bars[B_FREE]);
+      ++n;
+    };
     // X tile loader: thread -> (row tid / XT, XF features), XT threads per row
-    constexpr int XT = N_EPI / TILE, XF = D0 / XT;      // 4 threads per row, 8 features each
+    constexpr int XT = N_EPI / TILE, XF = D0 / XT;      // 2 threads per row, 16 features each
     const int xr = tid / XT, xh = tid % XT;
     float4 xv[XF / 4];
     float yv = 0.f;
@@ -340,6 +386,9 @@ mlp_tc_kernel(const int loss_kind, const float* __restrict__ params, const float
       if (tid < TILE) yv = (row0 + tid < n_rows) ? __ldcs(y + row0 + tid) : 0.f;
     };
     auto x_store = [&](int j) {
+      // pin the fp32 -> fp16 conversion HERE: hoisted to x_issue it would make the loads blocking (a DRAM latency per tile)
+#pragma unroll
+      for (int i = 0; i < XF / 4; ++i) asm volatile("" : "+f"(xv[i].x), "+f"(xv[i].y), "+f"(xv[i].z), "+f"(xv[i].w));
 #pragma unroll
       for (int i = 0; i < XF / 8; ++i)
         sts128(sX + j * 16384 + tile_chunk_off(TILE, xr, xh * XF + i * 8), pack8(xv[2 * i], xv[2 * i + 1]));
@@ -357,23 +406,15 @@ mlp_tc_kernel(const int loss_kind, const float* __restrict__ params, const float
       const bool row_valid = row0 + row < n_rows;
       TRACE_E(20);
       if (it + 1 < my_tiles) x_issue(tile + n_pairs);      // next tile's rows: in flight during phase (b)
-      // ---- (b) H1 = relu(Z1 + b1) -> sH1, four chunks (the bias is already in the accumulator) --------
+      // ---- (b) H1 = relu(Z1 + b1) -> sH1, two halves of 128 columns (the bias is already in the accumulator) ----
 #pragma unroll 1
-      for (int s = 0; s < 4; ++s, ++n) {
-        const uint32_t b = n & 1;
-        TRACE_E(40);
-        ok = mbar_wait(&bars[B_DONE0 + b], (n >> 1) & 1) && ok;
-        TRACE_E(41);
-        fence_after();
+      for (int h = 0; h < 2; ++h) {
         uint32_t v[CW];
-        tmem_ld<CW>(tm + TM_W0 + b * 64 + lane_base + hh * CW, v);
-        tmem_ld_wait();
-        TRACE_E(42);
-        fence_before();
-        warp_arrive(lane, &bars[B_FREE0 + b]);
+        TRACE_E(40);
+        take(v);
         TRACE_E(43);
-        if (s == 0 && it > 0) ok = mbar_wait(&bars[B_DW1], (it - 1) & 1) && ok;   // dW1 of the previous tile still reads sH1
-        const int c0 = s * 64 + hh * CW;
+        if (h == 0 && it > 0) ok = mbar_wait(&bars[B_DW1], (it - 1) & 1) && ok;   // dW1 of the previous tile still reads sH1
+        const int c0 = h * 128 + hh * CW;
 #pragma unroll
         for (int g8 = 0; g8 < CW / 8; ++g8) {   // relu on packed halves: one F2FP + one HMNMX2 per two elements
           uint4 o;
@@ -383,36 +424,29 @@ mlp_tc_kernel(const int loss_kind, const float* __restrict__ params, const float
           o.w = relu_h2(pack_half2(__uint_as_float(v[g8 * 8 + 6]), __uint_as_float(v[g8 * 8 + 7])));
           sts128(sH1 + tile_chunk_off(TILE, row, c0 + g8 * 8), o);
         }
+        fence_async_smem();
+        warp_arrive(lane, &bars[h == 0 ? B_H1A : B_H1]);
       }
-      fence_async_smem();
-      warp_arrive(lane, &bars[B_H1]);
       TRACE_E(21);
       if (it + 1 < my_tiles) x_store((it + 1) & 1);        // the other X buffer was last read by tile it-1's dW1
       // ---- (c) Z2h: partial output dot, exchange, dZ2h -> sDZ2 ---------------------------------------
       TRACE_E(22);
-      float part = 0.f;
-      const uint32_t n_c = n;
-      n += 2;
-#pragma unroll
-      for (int s = 0; s < 2; ++s) {
-        const uint32_t b = (n_c + s) & 1;
-        ok = mbar_wait(&bars[B_DONE0 + b], ((n_c + s) >> 1) & 1) && ok;
-        fence_after();
-        uint32_t v[CW];
-        tmem_ld<CW>(tm + TM_W0 + b * 64 + lane_base + hh * CW, v);
-        tmem_ld_wait();
-        const int c0 = s * 64 + hh * CW;
-#pragma unroll
-        for (int g4 = 0; g4 < CW / 4; ++g4) {
-          const float4 bv = lds128f(sF + (F_B2 + c0 + g4 * 4) * 4), wv = lds128f(sF + (F_W3 + c0 + g4 * 4) * 4);
-          part = fmaf(fmaxf(__uint_as_float(v[g4 * 4 + 0]) + bv.x, 0.f), wv.x, part);
-          part = fmaf(fmaxf(__uint_as_float(v[g4 * 4 + 1]) + bv.y, 0.f), wv.y, part);
-          part = fmaf(fmaxf(__uint_as_float(v[g4 * 4 + 2]) + bv.z, 0.f), wv.z, part);
-          part = fmaf(fmaxf(__uint_as_float(v[g4 * 4 + 3]) + bv.w, 0.f), wv.w, part);
-        }
-      }
-      TRACE_E(23);
       const int buf = it & 1;
+      const int cz = hh * CW;                              // my columns of this CTA's 128 layer-2 units
+      uint32_t z[CW];                                      // Z2h stays in registers across the exchange
+      take(z);
+      TRACE_E(44);
+      float p4[4] = {0.f, 0.f, 0.f, 0.f};   // four independent chains (a single one is CW dependent FMAs per thread)
+#pragma unroll
+      for (int g4 = 0; g4 < CW / 4; ++g4) {
+        const float4 bv = lds128f(sF + (F_B2 + cz + g4 * 4) * 4), wv = lds128f(sF + (F_W3 + cz + g4 * 4) * 4);
+        p4[0] = fmaf(fmaxf(__uint_as_float(z[g4 * 4 + 0]) + bv.x, 0.f), wv.x, p4[0]);
+        p4[1] = fmaf(fmaxf(__uint_as_float(z[g4 * 4 + 1]) + bv.y, 0.f), wv.y, p4[1]);
+        p4[2] = fmaf(fmaxf(__uint_as_float(z[g4 * 4 + 2]) + bv.z, 0.f), wv.z, p4[2]);
+        p4[3] = fmaf(fmaxf(__uint_as_float(z[g4 * 4 + 3]) + bv.w, 0.f), wv.w, p4[3]);
+      }
+      const float part = (p4[0] + p4[1]) + (p4[2] + p4[3]);
+      TRACE_E(23);
       f32[F_RP + hh * 128 + row] = part;
       named_bar_sync(1, N_EPI);
       float mine = 0.f;
@@ -441,68 +475,54 @@ mlp_tc_kernel(const int loss_kind, const float* __restrict__ params, const float
         }
         if (hh == 0) { acc_loss += lo; acc_b3 += g; }
       }
-      // second pass over Z2h (still in the two work buffers; the issuer needs them again only for dH1p)
 #pragma unroll
-      for (int s = 0; s < 2; ++s) {
-        const uint32_t b = (n_c + s) & 1;
-        const int c0 = s * 64 + hh * CW;
-        uint32_t v[CW];
-        tmem_ld<CW>(tm + TM_W0 + b * 64 + lane_base + hh * CW, v);
-        tmem_ld_wait();
-        fence_before();
-        warp_arrive(lane, &bars[B_FREE0 + b]);
-        float hg[CW];
+      for (int g8 = 0; g8 < CW / 8; ++g8) {
+        const float4 wa = lds128f(sF + (F_W3 + cz + g8 * 8) * 4), wb = lds128f(sF + (F_W3 + cz + g8 * 8 + 4) * 4);
+        const float4 ba = lds128f(sF + (F_B2 + cz + g8 * 8) * 4), bb = lds128f(sF + (F_B2 + cz + g8 * 8 + 4) * 4);
+        const float w8[8] = {wa.x, wa.y, wa.z, wa.w, wb.x, wb.y, wb.z, wb.w};
+        const float b8[8] = {ba.x, ba.y, ba.z, ba.w, bb.x, bb.y, bb.z, bb.w};
+        uint32_t o[4];
 #pragma unroll
-        for (int g8 = 0; g8 < CW / 8; ++g8) {
-          const float4 wa = lds128f(sF + (F_W3 + c0 + g8 * 8) * 4), wb = lds128f(sF + (F_W3 + c0 + g8 * 8 + 4) * 4);
-          const float4 ba = lds128f(sF + (F_B2 + c0 + g8 * 8) * 4), bb = lds128f(sF + (F_B2 + c0 + g8 * 8 + 4) * 4);
-          const float w8[8] = {wa.x, wa.y, wa.z, wa.w, wb.x, wb.y, wb.z, wb.w};
-          const float b8[8] = {ba.x, ba.y, ba.z, ba.w, bb.x, bb.y, bb.z, bb.w};
-          uint32_t o[4];
-#pragma unroll
-          for (int e = 0; e < 4; ++e) {
-            const float z0 = __uint_as_float(v[g8 * 8 + 2 * e]) + b8[2 * e], z1 = __uint_as_float(v[g8 * 8 + 2 * e + 1]) + b8[2 * e + 1];
-            hg[g8 * 8 + 2 * e] = fmaxf(z0, 0.f) * g;                 // -> dw3
-            hg[g8 * 8 + 2 * e + 1] = fmaxf(z1, 0.f) * g;
-            // dZ2 = (z > 0) * (g * w3): mask and product on packed halves
-            o[e] = mul_h2(gt0_h2(pack_half2(z0, z1)), pack_half2(g * w8[2 * e], g * w8[2 * e + 1]));
-          }
-          sts128(sDZ2 + tile_chunk_off(TILE, row, c0 + g8 * 8), make_uint4(o[0], o[1], o[2], o[3]));
+        for (int e = 0; e < 4; ++e) {
+          const int j = g8 * 8 + 2 * e;
+          const float z0 = __uint_as_float(z[j]) + b8[2 * e], z1 = __uint_as_float(z[j + 1]) + b8[2 * e + 1];
+          acc_w3[j >> 5][j & 31] = fmaf(fmaxf(z0, 0.f), g, acc_w3[j >> 5][j & 31]);                      // -> dw3
+          acc_w3[(j + 1) >> 5][(j + 1) & 31] = fmaf(fmaxf(z1, 0.f), g, acc_w3[(j + 1) >> 5][(j + 1) & 31]);
+          // dZ2 = (z > 0) * (g * w3): mask and product on packed halves
+          o[e] = mul_h2(gt0_h2(pack_half2(z0, z1)), pack_half2(g * w8[2 * e], g * w8[2 * e + 1]));
         }
-        acc_w3[s] += warp_colsum<CW>(hg, lane);
+        sts128(sDZ2 + tile_chunk_off(TILE, row, cz + g8 * 8), make_uint4(o[0], o[1], o[2], o[3]));
       }
       fence_async_smem();
       warp_arrive(lane, &bars[B_DZ2]);
       TRACE_E(26);
-      // ---- (d) dZ1p = relu'(H1) o dH1p in place over H1, four chunks -----------------------------------
+      // ---- (d) dZ1p = relu'(H1) o dH1p in place over H1, two halves of 128 columns ----------------------
 #pragma unroll 1
-      for (int s = 0; s < 4; ++s, ++n) {
-        const uint32_t b = n & 1;
-        TRACE_E(50);
-        ok = mbar_wait(&bars[B_DONE0 + b], (n >> 1) & 1) && ok;
-        TRACE_E(51);
-        fence_after();
+      for (int h = 0; h < 2; ++h) {
         uint32_t v[CW];
-        tmem_ld<CW>(tm + TM_W0 + b * 64 + lane_base + hh * CW, v);
-        tmem_ld_wait();
-        fence_before();
-        warp_arrive(lane, &bars[B_FREE0 + b]);
+        TRACE_E(50);
+        take(v);
         TRACE_E(52);
-        const int c0 = s * 64 + hh * CW;
+        const int c0 = h * 128 + hh * CW;
 #pragma unroll
-        for (int g8 = 0; g8 < CW / 8; ++g8) {
-          const uint32_t a = sH1 + tile_chunk_off(TILE, row, c0 + g8 * 8);
-          const uint4 h = lds128(a);
-          uint32_t o[4];   // dZ1 = (H1 > 0) * dH1p on packed halves
-          o[0] = mul_h2(gt0_h2(h.x), pack_half2(__uint_as_float(v[g8 * 8 + 0]), __uint_as_float(v[g8 * 8 + 1])));
-          o[1] = mul_h2(gt0_h2(h.y), pack_half2(__uint_as_float(v[g8 * 8 + 2]), __uint_as_float(v[g8 * 8 + 3])));
-          o[2] = mul_h2(gt0_h2(h.z), pack_half2(__uint_as_float(v[g8 * 8 + 4]), __uint_as_float(v[g8 * 8 + 5])));
-          o[3] = mul_h2(gt0_h2(h.w), pack_half2(__uint_as_float(v[g8 * 8 + 6]), __uint_as_float(v[g8 * 8 + 7])));
-          sts128(a, make_uint4(o[0], o[1], o[2], o[3]));
+        for (int g32 = 0; g32 < CW / 32; ++g32) {
+          uint4 m[4];   // loads first: volatile shared-memory accesses keep program order
+#pragma unroll
+          for (int k = 0; k < 4; ++k) m[k] = lds128(sH1 + tile_chunk_off(TILE, row, c0 + g32 * 32 + k * 8));
+#pragma unroll
+          for (int k = 0; k < 4; ++k) {
+            const int j = g32 * 32 + k * 8;
+            uint32_t o[4];   // dZ1 = (H1 > 0) * dH1p on packed halves
+            o[0] = mul_h2(gt0_h2(m[k].x), pack_half2(__uint_as_float(v[j + 0]), __uint_as_float(v[j + 1])));
+            o[1] = mul_h2(gt0_h2(m[k].y), pack_half2(__uint_as_float(v[j + 2]), __uint_as_float(v[j + 3])));
+            o[2] = mul_h2(gt0_h2(m[k].z), pack_half2(__uint_as_float(v[j + 4]), __uint_as_float(v[j + 5])));
+            o[3] = mul_h2(gt0_h2(m[k].w), pack_half2(__uint_as_float(v[j + 6]), __uint_as_float(v[j + 7])));
+            sts128(sH1 + tile_chunk_off(TILE, row, c0 + j), make_uint4(o[0], o[1], o[2], o[3]));
+          }
         }
+        fence_async_smem();
+        warp_arrive(lane, &bars[h == 0 ? B_DZ1A : B_DZ1]);   // half 0 in place: the issuer may start dW1 rows 0..127
       }
-      fence_async_smem();
-      warp_arrive(lane, &bars[B_DZ1]);
       TRACE_E(27);
     }
 
@@ -549,9 +569,10 @@ mlp_tc_kernel(const int loss_kind, const float* __restrict__ params, const float
         my[B2_OFF + rank * 128 + row] = __uint_as_float(w[0]);
       }
       // dw3h: per-warp column sums (lanes 0..CW-1 hold them) -> add the four row quarters in order
-      if (lane < CW) {
-        f32[F_RED + q * 128 + hh * CW + lane] = acc_w3[0];
-        f32[F_RED + q * 128 + 64 + hh * CW + lane] = acc_w3[1];
+#pragma unroll
+      for (int c = 0; c < CW / 32; ++c) {
+        const float cs = warp_colsum<32>(acc_w3[c], lane);
+        f32[F_RED + q * 128 + hh * CW + c * 32 + lane] = cs;
       }
       named_bar_sync(1, N_EPI);
       if (tid < 128)
@@ -655,8 +676,8 @@ int launch_main(int loss, const float* params, const float* X, const float* y, s
   long long* trace = nullptr;
   const char* trace_path = getenv("DLAS_TC_TRACE");   // debug only: this branch allocates and synchronises
   if (trace_path) {
-    DLAS_CUDA(cudaMalloc(&trace, 1024 * sizeof(long long)));
-    DLAS_CUDA(cudaMemsetAsync(trace, 0, 1024 * sizeof(long long), st));
+    DLAS_CUDA(cudaMalloc(&trace, 1536 * sizeof(long long)));
+    DLAS_CUDA(cudaMemsetAsync(trace, 0, 1536 * sizeof(long long), st));
   }
   {
     cudaLaunchConfig_t cfg = {};
@@ -674,14 +695,14 @@ int launch_main(int loss, const float* params, const float* X, const float* y, s
   prof_end(pi, st);
   DLAS_LAUNCH_CHECK();
   if (trace_path) {
-    long long h[1024];
+    long long h[1536];
     DLAS_CUDA(cudaMemcpyAsync(h, trace, sizeof(h), cudaMemcpyDeviceToHost, st));
     DLAS_CUDA(cudaStreamSynchronize(st));
     cudaFree(trace);
     FILE* f = fopen(trace_path, "w");
     if (f) {
-      for (int i = 0; i < 1024; ++i)
-        if (h[i]) fprintf(f, "%s %lld %lld\n", i < 512 ? "E" : "M", h[i] >> 48, h[i] & 0xFFFFFFFFFFFFll);
+      for (int i = 0; i < 1536; ++i)
+        if (h[i]) fprintf(f, "%s %lld %lld\n", i < 512 ? "E" : (i < 1024 ? "M" : "F"), h[i] >> 48, h[i] & 0xFFFFFFFFFFFFll);
       fclose(f);
     }
   }

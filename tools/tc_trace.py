@@ -20,9 +20,9 @@ os.environ["DLAS_TC_TRACE"] = "/tmp/tc_trace.txt"
 ops.mlp_grad(DIMS, 0, dlas.MODE_TC, p, X, y, gs, ws)
 torch.cuda.synchronize()
 ev = [l.split() for l in open("/tmp/tc_trace.txt")]
-for who in ("E", "M"):
+t0 = min(int(t) for w, k, t in ev)      # common origin: both roles stamp the same SM clock
+for who in ("E", "M", "F"):
     seq = [(int(k), int(t)) for w, k, t in ev if w == who]
-    t0 = seq[0][1]
     out = " ".join("%d:%d" % (k, t - t0) for k, t in seq)
     open(os.path.join(os.path.dirname(os.path.abspath(__file__)), "..", "gpurun_out", "tc_trace_%s.txt" % who), "w").write(out + "\n")
     print(who, out[:1500])

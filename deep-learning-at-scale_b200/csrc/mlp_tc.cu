@@ -437,13 +437,29 @@ mlp_tc_kernel(const int loss_kind, const float* __restrict__ params, const float
       take(z);
       TRACE_E(44);
       float p4[4] = {0.f, 0.f, 0.f, 0.f};   // four independent chains (a single one is CW dependent FMAs per thread)
+      {
+        // z <- H2 = relu(Z2 + b2) in place; partial dot with w3.  The constants of the next 8 columns are loaded
+        // before the current 8 are used: with two warps per scheduler a load-to-use distance of one instruction
+        // leaves the shared-memory latency exposed 16 times per pass.
+        float4 cb[2][2], cw[2][2];
+        auto fetch = [&](int blk, int s) {
+          cb[s][0] = lds128f(sF + (F_B2 + cz + blk * 8) * 4); cb[s][1] = lds128f(sF + (F_B2 + cz + blk * 8 + 4) * 4);
+          cw[s][0] = lds128f(sF + (F_W3 + cz + blk * 8) * 4); cw[s][1] = lds128f(sF + (F_W3 + cz + blk * 8 + 4) * 4);
+        };
+        fetch(0, 0);
 #pragma unroll
-      for (int g4 = 0; g4 < CW / 4; ++g4) {
-        const float4 bv = lds128f(sF + (F_B2 + cz + g4 * 4) * 4), wv = lds128f(sF + (F_W3 + cz + g4 * 4) * 4);
-        p4[0] = fmaf(fmaxf(__uint_as_float(z[g4 * 4 + 0]) + bv.x, 0.f), wv.x, p4[0]);
-        p4[1] = fmaf(fmaxf(__uint_as_float(z[g4 * 4 + 1]) + bv.y, 0.f), wv.y, p4[1]);
-        p4[2] = fmaf(fmaxf(__uint_as_float(z[g4 * 4 + 2]) + bv.z, 0.f), wv.z, p4[2]);
-        p4[3] = fmaf(fmaxf(__uint_as_float(z[g4 * 4 + 3]) + bv.w, 0.f), wv.w, p4[3]);
+        for (int blk = 0; blk < CW / 8; ++blk) {
+          const int s = blk & 1;
+          if (blk + 1 < CW / 8) fetch(blk + 1, s ^ 1);
+          const float b8[8] = {cb[s][0].x, cb[s][0].y, cb[s][0].z, cb[s][0].w, cb[s][1].x, cb[s][1].y, cb[s][1].z, cb[s][1].w};
+          const float w8[8] = {cw[s][0].x, cw[s][0].y, cw[s][0].z, cw[s][0].w, cw[s][1].x, cw[s][1].y, cw[s][1].z, cw[s][1].w};
+#pragma unroll
+          for (int e = 0; e < 8; ++e) {
+            const float r = fmaxf(__uint_as_float(z[blk * 8 + e]) + b8[e], 0.f);
+            p4[e & 3] = fmaf(r, w8[e], p4[e & 3]);
+            z[blk * 8 + e] = __float_as_uint(r);
+          }
+        }
       }
       const float part = (p4[0] + p4[1]) + (p4[2] + p4[3]);
       TRACE_E(23);
@@ -475,23 +491,29 @@ mlp_tc_kernel(const int loss_kind, const float* __restrict__ params, const float
         }
         if (hh == 0) { acc_loss += lo; acc_b3 += g; }
       }
+      {
+        float4 cw[2][2];
+        auto fetch = [&](int blk, int s) {
+          cw[s][0] = lds128f(sF + (F_W3 + cz + blk * 8) * 4); cw[s][1] = lds128f(sF + (F_W3 + cz + blk * 8 + 4) * 4);
+        };
+        fetch(0, 0);
 #pragma unroll
-      for (int g8 = 0; g8 < CW / 8; ++g8) {
-        const float4 wa = lds128f(sF + (F_W3 + cz + g8 * 8) * 4), wb = lds128f(sF + (F_W3 + cz + g8 * 8 + 4) * 4);
-        const float4 ba = lds128f(sF + (F_B2 + cz + g8 * 8) * 4), bb = lds128f(sF + (F_B2 + cz + g8 * 8 + 4) * 4);
-        const float w8[8] = {wa.x, wa.y, wa.z, wa.w, wb.x, wb.y, wb.z, wb.w};
-        const float b8[8] = {ba.x, ba.y, ba.z, ba.w, bb.x, bb.y, bb.z, bb.w};
-        uint32_t o[4];
+        for (int g8 = 0; g8 < CW / 8; ++g8) {
+          const int s = g8 & 1;
+          if (g8 + 1 < CW / 8) fetch(g8 + 1, s ^ 1);
+          const float w8[8] = {cw[s][0].x, cw[s][0].y, cw[s][0].z, cw[s][0].w, cw[s][1].x, cw[s][1].y, cw[s][1].z, cw[s][1].w};
+          uint32_t o[4];
 #pragma unroll
-        for (int e = 0; e < 4; ++e) {
-          const int j = g8 * 8 + 2 * e;
-          const float z0 = __uint_as_float(z[j]) + b8[2 * e], z1 = __uint_as_float(z[j + 1]) + b8[2 * e + 1];
-          acc_w3[j >> 5][j & 31] = fmaf(fmaxf(z0, 0.f), g, acc_w3[j >> 5][j & 31]);                      // -> dw3
-          acc_w3[(j + 1) >> 5][(j + 1) & 31] = fmaf(fmaxf(z1, 0.f), g, acc_w3[(j + 1) >> 5][(j + 1) & 31]);
-          // dZ2 = (z > 0) * (g * w3): mask and product on packed halves
-          o[e] = mul_h2(gt0_h2(pack_half2(z0, z1)), pack_half2(g * w8[2 * e], g * w8[2 * e + 1]));
+          for (int e = 0; e < 4; ++e) {
+            const int j = g8 * 8 + 2 * e;
+            const float r0 = __uint_as_float(z[j]), r1 = __uint_as_float(z[j + 1]);       // H2, from the first pass
+            acc_w3[j >> 5][j & 31] = fmaf(r0, g, acc_w3[j >> 5][j & 31]);                      // -> dw3
+            acc_w3[(j + 1) >> 5][(j + 1) & 31] = fmaf(r1, g, acc_w3[(j + 1) >> 5][(j + 1) & 31]);
+            // dZ2 = (H2 > 0) * (g * w3): mask and product on packed halves
+            o[e] = mul_h2(gt0_h2(pack_half2(r0, r1)), pack_half2(g * w8[2 * e], g * w8[2 * e + 1]));
+          }
+          sts128(sDZ2 + tile_chunk_off(TILE, row, cz + g8 * 8), make_uint4(o[0], o[1], o[2], o[3]));
         }
-        sts128(sDZ2 + tile_chunk_off(TILE, row, cz + g8 * 8), make_uint4(o[0], o[1], o[2], o[3]));
       }
       fence_async_smem();
       warp_arrive(lane, &bars[B_DZ2]);

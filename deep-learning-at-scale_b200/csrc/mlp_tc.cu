@@ -60,7 +60,7 @@ constexpr uint32_t S_W1 = 0, S_W2 = S_W1 + K1 * 4 * 128, S_X = S_W2 + 65536, S_H
 constexpr int F_B2 = 0, F_W3 = 128, F_Y = 256 /*[2][128]*/, F_PART = 512 /*[2][128]*/, F_RP = 768 /*[CSPLIT][128]*/,
               F_RED = F_RP + CSPLIT * 128 /*[4][128]*/, F_END = F_RED + 512;
 constexpr uint32_t S_BAR = S_F32 + F_END * 4;
-enum { B_DONE = 0, B_FREE, B_X0, B_X1, B_H1A, B_H1, B_DZ2, B_DZ1A, B_DZ1, B_DW1, B_ALL, B_XC0, B_XC1, N_BARS };
+enum { B_DONE = 0, B_FREE, B_X0, B_X1, B_H1A, B_H1, B_DZ2, B_DW2A, B_DW2B, B_DZ1A, B_DZ1, B_DW1, B_ALL, B_XC0, B_XC1, N_BARS };
 constexpr uint32_t S_TMEM = S_BAR + N_BARS * 8;
 constexpr uint32_t SMEM_BYTES = S_TMEM + 16;
 
@@ -135,7 +135,7 @@ mlp_tc_kernel(const int loss_kind, const float* __restrict__ params, const float
     mbar_init(&bars[B_X0], N_EPI / 32); mbar_init(&bars[B_X1], N_EPI / 32);
     mbar_init(&bars[B_H1A], N_EPI / 32); mbar_init(&bars[B_H1], N_EPI / 32); mbar_init(&bars[B_DZ2], N_EPI / 32); mbar_init(&bars[B_DZ1A], N_EPI / 32);
     mbar_init(&bars[B_DZ1], N_EPI / 32);
-    mbar_init(&bars[B_ALL], 1); mbar_init(&bars[B_DW1], 1);
+    mbar_init(&bars[B_ALL], 1); mbar_init(&bars[B_DW1], 1); mbar_init(&bars[B_DW2A], 1); mbar_init(&bars[B_DW2B], 1);
     mbar_init(&bars[B_XC0], 1); mbar_init(&bars[B_XC1], 1);   // exchange of the partial output dots: 1 arrival + 512 tx bytes
     mbar_fence_init();
   }
@@ -283,10 +283,10 @@ mlp_tc_kernel(const int loss_kind, const float* __restrict__ params, const float
       ok = mbar_wait(&bars[B_DZ2], it & 1) && ok;
       TRACE_M(16);
       fence_after();
-      // Order: dW2 rows 0..127 | dH1p half 0 | dW2 rows 128..255, db2 | dH1p half 1 | dW1 rows 0..127 | next tile's
+      // Order: dH1p half 0 | dW2 rows 0..127 | dH1p half 1 | dW2 rows 128..255 | db2 | dW1 rows 0..127 | next tile's
       // Z1 half 0 | dW1 rows 128..255.  The epilogue overwrites H1 with dZ1 in place, half by half: half h (H1 columns
-      // 128h..128h+127) may be written once the dW2 half that reads those columns as its M rows has completed, which
-      // the commit of dH1p half h implies (MMAs complete in issue order).
+      // 128h..128h+127) may be written once the dW2 half that reads those columns as its M rows has completed
+      // (B_DW2A / B_DW2B), so the epilogue fetches dH1p half h and the ReLU mask while that dW2 half still runs.
       auto issue_dw2 = [&](int mh) {
         if (leader) {
 #pragma unroll
@@ -317,17 +317,21 @@ mlp_tc_kernel(const int loss_kind, const float* __restrict__ params, const float
         }
         __syncwarp();
       };
-      issue_dw2(0);
-      TRACE_M(60);
       issue_dh1(0);
+      TRACE_M(60);
+      issue_dw2(0);
+      if (leader) mma_commit(&bars[B_DW2A]);   // H1 columns 0..127 may be overwritten once this arrives
+      __syncwarp();
+      issue_dh1(1);
       issue_dw2(1);
-      if (leader) {   // db2h += dZ2h^T 1
+      if (leader) {
+        mma_commit(&bars[B_DW2B]);             // ... and columns 128..255 after this one
+        // db2h += dZ2h^T 1
 #pragma unroll
         for (int i = 0; i < TILE / 16; ++i)
           mma_f16(tm + TM_DB2, dDZ2_mn + koff_mnmajor(i), dONES, ID_MN_KM_16, !(first && i == 0));
       }
       __syncwarp();
-      issue_dh1(1);
       TRACE_M(17);
       ok = mbar_wait(&bars[B_DZ1A], it & 1) && ok;    // dZ1 columns 0..127 are in place
       fence_after();
@@ -405,7 +409,6 @@ mlp_tc_kernel(const int loss_kind, const float* __restrict__ params, const float
       const size_t row0 = tile * TILE;
       const bool row_valid = row0 + row < n_rows;
       TRACE_E(20);
-      if (it + 1 < my_tiles) x_issue(tile + n_pairs);      // next tile's rows: in flight during phase (b)
       // ---- (b) H1 = relu(Z1 + b1) -> sH1, two halves of 128 columns (the bias is already in the accumulator) ----
 #pragma unroll 1
       for (int h = 0; h < 2; ++h) {
@@ -428,7 +431,9 @@ mlp_tc_kernel(const int loss_kind, const float* __restrict__ params, const float
         warp_arrive(lane, &bars[h == 0 ? B_H1A : B_H1]);
       }
       TRACE_E(21);
-      if (it + 1 < my_tiles) x_store((it + 1) & 1);        // the other X buffer was last read by tile it-1's dW1
+      // next tile's rows: loads issued here (the warps are about to wait for Z2h), converted and stored at the start of
+      // phase (d), where they wait for dH1p.  The other X buffer was last read by tile it-1's dW1 (waited for in (b)).
+      if (it + 1 < my_tiles) x_issue(tile + n_pairs);
       // ---- (c) Z2h: partial output dot, exchange, dZ2h -> sDZ2 ---------------------------------------
       TRACE_E(22);
       const int buf = it & 1;
@@ -518,6 +523,7 @@ mlp_tc_kernel(const int loss_kind, const float* __restrict__ params, const float
       fence_async_smem();
       warp_arrive(lane, &bars[B_DZ2]);
       TRACE_E(26);
+      if (it + 1 < my_tiles) x_store((it + 1) & 1);
       // ---- (d) dZ1p = relu'(H1) o dH1p in place over H1, two halves of 128 columns ----------------------
 #pragma unroll 1
       for (int h = 0; h < 2; ++h) {
@@ -531,6 +537,7 @@ mlp_tc_kernel(const int loss_kind, const float* __restrict__ params, const float
           uint4 m[4];   // loads first: volatile shared-memory accesses keep program order
 #pragma unroll
           for (int k = 0; k < 4; ++k) m[k] = lds128(sH1 + tile_chunk_off(TILE, row, c0 + g32 * 32 + k * 8));
+          if (g32 == 0) ok = mbar_wait(&bars[B_DW2A + h], it & 1) && ok;
 #pragma unroll
           for (int k = 0; k < 4; ++k) {
             const int j = g32 * 32 + k * 8;

@@ -98,9 +98,15 @@ __device__ __forceinline__ uint4 pack8(float4 a, float4 b) {
   return make_uint4(pack_half2(a.x, a.y), pack_half2(a.z, a.w), pack_half2(b.x, b.y), pack_half2(b.z, b.w));
 }
 
-// Debug trace (DLAS_TC_TRACE=<file>): SM-clock stamps of CTA 0, epilogue warp 0 (slots 0..), the issuer (slots 512..) and the last epilogue warp (slots 1024..)
+// Debug trace (library built with `build.py --trace`, run with DLAS_TC_TRACE=<file>): SM-clock stamps of CTA 0,
+// epilogue warp 0 (slots 0..), the issuer (slots 512..) and the last epilogue warp (slots 1024..)
+#ifdef DLAS_TC_TRACE
 #define TRACE_E(k) do { if (trace && blockIdx.x == 0 && lane == 0 && (warp == 0 || warp == N_EPI / 32 - 1) && te < 500) trace[(warp ? 1024 : 0) + te++] = ((long long)(k) << 48) | (clock64() & 0xFFFFFFFFFFFFll); } while (0)
 #define TRACE_M(k) do { if (trace && blockIdx.x == 0 && lane == 0 && tmm < 500) trace[512 + tmm++] = ((long long)(k) << 48) | (clock64() & 0xFFFFFFFFFFFFll); } while (0)
+#else
+#define TRACE_E(k) do { } while (0)
+#define TRACE_M(k) do { } while (0)
+#endif
 
 __global__ void __cluster_dims__(2, 1, 1) __launch_bounds__(NT, 1)
 mlp_tc_kernel(const int loss_kind, const float* __restrict__ params, const float* __restrict__ X_base,
@@ -108,9 +114,6 @@ mlp_tc_kernel(const int loss_kind, const float* __restrict__ params, const float
               unsigned* __restrict__ err_flag, const unsigned call_id, long long* __restrict__ trace,
               const long long* __restrict__ cursor) {
   // device-resident batch cursor (replayable steps): this launch works on rows [cursor*n_rows, (cursor+1)*n_rows)
-  const size_t batch0 = cursor ? (size_t)cursor[0] * n_rows : 0;
-  const float* __restrict__ X = X_base + batch0 * D0;
-  const float* __restrict__ y = y_base + batch0;
   extern __shared__ __align__(1024) uint8_t smem[];
   float* f32 = reinterpret_cast<float*>(smem + S_F32);
   uint64_t* bars = reinterpret_cast<uint64_t*>(smem + S_BAR);
@@ -140,9 +143,30 @@ mlp_tc_kernel(const int loss_kind, const float* __restrict__ params, const float
     mbar_fence_init();
   }
   if (warp == ISSUER_WARP) tmem_alloc(tmem_slot, TM_COLS);
+  // X tile loader (epilogue threads): thread -> (row tid / XT, XF features), XT threads per row
+  constexpr int XT = N_EPI / TILE, XF = D0 / XT;      // 2 threads per row, 16 features each
+  const int xr = tid / XT, xh = tid % XT;
+  float4 xv[XF / 4];
+  float yv = 0.f;
+  auto x_issue = [&](size_t tile, const float* __restrict__ X, const float* __restrict__ y) {
+    const size_t row0 = tile * TILE;
+    const bool in = row0 + xr < n_rows;
+    const float* src = X + (row0 + xr) * (size_t)D0 + xh * XF;
+#pragma unroll
+    for (int i = 0; i < XF / 4; ++i) xv[i] = in ? __ldcs(reinterpret_cast<const float4*>(src + i * 4)) : make_float4(0.f, 0.f, 0.f, 0.f);
+    if (tid < TILE) yv = (row0 + tid < n_rows) ? __ldcs(y + row0 + tid) : 0.f;
+  };
+  // The rows are inputs, not products of the previous kernel: with a host-side batch offset (no device cursor) the first
+  // tile's loads are issued before the dependency wait and complete under the weight set-up.
+  const int my_tiles = (n_tiles > (size_t)pair) ? (int)((n_tiles - pair + n_pairs - 1) / n_pairs) : 0;
+  const bool early_x = (cursor == nullptr);
+  if (early_x && tid < N_EPI && my_tiles > 0) x_issue(pair, X_base, y_base);
   // Programmatic dependent launch: everything above overlaps the tail of the previous kernel in the stream
   // (the optimiser update that produced `params`); from here on its writes are visible.
   asm volatile("griddepcontrol.wait;" ::: "memory");
+  const size_t batch0 = cursor ? (size_t)__ldcg(cursor) * n_rows : 0;   // the cursor is written by the previous step's kernels
+  const float* __restrict__ X = X_base + batch0 * D0;
+  const float* __restrict__ y = y_base + batch0;
   {
     // sW1 = [W1 ; b1 ; 0]: rows 0..31 weights, row 32 the bias (it multiplies the ones column of [x | 1 | 0]),
     // rows 33..47 zero -> Z1 comes out of the MMA with the bias already added
@@ -196,7 +220,6 @@ mlp_tc_kernel(const int loss_kind, const float* __restrict__ params, const float
 
   // dependents (the reduction kernel) may be scheduled from now on; they block in griddepcontrol.wait until this grid is done
   asm volatile("griddepcontrol.launch_dependents;" ::: "memory");
-  const int my_tiles = (n_tiles > (size_t)pair) ? (int)((n_tiles - pair + n_pairs - 1) / n_pairs) : 0;
 
   if (warp >= ISSUER_WARP) {
     // the issuer warpgroup hands most of its registers to the two epilogue warpgroups
@@ -291,7 +314,8 @@ mlp_tc_kernel(const int loss_kind, const float* __restrict__ params, const float
         if (leader) {
 #pragma unroll
           for (int i = 0; i < TILE / 16; ++i)
-            mma_f16(tm + TM_DW2 + mh * 128, dH1_mn + mnoff(TILE, mh * 128) + koff_mnmajor(i), dDZ2_mn + koff_mnmajor(i), ID_MN_MN_128,
+            // dW2h^T[c][k] (lane = layer-2 unit c, column = H1 unit k): the drain then stores 128 contiguous bytes per instruction
+            mma_f16(tm + TM_DW2 + mh * 128, dDZ2_mn + koff_mnmajor(i), dH1_mn + mnoff(TILE, mh * 128) + koff_mnmajor(i), ID_MN_MN_128,
                     !(first && i == 0));
         }
         __syncwarp();
@@ -376,19 +400,6 @@ mlp_tc_kernel(const int loss_kind, const float* __restrict__ params, const float
       warp_arrive(lane, &bars[B_FREE]);
       ++n;
     };
-    // X tile loader: thread -> (row tid / XT, XF features), XT threads per row
-    constexpr int XT = N_EPI / TILE, XF = D0 / XT;      // 2 threads per row, 16 features each
-    const int xr = tid / XT, xh = tid % XT;
-    float4 xv[XF / 4];
-    float yv = 0.f;
-    auto x_issue = [&](size_t tile) {
-      const size_t row0 = tile * TILE;
-      const bool in = row0 + xr < n_rows;
-      const float* src = X + (row0 + xr) * (size_t)D0 + xh * XF;
-#pragma unroll
-      for (int i = 0; i < XF / 4; ++i) xv[i] = in ? __ldcs(reinterpret_cast<const float4*>(src + i * 4)) : make_float4(0.f, 0.f, 0.f, 0.f);
-      if (tid < TILE) yv = (row0 + tid < n_rows) ? __ldcs(y + row0 + tid) : 0.f;
-    };
     auto x_store = [&](int j) {
       // pin the fp32 -> fp16 conversion HERE: hoisted to x_issue it would make the loads blocking (a DRAM latency per tile)
 #pragma unroll
@@ -401,7 +412,7 @@ mlp_tc_kernel(const int loss_kind, const float* __restrict__ params, const float
       warp_arrive(lane, &bars[B_X0 + j]);
     };
     if (my_tiles > 0) {
-      x_issue(pair);
+      if (!early_x) x_issue(pair, X, y);
       x_store(0);
     }
     for (int it = 0; it < my_tiles; ++it) {
@@ -433,7 +444,7 @@ mlp_tc_kernel(const int loss_kind, const float* __restrict__ params, const float
       TRACE_E(21);
       // next tile's rows: loads issued here (the warps are about to wait for Z2h), converted and stored at the start of
       // phase (d), where they wait for dH1p.  The other X buffer was last read by tile it-1's dW1 (waited for in (b)).
-      if (it + 1 < my_tiles) x_issue(tile + n_pairs);
+      if (it + 1 < my_tiles) x_issue(tile + n_pairs, X, y);
       // ---- (c) Z2h: partial output dot, exchange, dZ2h -> sDZ2 ---------------------------------------
       TRACE_E(22);
       const int buf = it & 1;
@@ -562,19 +573,18 @@ mlp_tc_kernel(const int loss_kind, const float* __restrict__ params, const float
       ok = mbar_wait(&bars[B_ALL], 0) && ok;
       fence_after();
       TRACE_E(31);
-      constexpr int DC = 128 / CSPLIT;                    // dW2 columns per thread and M half
+      constexpr int DC = 128 / CSPLIT;                    // H1 units (accumulator columns) per thread and half
 #pragma unroll 1
       for (int mh = 0; mh < 2; ++mh) {
-        float* dst = my + W2_OFF + (size_t)(mh * 128 + row) * D2 + rank * 128 + hh * DC;   // row in = mh*128+row
+        // accumulator: lane = layer-2 unit (row), column = H1 unit k  ->  W2[k][rank*128 + row]
+        float* dst = my + W2_OFF + (size_t)(mh * 128 + hh * DC) * D2 + rank * 128 + row;
 #pragma unroll 1
         for (int c0 = 0; c0 < DC; c0 += 32) {
           uint32_t v[32];
           tmem_ld32(tm + TM_DW2 + mh * 128 + lane_base + hh * DC + c0, v);
           tmem_ld_wait();
 #pragma unroll
-          for (int i = 0; i < 8; ++i)
-            *reinterpret_cast<float4*>(dst + c0 + i * 4) = make_float4(__uint_as_float(v[i * 4]), __uint_as_float(v[i * 4 + 1]),
-                                                                       __uint_as_float(v[i * 4 + 2]), __uint_as_float(v[i * 4 + 3]));
+          for (int i = 0; i < 32; ++i) dst[(size_t)(c0 + i) * D2] = __uint_as_float(v[i]);
         }
         // dW1p^T: lane = h1 unit, column = input feature; column 32 = db1
         const int h1 = mh * 128 + row;

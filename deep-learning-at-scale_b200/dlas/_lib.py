@@ -8,7 +8,8 @@ import ctypes as C
 import os
 
 _HERE = os.path.dirname(os.path.abspath(__file__))
-LIB_PATH = os.path.join(os.path.dirname(_HERE), "lib", "libdlas_b200.so")
+# DLAS_B200_LIB: debugging only (tools/tc_trace.py points it at the library built with `build.py --trace`)
+LIB_PATH = os.environ.get("DLAS_B200_LIB") or os.path.join(os.path.dirname(_HERE), "lib", "libdlas_b200.so")
 
 LOSS_MSE, LOSS_MAE_CLIP = 0, 1
 OPT_SGD, OPT_ADAM = 0, 1

@@ -3,7 +3,9 @@ phase breakdown of CTA 0 (epilogue thread 0 and the MMA issuer)."""
 import os
 import sys
 
-sys.path.insert(0, os.path.join(os.path.dirname(os.path.abspath(__file__)), "..", "deep-learning-at-scale_b200"))
+PKG = os.path.join(os.path.dirname(os.path.abspath(__file__)), "..", "deep-learning-at-scale_b200")
+sys.path.insert(0, PKG)
+os.environ["DLAS_B200_LIB"] = os.path.join(PKG, "lib", "libdlas_b200_trace.so")   # python deep-learning-at-scale_b200/build.py --trace
 import torch  # noqa: E402
 import dlas  # noqa: E402
 from dlas import ops  # noqa: E402

@@ -132,10 +132,32 @@ def reference_arm(args, rank):
                              "sample": "%d steps of %d rows, torch-CPU fp32 port of the step (Spark/Keras unavailable)" % (args.steps, rows)},
             "e2e": {"value": rate, "unit": "samples/s", "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0},
             "gpu_launches": 0}
-    print(json.dumps(line), flush=True)
+    emit(line)
+
+
+_REAL_STDOUT = None
+
+
+def claim_stdout():
+    """stdout carries exactly ONE JSON line: library banners written to fd 1 (NCCL prints its version there) are
+    sent to stderr for the rest of the run; emit() writes the line to the real stdout."""
+    global _REAL_STDOUT
+    if _REAL_STDOUT is None:
+        sys.stdout.flush()
+        _REAL_STDOUT = os.dup(1)
+        os.dup2(2, 1)
+
+
+def emit(line):
+    data = (json.dumps(line) + "\n").encode()
+    if _REAL_STDOUT is None:
+        sys.stdout.write(data.decode()); sys.stdout.flush()
+    else:
+        os.write(_REAL_STDOUT, data)
 
 
 def main():
+    claim_stdout()
     ap = argparse.ArgumentParser()
     ap.add_argument("--gpus", type=int, default=1)
     ap.add_argument("--steps", type=int, default=200)
@@ -346,7 +368,8 @@ def main():
         tfs = TRAIN_FLOP_PER_SAMPLE * B / kern_s / 1e12
         # my kernels per step: fp32 mode transpose + forward/backward + reduce + update; tc mode forward/backward +
         # (reduce fused with the update) at N=1, forward/backward + reduce + update at N>1 (NCCL's kernel not counted)
-        launches_per_step = (4 if mode == "fp32" else 2) if N == 1 else (5 if mode == "fp32" else 4)   # N>1: + update + cursor advance
+        # tc mode: forward/backward + one finishing kernel (reduce [+ NVLink push/poll exchange] + update [+ cursor advance]) at any N
+        launches_per_step = (4 if mode == "fp32" else 2) if N == 1 else (5 if mode == "fp32" else 2)
         line = {
             "metric": "static_ann_train_samples_per_s", "value": value, "unit": "samples/s", "n_gpus": N, "steps": K,
             "warmup": W, "ms_per_step": ms / K, "higher_is_better": True, "scaling": "weak", "vs_baseline": None,
@@ -377,7 +400,7 @@ def main():
             line["cpu_baseline"] = {"value": rate, "unit": "samples/s", "cores": thr, "kind": "port",
                                     "sample": "%d steps of %d rows (%.1f s) of the same 32-256-256-1 step, torch-CPU fp32 port; "
                                               "Spark local[*]/Keras unavailable on this box" % (n_steps, rows, dt)}
-        print(json.dumps(line), flush=True)
+        emit(line)
     if N > 1:
         # captured NCCL work keeps communicator resources alive: leave without the collective teardown
         del stepper

@@ -24,6 +24,11 @@ int tc_grad(const int* dims, int n_layers, int loss, const float* params, const 
 int tc_fit_step(const int* dims, int n_layers, int loss, const dlas_opt_cfg* cfg, float* params, float* m, float* v,
                 const float* X, const float* y, size_t n_rows, uint64_t iteration, float* loss_out, void* workspace,
                 size_t workspace_bytes, cudaStream_t st);
+size_t tc_dp_recv_words(int world);
+int tc_dp_step(const int* dims, int n_layers, int loss, const dlas_opt_cfg* cfg, float* params, float* m, float* v,
+               const float* X_base, const float* y_base, size_t batch_rows, dlas_step_state* state,
+               const uint64_t* recv_bases_dev, int rank, int world, float grad_scale, int64_t n_batches, float* loss_ring,
+               int64_t ring_len, void* workspace, size_t workspace_bytes, cudaStream_t st);
 
 namespace {
 int check_common(const char* fn, const int* dims, int n_layers, int loss, int mode) {
@@ -153,4 +158,25 @@ extern "C" int dlas_mlp_eval_loss(const int* dims, int n_layers, int loss, int m
   DLAS_REQUIRE(params && loss_sum && (n_rows == 0 || (X && y)), "dlas_mlp_eval_loss: null pointer");
   return simt_eval_loss(dims, n_layers, loss, params, X, y, n_rows, loss_sum, workspace, workspace_bytes,
                         (cudaStream_t)stream);
+}
+
+extern "C" size_t dlas_mlp_dp_recv_bytes(const int* dims, int n_layers, int mode, int world) {
+  if (!dims || mode != DLAS_MODE_TC || !tc_supported(dims, n_layers) || world < 1 || world > 8) return 0;
+  return tc_dp_recv_words(world) * 8;
+}
+
+extern "C" int dlas_mlp_dp_step_at(const int* dims, int n_layers, int loss, int mode, const dlas_opt_cfg* cfg, float* params,
+                                   float* m, float* v, const float* X_base, const float* y_base, size_t batch_rows,
+                                   dlas_step_state* state_dev, const uint64_t* recv_bases_dev, int rank, int world,
+                                   float grad_scale, int64_t n_batches, float* loss_ring, int64_t ring_len, void* workspace,
+                                   size_t workspace_bytes, void* stream) {
+  DLAS_CHECK_DEVICE();
+  int rc = check_common("dlas_mlp_dp_step_at", dims, n_layers, loss, mode);
+  if (rc != DLAS_OK) return rc;
+  if (mode != DLAS_MODE_TC) {
+    set_error("dlas_mlp_dp_step_at: DLAS_MODE_TC only (fp32 mode: dlas_mlp_grad_at -> dlas_dp_allreduce_update -> dlas_step_advance)");
+    return DLAS_ERR_UNSUPPORTED_SHAPE;
+  }
+  return tc_dp_step(dims, n_layers, loss, cfg, params, m, v, X_base, y_base, batch_rows, state_dev, recv_bases_dev, rank, world,
+                    grad_scale, n_batches, loss_ring, ring_len, workspace, workspace_bytes, (cudaStream_t)stream);
 }

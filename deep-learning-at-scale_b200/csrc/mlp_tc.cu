@@ -33,6 +33,7 @@
 #include "common.cuh"
 #include "optim_math.cuh"
 #include "tc_common.cuh"
+#include <math.h>
 #include <stdlib.h>
 
 namespace dlas {
@@ -640,22 +641,71 @@ mlp_tc_kernel(const int loss_kind, const float* __restrict__ params, const float
 // grad_sum[i] = sum of the partials of the CTAs that own entry i, in CTA order:
 //   W1, b1: every active CTA (each holds a partial);  W2[:, c], b2[c], w3[c]: CTAs of rank c/128;
 //   b3 and the loss sum: rank-0 CTAs.
-// With FUSE_OPT the optimiser update of entry i is applied in the same pass (single-GPU step: no
-// all-reduce sits between the gradient and the update), and the batch-mean loss goes to *loss_out.
+// FIN_GRAD:     the sums go to `out` (dlas_mlp_grad; a collective of the caller follows).
+// FIN_UPDATE:   the optimiser update of entry i is applied in the same pass (single-GPU step: no all-reduce sits
+//               between the gradient and the update), and the batch-mean loss goes to *loss_out.
+// FIN_EXCHANGE: data-parallel step over NVLink peer memory.  Every block PUSHES its 64 sums into every peer's receive
+//               buffer as 8-byte {value, epoch} words (epoch = iteration + 1; an aligned 8-byte store arrives whole), then
+//               polls ITS OWN receive buffer -- local memory -- until the peers' words of this epoch are there, adds the
+//               `world` values in rank order (same bits on every rank), applies the update, and the last block to finish
+//               advances the device-resident cursor and iteration.  One NVLink one-way latency per step, no flags, no
+//               separate all-reduce / update / advance kernels.  Receive buffer of a rank: [2 parities][world sources]
+//               [recv_stride words]; parity = iteration & 1, so a rank one step ahead never overwrites words still being
+//               read (it cannot get two steps ahead: it needs this rank's next words first).
+enum { FIN_GRAD = 0, FIN_UPDATE = 1, FIN_EXCHANGE = 2 };
+struct FinDp {
+  const unsigned long long* recv_bases;   // device array: address of every rank's receive buffer as mapped HERE
+  int rank, world;
+  size_t recv_stride;                     // 8-byte words per (parity, source)
+  dlas_opt_cfg cfg;
+  dlas_step_state* state;
+  long long n_batches;
+  float* loss_ring;
+  long long ring_len;
+};
+__device__ unsigned g_fin_done = 0;       // blocks of the current FIN_EXCHANGE launch that have finished (reset by the last)
+
+__device__ __forceinline__ void st_push(unsigned long long addr, float v, unsigned epoch) {
+  asm volatile("st.relaxed.sys.global.v2.b32 [%0], {%1, %2};" ::"l"(addr), "r"(__float_as_uint(v)), "r"(epoch) : "memory");
+}
+__device__ __forceinline__ uint2 ld_poll(unsigned long long addr) {
+  uint2 r;
+  asm volatile("ld.relaxed.sys.global.v2.b32 {%0, %1}, [%2];" : "=r"(r.x), "=r"(r.y) : "l"(addr) : "memory");
+  return r;
+}
+
 constexpr int RG = 4;   // thread groups per block of 64 entries (8 measured no faster)
-template <bool FUSE_OPT>
-__global__ void __launch_bounds__(64 * RG)
+constexpr int FIN_MAXW = 8;
+template <int MODE>
+__global__ void __launch_bounds__(64 * RG, 8)   // 8 blocks per SM: the whole grid is resident
 tc_reduce_kernel(const float* __restrict__ partials, int n_active_pairs, const unsigned* __restrict__ err_flag,
                  unsigned call_id, float* __restrict__ out, OptScalars opt, float grad_scale, float* __restrict__ params,
                  float* __restrict__ m, float* __restrict__ v, float* __restrict__ loss_out,
-                 const long long* __restrict__ state, size_t parity_stride) {
+                 const long long* __restrict__ state, size_t parity_stride, const FinDp dp) {
   // 64 consecutive entries per block; the list of contributing CTAs is cut into RG contiguous parts summed by RG
   // thread groups (more loads in flight: the pass is latency-bound), then added in quarter order -> still deterministic
   __shared__ float red[RG - 1][64];
+  __shared__ OptScalars o_dev;
+  __shared__ int failed;
   asm volatile("griddepcontrol.launch_dependents;" ::: "memory");   // next gradient kernel: set-up may overlap this pass
   asm volatile("griddepcontrol.wait;" ::: "memory");   // the gradient kernel has completed; its partials are visible
   const int i = blockIdx.x * 64 + (threadIdx.x & 63), grp = threadIdx.x >> 6;
   const bool live = i <= N_PARAMS;
+  long long it = 0, cur = 0;
+  if (MODE == FIN_EXCHANGE) {
+    it = __ldcg(&dp.state->iteration);
+    cur = __ldcg(&dp.state->cursor);
+    if (threadIdx.x == 0) {   // step-dependent scalars from the device-resident iteration (as opt_at_kernel, optim.cu)
+      double lr_t = (double)dp.cfg.lr / (1.0 + (double)dp.cfg.decay * (double)it);
+      if (dp.cfg.kind == DLAS_OPT_ADAM) {
+        const double t = (double)it + 1.0;
+        lr_t = lr_t * sqrt(1.0 - pow((double)dp.cfg.beta2, t)) / (1.0 - pow((double)dp.cfg.beta1, t));
+      }
+      o_dev.kind = dp.cfg.kind; o_dev.lr_t = (float)lr_t; o_dev.momentum = dp.cfg.momentum; o_dev.nesterov = dp.cfg.nesterov;
+      o_dev.beta1 = dp.cfg.beta1; o_dev.beta2 = dp.cfg.beta2; o_dev.eps = dp.cfg.eps;
+      failed = 0;
+    }
+  }
   int first = 0, step = 1;
   if (i >= W2_OFF && i < B2_OFF) { first = ((i - W2_OFF) % D2) / 128; step = 2; }
   else if (i >= B2_OFF && i < W3_OFF) { first = (i - B2_OFF) / 128; step = 2; }
@@ -670,14 +720,17 @@ tc_reduce_kernel(const float* __restrict__ partials, int n_active_pairs, const u
   }
   if (grp > 0) red[grp - 1][threadIdx.x & 63] = s;
   __syncthreads();
-  if (grp > 0 || !live) return;
+  if (grp == 0 && live) {
 #pragma unroll
-  for (int g2 = 0; g2 < RG - 1; ++g2) s += red[g2][threadIdx.x];
-  // an mbarrier wait timed out inside this call's tcgen05 kernel: fail loudly, never return numbers
-  if (*err_flag == call_id) s = __int_as_float(0x7fc00000);
-  if (out) out[(state && (state[1] & 1)) ? parity_stride + i : i] = s;   // state[1] = iteration: double-buffered bucket
-  if (FUSE_OPT) {
-    if (i == N_PARAMS) {
+    for (int g2 = 0; g2 < RG - 1; ++g2) s += red[g2][threadIdx.x];
+    // an mbarrier wait timed out inside this call's tcgen05 kernel: fail loudly, never return numbers
+    if (*err_flag == call_id) s = __int_as_float(0x7fc00000);
+  }
+  if (MODE != FIN_EXCHANGE) {
+    if (grp > 0 || !live) return;
+    if (MODE == FIN_GRAD) {
+      out[(state && (state[1] & 1)) ? parity_stride + i : i] = s;   // state[1] = iteration: double-buffered bucket
+    } else if (i == N_PARAMS) {
       if (loss_out) *loss_out = s * grad_scale;
     } else {
       float p = params[i], mi = m[i], vi = (opt.kind == 0) ? 0.f : v[i];
@@ -685,6 +738,59 @@ tc_reduce_kernel(const float* __restrict__ partials, int n_active_pairs, const u
       params[i] = p;
       m[i] = mi;
       if (opt.kind != 0) v[i] = vi;
+    }
+    return;
+  }
+  // ---- FIN_EXCHANGE -------------------------------------------------------------------------------------------
+  if (grp == 0 && live) {
+    const unsigned epoch = (unsigned)(it + 1);
+    const size_t slot = (size_t)(it & 1) * dp.world * dp.recv_stride + (size_t)i;   // + source * recv_stride
+    // push my sum into every peer's buffer, at source index = my rank (64 threads x 8 bytes: one 512-byte row per peer)
+    for (int r = 0; r < dp.world; ++r)
+      if (r != dp.rank) st_push(dp.recv_bases[r] + (slot + (size_t)dp.rank * dp.recv_stride) * 8, s, epoch);
+    // collect the peers' sums from my own buffer; every load first, spinning only on words that have not arrived
+    float q[FIN_MAXW];
+    const unsigned long long mine = dp.recv_bases[dp.rank];
+    bool ok = true;
+#pragma unroll
+    for (int r = 0; r < FIN_MAXW; ++r) {
+      q[r] = 0.f;
+      if (r < dp.world && r != dp.rank) {
+        const unsigned long long a = mine + (slot + (size_t)r * dp.recv_stride) * 8;
+        uint2 w = ld_poll(a);
+        for (unsigned spin = 0; w.y != epoch && spin < (1u << 21); ++spin) {
+          __nanosleep(20);
+          w = ld_poll(a);
+        }
+        if (w.y != epoch) ok = false;
+        q[r] = __uint_as_float(w.x);
+      } else if (r == dp.rank) {
+        q[r] = s;
+      }
+    }
+    if (!ok) failed = 1;
+    float sum = 0.f;
+#pragma unroll
+    for (int r = 0; r < FIN_MAXW; ++r) sum += q[r];          // rank order: bit-identical on every rank (absent ranks add +0)
+    if (!ok) sum = __int_as_float(0x7fc00000);
+    if (i == N_PARAMS) {
+      if (dp.loss_ring) dp.loss_ring[it % dp.ring_len] = sum * grad_scale;
+    } else {
+      float p = params[i], mi = m[i], vi = (o_dev.kind == 0) ? 0.f : v[i];
+      opt_update(o_dev, sum * grad_scale, p, mi, vi);
+      params[i] = p;
+      m[i] = mi;
+      if (o_dev.kind != 0) v[i] = vi;
+    }
+  }
+  // the last block to finish moves the cursor: every block has read the state by then
+  __syncthreads();
+  if (threadIdx.x == 0) {
+    __threadfence();
+    if (atomicAdd(&g_fin_done, 1u) == gridDim.x - 1) {
+      g_fin_done = 0;
+      dp.state->cursor = (cur + 1) % dp.n_batches;
+      dp.state->iteration = it + 1;
     }
   }
 }
@@ -752,10 +858,10 @@ int launch_main(int loss, const float* params, const float* X, const float* y, s
   return DLAS_OK;
 }
 
-template <bool FUSE>
+template <int MODE>
 int launch_reduce(cudaStream_t st, const float* partials, int nap, const unsigned* err, float* out, OptScalars o,
                   float grad_scale, float* params, float* m, float* v, float* loss_out, const long long* state = nullptr,
-                  size_t parity_stride = 0) {
+                  size_t parity_stride = 0, const FinDp& dp = FinDp{}) {
   cudaLaunchConfig_t cfg = {};
   cfg.gridDim = dim3((N_PARAMS + 1 + 63) / 64);
   cfg.blockDim = dim3(64 * RG);
@@ -765,8 +871,8 @@ int launch_reduce(cudaStream_t st, const float* partials, int nap, const unsigne
   at[0].val.programmaticStreamSerializationAllowed = 1;
   cfg.attrs = at;
   cfg.numAttrs = 1;
-  DLAS_CUDA(cudaLaunchKernelEx(&cfg, tc_reduce_kernel<FUSE>, partials, nap, err, g_call_id, out, o, grad_scale, params, m, v,
-                               loss_out, state, parity_stride));
+  DLAS_CUDA(cudaLaunchKernelEx(&cfg, tc_reduce_kernel<MODE>, partials, nap, err, g_call_id, out, o, grad_scale, params, m, v,
+                               loss_out, state, parity_stride, dp));
   return DLAS_OK;
 }
 
@@ -799,7 +905,7 @@ int tc_grad(const int* dims, int n_layers, int loss, const float* params, const 
   float* partials; unsigned* err; int nap;
   int rc = launch_main(loss, params, X, y, n_rows, workspace, workspace_bytes, st, &partials, &err, &nap, cursor);
   if (rc != DLAS_OK) return rc;
-  rc = launch_reduce<false>(st, partials, nap, err, grad_sum, OptScalars{}, 0.f, nullptr, nullptr, nullptr, nullptr,
+  rc = launch_reduce<FIN_GRAD>(st, partials, nap, err, grad_sum, OptScalars{}, 0.f, nullptr, nullptr, nullptr, nullptr,
                             parity_stride ? cursor : nullptr, parity_stride);
   if (rc != DLAS_OK) return rc;
   return DLAS_OK;
@@ -820,9 +926,40 @@ int tc_fit_step(const int* dims, int n_layers, int loss, const dlas_opt_cfg* cfg
   float* partials; unsigned* err; int nap;
   rc = launch_main(loss, params, X, y, n_rows, workspace, workspace_bytes, st, &partials, &err, &nap);
   if (rc != DLAS_OK) return rc;
-  rc = launch_reduce<true>(st, partials, nap, err, nullptr, o, 1.0f / (float)n_rows, params, m, v, loss_out);
+  rc = launch_reduce<FIN_UPDATE>(st, partials, nap, err, nullptr, o, 1.0f / (float)n_rows, params, m, v, loss_out);
   if (rc != DLAS_OK) return rc;
   return DLAS_OK;
+}
+
+
+// one whole data-parallel step in two launches (forward/backward, then reduce + exchange + update + advance)
+size_t tc_dp_recv_words(int world) { return 2 * (size_t)world * (((size_t)N_PARAMS + 1 + 63) & ~(size_t)63); }
+int tc_dp_step(const int* dims, int n_layers, int loss, const dlas_opt_cfg* cfg, float* params, float* m, float* v,
+               const float* X_base, const float* y_base, size_t batch_rows, dlas_step_state* state,
+               const uint64_t* recv_bases_dev, int rank, int world, float grad_scale, int64_t n_batches, float* loss_ring,
+               int64_t ring_len, void* workspace, size_t workspace_bytes, cudaStream_t st) {
+  if (!tc_supported(dims, n_layers)) {
+    set_error("DLAS_MODE_TC supports the 32-256-256-1 network only");
+    return DLAS_ERR_UNSUPPORTED_SHAPE;
+  }
+  DLAS_REQUIRE(cfg && params && m && state && recv_bases_dev && batch_rows > 0 && n_batches >= 1, "dlas_mlp_dp_step_at: bad arguments");
+  DLAS_REQUIRE(cfg->kind == DLAS_OPT_SGD || (cfg->kind == DLAS_OPT_ADAM && v), "dlas_mlp_dp_step_at: bad optimiser / missing v");
+  DLAS_REQUIRE(world >= 1 && world <= FIN_MAXW && rank >= 0 && rank < world, "dlas_mlp_dp_step_at: rank %d / world %d", rank, world);
+  DLAS_REQUIRE(loss_ring == nullptr || ring_len >= 1, "dlas_mlp_dp_step_at: ring_len < 1");
+  float* partials; unsigned* err; int nap;
+  int rc = launch_main(loss, params, X_base, y_base, batch_rows, workspace, workspace_bytes, st, &partials, &err, &nap,
+                       reinterpret_cast<const long long*>(state));
+  if (rc != DLAS_OK) return rc;
+  FinDp dp;
+  dp.recv_bases = reinterpret_cast<const unsigned long long*>(recv_bases_dev);
+  dp.rank = rank; dp.world = world;
+  dp.recv_stride = ((size_t)N_PARAMS + 1 + 63) & ~(size_t)63;
+  dp.cfg = *cfg;
+  dp.state = state;
+  dp.n_batches = n_batches;
+  dp.loss_ring = loss_ring;
+  dp.ring_len = ring_len;
+  return launch_reduce<FIN_EXCHANGE>(st, partials, nap, err, nullptr, OptScalars{}, grad_scale, params, m, v, nullptr, nullptr, 0, dp);
 }
 
 }  // namespace dlas

@@ -28,7 +28,7 @@ class OptCfg(C.Structure):
                 ("nesterov", C.c_int32), ("beta1", C.c_float), ("beta2", C.c_float), ("eps", C.c_float)]
 
 
-_p, _sz, _u64, _i, _f = C.c_void_p, C.c_size_t, C.c_uint64, C.c_int, C.c_float
+_p, _sz, _u64, _i, _f, _i64 = C.c_void_p, C.c_size_t, C.c_uint64, C.c_int, C.c_float, C.c_int64
 _ip = C.POINTER(C.c_int)
 
 # name -> (restype, argtypes); every symbol include/dlas_b200.h declares
@@ -59,6 +59,8 @@ SIGNATURES = {
     "dlas_mlp_predict": (_i, [_ip, _i, _i, _p, _p, _sz, _p, _p]),
     "dlas_mlp_eval_loss": (_i, [_ip, _i, _i, _i, _p, _p, _p, _sz, _p, _p, _sz, _p]),
     "dlas_mlp_grad_noalloc": (_i, [_ip, _i, _i, _p, _p, _p, _sz, _p, _p]),
+    "dlas_mlp_dp_recv_bytes": (_sz, [_ip, _i, _i, _i]),
+    "dlas_mlp_dp_step_at": (_i, [_ip, _i, _i, _i, _p, _p, _p, _p, _p, _p, _sz, _p, _p, _i, _i, _f, _i64, _p, _i64, _p, _sz, _p]),
     "dlas_lstm_n_params": (_sz, [_i, _i, _i]),
     "dlas_lstm_workspace_bytes": (_sz, [_i, _i, _i, _i, _sz]),
     "dlas_lstm_grad": (_i, [_i, _i, _i, _i, _i, _p, _p, _p, _sz, _p, _p, _sz, _p]),

@@ -403,17 +403,25 @@ class Sequential:
         # peer=True: the all-reduce and the update are ONE kernel of ours over NVLink peer memory
         # (dlas_dp_allreduce_update); peer=False: NCCL all-reduce between our kernels; None: peer when world > 1
         # and the ranks' memory can be mapped, else NCCL
-        bucket = None
+        bucket, recv = None, None
         if self.world > 1 and peer is not False:
             try:
-                bucket = parallel.PeerBucket(self.n_params, self.device)
+                n_recv = ops.mlp_dp_recv_bytes(dims, self.mode, self.world)
+                if n_recv:      # tensor-core mode: forward/backward + ONE kernel for reduce, exchange, update and advance
+                    recv = parallel.PeerRecvBuffer(n_recv, self.device)
+                else:
+                    bucket = parallel.PeerBucket(self.n_params, self.device)
             except Exception as e:   # no symmetric-memory support between these GPUs: NCCL path (still no CPU path)
                 if peer:
                     raise
                 print("dlas: peer-memory bucket unavailable (%s); using the NCCL all-reduce" % (e,))
-        self.dp_path = "peer-kernel" if bucket is not None else ("nccl" if self.world > 1 else "single")
+        self.dp_path = "peer-push" if recv is not None else "peer-kernel" if bucket is not None else ("nccl" if self.world > 1 else "single")
 
         def one_step():
+            if recv is not None:
+                ops.mlp_dp_step_at(dims, self.loss, self.mode, self.cfg, self.params, self.m, self.v, X, Y, local_batch, state,
+                                   recv.bases, self.rank, self.world, 1.0 / rows, n_batches, ring, self.workspace)
+                return
             if bucket is not None:
                 ops.mlp_grad_at(dims, self.loss, self.mode, self.params, X, Y, local_batch, state, bucket.buf, self.workspace,
                                 parity_stride=bucket.parity_stride)
@@ -436,7 +444,7 @@ class Sequential:
             one_step()
         self.iterations += warmup_steps               # capture records the step, it does not run it
         st = GraphStepper(self, graph, state, ring)
-        st.bucket = bucket      # keeps the mapped memory alive as long as the graph
+        st.bucket = bucket if bucket is not None else recv      # keeps the mapped memory alive as long as the graph
         return st
 
     def fit_host(self, x_host, y_host, batch_size, n_steps, losses_host=None, first_batch=0):

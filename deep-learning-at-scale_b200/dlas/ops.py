@@ -221,6 +221,20 @@ def dp_allreduce_update(cfg, params, m, v, peer_bases, rank, world, parity_strid
                                                stream_ptr()))
 
 
+def mlp_dp_recv_bytes(dims, mode, world):
+    return int(_lib.load().dlas_mlp_dp_recv_bytes(int_array(dims), len(dims) - 1, int(mode), int(world)))
+
+
+def mlp_dp_step_at(dims, loss, mode, cfg, params, m, v, X_base, y_base, batch_rows, state, recv_bases, rank, world, grad_scale,
+                   n_batches, loss_ring, workspace):
+    """One whole data-parallel step (DLAS_MODE_TC): forward/backward kernel + the reduce/push/poll/update/advance kernel."""
+    check(_lib.load().dlas_mlp_dp_step_at(int_array(dims), len(dims) - 1, int(loss), int(mode), C.byref(cfg), ptr(params), ptr(m),
+                                          ptr(v), ptr(X_base), ptr(y_base), int(batch_rows), ptr(state), ptr(recv_bases),
+                                          int(rank), int(world), float(grad_scale), int(n_batches), ptr(loss_ring),
+                                          0 if loss_ring is None else loss_ring.numel(), ptr(workspace), workspace.numel(),
+                                          stream_ptr()))
+
+
 def opt_step_at(cfg, params, m, v, grad_sum, grad_scale, state, loss_ring=None):
     check(_lib.load().dlas_opt_step_at(C.byref(cfg), ptr(params), ptr(m), ptr(v), ptr(grad_sum), params.numel(),
                                        float(grad_scale), ptr(state), ptr(loss_ring),

@@ -44,7 +44,7 @@ else:
     st.run(steps - 3)
     torch.cuda.synchronize()
     got = st.recent_losses(steps)
-    assert model.dp_path == ("peer-kernel" if path == "peer" else "nccl"), model.dp_path
+    assert model.dp_path == (("peer-push" if mode == "tc" else "peer-kernel") if path == "peer" else "nccl"), model.dp_path
 if every:
     parallel.average_([model.params])          # the oracle reports the replica mean after the last step
 w = model.get_weights_flat()

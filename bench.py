@@ -208,12 +208,15 @@ def main():
     losses = torch.zeros(max(K, W), dtype=torch.float32, device="cuda")
 
     stepper = None
+    use_graph = N > 1 or os.environ.get("DLAS_BENCH_GRAPH") == "1"     # N == 1 default: eager launches from the host loop
+    if use_graph and N == 1:
+        stepper = model.graph_stepper(X, y, B, global_rows=B, warmup_steps=W, peer=True)
     if N > 1:
         # one captured step (gradient kernels, all-reduce, update, cursor advance) replayed K times: no per-step host work
         stepper = model.graph_stepper(X, y, B, global_rows=B * N, warmup_steps=W)
 
     def run_steps(n, first):
-        if N == 1:
+        if stepper is None:
             done = 0
             while done < n:     # sequential batches, wrapping at the end of the shard
                 fb = (first + done) % n_batches
@@ -240,14 +243,14 @@ def main():
         e1.record()
         barrier()
     ms = e0.elapsed_time(e1)
-    final_loss = float(losses[K - 1].item()) if N == 1 else None
+    final_loss = float(losses[K - 1].item()) if stepper is None else float(stepper.recent_losses(1)[0])
     # Kernel time for the roofline: a SECOND pass over the same kind of steps with CUDA events around every launch of
     # the forward/backward kernel on its own stream (dlas_prof_*).  Kept out of the pass above because an event between
     # two kernels breaks their programmatic-dependent-launch overlap and would tax `value`; kernels inside a replayed
     # graph (N>1) cannot carry events at all, so there the same kernel is launched eagerly on the same shapes.
     ops.prof_read(ops.PROF_MLP_GRAD)
     ops.prof_enable(True)
-    if N == 1:
+    if stepper is None:
         run_steps(K, W + K)
     else:
         for s_ in range(10):

@@ -27,8 +27,9 @@ int tc_fit_step(const int* dims, int n_layers, int loss, const dlas_opt_cfg* cfg
 size_t tc_dp_recv_words(int world);
 int tc_dp_step(const int* dims, int n_layers, int loss, const dlas_opt_cfg* cfg, float* params, float* m, float* v,
                const float* X_base, const float* y_base, size_t batch_rows, dlas_step_state* state,
-               const uint64_t* recv_bases_dev, int rank, int world, float grad_scale, int64_t n_batches, float* loss_ring,
-               int64_t ring_len, void* workspace, size_t workspace_bytes, cudaStream_t st);
+               int64_t cursor0, int64_t iteration0, const uint64_t* recv_bases_dev, int rank, int world, float grad_scale,
+               int64_t n_batches, float* loss_ring, int64_t ring_len, int64_t n_steps, void* workspace, size_t workspace_bytes,
+               cudaStream_t st);
 
 namespace {
 int check_common(const char* fn, const int* dims, int n_layers, int loss, int mode) {
@@ -167,9 +168,10 @@ extern "C" size_t dlas_mlp_dp_recv_bytes(const int* dims, int n_layers, int mode
 
 extern "C" int dlas_mlp_dp_step_at(const int* dims, int n_layers, int loss, int mode, const dlas_opt_cfg* cfg, float* params,
                                    float* m, float* v, const float* X_base, const float* y_base, size_t batch_rows,
-                                   dlas_step_state* state_dev, const uint64_t* recv_bases_dev, int rank, int world,
-                                   float grad_scale, int64_t n_batches, float* loss_ring, int64_t ring_len, void* workspace,
-                                   size_t workspace_bytes, void* stream) {
+                                   dlas_step_state* state_dev, int64_t cursor0, int64_t iteration0,
+                                   const uint64_t* recv_bases_dev, int rank, int world,
+                                   float grad_scale, int64_t n_batches, float* loss_ring, int64_t ring_len, int64_t n_steps,
+                                   void* workspace, size_t workspace_bytes, void* stream) {
   DLAS_CHECK_DEVICE();
   int rc = check_common("dlas_mlp_dp_step_at", dims, n_layers, loss, mode);
   if (rc != DLAS_OK) return rc;
@@ -177,6 +179,6 @@ extern "C" int dlas_mlp_dp_step_at(const int* dims, int n_layers, int loss, int 
     set_error("dlas_mlp_dp_step_at: DLAS_MODE_TC only (fp32 mode: dlas_mlp_grad_at -> dlas_dp_allreduce_update -> dlas_step_advance)");
     return DLAS_ERR_UNSUPPORTED_SHAPE;
   }
-  return tc_dp_step(dims, n_layers, loss, cfg, params, m, v, X_base, y_base, batch_rows, state_dev, recv_bases_dev, rank, world,
-                    grad_scale, n_batches, loss_ring, ring_len, workspace, workspace_bytes, (cudaStream_t)stream);
+  return tc_dp_step(dims, n_layers, loss, cfg, params, m, v, X_base, y_base, batch_rows, state_dev, cursor0, iteration0, recv_bases_dev, rank, world,
+                    grad_scale, n_batches, loss_ring, ring_len, n_steps, workspace, workspace_bytes, (cudaStream_t)stream);
 }

@@ -658,7 +658,8 @@ struct FinDp {
   int rank, world;
   size_t recv_stride;                     // 8-byte words per (parity, source)
   dlas_opt_cfg cfg;
-  dlas_step_state* state;
+  dlas_step_state* state;                 // device-resident cursor / iteration (graph replay), or NULL: host-driven step
+  long long it_host;                      //   ... whose iteration is this and whose scalars are the kernel's `opt` argument
   long long n_batches;
   float* loss_ring;
   long long ring_len;
@@ -692,7 +693,10 @@ tc_reduce_kernel(const float* __restrict__ partials, int n_active_pairs, const u
   const int i = blockIdx.x * 64 + (threadIdx.x & 63), grp = threadIdx.x >> 6;
   const bool live = i <= N_PARAMS;
   long long it = 0, cur = 0;
-  if (MODE == FIN_EXCHANGE) {
+  if (MODE == FIN_EXCHANGE && dp.state == nullptr) {
+    it = dp.it_host;
+    if (threadIdx.x == 0) { o_dev = opt; failed = 0; }
+  } else if (MODE == FIN_EXCHANGE) {
     it = __ldcg(&dp.state->iteration);
     cur = __ldcg(&dp.state->cursor);
     if (threadIdx.x == 0) {   // step-dependent scalars from the device-resident iteration (as opt_at_kernel, optim.cu)
@@ -784,6 +788,7 @@ tc_reduce_kernel(const float* __restrict__ partials, int n_active_pairs, const u
     }
   }
   // the last block to finish moves the cursor: every block has read the state by then
+  if (dp.state == nullptr) return;
   __syncthreads();
   if (threadIdx.x == 0) {
     __threadfence();
@@ -936,30 +941,49 @@ int tc_fit_step(const int* dims, int n_layers, int loss, const dlas_opt_cfg* cfg
 size_t tc_dp_recv_words(int world) { return 2 * (size_t)world * (((size_t)N_PARAMS + 1 + 63) & ~(size_t)63); }
 int tc_dp_step(const int* dims, int n_layers, int loss, const dlas_opt_cfg* cfg, float* params, float* m, float* v,
                const float* X_base, const float* y_base, size_t batch_rows, dlas_step_state* state,
-               const uint64_t* recv_bases_dev, int rank, int world, float grad_scale, int64_t n_batches, float* loss_ring,
-               int64_t ring_len, void* workspace, size_t workspace_bytes, cudaStream_t st) {
+               int64_t cursor0, int64_t iteration0, const uint64_t* recv_bases_dev, int rank, int world, float grad_scale,
+               int64_t n_batches, float* loss_ring, int64_t ring_len, int64_t n_steps, void* workspace, size_t workspace_bytes,
+               cudaStream_t st) {
   if (!tc_supported(dims, n_layers)) {
     set_error("DLAS_MODE_TC supports the 32-256-256-1 network only");
     return DLAS_ERR_UNSUPPORTED_SHAPE;
   }
-  DLAS_REQUIRE(cfg && params && m && state && recv_bases_dev && batch_rows > 0 && n_batches >= 1, "dlas_mlp_dp_step_at: bad arguments");
+  DLAS_REQUIRE(cfg && params && m && recv_bases_dev && batch_rows > 0 && n_batches >= 1, "dlas_mlp_dp_step_at: bad arguments");
+  DLAS_REQUIRE(state || (cursor0 >= 0 && cursor0 < n_batches && iteration0 >= 0), "dlas_mlp_dp_step_at: host-driven call needs cursor0 in [0, n_batches) and iteration0 >= 0");
   DLAS_REQUIRE(cfg->kind == DLAS_OPT_SGD || (cfg->kind == DLAS_OPT_ADAM && v), "dlas_mlp_dp_step_at: bad optimiser / missing v");
   DLAS_REQUIRE(world >= 1 && world <= FIN_MAXW && rank >= 0 && rank < world, "dlas_mlp_dp_step_at: rank %d / world %d", rank, world);
   DLAS_REQUIRE(loss_ring == nullptr || ring_len >= 1, "dlas_mlp_dp_step_at: ring_len < 1");
-  float* partials; unsigned* err; int nap;
-  int rc = launch_main(loss, params, X_base, y_base, batch_rows, workspace, workspace_bytes, st, &partials, &err, &nap,
-                       reinterpret_cast<const long long*>(state));
-  if (rc != DLAS_OK) return rc;
+  DLAS_REQUIRE(n_steps >= 0, "dlas_mlp_dp_step_at: n_steps < 0");
   FinDp dp;
   dp.recv_bases = reinterpret_cast<const unsigned long long*>(recv_bases_dev);
   dp.rank = rank; dp.world = world;
   dp.recv_stride = ((size_t)N_PARAMS + 1 + 63) & ~(size_t)63;
   dp.cfg = *cfg;
   dp.state = state;
+  dp.it_host = 0;
   dp.n_batches = n_batches;
   dp.loss_ring = loss_ring;
   dp.ring_len = ring_len;
-  return launch_reduce<FIN_EXCHANGE>(st, partials, nap, err, nullptr, OptScalars{}, grad_scale, params, m, v, nullptr, nullptr, 0, dp);
+  // the state lives on the device: every step is the same two launches, chained by programmatic dependent launch
+  for (int64_t s = 0; s < n_steps; ++s) {
+    float* partials; unsigned* err; int nap;
+    OptScalars o{};
+    const float* Xs = X_base; const float* ys = y_base;
+    if (!state) {   // host-driven: batch offset and step scalars computed here, exactly as dlas_mlp_fit_steps does
+      const size_t b = (size_t)((cursor0 + s) % n_batches);
+      Xs += b * batch_rows * D0;
+      ys += b * batch_rows;
+      dp.it_host = iteration0 + s;
+      int rc = make_opt_scalars(cfg, (uint64_t)dp.it_host, o);
+      if (rc != DLAS_OK) return rc;
+    }
+    int rc = launch_main(loss, params, Xs, ys, batch_rows, workspace, workspace_bytes, st, &partials, &err, &nap,
+                         reinterpret_cast<const long long*>(state));
+    if (rc != DLAS_OK) return rc;
+    rc = launch_reduce<FIN_EXCHANGE>(st, partials, nap, err, nullptr, o, grad_scale, params, m, v, nullptr, nullptr, 0, dp);
+    if (rc != DLAS_OK) return rc;
+  }
+  return DLAS_OK;
 }
 
 }  // namespace dlas

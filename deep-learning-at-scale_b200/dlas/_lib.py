@@ -60,7 +60,7 @@ SIGNATURES = {
     "dlas_mlp_eval_loss": (_i, [_ip, _i, _i, _i, _p, _p, _p, _sz, _p, _p, _sz, _p]),
     "dlas_mlp_grad_noalloc": (_i, [_ip, _i, _i, _p, _p, _p, _sz, _p, _p]),
     "dlas_mlp_dp_recv_bytes": (_sz, [_ip, _i, _i, _i]),
-    "dlas_mlp_dp_step_at": (_i, [_ip, _i, _i, _i, _p, _p, _p, _p, _p, _p, _sz, _p, _p, _i, _i, _f, _i64, _p, _i64, _p, _sz, _p]),
+    "dlas_mlp_dp_step_at": (_i, [_ip, _i, _i, _i, _p, _p, _p, _p, _p, _p, _sz, _p, _i64, _i64, _p, _i, _i, _f, _i64, _p, _i64, _i64, _p, _sz, _p]),
     "dlas_lstm_n_params": (_sz, [_i, _i, _i]),
     "dlas_lstm_workspace_bytes": (_sz, [_i, _i, _i, _i, _sz]),
     "dlas_lstm_grad": (_i, [_i, _i, _i, _i, _i, _p, _p, _p, _sz, _p, _p, _sz, _p]),

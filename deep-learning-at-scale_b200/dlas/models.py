@@ -109,19 +109,24 @@ class ModelCheckpoint:
 
 
 class GraphStepper:
-    """Replays a captured training step (Sequential.graph_stepper)."""
+    """Replays a captured training step (Sequential.graph_stepper) -- or, when the whole step is the library's two
+    launches with device-resident state (dlas_mlp_dp_step_at), enqueues n steps with ONE call and no graph: launches
+    chained by programmatic dependent launch overlap their prologues, which replays of a one-step graph do not."""
 
-    def __init__(self, model, graph, state, ring):
-        self.model, self.graph, self.state, self.ring = model, graph, state, ring
+    def __init__(self, model, graph, state, ring, enqueue=None):
+        self.model, self.graph, self.state, self.ring, self.enqueue = model, graph, state, ring, enqueue
 
     def run(self, n_steps):
-        for _ in range(n_steps):
-            self.graph.replay()
+        if self.enqueue is not None:
+            self.enqueue(n_steps)
+        else:
+            for _ in range(n_steps):
+                self.graph.replay()
         self.model.iterations += n_steps
 
     def recent_losses(self, n):
         """The batch-mean losses of the last n steps (device ring buffer -> host)."""
-        it = int(self.state[1].item())
+        it = int(self.state[1].item()) if self.state is not None else self.model.iterations
         idx = torch.arange(it - n, it, device=self.ring.device) % self.ring.numel()
         return self.ring[idx].cpu().numpy()
 
@@ -404,6 +409,8 @@ class Sequential:
         # (dlas_dp_allreduce_update); peer=False: NCCL all-reduce between our kernels; None: peer when world > 1
         # and the ranks' memory can be mapped, else NCCL
         bucket, recv = None, None
+        if self.world == 1 and peer and ops.mlp_dp_recv_bytes(dims, self.mode, 1):
+            recv = parallel.LocalRecvBuffer(ops.mlp_dp_recv_bytes(dims, self.mode, 1), self.device)   # same two launches, no peers
         if self.world > 1 and peer is not False:
             try:
                 n_recv = ops.mlp_dp_recv_bytes(dims, self.mode, self.world)
@@ -417,11 +424,22 @@ class Sequential:
                 print("dlas: peer-memory bucket unavailable (%s); using the NCCL all-reduce" % (e,))
         self.dp_path = "peer-push" if recv is not None else "peer-kernel" if bucket is not None else ("nccl" if self.world > 1 else "single")
 
+        if recv is not None:
+            # host-driven: nothing to capture, the step is two launches; the host only counts batches
+            it0 = self.iterations
+
+            def enqueue(n):
+                done = self.iterations - it0
+                ops.mlp_dp_step_at(dims, self.loss, self.mode, self.cfg, self.params, self.m, self.v, X, Y, local_batch, None,
+                                   recv.bases, self.rank, self.world, 1.0 / rows, n_batches, ring, self.workspace, n_steps=n,
+                                   cursor0=done % n_batches, iteration0=self.iterations)
+            enqueue(warmup_steps)
+            self.iterations += warmup_steps
+            st = GraphStepper(self, None, None, ring, enqueue)
+            st.bucket = recv        # keeps the mapped memory alive as long as the stepper
+            return st
+
         def one_step():
-            if recv is not None:
-                ops.mlp_dp_step_at(dims, self.loss, self.mode, self.cfg, self.params, self.m, self.v, X, Y, local_batch, state,
-                                   recv.bases, self.rank, self.world, 1.0 / rows, n_batches, ring, self.workspace)
-                return
             if bucket is not None:
                 ops.mlp_grad_at(dims, self.loss, self.mode, self.params, X, Y, local_batch, state, bucket.buf, self.workspace,
                                 parity_stride=bucket.parity_stride)
@@ -444,7 +462,7 @@ class Sequential:
             one_step()
         self.iterations += warmup_steps               # capture records the step, it does not run it
         st = GraphStepper(self, graph, state, ring)
-        st.bucket = bucket if bucket is not None else recv      # keeps the mapped memory alive as long as the graph
+        st.bucket = bucket      # keeps the mapped memory alive as long as the graph
         return st
 
     def fit_host(self, x_host, y_host, batch_size, n_steps, losses_host=None, first_batch=0):

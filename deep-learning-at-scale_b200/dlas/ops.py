@@ -226,13 +226,13 @@ def mlp_dp_recv_bytes(dims, mode, world):
 
 
 def mlp_dp_step_at(dims, loss, mode, cfg, params, m, v, X_base, y_base, batch_rows, state, recv_bases, rank, world, grad_scale,
-                   n_batches, loss_ring, workspace):
-    """One whole data-parallel step (DLAS_MODE_TC): forward/backward kernel + the reduce/push/poll/update/advance kernel."""
+                   n_batches, loss_ring, workspace, n_steps=1, cursor0=0, iteration0=0):
+    """n_steps whole data-parallel steps (DLAS_MODE_TC): forward/backward kernel + the reduce/push/poll/update/advance kernel."""
     check(_lib.load().dlas_mlp_dp_step_at(int_array(dims), len(dims) - 1, int(loss), int(mode), C.byref(cfg), ptr(params), ptr(m),
-                                          ptr(v), ptr(X_base), ptr(y_base), int(batch_rows), ptr(state), ptr(recv_bases),
-                                          int(rank), int(world), float(grad_scale), int(n_batches), ptr(loss_ring),
-                                          0 if loss_ring is None else loss_ring.numel(), ptr(workspace), workspace.numel(),
-                                          stream_ptr()))
+                                          ptr(v), ptr(X_base), ptr(y_base), int(batch_rows), ptr(state), int(cursor0),
+                                          int(iteration0), ptr(recv_bases), int(rank), int(world), float(grad_scale), int(n_batches), ptr(loss_ring),
+                                          0 if loss_ring is None else loss_ring.numel(), int(n_steps), ptr(workspace),
+                                          workspace.numel(), stream_ptr()))
 
 
 def opt_step_at(cfg, params, m, v, grad_sum, grad_scale, state, loss_ring=None):

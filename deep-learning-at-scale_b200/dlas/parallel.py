@@ -86,6 +86,15 @@ class PeerRecvBuffer:
         self.bases = torch.tensor([int(p) for p in self.handle.buffer_ptrs], dtype=torch.int64, device=device)
 
 
+class LocalRecvBuffer:
+    """world == 1: dlas_mlp_dp_step_at has nobody to exchange with; the buffer is ordinary device memory."""
+
+    def __init__(self, n_bytes, device):
+        self.rank, self.world = 0, 1
+        self.buf = torch.zeros(n_bytes // 4, dtype=torch.float32, device=device)
+        self.bases = torch.tensor([self.buf.data_ptr()], dtype=torch.int64, device=device)
+
+
 def average_(tensors):
     """In-place MEAN over ranks of each tensor (periodic parameter averaging).  NCCL averages inside the collective;
     gloo (CPU tests) has no AVG, so there the sum is divided on the host."""

@@ -156,23 +156,28 @@ int dlas_dp_allreduce_update(const dlas_opt_cfg* cfg, float* params, float* m, f
                              const dlas_step_state* state_dev, float* loss_ring, int64_t ring_len,
                              void* stream);
 
-/* The whole data-parallel step of DLAS_MODE_TC in TWO launches (no reference counterpart; same averaging semantics as
+/* n_steps whole data-parallel steps of DLAS_MODE_TC, TWO launches each (no reference counterpart; same averaging semantics as
  * dlas_dp_allreduce_update): the forward/backward kernel on rows [cursor*batch_rows, ...) of this rank's shard, then ONE
  * kernel that sums the per-CTA partials, PUSHES the sums into every peer's receive buffer as 8-byte {value, epoch}
  * words (epoch = iteration + 1), polls its own receive buffer until the peers' words of this epoch have arrived, adds
  * the `world` values in rank order (bit-identical on every rank), applies the optimiser update with
  * g = sum * grad_scale, writes the batch-mean loss to loss_ring[iteration % ring_len] and advances the state
  * (cursor = (cursor + 1) % n_batches, iteration += 1).  One NVLink one-way latency per step; no flags, no NCCL call,
- * no host work; replayable in a CUDA graph.  Every rank owns a receive buffer of dlas_mlp_dp_recv_bytes(...) bytes,
+ * the call only enqueues 2*n_steps launches chained by programmatic dependent launch.  With state_dev != NULL the
+ * cursor and iteration are read from (and advanced in) device memory, so the call can be captured in a CUDA graph and
+ * replayed; with state_dev == NULL the call is host-driven: step s works on batch (cursor0 + s) % n_batches with the
+ * schedule of iteration iteration0 + s (the forward/backward kernel then loads its first rows before the previous
+ * step has finished).  Every rank owns a receive buffer of dlas_mlp_dp_recv_bytes(...) bytes,
  * ZEROED once by the caller, in memory its peers can store to (CUDA IPC / VMM / symmetric memory);
  * recv_bases_dev[r] = the address under which THIS process reaches rank r's buffer.  A rank whose peers' words do not
  * arrive within a bounded spin writes NaN into its parameters and loss ring instead of hanging. */
 size_t dlas_mlp_dp_recv_bytes(const int* dims, int n_layers, int mode, int world);   /* 0: not supported */
 int dlas_mlp_dp_step_at(const int* dims, int n_layers, int loss, int mode, const dlas_opt_cfg* cfg, float* params,
                         float* m, float* v, const float* X_base, const float* y_base, size_t batch_rows,
-                        dlas_step_state* state_dev, const uint64_t* recv_bases_dev, int rank, int world,
-                        float grad_scale, int64_t n_batches, float* loss_ring, int64_t ring_len, void* workspace,
-                        size_t workspace_bytes, void* stream);
+                        dlas_step_state* state_dev, int64_t cursor0, int64_t iteration0,
+                        const uint64_t* recv_bases_dev, int rank, int world,
+                        float grad_scale, int64_t n_batches, float* loss_ring, int64_t ring_len, int64_t n_steps,
+                        void* workspace, size_t workspace_bytes, void* stream);
 
 /* n_steps consecutive single-GPU mini-batch steps (the `model.fit` inner loop, cnn.py:127-128):
  * step s uses rows [b*batch, (b+1)*batch) with b = batch_order_host ? batch_order_host[s]

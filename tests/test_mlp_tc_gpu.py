@@ -181,3 +181,57 @@ def test_bench_batch_32768_steps_vs_oracle(dl):
     print("batch 32768: max per-step loss rel err %.3g; weights rel err %.3g" % (np.abs(got / ref - 1).max(), _relerr(p.cpu().numpy(), pr)))
     np.testing.assert_allclose(got, ref, rtol=TOL)
     assert _relerr(p.cpu().numpy(), pr) < TOL
+
+
+@pytest.mark.parametrize("optname", ["sgd", "adam"])
+def test_dp_step_world_1_matches_fit_steps(dl, optname):
+    """dlas_mlp_dp_step_at with nobody to exchange with is the single-GPU step: the host-driven flavour repeats
+    dlas_mlp_fit_steps (same kernels, same host scalars; bit for bit with SGD); the device-state flavour (cursor and iteration
+    in device memory, learning-rate schedule derived on the device) agrees to fp32 rounding of the schedule, wraps
+    its cursor at n_batches and leaves the advanced state behind."""
+    from dlas import ops
+    batch, nb, steps = 2048, 4, 6                      # 6 steps over 4 batches: the cursor wraps
+    X, y = O.synth_rows(O.BASE_SEED, 0, batch * nb, 32)
+    Xd, yd = _cuda(X), _cuda(y)
+    p0 = O.glorot_init(DIMS, O.BASE_SEED)
+    cfg = (dl.Adam() if optname == "adam" else dl.SGD(lr=0.001, momentum=0.99, decay=1e-6, nesterov=True)).cfg()
+    ws = ops.mlp_workspace(DIMS, dl.MODE_TC)
+    it0 = 7                                            # not the first iteration: the schedule must use it
+
+    def fresh():
+        p = _cuda(p0)
+        return p, torch.zeros_like(p), torch.zeros_like(p)
+
+    # reference: the fit_steps loop over the same batch sequence
+    p, m, v = fresh()
+    gs = torch.zeros(p.numel() + 1, device="cuda")
+    ref_losses = torch.zeros(steps, device="cuda")
+    ops.mlp_fit_steps(DIMS, dl.LOSS_MSE, dl.MODE_TC, cfg, p, m, v, Xd, yd, batch, steps, it0, ref_losses, gs, ws,
+                      batch_order=[s % nb for s in range(steps)])
+    torch.cuda.synchronize()
+    n_recv = ops.mlp_dp_recv_bytes(DIMS, dl.MODE_TC, 1)
+    assert n_recv > 0 and ops.mlp_dp_recv_bytes([8, 64, 64, 1], dl.MODE_TC, 1) == 0
+    recv = torch.zeros(n_recv // 4, device="cuda")
+    bases = torch.tensor([recv.data_ptr()], dtype=torch.int64, device="cuda")
+    ring = torch.zeros(16, device="cuda")
+    # host-driven
+    p1, m1, v1 = fresh()
+    ops.mlp_dp_step_at(DIMS, dl.LOSS_MSE, dl.MODE_TC, cfg, p1, m1, v1, Xd, yd, batch, None, bases, 0, 1, 1.0 / batch, nb, ring, ws,
+                       n_steps=steps, cursor0=0, iteration0=it0)
+    torch.cuda.synchronize()
+    idx = [(it0 + s) % 16 for s in range(steps)]
+    if optname == "sgd":
+        assert torch.equal(p1, p) and torch.equal(m1, m) and torch.equal(ring[idx], ref_losses)
+    else:   # Adam's update is compiled into two kernels whose multiply-adds may be contracted differently: last-bit noise
+        assert _relerr(p1.cpu().numpy(), p.cpu().numpy().astype(np.float64)) < 1e-6
+        np.testing.assert_allclose(ring[idx].cpu().numpy(), ref_losses.cpu().numpy(), rtol=1e-6)
+    # device state
+    p2, m2, v2 = fresh()
+    state = torch.tensor([0, it0], dtype=torch.int64, device="cuda")
+    ring.zero_()
+    ops.mlp_dp_step_at(DIMS, dl.LOSS_MSE, dl.MODE_TC, cfg, p2, m2, v2, Xd, yd, batch, state, bases, 0, 1, 1.0 / batch, nb, ring, ws,
+                       n_steps=steps)
+    torch.cuda.synchronize()
+    assert state.tolist() == [steps % nb, it0 + steps]
+    assert _relerr(p2.cpu().numpy(), p.cpu().numpy().astype(np.float64)) < 1e-6
+    np.testing.assert_allclose(ring[idx].cpu().numpy(), ref_losses.cpu().numpy(), rtol=1e-6)

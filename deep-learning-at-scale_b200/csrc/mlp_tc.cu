@@ -664,6 +664,15 @@ struct FinDp {
   float* loss_ring;
   long long ring_len;
 };
+#ifdef DLAS_TC_TRACE
+// trace build: per step (ring of 64) globaltimer stamps of block 0 and the last block: after the dependency wait, after
+// the reduction + push, after the poll; read back by tools/fin_trace.py through dlas_debug_fin_trace
+__device__ unsigned long long g_fin_trace[64][2][4];
+__device__ __forceinline__ unsigned long long gtime() { unsigned long long t; asm volatile("mov.u64 %0, %%globaltimer;" : "=l"(t)); return t; }
+#define FIN_STAMP(k) do { if (threadIdx.x == 0 && (blockIdx.x == 0 || blockIdx.x == gridDim.x - 1)) g_fin_trace[it & 63][blockIdx.x ? 1 : 0][k] = gtime(); } while (0)
+#else
+#define FIN_STAMP(k) do { } while (0)
+#endif
 __device__ unsigned g_fin_done = 0;       // blocks of the current FIN_EXCHANGE launch that have finished (reset by the last)
 
 __device__ __forceinline__ void st_push(unsigned long long addr, float v, unsigned epoch) {
@@ -710,6 +719,7 @@ tc_reduce_kernel(const float* __restrict__ partials, int n_active_pairs, const u
       failed = 0;
     }
   }
+  if (MODE == FIN_EXCHANGE) FIN_STAMP(0);
   int first = 0, step = 1;
   if (i >= W2_OFF && i < B2_OFF) { first = ((i - W2_OFF) % D2) / 128; step = 2; }
   else if (i >= B2_OFF && i < W3_OFF) { first = (i - B2_OFF) / 128; step = 2; }
@@ -752,6 +762,7 @@ tc_reduce_kernel(const float* __restrict__ partials, int n_active_pairs, const u
     // push my sum into every peer's buffer, at source index = my rank (64 threads x 8 bytes: one 512-byte row per peer)
     for (int r = 0; r < dp.world; ++r)
       if (r != dp.rank) st_push(dp.recv_bases[r] + (slot + (size_t)dp.rank * dp.recv_stride) * 8, s, epoch);
+    FIN_STAMP(1);
     // collect the peers' sums from my own buffer; every load first, spinning only on words that have not arrived
     float q[FIN_MAXW];
     const unsigned long long mine = dp.recv_bases[dp.rank];
@@ -772,6 +783,7 @@ tc_reduce_kernel(const float* __restrict__ partials, int n_active_pairs, const u
         q[r] = s;
       }
     }
+    FIN_STAMP(2);
     if (!ok) failed = 1;
     float sum = 0.f;
 #pragma unroll
@@ -787,6 +799,7 @@ tc_reduce_kernel(const float* __restrict__ partials, int n_active_pairs, const u
       if (o_dev.kind != 0) v[i] = vi;
     }
   }
+  FIN_STAMP(3);
   // the last block to finish moves the cursor: every block has read the state by then
   if (dp.state == nullptr) return;
   __syncthreads();
@@ -987,3 +1000,9 @@ int tc_dp_step(const int* dims, int n_layers, int loss, const dlas_opt_cfg* cfg,
 }
 
 }  // namespace dlas
+
+#ifdef DLAS_TC_TRACE
+extern "C" int dlas_debug_fin_trace(unsigned long long* host64x2x4) {   // trace library only
+  return cudaMemcpyFromSymbol(host64x2x4, dlas::g_fin_trace, sizeof(unsigned long long) * 64 * 2 * 4) == cudaSuccess ? 0 : -2;
+}
+#endif

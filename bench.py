@@ -341,6 +341,19 @@ def main():
             e1.record()
             torch.cuda.synchronize()
             return e0.elapsed_time(e1) * 1e-3 / n
+        # the headline network at other batch sizes: what each launch's fixed cost (weights -> fp16 tiles, accumulator drain,
+        # partial reduction + update) weighs against the per-tile work
+        if mode == "tc":
+            sweep = {}
+            ns = 20
+            Xw, yw = ops.synth_rows(1048576 * ns, DIMS[0])        # 2.8 GB: every step of a sweep point reads new rows
+            ls = torch.zeros(ns, device="cuda")
+            for rows_b in (16384, 262144, 1048576):
+                t = timed(lambda: ops.mlp_fit_steps(DIMS, model.loss, model.mode, model.cfg, model.params, model.m, model.v, Xw, yw,
+                                                    rows_b, ns, 0, ls, model.grad_sum, model.workspace), 2)
+                sweep[str(rows_b)] = {"samples_per_s": rows_b * ns / t, "us_per_step": t / ns * 1e6}
+            extras["static_ann_32_256_256_1_rows_per_step_sweep"] = sweep
+            del Xw, yw
         # dynamic ANN (config 4): 24 lags x 8 features -> 192-256-256-1, fp32 kernel, 65,536 windows per step
         dd = [192, 256, 256, 1]
         series, ys = ops.synth_rows(65536 + 23, 8)

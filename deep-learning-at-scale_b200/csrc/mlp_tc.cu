@@ -18,18 +18,25 @@
 // MMA floor per 128-row tile per CTA: 3584 cycles (256 + 1024 + 1024 + 1024 + 256), 93 % of the
 // 6680 SM-cycles the unsplit network needs per tile.
 //
-// Warp roles (288 threads): warps 0-7 epilogue (warp w: TMEM lane quarter w%4 = rows, column half
-// w/4 of each 64-column chunk), warp 8 = MMA issuer.  Every GEMM whose result feeds an epilogue is
-// cut into N=64 chunks that alternate between two 64-column TMEM work buffers, so the epilogue of
-// chunk i runs under the MMA of chunk i+1; dW2 / db2 / dW1 accumulate in their own TMEM columns for
-// the whole launch and need no per-tile epilogue.  X tiles are double-buffered (tile t+1 is loaded
-// during tile t).  mbarriers: mma_done[b] (tcgen05.commit -> epilogue), buf_free[b] (epilogue ->
-// issuer), x_ready[j] / h1_ready / dz2_ready / dz1_ready (operands in smem -> issuer).
+// Warp roles (384 threads): warps 0-7 epilogue (warp w: TMEM lane quarter w%4 = rows, column half w/4 of every
+// 128-column chunk, 64 columns per thread), warp 8 = MMA issuer, warps 9-11 idle: they complete the issuer's
+// warpgroup so that setmaxnreg can move its registers to the epilogue warps (104 / 200 per thread), which keep Z2h,
+// the dw3 accumulators and a prefetched block of constants in registers.  Z1 and dH1p are produced as two N=128
+// halves through ONE 128-column TMEM work buffer (mbarrier waits cost ~140 cycles each whatever their state --
+// tools/mbar_lat.cu -- so fewer, larger hand-overs win over double-buffered N=64 chunks); the issuer interleaves
+//   Z1 half 1 | Z2h (first K half as soon as H1 columns 0..127 are stored) | dH1p half 0 | dW2^T half 0 | dH1p half 1 |
+//   dW2^T half 1 | db2 | dW1 half 0 | next tile's Z1 half 0 | dW1 half 1
+// so that the epilogue of one piece runs under the MMAs of the next.  dW2^T / db2 / dW1^T accumulate in their own TMEM
+// columns for the whole launch (dW2 transposed: lane = layer-2 unit, so the drain stores 128 contiguous bytes per
+// instruction).  X tiles are double-buffered; their loads are issued where the epilogue warps are about to wait.
+// mbarriers: B_DONE (tcgen05.commit -> epilogue), B_FREE (work buffer read -> issuer), B_X*, B_H1A/B_H1, B_DZ2,
+// B_DW2A/B (H1 half may be overwritten), B_DZ1A/B_DZ1, B_DW1, B_XC* (pair exchange).
+// The step is finished by tc_reduce_kernel (below): per-CTA partials -> sums [-> NVLink push/poll exchange] -> update.
 //
 // Shared memory (fp16 tiles in the column-blocked SWIZZLE_128B layout of tc_common.cuh):
-//   sW1 [32][256] 16 KB | sW2 [256][128] 64 KB | sX[2] [128][64] 2x16 KB ([x | 1 | 0]) |
+//   sW1 [48][256] 24 KB ([W1; b1; 0]) | sW2 [256][128] 64 KB | sX[2] [128][64] 2x16 KB ([x | 1 | 0]) |
 //   sH1 [128][256] 64 KB (dZ1 overwrites it in place) | sDZ2 [128][128] 32 KB | ones [16][64] 2 KB | fp32 vectors
-// TMEM columns: [0,64) [64,128) work | [128,384) dW2 half | [384,432) [448,496) dW1^T halves | [496,512) db2
+// TMEM columns: [0,128) work | [128,384) dW2^T half | [384,432) [448,496) dW1^T halves | [496,512) db2
 #include "common.cuh"
 #include "optim_math.cuh"
 #include "tc_common.cuh"
@@ -145,8 +152,8 @@ mlp_tc_kernel(const int loss_kind, const float* __restrict__ params, const float
   }
   if (warp == ISSUER_WARP) tmem_alloc(tmem_slot, TM_COLS);
   // X tile loader (epilogue threads): thread -> (row tid / XT, XF features), XT threads per row
-  constexpr int XT = N_EPI / TILE, XF = D0 / XT;      // 2 threads per row, 16 features each
-  const int xr = tid / XT, xh = tid % XT;
+  constexpr int XT = N_EPI / TILE, XF = D0 / XT;      // 2 threads per row, 16 features each; a warp covers 32 rows of one
+  const int xr = tid % TILE, xh = tid / TILE;         // half, so its 16-byte stores into the swizzled tile do not conflict
   float4 xv[XF / 4];
   float yv = 0.f;
   auto x_issue = [&](size_t tile, const float* __restrict__ X, const float* __restrict__ y) {
@@ -634,7 +641,9 @@ mlp_tc_kernel(const int loss_kind, const float* __restrict__ params, const float
   // ---- teardown ----------------------------------------------------------------------------------------
   fence_before();
   __syncthreads();
-  cluster_sync_all();   // do not exit while the peer may still write our exchange buffer
+  // do not exit while the peer may still write our exchange buffer.  Relaxed: a releasing arrive would first wait for the
+  // acknowledgement of the 160 KB of partials this CTA has just stored (12 % of all stall samples in ncu's source view)
+  cluster_sync_relaxed();
   if (warp == ISSUER_WARP) tmem_dealloc(tm, TM_COLS);
 }
 

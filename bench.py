@@ -56,22 +56,28 @@ class ClockSampler:
         except Exception:
             self.nv = None
 
+    NAMES = {"hw_slowdown": 0x8, "sw_power_cap": 0x4, "hw_thermal_slowdown": 0x40, "sw_thermal_slowdown": 0x20,
+             "hw_power_brake": 0x80, "sync_boost": 0x10, "applications_clocks_setting": 0x2}
+
     def _run(self):
-        nv = self.nv
-        names = {"hw_slowdown": 0x8, "sw_power_cap": 0x4, "hw_thermal_slowdown": 0x40, "sw_thermal_slowdown": 0x20,
-                 "hw_power_brake": 0x80, "sync_boost": 0x10, "applications_clocks_setting": 0x2}
         while not self._stop.is_set():
-            for h in self.hs:
-                try:
-                    self.samples.append(nv.nvmlDeviceGetClockInfo(h, nv.NVML_CLOCK_SM))
-                    r = nv.nvmlDeviceGetCurrentClocksEventReasons(h) if hasattr(nv, "nvmlDeviceGetCurrentClocksEventReasons") \
-                        else nv.nvmlDeviceGetCurrentClocksThrottleReasons(h)
-                    for k, bit in names.items():
-                        if r & bit:
-                            self.reasons.add(k)
-                except Exception:
-                    pass
+            self.sample_once()
             self._stop.wait(self.period)
+
+    def sample_once(self):
+        nv = self.nv
+        if not nv:
+            return
+        for h in self.hs:
+            try:
+                self.samples.append(nv.nvmlDeviceGetClockInfo(h, nv.NVML_CLOCK_SM))
+                r = nv.nvmlDeviceGetCurrentClocksEventReasons(h) if hasattr(nv, "nvmlDeviceGetCurrentClocksEventReasons") \
+                    else nv.nvmlDeviceGetCurrentClocksThrottleReasons(h)
+                for k, bit in self.NAMES.items():
+                    if r & bit:
+                        self.reasons.add(k)
+            except Exception:
+                pass
 
     def __enter__(self):
         if self.nv:
@@ -244,14 +250,29 @@ def main():
     run_steps(W, 0)
     barrier()
     e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
-    # rank 0 samples ITS OWN GPU only (measured at N=8: a sampler in every rank 99 us/step, rank 0 sampling all eight
-    # GPUs 94 us, no sampler 71 us; at N=1 the sampler costs 0.2 us/step)
-    sampled = [] if os.environ.get("DLAS_BENCH_NO_SAMPLER") == "1" else ([local_rank] if rank == 0 else [])
-    with ClockSampler(sampled, period=0.004) as clk:
+    # Clocks.  N = 1: NVML sampled every 4 ms while the timed region runs (cost measured: 0.2 us per step).  N > 1: NVML in
+    # rank 0's process slows the ranks' lock-step whenever it is used around the region (measured at N=8, us per step:
+    # NVML never initialised 71; one sample before + one after the region 115; rank 0 sampling its own GPU inside the
+    # region 93; rank 0 sampling all eight 94; a sampler in every rank 99).  So at N > 1 the timed pass runs with NVML
+    # untouched and reports the SM clock the forward/backward kernel measures itself INSIDE the region (clock64 /
+    # globaltimer, dlas_prof_sm_clock); NVML clock and throttle reasons are then sampled every 4 ms during a second,
+    # untimed pass of the same K steps right after it.
+    no_nvml = os.environ.get("DLAS_BENCH_NO_SAMPLER") == "1"
+    in_region = (N == 1) and not no_nvml
+    clk = ClockSampler([local_rank] if (in_region and rank == 0) else [], period=0.004)
+    if mode == "tc":
+        ops.prof_sm_clock(reset=True)
+    with clk:
         e0.record()
         run_steps(K, W)
         e1.record()
         barrier()
+    device_mhz = ops.prof_sm_clock(reset=True) if mode == "tc" else None
+    if N > 1 and not no_nvml:
+        clk = ClockSampler([local_rank] if rank == 0 else [], period=0.004)
+        with clk:
+            run_steps(K, W + K)
+            barrier()
     ms = e0.elapsed_time(e1)
     final_loss = float(losses[K - 1].item()) if stepper is None else float(stepper.recent_losses(1)[0])
     # Kernel time for the roofline: a SECOND pass over the same kind of steps with CUDA events around every launch of
@@ -414,7 +435,11 @@ def main():
                          "hbm_frac": BYTES_PER_SAMPLE * B / kern_s / 1e9 / pk["hbm"]},
             "e2e": {"value": e2e_value, "unit": "samples/s", "h2d_bytes_per_step": B * BYTES_PER_SAMPLE, "d2h_bytes_per_step": 4},
             "gpu_launches": launches_per_step * K,
-            "clocks": clk.summary(),
+            "clocks": dict(clk.summary(), sm_mhz_in_kernel=device_mhz,
+                           when=("NVML every 4 ms inside the timed region" if in_region else
+                                 "sm_mhz_in_kernel: measured by the forward/backward kernel inside the timed region; NVML "
+                                 "clock and reasons: every 4 ms during an identical untimed pass right after it (NVML "
+                                 "use around the timed region slows the ranks' lock-step, see bench.py)")),
             "other_models": extras,
             "gilbert": {"metric": "gilbert_rows_per_s", "rows": g_rows * N, "variant": int(best), **gil[best], "all_variants": gil},
         }

@@ -106,6 +106,16 @@ __device__ __forceinline__ uint4 pack8(float4 a, float4 b) {
   return make_uint4(pack_half2(a.x, a.y), pack_half2(a.z, a.w), pack_half2(b.x, b.y), pack_half2(b.z, b.w));
 }
 
+// SM clock as the kernel itself sees it (dlas_prof_sm_clock): CTA 0 adds its clock64 and globaltimer deltas of every
+// launch; the ratio of the sums is the average SM frequency while this kernel runs.  For the benchmark's clocks line at
+// N > 1, where NVML queries during the timed region were measured to stall the ranks' steps.
+__device__ unsigned long long g_clk_sum[2] = {0ull, 0ull};
+__device__ __forceinline__ unsigned long long globaltimer_ns() {
+  unsigned long long t;
+  asm volatile("mov.u64 %0, %%globaltimer;" : "=l"(t));
+  return t;
+}
+
 // Debug trace (library built with `build.py --trace`, run with DLAS_TC_TRACE=<file>): SM-clock stamps of CTA 0,
 // epilogue warp 0 (slots 0..), the issuer (slots 512..) and the last epilogue warp (slots 1024..)
 #ifdef DLAS_TC_TRACE
@@ -137,6 +147,9 @@ mlp_tc_kernel(const int loss_kind, const float* __restrict__ params, const float
   bool ok = (sbase & 1023u) == 0;   // the swizzled tile layout needs a 1024-byte aligned base
   int te = 0, tmm = 0;
   TRACE_E(1);
+  const bool clk_owner = (blockIdx.x == 0 && tid == 0);
+  const long long clk_c0 = clk_owner ? clock64() : 0;
+  const unsigned long long clk_g0 = clk_owner ? globaltimer_ns() : 0ull;
 
   // ---- one-time set-up: barriers, TMEM, weights -> fp16 tiles -------------------------------------------
   if (tid == 0) {
@@ -637,6 +650,10 @@ mlp_tc_kernel(const int loss_kind, const float* __restrict__ params, const float
   }
   TRACE_E(32);
   if (!ok && lane == 0) atomicExch(err_flag, call_id);
+  if (clk_owner) {   // one writer, launches are stream-ordered
+    g_clk_sum[0] += (unsigned long long)(clock64() - clk_c0);
+    g_clk_sum[1] += globaltimer_ns() - clk_g0;
+  }
 
   // ---- teardown ----------------------------------------------------------------------------------------
   fence_before();
@@ -1009,6 +1026,20 @@ int tc_dp_step(const int* dims, int n_layers, int loss, const dlas_opt_cfg* cfg,
 }
 
 }  // namespace dlas
+
+extern "C" int dlas_prof_sm_clock(double* mhz_host, int reset) {
+  using namespace dlas;
+  DLAS_CHECK_DEVICE();
+  unsigned long long h[2] = {0ull, 0ull};
+  DLAS_CUDA(cudaDeviceSynchronize());
+  DLAS_CUDA(cudaMemcpyFromSymbol(h, g_clk_sum, sizeof(h)));
+  if (mhz_host) *mhz_host = h[1] ? (double)h[0] / (double)h[1] * 1e3 : 0.0;
+  if (reset) {
+    const unsigned long long z[2] = {0ull, 0ull};
+    DLAS_CUDA(cudaMemcpyToSymbol(g_clk_sum, z, sizeof(z)));
+  }
+  return DLAS_OK;
+}
 
 #ifdef DLAS_TC_TRACE
 extern "C" int dlas_debug_fin_trace(unsigned long long* host64x2x4) {   // trace library only

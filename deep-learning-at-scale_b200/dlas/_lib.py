@@ -59,6 +59,7 @@ SIGNATURES = {
     "dlas_mlp_predict": (_i, [_ip, _i, _i, _p, _p, _sz, _p, _p]),
     "dlas_mlp_eval_loss": (_i, [_ip, _i, _i, _i, _p, _p, _p, _sz, _p, _p, _sz, _p]),
     "dlas_mlp_grad_noalloc": (_i, [_ip, _i, _i, _p, _p, _p, _sz, _p, _p]),
+    "dlas_prof_sm_clock": (_i, [C.POINTER(C.c_double), _i]),
     "dlas_mlp_dp_recv_bytes": (_sz, [_ip, _i, _i, _i]),
     "dlas_mlp_dp_step_at": (_i, [_ip, _i, _i, _i, _p, _p, _p, _p, _p, _p, _sz, _p, _i64, _i64, _p, _i, _i, _f, _i64, _p, _i64, _i64, _p, _sz, _p]),
     "dlas_lstm_n_params": (_sz, [_i, _i, _i]),

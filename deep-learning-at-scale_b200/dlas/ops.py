@@ -221,6 +221,13 @@ def dp_allreduce_update(cfg, params, m, v, peer_bases, rank, world, parity_strid
                                                stream_ptr()))
 
 
+def prof_sm_clock(reset=True):
+    """Average SM MHz seen by the tensor-core MLP kernel since the last reset (0.0 if it has not run)."""
+    mhz = C.c_double(0.0)
+    check(_lib.load().dlas_prof_sm_clock(C.byref(mhz), 1 if reset else 0))
+    return float(mhz.value)
+
+
 def mlp_dp_recv_bytes(dims, mode, world):
     return int(_lib.load().dlas_mlp_dp_recv_bytes(int_array(dims), len(dims) - 1, int(mode), int(world)))
 

@@ -69,6 +69,10 @@ int dlas_sm_count(void);
 #define DLAS_PROF_MLP_GRAD 1
 int dlas_prof_enable(int on);
 int dlas_prof_read(int slot, float* ms_sum_host, int* count_host);
+/* Average SM clock (MHz) over the launches of the tensor-core MLP kernel since the last reset, measured by the kernel
+ * itself (sum of clock64 deltas / sum of globaltimer deltas of one CTA); 0 if it has not run.  Synchronises the
+ * device.  Lets the benchmark report the clock under load without NVML calls inside the timed region. */
+int dlas_prof_sm_clock(double* mhz_host, int reset);
 
 /* ---- Gilbert's equation: q = P*S^1.89/(435*R^0.546) ---------------------------------------
  * Replaces the "Physical model" script named at Readme.md:7-8 (no code in the snapshot; formula from

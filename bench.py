@@ -398,16 +398,19 @@ def main():
         t = timed(lambda: ml.train_on_batch(Xs, ysq), 3)
         extras["lstm_2x128_T48_batch4096"] = {"sequences_per_s": 4096 / t, "ms_per_step": t * 1e3, "mode": "fp32",
                                               "frac_of_bf16_sustained_peak": 57.41e6 * 4096 / t / 1e12 / pk["tf_sust"]}
-        # the script's own CNN (cnn.py:110-128) at its own batch of 20 and at 4096 rows per step, dropout on
+        # the script's own CNN (cnn.py:110-128) at its own batch of 20 and at 4096 rows per step, dropout on, through the
+        # epoch loop of the library (dlas_cnn_fit_steps: 6 launches per step, no Python between steps)
         for cb in (20, 4096):
-            Wc, _ = ops.synth_series(cb, 60, 1)
-            Wc = Wc.reshape(cb, 60)
+            nb_ = 32
+            Wc, _ = ops.synth_series(cb * nb_, 60, 1)
+            Wc = Wc.reshape(cb * nb_, 60)
             Xc, yc = Wc[:, :48].contiguous(), Wc[:, 48:].contiguous()
             mc = dlas.Sequential([dlas.Convolution1D(1, 100, 13, activation="relu"), dlas.Dropout(0.5), dlas.Flatten(), dlas.Dense(3600, 12)])
             mc.compile(loss=dlas.mae_clip, optimizer=dlas.SGD(lr=0.001, momentum=0.99, decay=1e-6, nesterov=True))
-            t = timed(lambda: mc.train_on_batch(Xc, yc), 20)
+            impl = mc._impl
+            t = timed(lambda: impl._fit_steps(Xc, yc, cb, list(range(nb_))), 3) / nb_
             extras["cnn_48_conv13x100_dense12_batch%d" % cb] = {"samples_per_s": cb / t, "us_per_step": t * 1e6, "mode": "fp32",
-                                                                 "launches_per_step": 7}
+                                                                 "launches_per_step": 6}
         del series, ys, Wd, yd, X8, y8, Xs, ysq, Wc, Xc, yc
 
     if rank == 0:

@@ -8,6 +8,7 @@
 // bit of (sample, unit) is the counter hash the oracle uses, so both draw the same mask.
 // Flat layout: Wc[K][F] (tap-major), bc[F], Wd[T*F][n_out] (Flatten is time-major: t*F + f), bd[n_out].
 #include "common.cuh"
+#include "optim_math.cuh"
 
 namespace dlas {
 namespace {
@@ -45,18 +46,19 @@ conv_kernel(const CnnDesc d, const float* __restrict__ p, const float* __restric
   }
 }
 
-// one warp per row: out = a Wd + bd; per-row loss; dout = d(sum of losses)/d(out)
+// one block per row (the script trains on 20 rows: a warp per row would leave 20 warps on the whole GPU): the eight warps
+// split the T*F inputs, warp sums are added in warp order; out = a Wd + bd; per-row loss; dout = d(sum of losses)/d(out)
 __global__ void __launch_bounds__(256)
 dense_kernel(const CnnDesc d, int loss, const float* __restrict__ p, const float* __restrict__ a, const float* __restrict__ y,
              size_t n_rows, float* __restrict__ out, float* __restrict__ dout, float* __restrict__ lossrow) {
-  const int lane = threadIdx.x & 31;
-  const size_t warp = ((size_t)blockIdx.x * 256 + threadIdx.x) >> 5, n_warps = ((size_t)gridDim.x * 256) >> 5;
-  for (size_t b = warp; b < n_rows; b += n_warps) {
+  __shared__ float part[8][MAXO];
+  const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
+  for (size_t b = blockIdx.x; b < n_rows; b += gridDim.x) {
     float acc[MAXO];
 #pragma unroll
     for (int o = 0; o < MAXO; ++o) acc[o] = 0.f;
     const float* ar = a + b * d.TF;
-    for (int j = lane; j < d.TF; j += 32) {
+    for (int j = threadIdx.x; j < d.TF; j += 256) {
       const float av = ar[j];
       const float* w = p + d.wd + (size_t)j * d.O;
 #pragma unroll
@@ -67,27 +69,33 @@ dense_kernel(const CnnDesc d, int loss, const float* __restrict__ p, const float
     for (int o = 0; o < MAXO; ++o)
 #pragma unroll
       for (int s = 16; s > 0; s >>= 1) acc[o] += __shfl_xor_sync(0xffffffffu, acc[o], s);
-    float mine = 0.f;   // lane o keeps output o
+    if (lane == 0) {
 #pragma unroll
-    for (int o = 0; o < MAXO; ++o)
-      if (lane == o) mine = acc[o];
-    float lo = 0.f;
-    if (lane < d.O) {
-      const float v = mine + __ldg(p + d.bd + lane);
-      out[b * d.O + lane] = v;
+      for (int o = 0; o < MAXO; ++o) part[warp][o] = acc[o];
+    }
+    __syncthreads();
+    if (warp == 0) {
+      float lo = 0.f;
+      if (lane < d.O) {
+        float v = 0.f;
+        for (int w8 = 0; w8 < 8; ++w8) v += part[w8][lane];
+        v += __ldg(p + d.bd + lane);
+        out[b * d.O + lane] = v;
+        if (y) {
+          const float dd = v - y[b * d.O + lane], inv = 1.0f / (float)d.O;
+          float g;
+          if (loss == DLAS_LOSS_MSE) { lo = dd * dd * inv; g = 2.0f * dd * inv; }
+          else { const float ab = fabsf(dd); lo = fminf(ab, 6.0f) * inv; g = (ab <= 6.0f) ? (dd > 0.f ? inv : (dd < 0.f ? -inv : 0.f)) : 0.f; }  // cnn.py:29-32
+          dout[b * d.O + lane] = g;
+        }
+      }
       if (y) {
-        const float dd = v - y[b * d.O + lane], inv = 1.0f / (float)d.O;
-        float g;
-        if (loss == DLAS_LOSS_MSE) { lo = dd * dd * inv; g = 2.0f * dd * inv; }
-        else { const float ab = fabsf(dd); lo = fminf(ab, 6.0f) * inv; g = (ab <= 6.0f) ? (dd > 0.f ? inv : (dd < 0.f ? -inv : 0.f)) : 0.f; }  // cnn.py:29-32
-        dout[b * d.O + lane] = g;
+#pragma unroll
+        for (int s = 16; s > 0; s >>= 1) lo += __shfl_xor_sync(0xffffffffu, lo, s);
+        if (lane == 0) lossrow[b] = lo;
       }
     }
-    if (y) {
-#pragma unroll
-      for (int s = 16; s > 0; s >>= 1) lo += __shfl_xor_sync(0xffffffffu, lo, s);
-      if (lane == 0) lossrow[b] = lo;
-    }
+    __syncthreads();
   }
 }
 
@@ -130,36 +138,59 @@ dflat_kernel(const CnnDesc d, const float* __restrict__ p, const float* __restri
   }
 }
 
-// partial[g][k*F+f] = sum_b sum_t dconv[b][t][f] x[b][t+k]; entries K*F.. hold dbc
+// partial[g][k*F+f] = sum_b sum_t dconv[b][t][f] x[b][t+k]; entries K*F.. hold dbc.  One WARP per entry: the lanes split
+// the (row, time) pairs of the group and their sums meet in a shuffle tree (1,400 entries only: a thread per entry would
+// walk 720 dependent steps at the script's batch of 20)
 __global__ void __launch_bounds__(256)
 dwc_kernel(const CnnDesc d, const float* __restrict__ dconv, const float* __restrict__ X, size_t n_rows, int rows_per_group,
            float* __restrict__ partial, size_t pstride) {
-  const int g = blockIdx.y;
+  const int g = blockIdx.y, lane = threadIdx.x & 31;
   const size_t b0 = (size_t)g * rows_per_group, b1 = min(n_rows, b0 + (size_t)rows_per_group);
-  const int e = blockIdx.x * 256 + threadIdx.x, n_w = d.K * d.F;
+  const int e = blockIdx.x * 8 + (threadIdx.x >> 5), n_w = d.K * d.F;
   if (e >= n_w + d.F) return;
+  const int n_idx = (int)(b1 - b0) * d.T;
   float s = 0.f;
   if (e < n_w) {
     const int k = e / d.F, f = e - k * d.F;
-    for (size_t b = b0; b < b1; ++b)
-      for (int t = 0; t < d.T; ++t) s = fmaf(dconv[b * d.TF + t * d.F + f], __ldg(X + b * d.L + t + k), s);
-    partial[(size_t)g * pstride + d.wc + e] = s;
+    for (int idx = lane; idx < n_idx; idx += 32) {
+      const size_t b = b0 + idx / d.T;
+      const int t = idx % d.T;
+      s = fmaf(dconv[b * d.TF + t * d.F + f], __ldg(X + b * d.L + t + k), s);
+    }
   } else {
     const int f = e - n_w;
-    for (size_t b = b0; b < b1; ++b)
-      for (int t = 0; t < d.T; ++t) s += dconv[b * d.TF + t * d.F + f];
-    partial[(size_t)g * pstride + d.bc + f] = s;
+    for (int idx = lane; idx < n_idx; idx += 32) {
+      const size_t b = b0 + idx / d.T;
+      const int t = idx % d.T;
+      s += dconv[b * d.TF + t * d.F + f];
+    }
   }
+#pragma unroll
+  for (int w = 16; w > 0; w >>= 1) s += __shfl_xor_sync(0xffffffffu, s, w);
+  if (lane == 0) partial[(size_t)g * pstride + (e < n_w ? d.wc + e : d.bc + (e - n_w))] = s;
 }
 
+// FUSE: the optimiser update is applied in the same pass (single-GPU step loop, dlas_cnn_fit_steps) and the batch-mean
+// loss goes to *loss_out; otherwise the sums go to grad_sum for the caller's collective.
+template <bool FUSE>
 __global__ void __launch_bounds__(256)
 cnn_reduce_kernel(const CnnDesc d, const float* __restrict__ partial, size_t pstride, int n_groups,
-                  const float* __restrict__ lossrow, size_t n_rows, float* __restrict__ grad_sum) {
+                  const float* __restrict__ lossrow, size_t n_rows, float* __restrict__ grad_sum, OptScalars opt,
+                  float grad_scale, float* __restrict__ params, float* __restrict__ m, float* __restrict__ v,
+                  float* __restrict__ loss_out) {
   const int i = blockIdx.x * 256 + threadIdx.x;
   if (i < d.n_params) {
     float s = 0.f;
     for (int g = 0; g < n_groups; ++g) s += partial[(size_t)g * pstride + i];
-    grad_sum[i] = s;
+    if (FUSE) {
+      float p = params[i], mi = m[i], vi = (opt.kind == 0) ? 0.f : v[i];
+      opt_update(opt, s * grad_scale, p, mi, vi);
+      params[i] = p;
+      m[i] = mi;
+      if (opt.kind != 0) v[i] = vi;
+    } else {
+      grad_sum[i] = s;
+    }
   }
   if (blockIdx.x == 0) {   // loss sum: 256 strided partial sums, then added in thread order
     __shared__ float red[256];
@@ -170,7 +201,8 @@ cnn_reduce_kernel(const CnnDesc d, const float* __restrict__ partial, size_t pst
     if (threadIdx.x == 0) {
       float t = 0.f;
       for (int k = 0; k < 256; ++k) t += red[k];
-      grad_sum[d.n_params] = t;
+      if (FUSE) { if (loss_out) *loss_out = t * grad_scale; }
+      else grad_sum[d.n_params] = t;
     }
   }
 }
@@ -220,22 +252,26 @@ static int cnn_forward(const CnnDesc& d, int loss, const float* params, const fl
                        uint64_t seed, uint64_t sample0, const Ws& w, cudaStream_t st) {
   conv_kernel<<<blocks_for(n_rows * d.TF), 256, 0, st>>>(d, params, X, n_rows, keep, stream_key(seed, STREAM_DROPOUT), sample0, w.a);
   DLAS_LAUNCH_CHECK();
-  dense_kernel<<<blocks_for(n_rows * 32), 256, 0, st>>>(d, loss, params, w.a, y, n_rows, w.out, w.dout, w.lossrow);
+  dense_kernel<<<(unsigned)(n_rows < 65535 ? n_rows : 65535), 256, 0, st>>>(d, loss, params, w.a, y, n_rows, w.out, w.dout, w.lossrow);
   DLAS_LAUNCH_CHECK();
   return DLAS_OK;
 }
 
-extern "C" int dlas_cnn_grad(int L, int K, int F, int n_out, int loss, const float* params, const float* X, const float* y,
-                             size_t n_rows, float keep, uint64_t dropout_seed, uint64_t sample0, float* grad_sum,
-                             void* workspace, size_t workspace_bytes, void* stream) {
-  DLAS_CHECK_DEVICE();
+namespace dlas { int make_opt_scalars(const dlas_opt_cfg* cfg, uint64_t iteration, OptScalars& o); }   // optim.cu
+
+// forward + backward + (sums -> grad_sum | fused update when upd != nullptr)
+struct CnnUpdate { OptScalars opt; float grad_scale; float *params, *m, *v, *loss_out; };
+static int cnn_grad_impl(int L, int K, int F, int n_out, int loss, const float* params, const float* X, const float* y,
+                         size_t n_rows, float keep, uint64_t dropout_seed, uint64_t sample0, float* grad_sum,
+                         void* workspace, size_t workspace_bytes, void* stream, const CnnUpdate* upd) {
   CnnDesc d;
   int rc = make_desc(L, K, F, n_out, d);
   if (rc != DLAS_OK) return rc;
   DLAS_REQUIRE(loss == DLAS_LOSS_MSE || loss == DLAS_LOSS_MAE_CLIP, "dlas_cnn_grad: unknown loss %d", loss);
   DLAS_REQUIRE(keep > 0.0f, "dlas_cnn_grad: keep probability %g must be > 0 (>= 1 disables dropout)", keep);
-  DLAS_REQUIRE(params && grad_sum && (n_rows == 0 || (X && y)), "dlas_cnn_grad: null pointer");
+  DLAS_REQUIRE(params && (grad_sum || upd) && (n_rows == 0 || (X && y)), "dlas_cnn_grad: null pointer");
   cudaStream_t st = (cudaStream_t)stream;
+  if (n_rows == 0 && upd) return DLAS_OK;
   if (n_rows == 0) {
     DLAS_CUDA(cudaMemsetAsync(grad_sum, 0, ((size_t)d.n_params + 1) * sizeof(float), st));
     return DLAS_OK;
@@ -252,11 +288,54 @@ extern "C" int dlas_cnn_grad(int L, int K, int F, int n_out, int loss, const flo
   DLAS_LAUNCH_CHECK();
   dflat_kernel<<<blocks_for(n_rows * d.TF), 256, 0, st>>>(d, params, w.dout, n_rows, keep, w.a);
   DLAS_LAUNCH_CHECK();
-  dim3 g2((d.K * d.F + d.F + 255) / 256, w.n_groups);
+  dim3 g2((d.K * d.F + d.F + 7) / 8, w.n_groups);   // a warp per entry
   dwc_kernel<<<g2, 256, 0, st>>>(d, w.a, X, n_rows, w.rows_per_group, w.partial, w.pstride);
   DLAS_LAUNCH_CHECK();
-  cnn_reduce_kernel<<<(d.n_params + 255) / 256, 256, 0, st>>>(d, w.partial, w.pstride, w.n_groups, w.lossrow, n_rows, grad_sum);
+  if (upd)
+    cnn_reduce_kernel<true><<<(d.n_params + 255) / 256, 256, 0, st>>>(d, w.partial, w.pstride, w.n_groups, w.lossrow, n_rows, nullptr,
+                                                                      upd->opt, upd->grad_scale, upd->params, upd->m, upd->v,
+                                                                      upd->loss_out);
+  else
+    cnn_reduce_kernel<false><<<(d.n_params + 255) / 256, 256, 0, st>>>(d, w.partial, w.pstride, w.n_groups, w.lossrow, n_rows, grad_sum,
+                                                                       OptScalars{}, 0.f, nullptr, nullptr, nullptr, nullptr);
   DLAS_LAUNCH_CHECK();
+  return DLAS_OK;
+}
+
+extern "C" int dlas_cnn_grad(int L, int K, int F, int n_out, int loss, const float* params, const float* X, const float* y,
+                             size_t n_rows, float keep, uint64_t dropout_seed, uint64_t sample0, float* grad_sum,
+                             void* workspace, size_t workspace_bytes, void* stream) {
+  DLAS_CHECK_DEVICE();
+  return cnn_grad_impl(L, K, F, n_out, loss, params, X, y, n_rows, keep, dropout_seed, sample0, grad_sum, workspace,
+                       workspace_bytes, stream, nullptr);
+}
+
+extern "C" int dlas_cnn_fit_steps(int L, int K, int F, int n_out, int loss, const dlas_opt_cfg* cfg, float* params, float* m,
+                                  float* v, const float* X, const float* y, size_t n_rows, int batch,
+                                  const int64_t* batch_order_host, int64_t first_batch, int n_steps, uint64_t iteration0,
+                                  float keep, uint64_t dropout_seed, float* step_losses, void* workspace,
+                                  size_t workspace_bytes, void* stream) {
+  DLAS_CHECK_DEVICE();
+  DLAS_REQUIRE(cfg && params && m && X && y, "dlas_cnn_fit_steps: null pointer");
+  DLAS_REQUIRE(batch >= 1 && n_steps >= 0, "dlas_cnn_fit_steps: batch %d, n_steps %d", batch, n_steps);
+  const size_t n_batches = n_rows / (size_t)batch;
+  DLAS_REQUIRE(n_batches >= 1 || n_steps == 0, "dlas_cnn_fit_steps: n_rows %zu < batch %d", n_rows, batch);
+  for (int s = 0; s < n_steps; ++s) {
+    const int64_t b = batch_order_host ? batch_order_host[s] : first_batch + s;
+    DLAS_REQUIRE(b >= 0 && (size_t)b < n_batches, "dlas_cnn_fit_steps: batch index %lld out of range (%zu batches)", (long long)b,
+                 n_batches);
+    CnnUpdate u;
+    int rc = make_opt_scalars(cfg, iteration0 + (uint64_t)s, u.opt);
+    if (rc != DLAS_OK) return rc;
+    DLAS_REQUIRE(u.opt.kind == DLAS_OPT_SGD || v != nullptr, "dlas_cnn_fit_steps: Adam needs the second-moment buffer v");
+    u.grad_scale = 1.0f / (float)batch;
+    u.params = params; u.m = m; u.v = v;
+    u.loss_out = step_losses ? step_losses + s : nullptr;
+    // the mask of step s is drawn for global samples [(iteration0 + s) * batch, ...): same bits as train_on_batch
+    rc = cnn_grad_impl(L, K, F, n_out, loss, params, X + (size_t)b * batch * L, y + (size_t)b * batch * n_out, (size_t)batch, keep,
+                       dropout_seed, (iteration0 + (uint64_t)s) * (uint64_t)batch, nullptr, workspace, workspace_bytes, stream, &u);
+    if (rc != DLAS_OK) return rc;
+  }
   return DLAS_OK;
 }
 

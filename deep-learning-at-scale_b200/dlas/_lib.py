@@ -69,6 +69,8 @@ SIGNATURES = {
     "dlas_cnn_n_params": (_sz, [_i, _i, _i, _i]),
     "dlas_cnn_workspace_bytes": (_sz, [_i, _i, _i, _i, _sz]),
     "dlas_cnn_grad": (_i, [_i, _i, _i, _i, _i, _p, _p, _p, _sz, _f, _u64, _u64, _p, _p, _sz, _p]),
+    "dlas_cnn_fit_steps": (_i, [_i, _i, _i, _i, _i, _p, _p, _p, _p, _p, _p, _sz, _i, C.POINTER(C.c_int64), _i64, _i, _u64, _f, _u64,
+                                _p, _p, _sz, _p]),
     "dlas_cnn_predict": (_i, [_i, _i, _i, _i, _p, _p, _sz, _p, _p, _sz, _p]),
 }
 

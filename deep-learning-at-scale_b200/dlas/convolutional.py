@@ -77,6 +77,14 @@ class CnnRegressor(FlatModel):
         return ops.cnn_grad(*self.shape, self.loss, self.params, X, y, grad_sum, ws, keep=keep,
                             dropout_seed=self.seed, sample0=sample0)
 
+    def _fit_steps(self, X, Y, batch, order):
+        """cnn.py:127-128's inner loop over the batches `order` of one epoch, in ONE call (dlas_cnn_fit_steps)."""
+        import torch
+        losses = torch.empty(len(order), dtype=torch.float32, device=self.device)
+        ops.cnn_fit_steps(*self.shape, self.loss, self.cfg, self.params, self.m, self.v, X, Y, batch, order, self.iterations,
+                          self.keep, self.seed, losses, self._workspace(batch))
+        return losses
+
     def _forward(self, X, ws):
         return ops.cnn_predict(*self.shape, self.params, X, ws)
 

@@ -88,10 +88,16 @@ class FlatModel:
             t0 = time.time()
             order = hashing.batch_order(self.seed, epoch, n_full) if shuffle else np.arange(n_full)
             losses, weights = [], []
-            for s in range(n_full):
-                b = int(order[s])
-                losses.append(self.train_on_batch(X[b * lb:(b + 1) * lb], Y[b * lb:(b + 1) * lb], global_rows=batch_size))
-                weights.append(lb)
+            if self.world == 1 and n_full and hasattr(self, "_fit_steps"):
+                # single GPU: the whole epoch's batch loop is one library call (no Python between the steps)
+                losses.append(self._fit_steps(X, Y, lb, [int(b) for b in order[:n_full]]))
+                weights += [lb] * n_full
+                self.iterations += n_full
+            else:
+                for s in range(n_full):
+                    b = int(order[s])
+                    losses.append(self.train_on_batch(X[b * lb:(b + 1) * lb], Y[b * lb:(b + 1) * lb], global_rows=batch_size))
+                    weights.append(lb)
             if rem:
                 losses.append(self.train_on_batch(X[n_full * lb:], Y[n_full * lb:], global_rows=rem * self.world))
                 weights.append(rem)

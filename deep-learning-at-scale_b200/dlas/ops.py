@@ -198,6 +198,18 @@ def cnn_grad(L, K, F, n_out, loss, params, X, y, grad_sum, workspace, keep=1.0, 
     return grad_sum
 
 
+def cnn_fit_steps(L, K, F, n_out, loss, cfg, params, m, v, X, y, batch, batch_order, iteration0, keep, dropout_seed, step_losses,
+                  workspace, first_batch=0, n_steps=None):
+    """n_steps single-GPU steps (gradient kernels + reduction fused with the update), batch order from the host."""
+    order = None
+    if batch_order is not None:
+        order = (C.c_int64 * len(batch_order))(*[int(b) for b in batch_order])
+        n_steps = len(batch_order)
+    check(_lib.load().dlas_cnn_fit_steps(L, K, F, n_out, int(loss), C.byref(cfg), ptr(params), ptr(m), ptr(v), ptr(X), ptr(y),
+                                         X.shape[0], int(batch), order, int(first_batch), int(n_steps), int(iteration0), float(keep),
+                                         int(dropout_seed), ptr(step_losses), ptr(workspace), workspace.numel(), stream_ptr()))
+
+
 def cnn_predict(L, K, F, n_out, params, X, workspace, out=None):
     if out is None:
         out = torch.empty((X.shape[0], n_out), dtype=torch.float32, device=X.device)

@@ -250,6 +250,16 @@ size_t dlas_cnn_workspace_bytes(int L, int K, int F, int n_out, size_t n_rows);
 int dlas_cnn_grad(int L, int K, int F, int n_out, int loss, const float* params, const float* X,
                   const float* y, size_t n_rows, float keep, uint64_t dropout_seed, uint64_t sample0,
                   float* grad_sum, void* workspace, size_t workspace_bytes, void* stream);
+/* n_steps consecutive single-GPU steps of the script's loop (model.fit, cnn.py:127-128, batch_size=20): step s trains on
+ * rows [b*batch, (b+1)*batch) with b = batch_order_host ? batch_order_host[s] : first_batch + s; the reduction of the
+ * gradient partials applies the optimiser update in the same kernel (six launches per step, no host work between
+ * steps); the dropout mask of step s is drawn for samples [(iteration0 + s)*batch, ...), as dlas_cnn_grad would with
+ * that sample0.  step_losses (device, n_steps floats, may be NULL) receives the batch-mean losses. */
+int dlas_cnn_fit_steps(int L, int K, int F, int n_out, int loss, const dlas_opt_cfg* cfg, float* params, float* m,
+                       float* v, const float* X, const float* y, size_t n_rows, int batch,
+                       const int64_t* batch_order_host, int64_t first_batch, int n_steps, uint64_t iteration0,
+                       float keep, uint64_t dropout_seed, float* step_losses, void* workspace,
+                       size_t workspace_bytes, void* stream);
 /* model.predict / test_on_batch (cnn.py:132): test-time forward, dropout off; yhat (n_rows, n_out) */
 int dlas_cnn_predict(int L, int K, int F, int n_out, const float* params, const float* X,
                      size_t n_rows, float* yhat, void* workspace, size_t workspace_bytes, void* stream);

@@ -165,3 +165,33 @@ def test_keras_facade_builds_the_script_model(dl):
     assert model.predict(X[:7]).shape == (7, 12)
     with pytest.raises(NotImplementedError):
         m2 = dlas.Sequential(); m2.add(dlas.Convolution1D(1, 4, 3, activation="relu")); m2.add(dlas.Dense(8, 1)); m2.compile()
+
+
+def test_fit_steps_matches_the_step_by_step_loop(dl):
+    """dlas_cnn_fit_steps (reduction fused with the update, batch order from the host) against dlas_cnn_grad +
+    dlas_opt_step called batch by batch: same masks (sample0 = iteration * batch), same losses, same weights."""
+    from dlas import ops
+    B, nb = 20, 6
+    p0, X, y = _data(CNN, B * nb, 9)
+    cfg = ops.make_opt_cfg(O.OPT_SGD, 0.001, momentum=0.99, decay=1e-6, nesterov=True)
+    order = [3, 0, 5, 1, 4, 2]
+    it0 = 11
+    Xd, yd = _cuda(X), _cuda(y)
+    ws = ops.cnn_workspace(*CNN, B)
+    # step by step
+    p = _cuda(p0); m = torch.zeros_like(p); v = torch.zeros_like(p)
+    gs = torch.zeros(p.numel() + 1, device="cuda")
+    ref = torch.zeros(nb, device="cuda")
+    for s, b in enumerate(order):
+        sl = slice(b * B, (b + 1) * B)
+        ops.cnn_grad(*CNN, O.LOSS_MAE_CLIP, p, Xd[sl], yd[sl], gs, ws, keep=0.5, dropout_seed=4, sample0=(it0 + s) * B)
+        ops.opt_step(cfg, p, m, v, gs, 1.0 / B, it0 + s, ref[s:s + 1])
+    # one call
+    p1 = _cuda(p0); m1 = torch.zeros_like(p1); v1 = torch.zeros_like(p1)
+    got = torch.zeros(nb, device="cuda")
+    ops.cnn_fit_steps(*CNN, O.LOSS_MAE_CLIP, cfg, p1, m1, v1, Xd, yd, B, order, it0, 0.5, 4, got, ws)
+    torch.cuda.synchronize()
+    np.testing.assert_allclose(got.cpu().numpy(), ref.cpu().numpy(), rtol=1e-6)
+    assert _relerr(p1.cpu().numpy(), p.cpu().numpy().astype(np.float64)) < 1e-6
+    with pytest.raises(Exception):
+        ops.cnn_fit_steps(*CNN, O.LOSS_MAE_CLIP, cfg, p1, m1, v1, Xd, yd, B, [nb], it0, 0.5, 4, got, ws)   # batch index out of range

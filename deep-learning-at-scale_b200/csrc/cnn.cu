@@ -1,8 +1,10 @@
 // The CNN of the reference script (cnn.py:110-114), fp32 on CUDA cores:
 //   Convolution1D(1, F=100, K=13, relu, valid) -> Dropout(0.5) -> Flatten -> Dense(T*F=3600, 12)
-// trained with mae_clip / SGD at batch 20 (cnn.py:117-128).  At that batch a step is launch-bound
-// (20 rows x 180 Kflop), so the path is five small deterministic kernels, no atomics:
-//   conv+relu+dropout -> dense forward + loss -> dWd partials -> dflat/dconv -> dWc partials -> reduce.
+// trained with mae_clip / SGD at batch 20 (cnn.py:117-128).  At that batch a step is launch- and latency-bound
+// (20 rows x 180 Kflop), so the path is six small deterministic kernels, no atomics, each shaped to have thousands of
+// threads even at 20 rows:
+//   conv+relu+dropout -> dense forward + loss (block per row) -> dWd partials -> dflat/dconv -> dWc partials (warp per
+//   entry) -> reduce (+ the optimiser update in dlas_cnn_fit_steps, which runs a whole epoch's batch loop in one call).
 // Row groups give the weight-gradient kernels parallelism at large batches; partials are added in
 // group order.  Dropout is "inverted" (x * mask / keep at train time, identity at test time); the mask
 // bit of (sample, unit) is the counter hash the oracle uses, so both draw the same mask.

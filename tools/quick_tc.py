@@ -1,3 +1,5 @@
+"""Ten-second check of the tcgen05 gradient call at 128 / 1,000 / 65,536 rows (finite sums, wall time): run it first under
+`timeout 45` after touching csrc/mlp_tc.cu -- a kernel that hangs costs GPU minutes, this costs seconds."""
 import sys, time
 sys.path.insert(0, "deep-learning-at-scale_b200"); sys.path.insert(0, "oracle")
 import torch, dlas

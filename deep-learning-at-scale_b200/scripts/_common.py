@@ -36,6 +36,9 @@ def parser(description):
     ap.add_argument("--optimizer", default="sgd", choices=["sgd", "adam"])
     ap.add_argument("--mode", default="fp32", choices=["fp32", "tc"])
     ap.add_argument("--seed", type=int, default=ops.BASE_SEED)
+    ap.add_argument("--one-hot", action="store_true",
+                    help="with --data: encode string columns as cnn.py:72-91 does (StringIndexer -> OneHotEncoder) and put "
+                         "them in front of the continuous columns (cnn.py:93-99); host-side, fitted once on all rows")
     return ap
 
 
@@ -46,12 +49,45 @@ def schema(args):
     print([(k, v if v in ("int", "float") else "string") for k, v in zip(names, types)])   # cnn.py:62 prints the schema
     cat = [k for k, v in zip(names, types) if v not in ("int", "float")]
     print("Categorical variables: " + ", ".join(cat))                                      # cnn.py:73
-    if cat:
-        print("notice: string columns are ignored on the GPU path (one-hot encoding is Spark-side ETL)")
+    if cat and not getattr(args, "one_hot", False):
+        print("notice: string columns are ignored (pass --one-hot to encode them as cnn.py:72-91 does)")
     cont = [k for k, v in zip(names, types) if v in ("int", "float") and k != args.targetColumn]
     if args.targetColumn not in names:
         raise SystemExit("targetColumn %r is not among columnNames" % args.targetColumn)
     return names, cont
+
+
+def string_index(values):
+    """Spark StringIndexer (cnn.py:75), default order: most frequent label first, ties by label ascending."""
+    labels, counts = np.unique(np.asarray(values, dtype=str), return_counts=True)
+    order = sorted(range(len(labels)), key=lambda i: (-counts[i], labels[i]))
+    rank = {labels[i]: r for r, i in enumerate(order)}
+    return np.fromiter((rank[str(v)] for v in values), dtype=np.int64, count=len(values)), [labels[i] for i in order]
+
+
+def one_hot_drop_last(index, n_labels):
+    """Spark OneHotEncoder (cnn.py:77-80), default dropLast=True: n_labels - 1 columns, the last label is all zeros."""
+    out = np.zeros((len(index), max(0, n_labels - 1)), dtype=np.float32)
+    keep = index < n_labels - 1
+    out[np.nonzero(keep)[0], index[keep]] = 1.0
+    return out
+
+
+def assemble_features(df, names, types, target, one_hot=False):
+    """VectorAssembler order of cnn.py:93-99: the encoded categorical columns first (argv order), then the continuous
+    columns in argv order -- WITHOUT the target (the reference leaks it).  The reference fits the
+    indexers separately on the train / validation / test splits (cnn.py:88-90), which gives the three splits different
+    encodings; here they are fitted once on all rows.  Returns (X float32 (n, F), y float32 (n, 1))."""
+    cont = [k for k, v in zip(names, types) if v in ("int", "float") and k != target]
+    cat = [k for k, v in zip(names, types) if v not in ("int", "float") and k != target]
+    blocks = []
+    if one_hot:
+        for c in cat:
+            idx, labels = string_index(df[c].to_numpy())
+            blocks.append(one_hot_drop_last(idx, len(labels)))
+    blocks.append(df[cont].to_numpy(dtype=np.float32).reshape(len(df), len(cont)))
+    X = np.ascontiguousarray(np.concatenate(blocks, axis=1), dtype=np.float32)
+    return X, df[[target]].to_numpy(dtype=np.float32)
 
 
 def load_rows(args, names, cont):
@@ -62,9 +98,8 @@ def load_rows(args, names, cont):
         raise SystemExit("give --data <csv> or --synthetic N")
     import pandas as pd
     df = pd.read_csv(args.data, header=None, names=names)
-    X = torch.as_tensor(df[cont].to_numpy(dtype=np.float32)).cuda()
-    y = torch.as_tensor(df[[args.targetColumn]].to_numpy(dtype=np.float32)).cuda()
-    return X, y
+    Xh, yh = assemble_features(df, names, args.columnTypes.split(","), args.targetColumn, one_hot=getattr(args, "one_hot", False))
+    return torch.as_tensor(Xh).cuda(), torch.as_tensor(yh).cuda()
 
 
 def split(X, y, seed):

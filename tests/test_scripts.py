@@ -47,7 +47,8 @@ def test_scripts_run_with_reference_argv(tmp_path, script, extra):
 
 
 @pytest.mark.gpu
-def test_static_ann_from_csv(tmp_path):
+@pytest.mark.parametrize("one_hot", [False, True])
+def test_static_ann_from_csv(tmp_path, one_hot):
     rng = np.random.default_rng(0)
     n = 5000
     A = rng.normal(size=(n, 3)).astype(np.float32)
@@ -58,7 +59,32 @@ def test_static_ann_from_csv(tmp_path):
             f.write("%g,%g,w%d,%g,%g\n" % (A[i, 0], A[i, 1], i % 7, A[i, 2], q[i]))
     r = subprocess.run([sys.executable, os.path.join(SCRIPTS, "static_ann.py"), "a,b,well,c,q", "float,float,string,float,float", "q",
                         str(tmp_path) + "/", "--data", path, "--hidden", "64,64", "--batch-size", "128", "--epochs", "30",
-                        "--optimizer", "adam", "--loss", "mse"], capture_output=True, text=True, timeout=600)
+                        "--optimizer", "adam", "--loss", "mse"] + (["--one-hot"] if one_hot else []), capture_output=True, text=True, timeout=600)
     assert r.returncode == 0, r.stdout[-1500:] + r.stderr[-1500:]
     loss = float(r.stdout.split("Testing set loss:")[1].split()[0])
     assert loss < 0.05 * float(np.var(q))      # it learns the linear map
+
+
+def test_feature_assembly_follows_the_reference_pipeline():
+    """cnn.py:72-99 restated on the host: StringIndexer (most frequent label first), OneHotEncoder (last label dropped),
+    categorical block in front of the continuous columns, target excluded (fixes D5)."""
+    import pandas as pd
+    sys.path.insert(0, SCRIPTS)
+    import _common as C
+    df = pd.DataFrame({"a": [1.0, 2.0, 3.0, 4.0, 5.0, 6.0], "well": ["w2", "w1", "w2", "w3", "w2", "w1"],
+                       "n": [1, 2, 3, 4, 5, 6], "q": [10.0, 20.0, 30.0, 40.0, 50.0, 60.0]})
+    names, types = ["a", "well", "n", "q"], ["float", "string", "int", "float"]
+    idx, labels = C.string_index(df["well"].to_numpy())
+    assert labels == ["w2", "w1", "w3"] and idx.tolist() == [0, 1, 0, 2, 0, 1]          # by frequency, descending
+    assert C.string_index(np.array(["b", "a", "a", "b"]))[1] == ["a", "b"]             # ties: label ascending
+    oh = C.one_hot_drop_last(idx, 3)
+    assert oh.shape == (6, 2) and oh.tolist() == [[1, 0], [0, 1], [1, 0], [0, 0], [1, 0], [0, 1]]
+    X, y = C.assemble_features(df, names, types, "q", one_hot=True)
+    assert X.dtype == np.float32 and X.shape == (6, 4) and y.shape == (6, 1)
+    np.testing.assert_array_equal(X[:, :2], oh)                                          # categorical block first (cnn.py:96)
+    np.testing.assert_array_equal(X[:, 2], df["a"]); np.testing.assert_array_equal(X[:, 3], df["n"])
+    np.testing.assert_array_equal(y[:, 0], df["q"])                                      # the target is not a feature
+    X0, _ = C.assemble_features(df, names, types, "q", one_hot=False)
+    np.testing.assert_array_equal(X0, X[:, 2:])                                          # default: numeric columns only
+    Xt, yt = C.assemble_features(df, names, types, "a", one_hot=True)                    # any numeric column can be the target
+    assert Xt.shape == (6, 4) and yt[:, 0].tolist() == df["a"].tolist()

@@ -77,3 +77,23 @@ def test_product_never_imports_oracle():
                 assert not pat.search(open(os.path.join(d, f), errors="replace").read()), f
             if f.endswith((".cu", ".cuh")):
                 assert "#include \"../../oracle" not in open(os.path.join(d, f), errors="replace").read(), f
+
+
+def declared_arity():
+    """name -> number of parameters of every prototype in the header (0 for `(void)`)."""
+    src = open(HEADER).read()
+    src = re.sub(r"/\*.*?\*/", "", src, flags=re.S)
+    out = {}
+    for name, params in re.findall(r"\b(dlas_[a-z0-9_]+)\s*\(([^;{}]*?)\)\s*;", src, flags=re.S):
+        p = params.strip()
+        out[name] = 0 if p in ("", "void") else p.count(",") + 1
+    return out
+
+
+def test_binding_arity_matches_header():
+    """A ctypes table that drifts from the header corrupts the call silently: same parameter count on both sides."""
+    from dlas import _lib
+    ar = declared_arity()
+    assert sorted(ar) == declared_symbols()
+    for name, (_res, args) in _lib.SIGNATURES.items():
+        assert len(args) == ar[name], "%s: header declares %d parameters, the binding passes %d" % (name, ar[name], len(args))

@@ -97,3 +97,18 @@ def test_binding_arity_matches_header():
     assert sorted(ar) == declared_symbols()
     for name, (_res, args) in _lib.SIGNATURES.items():
         assert len(args) == ar[name], "%s: header declares %d parameters, the binding passes %d" % (name, ar[name], len(args))
+
+
+def test_tensor_core_kernel_resource_budget(lib):
+    """ptxas -v of the tcgen05 kernel (kept by build.py): it launches with 168 registers x 384 threads (the whole register
+    file; setmaxnreg then moves registers between the warpgroups) and must not spill more than a few words -- a 300-byte
+    spill in the issuer once cost 40 % of the throughput."""
+    log = os.path.join(ROOT, "deep-learning-at-scale_b200", "build", "ptxas_mlp_tc.log")
+    if not os.path.exists(log):
+        pytest.skip("no ptxas log (library was not built by build.py in this tree)")
+    txt = open(log).read()
+    m = re.search(r"Function properties for \S*mlp_tc_kernel\S*\s+(\d+) bytes stack frame, (\d+) bytes spill stores, (\d+) bytes spill loads\s+"
+                  r"ptxas info\s+: Used (\d+) registers", txt)
+    assert m, "mlp_tc_kernel not found in the ptxas log"
+    stack, st, ld, regs = map(int, m.groups())
+    assert regs == 168 and stack <= 64 and st <= 64 and ld <= 64, (stack, st, ld, regs)

@@ -103,28 +103,103 @@ def n_cores():
         return os.cpu_count() or 1
 
 
-def cpu_port_rate(rows_per_step, n_steps, warmup=1):
-    """Times oracle/torch_cpu.py (the CPU port of the same training step) -- the ONLY place bench.py
-    executes anything under oracle/.  Returns (samples/s, seconds, threads)."""
-    sys.path.insert(0, os.path.join(ROOT, "oracle"))
+def _oracle_path():
+    p = os.path.join(ROOT, "oracle")
+    if p not in sys.path:
+        sys.path.insert(0, p)
+
+
+def cpu_port_rate(rows_per_step, n_steps, warmup=1, dims=None, n_blocks=4):
+    """Times oracle/torch_cpu.py (the CPU port of the same training step) -- bench.py executes oracle/ only here, in
+    gilbert_cpu_baseline (both: the cpu_baseline legs) and in dp_parity_gate (as the checker, outside every timed
+    region).  Returns (samples/s, seconds, threads)."""
+    _oracle_path()
     import numpy as np
     import torch
     import dlas_oracle as O
     import torch_cpu as T
+    dims = dims or DIMS
     torch.set_num_threads(n_cores())
-    n = rows_per_step * 4
+    n = rows_per_step * n_blocks
     rng = np.random.default_rng(0)   # values do not matter for timing; shapes and dtypes do
-    X = torch.from_numpy((rng.random((n, DIMS[0]), dtype=np.float32) * 2 - 1))
+    X = torch.from_numpy((rng.random((n, dims[0]), dtype=np.float32) * 2 - 1))
     y = torch.from_numpy((rng.random((n, 1), dtype=np.float32) * 2 - 1))
-    m = T.TorchCpuMlp(DIMS, O.glorot_init(DIMS, O.BASE_SEED))
+    m = T.TorchCpuMlp(dims, O.glorot_init(dims, O.BASE_SEED))
     for s in range(warmup):
         m.step(X[:rows_per_step], y[:rows_per_step])
     t0 = time.perf_counter()
     for s in range(n_steps):
-        b = s % 4
+        b = s % n_blocks
         m.step(X[b * rows_per_step:(b + 1) * rows_per_step], y[b * rows_per_step:(b + 1) * rows_per_step])
     dt = time.perf_counter() - t0
     return rows_per_step * n_steps / dt, dt, torch.get_num_threads()
+
+
+def gilbert_cpu_baseline(n_rows=20_000_000):
+    """the physical model as the vectorised NumPy fp32 expression over a >= 20 M-row slice of the same
+    synthetic inputs, one thread and all host threads (chunked)."""
+    _oracle_path()
+    import dlas_oracle as O
+    import torch_cpu as T
+    P, S, R = O.synth_gilbert(O.BASE_SEED, 0, n_rows)
+    out = {}
+    for name, thr in (("numpy_f32_1_thread", 1), ("numpy_f32_all_threads", n_cores())):
+        T.gilbert_numpy_f32(P[:1 << 20], S[:1 << 20], R[:1 << 20], threads=thr)
+        t0 = time.perf_counter()
+        T.gilbert_numpy_f32(P, S, R, threads=thr)
+        dt = time.perf_counter() - t0
+        out[name] = {"value": n_rows / dt, "unit": "rows/s", "cores": thr, "kind": "port",
+                     "sample": "%d rows of the config-2 inputs, q = P*S**1.89/(435*R**0.546) in NumPy fp32 (%.2f s)" % (n_rows, dt)}
+    return out
+
+
+def traffic_from_profiles(kernel, rows):
+    """roofline.traffic: DRAM bytes per launch of `kernel` from the committed ncu capture (profiles/ncu_traffic.json, written
+    by tools/ncu_summary.py), scaled by rows when the launch size differs.  (None, None) without a capture."""
+    try:
+        d = json.load(open(os.path.join(ROOT, "profiles", "ncu_traffic.json")))[kernel]
+        b = (d["dram_bytes_read"] + d["dram_bytes_write"]) * rows / d["rows_per_launch"]
+        return b, d["source"] + ("" if rows == d["rows_per_launch"] else " (scaled from %d rows per launch)" % d["rows_per_launch"])
+    except Exception:
+        return None, None
+
+
+def dp_parity_gate(dlas, torch, dist, mode, rank, world, local_rows_fn):
+    """BASELINE.md 5.5 "parity gates run before timing": 12 steps at global batch 8,192 of the benchmarked network through
+    the SAME stepper the timed region uses (Sequential.graph_stepper), compared with the single-process fp64 oracle on the
+    whole batches, plus the spread of a weight checksum over the ranks.  Returns the dp_parity object."""
+    _oracle_path()
+    import numpy as np
+    import dlas_oracle as O
+    batch, steps = 8192, 12
+    X, y = O.synth_rows(O.BASE_SEED, 0, batch * steps, DIMS[0])
+    p0 = O.glorot_init(DIMS, O.BASE_SEED)
+    mine = local_rows_fn(X.shape[0], batch, rank, world).numpy()
+    m = dlas.Sequential([dlas.Dense(32, 256, activation="relu"), dlas.Dense(256, 256, activation="relu"), dlas.Dense(256, 1)], mode=mode)
+    m.compile(loss="mse", optimizer=dlas.SGD(lr=0.001, momentum=0.99, decay=1e-6, nesterov=True))
+    m.set_weights_flat(p0)
+    Xl, yl = torch.from_numpy(X[mine]).cuda(), torch.from_numpy(y[mine]).cuda().reshape(-1, 1)
+    st = m.graph_stepper(Xl, yl, batch // world, global_rows=batch, warmup_steps=3)
+    st.run(steps - 3)
+    torch.cuda.synchronize()
+    got = st.recent_losses(steps)
+    w = m.get_weights_flat()
+    chk = torch.tensor([float(np.abs(w.astype(np.float64)).sum())], device="cuda", dtype=torch.float64)
+    lo, hi = chk.clone(), chk.clone()
+    if world > 1:
+        dist.all_reduce(lo, op=dist.ReduceOp.MIN)
+        dist.all_reduce(hi, op=dist.ReduceOp.MAX)
+    pr = p0.astype(np.float64)
+    ref = O.mlp_fit_steps(pr, DIMS, X.astype(np.float64), y.astype(np.float64), batch, steps, O.LOSS_MSE, O.sgd_config(), O.opt_state(pr.size))
+    lerr = float(np.abs(got / ref - 1).max())
+    werr = float(np.linalg.norm(w - pr) / np.linalg.norm(pr))
+    tol_l = 1e-4 if mode == "fp32" else 3e-4
+    res = {"path": m.dp_path, "steps": steps, "global_batch": batch, "loss_rel_err": lerr, "weights_rel_err": werr,
+           "rank_spread": float(hi.item() - lo.item()), "tolerance": {"loss": tol_l, "weights": 1e-4},
+           "checked_against": "fp64 oracle on the whole batches (oracle/dlas_oracle.py), before the timed region"}
+    res["ok"] = bool(lerr < tol_l and werr < 1e-4 and res["rank_spread"] == 0.0 and np.isfinite(got).all())
+    del st
+    return res
 
 
 def reference_arm(args, rank):
@@ -183,6 +258,7 @@ def main():
     ap.add_argument("--gilbert-variant", type=int, default=-1)
     ap.add_argument("--no-cpu-baseline", action="store_true")
     ap.add_argument("--no-extras", action="store_true", help="skip the dynamic-ANN / 8-64-64-1 / LSTM side measurements")
+    ap.add_argument("--no-sustained", action="store_true", help="skip the >= 2 s pass")
     args = ap.parse_args()
     rank = int(os.environ.get("RANK", "0"))
     local_rank = int(os.environ.get("LOCAL_RANK", "0"))
@@ -228,14 +304,14 @@ def main():
         # one captured step (gradient kernels, all-reduce, update, cursor advance) replayed K times: no per-step host work
         stepper = model.graph_stepper(X, y, B, global_rows=B * N, warmup_steps=W)
 
-    def run_steps(n, first):
+    def run_steps(n, first, keep=True):
         if stepper is None:
             done = 0
             while done < n:     # sequential batches, wrapping at the end of the shard
                 fb = (first + done) % n_batches
                 cnt = min(n - done, n_batches - fb)
                 ops.mlp_fit_steps(DIMS, model.loss, model.mode, model.cfg, model.params, model.m, model.v, X, y, B, cnt,
-                                  model.iterations, losses[done:], model.grad_sum, model.workspace, first_batch=fb)
+                                  model.iterations, losses[done:] if keep else None, model.grad_sum, model.workspace, first_batch=fb)
                 model.iterations += cnt
                 done += cnt
         else:
@@ -246,6 +322,19 @@ def main():
         if N > 1:
             dist.barrier()
         torch.cuda.synchronize()
+
+    # ---- parity gate of the N > 1 path, before any timing; a failed gate fails the run
+    dp_parity = None
+    if N > 1 or os.environ.get("DLAS_BENCH_GATE") == "1":
+        from dlas import parallel
+        dp_parity = dp_parity_gate(dlas, torch, dist, mode, rank, N, parallel.local_rows)
+        if not dp_parity["ok"]:
+            if rank == 0:
+                sys.stderr.write("bench.py: data-parallel parity gate FAILED: %s\n" % json.dumps(dp_parity))
+                emit({"metric": "static_ann_train_samples_per_s", "value": None, "n_gpus": N, "invalid": "dp_parity gate failed",
+                      "dp_parity": dp_parity})
+            torch.cuda.synchronize()
+            os._exit(3)
 
     run_steps(W, 0)
     barrier()
@@ -275,6 +364,33 @@ def main():
             barrier()
     ms = e0.elapsed_time(e1)
     final_loss = float(losses[K - 1].item()) if stepper is None else float(stepper.recent_losses(1)[0])
+    steps_done = W + K + (K if (N > 1 and not no_nvml) else 0)
+    # ---- sustained pass: the same steps for >= 2 s, so that the fraction can also be quoted against the SUSTAINED peak
+    # (the K-step region above is a burst of about a millisecond); clocks as above
+    sustained = None
+    if not args.no_sustained:
+        ks = int(min(200_000, max(K, 2.2 / max(1e-6, ms / K * 1e-3))))
+        if N > 1:
+            tks = torch.tensor([ks], device="cuda")
+            dist.all_reduce(tks, op=dist.ReduceOp.MAX)
+            ks = int(tks.item())
+        clk_s = ClockSampler([local_rank] if (in_region and rank == 0) else [], period=0.02)
+        if mode == "tc":
+            ops.prof_sm_clock(reset=True)
+        barrier()
+        with clk_s:
+            e0.record()
+            run_steps(ks, steps_done, keep=False)
+            e1.record()
+            barrier()
+        steps_done += ks
+        ts = torch.tensor([e0.elapsed_time(e1)], device="cuda")
+        if N > 1:
+            dist.all_reduce(ts, op=dist.ReduceOp.MAX)
+        s_ms = float(ts.item())
+        sustained = {"steps": ks, "seconds": s_ms * 1e-3, "value": N * B * ks / (s_ms * 1e-3), "unit": "samples/s",
+                     "us_per_step": s_ms / ks * 1e3, "sm_mhz_in_kernel": ops.prof_sm_clock(reset=True) if mode == "tc" else None,
+                     "clocks": clk_s.summary() if in_region else "NVML not sampled at N > 1 (see clocks.when)"}
     # Kernel time for the roofline: a SECOND pass over the same kind of steps with CUDA events around every launch of
     # the forward/backward kernel on its own stream (dlas_prof_*).  Kept out of the pass above because an event between
     # two kernels breaks their programmatic-dependent-launch overlap and would tax `value`; kernels inside a replayed
@@ -282,7 +398,7 @@ def main():
     ops.prof_read(ops.PROF_MLP_GRAD)
     ops.prof_enable(True)
     if stepper is None:
-        run_steps(K, W + K)
+        run_steps(K, steps_done)
     else:
         for s_ in range(10):
             b_ = s_ % n_batches
@@ -313,7 +429,30 @@ def main():
     if N > 1:
         dist.all_reduce(t, op=dist.ReduceOp.MAX)
     e2e_value = N * B * K / (float(t.item()) * 1e-3)
+    dp_path_e2e = "single" if N == 1 else getattr(model, "dp_path", None)
     del xh, yh
+
+    # ---- inference (a8: model.predict / test_on_batch, cnn.py:132) over resident rows: rows/s and its HBM fraction
+    # (algorithmic bytes = 32 fp32 features read + 1 fp32 prediction written per row)
+    n_pred = int(min(rows_rank, 8_388_608))
+    yhat = torch.empty((n_pred, 1), dtype=torch.float32, device="cuda")
+    for _ in range(2):
+        ops.mlp_predict(DIMS, model.mode, model.params, X[:n_pred], out=yhat)
+    barrier()
+    e0.record()
+    for r_ in range(5):
+        ops.mlp_predict(DIMS, model.mode, model.params, X[:n_pred], out=yhat)     # 1.07 GB per pass >> L2
+    e1.record()
+    barrier()
+    t = torch.tensor([e0.elapsed_time(e1)], device="cuda")
+    if N > 1:
+        dist.all_reduce(t, op=dist.ReduceOp.MAX)
+    pred_s = float(t.item()) * 1e-3 / 5
+    predict = {"rows_per_s": N * n_pred / pred_s, "rows_per_gpu_per_call": n_pred, "ms_per_call": pred_s * 1e3,
+               "kernel": "fp32 CUDA-core forward (both modes)",
+               "hbm_frac": n_pred * (DIMS[0] * 4 + 4) / pred_s / 1e9 / pk["hbm"],
+               "tensor_frac_of_bf16_burst": n_pred * 147_968 / pred_s / 1e12 / pk["tf_burst"]}
+    del yhat
 
     # ---- Gilbert rows/s vs HBM (config 2), sharded by rows, no collective
     del X, y
@@ -342,10 +481,10 @@ def main():
             dist.all_reduce(t, op=dist.ReduceOp.MAX)
         rows_s = N * g_rows * reps / (float(t.item()) * 1e-3)
         gbs = g_rows * GILBERT_BYTES_PER_ROW / (gk_ms / gk_n * 1e-3) / 1e9
+        g_traffic, g_src = traffic_from_profiles("gilbert_vec_kernel", g_rows)
         gil[str(var)] = {"rows_per_s": rows_s, "kernel_ms": gk_ms / gk_n,
                          "roofline": {"bound": "hbm", "achieved": gbs, "peak": pk["hbm"], "unit": "GB/s",
-                                      "frac": gbs / pk["hbm"],
-                                      "traffic": (3.179e9 * g_rows / 200_000_000)}}   # ncu: 2.400 GB read + 0.779 GB written per 200M rows (profiles/)
+                                      "frac": gbs / pk["hbm"], "traffic": g_traffic, "traffic_source": g_src}}
     best = max(gil, key=lambda k: gil[k]["rows_per_s"])
     del P, S, R, q
 
@@ -385,12 +524,37 @@ def main():
         t = timed(lambda: mdl.train_on_batch(Wd, yd), 5)
         extras["dynamic_ann_192_256_256_1"] = {"samples_per_s": 65536 / t, "mode": "fp32", "rows_per_step": 65536,
                                                "frac_of_bf16_sustained_peak": 591360 * 65536 / t / 1e12 / pk["tf_sust"]}
-        # static ANN 8-64-64-1 (config 1 shape), fp32 kernel
-        X8, y8 = ops.synth_rows(65536, 8)
-        m8 = dlas.Sequential([dlas.Dense(8, 64, activation="relu"), dlas.Dense(64, 64, activation="relu"), dlas.Dense(64, 1)])
+        # static ANN 8-64-64-1 (configs[0]): 1 M rows, one whole epoch through model.fit at batch 4096 (and one 65,536-row
+        # step for comparison with round 1); the CPU port runs the same epoch
+        X8, y8 = ops.synth_rows(1_000_000, 8)
+        m8 = dlas.Sequential([dlas.Dense(8, 64, activation="relu"), dlas.Dense(64, 64, activation="relu"), dlas.Dense(64, 1)],
+                             mode=("tc" if ops.mlp_mode_supported([8, 64, 64, 1], dlas.MODE_TC) and mode == "tc" else "fp32"))
         m8.compile(loss="mse", optimizer=dlas.SGD(lr=0.001, momentum=0.99, decay=1e-6, nesterov=True))
-        t = timed(lambda: m8.train_on_batch(X8, y8), 10)
-        extras["static_ann_8_64_64_1"] = {"samples_per_s": 65536 / t, "mode": "fp32", "rows_per_step": 65536}
+        t = timed(lambda: m8.train_on_batch(X8[:65536], y8[:65536]), 10)
+        m8.fit(X8, y8, nb_epoch=1, batch_size=4096, verbose=0)
+        torch.cuda.synchronize()
+        t0_ = time.perf_counter()
+        m8.fit(X8, y8, nb_epoch=1, batch_size=4096, verbose=0)
+        torch.cuda.synchronize()
+        t_epoch = time.perf_counter() - t0_
+        e8 = {"samples_per_s": 65536 / t, "mode": "fp32" if m8.mode == dlas.MODE_FP32 else "tc", "rows_per_step": 65536,
+              "epoch_1M_rows_batch_4096": {"samples_per_s": 1_000_000 / t_epoch, "seconds": t_epoch, "through": "model.fit (wall clock)"}}
+        if not args.no_cpu_baseline:
+            rate8, dt8, thr8 = cpu_port_rate(4096, 1_000_000 // 4096, warmup=2, dims=[8, 64, 64, 1], n_blocks=1_000_000 // 4096)
+            e8["cpu_baseline"] = {"value": rate8, "unit": "samples/s", "cores": thr8, "kind": "port",
+                                  "sample": "one epoch over 1 M rows at batch 4096 (%.2f s), torch-CPU fp32 port" % dt8}
+        extras["static_ann_8_64_64_1"] = e8
+        # the headline network at the reference's own batch size of 20 (cnn.py:128), for the record: launch-bound
+        Xr, yr = ops.synth_rows(20 * 2000, DIMS[0])
+        l20 = torch.zeros(2000, device="cuda")
+        for md_, nm_ in ((dlas.MODE_FP32, "fp32"),) + (((dlas.MODE_TC, "tc"),) if mode == "tc" else ()):
+            ws_ = ops.mlp_workspace(DIMS, md_)
+            mm_ = torch.zeros_like(model.params)
+            pp_ = model.params.clone()
+            t = timed(lambda: ops.mlp_fit_steps(DIMS, model.loss, md_, model.cfg, pp_, mm_, mm_.clone(), Xr, yr, 20, 2000, 0, l20,
+                                                model.grad_sum, ws_), 2)
+            extras.setdefault("static_ann_32_256_256_1_batch_20", {})[nm_] = {"samples_per_s": 20 * 2000 / t, "us_per_step": t / 2000 * 1e6}
+        del Xr, yr
         # LSTM 2x128, T=48, batch 4096 (config 5)
         Xs, ysq = ops.synth_series(4096, 48, 8)
         ml = dlas.Sequential([dlas.LSTM(128, input_shape=(48, 8), return_sequences=True), dlas.LSTM(128), dlas.Dense(1)])
@@ -414,6 +578,7 @@ def main():
         del series, ys, Wd, yd, X8, y8, Xs, ysq, Wc, Xc, yc
 
     if rank == 0:
+        tc_traffic, tc_src = traffic_from_profiles("mlp_tc_kernel", B) if mode == "tc" else (None, None)
         kern_s = kern_ms / max(1, kern_n) * 1e-3
         tfs = TRAIN_FLOP_PER_SAMPLE * B / kern_s / 1e12
         # my kernels per step: fp32 mode transpose + forward/backward + reduce + update; tc mode forward/backward +
@@ -423,18 +588,25 @@ def main():
         line = {
             "metric": "static_ann_train_samples_per_s", "value": value, "unit": "samples/s", "n_gpus": N, "steps": K,
             "warmup": W, "ms_per_step": ms / K, "higher_is_better": True, "scaling": "weak", "vs_baseline": None,
-            "dtype": "f32" if mode == "fp32" else "f16-operands/f32-accumulate (10-bit mantissa, as TF32)",
+            "dtype": "f32" if mode == "fp32" else
+                     "f16-operands/f32-accumulate (reduced-range mode: |value| <= 65504, 11-bit significand; stated tolerance vs the "
+                     "fp64 oracle: per-step loss 3e-4, weights 1e-4 -- tests/test_mlp_tc_gpu.py)",
             "data": "synthetic",
             "config": {"workload": WORKLOAD, "rows_per_gpu_per_step": B, "global_batch": B * N, "mode": mode,
                        "rows_resident_per_gpu": rows_rank, "l2": "inputs (%.1f GB per GPU) larger than L2; every step reads new rows"
-                       % (rows_rank * BYTES_PER_SAMPLE / 1e9), "parallelism": "dp%d" % N, "final_loss": final_loss},
-            "roofline": {"bound": "tensor", "achieved": tfs, "peak": pk["tf_sust"], "unit": "TFLOP/s", "frac": tfs / pk["tf_sust"],
-                         "traffic": (10.56e6 if (mode == "tc" and B == 65536) else None),   # ncu dram read+write per launch, profiles/r01_ncu_full_tc_final.txt
+                       % (rows_rank * BYTES_PER_SAMPLE / 1e9), "parallelism": "dp%d" % N, "final_loss": final_loss,
+                       "dp_path": getattr(model, "dp_path", None) or ("single" if N == 1 else None),
+                       "dp_path_e2e": dp_path_e2e},
+            # the K timed steps are a burst of about a millisecond: quoted against the BURST peak; `sustained` below carries
+            # the >= 2 s figure against the sustained peak
+            "roofline": {"bound": "tensor", "achieved": tfs, "peak": pk["tf_burst"], "unit": "TFLOP/s", "frac": tfs / pk["tf_burst"],
+                         "frac_of_sustained_peak": tfs / pk["tf_sust"],
+                         "traffic": tc_traffic, "traffic_source": tc_src,
                          "kernel": "mlp forward+loss+backward", "kernel_ms": kern_s * 1e3,
                          "kernel_share_of_step": (kern_ms / max(1, kern_n)) / (ms / K),
                          "kernel_timing": ("second pass of %d steps with CUDA events around every launch" % K) if N == 1
                          else "10 eager launches on the same shapes (graph replays cannot carry events)",
-                         "peak_source": pk["src"] + ", bf16 sustained",
+                         "peak_source": pk["src"] + ", bf16 burst",
                          "hbm_frac": BYTES_PER_SAMPLE * B / kern_s / 1e9 / pk["hbm"]},
             "e2e": {"value": e2e_value, "unit": "samples/s", "h2d_bytes_per_step": B * BYTES_PER_SAMPLE, "d2h_bytes_per_step": 4},
             "gpu_launches": launches_per_step * K,
@@ -443,10 +615,18 @@ def main():
                                  "sm_mhz_in_kernel: measured by the forward/backward kernel inside the timed region; NVML "
                                  "clock and reasons: every 4 ms during an identical untimed pass right after it (NVML "
                                  "use around the timed region slows the ranks' lock-step, see bench.py)")),
+            "sustained": sustained,
+            "predict": predict,
             "other_models": extras,
             "gilbert": {"metric": "gilbert_rows_per_s", "rows": g_rows * N, "variant": int(best), **gil[best], "all_variants": gil},
         }
+        if dp_parity is not None:
+            line["dp_parity"] = dp_parity
+        if sustained is not None:
+            sustained["frac_of_sustained_peak"] = sustained["value"] / N * TRAIN_FLOP_PER_SAMPLE / 1e12 / pk["tf_sust"]
+            sustained["note"] = "whole step (both kernels, launch hand-overs) over >= 2 s, against bf16_tflops_sustained"
         if N == 1 and not args.no_cpu_baseline:
+            line["gilbert"]["cpu_baseline"] = gilbert_cpu_baseline()
             rate1, _, _ = cpu_port_rate(8192, 2, warmup=1)
             rows = int(min(65536, max(4096, (rate1 * 1.0) // 4096 * 4096)))
             n_steps = int(max(3, min(2000, 15.0 * rate1 / rows)))      # ~15 s of CPU work

@@ -89,6 +89,9 @@ dp_allreduce_update_kernel(const dlas_opt_cfg cfg, float* __restrict__ p, float*
   for (int r = 0; r < MAXW; ++r) {         // rank order: bit-identical on every rank (absent ranks add +0)
     s.x += q[r].x; s.y += q[r].y; s.z += q[r].z; s.w += q[r].w;
   }
+  // a peer never announced this iteration: its bucket may be stale.  Poison every sum (parameters and loss become NaN on
+  // this rank) instead of applying a partial average -- the same failure the push/poll path shows (tc_reduce_kernel)
+  if (failed) s.x = s.y = s.z = s.w = __int_as_float(0x7fc00000);
   const float sv[4] = {s.x, s.y, s.z, s.w};
 #pragma unroll
   for (int e = 0; e < 4; ++e) {
@@ -100,7 +103,7 @@ dp_allreduce_update_kernel(const dlas_opt_cfg cfg, float* __restrict__ p, float*
       m[i] = mi;
       if (o.kind != 0) v[i] = vi;
     } else if (i == n && loss_ring) {
-      loss_ring[it % ring_len] = failed ? __int_as_float(0x7fc00000) : sv[e] * grad_scale;
+      loss_ring[it % ring_len] = sv[e] * grad_scale;
     }
   }
 }

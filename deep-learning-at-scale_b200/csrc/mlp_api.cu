@@ -23,13 +23,14 @@ int tc_grad(const int* dims, int n_layers, int loss, const float* params, const 
             const long long* cursor = nullptr, size_t parity_stride = 0);
 int tc_fit_step(const int* dims, int n_layers, int loss, const dlas_opt_cfg* cfg, float* params, float* m, float* v,
                 const float* X, const float* y, size_t n_rows, uint64_t iteration, float* loss_out, void* workspace,
-                size_t workspace_bytes, cudaStream_t st);
+                size_t workspace_bytes, cudaStream_t st, bool chained);
+int tc_status(const void* workspace, size_t workspace_bytes, cudaStream_t st);
 size_t tc_dp_recv_words(int world);
 int tc_dp_step(const int* dims, int n_layers, int loss, const dlas_opt_cfg* cfg, float* params, float* m, float* v,
                const float* X_base, const float* y_base, size_t batch_rows, dlas_step_state* state,
-               int64_t cursor0, int64_t iteration0, const uint64_t* recv_bases_dev, int rank, int world, float grad_scale,
-               int64_t n_batches, float* loss_ring, int64_t ring_len, int64_t n_steps, void* workspace, size_t workspace_bytes,
-               cudaStream_t st);
+               int64_t cursor0, int64_t iteration0, const int64_t* batch_order_host, const uint64_t* recv_bases_dev, int rank,
+               int world, float grad_scale, int64_t n_batches, float* loss_ring, int64_t ring_len, int64_t n_steps,
+               void* workspace, size_t workspace_bytes, cudaStream_t st);
 
 namespace {
 int check_common(const char* fn, const int* dims, int n_layers, int loss, int mode) {
@@ -125,7 +126,7 @@ extern "C" int dlas_mlp_fit_steps(const int* dims, int n_layers, int loss, int m
     const float* yb = y + (size_t)b * batch * dL;
     if (mode == DLAS_MODE_TC) {   // gradient kernel + (reduction fused with the update): two launches per step
       rc = tc_fit_step(dims, n_layers, loss, cfg, params, m, v, Xb, yb, batch, iteration0 + (uint64_t)s,
-                       step_losses ? step_losses + s : nullptr, workspace, workspace_bytes, st);
+                       step_losses ? step_losses + s : nullptr, workspace, workspace_bytes, st, /*chained=*/s > 0);
       if (rc != DLAS_OK) return rc;
       continue;
     }
@@ -169,7 +170,7 @@ extern "C" size_t dlas_mlp_dp_recv_bytes(const int* dims, int n_layers, int mode
 extern "C" int dlas_mlp_dp_step_at(const int* dims, int n_layers, int loss, int mode, const dlas_opt_cfg* cfg, float* params,
                                    float* m, float* v, const float* X_base, const float* y_base, size_t batch_rows,
                                    dlas_step_state* state_dev, int64_t cursor0, int64_t iteration0,
-                                   const uint64_t* recv_bases_dev, int rank, int world,
+                                   const int64_t* batch_order_host, const uint64_t* recv_bases_dev, int rank, int world,
                                    float grad_scale, int64_t n_batches, float* loss_ring, int64_t ring_len, int64_t n_steps,
                                    void* workspace, size_t workspace_bytes, void* stream) {
   DLAS_CHECK_DEVICE();
@@ -179,6 +180,19 @@ extern "C" int dlas_mlp_dp_step_at(const int* dims, int n_layers, int loss, int 
     set_error("dlas_mlp_dp_step_at: DLAS_MODE_TC only (fp32 mode: dlas_mlp_grad_at -> dlas_dp_allreduce_update -> dlas_step_advance)");
     return DLAS_ERR_UNSUPPORTED_SHAPE;
   }
-  return tc_dp_step(dims, n_layers, loss, cfg, params, m, v, X_base, y_base, batch_rows, state_dev, cursor0, iteration0, recv_bases_dev, rank, world,
+  return tc_dp_step(dims, n_layers, loss, cfg, params, m, v, X_base, y_base, batch_rows, state_dev, cursor0, iteration0, batch_order_host,
+                    recv_bases_dev, rank, world,
                     grad_scale, n_batches, loss_ring, ring_len, n_steps, workspace, workspace_bytes, (cudaStream_t)stream);
+}
+
+extern "C" int dlas_mlp_status(const int* dims, int n_layers, int mode, const void* workspace, size_t workspace_bytes,
+                               void* stream) {
+  DLAS_CHECK_DEVICE();
+  int rc = check_common("dlas_mlp_status", dims, n_layers, DLAS_LOSS_MSE, mode);
+  if (rc != DLAS_OK) return rc;
+  if (mode != DLAS_MODE_TC) {   // the fp32 kernels have no device-side failure mode to report; still a completion point
+    DLAS_CUDA(cudaStreamSynchronize((cudaStream_t)stream));
+    return DLAS_OK;
+  }
+  return tc_status(workspace, workspace_bytes, (cudaStream_t)stream);
 }

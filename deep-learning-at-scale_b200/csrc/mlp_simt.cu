@@ -15,6 +15,7 @@
 // Algorithmic work: 2*sum(in*out) flop forward and 4*sum(in*out) (minus the first layer's dX)
 // backward per row; 4*(in0+out) bytes per row from HBM.
 #include "common.cuh"
+#include <mutex>
 #include "simt_tiles.cuh"
 
 namespace dlas {
@@ -232,11 +233,13 @@ template <int KIND>
 int launch_main(const MlpDesc& d, int loss, const float* params, const float* WT, const float* X,
                 const float* y, size_t n_rows, float* partials, float* yhat, cudaStream_t st,
                 const long long* cursor = nullptr) {
-  static bool attr_set = false;
+  static bool attr_set[64] = {};   // per kernel instantiation AND per device: the attribute belongs to the device
   size_t smem = (size_t)d.smem_floats * sizeof(float);
-  if (!attr_set) {
+  int dev = 0;
+  DLAS_CUDA(cudaGetDevice(&dev));
+  if (dev < 0 || dev >= 64 || !attr_set[dev]) {
     DLAS_CUDA(cudaFuncSetAttribute(mlp_simt_kernel<KIND>, cudaFuncAttributeMaxDynamicSharedMemorySize, 227 * 1024));
-    attr_set = true;
+    if (dev >= 0 && dev < 64) attr_set[dev] = true;
   }
   mlp_simt_kernel<KIND><<<grid_size(), NT, smem, st>>>(d, loss, params, WT, X, y, n_rows, partials, yhat, cursor);
   DLAS_LAUNCH_CHECK();
@@ -335,7 +338,10 @@ int simt_predict(const int* dims, int n_layers, const float* params, const float
 // * In host code the array's name is only a stand-in, not a device address.  The first call on each
 //   device (with that device current) asks the runtime for the real address with
 //   cudaGetSymbolAddress and caches it; that first call should therefore be made before any stream
-//   capture begins.  Later calls only launch kernels and a memset.
+//   capture begins.  Because CUDA loads modules lazily, that first call is also when the driver
+//   places this array and the kernels on the GPU: make it (n_rows = 0 suffices) before the host's
+//   pool has taken all device memory, or set CUDA_MODULE_LOADING=EAGER.  Later calls only launch
+//   kernels and a memset and leave free device memory unchanged.
 // * All calls on a device share the one array and it keeps whatever the previous call left.  Each
 //   call clears the part it is about to use, and every CTA overwrites (not adds to) its slots on
 //   its first tile, so stale numbers are never read.  Two calls that overlap on the GPU (different
@@ -348,6 +354,7 @@ namespace {
 constexpr size_t kNoAllocFloats = DLAS_NOALLOC_SCRATCH_BYTES / sizeof(float);
 static __device__ __align__(256) float g_noalloc_scratch[kNoAllocFloats];
 float* g_noalloc_ptr[64];  // per device, filled on first use
+std::mutex g_noalloc_mu;   // two host threads making the very first call on one device
 }  // namespace
 }  // namespace dlas
 
@@ -373,12 +380,16 @@ extern "C" int dlas_mlp_grad_noalloc(const int* dims, int n_layers, int loss, co
   int dev = 0;
   DLAS_CUDA(cudaGetDevice(&dev));
   DLAS_REQUIRE(dev >= 0 && dev < 64, "dlas_mlp_grad_noalloc: device ordinal %d out of range", dev);
-  if (g_noalloc_ptr[dev] == nullptr) {  // once per device, with that device current
-    float* p = nullptr;
-    DLAS_CUDA(cudaGetSymbolAddress((void**)&p, g_noalloc_scratch));
-    g_noalloc_ptr[dev] = p;
+  float* scratch = nullptr;
+  {
+    std::lock_guard<std::mutex> lock(g_noalloc_mu);
+    if (g_noalloc_ptr[dev] == nullptr) {  // once per device, with that device current
+      float* p = nullptr;
+      DLAS_CUDA(cudaGetSymbolAddress((void**)&p, g_noalloc_scratch));
+      g_noalloc_ptr[dev] = p;
+    }
+    scratch = g_noalloc_ptr[dev];
   }
-  float* scratch = g_noalloc_ptr[dev];
   cudaStream_t st = (cudaStream_t)stream;
   if (n_rows == 0) {
     DLAS_CUDA(cudaMemsetAsync(grad_sum, 0, ((size_t)d.n_params + 1) * sizeof(float), st));

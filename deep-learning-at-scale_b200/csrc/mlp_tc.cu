@@ -130,7 +130,7 @@ __global__ void __cluster_dims__(2, 1, 1) __launch_bounds__(NT, 1)
 mlp_tc_kernel(const int loss_kind, const float* __restrict__ params, const float* __restrict__ X_base,
               const float* __restrict__ y_base, const size_t n_rows, float* __restrict__ partials,
               unsigned* __restrict__ err_flag, const unsigned call_id, long long* __restrict__ trace,
-              const long long* __restrict__ cursor) {
+              const long long* __restrict__ cursor, const int rows_ready) {
   // device-resident batch cursor (replayable steps): this launch works on rows [cursor*n_rows, (cursor+1)*n_rows)
   extern __shared__ __align__(1024) uint8_t smem[];
   float* f32 = reinterpret_cast<float*>(smem + S_F32);
@@ -177,10 +177,13 @@ mlp_tc_kernel(const int loss_kind, const float* __restrict__ params, const float
     for (int i = 0; i < XF / 4; ++i) xv[i] = in ? __ldcs(reinterpret_cast<const float4*>(src + i * 4)) : make_float4(0.f, 0.f, 0.f, 0.f);
     if (tid < TILE) yv = (row0 + tid < n_rows) ? __ldcs(y + row0 + tid) : 0.f;
   };
-  // The rows are inputs, not products of the previous kernel: with a host-side batch offset (no device cursor) the first
-  // tile's loads are issued before the dependency wait and complete under the weight set-up.
+  // rows_ready: the host states that X / y were NOT written by the kernel that precedes this one in the stream (the
+  // library's own step loops: the predecessor is the previous step's finishing kernel).  Only then, and with a host-side
+  // batch offset (no device cursor), the first tile's loads are issued before the dependency wait and complete under the
+  // weight set-up.  Single calls (dlas_mlp_grad, the first step of a loop) load after the wait: their predecessor may be
+  // the producer of the rows and may have released its dependents early.
   const int my_tiles = (n_tiles > (size_t)pair) ? (int)((n_tiles - pair + n_pairs - 1) / n_pairs) : 0;
-  const bool early_x = (cursor == nullptr);
+  const bool early_x = (cursor == nullptr) && rows_ready != 0;
   if (early_x && tid < N_EPI && my_tiles > 0) x_issue(pair, X_base, y_base);
   // Programmatic dependent launch: everything above overlaps the tail of the previous kernel in the stream
   // (the optimiser update that produced `params`); from here on its writes are visible.
@@ -701,20 +704,24 @@ __device__ __forceinline__ unsigned long long gtime() { unsigned long long t; as
 #endif
 __device__ unsigned g_fin_done = 0;       // blocks of the current FIN_EXCHANGE launch that have finished (reset by the last)
 
+// {value, epoch} travels as ONE 8-byte scalar access (low word = value bits, high word = epoch): an aligned .b64 access is
+// single-copy atomic, so a reader never sees the new epoch beside the old value (a .v2.b32 access is formally two scalar
+// accesses in unspecified order).
 __device__ __forceinline__ void st_push(unsigned long long addr, float v, unsigned epoch) {
-  asm volatile("st.relaxed.sys.global.v2.b32 [%0], {%1, %2};" ::"l"(addr), "r"(__float_as_uint(v)), "r"(epoch) : "memory");
+  const unsigned long long w = ((unsigned long long)epoch << 32) | (unsigned long long)__float_as_uint(v);
+  asm volatile("st.relaxed.sys.global.b64 [%0], %1;" ::"l"(addr), "l"(w) : "memory");
 }
 __device__ __forceinline__ uint2 ld_poll(unsigned long long addr) {
-  uint2 r;
-  asm volatile("ld.relaxed.sys.global.v2.b32 {%0, %1}, [%2];" : "=r"(r.x), "=r"(r.y) : "l"(addr) : "memory");
-  return r;
+  unsigned long long w;
+  asm volatile("ld.relaxed.sys.global.b64 %0, [%1];" : "=l"(w) : "l"(addr) : "memory");
+  return make_uint2((unsigned)(w & 0xffffffffull), (unsigned)(w >> 32));
 }
 
 constexpr int RG = 4;   // thread groups per block of 64 entries (8 measured no faster)
 constexpr int FIN_MAXW = 8;
 template <int MODE>
 __global__ void __launch_bounds__(64 * RG, 8)   // 8 blocks per SM: the whole grid is resident
-tc_reduce_kernel(const float* __restrict__ partials, int n_active_pairs, const unsigned* __restrict__ err_flag,
+tc_reduce_kernel(const float* __restrict__ partials, int n_active_pairs, unsigned* __restrict__ err_flag,
                  unsigned call_id, float* __restrict__ out, OptScalars opt, float grad_scale, float* __restrict__ params,
                  float* __restrict__ m, float* __restrict__ v, float* __restrict__ loss_out,
                  const long long* __restrict__ state, size_t parity_stride, const FinDp dp) {
@@ -765,7 +772,12 @@ tc_reduce_kernel(const float* __restrict__ partials, int n_active_pairs, const u
     for (int g2 = 0; g2 < RG - 1; ++g2) s += red[g2][threadIdx.x];
     // an mbarrier wait timed out inside this call's tcgen05 kernel: fail loudly, never return numbers
     if (*err_flag == call_id) s = __int_as_float(0x7fc00000);
+    // fp16 operands: a row value, activation or back-propagated term beyond +-65504 became inf in an operand tile, and
+    // inf (or inf * 0 = NaN) always reaches a gradient sum.  A non-finite sum is reported through the status words
+    // (dlas_mlp_status -> DLAS_ERR_RANGE); a diverged training raises the same flag.
+    if (!(fabsf(s) <= 3.0e38f)) err_flag[1] = call_id;
   }
+  if (blockIdx.x == 0 && threadIdx.x == 0) err_flag[2] = call_id;   // the launch the status words describe
   if (MODE != FIN_EXCHANGE) {
     if (grp > 0 || !live) return;
     if (MODE == FIN_GRAD) {
@@ -815,6 +827,7 @@ tc_reduce_kernel(const float* __restrict__ partials, int n_active_pairs, const u
 #pragma unroll
     for (int r = 0; r < FIN_MAXW; ++r) sum += q[r];          // rank order: bit-identical on every rank (absent ranks add +0)
     if (!ok) sum = __int_as_float(0x7fc00000);
+    if (!(fabsf(sum) <= 3.0e38f)) err_flag[1] = call_id;   // a peer's sum was non-finite, or the exchange timed out
     if (i == N_PARAMS) {
       if (dp.loss_ring) dp.loss_ring[it % dp.ring_len] = sum * grad_scale;
     } else {
@@ -845,7 +858,7 @@ unsigned g_call_id = 0x5eed0000u;
 
 int launch_main(int loss, const float* params, const float* X, const float* y, size_t n_rows, void* workspace,
                 size_t workspace_bytes, cudaStream_t st, float** partials_out, unsigned** err_out, int* n_active_pairs,
-                const long long* cursor = nullptr) {
+                const long long* cursor = nullptr, bool rows_ready = false) {
   size_t need = (size_t)n_ctas() * PSTRIDE * sizeof(float) + 256;
   if (workspace == nullptr || workspace_bytes < need) {
     set_error("mlp (tc): workspace of %zu bytes given, %zu needed", workspace_bytes, need);
@@ -854,20 +867,24 @@ int launch_main(int loss, const float* params, const float* X, const float* y, s
   DLAS_REQUIRE((((uintptr_t)X) & 15) == 0, "mlp (tc): X must be 16-byte aligned");
   float* partials = (float*)workspace;
   unsigned* err_flag = (unsigned*)((char*)workspace + (size_t)n_ctas() * PSTRIDE * sizeof(float));
-  static bool attr_set = false;
-  if (!attr_set) {
+  static bool attr_set[64] = {};   // the attribute is per device
+  int dev = 0;
+  DLAS_CUDA(cudaGetDevice(&dev));
+  if (dev < 0 || dev >= 64 || !attr_set[dev]) {
     DLAS_CUDA(cudaFuncSetAttribute(mlp_tc_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)SMEM_BYTES));
-    attr_set = true;
+    if (dev >= 0 && dev < 64) attr_set[dev] = true;
   }
   const int grid = n_ctas();
   ++g_call_id;   // the error word is never cleared: a kernel that times out writes THIS call's id into it
   int pi = prof_begin(DLAS_PROF_MLP_GRAD, st);
   long long* trace = nullptr;
-  const char* trace_path = getenv("DLAS_TC_TRACE");   // debug only: this branch allocates and synchronises
+#ifdef DLAS_TC_TRACE
+  const char* trace_path = getenv("DLAS_TC_TRACE");   // trace library only: this branch allocates and synchronises
   if (trace_path) {
     DLAS_CUDA(cudaMalloc(&trace, 1536 * sizeof(long long)));
     DLAS_CUDA(cudaMemsetAsync(trace, 0, 1536 * sizeof(long long), st));
   }
+#endif
   {
     cudaLaunchConfig_t cfg = {};
     cfg.gridDim = dim3(grid);
@@ -879,10 +896,12 @@ int launch_main(int loss, const float* params, const float* X, const float* y, s
     at[0].val.programmaticStreamSerializationAllowed = 1;
     cfg.attrs = at;
     cfg.numAttrs = 1;
-    DLAS_CUDA(cudaLaunchKernelEx(&cfg, mlp_tc_kernel, loss, params, X, y, n_rows, partials, err_flag, g_call_id, trace, cursor));
+    DLAS_CUDA(cudaLaunchKernelEx(&cfg, mlp_tc_kernel, loss, params, X, y, n_rows, partials, err_flag, g_call_id, trace, cursor,
+                                 rows_ready ? 1 : 0));
   }
   prof_end(pi, st);
   DLAS_LAUNCH_CHECK();
+#ifdef DLAS_TC_TRACE
   if (trace_path) {
     long long h[1536];
     DLAS_CUDA(cudaMemcpyAsync(h, trace, sizeof(h), cudaMemcpyDeviceToHost, st));
@@ -895,6 +914,7 @@ int launch_main(int loss, const float* params, const float* X, const float* y, s
       fclose(f);
     }
   }
+#endif
   size_t n_tiles = (n_rows + TILE - 1) / TILE;
   *n_active_pairs = (int)(n_tiles < (size_t)(grid / 2) ? n_tiles : (size_t)(grid / 2));
   *partials_out = partials;
@@ -903,7 +923,7 @@ int launch_main(int loss, const float* params, const float* X, const float* y, s
 }
 
 template <int MODE>
-int launch_reduce(cudaStream_t st, const float* partials, int nap, const unsigned* err, float* out, OptScalars o,
+int launch_reduce(cudaStream_t st, const float* partials, int nap, unsigned* err, float* out, OptScalars o,
                   float grad_scale, float* params, float* m, float* v, float* loss_out, const long long* state = nullptr,
                   size_t parity_stride = 0, const FinDp& dp = FinDp{}) {
   cudaLaunchConfig_t cfg = {};
@@ -934,6 +954,34 @@ size_t tc_workspace_bytes(const int* dims, int n_layers) {
   return tc > simt ? tc : simt;
 }
 
+// Status words at the end of the workspace (written by the kernels, never cleared): [0] id of the last launch in which an
+// mbarrier / exchange wait timed out, [1] id of the last launch that produced a non-finite gradient sum, [2] id of the
+// last launch.  A word describes the most recent launch iff it equals word [2]; NaN parameters keep every later launch
+// non-finite, so looking at the latest launch is enough.
+int tc_status(const void* workspace, size_t workspace_bytes, cudaStream_t st) {
+  const size_t off = (size_t)n_ctas() * PSTRIDE * sizeof(float);
+  if (workspace == nullptr || workspace_bytes < off + 256) {
+    set_error("dlas_mlp_status: workspace of %zu bytes given, %zu needed", workspace_bytes, off + 256);
+    return DLAS_ERR_WORKSPACE;
+  }
+  unsigned w[4] = {0u, 0u, 0u, 0u};
+  DLAS_CUDA(cudaMemcpyAsync(w, (const char*)workspace + off, sizeof(w), cudaMemcpyDeviceToHost, st));
+  DLAS_CUDA(cudaStreamSynchronize(st));
+  if (w[2] <= 0x5eed0000u || w[2] > g_call_id) return DLAS_OK;   // uninitialised memory: no launch of this process has used the workspace
+  if (w[0] == w[2]) {
+    set_error("tensor-core MLP step: a wait inside the kernels timed out (a peer rank did not deliver its sums, or the "
+              "GPU was pre-empted); the step's results were replaced by NaN");
+    return DLAS_ERR_TIMEOUT;
+  }
+  if (w[1] == w[2]) {
+    set_error("tensor-core MLP step: non-finite gradient sum.  DLAS_MODE_TC keeps rows, activations and back-propagated "
+              "terms as fp16 operands (|value| <= 65504, 11-bit significand); a value beyond that range became inf, or "
+              "the training diverged.  Rescale the feature / target columns or use DLAS_MODE_FP32");
+    return DLAS_ERR_RANGE;
+  }
+  return DLAS_OK;
+}
+
 // forward + loss + backward: grad_sum[0..n) gradient sums, grad_sum[n] loss sum
 int tc_grad(const int* dims, int n_layers, int loss, const float* params, const float* X, const float* y,
             size_t n_rows, float* grad_sum, void* workspace, size_t workspace_bytes, cudaStream_t st,
@@ -958,7 +1006,8 @@ int tc_grad(const int* dims, int n_layers, int loss, const float* params, const 
 // one whole single-GPU step: gradient kernel, then reduction fused with the optimiser update
 int tc_fit_step(const int* dims, int n_layers, int loss, const dlas_opt_cfg* cfg, float* params, float* m, float* v,
                 const float* X, const float* y, size_t n_rows, uint64_t iteration, float* loss_out, void* workspace,
-                size_t workspace_bytes, cudaStream_t st) {
+                size_t workspace_bytes, cudaStream_t st, bool chained) {
+  // chained: the kernel before this step in the stream is the previous step's finishing kernel of the same call
   if (!tc_supported(dims, n_layers)) {
     set_error("DLAS_MODE_TC supports the 32-256-256-1 network only");
     return DLAS_ERR_UNSUPPORTED_SHAPE;
@@ -968,7 +1017,7 @@ int tc_fit_step(const int* dims, int n_layers, int loss, const dlas_opt_cfg* cfg
   if (rc != DLAS_OK) return rc;
   DLAS_REQUIRE(o.kind == DLAS_OPT_SGD || v != nullptr, "Adam needs the second-moment buffer v");
   float* partials; unsigned* err; int nap;
-  rc = launch_main(loss, params, X, y, n_rows, workspace, workspace_bytes, st, &partials, &err, &nap);
+  rc = launch_main(loss, params, X, y, n_rows, workspace, workspace_bytes, st, &partials, &err, &nap, nullptr, chained);
   if (rc != DLAS_OK) return rc;
   rc = launch_reduce<FIN_UPDATE>(st, partials, nap, err, nullptr, o, 1.0f / (float)n_rows, params, m, v, loss_out);
   if (rc != DLAS_OK) return rc;
@@ -980,9 +1029,9 @@ int tc_fit_step(const int* dims, int n_layers, int loss, const dlas_opt_cfg* cfg
 size_t tc_dp_recv_words(int world) { return 2 * (size_t)world * (((size_t)N_PARAMS + 1 + 63) & ~(size_t)63); }
 int tc_dp_step(const int* dims, int n_layers, int loss, const dlas_opt_cfg* cfg, float* params, float* m, float* v,
                const float* X_base, const float* y_base, size_t batch_rows, dlas_step_state* state,
-               int64_t cursor0, int64_t iteration0, const uint64_t* recv_bases_dev, int rank, int world, float grad_scale,
-               int64_t n_batches, float* loss_ring, int64_t ring_len, int64_t n_steps, void* workspace, size_t workspace_bytes,
-               cudaStream_t st) {
+               int64_t cursor0, int64_t iteration0, const int64_t* batch_order_host, const uint64_t* recv_bases_dev, int rank,
+               int world, float grad_scale, int64_t n_batches, float* loss_ring, int64_t ring_len, int64_t n_steps,
+               void* workspace, size_t workspace_bytes, cudaStream_t st) {
   if (!tc_supported(dims, n_layers)) {
     set_error("DLAS_MODE_TC supports the 32-256-256-1 network only");
     return DLAS_ERR_UNSUPPORTED_SHAPE;
@@ -993,6 +1042,7 @@ int tc_dp_step(const int* dims, int n_layers, int loss, const dlas_opt_cfg* cfg,
   DLAS_REQUIRE(world >= 1 && world <= FIN_MAXW && rank >= 0 && rank < world, "dlas_mlp_dp_step_at: rank %d / world %d", rank, world);
   DLAS_REQUIRE(loss_ring == nullptr || ring_len >= 1, "dlas_mlp_dp_step_at: ring_len < 1");
   DLAS_REQUIRE(n_steps >= 0, "dlas_mlp_dp_step_at: n_steps < 0");
+  DLAS_REQUIRE(!(state && batch_order_host), "dlas_mlp_dp_step_at: batch_order_host needs the host-driven flavour (state_dev = NULL)");
   FinDp dp;
   dp.recv_bases = reinterpret_cast<const unsigned long long*>(recv_bases_dev);
   dp.rank = rank; dp.world = world;
@@ -1009,7 +1059,10 @@ int tc_dp_step(const int* dims, int n_layers, int loss, const dlas_opt_cfg* cfg,
     OptScalars o{};
     const float* Xs = X_base; const float* ys = y_base;
     if (!state) {   // host-driven: batch offset and step scalars computed here, exactly as dlas_mlp_fit_steps does
-      const size_t b = (size_t)((cursor0 + s) % n_batches);
+      const int64_t bo = batch_order_host ? batch_order_host[s] : (cursor0 + s) % n_batches;   // model.fit's shuffled order
+      DLAS_REQUIRE(bo >= 0 && bo < n_batches, "dlas_mlp_dp_step_at: batch index %lld out of range (%lld batches)", (long long)bo,
+                   (long long)n_batches);
+      const size_t b = (size_t)bo;
       Xs += b * batch_rows * D0;
       ys += b * batch_rows;
       dp.it_host = iteration0 + s;
@@ -1017,7 +1070,7 @@ int tc_dp_step(const int* dims, int n_layers, int loss, const dlas_opt_cfg* cfg,
       if (rc != DLAS_OK) return rc;
     }
     int rc = launch_main(loss, params, Xs, ys, batch_rows, workspace, workspace_bytes, st, &partials, &err, &nap,
-                         reinterpret_cast<const long long*>(state));
+                         reinterpret_cast<const long long*>(state), /*rows_ready=*/s > 0);
     if (rc != DLAS_OK) return rc;
     rc = launch_reduce<FIN_EXCHANGE>(st, partials, nap, err, nullptr, o, grad_scale, params, m, v, nullptr, nullptr, 0, dp);
     if (rc != DLAS_OK) return rc;

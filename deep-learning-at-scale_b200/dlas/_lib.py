@@ -49,6 +49,7 @@ SIGNATURES = {
     "dlas_mlp_mode_supported": (_i, [_ip, _i, _i]),
     "dlas_mlp_workspace_bytes": (_sz, [_ip, _i, _i]),
     "dlas_mlp_grad": (_i, [_ip, _i, _i, _i, _p, _p, _p, _sz, _p, _p, _sz, _p]),
+    "dlas_mlp_status": (_i, [_ip, _i, _i, _p, _sz, _p]),
     "dlas_opt_step": (_i, [C.POINTER(OptCfg), _p, _p, _p, _p, _sz, _f, _u64, _p, _p]),
     "dlas_mlp_grad_at": (_i, [_ip, _i, _i, _i, _p, _p, _p, _sz, _p, _p, _sz, _p, _sz, _p]),
     "dlas_dp_allreduce_update": (_i, [C.POINTER(OptCfg), _p, _p, _p, _p, _i, _i, _sz, _sz, _sz, _f, _p, _p, C.c_int64, _p]),
@@ -61,7 +62,7 @@ SIGNATURES = {
     "dlas_mlp_grad_noalloc": (_i, [_ip, _i, _i, _p, _p, _p, _sz, _p, _p]),
     "dlas_prof_sm_clock": (_i, [C.POINTER(C.c_double), _i]),
     "dlas_mlp_dp_recv_bytes": (_sz, [_ip, _i, _i, _i]),
-    "dlas_mlp_dp_step_at": (_i, [_ip, _i, _i, _i, _p, _p, _p, _p, _p, _p, _sz, _p, _i64, _i64, _p, _i, _i, _f, _i64, _p, _i64, _i64, _p, _sz, _p]),
+    "dlas_mlp_dp_step_at": (_i, [_ip, _i, _i, _i, _p, _p, _p, _p, _p, _p, _sz, _p, _i64, _i64, C.POINTER(C.c_int64), _p, _i, _i, _f, _i64, _p, _i64, _i64, _p, _sz, _p]),
     "dlas_lstm_n_params": (_sz, [_i, _i, _i]),
     "dlas_lstm_workspace_bytes": (_sz, [_i, _i, _i, _i, _sz]),
     "dlas_lstm_grad": (_i, [_i, _i, _i, _i, _i, _p, _p, _p, _sz, _p, _p, _sz, _p]),

@@ -215,12 +215,21 @@ class Sequential:
         return self._delegate(CnnRegressor(L, conv.filter_length, conv.nb_filter, dense.output_dim, drop, seed=self.seed,
                                            device=self.device), loss, optimizer)
 
-    def compile(self, loss="mse", optimizer=None, averaging="gradient", average_every=1):
+    def compile(self, loss="mse", optimizer=None, averaging="gradient", average_every=1, exchange="auto"):
         """averaging="gradient" (default): synchronous mean-gradient averaging every step, the parity semantics of
         SURVEY.md 8e.  averaging="parameter": Spark-driver-style periodic parameter averaging -- `average_every`
-        local steps per rank between averages of parameters and optimiser state."""
+        local steps per rank between averages of parameters and optimiser state.
+        exchange (world > 1, gradient averaging): "auto" = the library's two-launch step with the NVLink push/poll
+        exchange inside its finishing kernel (dlas_mlp_dp_step_at) where the mode supports it and the ranks' memory
+        can be mapped, else NCCL; "peer" = require it; "nccl" = all-reduce of the flat bucket between our kernels."""
         if averaging not in ("gradient", "parameter"):
             raise ValueError("averaging must be 'gradient' or 'parameter'")
+        if exchange not in ("auto", "peer", "nccl"):
+            raise ValueError("exchange must be 'auto', 'peer' or 'nccl'")
+        self.exchange = exchange
+        self._recv = None
+        self._recv_tried = False
+        self.dp_path = None
         self.average_every = int(average_every) if averaging == "parameter" else 0
         if not self.layers:
             raise ValueError("add layers before compile")
@@ -302,10 +311,55 @@ class Sequential:
             t = torch.as_tensor(np.asarray(a, dtype=np.float32), device=self.device)
         return t.reshape(-1, cols).contiguous()
 
+    def _dp_recv(self):
+        """The receive buffer of the push/poll exchange (world > 1, tensor-core mode), created and mapped on first use;
+        None when this model trains through NCCL instead (fp32 mode, exchange="nccl", parameter averaging, or the
+        ranks' memory cannot be mapped).  Every rank takes the same branch: the mapping is a collective."""
+        if self._recv_tried:
+            return self._recv
+        self._recv_tried = True
+        self.dp_path = "single" if self.world == 1 else "nccl"
+        if self.world == 1 or self.exchange == "nccl" or getattr(self, "average_every", 0) > 0:
+            return None
+        n_recv = ops.mlp_dp_recv_bytes(self.dims, self.mode, self.world)
+        if not n_recv:
+            if self.exchange == "peer":
+                raise _lib.DlasError(-5, "exchange='peer': dlas_mlp_dp_step_at does not support mode %d / widths %s" % (self.mode, self.dims))
+            return None
+        try:
+            self._recv = parallel.PeerRecvBuffer(n_recv, self.device)
+        except Exception as e:   # no symmetric-memory support between these GPUs: NCCL path (still no CPU path)
+            if self.exchange == "peer":
+                raise
+            print("dlas: peer-memory receive buffer unavailable (%s); using the NCCL all-reduce" % (e,))
+            return None
+        self._ring = torch.zeros(4096, dtype=torch.float32, device=self.device)
+        self.dp_path = "peer-push"
+        return self._recv
+
+    def _push_steps(self, X, Y, local_rows, global_rows, order=None, n_steps=1):
+        """n_steps data-parallel steps through dlas_mlp_dp_step_at (host-driven flavour) on batches `order` of
+        (X, Y); returns the ring indices holding their batch-mean losses."""
+        recv = self._recv
+        n_batches = max(1, X.shape[0] // local_rows)
+        if order is not None:
+            n_steps = len(order)
+        if n_steps > self._ring.numel():
+            self._ring = torch.zeros(n_steps, dtype=torch.float32, device=self.device)
+        it0 = self.iterations
+        ops.mlp_dp_step_at(self.dims, self.loss, self.mode, self.cfg, self.params, self.m, self.v, X, Y, local_rows, None,
+                           recv.bases, self.rank, self.world, 1.0 / float(global_rows), n_batches, self._ring, self.workspace,
+                           n_steps=n_steps, cursor0=0, iteration0=it0, batch_order=order)
+        self.iterations += n_steps
+        return (torch.arange(it0, it0 + n_steps, device=self.device) % self._ring.numel())
+
     def train_on_batch(self, X, y, global_rows=None):
         """One optimiser step on this rank's shard (X, y) of one global batch; returns the device
         scalar holding the global batch-mean loss (the LOCAL shard's mean loss in parameter-averaging mode)."""
         dims = self.dims
+        if self.world > 1 and self._dp_recv() is not None:
+            rows = global_rows if global_rows is not None else X.shape[0] * self.world
+            return self._ring[self._push_steps(X, y, X.shape[0], rows)]
         if getattr(self, "average_every", 0) > 0 and self.world > 1:
             # periodic PARAMETER averaging (optional mode): local step on the local mean gradient, no per-step collective;
             # every `average_every` steps parameters and optimiser state are replaced by their mean over ranks
@@ -343,6 +397,15 @@ class Sequential:
         n_local = X.shape[0]
         n_full = n_local // local_batch
         rem = n_local - n_full * local_batch
+        if self.world > 1:
+            # every rank must run the same number of steps of the same sizes: a rank with one batch more would wait for
+            # sums that never come (unequal shards are a caller error, not something to paper over)
+            mine = torch.tensor([n_full, -n_full, rem, -rem], dtype=torch.int64, device=self.device)
+            torch.distributed.all_reduce(mine, op=torch.distributed.ReduceOp.MAX)
+            if int(mine[0]) != -int(mine[1]) or int(mine[2]) != -int(mine[3]):
+                raise ValueError("fit: ranks hold different numbers of rows (this rank: %d full batches + %d rows); shard the "
+                                 "rows with dlas.parallel.local_rows so that every rank owns the same share of every batch" % (n_full, rem))
+            self._dp_recv()
         history = {"loss": [], "val_loss": []}
         callbacks = callbacks or []
         for epoch in range(n_epochs):
@@ -360,6 +423,12 @@ class Sequential:
                     ops.mlp_fit_steps(dims, self.loss, self.mode, self.cfg, self.params, self.m, self.v, Xr, Yr,
                                       rem, 1, self.iterations, losses[n_full:], self.grad_sum, self.workspace)
                     self.iterations += 1
+            elif self._recv is not None:
+                # the library's own data-parallel step (two launches, exchange inside the finishing kernel), one call per epoch
+                if n_full:
+                    losses[:n_full] = self._ring[self._push_steps(X, Y, local_batch, batch_size, order=order)]
+                if rem:
+                    losses[n_full:] = self._ring[self._push_steps(X[n_full * local_batch:], Y[n_full * local_batch:], rem, rem * self.world)]
             else:
                 for s in range(n_full):
                     b = int(order[s])
@@ -374,6 +443,7 @@ class Sequential:
             if rem:
                 w[-1] = float(rem)
             logs = {"loss": float((losses * w).sum().item() / max(1, n_local))}
+            ops.mlp_status(dims, self.mode, self.workspace)     # raises if a step failed on the device (timeout, fp16 range)
             if validation_data is not None:
                 logs["val_loss"] = self.evaluate(Xv, Yv)
             history["loss"].append(logs["loss"])
@@ -415,7 +485,10 @@ class Sequential:
             try:
                 n_recv = ops.mlp_dp_recv_bytes(dims, self.mode, self.world)
                 if n_recv:      # tensor-core mode: forward/backward + ONE kernel for reduce, exchange, update and advance
-                    recv = parallel.PeerRecvBuffer(n_recv, self.device)
+                    recv = self._recv if self._recv is not None else parallel.PeerRecvBuffer(n_recv, self.device)
+                    self._recv, self._recv_tried = recv, True
+                    if not hasattr(self, "_ring"):
+                        self._ring = torch.zeros(4096, dtype=torch.float32, device=self.device)
                 else:
                     bucket = parallel.PeerBucket(self.n_params, self.device)
             except Exception as e:   # no symmetric-memory support between these GPUs: NCCL path (still no CPU path)
@@ -482,6 +555,7 @@ class Sequential:
             self._copy_stream = torch.cuda.Stream(device=self.device)
             self._ready = [torch.cuda.Event() for _ in range(2)]
             self._free = [torch.cuda.Event() for _ in range(2)]
+            self._host_loss = torch.zeros(64, dtype=torch.float32, device=self.device)
         main = torch.cuda.current_stream()
         for ev in self._free:
             ev.record(main)
@@ -495,7 +569,14 @@ class Sequential:
                 self._hb[k][1].copy_(yv[b * lb:(b + 1) * lb], non_blocking=True)
                 self._ready[k].record(self._copy_stream)
             main.wait_event(self._ready[k])
-            lo = self.train_on_batch(self._hb[k][0], self._hb[k][1], global_rows=batch_size)
+            if self.world == 1 and getattr(self, "average_every", 0) == 0:
+                # single GPU: the library's step loop on the staging buffer (gradient kernel + reduction fused with the update)
+                lo = self._host_loss[s % 64:s % 64 + 1]
+                ops.mlp_fit_steps(dims, self.loss, self.mode, self.cfg, self.params, self.m, self.v, self._hb[k][0], self._hb[k][1],
+                                  lb, 1, self.iterations, lo, self.grad_sum, self.workspace)
+                self.iterations += 1
+            else:   # world > 1: dlas_mlp_dp_step_at on the staging buffer (push/poll exchange), or the NCCL step
+                lo = self.train_on_batch(self._hb[k][0], self._hb[k][1], global_rows=batch_size)
             losses_host[s:s + 1].copy_(lo, non_blocking=True)
             self._free[k].record(main)
         return losses_host

@@ -102,6 +102,12 @@ def mlp_grad(dims, loss, mode, params, X, y, grad_sum, workspace, n_rows=None):
     return grad_sum
 
 
+def mlp_status(dims, mode, workspace):
+    """Synchronise the current stream and raise DlasError if a step enqueued with this workspace failed on the device
+    (DLAS_ERR_TIMEOUT = -6, DLAS_ERR_RANGE = -7: the fp16 operand range of the tensor-core mode was exceeded)."""
+    check(_lib.load().dlas_mlp_status(int_array(dims), len(dims) - 1, int(mode), ptr(workspace), workspace.numel(), stream_ptr()))
+
+
 def opt_step(cfg, params, m, v, grad_sum, grad_scale, iteration, loss_out=None):
     check(_lib.load().dlas_opt_step(C.byref(cfg), ptr(params), ptr(m), ptr(v), ptr(grad_sum), params.numel(),
                                     float(grad_scale), int(iteration), ptr(loss_out), stream_ptr()))
@@ -245,11 +251,16 @@ def mlp_dp_recv_bytes(dims, mode, world):
 
 
 def mlp_dp_step_at(dims, loss, mode, cfg, params, m, v, X_base, y_base, batch_rows, state, recv_bases, rank, world, grad_scale,
-                   n_batches, loss_ring, workspace, n_steps=1, cursor0=0, iteration0=0):
-    """n_steps whole data-parallel steps (DLAS_MODE_TC): forward/backward kernel + the reduce/push/poll/update/advance kernel."""
+                   n_batches, loss_ring, workspace, n_steps=1, cursor0=0, iteration0=0, batch_order=None):
+    """n_steps whole data-parallel steps (DLAS_MODE_TC): forward/backward kernel + the reduce/push/poll/update/advance kernel.
+    batch_order (host-driven flavour only): the batch index of every step, e.g. model.fit's shuffled epoch order."""
+    order = None
+    if batch_order is not None:
+        order = (C.c_int64 * len(batch_order))(*[int(b) for b in batch_order])
+        n_steps = len(batch_order)
     check(_lib.load().dlas_mlp_dp_step_at(int_array(dims), len(dims) - 1, int(loss), int(mode), C.byref(cfg), ptr(params), ptr(m),
                                           ptr(v), ptr(X_base), ptr(y_base), int(batch_rows), ptr(state), int(cursor0),
-                                          int(iteration0), ptr(recv_bases), int(rank), int(world), float(grad_scale), int(n_batches), ptr(loss_ring),
+                                          int(iteration0), order, ptr(recv_bases), int(rank), int(world), float(grad_scale), int(n_batches), ptr(loss_ring),
                                           0 if loss_ring is None else loss_ring.numel(), int(n_steps), ptr(workspace),
                                           workspace.numel(), stream_ptr()))
 

@@ -36,10 +36,55 @@ def parser(description):
     ap.add_argument("--optimizer", default="sgd", choices=["sgd", "adam"])
     ap.add_argument("--mode", default="fp32", choices=["fp32", "tc"])
     ap.add_argument("--seed", type=int, default=ops.BASE_SEED)
+    ap.add_argument("--gpus", type=int, default=1,
+                    help="data-parallel training on G GPUs of this box: the script re-launches itself as G ranks "
+                         "(torch.distributed.run); under torchrun the ranks are taken from the environment")
+    ap.add_argument("--master-port", type=int, default=29541)
     ap.add_argument("--one-hot", action="store_true",
                     help="with --data: encode string columns as cnn.py:72-91 does (StringIndexer -> OneHotEncoder) and put "
                          "them in front of the continuous columns (cnn.py:93-99); host-side, fitted once on all rows")
     return ap
+
+
+def init_distributed(args):
+    """One process per GPU (SURVEY.md 8e).  `--gpus G` outside torchrun re-launches this script as G ranks on 127.0.0.1;
+    inside a rank: bind the GPU, join the NCCL process group, and leave printing to rank 0.  Returns (rank, world)."""
+    world = int(os.environ.get("WORLD_SIZE", "1"))
+    if world == 1 and getattr(args, "gpus", 1) > 1:
+        import subprocess
+        cmd = [sys.executable, "-m", "torch.distributed.run", "--nnodes=1", "--nproc-per-node", str(args.gpus),
+               "--master-addr", "127.0.0.1", "--master-port", str(args.master_port), sys.argv[0]] + sys.argv[1:]
+        raise SystemExit(subprocess.call(cmd))
+    if world == 1:
+        return 0, 1
+    import torch.distributed as dist
+    rank, local = int(os.environ["RANK"]), int(os.environ.get("LOCAL_RANK", "0"))
+    torch.cuda.set_device(local)
+    os.environ.setdefault("MASTER_ADDR", "127.0.0.1")
+    dist.init_process_group("nccl", device_id=torch.device("cuda", local))
+    if rank != 0:
+        sys.stdout = open(os.devnull, "w")      # the reference prints once (cnn.py:62,:73,:133-134): rank 0 does
+    return rank, world
+
+
+def shard(parts, batch_size, rank, world):
+    """This rank's rows of the train / validation / test parts.  Train: the rank's contiguous 1/world slice of every global
+    batch (dlas.parallel.local_rows), and the same share of the ragged tail (at most world-1 rows are dropped so that every
+    rank runs the same steps); validation / test: every world-th row (evaluate() pools sums and counts over the ranks)."""
+    if world == 1:
+        return parts
+    from dlas import parallel
+    (Xt, yt), val, test = parts
+    n = Xt.shape[0]
+    n_whole = n // batch_size * batch_size
+    idx = parallel.local_rows(n_whole, batch_size, rank, world).to(Xt.device)
+    tail = (n - n_whole) // world
+    if tail:
+        idx = torch.cat([idx, torch.arange(n_whole + rank * tail, n_whole + (rank + 1) * tail, device=Xt.device)])
+    out = [(Xt.index_select(0, idx).contiguous(), yt.index_select(0, idx).contiguous())]
+    for X, y in (val, test):
+        out.append((X[rank::world].contiguous(), y[rank::world].contiguous()))
+    return out
 
 
 def schema(args):
@@ -128,4 +173,11 @@ def train_and_report(model, args, name, train, val, test):
     test_set_loss = model.test_on_batch(test[0], test[1])                                               # cnn.py:132
     print("\nTime elapsed: %f s" % time_elapsed)                                                        # cnn.py:133
     print("Testing set loss: %f" % test_set_loss)                                                       # cnn.py:134
+    if getattr(model, "world", 1) > 1 or getattr(getattr(model, "_impl", None), "world", 1) > 1:
+        # mapped peer memory and NCCL communicators: leave without the collective teardown (as bench.py does)
+        import torch.distributed as dist
+        sys.stdout.flush()
+        torch.cuda.synchronize()
+        dist.barrier()
+        os._exit(0)
     return time_elapsed, test_set_loss

@@ -28,6 +28,8 @@ extern "C" {
 #define DLAS_ERR_UNSUPPORTED_DEVICE (-3)
 #define DLAS_ERR_WORKSPACE (-4)
 #define DLAS_ERR_UNSUPPORTED_SHAPE (-5)
+#define DLAS_ERR_TIMEOUT (-6)   /* a bounded wait inside a kernel expired (dlas_mlp_status)                 */
+#define DLAS_ERR_RANGE (-7)     /* fp16 operand range of DLAS_MODE_TC exceeded / non-finite gradient sums   */
 
 /* losses: cnn.py:29-32 (mae_clip); MSE from BASELINE.json config 1 */
 #define DLAS_LOSS_MSE 0
@@ -37,8 +39,13 @@ extern "C" {
 #define DLAS_OPT_ADAM 1
 /* arithmetic mode of the MLP kernels */
 #define DLAS_MODE_FP32 0   /* CUDA-core fp32, any layer widths                                   */
-#define DLAS_MODE_TC 1     /* tcgen05 tensor cores: fp16 operands (10-bit mantissa, as TF32),
-                              fp32 accumulation in TMEM; fixed shapes, see dlas_mlp_mode_supported */
+#define DLAS_MODE_TC 1     /* tcgen05 tensor cores: fp16 operands, fp32 accumulation in TMEM; fixed shapes,
+                              see dlas_mlp_mode_supported.  A REDUCED-RANGE mode: rows, hidden activations
+                              and back-propagated terms are rounded to fp16 -- TF32's 11-bit significand but
+                              a 5-bit exponent: |value| <= 65504, full precision down to 6.1e-5, flushed to
+                              zero below 6e-8.  Feed it standardised columns (raw wellhead pressures of a
+                              few thousand psig fit; cumulative volumes or timestamps do not).  Overflow is
+                              detected, never silent: dlas_mlp_status returns DLAS_ERR_RANGE.            */
 /* Gilbert kernel variants (same results within the stated 1e-6; differ in instruction mix) */
 #define DLAS_GILBERT_POLY 0  /* polynomial log2 for all three inputs                              */
 #define DLAS_GILBERT_MUFU 7  /* bit i set: input i (P,S,R) takes its mantissa log2 from MUFU.LG2  */
@@ -108,9 +115,20 @@ size_t dlas_mlp_workspace_bytes(const int* dims, int n_layers, int mode);
  * without the optimiser update.  Writes grad_sum[0..n_params) = SUM over rows of per-row
  * gradients (no 1/batch factor) and grad_sum[n_params] = SUM of per-row losses, so that
  * data-parallel shards can be added before the step.  Deterministic reduction order. */
+/* DLAS_MODE_TC only: the launch may start while the preceding kernel of the stream is still draining
+ * (programmatic dependent launch); X, y and params are read only after that kernel has completed, so a
+ * producer kernel enqueued just before this call is safe.  (The library's own multi-step loops load
+ * the next batch early; they know their predecessor.) */
 int dlas_mlp_grad(const int* dims, int n_layers, int loss, int mode, const float* params,
                   const float* X, const float* y, size_t n_rows, float* grad_sum, void* workspace,
                   size_t workspace_bytes, void* stream);
+
+/* Completion and health of the steps enqueued so far on `stream` with this workspace (no reference counterpart: Keras
+ * raises from inside fit).  Synchronises the stream, then returns DLAS_OK, DLAS_ERR_TIMEOUT (a bounded wait inside the
+ * kernels expired; that step's results are NaN) or DLAS_ERR_RANGE (DLAS_MODE_TC: a gradient sum was not finite -- an
+ * fp16 operand overflowed, see DLAS_MODE_TC, or the training diverged).  DLAS_MODE_FP32 only synchronises. */
+int dlas_mlp_status(const int* dims, int n_layers, int mode, const void* workspace, size_t workspace_bytes,
+                    void* stream);
 
 /* Optimiser update (cnn.py:117 SGD; Adam): g = grad_sum*grad_scale; `iteration` counts batches
  * already applied (Keras `iterations`).  m is the SGD velocity / Adam first moment, v the Adam
@@ -153,7 +171,7 @@ int dlas_step_advance(dlas_step_state* state_dev, int64_t n_batches, void* strea
  * the `world` buckets in rank order (so all ranks compute bit-identical sums) and applies dlas_opt_step_at's update
  * with g = sum * grad_scale.  No host work, no NCCL call; replayable in a CUDA graph.  The stream order must be
  * dlas_mlp_grad_at(..., grad_sum = own bucket, parity_stride) -> this call -> dlas_step_advance.  A rank that does
- * not see its peers within a bounded spin writes NaN into the loss ring instead of hanging. */
+ * not see its peers within a bounded spin writes NaN into its parameters and the loss ring instead of hanging. */
 int dlas_dp_allreduce_update(const dlas_opt_cfg* cfg, float* params, float* m, float* v,
                              const uint64_t* peer_bases_dev, int rank, int world, size_t n,
                              size_t parity_stride, size_t flags_offset, float grad_scale,
@@ -169,9 +187,10 @@ int dlas_dp_allreduce_update(const dlas_opt_cfg* cfg, float* params, float* m, f
  * (cursor = (cursor + 1) % n_batches, iteration += 1).  One NVLink one-way latency per step; no flags, no NCCL call,
  * the call only enqueues 2*n_steps launches chained by programmatic dependent launch.  With state_dev != NULL the
  * cursor and iteration are read from (and advanced in) device memory, so the call can be captured in a CUDA graph and
- * replayed; with state_dev == NULL the call is host-driven: step s works on batch (cursor0 + s) % n_batches with the
- * schedule of iteration iteration0 + s (the forward/backward kernel then loads its first rows before the previous
- * step has finished).  Every rank owns a receive buffer of dlas_mlp_dp_recv_bytes(...) bytes,
+ * replayed; with state_dev == NULL the call is host-driven: step s works on batch batch_order_host[s] (model.fit's
+ * shuffled epoch order, n_steps entries) or, with batch_order_host == NULL, on batch (cursor0 + s) % n_batches, with the
+ * schedule of iteration iteration0 + s (from the second step of a call on, the forward/backward kernel loads its first
+ * rows before the previous step has finished).  world == 1 is allowed (no peer, same two launches).  Every rank owns a receive buffer of dlas_mlp_dp_recv_bytes(...) bytes,
  * ZEROED once by the caller, in memory its peers can store to (CUDA IPC / VMM / symmetric memory);
  * recv_bases_dev[r] = the address under which THIS process reaches rank r's buffer.  A rank whose peers' words do not
  * arrive within a bounded spin writes NaN into its parameters and loss ring instead of hanging. */
@@ -179,7 +198,7 @@ size_t dlas_mlp_dp_recv_bytes(const int* dims, int n_layers, int mode, int world
 int dlas_mlp_dp_step_at(const int* dims, int n_layers, int loss, int mode, const dlas_opt_cfg* cfg, float* params,
                         float* m, float* v, const float* X_base, const float* y_base, size_t batch_rows,
                         dlas_step_state* state_dev, int64_t cursor0, int64_t iteration0,
-                        const uint64_t* recv_bases_dev, int rank, int world,
+                        const int64_t* batch_order_host, const uint64_t* recv_bases_dev, int rank, int world,
                         float grad_scale, int64_t n_batches, float* loss_ring, int64_t ring_len, int64_t n_steps,
                         void* workspace, size_t workspace_bytes, void* stream);
 
@@ -206,11 +225,16 @@ int dlas_mlp_eval_loss(const int* dims, int n_layers, int loss, int mode, const 
  * plug-in inside an executor that owns and has locked all device memory, a serving loop that bans
  * allocator calls because they stall the device).  Same arguments and results as dlas_mlp_grad in
  * DLAS_MODE_FP32; the per-CTA gradient partials live in a device array built into the library:
- * DLAS_NOALLOC_SCRATCH_BYTES per GPU, held from library load until the process exits.  Layer widths
- * that need more scratch than that are refused with DLAS_ERR_WORKSPACE.  It calls no allocating
- * routine.  The first call on each device looks up the array's device address, so make that call
- * before any stream capture starts.  All calls share the array: calls that overlap on the GPU
- * (two streams, two threads) race -- keep them on one stream. */
+ * DLAS_NOALLOC_SCRATCH_BYTES per GPU, held until the process exits.  Layer widths that need more
+ * scratch than that are refused with DLAS_ERR_WORKSPACE.  It calls no allocating routine.
+ * The FIRST call on each device is a warm-up: it looks up the array's device address, and -- CUDA
+ * loads modules lazily (the default since CUDA 12.2, and always with the static runtime this library
+ * links) -- it is also the moment the driver places the library's kernels and this array on that GPU.
+ * Make that first call (n_rows = 0 is enough) before the host's pool takes the rest of device memory
+ * and before any stream capture starts, or run the process with CUDA_MODULE_LOADING=EAGER; from the
+ * second call on a device onwards nothing is loaded and free device memory does not change.
+ * All calls share the array: calls that overlap on the GPU (two streams, two threads) race -- keep
+ * them on one stream. */
 #define DLAS_NOALLOC_SCRATCH_BYTES (4u << 20)
 int dlas_mlp_grad_noalloc(const int* dims, int n_layers, int loss, const float* params,
                           const float* X, const float* y, size_t n_rows, float* grad_sum,

@@ -42,11 +42,14 @@ def _both(_lib, ops, dims, loss, p, X, y):
     ref = torch.zeros(n + 1, device="cuda")
     ops.mlp_grad(dims, loss, _lib.MODE_FP32, p, X, y, ref, ops.mlp_workspace(dims, _lib.MODE_FP32))
     got = torch.full((n + 1,), float("nan"), device="cuda")
+    torch.cuda.synchronize()
+    free0 = torch.cuda.mem_get_info()[0]
     rc = lib.dlas_mlp_grad_noalloc(_lib.int_array(dims), len(dims) - 1, loss, _lib.ptr(p), _lib.ptr(X), _lib.ptr(y),
                                    X.shape[0], _lib.ptr(got), _lib.stream_ptr())
     assert rc == 0, lib.dlas_last_error()
     torch.cuda.synchronize()
-    return got.cpu().numpy(), ref.cpu().numpy()
+    taken = free0 - torch.cuda.mem_get_info()[0]     # device memory the call itself took (cudaMemGetInfo)
+    return got.cpu().numpy(), ref.cpu().numpy(), taken
 
 
 def test_two_calls_in_a_row_match_the_workspace_entry_point(env):
@@ -55,9 +58,13 @@ def test_two_calls_in_a_row_match_the_workspace_entry_point(env):
     p = _cuda(O.glorot_init(dims, 11))
     # first call: 6000 rows (all CTAs busy); second call: 70 rows, other data, other loss -- only three
     # CTAs get a tile, the rest of the array still holds the first call's partials
-    for n_rows, start, loss in ((6000, 0, 0), (70, 9000, 1)):
+    for call, (n_rows, start, loss) in enumerate(((6000, 0, 0), (70, 9000, 1))):
         Xh, yh = O.synth_rows(O.BASE_SEED, start, n_rows, dims[0])
-        got, ref = _both(_lib, ops, dims, loss, p, _cuda(Xh), _cuda(yh * 8))
+        got, ref, taken = _both(_lib, ops, dims, loss, p, _cuda(Xh), _cuda(yh * 8))
+        # The first call on a device may be the one that makes the driver load the library's module (kernels + the
+        # built-in array: CUDA loads lazily); from the second call on, free device memory must not move at all.
+        if call > 0:
+            assert taken == 0, "dlas_mlp_grad_noalloc took %d bytes of device memory on its second call" % taken
         assert np.isfinite(got).all()
         assert got[-1] == pytest.approx(ref[-1], rel=TOL)          # loss sum
         assert _relerr(got[:-1], ref[:-1]) < TOL                    # gradient sums

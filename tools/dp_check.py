@@ -16,7 +16,10 @@ from dlas import parallel  # noqa: E402
 import dlas_oracle as O  # noqa: E402
 
 mode = sys.argv[1] if len(sys.argv) > 1 else "fp32"
-path = "eager"          # eager: train_on_batch + NCCL; graph: replayed step + NCCL; peer: replayed step + our NVLink kernel
+# path: eager = train_on_batch per step (tc: the library's push/poll step; fp32: NCCL); nccl = train_on_batch with the NCCL
+# all-reduce forced; fit = model.fit with the shuffled epoch order (the reference's call, cnn.py:127-128); graph = replayed
+# step + NCCL; peer = stepper + our NVLink kernels; pavgK = parameter averaging every K steps
+path = "eager"
 if "-" in mode:
     mode, path = mode.split("-")
 rank, local, world = int(os.environ["RANK"]), int(os.environ["LOCAL_RANK"]), int(os.environ["WORLD_SIZE"])
@@ -30,15 +33,26 @@ mine = parallel.local_rows(X.shape[0], batch, rank, world).numpy()
 model = dlas.Sequential([dlas.Dense(32, 256, activation="relu"), dlas.Dense(256, 256, activation="relu"), dlas.Dense(256, 1)], mode=mode)
 every = int(path[4:]) if path.startswith("pavg") else 0      # e.g. fp32-pavg3: parameter averaging every 3 steps
 model.compile(loss="mse", optimizer=dlas.SGD(lr=0.001, momentum=0.99, decay=1e-6, nesterov=True),
-              averaging="parameter" if every else "gradient", average_every=max(1, every))
+              averaging="parameter" if every else "gradient", average_every=max(1, every),
+              exchange="nccl" if path in ("nccl", "graph") else "auto")
 model.set_weights_flat(p0)
 Xl, yl = torch.from_numpy(X[mine]).cuda(), torch.from_numpy(y[mine]).cuda().reshape(-1, 1)
 lb = batch // world
-if path == "eager" or every:
+order = None
+if path == "fit":
+    from dlas import hashing
+    order = hashing.batch_order(model.seed, 0, steps)
+    hist = model.fit(Xl, yl, nb_epoch=1, batch_size=batch, shuffle=True, verbose=0)
+    got = model._ring[torch.arange(steps, device="cuda") % model._ring.numel()].cpu().numpy() if model._recv is not None else None
+    assert model.dp_path == ("peer-push" if mode == "tc" else "nccl"), model.dp_path
+    epoch_loss = hist["loss"][0]
+elif path in ("eager", "nccl") or every:
     losses = []
     for s in range(steps):
         losses.append(model.train_on_batch(Xl[s * lb:(s + 1) * lb], yl[s * lb:(s + 1) * lb], global_rows=batch))
     got = torch.cat(losses).cpu().numpy()
+    if not every:
+        assert model.dp_path == ("peer-push" if (mode == "tc" and path == "eager") else "nccl"), model.dp_path
 else:
     st = model.graph_stepper(Xl, yl, lb, global_rows=batch, warmup_steps=3, peer=(path == "peer"))
     st.run(steps - 3)
@@ -61,7 +75,10 @@ if rank == 0:
                                         O.sgd_config(), world, every)
         got = ref
     else:
-        ref = O.mlp_fit_steps(pr, dims, X.astype(np.float64), y.astype(np.float64), batch, steps, O.LOSS_MSE, O.sgd_config(), O.opt_state(pr.size))
+        ref = O.mlp_fit_steps(pr, dims, X.astype(np.float64), y.astype(np.float64), batch, steps, O.LOSS_MSE, O.sgd_config(), O.opt_state(pr.size),
+                              order=order)
+        if got is None:      # fit through NCCL keeps no per-step ring: compare the epoch mean Keras reports
+            got, ref = np.asarray([epoch_loss]), np.asarray([ref.mean()])
     lerr = float(np.abs(got / ref - 1).max())
     werr = float(np.linalg.norm(w - pr) / np.linalg.norm(pr))
     same = float(hi.item() - lo.item())

@@ -40,6 +40,10 @@ def parser(description):
                     help="data-parallel training on G GPUs of this box: the script re-launches itself as G ranks "
                          "(torch.distributed.run); under torchrun the ranks are taken from the environment")
     ap.add_argument("--master-port", type=int, default=29541)
+    ap.add_argument("--standardize", action="store_true",
+                    help="z-score every feature column with the training split's mean / deviation before training (the "
+                         "reference feeds raw columns, cnn.py:53-65; --mode tc keeps rows as fp16 operands and needs "
+                         "columns within +-65504, see DLAS_MODE_TC in include/dlas_b200.h)")
     ap.add_argument("--one-hot", action="store_true",
                     help="with --data: encode string columns as cnn.py:72-91 does (StringIndexer -> OneHotEncoder) and put "
                          "them in front of the continuous columns (cnn.py:93-99); host-side, fitted once on all rows")
@@ -147,12 +151,16 @@ def load_rows(args, names, cont):
     return torch.as_tensor(Xh).cuda(), torch.as_tensor(yh).cuda()
 
 
-def split(X, y, seed):
+def split(X, y, seed, standardize=False):
     code = ops.split_codes(X.shape[0], seed=seed)
     parts = []
     for k in range(3):
         idx = (code == k).nonzero(as_tuple=True)[0]
         parts.append((X.index_select(0, idx).contiguous(), y.index_select(0, idx).contiguous()))
+    if standardize and parts[0][0].shape[0] > 1:     # --standardize: statistics of the training split only (host-side ETL)
+        mu = parts[0][0].mean(dim=0, keepdim=True)
+        sd = parts[0][0].std(dim=0, keepdim=True).clamp_min(1e-12)
+        parts = [(((Xp - mu) / sd).contiguous(), yp) for Xp, yp in parts]
     return parts
 
 

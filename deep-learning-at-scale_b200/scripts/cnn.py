@@ -27,7 +27,7 @@ if __name__ == "__main__":
         _, yr = C.load_rows(args, names, cont)
         W = yr.reshape(-1).unfold(0, span, 1)
     X, y = W[:, :args.seq_len].contiguous(), W[:, args.seq_len:].contiguous()
-    train, val, test = C.shard(C.split(X, y, args.seed), args.batch_size, rank, world)
+    train, val, test = C.shard(C.split(X, y, args.seed, args.standardize), args.batch_size, rank, world)
     model = dlas.Sequential(seed=args.seed)
     model.add(dlas.Convolution1D(1, args.filters, args.filter_length, activation="relu"))          # cnn.py:111
     model.add(dlas.Dropout(args.dropout))                                                           # cnn.py:112

@@ -17,7 +17,7 @@ if __name__ == "__main__":
     X, y = C.load_rows(args, names, cont)
     W = ops.lag_windows(X, args.lags)                       # (n - lags + 1, lags * F)
     yw = y[args.lags - 1:].contiguous()
-    train, val, test = C.shard(C.split(W, yw, args.seed), args.batch_size, rank, world)
+    train, val, test = C.shard(C.split(W, yw, args.seed, args.standardize), args.batch_size, rank, world)
     dims = [W.shape[1]] + [int(h) for h in args.hidden.split(",")] + [1]
     model = dlas.Sequential(mode=args.mode, seed=args.seed)
     for a, b in zip(dims[:-2], dims[1:-1]):

@@ -22,7 +22,7 @@ if __name__ == "__main__":
         Xr, yr = C.load_rows(args, names, cont)
         X = ops.lag_windows(Xr, args.seq_len)               # each window is one (T, F) sequence, batch-major
         y = yr[args.seq_len - 1:].contiguous()
-    train, val, test = C.shard(C.split(X, y, args.seed), args.batch_size, rank, world)
+    train, val, test = C.shard(C.split(X, y, args.seed, args.standardize), args.batch_size, rank, world)
     model = dlas.Sequential(seed=args.seed)
     for i in range(args.layers):
         model.add(dlas.LSTM(args.hidden, input_shape=(args.seq_len, len(cont)) if i == 0 else None,

@@ -12,7 +12,7 @@ if __name__ == "__main__":
     rank, world = C.init_distributed(args)
     names, cont = C.schema(args)
     X, y = C.load_rows(args, names, cont)
-    train, val, test = C.shard(C.split(X, y, args.seed), args.batch_size, rank, world)
+    train, val, test = C.shard(C.split(X, y, args.seed, args.standardize), args.batch_size, rank, world)
     dims = [int(X.shape[1])] + [int(h) for h in args.hidden.split(",")] + [1]   # len(cont), plus the one-hot columns with --one-hot
     model = dlas.Sequential(mode=args.mode, seed=args.seed)
     for a, b in zip(dims[:-2], dims[1:-1]):

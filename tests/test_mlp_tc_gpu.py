@@ -235,3 +235,125 @@ def test_dp_step_world_1_matches_fit_steps(dl, optname):
     assert state.tolist() == [steps % nb, it0 + steps]
     assert _relerr(p2.cpu().numpy(), p.cpu().numpy().astype(np.float64)) < 1e-6
     np.testing.assert_allclose(ring[idx].cpu().numpy(), ref_losses.cpu().numpy(), rtol=1e-6)
+
+
+def test_bench_batch_65536_steps_vs_oracle(dl):
+    """Four steps at the benchmark's own batch (65,536 rows per step): per-step loss and final weights within 1e-4 of
+    the fp64 oracle."""
+    from dlas import ops
+    batch, nb = 65536, 4
+    X, y = O.synth_rows(O.BASE_SEED, 0, batch * nb, 32)
+    p0 = O.glorot_init(DIMS, O.BASE_SEED)
+    p = _cuda(p0)
+    m, v = torch.zeros_like(p), torch.zeros_like(p)
+    gs = torch.zeros(p.numel() + 1, device="cuda")
+    losses = torch.zeros(nb, device="cuda")
+    cfg = dl.SGD(lr=0.001, momentum=0.99, decay=1e-6, nesterov=True).cfg()
+    ws = ops.mlp_workspace(DIMS, dl.MODE_TC)
+    ops.mlp_fit_steps(DIMS, dl.LOSS_MSE, dl.MODE_TC, cfg, p, m, v, _cuda(X), _cuda(y), batch, nb, 0, losses, gs, ws)
+    ops.mlp_status(DIMS, dl.MODE_TC, ws)
+    pr = p0.astype(np.float64)
+    ref = O.mlp_fit_steps(pr, DIMS, X.astype(np.float64), y.astype(np.float64), batch, nb, O.LOSS_MSE, O.sgd_config(),
+                          O.opt_state(pr.size))
+    got = losses.cpu().numpy()
+    print("batch 65536: max per-step loss rel err %.3g; weights rel err %.3g" % (np.abs(got / ref - 1).max(), _relerr(p.cpu().numpy(), pr)))
+    np.testing.assert_allclose(got, ref, rtol=TOL)
+    assert _relerr(p.cpu().numpy(), pr) < TOL
+
+
+def test_rows_produced_by_the_preceding_kernel(dl):
+    """include/dlas_b200.h: X / y / params may be written by the kernel enqueued right before dlas_mlp_grad on the same
+    stream.  The tcgen05 kernel is launched with programmatic stream serialisation (it may start while its predecessor
+    drains), so it must not touch the rows before its dependency wait: 200 repetitions of {copy kernel -> gradient} with
+    alternating contents, no host synchronisation in between, each bit-compared with a synchronised run."""
+    from dlas import ops
+    n = 9472 + 128
+    srcs = [tuple(_cuda(a) for a in O.synth_rows(O.BASE_SEED, 1000 * k, n, 32)) for k in range(2)]
+    p = _cuda(O.glorot_init(DIMS, 3))
+    ws = ops.mlp_workspace(DIMS, dl.MODE_TC)
+    ref = []
+    for Xs, ys in srcs:      # synchronised references
+        g = torch.zeros(p.numel() + 1, device="cuda")
+        ops.mlp_grad(DIMS, 0, dl.MODE_TC, p, Xs, ys, g, ws)
+        torch.cuda.synchronize()
+        ref.append(g.clone())
+    X, y = torch.empty_like(srcs[0][0]), torch.empty_like(srcs[0][1])
+    outs = [torch.zeros(p.numel() + 1, device="cuda") for _ in range(200)]
+    for i in range(200):
+        X.copy_(srcs[i & 1][0])          # producer kernels, same stream, immediately before
+        y.copy_(srcs[i & 1][1])
+        ops.mlp_grad(DIMS, 0, dl.MODE_TC, p, X, y, outs[i], ws)
+    torch.cuda.synchronize()
+    bad = [i for i in range(200) if not torch.equal(outs[i], ref[i & 1])]
+    assert not bad, "stale rows read in repetitions %s" % bad[:10]
+
+
+def test_fp16_range_is_guarded(dl):
+    """DLAS_MODE_TC is a reduced-range mode (fp16 operands, |value| <= 65504).  Wellhead-scale columns (P in [50, 5000],
+    S in [4, 128], R in [0.02, 10]: the ranges of the Gilbert inputs) train within the stated Adam tolerance of this mode;
+    a column around 1e5 does not fit, and that is reported -- dlas_mlp_status returns DLAS_ERR_RANGE -- never silent."""
+    from dlas import ops, _lib
+    batch, nb = 4096, 6
+    P, S, R = O.synth_gilbert(O.BASE_SEED, 0, batch * nb)
+    cols = [P, S, R]
+    X = np.stack([cols[j % 3] * (1.0 + 0.01 * (j // 3)) for j in range(32)], axis=1).astype(np.float32)
+    y = np.log10(O.gilbert(P, S, R)).astype(np.float32).reshape(-1, 1)
+    p0 = O.glorot_init(DIMS, O.BASE_SEED)
+    p0[:32 * 256] *= 1e-3        # first-layer weights sized for raw, unstandardised columns
+    p = _cuda(p0)
+    m, v = torch.zeros_like(p), torch.zeros_like(p)
+    gs = torch.zeros(p.numel() + 1, device="cuda")
+    losses = torch.zeros(nb, device="cuda")
+    ws = ops.mlp_workspace(DIMS, dl.MODE_TC)
+    adam = dl.Adam(lr=1e-6)              # raw columns of a few thousand: a step size that descends smoothly
+    ops.mlp_fit_steps(DIMS, dl.LOSS_MSE, dl.MODE_TC, adam.cfg(), p, m, v, _cuda(X), _cuda(y), batch, nb, 0, losses, gs, ws)
+    ops.mlp_status(DIMS, dl.MODE_TC, ws)                      # in range: no error
+    pr = p0.astype(np.float64)
+    ref = O.mlp_fit_steps(pr, DIMS, X.astype(np.float64), y.astype(np.float64), batch, nb, O.LOSS_MSE, O.adam_config(lr=1e-6), O.opt_state(pr.size))
+    got = losses.cpu().numpy()
+    print("wellhead-scale rows: max per-step loss rel err %.3g; weights rel err %.3g" % (np.abs(got / ref - 1).max(), _relerr(p.cpu().numpy(), pr)))
+    np.testing.assert_allclose(got, ref, rtol=5e-4)           # the mode's stated Adam tolerance (test_adam_batch_4096)
+    assert _relerr(p.cpu().numpy(), pr) < 2e-3
+    # out of range: one column of 1e5 .. 2e5
+    Xb = X.copy()
+    Xb[:, 5] = 1.0e5 + Xb[:, 5] * 20.0
+    p = _cuda(p0)
+    m.zero_(); v.zero_()
+    ops.mlp_fit_steps(DIMS, dl.LOSS_MSE, dl.MODE_TC, adam.cfg(), p, m, v, _cuda(Xb), _cuda(y), batch, 2, 0, losses, gs, ws)
+    with pytest.raises(_lib.DlasError) as e:
+        ops.mlp_status(DIMS, dl.MODE_TC, ws)
+    assert e.value.code == -7 and "65504" in str(e.value)
+    # the fp32 mode takes the same rows
+    p = _cuda(p0)
+    m.zero_(); v.zero_()
+    ws32 = ops.mlp_workspace(DIMS, dl.MODE_FP32)
+    ops.mlp_fit_steps(DIMS, dl.LOSS_MSE, dl.MODE_FP32, adam.cfg(), p, m, v, _cuda(Xb), _cuda(y), batch, 2, 0, losses, gs, ws32)
+    ops.mlp_status(DIMS, dl.MODE_FP32, ws32)
+    assert np.isfinite(losses[:2].cpu().numpy()).all()
+
+
+def test_dp_step_follows_the_batch_order(dl):
+    """dlas_mlp_dp_step_at with batch_order_host (model.fit's shuffled epoch) == dlas_mlp_fit_steps with the same order."""
+    from dlas import ops, hashing
+    batch, nb = 1024, 7
+    X, y = O.synth_rows(O.BASE_SEED, 0, batch * nb, 32)
+    Xd, yd = _cuda(X), _cuda(y)
+    order = hashing.batch_order(77, 0, nb)
+    cfg = dl.SGD(lr=0.001, momentum=0.99, decay=1e-6, nesterov=True).cfg()
+    ws = ops.mlp_workspace(DIMS, dl.MODE_TC)
+    res = []
+    for which in range(2):
+        p = _cuda(O.glorot_init(DIMS, O.BASE_SEED))
+        m, v = torch.zeros_like(p), torch.zeros_like(p)
+        if which == 0:
+            gs, ls = torch.zeros(p.numel() + 1, device="cuda"), torch.zeros(nb, device="cuda")
+            ops.mlp_fit_steps(DIMS, dl.LOSS_MSE, dl.MODE_TC, cfg, p, m, v, Xd, yd, batch, nb, 0, ls, gs, ws, batch_order=order)
+        else:
+            recv = torch.zeros(ops.mlp_dp_recv_bytes(DIMS, dl.MODE_TC, 1) // 4, device="cuda")
+            bases = torch.tensor([recv.data_ptr()], dtype=torch.int64, device="cuda")
+            ls = torch.zeros(nb, device="cuda")
+            ops.mlp_dp_step_at(DIMS, dl.LOSS_MSE, dl.MODE_TC, cfg, p, m, v, Xd, yd, batch, None, bases, 0, 1, 1.0 / batch, nb, ls, ws,
+                               iteration0=0, batch_order=order)
+        torch.cuda.synchronize()
+        res.append((p.clone(), ls.clone()))
+    assert torch.equal(res[0][0], res[1][0]) and torch.equal(res[0][1], res[1][1])

@@ -88,3 +88,61 @@ def test_feature_assembly_follows_the_reference_pipeline():
     np.testing.assert_array_equal(X0, X[:, 2:])                                          # default: numeric columns only
     Xt, yt = C.assemble_features(df, names, types, "a", one_hot=True)                    # any numeric column can be the target
     assert Xt.shape == (6, 4) and yt[:, 0].tolist() == df["a"].tolist()
+
+
+def test_shard_gives_every_rank_the_same_steps():
+    """scripts/_common.shard (--gpus G): rank r owns the r-th contiguous 1/G slice of every global batch and the same share
+    of the ragged tail, so every rank runs the same number of steps of the same sizes (a precondition of model.fit)."""
+    import torch
+    sys.path.insert(0, SCRIPTS)
+    import _common as C
+    n, B, W = 1000, 96, 4                     # 10 whole batches of 96 + a tail of 40 rows
+    X = torch.arange(n, dtype=torch.float32).reshape(n, 1)
+    parts = [(X, X.clone()), (X[:50], X[:50]), (X[:31], X[:31])]
+    got = [C.shard(parts, B, r, W) for r in range(W)]
+    assert {g[0][0].shape[0] for g in got} == {10 * (B // W) + 40 // W}
+    for b in range(10):                        # the union of the ranks' slices of batch b is batch b, in rank order
+        rows = torch.cat([g[0][0][b * 24:(b + 1) * 24, 0] for g in got])
+        assert rows.tolist() == list(range(b * B, (b + 1) * B))
+    tail = torch.cat([g[0][0][240:, 0] for g in got])
+    assert tail.tolist() == list(range(960, 1000))
+    assert sum(g[1][0].shape[0] for g in got) == 50 and sum(g[2][0].shape[0] for g in got) == 31
+    assert C.shard(parts, B, 0, 1) is parts
+
+
+def _wellhead_csv(path, n, big_column=False):
+    sys.path.insert(0, os.path.join(ROOT, "oracle"))
+    import dlas_oracle as O
+    P, S, R = O.synth_gilbert(O.BASE_SEED, 0, n)
+    cols = [P, S, R]
+    X = np.stack([cols[j % 3] * (1.0 + 0.01 * (j // 3)) for j in range(32)], axis=1)
+    if big_column:
+        X[:, 5] = 1.0e5 + 20.0 * X[:, 5]
+    q = np.log10(O.gilbert(P, S, R))
+    np.savetxt(path, np.concatenate([X, q[:, None]], axis=1), delimiter=",", fmt="%.7g")
+    names = ",".join("c%d" % i for i in range(32)) + ",q"
+    return names, ",".join(["float"] * 33)
+
+
+@pytest.mark.gpu
+def test_static_ann_tc_mode_on_wellhead_scale_columns(tmp_path):
+    """Raw wellhead columns (P 50..5000 psig, S 4..128, R 0.02..10) through the drop-in script in the tensor-core mode:
+    with --standardize the fp16-operand run ends where the fp32 run does; a column beyond the fp16 range without it is
+    refused loudly (DLAS_ERR_RANGE), and the fp32 mode takes the same file."""
+    path = str(tmp_path / "wells.csv")
+    names, types = _wellhead_csv(path, 30000)
+    common = ["--data", path, "--hidden", "256,256", "--batch-size", "1024", "--epochs", "4", "--optimizer", "adam", "--loss", "mse"]
+    losses = {}
+    for mode in ("fp32", "tc"):
+        r = subprocess.run([sys.executable, os.path.join(SCRIPTS, "static_ann.py"), names, types, "q", str(tmp_path) + "/" + mode + "/"]
+                           + common + ["--mode", mode, "--standardize"], capture_output=True, text=True, timeout=600)
+        assert r.returncode == 0, r.stdout[-1500:] + r.stderr[-1500:]
+        losses[mode] = float(r.stdout.split("Testing set loss:")[1].split()[0])
+    assert np.isfinite(losses["tc"]) and losses["tc"] == pytest.approx(losses["fp32"], rel=2e-2), losses
+    names, types = _wellhead_csv(path, 8000, big_column=True)
+    r = subprocess.run([sys.executable, os.path.join(SCRIPTS, "static_ann.py"), names, types, "q", str(tmp_path) + "/big/"] + common
+                       + ["--mode", "tc", "--epochs", "1"], capture_output=True, text=True, timeout=600)
+    assert r.returncode != 0 and "65504" in (r.stdout + r.stderr), r.stdout[-800:] + r.stderr[-800:]
+    r = subprocess.run([sys.executable, os.path.join(SCRIPTS, "static_ann.py"), names, types, "q", str(tmp_path) + "/big32/"] + common
+                       + ["--mode", "fp32", "--epochs", "1", "--standardize"], capture_output=True, text=True, timeout=600)
+    assert r.returncode == 0, r.stdout[-1500:] + r.stderr[-1500:]

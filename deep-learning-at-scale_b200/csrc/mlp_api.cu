@@ -7,11 +7,11 @@ namespace dlas {
 size_t simt_workspace_bytes(const int* dims, int n_layers);
 int simt_grad(const int* dims, int n_layers, int loss, const float* params, const float* X, const float* y,
               size_t n_rows, float* grad_sum, void* workspace, size_t workspace_bytes, cudaStream_t st,
-              const long long* cursor = nullptr, size_t parity_stride = 0);
+              const long long* cursor = nullptr, size_t parity_stride = 0, size_t ldx = 0);
 int simt_eval_loss(const int* dims, int n_layers, int loss, const float* params, const float* X, const float* y,
-                   size_t n_rows, float* loss_sum, void* workspace, size_t workspace_bytes, cudaStream_t st);
+                   size_t n_rows, float* loss_sum, void* workspace, size_t workspace_bytes, cudaStream_t st, size_t ldx = 0);
 int simt_predict(const int* dims, int n_layers, const float* params, const float* X, size_t n_rows, float* yhat,
-                 cudaStream_t st);
+                 cudaStream_t st, size_t ldx = 0);
 // optim.cu
 int opt_step_impl(const dlas_opt_cfg* cfg, float* params, float* m, float* v, const float* grad_sum, size_t n,
                   float grad_scale, uint64_t iteration, float* loss_out, cudaStream_t st);
@@ -20,10 +20,10 @@ bool tc_supported(const int* dims, int n_layers);
 size_t tc_workspace_bytes(const int* dims, int n_layers);
 int tc_grad(const int* dims, int n_layers, int loss, const float* params, const float* X, const float* y,
             size_t n_rows, float* grad_sum, void* workspace, size_t workspace_bytes, cudaStream_t st,
-            const long long* cursor = nullptr, size_t parity_stride = 0);
+            const long long* cursor = nullptr, size_t parity_stride = 0, size_t ldx = 0);
 int tc_fit_step(const int* dims, int n_layers, int loss, const dlas_opt_cfg* cfg, float* params, float* m, float* v,
                 const float* X, const float* y, size_t n_rows, uint64_t iteration, float* loss_out, void* workspace,
-                size_t workspace_bytes, cudaStream_t st, bool chained);
+                size_t workspace_bytes, cudaStream_t st, bool chained, size_t ldx = 0);
 int tc_status(const void* workspace, size_t workspace_bytes, cudaStream_t st);
 size_t tc_dp_recv_words(int world);
 int tc_dp_step(const int* dims, int n_layers, int loss, const dlas_opt_cfg* cfg, float* params, float* m, float* v,
@@ -69,18 +69,37 @@ extern "C" size_t dlas_mlp_workspace_bytes(const int* dims, int n_layers, int mo
   return simt_workspace_bytes(dims, n_layers);
 }
 
-extern "C" int dlas_mlp_grad(const int* dims, int n_layers, int loss, int mode, const float* params,
-                             const float* X, const float* y, size_t n_rows, float* grad_sum,
-                             void* workspace, size_t workspace_bytes, void* stream) {
+namespace {
+int check_stride(const char* fn, const int* dims, size_t x_row_stride) {
+  DLAS_REQUIRE(x_row_stride >= 1 && x_row_stride <= (size_t)dims[0],
+               "%s: x_row_stride %zu not in 1..dims[0] = %d (dims[0] = dense rows; less = overlapping lag windows)", fn,
+               x_row_stride, dims[0]);
+  return DLAS_OK;
+}
+}  // namespace
+
+extern "C" int dlas_mlp_grad_strided(const int* dims, int n_layers, int loss, int mode, const float* params,
+                                     const float* X, size_t x_row_stride, const float* y, size_t n_rows, float* grad_sum,
+                                     void* workspace, size_t workspace_bytes, void* stream) {
   DLAS_CHECK_DEVICE();
   int rc = check_common("dlas_mlp_grad", dims, n_layers, loss, mode);
   if (rc != DLAS_OK) return rc;
   DLAS_REQUIRE(params && grad_sum && (n_rows == 0 || (X && y)), "dlas_mlp_grad: null pointer");
+  rc = check_stride("dlas_mlp_grad_strided", dims, x_row_stride);
+  if (rc != DLAS_OK) return rc;
   if (mode == DLAS_MODE_TC)
     return tc_grad(dims, n_layers, loss, params, X, y, n_rows, grad_sum, workspace, workspace_bytes,
-                   (cudaStream_t)stream);
+                   (cudaStream_t)stream, nullptr, 0, x_row_stride);
   return simt_grad(dims, n_layers, loss, params, X, y, n_rows, grad_sum, workspace, workspace_bytes,
-                   (cudaStream_t)stream);
+                   (cudaStream_t)stream, nullptr, 0, x_row_stride);
+}
+
+extern "C" int dlas_mlp_grad(const int* dims, int n_layers, int loss, int mode, const float* params,
+                             const float* X, const float* y, size_t n_rows, float* grad_sum,
+                             void* workspace, size_t workspace_bytes, void* stream) {
+  if (!dims) { set_error("dlas_mlp_grad: dims is null"); return DLAS_ERR_INVALID; }
+  return dlas_mlp_grad_strided(dims, n_layers, loss, mode, params, X, (size_t)dims[0], y, n_rows, grad_sum, workspace,
+                               workspace_bytes, stream);
 }
 
 extern "C" int dlas_mlp_grad_at(const int* dims, int n_layers, int loss, int mode, const float* params,
@@ -106,8 +125,22 @@ extern "C" int dlas_mlp_fit_steps(const int* dims, int n_layers, int loss, int m
                                   const int64_t* batch_order_host, int64_t first_batch, int n_steps,
                                   uint64_t iteration0, float* step_losses, float* grad_sum,
                                   void* workspace, size_t workspace_bytes, void* stream) {
+  if (!dims) { set_error("dlas_mlp_fit_steps: dims is null"); return DLAS_ERR_INVALID; }
+  return dlas_mlp_fit_steps_strided(dims, n_layers, loss, mode, cfg, params, m, v, X, (size_t)dims[0], y, n_rows, batch,
+                                    batch_order_host, first_batch, n_steps, iteration0, step_losses, grad_sum, workspace,
+                                    workspace_bytes, stream);
+}
+
+extern "C" int dlas_mlp_fit_steps_strided(const int* dims, int n_layers, int loss, int mode,
+                                          const dlas_opt_cfg* cfg, float* params, float* m, float* v,
+                                          const float* X, size_t x_row_stride, const float* y, size_t n_rows, int batch,
+                                          const int64_t* batch_order_host, int64_t first_batch, int n_steps,
+                                          uint64_t iteration0, float* step_losses, float* grad_sum,
+                                          void* workspace, size_t workspace_bytes, void* stream) {
   DLAS_CHECK_DEVICE();
   int rc = check_common("dlas_mlp_fit_steps", dims, n_layers, loss, mode);
+  if (rc != DLAS_OK) return rc;
+  rc = check_stride("dlas_mlp_fit_steps_strided", dims, x_row_stride);
   if (rc != DLAS_OK) return rc;
   DLAS_REQUIRE(cfg && params && m && X && y && grad_sum, "dlas_mlp_fit_steps: null pointer");
   DLAS_REQUIRE(batch >= 1, "dlas_mlp_fit_steps: batch %d < 1", batch);
@@ -116,7 +149,7 @@ extern "C" int dlas_mlp_fit_steps(const int* dims, int n_layers, int loss, int m
   DLAS_REQUIRE(n_batches >= 1 || n_steps == 0,      // pass it as its own call with batch = remainder
                "dlas_mlp_fit_steps: n_rows %zu < batch %d", n_rows, batch);
   const size_t n_params = dlas_mlp_n_params(dims, n_layers);
-  const size_t d0 = dims[0], dL = dims[n_layers];
+  const size_t d0 = x_row_stride, dL = dims[n_layers];   // batch b starts b*batch rows further: b*batch*stride floats
   cudaStream_t st = (cudaStream_t)stream;
   for (int s = 0; s < n_steps; ++s) {
     int64_t b = batch_order_host ? batch_order_host[s] : first_batch + s;
@@ -126,11 +159,11 @@ extern "C" int dlas_mlp_fit_steps(const int* dims, int n_layers, int loss, int m
     const float* yb = y + (size_t)b * batch * dL;
     if (mode == DLAS_MODE_TC) {   // gradient kernel + (reduction fused with the update): two launches per step
       rc = tc_fit_step(dims, n_layers, loss, cfg, params, m, v, Xb, yb, batch, iteration0 + (uint64_t)s,
-                       step_losses ? step_losses + s : nullptr, workspace, workspace_bytes, st, /*chained=*/s > 0);
+                       step_losses ? step_losses + s : nullptr, workspace, workspace_bytes, st, /*chained=*/s > 0, x_row_stride);
       if (rc != DLAS_OK) return rc;
       continue;
     }
-    rc = simt_grad(dims, n_layers, loss, params, Xb, yb, batch, grad_sum, workspace, workspace_bytes, st);
+    rc = simt_grad(dims, n_layers, loss, params, Xb, yb, batch, grad_sum, workspace, workspace_bytes, st, nullptr, 0, x_row_stride);
     if (rc != DLAS_OK) return rc;
     rc = opt_step_impl(cfg, params, m, v, grad_sum, n_params, 1.0f / (float)batch, iteration0 + (uint64_t)s,
                        step_losses ? step_losses + s : nullptr, st);
@@ -141,25 +174,43 @@ extern "C" int dlas_mlp_fit_steps(const int* dims, int n_layers, int loss, int m
 
 extern "C" int dlas_mlp_predict(const int* dims, int n_layers, int mode, const float* params,
                                 const float* X, size_t n_rows, float* yhat, void* stream) {
+  if (!dims) { set_error("dlas_mlp_predict: dims is null"); return DLAS_ERR_INVALID; }
+  return dlas_mlp_predict_strided(dims, n_layers, mode, params, X, (size_t)dims[0], n_rows, yhat, stream);
+}
+
+extern "C" int dlas_mlp_predict_strided(const int* dims, int n_layers, int mode, const float* params,
+                                        const float* X, size_t x_row_stride, size_t n_rows, float* yhat, void* stream) {
   DLAS_CHECK_DEVICE();
   int rc = check_common("dlas_mlp_predict", dims, n_layers, DLAS_LOSS_MSE, DLAS_MODE_FP32);
   if (rc != DLAS_OK) return rc;
   DLAS_REQUIRE(mode == DLAS_MODE_FP32 || mode == DLAS_MODE_TC, "dlas_mlp_predict: unknown mode %d", mode);
   DLAS_REQUIRE(params && (n_rows == 0 || (X && yhat)), "dlas_mlp_predict: null pointer");
   // inference runs the fp32 kernel in both modes (HBM-leaning)
-  return simt_predict(dims, n_layers, params, X, n_rows, yhat, (cudaStream_t)stream);
+  rc = check_stride("dlas_mlp_predict_strided", dims, x_row_stride);
+  if (rc != DLAS_OK) return rc;
+  return simt_predict(dims, n_layers, params, X, n_rows, yhat, (cudaStream_t)stream, x_row_stride);
 }
 
 extern "C" int dlas_mlp_eval_loss(const int* dims, int n_layers, int loss, int mode, const float* params,
                                   const float* X, const float* y, size_t n_rows, float* loss_sum,
                                   void* workspace, size_t workspace_bytes, void* stream) {
+  if (!dims) { set_error("dlas_mlp_eval_loss: dims is null"); return DLAS_ERR_INVALID; }
+  return dlas_mlp_eval_loss_strided(dims, n_layers, loss, mode, params, X, (size_t)dims[0], y, n_rows, loss_sum, workspace,
+                                    workspace_bytes, stream);
+}
+
+extern "C" int dlas_mlp_eval_loss_strided(const int* dims, int n_layers, int loss, int mode, const float* params,
+                                          const float* X, size_t x_row_stride, const float* y, size_t n_rows, float* loss_sum,
+                                          void* workspace, size_t workspace_bytes, void* stream) {
   DLAS_CHECK_DEVICE();
   int rc = check_common("dlas_mlp_eval_loss", dims, n_layers, loss, DLAS_MODE_FP32);
   if (rc != DLAS_OK) return rc;
   DLAS_REQUIRE(mode == DLAS_MODE_FP32 || mode == DLAS_MODE_TC, "dlas_mlp_eval_loss: unknown mode %d", mode);
   DLAS_REQUIRE(params && loss_sum && (n_rows == 0 || (X && y)), "dlas_mlp_eval_loss: null pointer");
+  rc = check_stride("dlas_mlp_eval_loss_strided", dims, x_row_stride);
+  if (rc != DLAS_OK) return rc;
   return simt_eval_loss(dims, n_layers, loss, params, X, y, n_rows, loss_sum, workspace, workspace_bytes,
-                        (cudaStream_t)stream);
+                        (cudaStream_t)stream, x_row_stride);
 }
 
 extern "C" size_t dlas_mlp_dp_recv_bytes(const int* dims, int n_layers, int mode, int world) {

@@ -36,6 +36,8 @@ struct MlpDesc {
   int n_params;
   int max_w;
   int smem_floats;
+  int ldx;                // floats between consecutive rows of X (dims[0] for a dense matrix; the raw feature count for
+                          // lag windows laid over a series: window i = dims[0] contiguous floats starting at row i)
 };
 
 int make_desc(const int* dims, int n_layers, MlpDesc& d) {
@@ -57,6 +59,7 @@ int make_desc(const int* dims, int n_layers, MlpDesc& d) {
     o += dims[l + 1];
   }
   d.n_params = o;
+  d.ldx = dims[0];
   d.max_w = mw;
   d.dz_off[0] = so;
   so += mw * RS;
@@ -96,7 +99,7 @@ mlp_simt_kernel(const MlpDesc d, const int loss, const float* __restrict__ param
                 const long long* __restrict__ cursor) {
   // device-resident batch cursor (replayable steps): rows [cursor*n_rows, (cursor+1)*n_rows)
   const size_t batch0 = cursor ? (size_t)cursor[0] * n_rows : 0;
-  const float* __restrict__ X = X_base + batch0 * d.dims[0];
+  const float* __restrict__ X = X_base + batch0 * d.ldx;
   const float* __restrict__ y = y_base ? y_base + batch0 * d.dims[d.n_layers] : nullptr;
   extern __shared__ __align__(16) float smem[];
   const int L = d.n_layers;
@@ -112,10 +115,17 @@ mlp_simt_kernel(const MlpDesc d, const int loss, const float* __restrict__ param
     // ---- X tile -> actT[0] (coalesced global reads, transposed smem writes)
     {
       float* a0 = smem + d.act_off[0];
-      const float* xg = X + row0 * (size_t)d0;
-      for (int idx = threadIdx.x; idx < R * d0; idx += NT) {
-        int r = idx / d0, k = idx - r * d0;
-        a0[k * RS + r] = (r < nr) ? __ldcs(xg + idx) : 0.0f;
+      const float* xg = X + row0 * (size_t)d.ldx;
+      if (d.ldx == d0) {
+        for (int idx = threadIdx.x; idx < R * d0; idx += NT) {
+          int r = idx / d0, k = idx - r * d0;
+          a0[k * RS + r] = (r < nr) ? __ldcs(xg + idx) : 0.0f;
+        }
+      } else {   // overlapping windows: neighbouring rows share floats, keep them in cache (no streaming hint)
+        for (int idx = threadIdx.x; idx < R * d0; idx += NT) {
+          int r = idx / d0, k = idx - r * d0;
+          a0[k * RS + r] = (r < nr) ? __ldg(xg + (size_t)r * d.ldx + k) : 0.0f;
+        }
       }
     }
     __syncthreads();
@@ -257,10 +267,11 @@ size_t simt_workspace_bytes(const int* dims, int n_layers) {
 
 int simt_grad(const int* dims, int n_layers, int loss, const float* params, const float* X, const float* y,
               size_t n_rows, float* grad_sum, void* workspace, size_t workspace_bytes, cudaStream_t st,
-              const long long* cursor, size_t parity_stride) {
+              const long long* cursor, size_t parity_stride, size_t ldx) {
   MlpDesc d;
   int rc = make_desc(dims, n_layers, d);
   if (rc != DLAS_OK) return rc;
+  if (ldx) d.ldx = (int)ldx;
   size_t need = simt_workspace_bytes(dims, n_layers);
   if (workspace == nullptr || workspace_bytes < need) {
     set_error("mlp: workspace of %zu bytes given, %zu needed", workspace_bytes, need);
@@ -290,10 +301,11 @@ int simt_grad(const int* dims, int n_layers, int loss, const float* params, cons
 
 int simt_eval_loss(const int* dims, int n_layers, int loss, const float* params, const float* X,
                    const float* y, size_t n_rows, float* loss_sum, void* workspace, size_t workspace_bytes,
-                   cudaStream_t st) {
+                   cudaStream_t st, size_t ldx) {
   MlpDesc d;
   int rc = make_desc(dims, n_layers, d);
   if (rc != DLAS_OK) return rc;
+  if (ldx) d.ldx = (int)ldx;
   size_t need = simt_workspace_bytes(dims, n_layers);
   if (workspace == nullptr || workspace_bytes < need) {
     set_error("mlp: workspace of %zu bytes given, %zu needed", workspace_bytes, need);
@@ -314,10 +326,11 @@ int simt_eval_loss(const int* dims, int n_layers, int loss, const float* params,
 }
 
 int simt_predict(const int* dims, int n_layers, const float* params, const float* X, size_t n_rows,
-                 float* yhat, cudaStream_t st) {
+                 float* yhat, cudaStream_t st, size_t ldx) {
   MlpDesc d;
   int rc = make_desc(dims, n_layers, d);
   if (rc != DLAS_OK) return rc;
+  if (ldx) d.ldx = (int)ldx;
   if (n_rows == 0) return DLAS_OK;
   return launch_main<KIND_PREDICT>(d, DLAS_LOSS_MSE, params, nullptr, X, nullptr, n_rows, nullptr, yhat, st);
 }

@@ -130,7 +130,8 @@ __global__ void __cluster_dims__(2, 1, 1) __launch_bounds__(NT, 1)
 mlp_tc_kernel(const int loss_kind, const float* __restrict__ params, const float* __restrict__ X_base,
               const float* __restrict__ y_base, const size_t n_rows, float* __restrict__ partials,
               unsigned* __restrict__ err_flag, const unsigned call_id, long long* __restrict__ trace,
-              const long long* __restrict__ cursor, const int rows_ready) {
+              const long long* __restrict__ cursor, const int rows_ready, const size_t ldx) {
+  // ldx: floats between consecutive rows of X (32 for a dense matrix; smaller for lag windows laid over a raw series)
   // device-resident batch cursor (replayable steps): this launch works on rows [cursor*n_rows, (cursor+1)*n_rows)
   extern __shared__ __align__(1024) uint8_t smem[];
   float* f32 = reinterpret_cast<float*>(smem + S_F32);
@@ -172,7 +173,7 @@ mlp_tc_kernel(const int loss_kind, const float* __restrict__ params, const float
   auto x_issue = [&](size_t tile, const float* __restrict__ X, const float* __restrict__ y) {
     const size_t row0 = tile * TILE;
     const bool in = row0 + xr < n_rows;
-    const float* src = X + (row0 + xr) * (size_t)D0 + xh * XF;
+    const float* src = X + (row0 + xr) * ldx + xh * XF;
 #pragma unroll
     for (int i = 0; i < XF / 4; ++i) xv[i] = in ? __ldcs(reinterpret_cast<const float4*>(src + i * 4)) : make_float4(0.f, 0.f, 0.f, 0.f);
     if (tid < TILE) yv = (row0 + tid < n_rows) ? __ldcs(y + row0 + tid) : 0.f;
@@ -189,7 +190,7 @@ mlp_tc_kernel(const int loss_kind, const float* __restrict__ params, const float
   // (the optimiser update that produced `params`); from here on its writes are visible.
   asm volatile("griddepcontrol.wait;" ::: "memory");
   const size_t batch0 = cursor ? (size_t)__ldcg(cursor) * n_rows : 0;   // the cursor is written by the previous step's kernels
-  const float* __restrict__ X = X_base + batch0 * D0;
+  const float* __restrict__ X = X_base + batch0 * ldx;
   const float* __restrict__ y = y_base + batch0;
   {
     // sW1 = [W1 ; b1 ; 0]: rows 0..31 weights, row 32 the bias (it multiplies the ones column of [x | 1 | 0]),
@@ -858,7 +859,9 @@ unsigned g_call_id = 0x5eed0000u;
 
 int launch_main(int loss, const float* params, const float* X, const float* y, size_t n_rows, void* workspace,
                 size_t workspace_bytes, cudaStream_t st, float** partials_out, unsigned** err_out, int* n_active_pairs,
-                const long long* cursor = nullptr, bool rows_ready = false) {
+                const long long* cursor = nullptr, bool rows_ready = false, size_t ldx = 0) {
+  if (ldx == 0) ldx = D0;
+  DLAS_REQUIRE(ldx % 4 == 0, "mlp (tc): the row stride of X must be a multiple of 4 floats (16-byte row loads), got %zu", ldx);
   size_t need = (size_t)n_ctas() * PSTRIDE * sizeof(float) + 256;
   if (workspace == nullptr || workspace_bytes < need) {
     set_error("mlp (tc): workspace of %zu bytes given, %zu needed", workspace_bytes, need);
@@ -897,7 +900,7 @@ int launch_main(int loss, const float* params, const float* X, const float* y, s
     cfg.attrs = at;
     cfg.numAttrs = 1;
     DLAS_CUDA(cudaLaunchKernelEx(&cfg, mlp_tc_kernel, loss, params, X, y, n_rows, partials, err_flag, g_call_id, trace, cursor,
-                                 rows_ready ? 1 : 0));
+                                 rows_ready ? 1 : 0, ldx));
   }
   prof_end(pi, st);
   DLAS_LAUNCH_CHECK();
@@ -985,7 +988,7 @@ int tc_status(const void* workspace, size_t workspace_bytes, cudaStream_t st) {
 // forward + loss + backward: grad_sum[0..n) gradient sums, grad_sum[n] loss sum
 int tc_grad(const int* dims, int n_layers, int loss, const float* params, const float* X, const float* y,
             size_t n_rows, float* grad_sum, void* workspace, size_t workspace_bytes, cudaStream_t st,
-            const long long* cursor, size_t parity_stride) {
+            const long long* cursor, size_t parity_stride, size_t ldx) {
   if (!tc_supported(dims, n_layers)) {
     set_error("DLAS_MODE_TC supports the 32-256-256-1 network only");
     return DLAS_ERR_UNSUPPORTED_SHAPE;
@@ -995,7 +998,7 @@ int tc_grad(const int* dims, int n_layers, int loss, const float* params, const 
     return DLAS_OK;
   }
   float* partials; unsigned* err; int nap;
-  int rc = launch_main(loss, params, X, y, n_rows, workspace, workspace_bytes, st, &partials, &err, &nap, cursor);
+  int rc = launch_main(loss, params, X, y, n_rows, workspace, workspace_bytes, st, &partials, &err, &nap, cursor, false, ldx);
   if (rc != DLAS_OK) return rc;
   rc = launch_reduce<FIN_GRAD>(st, partials, nap, err, grad_sum, OptScalars{}, 0.f, nullptr, nullptr, nullptr, nullptr,
                             parity_stride ? cursor : nullptr, parity_stride);
@@ -1006,7 +1009,7 @@ int tc_grad(const int* dims, int n_layers, int loss, const float* params, const 
 // one whole single-GPU step: gradient kernel, then reduction fused with the optimiser update
 int tc_fit_step(const int* dims, int n_layers, int loss, const dlas_opt_cfg* cfg, float* params, float* m, float* v,
                 const float* X, const float* y, size_t n_rows, uint64_t iteration, float* loss_out, void* workspace,
-                size_t workspace_bytes, cudaStream_t st, bool chained) {
+                size_t workspace_bytes, cudaStream_t st, bool chained, size_t ldx) {
   // chained: the kernel before this step in the stream is the previous step's finishing kernel of the same call
   if (!tc_supported(dims, n_layers)) {
     set_error("DLAS_MODE_TC supports the 32-256-256-1 network only");
@@ -1017,7 +1020,7 @@ int tc_fit_step(const int* dims, int n_layers, int loss, const dlas_opt_cfg* cfg
   if (rc != DLAS_OK) return rc;
   DLAS_REQUIRE(o.kind == DLAS_OPT_SGD || v != nullptr, "Adam needs the second-moment buffer v");
   float* partials; unsigned* err; int nap;
-  rc = launch_main(loss, params, X, y, n_rows, workspace, workspace_bytes, st, &partials, &err, &nap, nullptr, chained);
+  rc = launch_main(loss, params, X, y, n_rows, workspace, workspace_bytes, st, &partials, &err, &nap, nullptr, chained, ldx);
   if (rc != DLAS_OK) return rc;
   rc = launch_reduce<FIN_UPDATE>(st, partials, nap, err, nullptr, o, 1.0f / (float)n_rows, params, m, v, loss_out);
   if (rc != DLAS_OK) return rc;

@@ -305,6 +305,10 @@ class Sequential:
 
     # -- helpers
     def _to_dev(self, a, cols):
+        if isinstance(a, ops.LagWindows):       # lag windows over a resident series: read in place with a row stride
+            if a.shape[1] != cols:
+                raise ValueError("LagWindows of width %d given to a model with %d inputs" % (a.shape[1], cols))
+            return a
         if isinstance(a, torch.Tensor):
             t = a.to(device=self.device, dtype=torch.float32)
         else:
@@ -341,6 +345,8 @@ class Sequential:
         """n_steps data-parallel steps through dlas_mlp_dp_step_at (host-driven flavour) on batches `order` of
         (X, Y); returns the ring indices holding their batch-mean losses."""
         recv = self._recv
+        if isinstance(X, ops.LagWindows):
+            raise NotImplementedError("LagWindows inputs train through exchange='nccl' at world > 1")
         n_batches = max(1, X.shape[0] // local_rows)
         if order is not None:
             n_steps = len(order)

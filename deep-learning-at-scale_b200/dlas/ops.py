@@ -94,11 +94,45 @@ def make_opt_cfg(kind, lr, momentum=0.0, decay=0.0, nesterov=False, beta1=0.9, b
                        float(beta1), float(beta2), float(eps))
 
 
+class LagWindows:
+    """Lag windows laid over a raw series WITHOUT materialising them (dynamic ANN, Readme.md:19): window i is rows
+    i .. i + n_lags - 1 of `series` (n, F) flattened lag-major = the n_lags * F contiguous floats starting at row i, so
+    the window matrix is just the series read with a row stride of F floats (dlas_mlp_*_strided).  shape mirrors the
+    materialised (n - n_lags + 1, n_lags * F) matrix ops.lag_windows would build; rows [a, b) by slicing."""
+
+    def __init__(self, series, n_lags, start=0, count=None):
+        _dev_f32(series, "series")
+        self.series, self.n_lags, self.start = series, int(n_lags), int(start)
+        total = series.shape[0] - self.n_lags + 1
+        self.count = total - self.start if count is None else int(count)
+        if self.count < 0 or self.start + self.count > max(total, 0):
+            raise ValueError("window range [%d, %d) outside the %d windows of this series" % (self.start, self.start + self.count, total))
+        self.row_stride = int(series.shape[1])
+        self.shape = (self.count, self.n_lags * self.row_stride)
+        self.device = series.device
+
+    def __getitem__(self, sl):
+        if not isinstance(sl, slice) or sl.step not in (None, 1):
+            raise TypeError("LagWindows supports contiguous row slices only")
+        a, b, _ = sl.indices(self.count)
+        return LagWindows(self.series, self.n_lags, self.start + a, max(0, b - a))
+
+    def data_ptr(self):
+        return self.series.data_ptr() + self.start * self.row_stride * 4
+
+    def materialize(self):
+        return lag_windows(self.series, self.n_lags)[self.start:self.start + self.count]
+
+
+def _x_stride(X, dims):
+    return X.row_stride if isinstance(X, LagWindows) else int(dims[0])
+
+
 def mlp_grad(dims, loss, mode, params, X, y, grad_sum, workspace, n_rows=None):
     n_rows = X.shape[0] if n_rows is None else n_rows
-    check(_lib.load().dlas_mlp_grad(int_array(dims), len(dims) - 1, int(loss), int(mode), ptr(params), ptr(X),
-                                    ptr(y), n_rows, ptr(grad_sum), ptr(workspace), workspace.numel(),
-                                    stream_ptr()))
+    check(_lib.load().dlas_mlp_grad_strided(int_array(dims), len(dims) - 1, int(loss), int(mode), ptr(params), ptr(X),
+                                            _x_stride(X, dims), ptr(y), n_rows, ptr(grad_sum), ptr(workspace), workspace.numel(),
+                                            stream_ptr()))
     return grad_sum
 
 
@@ -118,28 +152,29 @@ def mlp_fit_steps(dims, loss, mode, cfg, params, m, v, X, y, batch, n_steps, ite
     order = None
     if batch_order is not None:
         order = (C.c_int64 * len(batch_order))(*[int(b) for b in batch_order])
-    check(_lib.load().dlas_mlp_fit_steps(int_array(dims), len(dims) - 1, int(loss), int(mode), C.byref(cfg),
-                                         ptr(params), ptr(m), ptr(v), ptr(X), ptr(y), X.shape[0], int(batch),
+    check(_lib.load().dlas_mlp_fit_steps_strided(int_array(dims), len(dims) - 1, int(loss), int(mode), C.byref(cfg),
+                                         ptr(params), ptr(m), ptr(v), ptr(X), _x_stride(X, dims), ptr(y), X.shape[0], int(batch),
                                          order, int(first_batch), int(n_steps), int(iteration0),
                                          ptr(step_losses), ptr(grad_sum), ptr(workspace), workspace.numel(),
                                          stream_ptr()))
 
 
 def mlp_predict(dims, mode, params, X, out=None):
-    _dev_f32(X, "X")
+    if not isinstance(X, LagWindows):
+        _dev_f32(X, "X")
     if out is None:
         out = torch.empty((X.shape[0], dims[-1]), dtype=torch.float32, device=X.device)
-    check(_lib.load().dlas_mlp_predict(int_array(dims), len(dims) - 1, int(mode), ptr(params), ptr(X), X.shape[0],
-                                       ptr(out), stream_ptr()))
+    check(_lib.load().dlas_mlp_predict_strided(int_array(dims), len(dims) - 1, int(mode), ptr(params), ptr(X), _x_stride(X, dims),
+                                               X.shape[0], ptr(out), stream_ptr()))
     return out
 
 
 def mlp_eval_loss(dims, loss, mode, params, X, y, workspace, loss_sum=None):
     if loss_sum is None:
         loss_sum = torch.empty(1, dtype=torch.float32, device=X.device)
-    check(_lib.load().dlas_mlp_eval_loss(int_array(dims), len(dims) - 1, int(loss), int(mode), ptr(params), ptr(X),
-                                         ptr(y), X.shape[0], ptr(loss_sum), ptr(workspace), workspace.numel(),
-                                         stream_ptr()))
+    check(_lib.load().dlas_mlp_eval_loss_strided(int_array(dims), len(dims) - 1, int(loss), int(mode), ptr(params), ptr(X),
+                                                 _x_stride(X, dims), ptr(y), X.shape[0], ptr(loss_sum), ptr(workspace),
+                                                 workspace.numel(), stream_ptr()))
     return loss_sum
 
 

@@ -212,6 +212,27 @@ int dlas_mlp_fit_steps(const int* dims, int n_layers, int loss, int mode, const 
                        int64_t first_batch, int n_steps, uint64_t iteration0, float* step_losses,
                        float* grad_sum, void* workspace, size_t workspace_bytes, void* stream);
 
+/* Row-strided variants (dynamic ANN, Readme.md:19; no code in the snapshot): row i of the input is the dims[0] contiguous
+ * floats starting at X + i * x_row_stride.  x_row_stride == dims[0] is the dense matrix of the plain entry points (which
+ * call these); x_row_stride = F < dims[0] lays n_lags = dims[0] / F overlapping LAG WINDOWS over a raw series of
+ * F-feature rows -- window i = rows i .. i + n_lags - 1, lag-major, exactly what dlas_lag_windows_f32 would materialise
+ * (bit-identical results), without the n_lags-fold copy: a 24-lag window over 8 features costs 36 bytes of HBM traffic
+ * per sample instead of 772.  The series must hold n_rows + n_lags - 1 rows; y[i] belongs to window i; batch b of the
+ * step loop starts b * batch rows further.  DLAS_MODE_TC needs x_row_stride % 4 == 0. */
+int dlas_mlp_grad_strided(const int* dims, int n_layers, int loss, int mode, const float* params,
+                          const float* X, size_t x_row_stride, const float* y, size_t n_rows, float* grad_sum,
+                          void* workspace, size_t workspace_bytes, void* stream);
+int dlas_mlp_fit_steps_strided(const int* dims, int n_layers, int loss, int mode, const dlas_opt_cfg* cfg,
+                               float* params, float* m, float* v, const float* X, size_t x_row_stride,
+                               const float* y, size_t n_rows, int batch, const int64_t* batch_order_host,
+                               int64_t first_batch, int n_steps, uint64_t iteration0, float* step_losses,
+                               float* grad_sum, void* workspace, size_t workspace_bytes, void* stream);
+int dlas_mlp_predict_strided(const int* dims, int n_layers, int mode, const float* params, const float* X,
+                             size_t x_row_stride, size_t n_rows, float* yhat, void* stream);
+int dlas_mlp_eval_loss_strided(const int* dims, int n_layers, int loss, int mode, const float* params,
+                               const float* X, size_t x_row_stride, const float* y, size_t n_rows,
+                               float* loss_sum, void* workspace, size_t workspace_bytes, void* stream);
+
 /* Inference (model.predict / test_on_batch, cnn.py:132): yhat (n_rows, dims[n_layers]). */
 int dlas_mlp_predict(const int* dims, int n_layers, int mode, const float* params, const float* X,
                      size_t n_rows, float* yhat, void* stream);

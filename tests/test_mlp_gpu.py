@@ -238,3 +238,62 @@ def test_graph_replayed_steps_match_host_driven_steps(dl, mode, dims):
                           O.mlp_fit_steps(pr, dims, X.astype(np.float64), y.astype(np.float64), batch, 4, O.LOSS_MSE, cfg, stt)])
     np.testing.assert_allclose(st.recent_losses(8), ref[-8:], rtol=3e-4 if mode == "tc" else 1e-4)
     assert _relerr(a.get_weights_flat(), pr) < 1e-4
+
+
+def test_lag_windows_read_in_place_match_the_materialised_windows(dl):
+    """dlas_mlp_*_strided: 24-lag windows laid over the raw (n, 8) series (row stride 8 floats, nothing copied) give the
+    SAME BITS as the materialised (n-23, 192) window matrix -- gradient sums, predictions, loss sum and three fit steps."""
+    from dlas import ops
+    dims = [192, 256, 256, 1]
+    n = 3000
+    s, ys = O.synth_rows(O.BASE_SEED, 0, n, 8)
+    series = _cuda(s)
+    yw = _cuda(ys[23:])
+    W = ops.lag_windows(series, 24)                 # materialised: (n - 23, 192)
+    V = dl.LagWindows(series, 24)                   # in place
+    assert V.shape == tuple(W.shape)
+    p = _cuda(O.glorot_init(dims, 5))
+    ws = ops.mlp_workspace(dims, 0)
+    ga, gb = (torch.zeros(p.numel() + 1, device="cuda") for _ in range(2))
+    ops.mlp_grad(dims, 0, 0, p, W, yw, ga, ws)
+    ops.mlp_grad(dims, 0, 0, p, V, yw, gb, ws)
+    assert torch.equal(ga, gb)
+    assert torch.equal(ops.mlp_predict(dims, 0, p, W), ops.mlp_predict(dims, 0, p, V))
+    assert torch.equal(ops.mlp_eval_loss(dims, 1, 0, p, W, yw, ws), ops.mlp_eval_loss(dims, 1, 0, p, V, yw, ws))
+    # a slice of the windows (rows 100..1124) and the batch loop (3 steps of 512 windows, shuffled order)
+    ops.mlp_grad(dims, 0, 0, p, W[100:1124].contiguous(), yw[100:1124].contiguous(), ga, ws)
+    ops.mlp_grad(dims, 0, 0, p, V[100:1124], yw[100:1124].contiguous(), gb, ws)
+    assert torch.equal(ga, gb)
+    cfg = dl.SGD(lr=0.001, momentum=0.99, decay=1e-6, nesterov=True).cfg()
+    res = []
+    for Xin in (W, V):
+        q = p.clone()
+        m, v = torch.zeros_like(q), torch.zeros_like(q)
+        ls = torch.zeros(3, device="cuda")
+        ops.mlp_fit_steps(dims, 0, 0, cfg, q, m, v, Xin, yw, 512, 3, 0, ls, ga, ws, batch_order=[4, 0, 2])
+        torch.cuda.synchronize()
+        res.append((q, ls))
+    assert torch.equal(res[0][0], res[1][0]) and torch.equal(res[0][1], res[1][1])
+    # through the facade
+    model = dl.Sequential([dl.Dense(192, 256, activation="relu"), dl.Dense(256, 256, activation="relu"), dl.Dense(256, 1)])
+    model.compile(loss="mse", optimizer=dl.SGD(lr=0.001, momentum=0.99, decay=1e-6, nesterov=True))
+    model.set_weights_flat(p.cpu().numpy())
+    h = model.fit(V, yw, nb_epoch=1, batch_size=512, verbose=0)
+    assert np.isfinite(h["loss"][0])
+    assert model.evaluate(V, yw) == pytest.approx(model.evaluate(W, yw), rel=0, abs=0)
+
+
+def test_lag_windows_in_tensor_core_mode(dl):
+    """4-lag windows over an 8-feature series are a 32-256-256-1 dynamic ANN: the tcgen05 kernel reads them in place too."""
+    from dlas import ops
+    dims = [32, 256, 256, 1]
+    s, ys = O.synth_rows(O.BASE_SEED, 0, 5000, 8)
+    series, yw = _cuda(s), _cuda(ys[3:])
+    W, V = ops.lag_windows(series, 4), dl.LagWindows(series, 4)
+    p = _cuda(O.glorot_init(dims, 5))
+    ws = ops.mlp_workspace(dims, dl.MODE_TC)
+    ga, gb = (torch.zeros(p.numel() + 1, device="cuda") for _ in range(2))
+    ops.mlp_grad(dims, 0, dl.MODE_TC, p, W, yw, ga, ws)
+    ops.mlp_grad(dims, 0, dl.MODE_TC, p, V, yw, gb, ws)
+    torch.cuda.synchronize()
+    assert torch.isfinite(ga).all() and torch.equal(ga, gb)

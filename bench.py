@@ -449,7 +449,7 @@ def main():
         dist.all_reduce(t, op=dist.ReduceOp.MAX)
     pred_s = float(t.item()) * 1e-3 / 5
     predict = {"rows_per_s": N * n_pred / pred_s, "rows_per_gpu_per_call": n_pred, "ms_per_call": pred_s * 1e3,
-               "kernel": "fp32 CUDA-core forward (both modes)",
+               "kernel": "forward-only kind of the tcgen05 kernel (mlp_tc_kernel<K_PREDICT>)" if mode == "tc" else "fp32 CUDA-core forward",
                "hbm_frac": n_pred * (DIMS[0] * 4 + 4) / pred_s / 1e9 / pk["hbm"],
                "tensor_frac_of_bf16_burst": n_pred * 147_968 / pred_s / 1e12 / pk["tf_burst"]}
     del yhat

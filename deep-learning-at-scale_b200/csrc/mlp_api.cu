@@ -23,7 +23,11 @@ int tc_grad(const int* dims, int n_layers, int loss, const float* params, const 
             const long long* cursor = nullptr, size_t parity_stride = 0, size_t ldx = 0);
 int tc_fit_step(const int* dims, int n_layers, int loss, const dlas_opt_cfg* cfg, float* params, float* m, float* v,
                 const float* X, const float* y, size_t n_rows, uint64_t iteration, float* loss_out, void* workspace,
-                size_t workspace_bytes, cudaStream_t st, bool chained, size_t ldx = 0);
+                size_t workspace_bytes, cudaStream_t st, bool chained, size_t ldx = 0, bool more_follow = false);
+int tc_predict(const int* dims, int n_layers, const float* params, const float* X, size_t n_rows, float* yhat, cudaStream_t st,
+               size_t ldx);
+int tc_eval_loss(const int* dims, int n_layers, int loss, const float* params, const float* X, const float* y, size_t n_rows,
+                 float* loss_sum, void* workspace, size_t workspace_bytes, cudaStream_t st, size_t ldx);
 int tc_status(const void* workspace, size_t workspace_bytes, cudaStream_t st);
 size_t tc_dp_recv_words(int world);
 int tc_dp_step(const int* dims, int n_layers, int loss, const dlas_opt_cfg* cfg, float* params, float* m, float* v,
@@ -159,7 +163,8 @@ extern "C" int dlas_mlp_fit_steps_strided(const int* dims, int n_layers, int los
     const float* yb = y + (size_t)b * batch * dL;
     if (mode == DLAS_MODE_TC) {   // gradient kernel + (reduction fused with the update): two launches per step
       rc = tc_fit_step(dims, n_layers, loss, cfg, params, m, v, Xb, yb, batch, iteration0 + (uint64_t)s,
-                       step_losses ? step_losses + s : nullptr, workspace, workspace_bytes, st, /*chained=*/s > 0, x_row_stride);
+                       step_losses ? step_losses + s : nullptr, workspace, workspace_bytes, st, /*chained=*/s > 0, x_row_stride,
+                       /*more_follow=*/s + 1 < n_steps);
       if (rc != DLAS_OK) return rc;
       continue;
     }
@@ -185,9 +190,12 @@ extern "C" int dlas_mlp_predict_strided(const int* dims, int n_layers, int mode,
   if (rc != DLAS_OK) return rc;
   DLAS_REQUIRE(mode == DLAS_MODE_FP32 || mode == DLAS_MODE_TC, "dlas_mlp_predict: unknown mode %d", mode);
   DLAS_REQUIRE(params && (n_rows == 0 || (X && yhat)), "dlas_mlp_predict: null pointer");
-  // inference runs the fp32 kernel in both modes (HBM-leaning)
   rc = check_stride("dlas_mlp_predict_strided", dims, x_row_stride);
   if (rc != DLAS_OK) return rc;
+  if (mode == DLAS_MODE_TC) {   // forward-only kind of the tcgen05 kernel
+    if (!tc_supported(dims, n_layers)) { set_error("dlas_mlp_predict: DLAS_MODE_TC does not support these layer widths"); return DLAS_ERR_UNSUPPORTED_SHAPE; }
+    return tc_predict(dims, n_layers, params, X, n_rows, yhat, (cudaStream_t)stream, x_row_stride);
+  }
   return simt_predict(dims, n_layers, params, X, n_rows, yhat, (cudaStream_t)stream, x_row_stride);
 }
 
@@ -209,6 +217,10 @@ extern "C" int dlas_mlp_eval_loss_strided(const int* dims, int n_layers, int los
   DLAS_REQUIRE(params && loss_sum && (n_rows == 0 || (X && y)), "dlas_mlp_eval_loss: null pointer");
   rc = check_stride("dlas_mlp_eval_loss_strided", dims, x_row_stride);
   if (rc != DLAS_OK) return rc;
+  if (mode == DLAS_MODE_TC) {
+    if (!tc_supported(dims, n_layers)) { set_error("dlas_mlp_eval_loss: DLAS_MODE_TC does not support these layer widths"); return DLAS_ERR_UNSUPPORTED_SHAPE; }
+    return tc_eval_loss(dims, n_layers, loss, params, X, y, n_rows, loss_sum, workspace, workspace_bytes, (cudaStream_t)stream, x_row_stride);
+  }
   return simt_eval_loss(dims, n_layers, loss, params, X, y, n_rows, loss_sum, workspace, workspace_bytes,
                         (cudaStream_t)stream, x_row_stride);
 }

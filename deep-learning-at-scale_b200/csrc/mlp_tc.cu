@@ -68,7 +68,12 @@ constexpr uint32_t S_W1 = 0, S_W2 = S_W1 + K1 * 4 * 128, S_X = S_W2 + 65536, S_H
 constexpr int F_B2 = 0, F_W3 = 128, F_Y = 256 /*[2][128]*/, F_PART = 512 /*[2][128]*/, F_RP = 768 /*[CSPLIT][128]*/,
               F_RED = F_RP + CSPLIT * 128 /*[4][128]*/, F_END = F_RED + 512;
 constexpr uint32_t S_BAR = S_F32 + F_END * 4;
-enum { B_DONE = 0, B_FREE, B_X0, B_X1, B_H1A, B_H1, B_DZ2, B_DW2A, B_DW2B, B_DZ1A, B_DZ1, B_DW1, B_ALL, B_XC0, B_XC1, N_BARS };
+enum { B_DONE = 0, B_FREE, B_X0, B_X1, B_H1A, B_H1, B_DZ2, B_DW2A, B_DW2B, B_DZ1A, B_DZ1, B_DW1, B_ALL, B_XC0, B_XC1, B_WIMG, N_BARS };
+// fp16 image of the weights in the kernel's own tile layout, kept in the workspace by the finishing kernel of a step loop
+// (tc_reduce_kernel writes every updated parameter into it), so that the next step's set-up is three bulk copies instead of
+// a 160 KB fp32 read + convert per CTA:  [sW1 tile 24 KB: W1 rows, b1 row, zero rows][sW2 tile of rank 0 64 KB][rank 1 64 KB]
+constexpr uint32_t IMG_W1_BYTES = K1 * 4 * 128, IMG_W2_BYTES = 65536, IMG_BYTES = IMG_W1_BYTES + 2 * IMG_W2_BYTES;
+enum { K_TRAIN = 0, K_EVAL = 1, K_PREDICT = 2 };
 constexpr uint32_t S_TMEM = S_BAR + N_BARS * 8;
 constexpr uint32_t SMEM_BYTES = S_TMEM + 16;
 
@@ -126,11 +131,17 @@ __device__ __forceinline__ unsigned long long globaltimer_ns() {
 #define TRACE_M(k) do { } while (0)
 #endif
 
+// KIND: K_TRAIN forward + loss + backward (partials out); K_EVAL forward + loss (loss partial out: validation pass,
+// cnn.py:121); K_PREDICT forward only (yhat out: model.predict / test_on_batch, cnn.py:132).  The forward-only kinds run
+// Z1 | E1 | Z2h | partial dot + exchange per tile and leave the accumulator columns unused.
+template <int KIND>
 __global__ void __cluster_dims__(2, 1, 1) __launch_bounds__(NT, 1)
 mlp_tc_kernel(const int loss_kind, const float* __restrict__ params, const float* __restrict__ X_base,
               const float* __restrict__ y_base, const size_t n_rows, float* __restrict__ partials,
               unsigned* __restrict__ err_flag, const unsigned call_id, long long* __restrict__ trace,
-              const long long* __restrict__ cursor, const int rows_ready, const size_t ldx) {
+              const long long* __restrict__ cursor, const int rows_ready, const size_t ldx,
+              const uint8_t* __restrict__ w_image, float* __restrict__ yhat_out) {
+  constexpr bool TRAIN = (KIND == K_TRAIN);
   // ldx: floats between consecutive rows of X (32 for a dense matrix; smaller for lag windows laid over a raw series)
   // device-resident batch cursor (replayable steps): this launch works on rows [cursor*n_rows, (cursor+1)*n_rows)
   extern __shared__ __align__(1024) uint8_t smem[];
@@ -162,6 +173,7 @@ mlp_tc_kernel(const int loss_kind, const float* __restrict__ params, const float
     mbar_init(&bars[B_DZ1], N_EPI / 32);
     mbar_init(&bars[B_ALL], 1); mbar_init(&bars[B_DW1], 1); mbar_init(&bars[B_DW2A], 1); mbar_init(&bars[B_DW2B], 1);
     mbar_init(&bars[B_XC0], 1); mbar_init(&bars[B_XC1], 1);   // exchange of the partial output dots: 1 arrival + 512 tx bytes
+    mbar_init(&bars[B_WIMG], 1);                               // weight image: 1 arrival + 88 KB of bulk-copy bytes
     mbar_fence_init();
   }
   if (warp == ISSUER_WARP) tmem_alloc(tmem_slot, TM_COLS);
@@ -176,7 +188,7 @@ mlp_tc_kernel(const int loss_kind, const float* __restrict__ params, const float
     const float* src = X + (row0 + xr) * ldx + xh * XF;
 #pragma unroll
     for (int i = 0; i < XF / 4; ++i) xv[i] = in ? __ldcs(reinterpret_cast<const float4*>(src + i * 4)) : make_float4(0.f, 0.f, 0.f, 0.f);
-    if (tid < TILE) yv = (row0 + tid < n_rows) ? __ldcs(y + row0 + tid) : 0.f;
+    if (KIND != K_PREDICT && tid < TILE) yv = (row0 + tid < n_rows) ? __ldcs(y + row0 + tid) : 0.f;
   };
   // rows_ready: the host states that X / y were NOT written by the kernel that precedes this one in the stream (the
   // library's own step loops: the predecessor is the previous step's finishing kernel).  Only then, and with a host-side
@@ -191,8 +203,17 @@ mlp_tc_kernel(const int loss_kind, const float* __restrict__ params, const float
   asm volatile("griddepcontrol.wait;" ::: "memory");
   const size_t batch0 = cursor ? (size_t)__ldcg(cursor) * n_rows : 0;   // the cursor is written by the previous step's kernels
   const float* __restrict__ X = X_base + batch0 * ldx;
-  const float* __restrict__ y = y_base + batch0;
-  {
+  const float* __restrict__ y = (KIND == K_PREDICT) ? nullptr : y_base + batch0;
+  if (w_image != nullptr) {
+    // the finishing kernel of the previous step left the updated weights as fp16 tiles: fetch them with the copy engine
+    if (tid == 0) {
+      mbar_arrive_expect_tx(&bars[B_WIMG], IMG_W1_BYTES + IMG_W2_BYTES);
+      bulk_g2s(sW1, w_image, IMG_W1_BYTES, &bars[B_WIMG]);
+#pragma unroll
+      for (int c = 0; c < 4; ++c)
+        bulk_g2s(sW2 + c * 16384, w_image + IMG_W1_BYTES + rank * IMG_W2_BYTES + c * 16384, 16384, &bars[B_WIMG]);
+    }
+  } else {
     // sW1 = [W1 ; b1 ; 0]: rows 0..31 weights, row 32 the bias (it multiplies the ones column of [x | 1 | 0]),
     // rows 33..47 zero -> Z1 comes out of the MMA with the bias already added
     for (int idx = tid; idx < K1 * (D1 / 8); idx += NT) {
@@ -223,6 +244,8 @@ mlp_tc_kernel(const int loss_kind, const float* __restrict__ params, const float
         if (idx < D1 * 16) sts128(sW2 + tile_chunk_off(D1, idx >> 4, (idx & 15) * 8), pack8(a[u], b[u]));
       }
     }
+  }
+  {
     if (tid < 128) {
       f32[F_B2 + tid] = __ldg(params + B2_OFF + rank * 128 + tid);
       f32[F_W3 + tid] = __ldg(params + W3_OFF + rank * 128 + tid);
@@ -294,6 +317,7 @@ mlp_tc_kernel(const int loss_kind, const float* __restrict__ params, const float
       __syncwarp();
       ++n;
     };
+    if (w_image != nullptr) ok = mbar_wait(&bars[B_WIMG], 0) && ok;   // bulk copies of the weight tiles have landed
     if (my_tiles > 0) {
       ok = mbar_wait(&bars[B_X0], 0) && ok;
       issue_z1(0, 0);
@@ -328,6 +352,13 @@ mlp_tc_kernel(const int loss_kind, const float* __restrict__ params, const float
       __syncwarp();
       ++n;
       TRACE_M(14);
+      if (!TRAIN) {   // forward only: the next tile's first Z1 half follows at once (work buffer free after the partial-dot pass)
+        if (it + 1 < my_tiles) {
+          ok = mbar_wait(&bars[B_X0 + (xb ^ 1)], ((it + 1) >> 1) & 1) && ok;
+          issue_z1(xb ^ 1, 0);
+        }
+        continue;
+      }
       ok = mbar_wait(&bars[B_DZ2], it & 1) && ok;
       TRACE_M(16);
       fence_after();
@@ -452,7 +483,8 @@ mlp_tc_kernel(const int loss_kind, const float* __restrict__ params, const float
         TRACE_E(40);
         take(v);
         TRACE_E(43);
-        if (h == 0 && it > 0) ok = mbar_wait(&bars[B_DW1], (it - 1) & 1) && ok;   // dW1 of the previous tile still reads sH1
+        if (TRAIN && h == 0 && it > 0) ok = mbar_wait(&bars[B_DW1], (it - 1) & 1) && ok;   // dW1 of the previous tile still reads sH1
+        // (forward only: sH1 was last read by the previous tile's Z2h, whose completion this thread has already seen)
         const int c0 = h * 128 + hh * CW;
 #pragma unroll
         for (int g8 = 0; g8 < CW / 8; ++g8) {   // relu on packed halves: one F2FP + one HMNMX2 per two elements
@@ -514,10 +546,17 @@ mlp_tc_kernel(const int loss_kind, const float* __restrict__ params, const float
       if (tid == 0) mbar_arrive_expect_tx(&bars[B_XC0 + buf], 512);
       if (hh == 0) st_async_f32(peer_part + (uint32_t)(buf * 128 + row) * 4, mine, peer_xc + (uint32_t)buf * 8);
       TRACE_E(24);
+      // the next tile's rows (loaded during the Z2h wait) are converted and stored while the partial dots cross the pair
+      if (it + 1 < my_tiles) x_store((it + 1) & 1);
       ok = mbar_wait(&bars[B_XC0 + buf], (it >> 1) & 1) && ok;
       TRACE_E(25);
       const float other = f32[F_PART + buf * 128 + row];
       const float yhat = (rank == 0 ? mine + other : other + mine) + b3;   // same value on both CTAs
+      if (KIND == K_PREDICT) {
+        // a timed-out wait in this thread poisons its rows (the predict entry point has no status words)
+        if (rank == 0 && hh == 0 && row_valid) yhat_out[row0 + row] = ok ? yhat : __int_as_float(0x7fc00000);
+        continue;
+      }
       float g = 0.f;
       if (row_valid) {
         const float d = yhat - f32[F_Y + buf * 128 + row];
@@ -532,6 +571,7 @@ mlp_tc_kernel(const int loss_kind, const float* __restrict__ params, const float
         }
         if (hh == 0) { acc_loss += lo; acc_b3 += g; }
       }
+      if (KIND == K_EVAL) continue;
       {
         float4 cw[2][2];
         auto fetch = [&](int blk, int s) {
@@ -559,7 +599,6 @@ mlp_tc_kernel(const int loss_kind, const float* __restrict__ params, const float
       fence_async_smem();
       warp_arrive(lane, &bars[B_DZ2]);
       TRACE_E(26);
-      if (it + 1 < my_tiles) x_store((it + 1) & 1);
       // ---- (d) dZ1p = relu'(H1) o dH1p in place over H1, two halves of 128 columns ----------------------
 #pragma unroll 1
       for (int h = 0; h < 2; ++h) {
@@ -593,7 +632,16 @@ mlp_tc_kernel(const int loss_kind, const float* __restrict__ params, const float
 
     // ---- drain the accumulators into this CTA's partial vector -----------------------------------------
     float* my = partials + (size_t)blockIdx.x * PSTRIDE;
-    if (my_tiles > 0) {
+    if (KIND == K_EVAL && my_tiles > 0) {   // loss sum of this pair's rows: fixed-order sum over the 128 rows
+      if (hh == 0) f32[F_RED + row] = acc_loss;
+      named_bar_sync(1, N_EPI);
+      if (rank == 0 && tid == 0) {
+        float s = 0.f;
+        for (int i = 0; i < 128; ++i) s += f32[F_RED + i];
+        my[N_PARAMS] = s;
+      }
+    }
+    if (TRAIN && my_tiles > 0) {
       TRACE_E(30);
       ok = mbar_wait(&bars[B_ALL], 0) && ok;
       fence_after();
@@ -653,7 +701,7 @@ mlp_tc_kernel(const int loss_kind, const float* __restrict__ params, const float
     }
   }
   TRACE_E(32);
-  if (!ok && lane == 0) atomicExch(err_flag, call_id);
+  if (!ok && lane == 0 && err_flag != nullptr) atomicExch(err_flag, call_id);
   if (clk_owner) {   // one writer, launches are stream-ordered
     g_clk_sum[0] += (unsigned long long)(clock64() - clk_c0);
     g_clk_sum[1] += globaltimer_ns() - clk_g0;
@@ -718,6 +766,24 @@ __device__ __forceinline__ uint2 ld_poll(unsigned long long addr) {
   return make_uint2((unsigned)(w & 0xffffffffull), (unsigned)(w >> 32));
 }
 
+// the updated parameter i as fp16 at its place in the weight image (see IMG_*); b2, w3, b3 are not part of the operand tiles
+__device__ __forceinline__ void img_store(uint8_t* img, int i, float p) {
+  uint32_t off;
+  if (i < B1_OFF) {
+    const int r = i / D1, c = i - r * D1;
+    off = tile_chunk_off(K1, r, c & ~7) + (uint32_t)(c & 7) * 2;
+  } else if (i < W2_OFF) {
+    const int c = i - B1_OFF;
+    off = tile_chunk_off(K1, D0, c & ~7) + (uint32_t)(c & 7) * 2;        // the bias row of [W1 ; b1 ; 0]
+  } else if (i < B2_OFF) {
+    const int k = (i - W2_OFF) / D2, c2 = (i - W2_OFF) - k * D2, cc = c2 & 127;
+    off = IMG_W1_BYTES + (uint32_t)(c2 >> 7) * IMG_W2_BYTES + tile_chunk_off(D1, k, cc & ~7) + (uint32_t)(cc & 7) * 2;
+  } else {
+    return;
+  }
+  *reinterpret_cast<__half*>(img + off) = __float2half_rn(p);
+}
+
 constexpr int RG = 4;   // thread groups per block of 64 entries (8 measured no faster)
 constexpr int FIN_MAXW = 8;
 template <int MODE>
@@ -725,7 +791,7 @@ __global__ void __launch_bounds__(64 * RG, 8)   // 8 blocks per SM: the whole gr
 tc_reduce_kernel(const float* __restrict__ partials, int n_active_pairs, unsigned* __restrict__ err_flag,
                  unsigned call_id, float* __restrict__ out, OptScalars opt, float grad_scale, float* __restrict__ params,
                  float* __restrict__ m, float* __restrict__ v, float* __restrict__ loss_out,
-                 const long long* __restrict__ state, size_t parity_stride, const FinDp dp) {
+                 const long long* __restrict__ state, size_t parity_stride, const FinDp dp, uint8_t* __restrict__ img_out) {
   // 64 consecutive entries per block; the list of contributing CTAs is cut into RG contiguous parts summed by RG
   // thread groups (more loads in flight: the pass is latency-bound), then added in quarter order -> still deterministic
   __shared__ float red[RG - 1][64];
@@ -791,6 +857,11 @@ tc_reduce_kernel(const float* __restrict__ partials, int n_active_pairs, unsigne
       params[i] = p;
       m[i] = mi;
       if (opt.kind != 0) v[i] = vi;
+      if (img_out) {
+        img_store(img_out, i, p);
+        if (i < (K1 - D0 - 1) * D1)      // rows 33..47 of the [W1 ; b1 ; 0] tile are zero (the workspace is not initialised)
+          *reinterpret_cast<__half*>(img_out + tile_chunk_off(K1, D0 + 1 + i / D1, (i % D1) & ~7) + (uint32_t)(i & 7) * 2) = __float2half_rn(0.f);
+      }
     }
     return;
   }
@@ -837,6 +908,11 @@ tc_reduce_kernel(const float* __restrict__ partials, int n_active_pairs, unsigne
       params[i] = p;
       m[i] = mi;
       if (o_dev.kind != 0) v[i] = vi;
+      if (img_out) {
+        img_store(img_out, i, p);
+        if (i < (K1 - D0 - 1) * D1)
+          *reinterpret_cast<__half*>(img_out + tile_chunk_off(K1, D0 + 1 + i / D1, (i % D1) & ~7) + (uint32_t)(i & 7) * 2) = __float2half_rn(0.f);
+      }
     }
   }
   FIN_STAMP(3);
@@ -854,27 +930,49 @@ tc_reduce_kernel(const float* __restrict__ partials, int n_active_pairs, unsigne
 }
 
 
+// validation / test loss (K_EVAL launches): sum of the rank-0 CTAs' loss partials in CTA order
+__global__ void __launch_bounds__(32)
+tc_loss_reduce_kernel(const float* __restrict__ partials, int n_active_pairs, unsigned* __restrict__ err_flag, unsigned call_id,
+                      float* __restrict__ loss_sum) {
+  asm volatile("griddepcontrol.launch_dependents;" ::: "memory");
+  asm volatile("griddepcontrol.wait;" ::: "memory");
+  if (threadIdx.x == 0) {
+    float s = 0.f;
+    for (int p = 0; p < n_active_pairs; ++p) s += partials[(size_t)(2 * p) * PSTRIDE + N_PARAMS];
+    if (*err_flag == call_id) s = __int_as_float(0x7fc00000);
+    if (!(fabsf(s) <= 3.0e38f)) err_flag[1] = call_id;
+    err_flag[2] = call_id;
+    *loss_sum = s;
+  }
+}
+
 int n_ctas() { return (sm_count() / 2) * 2; }
 unsigned g_call_id = 0x5eed0000u;
 
+size_t ws_partials_bytes() { return (size_t)n_ctas() * PSTRIDE * sizeof(float); }
+size_t ws_need() { return ws_partials_bytes() + 256 + IMG_BYTES; }
+uint8_t* ws_image(void* workspace) { return (uint8_t*)workspace + ws_partials_bytes() + 256; }
+
+template <int KIND = K_TRAIN>
 int launch_main(int loss, const float* params, const float* X, const float* y, size_t n_rows, void* workspace,
                 size_t workspace_bytes, cudaStream_t st, float** partials_out, unsigned** err_out, int* n_active_pairs,
-                const long long* cursor = nullptr, bool rows_ready = false, size_t ldx = 0) {
+                const long long* cursor = nullptr, bool rows_ready = false, size_t ldx = 0, const uint8_t* w_image = nullptr,
+                float* yhat = nullptr) {
   if (ldx == 0) ldx = D0;
   DLAS_REQUIRE(ldx % 4 == 0, "mlp (tc): the row stride of X must be a multiple of 4 floats (16-byte row loads), got %zu", ldx);
-  size_t need = (size_t)n_ctas() * PSTRIDE * sizeof(float) + 256;
-  if (workspace == nullptr || workspace_bytes < need) {
+  size_t need = ws_need();
+  if (KIND != K_PREDICT && (workspace == nullptr || workspace_bytes < need)) {
     set_error("mlp (tc): workspace of %zu bytes given, %zu needed", workspace_bytes, need);
     return DLAS_ERR_WORKSPACE;
   }
   DLAS_REQUIRE((((uintptr_t)X) & 15) == 0, "mlp (tc): X must be 16-byte aligned");
-  float* partials = (float*)workspace;
-  unsigned* err_flag = (unsigned*)((char*)workspace + (size_t)n_ctas() * PSTRIDE * sizeof(float));
+  float* partials = (KIND == K_PREDICT) ? nullptr : (float*)workspace;
+  unsigned* err_flag = (KIND == K_PREDICT) ? nullptr : (unsigned*)((char*)workspace + ws_partials_bytes());
   static bool attr_set[64] = {};   // the attribute is per device
   int dev = 0;
   DLAS_CUDA(cudaGetDevice(&dev));
   if (dev < 0 || dev >= 64 || !attr_set[dev]) {
-    DLAS_CUDA(cudaFuncSetAttribute(mlp_tc_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)SMEM_BYTES));
+    DLAS_CUDA(cudaFuncSetAttribute(mlp_tc_kernel<KIND>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)SMEM_BYTES));
     if (dev >= 0 && dev < 64) attr_set[dev] = true;
   }
   const int grid = n_ctas();
@@ -899,8 +997,8 @@ int launch_main(int loss, const float* params, const float* X, const float* y, s
     at[0].val.programmaticStreamSerializationAllowed = 1;
     cfg.attrs = at;
     cfg.numAttrs = 1;
-    DLAS_CUDA(cudaLaunchKernelEx(&cfg, mlp_tc_kernel, loss, params, X, y, n_rows, partials, err_flag, g_call_id, trace, cursor,
-                                 rows_ready ? 1 : 0, ldx));
+    DLAS_CUDA(cudaLaunchKernelEx(&cfg, mlp_tc_kernel<KIND>, loss, params, X, y, n_rows, partials, err_flag, g_call_id, trace, cursor,
+                                 rows_ready ? 1 : 0, ldx, w_image, yhat));
   }
   prof_end(pi, st);
   DLAS_LAUNCH_CHECK();
@@ -919,16 +1017,16 @@ int launch_main(int loss, const float* params, const float* X, const float* y, s
   }
 #endif
   size_t n_tiles = (n_rows + TILE - 1) / TILE;
-  *n_active_pairs = (int)(n_tiles < (size_t)(grid / 2) ? n_tiles : (size_t)(grid / 2));
-  *partials_out = partials;
-  *err_out = err_flag;
+  if (n_active_pairs) *n_active_pairs = (int)(n_tiles < (size_t)(grid / 2) ? n_tiles : (size_t)(grid / 2));
+  if (partials_out) *partials_out = partials;
+  if (err_out) *err_out = err_flag;
   return DLAS_OK;
 }
 
 template <int MODE>
 int launch_reduce(cudaStream_t st, const float* partials, int nap, unsigned* err, float* out, OptScalars o,
                   float grad_scale, float* params, float* m, float* v, float* loss_out, const long long* state = nullptr,
-                  size_t parity_stride = 0, const FinDp& dp = FinDp{}) {
+                  size_t parity_stride = 0, const FinDp& dp = FinDp{}, uint8_t* img_out = nullptr) {
   cudaLaunchConfig_t cfg = {};
   cfg.gridDim = dim3((N_PARAMS + 1 + 63) / 64);
   cfg.blockDim = dim3(64 * RG);
@@ -939,7 +1037,7 @@ int launch_reduce(cudaStream_t st, const float* partials, int nap, unsigned* err
   cfg.attrs = at;
   cfg.numAttrs = 1;
   DLAS_CUDA(cudaLaunchKernelEx(&cfg, tc_reduce_kernel<MODE>, partials, nap, err, g_call_id, out, o, grad_scale, params, m, v,
-                               loss_out, state, parity_stride, dp));
+                               loss_out, state, parity_stride, dp, img_out));
   return DLAS_OK;
 }
 
@@ -952,7 +1050,7 @@ bool tc_supported(const int* dims, int n_layers) {
 }
 
 size_t tc_workspace_bytes(const int* dims, int n_layers) {
-  size_t tc = (size_t)n_ctas() * PSTRIDE * sizeof(float) + 256;   // partials + error word
+  size_t tc = ws_need();   // partials + status words + fp16 weight image
   size_t simt = simt_workspace_bytes(dims, n_layers);             // eval / predict share the workspace
   return tc > simt ? tc : simt;
 }
@@ -1006,11 +1104,51 @@ int tc_grad(const int* dims, int n_layers, int loss, const float* params, const 
   return DLAS_OK;
 }
 
+// model.predict / test_on_batch on the tensor cores (forward-only kind of the same kernel; no scratch, no second launch)
+int tc_predict(const int* dims, int n_layers, const float* params, const float* X, size_t n_rows, float* yhat, cudaStream_t st,
+               size_t ldx) {
+  if (!tc_supported(dims, n_layers)) {
+    set_error("DLAS_MODE_TC supports the 32-256-256-1 network only");
+    return DLAS_ERR_UNSUPPORTED_SHAPE;
+  }
+  if (n_rows == 0) return DLAS_OK;
+  return launch_main<K_PREDICT>(DLAS_LOSS_MSE, params, X, nullptr, n_rows, nullptr, 0, st, nullptr, nullptr, nullptr, nullptr, false, ldx,
+                                nullptr, yhat);
+}
+
+// validation / test loss sum on the tensor cores: forward + loss kind, then the sum of the pairs' loss partials
+int tc_eval_loss(const int* dims, int n_layers, int loss, const float* params, const float* X, const float* y, size_t n_rows,
+                 float* loss_sum, void* workspace, size_t workspace_bytes, cudaStream_t st, size_t ldx) {
+  if (!tc_supported(dims, n_layers)) {
+    set_error("DLAS_MODE_TC supports the 32-256-256-1 network only");
+    return DLAS_ERR_UNSUPPORTED_SHAPE;
+  }
+  if (n_rows == 0) {
+    DLAS_CUDA(cudaMemsetAsync(loss_sum, 0, sizeof(float), st));
+    return DLAS_OK;
+  }
+  float* partials; unsigned* err; int nap;
+  int rc = launch_main<K_EVAL>(loss, params, X, y, n_rows, workspace, workspace_bytes, st, &partials, &err, &nap, nullptr, false, ldx);
+  if (rc != DLAS_OK) return rc;
+  cudaLaunchConfig_t cfg = {};
+  cfg.gridDim = dim3(1);
+  cfg.blockDim = dim3(32);
+  cfg.stream = st;
+  cudaLaunchAttribute at[1];
+  at[0].id = cudaLaunchAttributeProgrammaticStreamSerialization;
+  at[0].val.programmaticStreamSerializationAllowed = 1;
+  cfg.attrs = at;
+  cfg.numAttrs = 1;
+  DLAS_CUDA(cudaLaunchKernelEx(&cfg, tc_loss_reduce_kernel, (const float*)partials, nap, err, g_call_id, loss_sum));
+  return DLAS_OK;
+}
+
 // one whole single-GPU step: gradient kernel, then reduction fused with the optimiser update
 int tc_fit_step(const int* dims, int n_layers, int loss, const dlas_opt_cfg* cfg, float* params, float* m, float* v,
                 const float* X, const float* y, size_t n_rows, uint64_t iteration, float* loss_out, void* workspace,
-                size_t workspace_bytes, cudaStream_t st, bool chained, size_t ldx) {
-  // chained: the kernel before this step in the stream is the previous step's finishing kernel of the same call
+                size_t workspace_bytes, cudaStream_t st, bool chained, size_t ldx, bool more_follow) {
+  // chained: the kernel before this step in the stream is the previous step's finishing kernel of the same call (which left
+  // the fp16 weight image in the workspace); more_follow: another step of the same call follows (leave the image for it)
   if (!tc_supported(dims, n_layers)) {
     set_error("DLAS_MODE_TC supports the 32-256-256-1 network only");
     return DLAS_ERR_UNSUPPORTED_SHAPE;
@@ -1020,9 +1158,11 @@ int tc_fit_step(const int* dims, int n_layers, int loss, const dlas_opt_cfg* cfg
   if (rc != DLAS_OK) return rc;
   DLAS_REQUIRE(o.kind == DLAS_OPT_SGD || v != nullptr, "Adam needs the second-moment buffer v");
   float* partials; unsigned* err; int nap;
-  rc = launch_main(loss, params, X, y, n_rows, workspace, workspace_bytes, st, &partials, &err, &nap, nullptr, chained, ldx);
+  rc = launch_main(loss, params, X, y, n_rows, workspace, workspace_bytes, st, &partials, &err, &nap, nullptr, chained, ldx,
+                   chained ? ws_image(workspace) : nullptr);
   if (rc != DLAS_OK) return rc;
-  rc = launch_reduce<FIN_UPDATE>(st, partials, nap, err, nullptr, o, 1.0f / (float)n_rows, params, m, v, loss_out);
+  rc = launch_reduce<FIN_UPDATE>(st, partials, nap, err, nullptr, o, 1.0f / (float)n_rows, params, m, v, loss_out, nullptr, 0, FinDp{},
+                                 more_follow ? ws_image(workspace) : nullptr);
   if (rc != DLAS_OK) return rc;
   return DLAS_OK;
 }
@@ -1073,9 +1213,10 @@ int tc_dp_step(const int* dims, int n_layers, int loss, const dlas_opt_cfg* cfg,
       if (rc != DLAS_OK) return rc;
     }
     int rc = launch_main(loss, params, Xs, ys, batch_rows, workspace, workspace_bytes, st, &partials, &err, &nap,
-                         reinterpret_cast<const long long*>(state), /*rows_ready=*/s > 0);
+                         reinterpret_cast<const long long*>(state), /*rows_ready=*/s > 0, 0, s > 0 ? ws_image(workspace) : nullptr);
     if (rc != DLAS_OK) return rc;
-    rc = launch_reduce<FIN_EXCHANGE>(st, partials, nap, err, nullptr, o, grad_scale, params, m, v, nullptr, nullptr, 0, dp);
+    rc = launch_reduce<FIN_EXCHANGE>(st, partials, nap, err, nullptr, o, grad_scale, params, m, v, nullptr, nullptr, 0, dp,
+                                     s + 1 < n_steps ? ws_image(workspace) : nullptr);
     if (rc != DLAS_OK) return rc;
   }
   return DLAS_OK;

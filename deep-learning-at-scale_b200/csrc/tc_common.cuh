@@ -184,6 +184,13 @@ __device__ __forceinline__ void st_cluster_f32(uint32_t caddr, float v) {
   asm volatile("st.shared::cluster.f32 [%0], %1;" ::"r"(caddr), "f"(v) : "memory");
 }
 
+// bulk copy global -> this CTA's shared memory (TMA engine, no tensor map: UBLKCP); completes `bytes` transaction bytes on
+// the mbarrier.  Addresses and size are multiples of 16.
+__device__ __forceinline__ void bulk_g2s(uint32_t sdst, const void* gsrc, uint32_t bytes, uint64_t* bar) {
+  asm volatile("cp.async.bulk.shared::cluster.global.mbarrier::complete_tx::bytes [%0], [%1], %2, [%3];" ::"r"(sdst), "l"(gsrc),
+               "r"(bytes), "r"(smem_u32(bar)) : "memory");
+}
+
 // packed fp16 helpers for the epilogues (one instruction per two elements)
 __device__ __forceinline__ uint32_t relu_h2(uint32_t a) {
   uint32_t r;

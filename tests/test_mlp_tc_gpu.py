@@ -357,3 +357,59 @@ def test_dp_step_follows_the_batch_order(dl):
         torch.cuda.synchronize()
         res.append((p.clone(), ls.clone()))
     assert torch.equal(res[0][0], res[1][0]) and torch.equal(res[0][1], res[1][1])
+
+
+@pytest.mark.parametrize("n", [1, 127, 128, 9472 * 2 + 77, 300000])
+def test_predict_and_eval_loss_on_the_tensor_cores(dl, n):
+    """model.predict / test_on_batch (cnn.py:132) in tensor-core mode run the forward-only kinds of the tcgen05 kernel.
+    Stated tolerance: every prediction within 2e-3 of max|yhat| of the fp64 oracle (one row's fp16 operand rounding,
+    2^-11 per term, is not averaged over a batch); loss sums within 3e-4 from 4096 rows up (averaged over rows, like the
+    training loss), 1e-2 below."""
+    from dlas import ops
+    X, y = O.synth_rows(O.BASE_SEED, 77, n, 32)
+    p = O.glorot_init(DIMS, 21)
+    p[8192:8448] = 0.05 * np.sin(np.arange(256))
+    p[73984:74240] = 0.05 * np.cos(np.arange(256))
+    p[-1] = 0.1
+    Xd, yd, pd = _cuda(X), _cuda(y), _cuda(p)
+    ref = O.mlp_forward(p.astype(np.float64), DIMS, X.astype(np.float64))[-1]
+    got = ops.mlp_predict(DIMS, dl.MODE_TC, pd, Xd).cpu().numpy()
+    assert got.shape == (n, 1) and np.isfinite(got).all()
+    assert np.abs(got - ref).max() < 2e-3 * max(1.0, np.abs(ref).max())
+    ws = ops.mlp_workspace(DIMS, dl.MODE_TC)
+    for loss in (O.LOSS_MSE, O.LOSS_MAE_CLIP):
+        yy = y * (8.0 if loss == O.LOSS_MAE_CLIP else 1.0)
+        ls = float(ops.mlp_eval_loss(DIMS, loss, dl.MODE_TC, pd, Xd, _cuda(yy), ws).item())
+        ops.mlp_status(DIMS, dl.MODE_TC, ws)
+        lr, _ = O.mlp_loss_grad_sums(p.astype(np.float64), DIMS, X.astype(np.float64), yy.astype(np.float64).reshape(-1, 1), loss)
+        # a loss over few rows carries single predictions' operand rounding: 1e-2 below 4096 rows, the mode's 3e-4 above
+        tol = (LOSS_TOL if n >= 4096 else 1e-2) + (2.0 / n if loss == O.LOSS_MAE_CLIP else 0.0)
+        assert ls == pytest.approx(lr, rel=tol, abs=1e-6)
+    # deterministic
+    assert np.array_equal(got, ops.mlp_predict(DIMS, dl.MODE_TC, pd, Xd).cpu().numpy())
+
+
+def test_step_loop_uses_the_same_weights_as_single_steps(dl):
+    """Inside a multi-step call the forward/backward kernel takes its fp16 weight tiles from the image the previous step's
+    finishing kernel left in the workspace (bulk copies) instead of converting the fp32 parameters itself: the bits must be
+    the same as three calls of one step each (which always convert)."""
+    from dlas import ops
+    batch, nb = 4096, 3
+    X, y = O.synth_rows(O.BASE_SEED, 0, batch * nb, 32)
+    Xd, yd = _cuda(X), _cuda(y)
+    ws = ops.mlp_workspace(DIMS, dl.MODE_TC)
+    res = []
+    for opt in (dl.SGD(lr=0.001, momentum=0.99, decay=1e-6, nesterov=True), dl.Adam()):
+        outs = []
+        for single in (False, True):
+            p = _cuda(O.glorot_init(DIMS, O.BASE_SEED))
+            m, v = torch.zeros_like(p), torch.zeros_like(p)
+            gs, ls = torch.zeros(p.numel() + 1, device="cuda"), torch.zeros(nb, device="cuda")
+            if single:
+                for s in range(nb):
+                    ops.mlp_fit_steps(DIMS, dl.LOSS_MSE, dl.MODE_TC, opt.cfg(), p, m, v, Xd, yd, batch, 1, s, ls[s:], gs, ws, first_batch=s)
+            else:
+                ops.mlp_fit_steps(DIMS, dl.LOSS_MSE, dl.MODE_TC, opt.cfg(), p, m, v, Xd, yd, batch, nb, 0, ls, gs, ws)
+            torch.cuda.synchronize()
+            outs.append((p.clone(), ls.clone()))
+        assert torch.equal(outs[0][0], outs[1][0]) and torch.equal(outs[0][1], outs[1][1])

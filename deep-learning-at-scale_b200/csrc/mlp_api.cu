@@ -29,6 +29,19 @@ int tc_predict(const int* dims, int n_layers, const float* params, const float* 
 int tc_eval_loss(const int* dims, int n_layers, int loss, const float* params, const float* X, const float* y, size_t n_rows,
                  float* loss_sum, void* workspace, size_t workspace_bytes, cudaStream_t st, size_t ldx);
 int tc_status(const void* workspace, size_t workspace_bytes, cudaStream_t st);
+// mlp_tc64.cu: the d0-64-64-1 network (d0 <= 15) on tcgen05, one CTA per tile
+bool tc64_supported(const int* dims, int n_layers);
+size_t tc64_workspace_bytes(const int* dims);
+int tc64_status(const int* dims, const void* workspace, size_t workspace_bytes, cudaStream_t st);
+int tc64_grad(const int* dims, int loss, const float* params, const float* X, const float* y, size_t n_rows, float* grad_sum,
+              void* workspace, size_t workspace_bytes, cudaStream_t st, const long long* cursor, size_t parity_stride, size_t ldx);
+int tc64_fit_step(const int* dims, int loss, const dlas_opt_cfg* cfg, float* params, float* m, float* v, const float* X,
+                  const float* y, size_t n_rows, uint64_t iteration, float* loss_out, void* workspace, size_t workspace_bytes,
+                  cudaStream_t st, size_t ldx);
+int tc64_predict(const int* dims, const float* params, const float* X, size_t n_rows, float* yhat, cudaStream_t st, size_t ldx);
+int tc64_eval_loss(const int* dims, int loss, const float* params, const float* X, const float* y, size_t n_rows, float* loss_sum,
+                   void* workspace, size_t workspace_bytes, cudaStream_t st, size_t ldx);
+inline bool tc_any(const int* dims, int n_layers) { return tc_supported(dims, n_layers) || tc64_supported(dims, n_layers); }
 size_t tc_dp_recv_words(int world);
 int tc_dp_step(const int* dims, int n_layers, int loss, const dlas_opt_cfg* cfg, float* params, float* m, float* v,
                const float* X_base, const float* y_base, size_t batch_rows, dlas_step_state* state,
@@ -42,7 +55,7 @@ int check_common(const char* fn, const int* dims, int n_layers, int loss, int mo
   DLAS_REQUIRE(n_layers >= 1 && n_layers <= 8, "%s: n_layers %d not in 1..8", fn, n_layers);
   DLAS_REQUIRE(loss == DLAS_LOSS_MSE || loss == DLAS_LOSS_MAE_CLIP, "%s: unknown loss %d", fn, loss);
   DLAS_REQUIRE(mode == DLAS_MODE_FP32 || mode == DLAS_MODE_TC, "%s: unknown mode %d", fn, mode);
-  if (mode == DLAS_MODE_TC && !tc_supported(dims, n_layers)) {
+  if (mode == DLAS_MODE_TC && !tc_any(dims, n_layers)) {
     set_error("%s: DLAS_MODE_TC does not support these layer widths (see dlas_mlp_mode_supported)", fn);
     return DLAS_ERR_UNSUPPORTED_SHAPE;
   }
@@ -63,12 +76,16 @@ extern "C" size_t dlas_mlp_n_params(const int* dims, int n_layers) {
 extern "C" int dlas_mlp_mode_supported(const int* dims, int n_layers, int mode) {
   if (!dims || n_layers < 1 || n_layers > 8) return 0;
   if (mode == DLAS_MODE_FP32) return simt_workspace_bytes(dims, n_layers) > 0 ? 1 : 0;
-  if (mode == DLAS_MODE_TC) return tc_supported(dims, n_layers) ? 1 : 0;
+  if (mode == DLAS_MODE_TC) return tc_any(dims, n_layers) ? 1 : 0;
   return 0;
 }
 
 extern "C" size_t dlas_mlp_workspace_bytes(const int* dims, int n_layers, int mode) {
   if (!dims || n_layers < 1 || n_layers > 8) return 0;
+  if (mode == DLAS_MODE_TC && tc64_supported(dims, n_layers)) {   // eval / predict in fp32 mode may share the workspace
+    size_t a = tc64_workspace_bytes(dims), b = simt_workspace_bytes(dims, n_layers);
+    return a > b ? a : b;
+  }
   if (mode == DLAS_MODE_TC) return tc_supported(dims, n_layers) ? tc_workspace_bytes(dims, n_layers) : 0;
   return simt_workspace_bytes(dims, n_layers);
 }
@@ -91,6 +108,8 @@ extern "C" int dlas_mlp_grad_strided(const int* dims, int n_layers, int loss, in
   DLAS_REQUIRE(params && grad_sum && (n_rows == 0 || (X && y)), "dlas_mlp_grad: null pointer");
   rc = check_stride("dlas_mlp_grad_strided", dims, x_row_stride);
   if (rc != DLAS_OK) return rc;
+  if (mode == DLAS_MODE_TC && tc64_supported(dims, n_layers))
+    return tc64_grad(dims, loss, params, X, y, n_rows, grad_sum, workspace, workspace_bytes, (cudaStream_t)stream, nullptr, 0, x_row_stride);
   if (mode == DLAS_MODE_TC)
     return tc_grad(dims, n_layers, loss, params, X, y, n_rows, grad_sum, workspace, workspace_bytes,
                    (cudaStream_t)stream, nullptr, 0, x_row_stride);
@@ -116,6 +135,9 @@ extern "C" int dlas_mlp_grad_at(const int* dims, int n_layers, int loss, int mod
   DLAS_REQUIRE(params && grad_sum && X_base && y_base && state_dev, "dlas_mlp_grad_at: null pointer");
   DLAS_REQUIRE(batch_rows >= 1, "dlas_mlp_grad_at: batch_rows is 0");
   const long long* cursor = reinterpret_cast<const long long*>(&state_dev->cursor);
+  if (mode == DLAS_MODE_TC && tc64_supported(dims, n_layers))
+    return tc64_grad(dims, loss, params, X_base, y_base, batch_rows, grad_sum, workspace, workspace_bytes, (cudaStream_t)stream, cursor,
+                     parity_stride, 0);
   if (mode == DLAS_MODE_TC)
     return tc_grad(dims, n_layers, loss, params, X_base, y_base, batch_rows, grad_sum, workspace, workspace_bytes,
                    (cudaStream_t)stream, cursor, parity_stride);
@@ -161,6 +183,12 @@ extern "C" int dlas_mlp_fit_steps_strided(const int* dims, int n_layers, int los
                  (long long)b, n_batches);
     const float* Xb = X + (size_t)b * batch * d0;
     const float* yb = y + (size_t)b * batch * dL;
+    if (mode == DLAS_MODE_TC && tc64_supported(dims, n_layers)) {
+      rc = tc64_fit_step(dims, loss, cfg, params, m, v, Xb, yb, batch, iteration0 + (uint64_t)s, step_losses ? step_losses + s : nullptr,
+                         workspace, workspace_bytes, st, x_row_stride);
+      if (rc != DLAS_OK) return rc;
+      continue;
+    }
     if (mode == DLAS_MODE_TC) {   // gradient kernel + (reduction fused with the update): two launches per step
       rc = tc_fit_step(dims, n_layers, loss, cfg, params, m, v, Xb, yb, batch, iteration0 + (uint64_t)s,
                        step_losses ? step_losses + s : nullptr, workspace, workspace_bytes, st, /*chained=*/s > 0, x_row_stride,
@@ -193,6 +221,7 @@ extern "C" int dlas_mlp_predict_strided(const int* dims, int n_layers, int mode,
   rc = check_stride("dlas_mlp_predict_strided", dims, x_row_stride);
   if (rc != DLAS_OK) return rc;
   if (mode == DLAS_MODE_TC) {   // forward-only kind of the tcgen05 kernel
+    if (tc64_supported(dims, n_layers)) return tc64_predict(dims, params, X, n_rows, yhat, (cudaStream_t)stream, x_row_stride);
     if (!tc_supported(dims, n_layers)) { set_error("dlas_mlp_predict: DLAS_MODE_TC does not support these layer widths"); return DLAS_ERR_UNSUPPORTED_SHAPE; }
     return tc_predict(dims, n_layers, params, X, n_rows, yhat, (cudaStream_t)stream, x_row_stride);
   }
@@ -218,6 +247,8 @@ extern "C" int dlas_mlp_eval_loss_strided(const int* dims, int n_layers, int los
   rc = check_stride("dlas_mlp_eval_loss_strided", dims, x_row_stride);
   if (rc != DLAS_OK) return rc;
   if (mode == DLAS_MODE_TC) {
+    if (tc64_supported(dims, n_layers))
+      return tc64_eval_loss(dims, loss, params, X, y, n_rows, loss_sum, workspace, workspace_bytes, (cudaStream_t)stream, x_row_stride);
     if (!tc_supported(dims, n_layers)) { set_error("dlas_mlp_eval_loss: DLAS_MODE_TC does not support these layer widths"); return DLAS_ERR_UNSUPPORTED_SHAPE; }
     return tc_eval_loss(dims, n_layers, loss, params, X, y, n_rows, loss_sum, workspace, workspace_bytes, (cudaStream_t)stream, x_row_stride);
   }
@@ -257,5 +288,6 @@ extern "C" int dlas_mlp_status(const int* dims, int n_layers, int mode, const vo
     DLAS_CUDA(cudaStreamSynchronize((cudaStream_t)stream));
     return DLAS_OK;
   }
+  if (tc64_supported(dims, n_layers)) return tc64_status(dims, workspace, workspace_bytes, (cudaStream_t)stream);
   return tc_status(workspace, workspace_bytes, (cudaStream_t)stream);
 }

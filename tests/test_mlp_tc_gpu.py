@@ -27,7 +27,7 @@ def dl():
     import dlas
     from dlas import ops
     assert ops.mlp_mode_supported(DIMS, dlas.MODE_TC)
-    assert not ops.mlp_mode_supported([8, 64, 64, 1], dlas.MODE_TC)
+    assert ops.mlp_mode_supported([8, 64, 64, 1], dlas.MODE_TC) and not ops.mlp_mode_supported([16, 64, 64, 1], dlas.MODE_TC)
     return dlas
 
 

@@ -15,47 +15,26 @@
 // Flat layout: per layer K[(d_l+H)][4H] (input rows then recurrent rows), b[4H]; head w[H], b[1].
 #include "common.cuh"
 #include "simt_tiles.cuh"
+#include "lstm_common.cuh"
 
 namespace dlas {
+// lstm_tc.cu: tcgen05 stages, interchangeable with the fp32 kernels below (same stash and parameter layout)
+bool lstm_tc_supported(const lstm::LstmDesc& d);
+size_t lstm_tc_dw_partial_floats(const lstm::LstmDesc& d);
+int lstm_tc_dw(const lstm::LstmDesc& d, const float* X, const float* stash, size_t n_seq, float* grad_sum, float* tc_partials,
+               unsigned* err_flag, cudaStream_t st);
+
 namespace {
+using namespace lstm;
+// stages of DLAS_MODE_TC (bits of the internal mode word; DLAS_MODE_TC = every stage the shape supports; the tests pass
+// 0x100 | bits to exchange single stages)
+enum { TC_FWD = 1, TC_BWD = 2, TC_DW = 4 };
 
 constexpr int BT = 8;      // sequences per recurrence tile
 constexpr int BS = 12;     // padded row stride of the transposed recurrence tiles
 constexpr int NT = 512;
 constexpr int DR = 32;     // (seq,t) rows per weight-gradient tile
 constexpr int DRS = 36;
-constexpr int MAXL = 4;
-
-struct LstmDesc {
-  int d_in, H, L, T;
-  int k_off[MAXL], b_off[MAXL], d_l[MAXL];
-  int hw_off, hb_off, n_params;
-};
-
-int make_desc(int d_in, int H, int L, int T, LstmDesc& d) {
-  DLAS_REQUIRE(L >= 1 && L <= MAXL, "lstm: n_layers %d not in 1..%d", L, MAXL);
-  DLAS_REQUIRE(H >= 1 && H <= 128 && d_in >= 1 && d_in <= 128, "lstm: hidden %d / d_in %d not in 1..128", H, d_in);
-  DLAS_REQUIRE(T >= 1, "lstm: T %d < 1", T);
-  d.d_in = d_in; d.H = H; d.L = L; d.T = T;
-  int o = 0, dl = d_in;
-  for (int l = 0; l < L; ++l) {
-    d.k_off[l] = o; o += (dl + H) * 4 * H;
-    d.b_off[l] = o; o += 4 * H;
-    d.d_l[l] = dl;
-    dl = H;
-  }
-  d.hw_off = o; o += H;
-  d.hb_off = o; o += 1;
-  d.n_params = o;
-  return DLAS_OK;
-}
-
-__host__ __device__ inline size_t pstride(int n_params) { return ((size_t)n_params + 1 + 3) & ~(size_t)3; }
-// stash[seq][l][t][comp][H], comp: 0 i, 1 f, 2 g, 3 o, 4 c, 5 h (0..3 become dz after the backward pass)
-__device__ __forceinline__ size_t stash_idx(const LstmDesc& d, size_t seq, int l, int t, int comp) {
-  return ((((seq * d.L + l) * d.T + t) * 6) + comp) * (size_t)d.H;
-}
-
 __device__ __forceinline__ float sigmoidf_(float x) { return 1.0f / (1.0f + expf(-x)); }
 
 // smem: xh[(dmax+H)][BS] | z[4H][BS] | c[H][BS] | aux[H][BS]
@@ -294,7 +273,7 @@ lstm_reduce_kernel(const float* __restrict__ partials, size_t stride, int n_acti
   out[i0 + i] = s;
 }
 
-struct Ws { float *stash, *dseq, *KT, *partials, *yhat; size_t bytes; };
+struct Ws { float *stash, *dseq, *KT, *partials, *yhat, *tcp; unsigned* status; size_t bytes; };
 Ws carve_ws(const LstmDesc& d, size_t n_seq, void* base) {
   Ws w;
   size_t o = 0;
@@ -304,6 +283,8 @@ Ws carve_ws(const LstmDesc& d, size_t n_seq, void* base) {
   w.KT = take(d.n_params);
   w.partials = take((size_t)sm_count() * pstride(d.n_params));
   w.yhat = take(n_seq);
+  w.tcp = take(lstm_tc_supported(d) ? lstm_tc_dw_partial_floats(d) : 0);      // tensor-core weight-gradient partials
+  w.status = reinterpret_cast<unsigned*>(take(64));                              // status words of the tensor-core kernels
   w.bytes = o * sizeof(float);
   return w;
 }
@@ -357,12 +338,45 @@ extern "C" int dlas_lstm_predict(int d_in, int hidden, int n_layers, int T, cons
   return DLAS_OK;
 }
 
+namespace dlas {
+namespace {
+// mode word -> stage bits
+int stage_bits(int mode, const LstmDesc& d, const char* fn, int* bits) {
+  *bits = 0;
+  if (mode == DLAS_MODE_FP32) return DLAS_OK;
+  if (mode != DLAS_MODE_TC && (mode & ~0x7) != 0x100) { set_error("%s: unknown mode %d", fn, mode); return DLAS_ERR_INVALID; }
+  if (!lstm_tc_supported(d)) {
+    set_error("%s: DLAS_MODE_TC needs hidden = 128 and d_in <= 16 (got hidden %d, d_in %d)", fn, d.H, d.d_in);
+    return DLAS_ERR_UNSUPPORTED_SHAPE;
+  }
+  *bits = (mode == DLAS_MODE_TC) ? (TC_DW) : (mode & 0x7);
+  return DLAS_OK;
+}
+}  // namespace
+}  // namespace dlas
+
+extern "C" int dlas_lstm_mode_supported(int d_in, int hidden, int n_layers, int mode) {
+  LstmDesc d;
+  if (make_desc(d_in, hidden, n_layers, 1, d) != DLAS_OK) return 0;
+  return mode == DLAS_MODE_FP32 || (mode == DLAS_MODE_TC && lstm_tc_supported(d)) ? 1 : 0;
+}
+
 extern "C" int dlas_lstm_grad(int d_in, int hidden, int n_layers, int T, int loss, const float* params,
                               const float* X, const float* y, size_t n_seq, float* grad_sum, void* workspace,
                               size_t workspace_bytes, void* stream) {
+  return dlas_lstm_grad_mode(DLAS_MODE_FP32, d_in, hidden, n_layers, T, loss, params, X, y, n_seq, grad_sum, workspace,
+                             workspace_bytes, stream);
+}
+
+extern "C" int dlas_lstm_grad_mode(int mode, int d_in, int hidden, int n_layers, int T, int loss, const float* params,
+                                   const float* X, const float* y, size_t n_seq, float* grad_sum, void* workspace,
+                                   size_t workspace_bytes, void* stream) {
   DLAS_CHECK_DEVICE();
   LstmDesc d;
   int rc = make_desc(d_in, hidden, n_layers, T, d);
+  if (rc != DLAS_OK) return rc;
+  int bits = 0;
+  rc = stage_bits(mode, d, "dlas_lstm_grad_mode", &bits);
   if (rc != DLAS_OK) return rc;
   DLAS_REQUIRE(loss == DLAS_LOSS_MSE || loss == DLAS_LOSS_MAE_CLIP, "dlas_lstm_grad: unknown loss %d", loss);
   DLAS_REQUIRE(params && grad_sum && (n_seq == 0 || (X && y)), "dlas_lstm_grad: null pointer");
@@ -392,15 +406,20 @@ extern "C" int dlas_lstm_grad(int d_in, int hidden, int n_layers, int T, int los
   DLAS_LAUNCH_CHECK();
   lstm_bwd_kernel<<<grid, NT, smem, st>>>(d, loss, params, w.KT, y, w.yhat, n_seq, w.stash, w.dseq, w.partials);
   DLAS_LAUNCH_CHECK();
-  lstm_dw_kernel<<<grid, NT, smem_dw, st>>>(d, X, w.stash, n_seq, w.partials);
-  DLAS_LAUNCH_CHECK();
-  // layer parameters: CTAs that owned at least one (seq,t) tile; head + loss: every CTA wrote its slot
-  size_t n_tiles = (n_seq * (size_t)T + DR - 1) / DR;
-  int n_active = (int)(n_tiles < (size_t)grid ? n_tiles : (size_t)grid);
   size_t n_layer_params = (size_t)d.hw_off;
-  lstm_reduce_kernel<<<(unsigned)((n_layer_params + 255) / 256), 256, 0, st>>>(w.partials, pstride(d.n_params), n_active,
-                                                                             0, n_layer_params, grad_sum);
-  DLAS_LAUNCH_CHECK();
+  if (bits & TC_DW) {   // weight gradient as a tcgen05 GEMM over all (sequence, t) rows
+    rc = lstm_tc_dw(d, X, w.stash, n_seq, grad_sum, w.tcp, w.status, st);
+    if (rc != DLAS_OK) return rc;
+  } else {
+    lstm_dw_kernel<<<grid, NT, smem_dw, st>>>(d, X, w.stash, n_seq, w.partials);
+    DLAS_LAUNCH_CHECK();
+    // layer parameters: CTAs that owned at least one (seq,t) tile; head + loss: every CTA wrote its slot
+    size_t n_tiles = (n_seq * (size_t)T + DR - 1) / DR;
+    int n_active = (int)(n_tiles < (size_t)grid ? n_tiles : (size_t)grid);
+    lstm_reduce_kernel<<<(unsigned)((n_layer_params + 255) / 256), 256, 0, st>>>(w.partials, pstride(d.n_params), n_active,
+                                                                               0, n_layer_params, grad_sum);
+    DLAS_LAUNCH_CHECK();
+  }
   size_t n_head = (size_t)d.H + 2;  // w[H], b, loss
   lstm_reduce_kernel<<<(unsigned)((n_head + 255) / 256), 256, 0, st>>>(w.partials, pstride(d.n_params), grid,
                                                                      n_layer_params, n_head, grad_sum);

@@ -1,0 +1,43 @@
+// Shared by lstm.cu (fp32 CUDA-core kernels) and lstm_tc.cu (tcgen05 kernels): parameter layout and BPTT stash indexing of
+// the LSTM regressor (Readme.md:21; BASELINE.json configs[4]).
+#pragma once
+#include "common.cuh"
+
+namespace dlas {
+namespace lstm {
+
+constexpr int MAXL = 4;
+
+struct LstmDesc {
+  int d_in, H, L, T;
+  int k_off[MAXL], b_off[MAXL], d_l[MAXL];
+  int hw_off, hb_off, n_params;
+};
+
+inline int make_desc(int d_in, int H, int L, int T, LstmDesc& d) {
+  DLAS_REQUIRE(L >= 1 && L <= MAXL, "lstm: n_layers %d not in 1..%d", L, MAXL);
+  DLAS_REQUIRE(H >= 1 && H <= 128 && d_in >= 1 && d_in <= 128, "lstm: hidden %d / d_in %d not in 1..128", H, d_in);
+  DLAS_REQUIRE(T >= 1, "lstm: T %d < 1", T);
+  d.d_in = d_in; d.H = H; d.L = L; d.T = T;
+  int o = 0, dl = d_in;
+  for (int l = 0; l < L; ++l) {
+    d.k_off[l] = o; o += (dl + H) * 4 * H;
+    d.b_off[l] = o; o += 4 * H;
+    d.d_l[l] = dl;
+    dl = H;
+  }
+  d.hw_off = o; o += H;
+  d.hb_off = o; o += 1;
+  d.n_params = o;
+  return DLAS_OK;
+}
+
+__host__ __device__ inline size_t pstride(int n_params) { return ((size_t)n_params + 1 + 3) & ~(size_t)3; }
+// stash[seq][l][t][comp][H], comp: 0 i, 1 f, 2 g, 3 o, 4 c, 5 h (0..3 become dz after the backward pass)
+__device__ __forceinline__ size_t stash_idx(const LstmDesc& d, size_t seq, int l, int t, int comp) {
+  return ((((seq * d.L + l) * d.T + t) * 6) + comp) * (size_t)d.H;
+}
+
+
+}  // namespace lstm
+}  // namespace dlas

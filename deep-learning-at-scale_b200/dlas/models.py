@@ -181,7 +181,8 @@ class Sequential:
         if rec[0].input_shape is None or len({l.units for l in rec}) != 1:
             raise NotImplementedError("first LSTM needs input_shape=(T, d_in); all LSTM layers share one width")
         T, d_in = rec[0].input_shape
-        return self._delegate(LSTMRegressor(d_in, rec[0].units, len(rec), T, seed=self.seed, device=self.device), loss, optimizer)
+        return self._delegate(LSTMRegressor(d_in, rec[0].units, len(rec), T, seed=self.seed, device=self.device, mode=self.mode),
+                              loss, optimizer)
 
     def _delegate(self, impl, loss, optimizer):
         self._impl = impl

@@ -205,9 +205,13 @@ def lstm_workspace(d_in, hidden, n_layers, T, n_seq, device="cuda"):
     return torch.empty(nbytes, dtype=torch.uint8, device=device)
 
 
-def lstm_grad(d_in, hidden, n_layers, T, loss, params, X, y, grad_sum, workspace):
-    check(_lib.load().dlas_lstm_grad(d_in, hidden, n_layers, T, int(loss), ptr(params), ptr(X), ptr(y), X.shape[0],
-                                     ptr(grad_sum), ptr(workspace), workspace.numel(), stream_ptr()))
+def lstm_mode_supported(d_in, hidden, n_layers, mode):
+    return bool(_lib.load().dlas_lstm_mode_supported(int(d_in), int(hidden), int(n_layers), int(mode)))
+
+
+def lstm_grad(d_in, hidden, n_layers, T, loss, params, X, y, grad_sum, workspace, mode=_lib.MODE_FP32):
+    check(_lib.load().dlas_lstm_grad_mode(int(mode), d_in, hidden, n_layers, T, int(loss), ptr(params), ptr(X), ptr(y), X.shape[0],
+                                          ptr(grad_sum), ptr(workspace), workspace.numel(), stream_ptr()))
     return grad_sum
 
 

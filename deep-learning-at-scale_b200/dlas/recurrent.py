@@ -28,9 +28,10 @@ class LSTM:
 
 
 class LSTMRegressor(FlatModel):
-    def __init__(self, d_in, hidden, n_layers, T, seed=ops.BASE_SEED, device=None):
+    def __init__(self, d_in, hidden, n_layers, T, seed=ops.BASE_SEED, device=None, mode=_lib.MODE_FP32):
         super().__init__(seed, device)
         self.d_in, self.hidden, self.n_layers, self.T = int(d_in), int(hidden), int(n_layers), int(T)
+        self.mode = int(mode)     # MODE_TC: the stages with a tcgen05 kernel run on the tensor cores (include/dlas_b200.h)
 
     def _init_params(self):
         H, p, o, d = self.hidden, [], 0, self.d_in
@@ -51,6 +52,8 @@ class LSTMRegressor(FlatModel):
         n = ops.lstm_n_params(self.d_in, self.hidden, self.n_layers)
         if n == 0:
             raise _lib.DlasError(-5, "LSTM shape not supported")
+        if not ops.lstm_mode_supported(self.d_in, self.hidden, self.n_layers, self.mode):
+            raise _lib.DlasError(-5, "LSTM d_in=%d hidden=%d is not supported in mode %d" % (self.d_in, self.hidden, self.mode))
         return n
 
     def _make_workspace(self, n_seq):
@@ -60,7 +63,7 @@ class LSTMRegressor(FlatModel):
         return X.reshape(-1, self.T, self.d_in)
 
     def _grad(self, X, y, grad_sum, ws, train, global_rows):
-        return ops.lstm_grad(self.d_in, self.hidden, self.n_layers, self.T, self.loss, self.params, X, y, grad_sum, ws)
+        return ops.lstm_grad(self.d_in, self.hidden, self.n_layers, self.T, self.loss, self.params, X, y, grad_sum, ws, mode=self.mode)
 
     def _forward(self, X, ws):
         return ops.lstm_predict(self.d_in, self.hidden, self.n_layers, self.T, self.params, X, ws)

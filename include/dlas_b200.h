@@ -274,6 +274,14 @@ size_t dlas_lstm_workspace_bytes(int d_in, int hidden, int n_layers, int T, size
 int dlas_lstm_grad(int d_in, int hidden, int n_layers, int T, int loss, const float* params,
                    const float* X, const float* y, size_t n_seq, float* grad_sum, void* workspace,
                    size_t workspace_bytes, void* stream);
+/* The same step with an arithmetic mode (dlas_lstm_grad is mode DLAS_MODE_FP32).  DLAS_MODE_TC (hidden = 128, d_in <= 16;
+ * dlas_lstm_mode_supported) runs the stages that have a tcgen05 kernel on the tensor cores -- fp16 operands, fp32
+ * accumulation in TMEM, fp32 cell state -- and the others in fp32; stash and parameter layout are the same, the
+ * workspace size does not depend on the mode.  Stated tolerance of the mode: tests/test_lstm_gpu.py. */
+int dlas_lstm_mode_supported(int d_in, int hidden, int n_layers, int mode);
+int dlas_lstm_grad_mode(int mode, int d_in, int hidden, int n_layers, int T, int loss, const float* params,
+                        const float* X, const float* y, size_t n_seq, float* grad_sum, void* workspace,
+                        size_t workspace_bytes, void* stream);
 /* forward only: yhat (n_seq) -- model.predict / test_on_batch, cnn.py:132 */
 int dlas_lstm_predict(int d_in, int hidden, int n_layers, int T, const float* params,
                       const float* X, size_t n_seq, float* yhat, void* workspace,

@@ -1,0 +1,91 @@
+"""GPU parity of the tensor-core stages of the LSTM path (DLAS_MODE_TC: hidden 128, d_in <= 16; fp16 operands, fp32
+accumulation, fp32 cell state).  Every stage can be exchanged for its fp32 counterpart (mode 0x100 | stage bits: 1 forward
+recurrence, 2 backward recurrence, 4 weight gradient), so each is first compared with the fp32 kernels on the same stash,
+then the whole mode with the fp64 oracle.  Stated tolerances: a stage against fp32 2e-3 on gradient blocks (operand
+rounding 2^-11, averaged over the rows of the batch), the mode against the oracle 5e-3 on gradients and 1e-3 on the loss."""
+import numpy as np
+import pytest
+import torch
+
+import dlas_oracle as O
+
+pytestmark = pytest.mark.gpu
+TC_FWD, TC_BWD, TC_DW = 1, 2, 4
+
+
+@pytest.fixture(scope="module")
+def dl():
+    import __graft_entry__ as G
+    G.build()
+    import dlas
+    return dlas
+
+
+def _cuda(a):
+    return torch.from_numpy(np.ascontiguousarray(a, dtype=np.float32)).cuda()
+
+
+def _relerr(a, b):
+    return float(np.linalg.norm(np.asarray(a, np.float64) - b) / max(np.linalg.norm(b), 1e-300))
+
+
+def _setup(d, h, nl, T, B, seed):
+    rng = np.random.default_rng(seed)
+    p = O.lstm_init(d, h, nl, 100 + seed)
+    p = p + 0.02 * rng.standard_normal(p.size).astype(np.float32)      # non-zero biases
+    X = rng.standard_normal((B, T, d)).astype(np.float32)
+    y = rng.standard_normal((B, 1)).astype(np.float32)
+    return p, X, y
+
+
+def _grad(mode, d, h, nl, T, loss, p, X, y):
+    from dlas import ops
+    ws = ops.lstm_workspace(d, h, nl, T, X.shape[0])
+    gs = torch.zeros(ops.lstm_n_params(d, h, nl) + 1, device="cuda")
+    ops.lstm_grad(d, h, nl, T, loss, _cuda(p), _cuda(X), _cuda(y), gs, ws, mode=mode)
+    torch.cuda.synchronize()
+    g = gs.cpu().numpy()
+    assert np.isfinite(g).all()
+    return g
+
+
+def _blocks(d, h, nl, g, ref):
+    offs, head, n = O.lstm_offsets(d, h, nl)
+    out = {}
+    for li, (k, b, dl_) in enumerate(offs):
+        nk = (dl_ + h) * 4 * h
+        out["K%d" % li] = _relerr(g[k:k + nk], ref[k:k + nk])
+        out["b%d" % li] = _relerr(g[b:b + 4 * h], ref[b:b + 4 * h])
+    return out
+
+
+@pytest.mark.parametrize("shape", [(8, 128, 2, 48, 300), (8, 128, 2, 48, 37), (5, 128, 1, 3, 1), (16, 128, 3, 6, 700)])
+def test_weight_gradient_stage_vs_fp32(dl, shape):
+    """dK, db from the tcgen05 GEMM over all (sequence, t) rows vs the fp32 kernel on the same stash: the other entries
+    (head, loss) come from the same fp32 kernels and must be bit-identical."""
+    from dlas import ops
+    d, h, nl, T, B = shape
+    assert ops.lstm_mode_supported(d, h, nl, dl.MODE_TC) and not ops.lstm_mode_supported(d, 64, nl, dl.MODE_TC)
+    p, X, y = _setup(d, h, nl, T, B, B)
+    ref = _grad(dl.MODE_FP32, d, h, nl, T, 0, p, X, y)
+    got = _grad(0x100 | TC_DW, d, h, nl, T, 0, p, X, y)
+    errs = _blocks(d, h, nl, got[:-1], ref[:-1].astype(np.float64))
+    print(shape, errs)
+    _, (hw, hb), n = O.lstm_offsets(d, h, nl)
+    assert np.array_equal(got[hw:], ref[hw:])          # head weights, head bias, loss sum
+    tol = 2e-3 if B * T >= 1000 else 1e-2
+    assert max(errs.values()) < tol
+    again = _grad(0x100 | TC_DW, d, h, nl, T, 0, p, X, y)
+    assert np.array_equal(got, again)                  # deterministic
+
+
+def test_mode_tc_vs_oracle(dl):
+    d, h, nl, T, B = 8, 128, 2, 24, 256
+    p, X, y = _setup(d, h, nl, T, B, 7)
+    for loss in (O.LOSS_MSE, O.LOSS_MAE_CLIP):
+        yy = y * (8.0 if loss == O.LOSS_MAE_CLIP else 1.0)
+        got = _grad(dl.MODE_TC, d, h, nl, T, loss, p, X, yy)
+        lr, gref = O.lstm_loss_grad_sums(p.astype(np.float64), d, h, nl, X.astype(np.float64), yy.astype(np.float64), loss)
+        print("loss", loss, abs(got[-1] / lr - 1), _relerr(got[:-1], gref))
+        assert got[-1] == pytest.approx(lr, rel=1e-3)
+        assert _relerr(got[:-1], gref) < 5e-3 + (2.0 / B if loss else 0.0)

@@ -21,6 +21,8 @@ namespace dlas {
 // lstm_tc.cu: tcgen05 stages, interchangeable with the fp32 kernels below (same stash and parameter layout)
 bool lstm_tc_supported(const lstm::LstmDesc& d);
 size_t lstm_tc_dw_partial_floats(const lstm::LstmDesc& d);
+int lstm_tc_fwd(const lstm::LstmDesc& d, const float* params, const float* X, size_t n_seq, float* stash, float* yhat,
+                unsigned* err_flag, cudaStream_t st);
 int lstm_tc_dw(const lstm::LstmDesc& d, const float* X, const float* stash, size_t n_seq, float* grad_sum, float* tc_partials,
                unsigned* err_flag, cudaStream_t st);
 
@@ -304,6 +306,23 @@ int set_smem(Kern k, size_t bytes) {
 
 using namespace dlas;
 
+namespace dlas {
+namespace {
+// mode word -> stage bits
+int stage_bits(int mode, const LstmDesc& d, const char* fn, int* bits) {
+  *bits = 0;
+  if (mode == DLAS_MODE_FP32) return DLAS_OK;
+  if (mode != DLAS_MODE_TC && (mode & ~0x7) != 0x100) { set_error("%s: unknown mode %d", fn, mode); return DLAS_ERR_INVALID; }
+  if (!lstm_tc_supported(d)) {
+    set_error("%s: DLAS_MODE_TC needs hidden = 128 and d_in <= 16 (got hidden %d, d_in %d)", fn, d.H, d.d_in);
+    return DLAS_ERR_UNSUPPORTED_SHAPE;
+  }
+  *bits = (mode == DLAS_MODE_TC) ? (TC_FWD | TC_DW) : (mode & 0x7);
+  return DLAS_OK;
+}
+}  // namespace
+}  // namespace dlas
+
 extern "C" size_t dlas_lstm_n_params(int d_in, int hidden, int n_layers) {
   LstmDesc d;
   if (make_desc(d_in, hidden, n_layers, 1, d) != DLAS_OK) return 0;
@@ -318,9 +337,17 @@ extern "C" size_t dlas_lstm_workspace_bytes(int d_in, int hidden, int n_layers, 
 
 extern "C" int dlas_lstm_predict(int d_in, int hidden, int n_layers, int T, const float* params, const float* X,
                                  size_t n_seq, float* yhat, void* workspace, size_t workspace_bytes, void* stream) {
+  return dlas_lstm_predict_mode(DLAS_MODE_FP32, d_in, hidden, n_layers, T, params, X, n_seq, yhat, workspace, workspace_bytes, stream);
+}
+
+extern "C" int dlas_lstm_predict_mode(int mode, int d_in, int hidden, int n_layers, int T, const float* params, const float* X,
+                                      size_t n_seq, float* yhat, void* workspace, size_t workspace_bytes, void* stream) {
   DLAS_CHECK_DEVICE();
   LstmDesc d;
   int rc = make_desc(d_in, hidden, n_layers, T, d);
+  if (rc != DLAS_OK) return rc;
+  int bits = 0;
+  rc = stage_bits(mode, d, "dlas_lstm_predict_mode", &bits);
   if (rc != DLAS_OK) return rc;
   if (n_seq == 0) return DLAS_OK;
   DLAS_REQUIRE(params && X && yhat, "dlas_lstm_predict: null pointer");
@@ -333,27 +360,11 @@ extern "C" int dlas_lstm_predict(int d_in, int hidden, int n_layers, int T, cons
   size_t smem = rec_smem_bytes(d);
   rc = set_smem(lstm_fwd_kernel, smem);
   if (rc != DLAS_OK) return rc;
+  if (bits & TC_FWD) return lstm_tc_fwd(d, params, X, n_seq, w.stash, yhat, w.status, st);
   lstm_fwd_kernel<<<sm_count(), NT, smem, st>>>(d, params, X, n_seq, w.stash, yhat);
   DLAS_LAUNCH_CHECK();
   return DLAS_OK;
 }
-
-namespace dlas {
-namespace {
-// mode word -> stage bits
-int stage_bits(int mode, const LstmDesc& d, const char* fn, int* bits) {
-  *bits = 0;
-  if (mode == DLAS_MODE_FP32) return DLAS_OK;
-  if (mode != DLAS_MODE_TC && (mode & ~0x7) != 0x100) { set_error("%s: unknown mode %d", fn, mode); return DLAS_ERR_INVALID; }
-  if (!lstm_tc_supported(d)) {
-    set_error("%s: DLAS_MODE_TC needs hidden = 128 and d_in <= 16 (got hidden %d, d_in %d)", fn, d.H, d.d_in);
-    return DLAS_ERR_UNSUPPORTED_SHAPE;
-  }
-  *bits = (mode == DLAS_MODE_TC) ? (TC_DW) : (mode & 0x7);
-  return DLAS_OK;
-}
-}  // namespace
-}  // namespace dlas
 
 extern "C" int dlas_lstm_mode_supported(int d_in, int hidden, int n_layers, int mode) {
   LstmDesc d;
@@ -402,8 +413,13 @@ extern "C" int dlas_lstm_grad_mode(int mode, int d_in, int hidden, int n_layers,
   if (rc != DLAS_OK) return rc;
   transpose_kernel<<<64, 256, 0, st>>>(d, params, w.KT);
   DLAS_LAUNCH_CHECK();
-  lstm_fwd_kernel<<<grid, NT, smem, st>>>(d, params, X, n_seq, w.stash, w.yhat);
-  DLAS_LAUNCH_CHECK();
+  if (bits & TC_FWD) {   // persistent recurrence on the tensor cores
+    rc = lstm_tc_fwd(d, params, X, n_seq, w.stash, w.yhat, w.status, st);
+    if (rc != DLAS_OK) return rc;
+  } else {
+    lstm_fwd_kernel<<<grid, NT, smem, st>>>(d, params, X, n_seq, w.stash, w.yhat);
+    DLAS_LAUNCH_CHECK();
+  }
   lstm_bwd_kernel<<<grid, NT, smem, st>>>(d, loss, params, w.KT, y, w.yhat, n_seq, w.stash, w.dseq, w.partials);
   DLAS_LAUNCH_CHECK();
   size_t n_layer_params = (size_t)d.hw_off;

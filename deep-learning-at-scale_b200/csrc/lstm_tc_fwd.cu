@@ -1,0 +1,263 @@
+// LSTM forward recurrence on the tensor cores (DLAS_MODE_TC stage "forward"; Readme.md:21, BASELINE.json configs[4]).
+// A persistent kernel: a CTA PAIR walks a tile of 128 sequences through all T steps of every layer with the state on chip.
+//   * CTA `rank` of the pair owns hidden units [64 rank, 64 rank + 64): its 4 x 64 = 256 gate columns of K_l stay in shared
+//     memory as one fp16 tile (128 KB for a 256-row layer), the cell state c of its units stays in registers (fp32), and
+//     h_{t-1} of ALL 128 units sits in the A tile [128 sequences][x_t | h_{t-1}] (fp16) that tcgen05.mma reads.
+//   * per step: z = [x_t | h_{t-1}] K_l[:, own columns]  (M = 128 sequences, N = 256, K = 144 / 256; fp32 in TMEM), then the
+//     epilogue warps (thread = sequence row x 32 units) apply the gate non-linearities, update c, write i,f,g,o,c,h to the
+//     stash (fp32, the layout of lstm.cu, so the fp32 BPTT can consume it) and store h_t as fp16 into BOTH CTAs' A tiles
+//     (own half locally, the other through distributed shared memory) -- the only exchange of the recurrence.
+//   * hand-over by mbarriers only: B_A (own rows of the next step are in place), B_PH (the peer's half of h has arrived:
+//     remote arrive, cluster-scope release/acquire), B_Z (tcgen05.commit), B_PZ (the peer's MMA of this step has completed,
+//     so its A tile may be overwritten).
+#include "common.cuh"
+#include "lstm_common.cuh"
+#include "tc_common.cuh"
+
+namespace dlas {
+namespace {
+using namespace tc;
+using namespace lstm;
+
+constexpr int HT = 128, TS = 128, XW0 = 16, UH = 64;      // hidden width, sequences per tile, padded d_in, units per CTA
+__host__ __device__ inline int xw_of(int l) { return l == 0 ? XW0 : HT; }
+constexpr int N_EPI = 256, ISSUER_WARP = 8, NT = 288;
+constexpr uint32_t S_W = 0 /*[256 rows][256 gate cols] 128 KB*/, S_A = 131072 /*[128][256] 64 KB*/, S_F32 = 196608 /*bias[256]*/,
+                   S_BAR = S_F32 + 1024;
+enum { B_A = 0, B_PH, B_Z, B_PZ, N_BARS };
+constexpr uint32_t S_TMEM = S_BAR + N_BARS * 8, SMEM_BYTES = S_TMEM + 16, TM_COLS = 256;
+
+__device__ __forceinline__ float sigm(float x) { return __fdividef(1.0f, 1.0f + __expf(-x)); }
+__device__ __forceinline__ float tanh_(float x) { return 2.0f * sigm(2.0f * x) - 1.0f; }
+
+__global__ void __cluster_dims__(2, 1, 1) __launch_bounds__(NT, 1)
+lstm_fwd_tc_kernel(const LstmDesc d, const float* __restrict__ params, const float* __restrict__ X, const size_t n_seq,
+                   float* __restrict__ stash, unsigned* __restrict__ err_flag, const unsigned call_id) {
+  extern __shared__ __align__(1024) uint8_t smem[];
+  float* bias = reinterpret_cast<float*>(smem + S_F32);
+  uint64_t* bars = reinterpret_cast<uint64_t*>(smem + S_BAR);
+  uint32_t* tmem_slot = reinterpret_cast<uint32_t*>(smem + S_TMEM);
+  const uint32_t sbase = smem_u32(smem);
+  const uint32_t sW = sbase + S_W, sA = sbase + S_A;
+  const int tid = threadIdx.x, warp = tid >> 5, lane = tid & 31;
+  const uint32_t rank = cluster_ctarank();
+  const int pair = blockIdx.x >> 1, n_pairs = gridDim.x >> 1;
+  const int T = d.T;
+  const size_t n_tiles = (n_seq + TS - 1) / TS;
+  bool ok = (sbase & 1023u) == 0;
+  if (tid == 0) {
+    mbar_init(&bars[B_A], N_EPI / 32); mbar_init(&bars[B_PH], N_EPI / 32);
+    mbar_init(&bars[B_Z], 1); mbar_init(&bars[B_PZ], 1);
+    mbar_fence_init();
+  }
+  if (warp == ISSUER_WARP) tmem_alloc(tmem_slot, TM_COLS);
+  fence_before();
+  __syncthreads();
+  fence_after();
+  cluster_sync_all();       // the peer is running and its barriers are initialised: remote arrivals / stores may start
+  const uint32_t tm = *tmem_slot;
+  const uint32_t peerA = map_to_cta(sA, rank ^ 1u);
+  const uint32_t peer_PH = map_to_cta(smem_u32(&bars[B_PH]), rank ^ 1u), peer_PZ = map_to_cta(smem_u32(&bars[B_PZ]), rank ^ 1u);
+  uint32_t q = 0;           // round = (tile, layer, step): every barrier completes exactly one phase per round
+
+  // epilogue thread -> (row of the tile, 32 of this CTA's 64 units)
+  const int q4 = warp & 3, hh = (warp >> 2) & 1;
+  const int row = q4 * 32 + lane;
+  const uint32_t lane_base = (uint32_t)(q4 * 32) << 16;
+
+  for (size_t tile = pair; tile < n_tiles; tile += n_pairs) {
+    const size_t seq = tile * TS + row;
+    const bool valid = (warp < ISSUER_WARP) && seq < n_seq;
+    for (int l = 0; l < d.L; ++l) {
+      const int dl = d.d_l[l], xw = xw_of(l), nk = xw + HT;
+      // ---- this layer's weights -> fp16 tile: row n of [x | h] (n < xw: input row n, zero beyond d_l; else recurrent row),
+      // column g*64 + u = gate g of this CTA's unit u.  Everybody is past the previous layer here (barrier below).
+      {
+        const float* K = params + d.k_off[l];
+        for (int idx = tid; idx < nk * 32; idx += NT) {       // 32 chunks of 8 columns per row
+          const int n = idx >> 5, c = (idx & 31) * 8, g = c >> 6, u = c & 63;
+          const int k = (n < xw) ? (n < dl ? n : -1) : dl + (n - xw);
+          float4 a = make_float4(0.f, 0.f, 0.f, 0.f), e = a;
+          if (k >= 0) {
+            const float* src = K + (size_t)k * 4 * HT + g * HT + UH * rank + u;
+            a = __ldg(reinterpret_cast<const float4*>(src));
+            e = __ldg(reinterpret_cast<const float4*>(src + 4));
+          }
+          sts128(sW + tile_chunk_off(256, n, c), make_uint4(pack_half2(a.x, a.y), pack_half2(a.z, a.w), pack_half2(e.x, e.y), pack_half2(e.z, e.w)));
+        }
+        if (tid < 256) bias[tid] = __ldg(params + d.b_off[l] + (tid >> 6) * HT + UH * rank + (tid & 63));
+      }
+      // x part of step t for this thread's row(s): layer 0 -> 16 columns from X (threads of unit half 0), layers above ->
+      // 64 of the 128 columns of h_t of the layer below (stash, written earlier by this pair; read through L2)
+      auto x_store = [&](int t) {
+        if (l == 0) {
+          if (hh == 0) {
+            float xv[XW0];
+#pragma unroll
+            for (int k = 0; k < XW0; ++k) xv[k] = (valid && k < dl) ? __ldg(X + (seq * T + t) * (size_t)dl + k) : 0.f;
+            sts128(sA + tile_chunk_off(TS, row, 0), make_uint4(pack_half2(xv[0], xv[1]), pack_half2(xv[2], xv[3]), pack_half2(xv[4], xv[5]), pack_half2(xv[6], xv[7])));
+            sts128(sA + tile_chunk_off(TS, row, 8), make_uint4(pack_half2(xv[8], xv[9]), pack_half2(xv[10], xv[11]), pack_half2(xv[12], xv[13]), pack_half2(xv[14], xv[15])));
+          }
+        } else {
+          const float* src = stash + stash_idx(d, valid ? seq : 0, l - 1, t, 5) + hh * 64;
+#pragma unroll 4
+          for (int c8 = 0; c8 < 8; ++c8) {
+            float4 a = make_float4(0.f, 0.f, 0.f, 0.f), e = a;
+            if (valid) { a = __ldcg(reinterpret_cast<const float4*>(src + c8 * 8)); e = __ldcg(reinterpret_cast<const float4*>(src + c8 * 8 + 4)); }
+            sts128(sA + tile_chunk_off(TS, row, hh * 64 + c8 * 8), make_uint4(pack_half2(a.x, a.y), pack_half2(a.z, a.w), pack_half2(e.x, e.y), pack_half2(e.z, e.w)));
+          }
+        }
+      };
+      // ---- layer prologue: h_{-1} = 0 in the whole recurrent part of the A tile, x_0 in place -------------
+      float c_state[32];
+      if (warp < ISSUER_WARP) {
+#pragma unroll
+        for (int j = 0; j < 32; ++j) c_state[j] = 0.f;
+#pragma unroll
+        for (int c8 = 0; c8 < 8; ++c8) sts128(sA + tile_chunk_off(TS, row, xw + hh * 64 + c8 * 8), make_uint4(0u, 0u, 0u, 0u));
+        x_store(0);
+      }
+      fence_async_smem();
+      __syncthreads();          // weights, bias, A tile of step 0 complete in this CTA
+      if (warp < ISSUER_WARP) {
+        if (lane == 0) { mbar_arrive(&bars[B_A]); mbar_arrive_remote(peer_PH); }   // nothing to send for step 0: phases stay in step
+      }
+      if (warp == ISSUER_WARP) {
+        // =========================== MMA issuer ===========================
+        const bool leader = elect_one();
+        constexpr uint32_t ID_Z = make_idesc(128, 256, false, true);
+        const uint64_t dA = desc_kmajor(sA, TS, 0, 0), dW = desc_mnmajor(sW, 256, 0, 0);
+        for (int t = 0; t < T; ++t, ++q) {
+          ok = mbar_wait(&bars[B_A], q & 1) && ok;
+          ok = mbar_wait_cluster(&bars[B_PH], q & 1) && ok;        // the peer's half of h_{t-1} is in my A tile
+          fence_after();
+          if (leader) {
+            for (int i = 0; i < nk / 16; ++i)
+              mma_f16(tm, dA + koff_kmajor(TS, i), dW + koff_mnmajor(i), ID_Z, i > 0);
+            mma_commit(&bars[B_Z]);
+          }
+          __syncwarp();
+          ok = mbar_wait(&bars[B_Z], q & 1) && ok;                 // my MMA has read my A tile: tell the peer it may overwrite its half
+          if (lane == 0) mbar_arrive_remote(peer_PZ);
+          __syncwarp();
+        }
+      } else {
+        // =========================== epilogue warps ===========================
+        for (int t = 0; t < T; ++t, ++q) {
+          ok = mbar_wait(&bars[B_Z], q & 1) && ok;
+          fence_after();
+          // gates of this row's 32 units: columns g*64 + hh*32 + j of the accumulator
+          uint32_t v[32];
+          float ig[32], hout[32];
+          float* st_base = stash + stash_idx(d, valid ? seq : 0, l, t, 0) + UH * rank + hh * 32;
+          auto put = [&](int comp, const float (&a)[32]) {
+            if (valid) {
+#pragma unroll
+              for (int j4 = 0; j4 < 8; ++j4)
+                *reinterpret_cast<float4*>(st_base + (size_t)comp * HT + j4 * 4) = make_float4(a[j4 * 4], a[j4 * 4 + 1], a[j4 * 4 + 2], a[j4 * 4 + 3]);
+            }
+          };
+          const float* bb = bias + hh * 32;
+          tmem_ld32(tm + lane_base + 0 * 64 + hh * 32, v);           // i
+          tmem_ld_wait();
+#pragma unroll
+          for (int j = 0; j < 32; ++j) ig[j] = sigm(__uint_as_float(v[j]) + bb[j]);
+          put(0, ig);
+          tmem_ld32(tm + lane_base + 2 * 64 + hh * 32, v);           // g
+          tmem_ld_wait();
+#pragma unroll
+          for (int j = 0; j < 32; ++j) hout[j] = tanh_(__uint_as_float(v[j]) + bb[128 + j]);
+          put(2, hout);
+#pragma unroll
+          for (int j = 0; j < 32; ++j) ig[j] *= hout[j];
+          tmem_ld32(tm + lane_base + 1 * 64 + hh * 32, v);           // f
+          tmem_ld_wait();
+#pragma unroll
+          for (int j = 0; j < 32; ++j) hout[j] = sigm(__uint_as_float(v[j]) + bb[64 + j]);
+          put(1, hout);
+#pragma unroll
+          for (int j = 0; j < 32; ++j) c_state[j] = fmaf(hout[j], c_state[j], ig[j]);
+          put(4, c_state);
+          tmem_ld32(tm + lane_base + 3 * 64 + hh * 32, v);           // o
+          tmem_ld_wait();
+          fence_before();
+#pragma unroll
+          for (int j = 0; j < 32; ++j) ig[j] = sigm(__uint_as_float(v[j]) + bb[192 + j]);
+          put(3, ig);
+#pragma unroll
+          for (int j = 0; j < 32; ++j) hout[j] = ig[j] * tanh_(c_state[j]);
+          put(5, hout);
+          // the peer's MMA of this step has completed (waited every round so that no phase is ever skipped)
+          ok = mbar_wait_cluster(&bars[B_PZ], q & 1) && ok;
+          if (t + 1 < T) {
+            // h_t -> recurrent part of both A tiles (fp16), then the next step's input part
+#pragma unroll
+            for (int c8 = 0; c8 < 4; ++c8) {
+              const uint4 o = make_uint4(pack_half2(hout[c8 * 8], hout[c8 * 8 + 1]), pack_half2(hout[c8 * 8 + 2], hout[c8 * 8 + 3]),
+                                         pack_half2(hout[c8 * 8 + 4], hout[c8 * 8 + 5]), pack_half2(hout[c8 * 8 + 6], hout[c8 * 8 + 7]));
+              const uint32_t off = tile_chunk_off(TS, row, xw + UH * rank + hh * 32 + c8 * 8);
+              sts128(sA + off, o);
+              st_cluster_v4(peerA + off, o);
+            }
+            x_store(t + 1);
+            fence_async_all();
+            __syncwarp();
+            if (lane == 0) { mbar_arrive(&bars[B_A]); mbar_arrive_remote(peer_PH); }
+          }
+        }
+      }
+      // everybody of this CTA is past the layer's last round before the weights / A tile are rewritten
+      fence_before();
+      __syncthreads();
+      fence_after();
+    }
+  }
+  if (!ok && lane == 0 && err_flag != nullptr) atomicExch(err_flag, call_id);
+  // ---- teardown: no remote store or arrival may target a CTA that has exited ----
+  fence_before();
+  __syncthreads();
+  cluster_sync_all();
+  if (warp == ISSUER_WARP) tmem_dealloc(tm, TM_COLS);
+}
+
+// head: Dense(H -> 1) on the last hidden state of the top layer (fp32, one warp per sequence)
+__global__ void __launch_bounds__(256)
+lstm_head_kernel(const LstmDesc d, const float* __restrict__ params, const float* __restrict__ stash, const size_t n_seq,
+                 const unsigned* __restrict__ err_flag, const unsigned call_id, float* __restrict__ yhat) {
+  const size_t s = (size_t)blockIdx.x * 8 + (threadIdx.x >> 5);
+  const int lane = threadIdx.x & 31;
+  if (s >= n_seq) return;
+  const float* h = stash + stash_idx(d, s, d.L - 1, d.T - 1, 5);
+  float a = 0.f;
+  for (int u = lane; u < d.H; u += 32) a += h[u] * __ldg(params + d.hw_off + u);
+#pragma unroll
+  for (int o = 16; o > 0; o >>= 1) a += __shfl_down_sync(0xffffffffu, a, o);
+  if (lane == 0) yhat[s] = (err_flag && *err_flag == call_id) ? __int_as_float(0x7fc00000) : a + __ldg(params + d.hb_off);
+}
+
+}  // namespace
+
+extern unsigned g_lstm_call_id;   // lstm_tc.cu
+
+// forward over all layers and steps: fills the stash (i, f, g, o, c, h per sequence, layer, step) and yhat
+int lstm_tc_fwd(const lstm::LstmDesc& d, const float* params, const float* X, size_t n_seq, float* stash, float* yhat,
+                unsigned* err_flag, cudaStream_t st) {
+  static bool attr_set[64] = {};
+  int dev = 0;
+  DLAS_CUDA(cudaGetDevice(&dev));
+  if (dev < 0 || dev >= 64 || !attr_set[dev]) {
+    DLAS_CUDA(cudaFuncSetAttribute(lstm_fwd_tc_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)SMEM_BYTES));
+    if (dev >= 0 && dev < 64) attr_set[dev] = true;
+  }
+  ++g_lstm_call_id;
+  const size_t n_tiles = (n_seq + TS - 1) / TS;
+  const int max_pairs = sm_count() / 2;
+  const int pairs = (int)(n_tiles < (size_t)max_pairs ? n_tiles : (size_t)max_pairs);
+  lstm_fwd_tc_kernel<<<2 * pairs, NT, SMEM_BYTES, st>>>(d, params, X, n_seq, stash, err_flag, g_lstm_call_id);
+  DLAS_LAUNCH_CHECK();
+  lstm_head_kernel<<<(unsigned)((n_seq + 7) / 8), 256, 0, st>>>(d, params, stash, n_seq, err_flag, g_lstm_call_id, yhat);
+  DLAS_LAUNCH_CHECK();
+  return DLAS_OK;
+}
+
+}  // namespace dlas

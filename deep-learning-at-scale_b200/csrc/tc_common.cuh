@@ -191,6 +191,30 @@ __device__ __forceinline__ void bulk_g2s(uint32_t sdst, const void* gsrc, uint32
                "r"(bytes), "r"(smem_u32(bar)) : "memory");
 }
 
+// ---- cross-CTA hand-over of operand tiles (LSTM recurrence: each CTA of a pair writes its half of h_t into the peer's
+// A tile, which the peer's tcgen05.mma then reads) -------------------------------------------------------------------
+// 16-byte store into a peer CTA's shared memory (address from map_to_cta)
+__device__ __forceinline__ void st_cluster_v4(uint32_t caddr, uint4 v) {
+  asm volatile("st.shared::cluster.v4.b32 [%0], {%1,%2,%3,%4};" ::"r"(caddr), "r"(v.x), "r"(v.y), "r"(v.z), "r"(v.w) : "memory");
+}
+// generic-proxy writes (own or peer shared memory) -> visible to async-proxy readers (tcgen05.mma operand fetch)
+__device__ __forceinline__ void fence_async_all() { asm volatile("fence.proxy.async;" ::: "memory"); }
+// arrive on a mbarrier of a peer CTA (address from map_to_cta), releasing this thread's earlier writes at cluster scope
+__device__ __forceinline__ void mbar_arrive_remote(uint32_t cbar) {
+  asm volatile("mbarrier.arrive.release.cluster.shared::cluster.b64 _, [%0];" ::"r"(cbar) : "memory");
+}
+// bounded wait with cluster-scope acquire: pairs with mbar_arrive_remote
+__device__ __forceinline__ bool mbar_wait_cluster(uint64_t* bar, uint32_t parity) {
+  uint32_t a = smem_u32(bar);
+  for (uint32_t it = 0; it < (1u << 26); ++it) {
+    uint32_t ok;
+    asm volatile("{\n\t.reg .pred p;\n\tmbarrier.try_wait.parity.acquire.cluster.shared::cta.b64 p, [%1], %2;\n\tselp.u32 %0, 1, 0, p;\n\t}"
+                 : "=r"(ok) : "r"(a), "r"(parity) : "memory");
+    if (ok) return true;
+  }
+  return false;
+}
+
 // packed fp16 helpers for the epilogues (one instruction per two elements)
 __device__ __forceinline__ uint32_t relu_h2(uint32_t a) {
   uint32_t r;

@@ -73,6 +73,7 @@ SIGNATURES = {
     "dlas_lstm_grad": (_i, [_i, _i, _i, _i, _i, _p, _p, _p, _sz, _p, _p, _sz, _p]),
     "dlas_lstm_mode_supported": (_i, [_i, _i, _i, _i]),
     "dlas_lstm_grad_mode": (_i, [_i, _i, _i, _i, _i, _i, _p, _p, _p, _sz, _p, _p, _sz, _p]),
+    "dlas_lstm_predict_mode": (_i, [_i, _i, _i, _i, _i, _p, _p, _sz, _p, _p, _sz, _p]),
     "dlas_lstm_predict": (_i, [_i, _i, _i, _i, _p, _p, _sz, _p, _p, _sz, _p]),
     "dlas_cnn_n_params": (_sz, [_i, _i, _i, _i]),
     "dlas_cnn_workspace_bytes": (_sz, [_i, _i, _i, _i, _sz]),

@@ -215,10 +215,10 @@ def lstm_grad(d_in, hidden, n_layers, T, loss, params, X, y, grad_sum, workspace
     return grad_sum
 
 
-def lstm_predict(d_in, hidden, n_layers, T, params, X, workspace, out=None):
+def lstm_predict(d_in, hidden, n_layers, T, params, X, workspace, out=None, mode=_lib.MODE_FP32):
     if out is None:
         out = torch.empty((X.shape[0], 1), dtype=torch.float32, device=X.device)
-    check(_lib.load().dlas_lstm_predict(d_in, hidden, n_layers, T, ptr(params), ptr(X), X.shape[0], ptr(out),
+    check(_lib.load().dlas_lstm_predict_mode(int(mode), d_in, hidden, n_layers, T, ptr(params), ptr(X), X.shape[0], ptr(out),
                                         ptr(workspace), workspace.numel(), stream_ptr()))
     return out
 

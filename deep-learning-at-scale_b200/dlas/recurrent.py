@@ -66,7 +66,7 @@ class LSTMRegressor(FlatModel):
         return ops.lstm_grad(self.d_in, self.hidden, self.n_layers, self.T, self.loss, self.params, X, y, grad_sum, ws, mode=self.mode)
 
     def _forward(self, X, ws):
-        return ops.lstm_predict(self.d_in, self.hidden, self.n_layers, self.T, self.params, X, ws)
+        return ops.lstm_predict(self.d_in, self.hidden, self.n_layers, self.T, self.params, X, ws, mode=self.mode)
 
     def _describe(self):
         return {"lstm": [self.d_in, self.hidden, self.n_layers, self.T]}

@@ -282,6 +282,9 @@ int dlas_lstm_mode_supported(int d_in, int hidden, int n_layers, int mode);
 int dlas_lstm_grad_mode(int mode, int d_in, int hidden, int n_layers, int T, int loss, const float* params,
                         const float* X, const float* y, size_t n_seq, float* grad_sum, void* workspace,
                         size_t workspace_bytes, void* stream);
+int dlas_lstm_predict_mode(int mode, int d_in, int hidden, int n_layers, int T, const float* params,
+                           const float* X, size_t n_seq, float* yhat, void* workspace,
+                           size_t workspace_bytes, void* stream);
 /* forward only: yhat (n_seq) -- model.predict / test_on_batch, cnn.py:132 */
 int dlas_lstm_predict(int d_in, int hidden, int n_layers, int T, const float* params,
                       const float* X, size_t n_seq, float* yhat, void* workspace,

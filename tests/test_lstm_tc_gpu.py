@@ -89,3 +89,26 @@ def test_mode_tc_vs_oracle(dl):
         print("loss", loss, abs(got[-1] / lr - 1), _relerr(got[:-1], gref))
         assert got[-1] == pytest.approx(lr, rel=1e-3)
         assert _relerr(got[:-1], gref) < 5e-3 + (2.0 / B if loss else 0.0)
+
+
+@pytest.mark.parametrize("shape", [(8, 128, 2, 48, 300), (8, 128, 2, 48, 37), (5, 128, 1, 3, 1), (16, 128, 3, 6, 700), (8, 128, 2, 5, 9472 + 128 + 3)])
+def test_forward_recurrence_stage_vs_fp32(dl, shape):
+    """The persistent tcgen05 recurrence (state on chip, CTA pair exchanging h through distributed shared memory) against
+    the fp32 forward: predictions within 2e-3 of max|yhat| (fp16 operands, recurrence of T steps), and the gradient of the
+    step whose BPTT / weight gradient stay fp32 but consume the tensor-core stash within 1e-2."""
+    from dlas import ops
+    d, h, nl, T, B = shape
+    p, X, y = _setup(d, h, nl, T, B, B + 1)
+    ws = ops.lstm_workspace(d, h, nl, T, B)
+    ref = ops.lstm_predict(d, h, nl, T, _cuda(p), _cuda(X), ws).cpu().numpy()
+    got = ops.lstm_predict(d, h, nl, T, _cuda(p), _cuda(X), ws, mode=0x100 | TC_FWD).cpu().numpy()
+    assert np.isfinite(got).all()
+    print(shape, "max |dyhat| / max|yhat| = %.3g" % (np.abs(got - ref).max() / np.abs(ref).max()))
+    assert np.abs(got - ref).max() < 2e-3 * max(1.0, np.abs(ref).max())
+    again = ops.lstm_predict(d, h, nl, T, _cuda(p), _cuda(X), ws, mode=0x100 | TC_FWD).cpu().numpy()
+    assert np.array_equal(got, again)
+    if B <= 1000:
+        g32 = _grad(dl.MODE_FP32, d, h, nl, T, 0, p, X, y)
+        gtc = _grad(0x100 | TC_FWD, d, h, nl, T, 0, p, X, y)
+        assert gtc[-1] == pytest.approx(g32[-1], rel=2e-3)
+        assert _relerr(gtc[:-1], g32[:-1].astype(np.float64)) < (1e-2 if B * T >= 1000 else 5e-2)

@@ -23,6 +23,8 @@ bool lstm_tc_supported(const lstm::LstmDesc& d);
 size_t lstm_tc_dw_partial_floats(const lstm::LstmDesc& d);
 int lstm_tc_fwd(const lstm::LstmDesc& d, const float* params, const float* X, size_t n_seq, float* stash, float* yhat,
                 unsigned* err_flag, cudaStream_t st);
+int lstm_tc_bwd(const lstm::LstmDesc& d, int loss, const float* params, const float* y, float* yhat_dy, size_t n_seq,
+                float* stash, float* dseqP, float* partials, int n_blocks, unsigned* err_flag, cudaStream_t st);
 int lstm_tc_dw(const lstm::LstmDesc& d, const float* X, const float* stash, size_t n_seq, float* grad_sum, float* tc_partials,
                unsigned* err_flag, cudaStream_t st);
 
@@ -275,7 +277,7 @@ lstm_reduce_kernel(const float* __restrict__ partials, size_t stride, int n_acti
   out[i0 + i] = s;
 }
 
-struct Ws { float *stash, *dseq, *KT, *partials, *yhat, *tcp; unsigned* status; size_t bytes; };
+struct Ws { float *stash, *dseq, *KT, *partials, *yhat, *tcp, *dseqP; unsigned* status; size_t bytes; };
 Ws carve_ws(const LstmDesc& d, size_t n_seq, void* base) {
   Ws w;
   size_t o = 0;
@@ -286,6 +288,8 @@ Ws carve_ws(const LstmDesc& d, size_t n_seq, void* base) {
   w.partials = take((size_t)sm_count() * pstride(d.n_params));
   w.yhat = take(n_seq);
   w.tcp = take(lstm_tc_supported(d) ? lstm_tc_dw_partial_floats(d) : 0);      // tensor-core weight-gradient partials
+  // tensor-core BPTT: the two CTAs of a pair write partial dx of a layer into separate buffers (x 2 sets from 3 layers up)
+  w.dseqP = take(lstm_tc_supported(d) && d.L > 1 ? (size_t)(d.L >= 3 ? 4 : 2) * n_seq * d.T * (size_t)d.H : 0);
   w.status = reinterpret_cast<unsigned*>(take(64));                              // status words of the tensor-core kernels
   w.bytes = o * sizeof(float);
   return w;
@@ -317,7 +321,7 @@ int stage_bits(int mode, const LstmDesc& d, const char* fn, int* bits) {
     set_error("%s: DLAS_MODE_TC needs hidden = 128 and d_in <= 16 (got hidden %d, d_in %d)", fn, d.H, d.d_in);
     return DLAS_ERR_UNSUPPORTED_SHAPE;
   }
-  *bits = (mode == DLAS_MODE_TC) ? (TC_FWD | TC_DW) : (mode & 0x7);
+  *bits = (mode == DLAS_MODE_TC) ? (TC_FWD | TC_BWD | TC_DW) : (mode & 0x7);
   return DLAS_OK;
 }
 }  // namespace
@@ -420,8 +424,13 @@ extern "C" int dlas_lstm_grad_mode(int mode, int d_in, int hidden, int n_layers,
     lstm_fwd_kernel<<<grid, NT, smem, st>>>(d, params, X, n_seq, w.stash, w.yhat);
     DLAS_LAUNCH_CHECK();
   }
-  lstm_bwd_kernel<<<grid, NT, smem, st>>>(d, loss, params, w.KT, y, w.yhat, n_seq, w.stash, w.dseq, w.partials);
-  DLAS_LAUNCH_CHECK();
+  if (bits & TC_BWD) {   // loss + head gradient, then the backward recurrence on the tensor cores
+    rc = lstm_tc_bwd(d, loss, params, y, w.yhat, n_seq, w.stash, w.dseqP, w.partials, grid, w.status, st);
+    if (rc != DLAS_OK) return rc;
+  } else {
+    lstm_bwd_kernel<<<grid, NT, smem, st>>>(d, loss, params, w.KT, y, w.yhat, n_seq, w.stash, w.dseq, w.partials);
+    DLAS_LAUNCH_CHECK();
+  }
   size_t n_layer_params = (size_t)d.hw_off;
   if (bits & TC_DW) {   // weight gradient as a tcgen05 GEMM over all (sequence, t) rows
     rc = lstm_tc_dw(d, X, w.stash, n_seq, grad_sum, w.tcp, w.status, st);

@@ -112,3 +112,24 @@ def test_forward_recurrence_stage_vs_fp32(dl, shape):
         gtc = _grad(0x100 | TC_FWD, d, h, nl, T, 0, p, X, y)
         assert gtc[-1] == pytest.approx(g32[-1], rel=2e-3)
         assert _relerr(gtc[:-1], g32[:-1].astype(np.float64)) < (1e-2 if B * T >= 1000 else 5e-2)
+
+
+@pytest.mark.parametrize("shape", [(8, 128, 2, 48, 300), (8, 128, 2, 48, 37), (5, 128, 1, 3, 1), (16, 128, 3, 6, 700), (8, 128, 4, 5, 130)])
+@pytest.mark.parametrize("loss", [O.LOSS_MSE, O.LOSS_MAE_CLIP])
+def test_backward_recurrence_stage_vs_fp32(dl, shape, loss):
+    """BPTT on the tensor cores (dz K^T per step, partial dh exchanged inside the CTA pair) on the fp32 forward's stash,
+    weight gradient in fp32: the loss sum is computed in fp32 from the same predictions (bit-identical), gradients
+    within 5e-3 per block (fp16 operands through T steps of recurrence)."""
+    d, h, nl, T, B = shape
+    p, X, y = _setup(d, h, nl, T, B, B + 2)
+    yy = y * (8.0 if loss == O.LOSS_MAE_CLIP else 1.0)
+    ref = _grad(dl.MODE_FP32, d, h, nl, T, loss, p, X, yy)
+    got = _grad(0x100 | TC_BWD, d, h, nl, T, loss, p, X, yy)
+    errs = _blocks(d, h, nl, got[:-1], ref[:-1].astype(np.float64))
+    _, (hw, hb), n = O.lstm_offsets(d, h, nl)
+    print(shape, loss, errs, "head", _relerr(got[hw:hw + h], ref[hw:hw + h].astype(np.float64)))
+    assert got[-1] == pytest.approx(ref[-1], rel=1e-6)
+    assert _relerr(got[hw:hw + h + 1], ref[hw:hw + h + 1].astype(np.float64)) < 1e-5      # head: fp32, another summation order
+    assert max(errs.values()) < (5e-3 if B * T >= 1000 else 3e-2)
+    again = _grad(0x100 | TC_BWD, d, h, nl, T, loss, p, X, yy)
+    assert np.array_equal(got, again)

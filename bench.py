@@ -559,11 +559,18 @@ def main():
         del Xr, yr
         # LSTM 2x128, T=48, batch 4096 (config 5)
         Xs, ysq = ops.synth_series(4096, 48, 8)
-        ml = dlas.Sequential([dlas.LSTM(128, input_shape=(48, 8), return_sequences=True), dlas.LSTM(128), dlas.Dense(1)])
-        ml.compile(loss="mse", optimizer=dlas.SGD(lr=0.001, momentum=0.99, decay=1e-6, nesterov=True))
-        t = timed(lambda: ml.train_on_batch(Xs, ysq), 3)
-        extras["lstm_2x128_T48_batch4096"] = {"sequences_per_s": 4096 / t, "ms_per_step": t * 1e3, "mode": "fp32",
-                                              "frac_of_bf16_sustained_peak": 57.41e6 * 4096 / t / 1e12 / pk["tf_sust"]}
+        for lm in ("fp32", "tc"):
+            if lm == "tc" and not ops.lstm_mode_supported(8, 128, 2, dlas.MODE_TC):
+                continue
+            ml = dlas.Sequential([dlas.LSTM(128, input_shape=(48, 8), return_sequences=True), dlas.LSTM(128), dlas.Dense(1)], mode=lm)
+            ml.compile(loss="mse", optimizer=dlas.SGD(lr=0.001, momentum=0.99, decay=1e-6, nesterov=True))
+            t = timed(lambda: ml.train_on_batch(Xs, ysq), 5)
+            tp = timed(lambda: ml.predict(Xs), 5)
+            extras["lstm_2x128_T48_batch4096" + ("" if lm == "tc" else "_fp32")] = {
+                "sequences_per_s": 4096 / t, "ms_per_step": t * 1e3, "mode": lm,
+                "frac_of_bf16_sustained_peak": 57.41e6 * 4096 / t / 1e12 / pk["tf_sust"],
+                "predict_sequences_per_s": 4096 / tp}
+            del ml
         # the script's own CNN (cnn.py:110-128) at its own batch of 20 and at 4096 rows per step, dropout on, through the
         # epoch loop of the library (dlas_cnn_fit_steps: 6 launches per step, no Python between steps)
         for cb in (20, 4096):
@@ -578,6 +585,40 @@ def main():
             extras["cnn_48_conv13x100_dense12_batch%d" % cb] = {"samples_per_s": cb / t, "us_per_step": t * 1e6, "mode": "fp32",
                                                                  "launches_per_step": 6}
         del series, ys, Wd, yd, X8, y8, Xs, ysq, Wc, Xc, yc
+
+    if N > 1 and not args.no_extras:
+        def timed_dp(fn, n):
+            for _ in range(2):
+                fn()
+            barrier()
+            e0.record()
+            for _ in range(n):
+                fn()
+            e1.record()
+            barrier()
+            tt = torch.tensor([e0.elapsed_time(e1)], device="cuda")
+            dist.all_reduce(tt, op=dist.ReduceOp.MAX)
+            return float(tt.item()) * 1e-3 / n
+        # configs[4]: LSTM 2x128, T = 48, GLOBAL batch 4096 split over the ranks (strong scaling, as BASELINE.json states it)
+        lb = 4096 // N
+        Xs, ysq = ops.synth_series(lb, 48, 8, start=rank * lb)
+        lm = "tc" if ops.lstm_mode_supported(8, 128, 2, dlas.MODE_TC) else "fp32"
+        ml = dlas.Sequential([dlas.LSTM(128, input_shape=(48, 8), return_sequences=True), dlas.LSTM(128), dlas.Dense(1)], mode=lm)
+        ml.compile(loss="mse", optimizer=dlas.SGD(lr=0.001, momentum=0.99, decay=1e-6, nesterov=True))
+        t = timed_dp(lambda: ml.train_on_batch(Xs, ysq, global_rows=4096), 5)
+        extras["lstm_2x128_T48_batch4096"] = {"sequences_per_s": 4096 / t, "ms_per_step": t * 1e3, "mode": lm, "scaling": "strong",
+                                              "sequences_per_gpu_per_step": lb, "exchange": "nccl all-reduce of the 807 KB bucket"}
+        del ml, Xs, ysq
+        # configs[3]: dynamic ANN 192-256-256-1, 65,536 windows per GPU per step read in place from the raw series (weak scaling)
+        series, ys = ops.synth_rows(65536 + 23, 8, start=rank * 65536)
+        Wd = dlas.LagWindows(series, 24)
+        mdl = dlas.Sequential([dlas.Dense(192, 256, activation="relu"), dlas.Dense(256, 256, activation="relu"), dlas.Dense(256, 1)])
+        mdl.compile(loss="mse", optimizer=dlas.SGD(lr=0.001, momentum=0.99, decay=1e-6, nesterov=True), exchange="nccl")
+        yd = ys[23:].contiguous()
+        t = timed_dp(lambda: mdl.train_on_batch(Wd, yd, global_rows=65536 * N), 5)
+        extras["dynamic_ann_192_256_256_1"] = {"samples_per_s": 65536 * N / t, "mode": "fp32", "rows_per_gpu_per_step": 65536,
+                                               "scaling": "weak", "exchange": "nccl all-reduce of the 462 KB bucket"}
+        del mdl, series, ys, Wd, yd
 
     if rank == 0:
         tc_traffic, tc_src = traffic_from_profiles("mlp_tc_kernel", B) if mode == "tc" else (None, None)

@@ -151,7 +151,7 @@ lstm_bwd_tc_kernel(const LstmDesc d, const float* __restrict__ params, float* __
             ok = mbar_wait(&bars[B_Z], (q - 1) & 1) && ok;
             fence_after();
             uint32_t v[32];
-            if (l > 0 && valid) {
+            if (l > 0) {   // (warp-uniform: tcgen05.ld is warp-collective; only the stores depend on the row being valid)
               float* dst = dsW + (size_t)rank * pstr + (sq * T + (t + 1)) * (size_t)HT + hh * 64;
 #pragma unroll
               for (int c = 0; c < 2; ++c) {
@@ -159,7 +159,7 @@ lstm_bwd_tc_kernel(const LstmDesc d, const float* __restrict__ params, float* __
                 tmem_ld_wait();
 #pragma unroll
                 for (int j4 = 0; j4 < 8; ++j4)
-                  *reinterpret_cast<float4*>(dst + c * 32 + j4 * 4) = make_float4(__uint_as_float(v[j4 * 4]), __uint_as_float(v[j4 * 4 + 1]),
+                  if (valid) *reinterpret_cast<float4*>(dst + c * 32 + j4 * 4) = make_float4(__uint_as_float(v[j4 * 4]), __uint_as_float(v[j4 * 4 + 1]),
                                                                                  __uint_as_float(v[j4 * 4 + 2]), __uint_as_float(v[j4 * 4 + 3]));
               }
             }
@@ -266,7 +266,7 @@ lstm_bwd_tc_kernel(const LstmDesc d, const float* __restrict__ params, float* __
         // ---- the layer's last MMA (step 0): only its dx columns are needed (layers above 0) ----
         ok = mbar_wait(&bars[B_Z], (q - 1) & 1) && ok;
         fence_after();
-        if (l > 0 && valid) {
+        if (l > 0) {
           uint32_t v[32];
           float* dst = dsW + (size_t)rank * pstr + (sq * T + 0) * (size_t)HT + hh * 64;
 #pragma unroll
@@ -275,7 +275,7 @@ lstm_bwd_tc_kernel(const LstmDesc d, const float* __restrict__ params, float* __
             tmem_ld_wait();
 #pragma unroll
             for (int j4 = 0; j4 < 8; ++j4)
-              *reinterpret_cast<float4*>(dst + c * 32 + j4 * 4) = make_float4(__uint_as_float(v[j4 * 4]), __uint_as_float(v[j4 * 4 + 1]),
+              if (valid) *reinterpret_cast<float4*>(dst + c * 32 + j4 * 4) = make_float4(__uint_as_float(v[j4 * 4]), __uint_as_float(v[j4 * 4 + 1]),
                                                                              __uint_as_float(v[j4 * 4 + 2]), __uint_as_float(v[j4 * 4 + 3]));
           }
         }

@@ -11,7 +11,7 @@ pytestmark = pytest.mark.gpu
 ROOT = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
 
 
-@pytest.mark.parametrize("mode", ["fp32", "tc", "tc-nccl", "tc-fit", "fp32-fit", "tc-graph", "tc-peer", "fp32-peer", "fp32-pavg3"])
+@pytest.mark.parametrize("mode", ["fp32", "tc", "tc-nccl", "tc-fit", "fp32-fit", "tc-graph", "tc-peer", "fp32-peer", "fp32-pavg3", "lstm-fp32", "lstm-tc"])
 def test_dp_two_ranks_match_oracle(mode):
     if torch.cuda.device_count() < 2:
         pytest.skip("needs 2 GPUs")

@@ -25,6 +25,42 @@ if "-" in mode:
 rank, local, world = int(os.environ["RANK"]), int(os.environ["LOCAL_RANK"]), int(os.environ["WORLD_SIZE"])
 torch.cuda.set_device(local)
 dist.init_process_group("nccl", device_id=torch.device("cuda", local))
+if mode == "lstm":
+    # data-parallel LSTM (configs[4] shape, smaller batch): every rank trains on its slice of each global batch, the flat
+    # bucket is all-reduced by NCCL between our kernels; compared with the single-process fp64 oracle
+    lmode = path if path in ("fp32", "tc") else "fp32"
+    d_in, H, L, T, batch, steps = 8, 128, 2, 12, 256, 4
+    Xs, ys = O.synth_series(O.BASE_SEED, 0, batch * steps, T, d_in)
+    p0 = O.lstm_init(d_in, H, L, O.BASE_SEED)
+    mine = parallel.local_rows(Xs.shape[0], batch, rank, world).numpy()
+    ml = dlas.Sequential([dlas.LSTM(H, input_shape=(T, d_in), return_sequences=True), dlas.LSTM(H), dlas.Dense(1)], mode=lmode)
+    ml.compile(loss="mse", optimizer=dlas.SGD(lr=0.001, momentum=0.99, decay=1e-6, nesterov=True))
+    ml.set_weights_flat(p0)
+    Xl, yl = torch.from_numpy(Xs[mine]).cuda(), torch.from_numpy(ys[mine]).cuda().reshape(-1, 1)
+    lb = batch // world
+    got = torch.cat([ml.train_on_batch(Xl[s * lb:(s + 1) * lb], yl[s * lb:(s + 1) * lb], global_rows=batch) for s in range(steps)]).cpu().numpy()
+    w = ml.get_weights_flat()
+    chk = torch.tensor([float(np.abs(w).sum())], device="cuda", dtype=torch.float64)
+    lo, hi = chk.clone(), chk.clone()
+    dist.all_reduce(lo, op=dist.ReduceOp.MIN)
+    dist.all_reduce(hi, op=dist.ReduceOp.MAX)
+    ok = True
+    if rank == 0:
+        pr = p0.astype(np.float64)
+        ref = O.lstm_fit_steps(pr, d_in, H, L, Xs.astype(np.float64), ys.astype(np.float64), batch, steps, O.LOSS_MSE, O.sgd_config(),
+                               O.opt_state(pr.size))
+        lerr = float(np.abs(got / ref - 1).max())
+        werr = float(np.linalg.norm(w - pr) / np.linalg.norm(pr))
+        same = float(hi.item() - lo.item())
+        tol_l, tol_w = (1e-4, 1e-4) if lmode == "fp32" else (1e-3, 1e-4)
+        ok = lerr < tol_l and werr < tol_w and same == 0.0
+        print("dp_check world=%d mode=lstm path=%s: max loss rel err %.3g, weights rel err %.3g, rank spread %.3g -> %s"
+              % (world, lmode, lerr, werr, same, "OK" if ok else "FAIL"), flush=True)
+    flag = torch.tensor([0 if ok else 1], device="cuda")
+    dist.broadcast(flag, 0)
+    torch.cuda.synchronize()
+    sys.stdout.flush()
+    os._exit(int(flag.item()))
 dims = [32, 256, 256, 1]
 batch, steps = 8192, 12
 X, y = O.synth_rows(O.BASE_SEED, 0, batch * steps, 32)

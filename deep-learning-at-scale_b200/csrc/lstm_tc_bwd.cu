@@ -23,7 +23,8 @@ using namespace lstm;
 
 constexpr int HT = 128, TS = 128, XW0 = 16, UH = 64;
 __host__ __device__ inline int xw_of(int l) { return l == 0 ? XW0 : HT; }
-constexpr int N_EPI = 256, ISSUER_WARP = 8, NT = 288;
+constexpr int N_EPI = 512, ISSUER_WARP = 16, NT = 544;   // 16 epilogue warps: the step is bound by the latency of the stash reads
+constexpr int UT = 16;                                     // units per epilogue thread
 constexpr uint32_t S_W = 0 /*[256 rows][256 gate cols] fp16, 128 KB*/, S_DZ = 131072 /*[128][256] fp16, 64 KB*/,
                    S_RECV = 196608 /*[128][64] fp32, 32 KB*/, S_BAR = S_RECV + 32768;
 enum { B_A = 0, B_Z, B_RFULL, B_RFREE, N_BARS };
@@ -93,10 +94,10 @@ lstm_bwd_tc_kernel(const LstmDesc d, const float* __restrict__ params, float* __
   const uint32_t peer_RFULL = map_to_cta(smem_u32(&bars[B_RFULL]), rank ^ 1u), peer_RFREE = map_to_cta(smem_u32(&bars[B_RFREE]), rank ^ 1u);
   uint32_t q = 0;
 
-  const int q4 = warp & 3, hh = (warp >> 2) & 1;
+  const int q4 = warp & 3, hh = (warp >> 2) & 3;
   const int row = q4 * 32 + lane;
   const uint32_t lane_base = (uint32_t)(q4 * 32) << 16;
-  const int u0 = UH * (int)rank + hh * 32;                // first of this thread's 32 units
+  const int u0 = UH * (int)rank + hh * UT;                // first of this thread's 16 units
 
   for (size_t tile = pair; tile < n_tiles; tile += n_pairs) {
     const size_t seq = tile * TS + row;
@@ -140,22 +141,29 @@ lstm_bwd_tc_kernel(const LstmDesc d, const float* __restrict__ params, float* __
         }
       } else {
         // =========================== epilogue warps ===========================
-        float dc_next[32], dh_rec[32];
+        float dc_next[UT], dh_rec[UT];
 #pragma unroll
-        for (int j = 0; j < 32; ++j) dc_next[j] = 0.f;
+        for (int j = 0; j < UT; ++j) dc_next[j] = 0.f;
         const float* hw = params + d.hw_off + u0;
         for (int t = T - 1; t >= 0; --t, ++q) {
           const bool first = (t == T - 1);
+          if (valid && t > 0) {   // step t-1's stash lines (and the layer above's dx): into L2 a round ahead
+            const float* nx = stash + stash_idx(d, sq, l, t - 1, 0) + u0;
+#pragma unroll
+            for (int c = 0; c < 5; ++c) prefetch_l2(nx + c * HT);
+            if (t > 1) prefetch_l2(stash + stash_idx(d, sq, l, t - 2, 4) + u0);
+            if (l < d.L - 1) { prefetch_l2(dsR + (sq * T + t - 1) * (size_t)HT + u0); prefetch_l2(dsR + pstr + (sq * T + t - 1) * (size_t)HT + u0); }
+          }
           // ---- what the previous round's MMA (step t+1) produced: dx partial, my units' dh partial, the peer's units'
           if (!first) {
             ok = mbar_wait(&bars[B_Z], (q - 1) & 1) && ok;
             fence_after();
             uint32_t v[32];
             if (l > 0) {   // (warp-uniform: tcgen05.ld is warp-collective; only the stores depend on the row being valid)
-              float* dst = dsW + (size_t)rank * pstr + (sq * T + (t + 1)) * (size_t)HT + hh * 64;
+              float* dst = dsW + (size_t)rank * pstr + (sq * T + (t + 1)) * (size_t)HT + hh * 32;
 #pragma unroll
-              for (int c = 0; c < 2; ++c) {
-                tmem_ld32(tm + lane_base + hh * 64 + c * 32, v);
+              for (int c = 0; c < 1; ++c) {
+                tmem_ld32(tm + lane_base + hh * 32 + c * 32, v);
                 tmem_ld_wait();
 #pragma unroll
                 for (int j4 = 0; j4 < 8; ++j4)
@@ -163,52 +171,52 @@ lstm_bwd_tc_kernel(const LstmDesc d, const float* __restrict__ params, float* __
                                                                                  __uint_as_float(v[j4 * 4 + 2]), __uint_as_float(v[j4 * 4 + 3]));
               }
             }
-            tmem_ld32(tm + lane_base + xw + UH * (rank ^ 1u) + hh * 32, v);     // the peer's units: send
+            tmem_ld16(tm + lane_base + xw + UH * (rank ^ 1u) + hh * UT, *reinterpret_cast<uint32_t(*)[16]>(&v[0]));   // the peer's units: send
             tmem_ld_wait();
             if (q >= 1) ok = mbar_wait_cluster(&bars[B_RFREE], (q - 1) & 1) && ok;   // the peer has read what I sent last round
 #pragma unroll
-            for (int j4 = 0; j4 < 8; ++j4)
-              st_cluster_v4(peerRecv + recv_off(row, hh * 8 + j4), make_uint4(v[j4 * 4], v[j4 * 4 + 1], v[j4 * 4 + 2], v[j4 * 4 + 3]));
-            tmem_ld32(tm + lane_base + xw + u0, v);                             // my units: keep
+            for (int j4 = 0; j4 < UT / 4; ++j4)
+              st_cluster_v4(peerRecv + recv_off(row, hh * 4 + j4), make_uint4(v[j4 * 4], v[j4 * 4 + 1], v[j4 * 4 + 2], v[j4 * 4 + 3]));
+            tmem_ld16(tm + lane_base + xw + u0, *reinterpret_cast<uint32_t(*)[16]>(&v[0]));                    // my units: keep
             tmem_ld_wait();
             fence_before();
 #pragma unroll
-            for (int j = 0; j < 32; ++j) dh_rec[j] = __uint_as_float(v[j]);
+            for (int j = 0; j < UT; ++j) dh_rec[j] = __uint_as_float(v[j]);
           } else {
             if (q >= 1) ok = mbar_wait_cluster(&bars[B_RFREE], (q - 1) & 1) && ok;   // nothing to send: phases stay in step
 #pragma unroll
-            for (int j = 0; j < 32; ++j) dh_rec[j] = 0.f;
+            for (int j = 0; j < UT; ++j) dh_rec[j] = 0.f;
           }
           __syncwarp();
           if (lane == 0) mbar_arrive_remote(peer_RFULL);
           ok = mbar_wait_cluster(&bars[B_RFULL], q & 1) && ok;
           if (!first) {
 #pragma unroll
-            for (int j4 = 0; j4 < 8; ++j4) {
-              const float4 r = lds128f(sRecv + recv_off(row, hh * 8 + j4));
+            for (int j4 = 0; j4 < UT / 4; ++j4) {
+              const float4 r = lds128f(sRecv + recv_off(row, hh * 4 + j4));
               dh_rec[j4 * 4] += r.x; dh_rec[j4 * 4 + 1] += r.y; dh_rec[j4 * 4 + 2] += r.z; dh_rec[j4 * 4 + 3] += r.w;
             }
           }
           __syncwarp();
           if (lane == 0) mbar_arrive_remote(peer_RFREE);
-          // ---- gate gradients of step t for this row's 32 units, 8 units at a time ----
+          // ---- gate gradients of step t for this row's 16 units, 8 units at a time ----
           const float* st = stash + stash_idx(d, sq, l, t, 0) + u0;
           float* stw = stash + stash_idx(d, sq, l, t, 0) + u0;
           const float* cp = stash + stash_idx(d, sq, l, t > 0 ? t - 1 : 0, 4) + u0;
           const float dyr = (l == d.L - 1 && first && valid) ? __ldg(dy + sq) : 0.f;
           const float* din0 = dsR + (sq * T + t) * (size_t)HT + u0;              // dx partials of the layer above (both CTAs')
 #pragma unroll
-          for (int b8 = 0; b8 < 4; ++b8) {
+          for (int b8 = 0; b8 < UT / 8; ++b8) {
             float gi[8], gf[8], gg[8], go[8], cc[8], cpv[8], dhv[8];
 #pragma unroll
             for (int h4 = 0; h4 < 2; ++h4) {
               const int o = b8 * 8 + h4 * 4;
               float4 a = make_float4(0.f, 0.f, 0.f, 0.f), f4 = a, g4 = a, o4 = a, c4 = a, p4 = a, d4 = a;
               if (valid) {
-                a = __ldcs(reinterpret_cast<const float4*>(st + o));
-                f4 = __ldcs(reinterpret_cast<const float4*>(st + HT + o));
-                g4 = __ldcs(reinterpret_cast<const float4*>(st + 2 * HT + o));
-                o4 = __ldcs(reinterpret_cast<const float4*>(st + 3 * HT + o));
+                a = __ldg(reinterpret_cast<const float4*>(st + o));
+                f4 = __ldg(reinterpret_cast<const float4*>(st + HT + o));
+                g4 = __ldg(reinterpret_cast<const float4*>(st + 2 * HT + o));
+                o4 = __ldg(reinterpret_cast<const float4*>(st + 3 * HT + o));
                 c4 = __ldg(reinterpret_cast<const float4*>(st + 4 * HT + o));
                 if (t > 0) p4 = __ldg(reinterpret_cast<const float4*>(cp + o));
                 if (l < d.L - 1) {
@@ -253,7 +261,7 @@ lstm_bwd_tc_kernel(const LstmDesc d, const float* __restrict__ params, float* __
               }
             }
             // fp16 A tile of the next MMA: column g*64 + (unit within this CTA)
-            const int cu = hh * 32 + b8 * 8;
+            const int cu = hh * UT + b8 * 8;
             sts128(sDZ + tile_chunk_off(TS, row, 0 * 64 + cu), make_uint4(pack_half2(zi[0], zi[1]), pack_half2(zi[2], zi[3]), pack_half2(zi[4], zi[5]), pack_half2(zi[6], zi[7])));
             sts128(sDZ + tile_chunk_off(TS, row, 1 * 64 + cu), make_uint4(pack_half2(zf[0], zf[1]), pack_half2(zf[2], zf[3]), pack_half2(zf[4], zf[5]), pack_half2(zf[6], zf[7])));
             sts128(sDZ + tile_chunk_off(TS, row, 2 * 64 + cu), make_uint4(pack_half2(zg[0], zg[1]), pack_half2(zg[2], zg[3]), pack_half2(zg[4], zg[5]), pack_half2(zg[6], zg[7])));
@@ -268,10 +276,10 @@ lstm_bwd_tc_kernel(const LstmDesc d, const float* __restrict__ params, float* __
         fence_after();
         if (l > 0) {
           uint32_t v[32];
-          float* dst = dsW + (size_t)rank * pstr + (sq * T + 0) * (size_t)HT + hh * 64;
+          float* dst = dsW + (size_t)rank * pstr + (sq * T + 0) * (size_t)HT + hh * 32;
 #pragma unroll
-          for (int c = 0; c < 2; ++c) {
-            tmem_ld32(tm + lane_base + hh * 64 + c * 32, v);
+          for (int c = 0; c < 1; ++c) {
+            tmem_ld32(tm + lane_base + hh * 32 + c * 32, v);
             tmem_ld_wait();
 #pragma unroll
             for (int j4 = 0; j4 < 8; ++j4)

@@ -4,7 +4,7 @@
 //     memory as one fp16 tile (128 KB for a 256-row layer), the cell state c of its units stays in registers (fp32), and
 //     h_{t-1} of ALL 128 units sits in the A tile [128 sequences][x_t | h_{t-1}] (fp16) that tcgen05.mma reads.
 //   * per step: z = [x_t | h_{t-1}] K_l[:, own columns]  (M = 128 sequences, N = 256, K = 144 / 256; fp32 in TMEM), then the
-//     epilogue warps (thread = sequence row x 32 units) apply the gate non-linearities, update c, write i,f,g,o,c,h to the
+//     epilogue warps (thread = sequence row x 16 units) apply the gate non-linearities, update c, write i,f,g,o,c,h to the
 //     stash (fp32, the layout of lstm.cu, so the fp32 BPTT can consume it) and store h_t as fp16 into BOTH CTAs' A tiles
 //     (own half locally, the other through distributed shared memory) -- the only exchange of the recurrence.
 //   * hand-over by mbarriers only: B_A (own rows of the next step are in place), B_PH (the peer's half of h has arrived:
@@ -21,7 +21,9 @@ using namespace lstm;
 
 constexpr int HT = 128, TS = 128, XW0 = 16, UH = 64;      // hidden width, sequences per tile, padded d_in, units per CTA
 __host__ __device__ inline int xw_of(int l) { return l == 0 ? XW0 : HT; }
-constexpr int N_EPI = 256, ISSUER_WARP = 8, NT = 288;
+constexpr int N_EPI = 512, ISSUER_WARP = 16, NT = 544;   // 16 epilogue warps (4 per TMEM lane quarter, 16 units each): the epilogue
+                                                           // is bound by memory and MUFU latency, so more warps in flight pay
+constexpr int UT = 16;                                     // units per epilogue thread
 constexpr uint32_t S_W = 0 /*[256 rows][256 gate cols] 128 KB*/, S_A = 131072 /*[128][256] 64 KB*/, S_F32 = 196608 /*bias[256]*/,
                    S_BAR = S_F32 + 1024;
 enum { B_A = 0, B_PH, B_Z, B_PZ, N_BARS };
@@ -61,7 +63,7 @@ lstm_fwd_tc_kernel(const LstmDesc d, const float* __restrict__ params, const flo
   uint32_t q = 0;           // round = (tile, layer, step): every barrier completes exactly one phase per round
 
   // epilogue thread -> (row of the tile, 32 of this CTA's 64 units)
-  const int q4 = warp & 3, hh = (warp >> 2) & 1;
+  const int q4 = warp & 3, hh = (warp >> 2) & 3;
   const int row = q4 * 32 + lane;
   const uint32_t lane_base = (uint32_t)(q4 * 32) << 16;
 
@@ -99,22 +101,22 @@ lstm_fwd_tc_kernel(const LstmDesc d, const float* __restrict__ params, const flo
             sts128(sA + tile_chunk_off(TS, row, 8), make_uint4(pack_half2(xv[8], xv[9]), pack_half2(xv[10], xv[11]), pack_half2(xv[12], xv[13]), pack_half2(xv[14], xv[15])));
           }
         } else {
-          const float* src = stash + stash_idx(d, valid ? seq : 0, l - 1, t, 5) + hh * 64;
-#pragma unroll 4
-          for (int c8 = 0; c8 < 8; ++c8) {
+          const float* src = stash + stash_idx(d, valid ? seq : 0, l - 1, t, 5) + hh * 32;
+#pragma unroll
+          for (int c8 = 0; c8 < 4; ++c8) {
             float4 a = make_float4(0.f, 0.f, 0.f, 0.f), e = a;
             if (valid) { a = __ldcg(reinterpret_cast<const float4*>(src + c8 * 8)); e = __ldcg(reinterpret_cast<const float4*>(src + c8 * 8 + 4)); }
-            sts128(sA + tile_chunk_off(TS, row, hh * 64 + c8 * 8), make_uint4(pack_half2(a.x, a.y), pack_half2(a.z, a.w), pack_half2(e.x, e.y), pack_half2(e.z, e.w)));
+            sts128(sA + tile_chunk_off(TS, row, hh * 32 + c8 * 8), make_uint4(pack_half2(a.x, a.y), pack_half2(a.z, a.w), pack_half2(e.x, e.y), pack_half2(e.z, e.w)));
           }
         }
       };
       // ---- layer prologue: h_{-1} = 0 in the whole recurrent part of the A tile, x_0 in place -------------
-      float c_state[32];
+      float c_state[UT];
       if (warp < ISSUER_WARP) {
 #pragma unroll
-        for (int j = 0; j < 32; ++j) c_state[j] = 0.f;
+        for (int j = 0; j < UT; ++j) c_state[j] = 0.f;
 #pragma unroll
-        for (int c8 = 0; c8 < 8; ++c8) sts128(sA + tile_chunk_off(TS, row, xw + hh * 64 + c8 * 8), make_uint4(0u, 0u, 0u, 0u));
+        for (int c8 = 0; c8 < 4; ++c8) sts128(sA + tile_chunk_off(TS, row, xw + hh * 32 + c8 * 8), make_uint4(0u, 0u, 0u, 0u));
         x_store(0);
       }
       fence_async_smem();
@@ -144,58 +146,60 @@ lstm_fwd_tc_kernel(const LstmDesc d, const float* __restrict__ params, const flo
       } else {
         // =========================== epilogue warps ===========================
         for (int t = 0; t < T; ++t, ++q) {
+          // the layer below's h two steps ahead: into L2 now, read at the end of the next round
+          if (l > 0 && valid && t + 2 < T) prefetch_l2(stash + stash_idx(d, seq, l - 1, t + 2, 5) + hh * 32);
           ok = mbar_wait(&bars[B_Z], q & 1) && ok;
           fence_after();
-          // gates of this row's 32 units: columns g*64 + hh*32 + j of the accumulator
-          uint32_t v[32];
-          float ig[32], hout[32];
-          float* st_base = stash + stash_idx(d, valid ? seq : 0, l, t, 0) + UH * rank + hh * 32;
-          auto put = [&](int comp, const float (&a)[32]) {
+          // gates of this row's 16 units: columns g*64 + hh*16 + j of the accumulator
+          uint32_t v[UT];
+          float ig[UT], hout[UT];
+          float* st_base = stash + stash_idx(d, valid ? seq : 0, l, t, 0) + UH * rank + hh * UT;
+          auto put = [&](int comp, const float (&a)[UT]) {
             if (valid) {
 #pragma unroll
-              for (int j4 = 0; j4 < 8; ++j4)
+              for (int j4 = 0; j4 < UT / 4; ++j4)
                 *reinterpret_cast<float4*>(st_base + (size_t)comp * HT + j4 * 4) = make_float4(a[j4 * 4], a[j4 * 4 + 1], a[j4 * 4 + 2], a[j4 * 4 + 3]);
             }
           };
-          const float* bb = bias + hh * 32;
-          tmem_ld32(tm + lane_base + 0 * 64 + hh * 32, v);           // i
+          const float* bb = bias + hh * UT;
+          tmem_ld16(tm + lane_base + 0 * 64 + hh * UT, v);           // i
           tmem_ld_wait();
 #pragma unroll
-          for (int j = 0; j < 32; ++j) ig[j] = sigm(__uint_as_float(v[j]) + bb[j]);
+          for (int j = 0; j < UT; ++j) ig[j] = sigm(__uint_as_float(v[j]) + bb[j]);
           put(0, ig);
-          tmem_ld32(tm + lane_base + 2 * 64 + hh * 32, v);           // g
+          tmem_ld16(tm + lane_base + 2 * 64 + hh * UT, v);           // g
           tmem_ld_wait();
 #pragma unroll
-          for (int j = 0; j < 32; ++j) hout[j] = tanh_(__uint_as_float(v[j]) + bb[128 + j]);
+          for (int j = 0; j < UT; ++j) hout[j] = tanh_(__uint_as_float(v[j]) + bb[128 + j]);
           put(2, hout);
 #pragma unroll
-          for (int j = 0; j < 32; ++j) ig[j] *= hout[j];
-          tmem_ld32(tm + lane_base + 1 * 64 + hh * 32, v);           // f
+          for (int j = 0; j < UT; ++j) ig[j] *= hout[j];
+          tmem_ld16(tm + lane_base + 1 * 64 + hh * UT, v);           // f
           tmem_ld_wait();
 #pragma unroll
-          for (int j = 0; j < 32; ++j) hout[j] = sigm(__uint_as_float(v[j]) + bb[64 + j]);
+          for (int j = 0; j < UT; ++j) hout[j] = sigm(__uint_as_float(v[j]) + bb[64 + j]);
           put(1, hout);
 #pragma unroll
-          for (int j = 0; j < 32; ++j) c_state[j] = fmaf(hout[j], c_state[j], ig[j]);
+          for (int j = 0; j < UT; ++j) c_state[j] = fmaf(hout[j], c_state[j], ig[j]);
           put(4, c_state);
-          tmem_ld32(tm + lane_base + 3 * 64 + hh * 32, v);           // o
+          tmem_ld16(tm + lane_base + 3 * 64 + hh * UT, v);           // o
           tmem_ld_wait();
           fence_before();
 #pragma unroll
-          for (int j = 0; j < 32; ++j) ig[j] = sigm(__uint_as_float(v[j]) + bb[192 + j]);
+          for (int j = 0; j < UT; ++j) ig[j] = sigm(__uint_as_float(v[j]) + bb[192 + j]);
           put(3, ig);
 #pragma unroll
-          for (int j = 0; j < 32; ++j) hout[j] = ig[j] * tanh_(c_state[j]);
+          for (int j = 0; j < UT; ++j) hout[j] = ig[j] * tanh_(c_state[j]);
           put(5, hout);
           // the peer's MMA of this step has completed (waited every round so that no phase is ever skipped)
           ok = mbar_wait_cluster(&bars[B_PZ], q & 1) && ok;
           if (t + 1 < T) {
             // h_t -> recurrent part of both A tiles (fp16), then the next step's input part
 #pragma unroll
-            for (int c8 = 0; c8 < 4; ++c8) {
+            for (int c8 = 0; c8 < UT / 8; ++c8) {
               const uint4 o = make_uint4(pack_half2(hout[c8 * 8], hout[c8 * 8 + 1]), pack_half2(hout[c8 * 8 + 2], hout[c8 * 8 + 3]),
                                          pack_half2(hout[c8 * 8 + 4], hout[c8 * 8 + 5]), pack_half2(hout[c8 * 8 + 6], hout[c8 * 8 + 7]));
-              const uint32_t off = tile_chunk_off(TS, row, xw + UH * rank + hh * 32 + c8 * 8);
+              const uint32_t off = tile_chunk_off(TS, row, xw + UH * rank + hh * UT + c8 * 8);
               sts128(sA + off, o);
               st_cluster_v4(peerA + off, o);
             }

@@ -215,6 +215,9 @@ __device__ __forceinline__ bool mbar_wait_cluster(uint64_t* bar, uint32_t parity
   return false;
 }
 
+// bring the 128-byte line at p into L2 (no register, no wait): the recurrences touch each stash line once, a round ahead
+__device__ __forceinline__ void prefetch_l2(const void* p) { asm volatile("prefetch.global.L2 [%0];" ::"l"(p)); }
+
 // packed fp16 helpers for the epilogues (one instruction per two elements)
 __device__ __forceinline__ uint32_t relu_h2(uint32_t a) {
   uint32_t r;

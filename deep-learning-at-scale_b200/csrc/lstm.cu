@@ -282,14 +282,15 @@ Ws carve_ws(const LstmDesc& d, size_t n_seq, void* base) {
   Ws w;
   size_t o = 0;
   auto take = [&](size_t n) { float* p = base ? (float*)base + o : nullptr; o += (n + 63) & ~(size_t)63; return p; };
-  w.stash = take(n_seq * d.L * d.T * 6 * (size_t)d.H);
+  const size_t n_pad = (n_seq + 31) & ~(size_t)31;       // the tensor-core kernels' stash layout blocks sequences by 32
+  w.stash = take(n_pad * d.L * d.T * 6 * (size_t)d.H);
   w.dseq = take(d.L > 1 ? n_seq * d.T * (size_t)d.H : 0);
   w.KT = take(d.n_params);
   w.partials = take((size_t)sm_count() * pstride(d.n_params));
   w.yhat = take(n_seq);
   w.tcp = take(lstm_tc_supported(d) ? lstm_tc_dw_partial_floats(d) : 0);      // tensor-core weight-gradient partials
   // tensor-core BPTT: the two CTAs of a pair write partial dx of a layer into separate buffers (x 2 sets from 3 layers up)
-  w.dseqP = take(lstm_tc_supported(d) && d.L > 1 ? (size_t)(d.L >= 3 ? 4 : 2) * n_seq * d.T * (size_t)d.H : 0);
+  w.dseqP = take(lstm_tc_supported(d) && d.L > 1 ? (size_t)(d.L >= 3 ? 4 : 2) * n_pad * d.T * (size_t)d.H : 0);
   w.status = reinterpret_cast<unsigned*>(take(64));                              // status words of the tensor-core kernels
   w.bytes = o * sizeof(float);
   return w;
@@ -353,6 +354,7 @@ extern "C" int dlas_lstm_predict_mode(int mode, int d_in, int hidden, int n_laye
   int bits = 0;
   rc = stage_bits(mode, d, "dlas_lstm_predict_mode", &bits);
   if (rc != DLAS_OK) return rc;
+  if (bits & TC_FWD) { d.fast = 1; d.n_pad = (n_seq + 31) & ~(size_t)31; }   // only tensor-core kernels touch the stash here
   if (n_seq == 0) return DLAS_OK;
   DLAS_REQUIRE(params && X && yhat, "dlas_lstm_predict: null pointer");
   Ws w = carve_ws(d, n_seq, workspace);
@@ -393,6 +395,8 @@ extern "C" int dlas_lstm_grad_mode(int mode, int d_in, int hidden, int n_layers,
   int bits = 0;
   rc = stage_bits(mode, d, "dlas_lstm_grad_mode", &bits);
   if (rc != DLAS_OK) return rc;
+  // every stage on the tensor cores: the stash may use their own (coalesced) layout; a mix keeps the fp32 kernels' layout
+  if ((bits & (TC_FWD | TC_BWD | TC_DW)) == (TC_FWD | TC_BWD | TC_DW)) { d.fast = 1; d.n_pad = (n_seq + 31) & ~(size_t)31; }
   DLAS_REQUIRE(loss == DLAS_LOSS_MSE || loss == DLAS_LOSS_MAE_CLIP, "dlas_lstm_grad: unknown loss %d", loss);
   DLAS_REQUIRE(params && grad_sum && (n_seq == 0 || (X && y)), "dlas_lstm_grad: null pointer");
   cudaStream_t st = (cudaStream_t)stream;

@@ -12,6 +12,8 @@ struct LstmDesc {
   int d_in, H, L, T;
   int k_off[MAXL], b_off[MAXL], d_l[MAXL];
   int hw_off, hb_off, n_params;
+  int fast;            // stash layout: 0 = [seq][l][t][comp][H] (the fp32 kernels'), 1 = the tensor-core kernels' own (below)
+  size_t n_pad;        // sequences rounded up to 32 (fast layout)
 };
 
 inline int make_desc(int d_in, int H, int L, int T, LstmDesc& d) {
@@ -19,6 +21,7 @@ inline int make_desc(int d_in, int H, int L, int T, LstmDesc& d) {
   DLAS_REQUIRE(H >= 1 && H <= 128 && d_in >= 1 && d_in <= 128, "lstm: hidden %d / d_in %d not in 1..128", H, d_in);
   DLAS_REQUIRE(T >= 1, "lstm: T %d < 1", T);
   d.d_in = d_in; d.H = H; d.L = L; d.T = T;
+  d.fast = 0; d.n_pad = 0;
   int o = 0, dl = d_in;
   for (int l = 0; l < L; ++l) {
     d.k_off[l] = o; o += (dl + H) * 4 * H;
@@ -38,6 +41,21 @@ __device__ __forceinline__ size_t stash_idx(const LstmDesc& d, size_t seq, int l
   return ((((seq * d.L + l) * d.T + t) * 6) + comp) * (size_t)d.H;
 }
 
+// Stash access of the tensor-core kernels.  Their epilogue threads own one sequence (TMEM lane) and 16 consecutive units; in
+// the fp32 layout a warp's 16-byte accesses would touch 32 different lines.  The fast layout (used when every stage of the
+// step runs on the tensor cores) is [l][t][comp][16-unit group][sequence block of 32][4 x float4][32 sequences][4]: the
+// warp's lanes then read / write 512 contiguous bytes per instruction.  `unit` is a multiple of 4 for the float4 form.
+__device__ __forceinline__ size_t sidx(const LstmDesc& d, size_t seq, int l, int t, int comp, int unit) {
+  if (!d.fast) return stash_idx(d, seq, l, t, comp) + unit;
+  const size_t slab = ((((size_t)l * d.T + t) * 6 + comp) * (d.H >> 4) + (unit >> 4)) * (d.n_pad * 16);
+  return slab + (((seq >> 5) * 4 + ((unit >> 2) & 3)) * 32 + (seq & 31)) * 4 + (unit & 3);
+}
+// partial dx of a layer ([rank-partial][sequence][t][unit] in the fp32-compatible form): same idea
+__device__ __forceinline__ size_t didx(const LstmDesc& d, size_t seq, int t, int unit) {
+  if (!d.fast) return (seq * d.T + t) * (size_t)d.H + unit;
+  const size_t slab = ((size_t)t * (d.H >> 4) + (unit >> 4)) * (d.n_pad * 16);
+  return slab + (((seq >> 5) * 4 + ((unit >> 2) & 3)) * 32 + (seq & 31)) * 4 + (unit & 3);
+}
 
 }  // namespace lstm
 }  // namespace dlas

@@ -47,7 +47,10 @@ lstm_dw_tc_kernel(const LstmDesc d, const float* __restrict__ X, const float* __
   const int jc = blockIdx.x & 3, slice = blockIdx.x >> 2, n_slices = gridDim.x >> 2;
   const int T = d.T;
   const size_t n_rows = n_seq * (size_t)T;
-  const size_t n_chunks = (n_rows + CH - 1) / CH;
+  // chunk = 128 rows of the long K dimension.  fp32-compatible stash: consecutive (sequence, t) rows; fast layout: 128
+  // consecutive sequences at one t (the order of the rows does not matter to the sum, only to the memory pattern)
+  const size_t n_blk = (n_seq + CH - 1) / CH;
+  const size_t n_chunks = d.fast ? n_blk * (size_t)T : (n_rows + CH - 1) / CH;
   const int my_chunks = (n_chunks > (size_t)slice) ? (int)((n_chunks - slice + n_slices - 1) / n_slices) : 0;
   bool ok = (sbase & 1023u) == 0;
   if (tid == 0) {
@@ -92,22 +95,34 @@ lstm_dw_tc_kernel(const LstmDesc d, const float* __restrict__ X, const float* __
     } else {
       // ---- loaders: two threads per row; half 0 = the input part of [x | h_prev] and dz columns 0..63, half 1 = h_prev
       // and dz columns 64..127.  fp32 from the stash / X -> fp16 chunks of the swizzled tiles.
-      const int r = tid >> 1, half = tid & 1;
+      const int r = tid & 127, half = tid >> 7;     // a warp = 32 consecutive rows of one half: coalesced in the fast layout
       uint32_t u = use;
       for (int c = 0; c < my_chunks; ++c, ++u) {
         const int b = u & 1;
-        const size_t row = ((size_t)slice + (size_t)c * n_slices) * CH + r;
-        const bool in = row < n_rows;
-        const size_t seq = in ? row / T : 0;
-        const int t = in ? (int)(row - seq * T) : 0;
+        const size_t ci = (size_t)slice + (size_t)c * n_slices;
+        size_t seq; int t; bool in;
+        if (d.fast) {
+          t = (int)(ci % T);
+          seq = (ci / T) * CH + r;
+          in = seq < n_seq;
+        } else {
+          const size_t row_ = ci * CH + r;
+          in = row_ < n_rows;
+          seq = in ? row_ / T : 0;
+          t = in ? (int)(row_ - seq * T) : 0;
+        }
+        if (!in) { seq = 0; t = 0; }
+        const size_t row = seq * T + t;               // row of X
         if (u >= 2) ok = mbar_wait(&bars[B_FREE0 + b], ((u >> 1) - 1) & 1) && ok;   // the MMAs of use u-2 have read this buffer
         const uint32_t tDZ = sDZ + b * 32768, tA = sA + b * 65536;
         {  // dz: 64 floats of gate jc
-          const float* src = stash + stash_idx(d, seq, l, t, jc) + half * 64;
 #pragma unroll 4
           for (int q = 0; q < 8; ++q) {
             float4 a = make_float4(0.f, 0.f, 0.f, 0.f), e = a;
-            if (in) { a = __ldcs(reinterpret_cast<const float4*>(src + q * 8)); e = __ldcs(reinterpret_cast<const float4*>(src + q * 8 + 4)); }
+            if (in) {
+              a = __ldcs(reinterpret_cast<const float4*>(stash + sidx(d, seq, l, t, jc, half * 64 + q * 8)));
+              e = __ldcs(reinterpret_cast<const float4*>(stash + sidx(d, seq, l, t, jc, half * 64 + q * 8 + 4)));
+            }
             sts128(tDZ + tile_chunk_off(CH, r, half * 64 + q * 8),
                    make_uint4(pack_half2(a.x, a.y), pack_half2(a.z, a.w), pack_half2(e.x, e.y), pack_half2(e.z, e.w)));
           }
@@ -121,12 +136,15 @@ lstm_dw_tc_kernel(const LstmDesc d, const float* __restrict__ X, const float* __
         } else {
           // half 0 (l > 0): h of the layer below at t -> columns 0..127; half 1: h_{t-1} of this layer -> columns xw..xw+127
           const bool have = in && (half == 0 || t > 0);
-          const float* src = (half == 0) ? stash + stash_idx(d, seq, l - 1, t, 5) : stash + stash_idx(d, seq, l, t > 0 ? t - 1 : 0, 5);
+          const int sl = (half == 0) ? l - 1 : l, stt = (half == 0) ? t : (t > 0 ? t - 1 : 0);
           const int c0 = (half == 0) ? 0 : xw;
 #pragma unroll 4
           for (int q = 0; q < 16; ++q) {
             float4 a = make_float4(0.f, 0.f, 0.f, 0.f), e = a;
-            if (have) { a = __ldg(reinterpret_cast<const float4*>(src + q * 8)); e = __ldg(reinterpret_cast<const float4*>(src + q * 8 + 4)); }
+            if (have) {
+              a = __ldg(reinterpret_cast<const float4*>(stash + sidx(d, seq, sl, stt, 5, q * 8)));
+              e = __ldg(reinterpret_cast<const float4*>(stash + sidx(d, seq, sl, stt, 5, q * 8 + 4)));
+            }
             sts128(tA + tile_chunk_off(CH, r, c0 + q * 8),
                    make_uint4(pack_half2(a.x, a.y), pack_half2(a.z, a.w), pack_half2(e.x, e.y), pack_half2(e.z, e.w)));
           }

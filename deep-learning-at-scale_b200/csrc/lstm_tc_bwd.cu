@@ -50,7 +50,7 @@ lstm_head_grad_kernel(const LstmDesc d, const int loss, const float* __restrict_
     float g, lo;
     if (loss == DLAS_LOSS_MSE) { lo = dd * dd; g = 2.0f * dd; }
     else { const float a = fabsf(dd); lo = fminf(a, 6.0f); g = (a <= 6.0f) ? (dd > 0.0f ? 1.0f : (dd < 0.0f ? -1.0f : 0.0f)) : 0.0f; }
-    if (u < d.H) acc += stash[stash_idx(d, s, d.L - 1, d.T - 1, 5) + u] * g;
+    if (u < d.H) acc += stash[sidx(d, s, d.L - 1, d.T - 1, 5, u)] * g;
     else if (u == d.H) acc += g;
     else if (u == d.H + 1) acc += lo;
     __syncthreads();                    // every thread has read yhat[s] before it becomes dy[s]
@@ -74,7 +74,7 @@ lstm_bwd_tc_kernel(const LstmDesc d, const float* __restrict__ params, float* __
   const int pair = blockIdx.x >> 1, n_pairs = gridDim.x >> 1;
   const int T = d.T;
   const size_t n_tiles = (n_seq + TS - 1) / TS;
-  const size_t pstr = n_seq * (size_t)T * HT;            // floats per partial dseq buffer
+  const size_t pstr = (d.fast ? d.n_pad : n_seq) * (size_t)T * HT;   // floats per partial dseq buffer
   // dseqP: [set][CTA rank][sequence][t][unit].  A layer writes the set of its own parity and reads the other one, so a middle
   // layer (3 layers and more) never overwrites a partial its peer may still be reading; up to 2 layers use one set.
   const int n_sets = d.L >= 3 ? 2 : 1;
@@ -148,11 +148,10 @@ lstm_bwd_tc_kernel(const LstmDesc d, const float* __restrict__ params, float* __
         for (int t = T - 1; t >= 0; --t, ++q) {
           const bool first = (t == T - 1);
           if (valid && t > 0) {   // step t-1's stash lines (and the layer above's dx): into L2 a round ahead
-            const float* nx = stash + stash_idx(d, sq, l, t - 1, 0) + u0;
 #pragma unroll
-            for (int c = 0; c < 5; ++c) prefetch_l2(nx + c * HT);
-            if (t > 1) prefetch_l2(stash + stash_idx(d, sq, l, t - 2, 4) + u0);
-            if (l < d.L - 1) { prefetch_l2(dsR + (sq * T + t - 1) * (size_t)HT + u0); prefetch_l2(dsR + pstr + (sq * T + t - 1) * (size_t)HT + u0); }
+            for (int c = 0; c < 5; ++c) prefetch_l2(stash + sidx(d, sq, l, t - 1, c, u0));
+            if (t > 1) prefetch_l2(stash + sidx(d, sq, l, t - 2, 4, u0));
+            if (l < d.L - 1) { prefetch_l2(dsR + didx(d, sq, t - 1, u0)); prefetch_l2(dsR + pstr + didx(d, sq, t - 1, u0)); }
           }
           // ---- what the previous round's MMA (step t+1) produced: dx partial, my units' dh partial, the peer's units'
           if (!first) {
@@ -160,14 +159,14 @@ lstm_bwd_tc_kernel(const LstmDesc d, const float* __restrict__ params, float* __
             fence_after();
             uint32_t v[32];
             if (l > 0) {   // (warp-uniform: tcgen05.ld is warp-collective; only the stores depend on the row being valid)
-              float* dst = dsW + (size_t)rank * pstr + (sq * T + (t + 1)) * (size_t)HT + hh * 32;
+              float* dst = dsW + (size_t)rank * pstr;
 #pragma unroll
               for (int c = 0; c < 1; ++c) {
                 tmem_ld32(tm + lane_base + hh * 32 + c * 32, v);
                 tmem_ld_wait();
 #pragma unroll
                 for (int j4 = 0; j4 < 8; ++j4)
-                  if (valid) *reinterpret_cast<float4*>(dst + c * 32 + j4 * 4) = make_float4(__uint_as_float(v[j4 * 4]), __uint_as_float(v[j4 * 4 + 1]),
+                  if (valid) *reinterpret_cast<float4*>(dst + didx(d, sq, t + 1, hh * 32 + j4 * 4)) = make_float4(__uint_as_float(v[j4 * 4]), __uint_as_float(v[j4 * 4 + 1]),
                                                                                  __uint_as_float(v[j4 * 4 + 2]), __uint_as_float(v[j4 * 4 + 3]));
               }
             }
@@ -200,11 +199,9 @@ lstm_bwd_tc_kernel(const LstmDesc d, const float* __restrict__ params, float* __
           __syncwarp();
           if (lane == 0) mbar_arrive_remote(peer_RFREE);
           // ---- gate gradients of step t for this row's 16 units, 8 units at a time ----
-          const float* st = stash + stash_idx(d, sq, l, t, 0) + u0;
-          float* stw = stash + stash_idx(d, sq, l, t, 0) + u0;
-          const float* cp = stash + stash_idx(d, sq, l, t > 0 ? t - 1 : 0, 4) + u0;
+
           const float dyr = (l == d.L - 1 && first && valid) ? __ldg(dy + sq) : 0.f;
-          const float* din0 = dsR + (sq * T + t) * (size_t)HT + u0;              // dx partials of the layer above (both CTAs')
+
 #pragma unroll
           for (int b8 = 0; b8 < UT / 8; ++b8) {
             float gi[8], gf[8], gg[8], go[8], cc[8], cpv[8], dhv[8];
@@ -213,15 +210,15 @@ lstm_bwd_tc_kernel(const LstmDesc d, const float* __restrict__ params, float* __
               const int o = b8 * 8 + h4 * 4;
               float4 a = make_float4(0.f, 0.f, 0.f, 0.f), f4 = a, g4 = a, o4 = a, c4 = a, p4 = a, d4 = a;
               if (valid) {
-                a = __ldg(reinterpret_cast<const float4*>(st + o));
-                f4 = __ldg(reinterpret_cast<const float4*>(st + HT + o));
-                g4 = __ldg(reinterpret_cast<const float4*>(st + 2 * HT + o));
-                o4 = __ldg(reinterpret_cast<const float4*>(st + 3 * HT + o));
-                c4 = __ldg(reinterpret_cast<const float4*>(st + 4 * HT + o));
-                if (t > 0) p4 = __ldg(reinterpret_cast<const float4*>(cp + o));
+                a = __ldg(reinterpret_cast<const float4*>(stash + sidx(d, sq, l, t, 0, u0 + o)));
+                f4 = __ldg(reinterpret_cast<const float4*>(stash + sidx(d, sq, l, t, 1, u0 + o)));
+                g4 = __ldg(reinterpret_cast<const float4*>(stash + sidx(d, sq, l, t, 2, u0 + o)));
+                o4 = __ldg(reinterpret_cast<const float4*>(stash + sidx(d, sq, l, t, 3, u0 + o)));
+                c4 = __ldg(reinterpret_cast<const float4*>(stash + sidx(d, sq, l, t, 4, u0 + o)));
+                if (t > 0) p4 = __ldg(reinterpret_cast<const float4*>(stash + sidx(d, sq, l, t - 1, 4, u0 + o)));
                 if (l < d.L - 1) {
-                  const float4 d0 = __ldcg(reinterpret_cast<const float4*>(din0 + o));
-                  const float4 d1 = __ldcg(reinterpret_cast<const float4*>(din0 + pstr + o));
+                  const float4 d0 = __ldcg(reinterpret_cast<const float4*>(dsR + didx(d, sq, t, u0 + o)));
+                  const float4 d1 = __ldcg(reinterpret_cast<const float4*>(dsR + pstr + didx(d, sq, t, u0 + o)));
                   d4 = make_float4(d0.x + d1.x, d0.y + d1.y, d0.z + d1.z, d0.w + d1.w);
                 } else if (first) {
                   const float4 w4 = __ldg(reinterpret_cast<const float4*>(hw + o));
@@ -254,10 +251,10 @@ lstm_bwd_tc_kernel(const LstmDesc d, const float* __restrict__ params, float* __
 #pragma unroll
               for (int h4 = 0; h4 < 2; ++h4) {
                 const int o = b8 * 8 + h4 * 4, e = h4 * 4;
-                *reinterpret_cast<float4*>(stw + o) = make_float4(zi[e], zi[e + 1], zi[e + 2], zi[e + 3]);
-                *reinterpret_cast<float4*>(stw + HT + o) = make_float4(zf[e], zf[e + 1], zf[e + 2], zf[e + 3]);
-                *reinterpret_cast<float4*>(stw + 2 * HT + o) = make_float4(zg[e], zg[e + 1], zg[e + 2], zg[e + 3]);
-                *reinterpret_cast<float4*>(stw + 3 * HT + o) = make_float4(zo[e], zo[e + 1], zo[e + 2], zo[e + 3]);
+                *reinterpret_cast<float4*>(stash + sidx(d, sq, l, t, 0, u0 + o)) = make_float4(zi[e], zi[e + 1], zi[e + 2], zi[e + 3]);
+                *reinterpret_cast<float4*>(stash + sidx(d, sq, l, t, 1, u0 + o)) = make_float4(zf[e], zf[e + 1], zf[e + 2], zf[e + 3]);
+                *reinterpret_cast<float4*>(stash + sidx(d, sq, l, t, 2, u0 + o)) = make_float4(zg[e], zg[e + 1], zg[e + 2], zg[e + 3]);
+                *reinterpret_cast<float4*>(stash + sidx(d, sq, l, t, 3, u0 + o)) = make_float4(zo[e], zo[e + 1], zo[e + 2], zo[e + 3]);
               }
             }
             // fp16 A tile of the next MMA: column g*64 + (unit within this CTA)
@@ -276,14 +273,14 @@ lstm_bwd_tc_kernel(const LstmDesc d, const float* __restrict__ params, float* __
         fence_after();
         if (l > 0) {
           uint32_t v[32];
-          float* dst = dsW + (size_t)rank * pstr + (sq * T + 0) * (size_t)HT + hh * 32;
+          float* dst = dsW + (size_t)rank * pstr;
 #pragma unroll
           for (int c = 0; c < 1; ++c) {
             tmem_ld32(tm + lane_base + hh * 32 + c * 32, v);
             tmem_ld_wait();
 #pragma unroll
             for (int j4 = 0; j4 < 8; ++j4)
-              if (valid) *reinterpret_cast<float4*>(dst + c * 32 + j4 * 4) = make_float4(__uint_as_float(v[j4 * 4]), __uint_as_float(v[j4 * 4 + 1]),
+              if (valid) *reinterpret_cast<float4*>(dst + didx(d, sq, 0, hh * 32 + j4 * 4)) = make_float4(__uint_as_float(v[j4 * 4]), __uint_as_float(v[j4 * 4 + 1]),
                                                                              __uint_as_float(v[j4 * 4 + 2]), __uint_as_float(v[j4 * 4 + 3]));
           }
         }

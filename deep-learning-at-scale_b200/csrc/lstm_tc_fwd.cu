@@ -101,11 +101,13 @@ lstm_fwd_tc_kernel(const LstmDesc d, const float* __restrict__ params, const flo
             sts128(sA + tile_chunk_off(TS, row, 8), make_uint4(pack_half2(xv[8], xv[9]), pack_half2(xv[10], xv[11]), pack_half2(xv[12], xv[13]), pack_half2(xv[14], xv[15])));
           }
         } else {
-          const float* src = stash + stash_idx(d, valid ? seq : 0, l - 1, t, 5) + hh * 32;
 #pragma unroll
           for (int c8 = 0; c8 < 4; ++c8) {
             float4 a = make_float4(0.f, 0.f, 0.f, 0.f), e = a;
-            if (valid) { a = __ldcg(reinterpret_cast<const float4*>(src + c8 * 8)); e = __ldcg(reinterpret_cast<const float4*>(src + c8 * 8 + 4)); }
+            if (valid) {
+              a = __ldcg(reinterpret_cast<const float4*>(stash + sidx(d, seq, l - 1, t, 5, hh * 32 + c8 * 8)));
+              e = __ldcg(reinterpret_cast<const float4*>(stash + sidx(d, seq, l - 1, t, 5, hh * 32 + c8 * 8 + 4)));
+            }
             sts128(sA + tile_chunk_off(TS, row, hh * 32 + c8 * 8), make_uint4(pack_half2(a.x, a.y), pack_half2(a.z, a.w), pack_half2(e.x, e.y), pack_half2(e.z, e.w)));
           }
         }
@@ -147,18 +149,21 @@ lstm_fwd_tc_kernel(const LstmDesc d, const float* __restrict__ params, const flo
         // =========================== epilogue warps ===========================
         for (int t = 0; t < T; ++t, ++q) {
           // the layer below's h two steps ahead: into L2 now, read at the end of the next round
-          if (l > 0 && valid && t + 2 < T) prefetch_l2(stash + stash_idx(d, seq, l - 1, t + 2, 5) + hh * 32);
+          if (l > 0 && valid && t + 2 < T) {
+            prefetch_l2(stash + sidx(d, seq, l - 1, t + 2, 5, hh * 32));
+            if (d.fast) prefetch_l2(stash + sidx(d, seq, l - 1, t + 2, 5, hh * 32 + 16));
+          }
           ok = mbar_wait(&bars[B_Z], q & 1) && ok;
           fence_after();
           // gates of this row's 16 units: columns g*64 + hh*16 + j of the accumulator
           uint32_t v[UT];
           float ig[UT], hout[UT];
-          float* st_base = stash + stash_idx(d, valid ? seq : 0, l, t, 0) + UH * rank + hh * UT;
+          const int ub = UH * (int)rank + hh * UT;
           auto put = [&](int comp, const float (&a)[UT]) {
             if (valid) {
 #pragma unroll
               for (int j4 = 0; j4 < UT / 4; ++j4)
-                *reinterpret_cast<float4*>(st_base + (size_t)comp * HT + j4 * 4) = make_float4(a[j4 * 4], a[j4 * 4 + 1], a[j4 * 4 + 2], a[j4 * 4 + 3]);
+                *reinterpret_cast<float4*>(stash + sidx(d, seq, l, t, comp, ub + j4 * 4)) = make_float4(a[j4 * 4], a[j4 * 4 + 1], a[j4 * 4 + 2], a[j4 * 4 + 3]);
             }
           };
           const float* bb = bias + hh * UT;
@@ -231,9 +236,8 @@ lstm_head_kernel(const LstmDesc d, const float* __restrict__ params, const float
   const size_t s = (size_t)blockIdx.x * 8 + (threadIdx.x >> 5);
   const int lane = threadIdx.x & 31;
   if (s >= n_seq) return;
-  const float* h = stash + stash_idx(d, s, d.L - 1, d.T - 1, 5);
   float a = 0.f;
-  for (int u = lane; u < d.H; u += 32) a += h[u] * __ldg(params + d.hw_off + u);
+  for (int u = lane; u < d.H; u += 32) a += stash[sidx(d, s, d.L - 1, d.T - 1, 5, u)] * __ldg(params + d.hw_off + u);
 #pragma unroll
   for (int o = 16; o > 0; o >>= 1) a += __shfl_down_sync(0xffffffffu, a, o);
   if (lane == 0) yhat[s] = (err_flag && *err_flag == call_id) ? __int_as_float(0x7fc00000) : a + __ldg(params + d.hb_off);

@@ -133,3 +133,22 @@ def test_backward_recurrence_stage_vs_fp32(dl, shape, loss):
     assert max(errs.values()) < (5e-3 if B * T >= 1000 else 3e-2)
     again = _grad(0x100 | TC_BWD, d, h, nl, T, loss, p, X, yy)
     assert np.array_equal(got, again)
+
+
+@pytest.mark.parametrize("shape", [(8, 128, 2, 48, 300), (16, 128, 3, 6, 77), (3, 128, 1, 9, 1), (8, 128, 2, 4, 9472 + 128 + 45)])
+def test_whole_mode_on_ragged_batches_vs_fp32(dl, shape):
+    """DLAS_MODE_TC end to end (all three stages, the tensor-core kernels' own stash layout) against the fp32 path on
+    batches that are no multiple of the 128-sequence tile / the 32-sequence layout block."""
+    from dlas import ops
+    d, h, nl, T, B = shape
+    p, X, y = _setup(d, h, nl, T, B, B + 3)
+    ref = _grad(dl.MODE_FP32, d, h, nl, T, 0, p, X, y)
+    got = _grad(dl.MODE_TC, d, h, nl, T, 0, p, X, y)
+    errs = _blocks(d, h, nl, got[:-1], ref[:-1].astype(np.float64))
+    print(shape, errs)
+    assert got[-1] == pytest.approx(ref[-1], rel=2e-3)
+    assert max(errs.values()) < (1e-2 if B * T >= 1000 else 5e-2)
+    ws = ops.lstm_workspace(d, h, nl, T, B)
+    y32 = ops.lstm_predict(d, h, nl, T, _cuda(p), _cuda(X), ws).cpu().numpy()
+    ytc = ops.lstm_predict(d, h, nl, T, _cuda(p), _cuda(X), ws, mode=dl.MODE_TC).cpu().numpy()
+    assert np.abs(ytc - y32).max() < 2e-3 * max(1.0, np.abs(y32).max())

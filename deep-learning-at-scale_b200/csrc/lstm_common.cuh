@@ -45,6 +45,25 @@ __device__ __forceinline__ size_t stash_idx(const LstmDesc& d, size_t seq, int l
 // the fp32 layout a warp's 16-byte accesses would touch 32 different lines.  The fast layout (used when every stage of the
 // step runs on the tensor cores) is [l][t][comp][16-unit group][sequence block of 32][4 x float4][32 sequences][4]: the
 // warp's lanes then read / write 512 contiguous bytes per instruction.  `unit` is a multiple of 4 for the float4 form.
+struct StashPos {     // the per-sequence part of a fast-layout address, computed once per thread and tile / chunk
+  size_t inner, ugs;
+};
+__device__ __forceinline__ StashPos stash_pos(const LstmDesc& d, size_t seq) {
+  StashPos p;
+  p.inner = (((seq >> 5) * 4) * 32 + (seq & 31)) * 4;
+  p.ugs = d.n_pad * 16;
+  return p;
+}
+template <bool FAST>
+__device__ __forceinline__ size_t sidx(const LstmDesc& d, const StashPos& p, size_t seq, int l, int t, int comp, int unit) {
+  if (!FAST) return stash_idx(d, seq, l, t, comp) + unit;
+  return (size_t)(((l * d.T + t) * 6 + comp) * (d.H >> 4) + (unit >> 4)) * p.ugs + p.inner + (size_t)((((unit >> 2) & 3) << 7) + (unit & 3));
+}
+template <bool FAST>
+__device__ __forceinline__ size_t didx(const LstmDesc& d, const StashPos& p, size_t seq, int t, int unit) {
+  if (!FAST) return (seq * d.T + t) * (size_t)d.H + unit;
+  return (size_t)(t * (d.H >> 4) + (unit >> 4)) * p.ugs + p.inner + (size_t)((((unit >> 2) & 3) << 7) + (unit & 3));
+}
 __device__ __forceinline__ size_t sidx(const LstmDesc& d, size_t seq, int l, int t, int comp, int unit) {
   if (!d.fast) return stash_idx(d, seq, l, t, comp) + unit;
   const size_t slab = ((((size_t)l * d.T + t) * 6 + comp) * (d.H >> 4) + (unit >> 4)) * (d.n_pad * 16);

@@ -34,6 +34,7 @@ constexpr uint32_t TM_ACC = 0, TM_DB = 256, TM_COLS = 512;
 constexpr int PART = 256 * 128 + 128;   // floats per (layer, CTA) partial: [k 0..255][128 gate cols] then db[128]
 }  // namespace dw
 
+template <bool FAST>
 __global__ void __launch_bounds__(dw::NT, 1)
 lstm_dw_tc_kernel(const LstmDesc d, const float* __restrict__ X, const float* __restrict__ stash, const size_t n_seq,
                   float* __restrict__ partials, unsigned* __restrict__ err_flag, const unsigned call_id) {
@@ -50,7 +51,7 @@ lstm_dw_tc_kernel(const LstmDesc d, const float* __restrict__ X, const float* __
   // chunk = 128 rows of the long K dimension.  fp32-compatible stash: consecutive (sequence, t) rows; fast layout: 128
   // consecutive sequences at one t (the order of the rows does not matter to the sum, only to the memory pattern)
   const size_t n_blk = (n_seq + CH - 1) / CH;
-  const size_t n_chunks = d.fast ? n_blk * (size_t)T : (n_rows + CH - 1) / CH;
+  const size_t n_chunks = FAST ? n_blk * (size_t)T : (n_rows + CH - 1) / CH;
   const int my_chunks = (n_chunks > (size_t)slice) ? (int)((n_chunks - slice + n_slices - 1) / n_slices) : 0;
   bool ok = (sbase & 1023u) == 0;
   if (tid == 0) {
@@ -101,7 +102,7 @@ lstm_dw_tc_kernel(const LstmDesc d, const float* __restrict__ X, const float* __
         const int b = u & 1;
         const size_t ci = (size_t)slice + (size_t)c * n_slices;
         size_t seq; int t; bool in;
-        if (d.fast) {
+        if (FAST) {
           t = (int)(ci % T);
           seq = (ci / T) * CH + r;
           in = seq < n_seq;
@@ -113,15 +114,16 @@ lstm_dw_tc_kernel(const LstmDesc d, const float* __restrict__ X, const float* __
         }
         if (!in) { seq = 0; t = 0; }
         const size_t row = seq * T + t;               // row of X
+        const StashPos sp = stash_pos(d, seq);
         if (u >= 2) ok = mbar_wait(&bars[B_FREE0 + b], ((u >> 1) - 1) & 1) && ok;   // the MMAs of use u-2 have read this buffer
         const uint32_t tDZ = sDZ + b * 32768, tA = sA + b * 65536;
         {  // dz: 64 floats of gate jc
-#pragma unroll 4
+#pragma unroll
           for (int q = 0; q < 8; ++q) {
             float4 a = make_float4(0.f, 0.f, 0.f, 0.f), e = a;
             if (in) {
-              a = __ldcs(reinterpret_cast<const float4*>(stash + sidx(d, seq, l, t, jc, half * 64 + q * 8)));
-              e = __ldcs(reinterpret_cast<const float4*>(stash + sidx(d, seq, l, t, jc, half * 64 + q * 8 + 4)));
+              a = __ldcs(reinterpret_cast<const float4*>(stash + sidx<FAST>(d, sp, seq, l, t, jc, half * 64 + q * 8)));
+              e = __ldcs(reinterpret_cast<const float4*>(stash + sidx<FAST>(d, sp, seq, l, t, jc, half * 64 + q * 8 + 4)));
             }
             sts128(tDZ + tile_chunk_off(CH, r, half * 64 + q * 8),
                    make_uint4(pack_half2(a.x, a.y), pack_half2(a.z, a.w), pack_half2(e.x, e.y), pack_half2(e.z, e.w)));
@@ -138,12 +140,12 @@ lstm_dw_tc_kernel(const LstmDesc d, const float* __restrict__ X, const float* __
           const bool have = in && (half == 0 || t > 0);
           const int sl = (half == 0) ? l - 1 : l, stt = (half == 0) ? t : (t > 0 ? t - 1 : 0);
           const int c0 = (half == 0) ? 0 : xw;
-#pragma unroll 4
+#pragma unroll
           for (int q = 0; q < 16; ++q) {
             float4 a = make_float4(0.f, 0.f, 0.f, 0.f), e = a;
             if (have) {
-              a = __ldg(reinterpret_cast<const float4*>(stash + sidx(d, seq, sl, stt, 5, q * 8)));
-              e = __ldg(reinterpret_cast<const float4*>(stash + sidx(d, seq, sl, stt, 5, q * 8 + 4)));
+              a = __ldg(reinterpret_cast<const float4*>(stash + sidx<FAST>(d, sp, seq, sl, stt, 5, q * 8)));
+              e = __ldg(reinterpret_cast<const float4*>(stash + sidx<FAST>(d, sp, seq, sl, stt, 5, q * 8 + 4)));
             }
             sts128(tA + tile_chunk_off(CH, r, c0 + q * 8),
                    make_uint4(pack_half2(a.x, a.y), pack_half2(a.z, a.w), pack_half2(e.x, e.y), pack_half2(e.z, e.w)));
@@ -228,12 +230,14 @@ int lstm_tc_dw(const lstm::LstmDesc& d, const float* X, const float* stash, size
   int dev = 0;
   DLAS_CUDA(cudaGetDevice(&dev));
   if (dev < 0 || dev >= 64 || !attr_set[dev]) {
-    DLAS_CUDA(cudaFuncSetAttribute(lstm_dw_tc_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)dw::SMEM_BYTES));
+    DLAS_CUDA(cudaFuncSetAttribute(lstm_dw_tc_kernel<false>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)dw::SMEM_BYTES));
+    DLAS_CUDA(cudaFuncSetAttribute(lstm_dw_tc_kernel<true>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)dw::SMEM_BYTES));
     if (dev >= 0 && dev < 64) attr_set[dev] = true;
   }
   ++g_lstm_call_id;
   const int grid = lstm_tc_ctas();
-  lstm_dw_tc_kernel<<<grid, dw::NT, dw::SMEM_BYTES, st>>>(d, X, stash, n_seq, tc_partials, err_flag, g_lstm_call_id);
+  if (d.fast) lstm_dw_tc_kernel<true><<<grid, dw::NT, dw::SMEM_BYTES, st>>>(d, X, stash, n_seq, tc_partials, err_flag, g_lstm_call_id);
+  else lstm_dw_tc_kernel<false><<<grid, dw::NT, dw::SMEM_BYTES, st>>>(d, X, stash, n_seq, tc_partials, err_flag, g_lstm_call_id);
   DLAS_LAUNCH_CHECK();
   const int max_rows = 2 * HT + 1;
   dim3 rg((unsigned)((max_rows * 4 * HT + 255) / 256), (unsigned)d.L);

@@ -61,6 +61,7 @@ lstm_head_grad_kernel(const LstmDesc d, const int loss, const float* __restrict_
   else if (u == d.H + 1) my[d.n_params] = acc;
 }
 
+template <bool FAST>
 __global__ void __cluster_dims__(2, 1, 1) __launch_bounds__(NT, 1)
 lstm_bwd_tc_kernel(const LstmDesc d, const float* __restrict__ params, float* __restrict__ stash, const float* __restrict__ dy,
                    float* __restrict__ dseqP, const size_t n_seq, unsigned* __restrict__ err_flag, const unsigned call_id) {
@@ -74,7 +75,7 @@ lstm_bwd_tc_kernel(const LstmDesc d, const float* __restrict__ params, float* __
   const int pair = blockIdx.x >> 1, n_pairs = gridDim.x >> 1;
   const int T = d.T;
   const size_t n_tiles = (n_seq + TS - 1) / TS;
-  const size_t pstr = (d.fast ? d.n_pad : n_seq) * (size_t)T * HT;   // floats per partial dseq buffer
+  const size_t pstr = (FAST ? d.n_pad : n_seq) * (size_t)T * HT;   // floats per partial dseq buffer
   // dseqP: [set][CTA rank][sequence][t][unit].  A layer writes the set of its own parity and reads the other one, so a middle
   // layer (3 layers and more) never overwrites a partial its peer may still be reading; up to 2 layers use one set.
   const int n_sets = d.L >= 3 ? 2 : 1;
@@ -103,6 +104,7 @@ lstm_bwd_tc_kernel(const LstmDesc d, const float* __restrict__ params, float* __
     const size_t seq = tile * TS + row;
     const bool valid = (warp < ISSUER_WARP) && seq < n_seq;
     const size_t sq = valid ? seq : 0;
+    const StashPos sp = stash_pos(d, sq);
     for (int l = d.L - 1; l >= 0; --l) {
       const int dl = d.d_l[l], xw = xw_of(l), nk = xw + HT;
       float* dsW = dseqP + (size_t)(n_sets == 2 ? (l & 1) : 0) * 2 * pstr;              // this layer's dx partials
@@ -149,9 +151,9 @@ lstm_bwd_tc_kernel(const LstmDesc d, const float* __restrict__ params, float* __
           const bool first = (t == T - 1);
           if (valid && t > 0) {   // step t-1's stash lines (and the layer above's dx): into L2 a round ahead
 #pragma unroll
-            for (int c = 0; c < 5; ++c) prefetch_l2(stash + sidx(d, sq, l, t - 1, c, u0));
-            if (t > 1) prefetch_l2(stash + sidx(d, sq, l, t - 2, 4, u0));
-            if (l < d.L - 1) { prefetch_l2(dsR + didx(d, sq, t - 1, u0)); prefetch_l2(dsR + pstr + didx(d, sq, t - 1, u0)); }
+            for (int c = 0; c < 5; ++c) prefetch_l2(stash + sidx<FAST>(d, sp, sq, l, t - 1, c, u0));
+            if (t > 1) prefetch_l2(stash + sidx<FAST>(d, sp, sq, l, t - 2, 4, u0));
+            if (l < d.L - 1) { prefetch_l2(dsR + didx<FAST>(d, sp, sq, t - 1, u0)); prefetch_l2(dsR + pstr + didx<FAST>(d, sp, sq, t - 1, u0)); }
           }
           // ---- what the previous round's MMA (step t+1) produced: dx partial, my units' dh partial, the peer's units'
           if (!first) {
@@ -166,7 +168,7 @@ lstm_bwd_tc_kernel(const LstmDesc d, const float* __restrict__ params, float* __
                 tmem_ld_wait();
 #pragma unroll
                 for (int j4 = 0; j4 < 8; ++j4)
-                  if (valid) *reinterpret_cast<float4*>(dst + didx(d, sq, t + 1, hh * 32 + j4 * 4)) = make_float4(__uint_as_float(v[j4 * 4]), __uint_as_float(v[j4 * 4 + 1]),
+                  if (valid) *reinterpret_cast<float4*>(dst + didx<FAST>(d, sp, sq, t + 1, hh * 32 + j4 * 4)) = make_float4(__uint_as_float(v[j4 * 4]), __uint_as_float(v[j4 * 4 + 1]),
                                                                                  __uint_as_float(v[j4 * 4 + 2]), __uint_as_float(v[j4 * 4 + 3]));
               }
             }
@@ -210,15 +212,15 @@ lstm_bwd_tc_kernel(const LstmDesc d, const float* __restrict__ params, float* __
               const int o = b8 * 8 + h4 * 4;
               float4 a = make_float4(0.f, 0.f, 0.f, 0.f), f4 = a, g4 = a, o4 = a, c4 = a, p4 = a, d4 = a;
               if (valid) {
-                a = __ldg(reinterpret_cast<const float4*>(stash + sidx(d, sq, l, t, 0, u0 + o)));
-                f4 = __ldg(reinterpret_cast<const float4*>(stash + sidx(d, sq, l, t, 1, u0 + o)));
-                g4 = __ldg(reinterpret_cast<const float4*>(stash + sidx(d, sq, l, t, 2, u0 + o)));
-                o4 = __ldg(reinterpret_cast<const float4*>(stash + sidx(d, sq, l, t, 3, u0 + o)));
-                c4 = __ldg(reinterpret_cast<const float4*>(stash + sidx(d, sq, l, t, 4, u0 + o)));
-                if (t > 0) p4 = __ldg(reinterpret_cast<const float4*>(stash + sidx(d, sq, l, t - 1, 4, u0 + o)));
+                a = __ldg(reinterpret_cast<const float4*>(stash + sidx<FAST>(d, sp, sq, l, t, 0, u0 + o)));
+                f4 = __ldg(reinterpret_cast<const float4*>(stash + sidx<FAST>(d, sp, sq, l, t, 1, u0 + o)));
+                g4 = __ldg(reinterpret_cast<const float4*>(stash + sidx<FAST>(d, sp, sq, l, t, 2, u0 + o)));
+                o4 = __ldg(reinterpret_cast<const float4*>(stash + sidx<FAST>(d, sp, sq, l, t, 3, u0 + o)));
+                c4 = __ldg(reinterpret_cast<const float4*>(stash + sidx<FAST>(d, sp, sq, l, t, 4, u0 + o)));
+                if (t > 0) p4 = __ldg(reinterpret_cast<const float4*>(stash + sidx<FAST>(d, sp, sq, l, t - 1, 4, u0 + o)));
                 if (l < d.L - 1) {
-                  const float4 d0 = __ldcg(reinterpret_cast<const float4*>(dsR + didx(d, sq, t, u0 + o)));
-                  const float4 d1 = __ldcg(reinterpret_cast<const float4*>(dsR + pstr + didx(d, sq, t, u0 + o)));
+                  const float4 d0 = __ldcg(reinterpret_cast<const float4*>(dsR + didx<FAST>(d, sp, sq, t, u0 + o)));
+                  const float4 d1 = __ldcg(reinterpret_cast<const float4*>(dsR + pstr + didx<FAST>(d, sp, sq, t, u0 + o)));
                   d4 = make_float4(d0.x + d1.x, d0.y + d1.y, d0.z + d1.z, d0.w + d1.w);
                 } else if (first) {
                   const float4 w4 = __ldg(reinterpret_cast<const float4*>(hw + o));
@@ -251,10 +253,10 @@ lstm_bwd_tc_kernel(const LstmDesc d, const float* __restrict__ params, float* __
 #pragma unroll
               for (int h4 = 0; h4 < 2; ++h4) {
                 const int o = b8 * 8 + h4 * 4, e = h4 * 4;
-                *reinterpret_cast<float4*>(stash + sidx(d, sq, l, t, 0, u0 + o)) = make_float4(zi[e], zi[e + 1], zi[e + 2], zi[e + 3]);
-                *reinterpret_cast<float4*>(stash + sidx(d, sq, l, t, 1, u0 + o)) = make_float4(zf[e], zf[e + 1], zf[e + 2], zf[e + 3]);
-                *reinterpret_cast<float4*>(stash + sidx(d, sq, l, t, 2, u0 + o)) = make_float4(zg[e], zg[e + 1], zg[e + 2], zg[e + 3]);
-                *reinterpret_cast<float4*>(stash + sidx(d, sq, l, t, 3, u0 + o)) = make_float4(zo[e], zo[e + 1], zo[e + 2], zo[e + 3]);
+                *reinterpret_cast<float4*>(stash + sidx<FAST>(d, sp, sq, l, t, 0, u0 + o)) = make_float4(zi[e], zi[e + 1], zi[e + 2], zi[e + 3]);
+                *reinterpret_cast<float4*>(stash + sidx<FAST>(d, sp, sq, l, t, 1, u0 + o)) = make_float4(zf[e], zf[e + 1], zf[e + 2], zf[e + 3]);
+                *reinterpret_cast<float4*>(stash + sidx<FAST>(d, sp, sq, l, t, 2, u0 + o)) = make_float4(zg[e], zg[e + 1], zg[e + 2], zg[e + 3]);
+                *reinterpret_cast<float4*>(stash + sidx<FAST>(d, sp, sq, l, t, 3, u0 + o)) = make_float4(zo[e], zo[e + 1], zo[e + 2], zo[e + 3]);
               }
             }
             // fp16 A tile of the next MMA: column g*64 + (unit within this CTA)
@@ -280,7 +282,7 @@ lstm_bwd_tc_kernel(const LstmDesc d, const float* __restrict__ params, float* __
             tmem_ld_wait();
 #pragma unroll
             for (int j4 = 0; j4 < 8; ++j4)
-              if (valid) *reinterpret_cast<float4*>(dst + didx(d, sq, 0, hh * 32 + j4 * 4)) = make_float4(__uint_as_float(v[j4 * 4]), __uint_as_float(v[j4 * 4 + 1]),
+              if (valid) *reinterpret_cast<float4*>(dst + didx<FAST>(d, sp, sq, 0, hh * 32 + j4 * 4)) = make_float4(__uint_as_float(v[j4 * 4]), __uint_as_float(v[j4 * 4 + 1]),
                                                                              __uint_as_float(v[j4 * 4 + 2]), __uint_as_float(v[j4 * 4 + 3]));
           }
         }
@@ -309,7 +311,8 @@ int lstm_tc_bwd(const lstm::LstmDesc& d, int loss, const float* params, const fl
   int dev = 0;
   DLAS_CUDA(cudaGetDevice(&dev));
   if (dev < 0 || dev >= 64 || !attr_set[dev]) {
-    DLAS_CUDA(cudaFuncSetAttribute(lstm_bwd_tc_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)SMEM_BYTES));
+    DLAS_CUDA(cudaFuncSetAttribute(lstm_bwd_tc_kernel<false>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)SMEM_BYTES));
+    DLAS_CUDA(cudaFuncSetAttribute(lstm_bwd_tc_kernel<true>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)SMEM_BYTES));
     if (dev >= 0 && dev < 64) attr_set[dev] = true;
   }
   ++g_lstm_call_id;
@@ -318,7 +321,8 @@ int lstm_tc_bwd(const lstm::LstmDesc& d, int loss, const float* params, const fl
   const size_t n_tiles = (n_seq + TS - 1) / TS;
   const int max_pairs = sm_count() / 2;
   const int pairs = (int)(n_tiles < (size_t)max_pairs ? n_tiles : (size_t)max_pairs);
-  lstm_bwd_tc_kernel<<<2 * pairs, NT, SMEM_BYTES, st>>>(d, params, stash, yhat_dy, dseqP, n_seq, err_flag, g_lstm_call_id);
+  if (d.fast) lstm_bwd_tc_kernel<true><<<2 * pairs, NT, SMEM_BYTES, st>>>(d, params, stash, yhat_dy, dseqP, n_seq, err_flag, g_lstm_call_id);
+  else lstm_bwd_tc_kernel<false><<<2 * pairs, NT, SMEM_BYTES, st>>>(d, params, stash, yhat_dy, dseqP, n_seq, err_flag, g_lstm_call_id);
   DLAS_LAUNCH_CHECK();
   return DLAS_OK;
 }

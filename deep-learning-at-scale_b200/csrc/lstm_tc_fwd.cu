@@ -32,6 +32,7 @@ constexpr uint32_t S_TMEM = S_BAR + N_BARS * 8, SMEM_BYTES = S_TMEM + 16, TM_COL
 __device__ __forceinline__ float sigm(float x) { return __fdividef(1.0f, 1.0f + __expf(-x)); }
 __device__ __forceinline__ float tanh_(float x) { return 2.0f * sigm(2.0f * x) - 1.0f; }
 
+template <bool FAST>
 __global__ void __cluster_dims__(2, 1, 1) __launch_bounds__(NT, 1)
 lstm_fwd_tc_kernel(const LstmDesc d, const float* __restrict__ params, const float* __restrict__ X, const size_t n_seq,
                    float* __restrict__ stash, unsigned* __restrict__ err_flag, const unsigned call_id) {
@@ -70,6 +71,7 @@ lstm_fwd_tc_kernel(const LstmDesc d, const float* __restrict__ params, const flo
   for (size_t tile = pair; tile < n_tiles; tile += n_pairs) {
     const size_t seq = tile * TS + row;
     const bool valid = (warp < ISSUER_WARP) && seq < n_seq;
+    const StashPos sp = stash_pos(d, valid ? seq : 0);
     for (int l = 0; l < d.L; ++l) {
       const int dl = d.d_l[l], xw = xw_of(l), nk = xw + HT;
       // ---- this layer's weights -> fp16 tile: row n of [x | h] (n < xw: input row n, zero beyond d_l; else recurrent row),
@@ -105,8 +107,8 @@ lstm_fwd_tc_kernel(const LstmDesc d, const float* __restrict__ params, const flo
           for (int c8 = 0; c8 < 4; ++c8) {
             float4 a = make_float4(0.f, 0.f, 0.f, 0.f), e = a;
             if (valid) {
-              a = __ldcg(reinterpret_cast<const float4*>(stash + sidx(d, seq, l - 1, t, 5, hh * 32 + c8 * 8)));
-              e = __ldcg(reinterpret_cast<const float4*>(stash + sidx(d, seq, l - 1, t, 5, hh * 32 + c8 * 8 + 4)));
+              a = __ldcg(reinterpret_cast<const float4*>(stash + sidx<FAST>(d, sp, seq, l - 1, t, 5, hh * 32 + c8 * 8)));
+              e = __ldcg(reinterpret_cast<const float4*>(stash + sidx<FAST>(d, sp, seq, l - 1, t, 5, hh * 32 + c8 * 8 + 4)));
             }
             sts128(sA + tile_chunk_off(TS, row, hh * 32 + c8 * 8), make_uint4(pack_half2(a.x, a.y), pack_half2(a.z, a.w), pack_half2(e.x, e.y), pack_half2(e.z, e.w)));
           }
@@ -150,8 +152,8 @@ lstm_fwd_tc_kernel(const LstmDesc d, const float* __restrict__ params, const flo
         for (int t = 0; t < T; ++t, ++q) {
           // the layer below's h two steps ahead: into L2 now, read at the end of the next round
           if (l > 0 && valid && t + 2 < T) {
-            prefetch_l2(stash + sidx(d, seq, l - 1, t + 2, 5, hh * 32));
-            if (d.fast) prefetch_l2(stash + sidx(d, seq, l - 1, t + 2, 5, hh * 32 + 16));
+            prefetch_l2(stash + sidx<FAST>(d, sp, seq, l - 1, t + 2, 5, hh * 32));
+            if (FAST) prefetch_l2(stash + sidx<FAST>(d, sp, seq, l - 1, t + 2, 5, hh * 32 + 16));
           }
           ok = mbar_wait(&bars[B_Z], q & 1) && ok;
           fence_after();
@@ -163,7 +165,7 @@ lstm_fwd_tc_kernel(const LstmDesc d, const float* __restrict__ params, const flo
             if (valid) {
 #pragma unroll
               for (int j4 = 0; j4 < UT / 4; ++j4)
-                *reinterpret_cast<float4*>(stash + sidx(d, seq, l, t, comp, ub + j4 * 4)) = make_float4(a[j4 * 4], a[j4 * 4 + 1], a[j4 * 4 + 2], a[j4 * 4 + 3]);
+                *reinterpret_cast<float4*>(stash + sidx<FAST>(d, sp, seq, l, t, comp, ub + j4 * 4)) = make_float4(a[j4 * 4], a[j4 * 4 + 1], a[j4 * 4 + 2], a[j4 * 4 + 3]);
             }
           };
           const float* bb = bias + hh * UT;
@@ -254,14 +256,16 @@ int lstm_tc_fwd(const lstm::LstmDesc& d, const float* params, const float* X, si
   int dev = 0;
   DLAS_CUDA(cudaGetDevice(&dev));
   if (dev < 0 || dev >= 64 || !attr_set[dev]) {
-    DLAS_CUDA(cudaFuncSetAttribute(lstm_fwd_tc_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)SMEM_BYTES));
+    DLAS_CUDA(cudaFuncSetAttribute(lstm_fwd_tc_kernel<false>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)SMEM_BYTES));
+    DLAS_CUDA(cudaFuncSetAttribute(lstm_fwd_tc_kernel<true>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)SMEM_BYTES));
     if (dev >= 0 && dev < 64) attr_set[dev] = true;
   }
   ++g_lstm_call_id;
   const size_t n_tiles = (n_seq + TS - 1) / TS;
   const int max_pairs = sm_count() / 2;
   const int pairs = (int)(n_tiles < (size_t)max_pairs ? n_tiles : (size_t)max_pairs);
-  lstm_fwd_tc_kernel<<<2 * pairs, NT, SMEM_BYTES, st>>>(d, params, X, n_seq, stash, err_flag, g_lstm_call_id);
+  if (d.fast) lstm_fwd_tc_kernel<true><<<2 * pairs, NT, SMEM_BYTES, st>>>(d, params, X, n_seq, stash, err_flag, g_lstm_call_id);
+  else lstm_fwd_tc_kernel<false><<<2 * pairs, NT, SMEM_BYTES, st>>>(d, params, X, n_seq, stash, err_flag, g_lstm_call_id);
   DLAS_LAUNCH_CHECK();
   lstm_head_kernel<<<(unsigned)((n_seq + 7) / 8), 256, 0, st>>>(d, params, stash, n_seq, err_flag, g_lstm_call_id, yhat);
   DLAS_LAUNCH_CHECK();

@@ -514,18 +514,29 @@ def main():
                 sweep[str(rows_b)] = {"samples_per_s": rows_b * ns / t, "us_per_step": t / ns * 1e6}
             extras["static_ann_32_256_256_1_rows_per_step_sweep"] = sweep
             del Xw, yw
-        # dynamic ANN (config 4): 24 lags x 8 features -> 192-256-256-1, fp32 kernel, 65,536 windows per step
+        # dynamic ANN (config 4): 24 lags x 8 features -> 192-256-256-1, 65,536 windows per step; tensor-core mode = layer 1 in
+        # mlp_tc_l1.cu around the CTA-pair kernel (five launches per step), fp32 mode = the CUDA-core kernels
         dd = [192, 256, 256, 1]
         series, ys = ops.synth_rows(65536 + 23, 8)
         Wd = dlas.LagWindows(series, 24)       # windows read in place from the raw series (row stride 8): 36 B per sample
-        mdl = dlas.Sequential([dlas.Dense(192, 256, activation="relu"), dlas.Dense(256, 256, activation="relu"), dlas.Dense(256, 1)])
-        mdl.compile(loss="mse", optimizer=dlas.SGD(lr=0.001, momentum=0.99, decay=1e-6, nesterov=True))
         yd = ys[23:].contiguous()
-        t = timed(lambda: mdl.train_on_batch(Wd, yd), 5)
-        extras["dynamic_ann_192_256_256_1"] = {"samples_per_s": 65536 / t, "mode": "fp32", "rows_per_step": 65536,
-                                               "input": "24-lag windows gathered from the raw (n, 8) series inside the kernel "
-                                                        "(dlas_mlp_grad_strided): 36 algorithmic bytes per sample, no materialised copy",
-                                               "frac_of_bf16_sustained_peak": 591360 * 65536 / t / 1e12 / pk["tf_sust"]}
+        for dm in ("fp32", "tc"):
+            if dm == "tc" and not (mode == "tc" and ops.mlp_mode_supported(dd, dlas.MODE_TC)):
+                continue
+            mdl = dlas.Sequential([dlas.Dense(192, 256, activation="relu"), dlas.Dense(256, 256, activation="relu"), dlas.Dense(256, 1)], mode=dm)
+            mdl.compile(loss="mse", optimizer=dlas.SGD(lr=0.001, momentum=0.99, decay=1e-6, nesterov=True))
+            t = timed(lambda: mdl.train_on_batch(Wd, yd), 5)
+            ls4 = torch.zeros(4, device="cuda")
+            tf = timed(lambda: ops.mlp_fit_steps(dd, mdl.loss, mdl.mode, mdl.cfg, mdl.params, mdl.m, mdl.v, Wd, yd, 65536, 4, 0, ls4,
+                                                 mdl.grad_sum, mdl.workspace, batch_order=np.zeros(4, dtype=np.int64)), 3) / 4
+            ops.mlp_status(dd, mdl.mode, mdl.workspace)
+            extras["dynamic_ann_192_256_256_1" + ("" if dm == "tc" or mode != "tc" else "_fp32")] = {
+                "samples_per_s": 65536 / tf, "us_per_step": tf * 1e6, "train_on_batch_samples_per_s": 65536 / t, "mode": dm,
+                "rows_per_step": 65536,
+                "input": "24-lag windows gathered from the raw (n, 8) series inside the kernels "
+                         "(dlas_mlp_fit_steps_strided): 36 algorithmic bytes per sample, no materialised copy",
+                "frac_of_bf16_sustained_peak": 591360 * 65536 / tf / 1e12 / pk["tf_sust"]}
+            del mdl
         # static ANN 8-64-64-1 (configs[0]): 1 M rows, one whole epoch through model.fit at batch 4096 (and one 65,536-row
         # step for comparison with round 1); the CPU port runs the same epoch
         X8, y8 = ops.synth_rows(1_000_000, 8)
@@ -612,11 +623,12 @@ def main():
         # configs[3]: dynamic ANN 192-256-256-1, 65,536 windows per GPU per step read in place from the raw series (weak scaling)
         series, ys = ops.synth_rows(65536 + 23, 8, start=rank * 65536)
         Wd = dlas.LagWindows(series, 24)
-        mdl = dlas.Sequential([dlas.Dense(192, 256, activation="relu"), dlas.Dense(256, 256, activation="relu"), dlas.Dense(256, 1)])
+        dm = "tc" if (mode == "tc" and ops.mlp_mode_supported([192, 256, 256, 1], dlas.MODE_TC)) else "fp32"
+        mdl = dlas.Sequential([dlas.Dense(192, 256, activation="relu"), dlas.Dense(256, 256, activation="relu"), dlas.Dense(256, 1)], mode=dm)
         mdl.compile(loss="mse", optimizer=dlas.SGD(lr=0.001, momentum=0.99, decay=1e-6, nesterov=True), exchange="nccl")
         yd = ys[23:].contiguous()
         t = timed_dp(lambda: mdl.train_on_batch(Wd, yd, global_rows=65536 * N), 5)
-        extras["dynamic_ann_192_256_256_1"] = {"samples_per_s": 65536 * N / t, "mode": "fp32", "rows_per_gpu_per_step": 65536,
+        extras["dynamic_ann_192_256_256_1"] = {"samples_per_s": 65536 * N / t, "mode": dm, "rows_per_gpu_per_step": 65536,
                                                "scaling": "weak", "exchange": "nccl all-reduce of the 462 KB bucket"}
         del mdl, series, ys, Wd, yd
 

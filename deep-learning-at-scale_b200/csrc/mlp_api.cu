@@ -41,7 +41,17 @@ int tc64_fit_step(const int* dims, int loss, const dlas_opt_cfg* cfg, float* par
 int tc64_predict(const int* dims, const float* params, const float* X, size_t n_rows, float* yhat, cudaStream_t st, size_t ldx);
 int tc64_eval_loss(const int* dims, int loss, const float* params, const float* X, const float* y, size_t n_rows, float* loss_sum,
                    void* workspace, size_t workspace_bytes, cudaStream_t st, size_t ldx);
-inline bool tc_any(const int* dims, int n_layers) { return tc_supported(dims, n_layers) || tc64_supported(dims, n_layers); }
+// mlp_tc.cu + mlp_tc_l1.cu: d0-256-256-1 with 64 <= d0 <= 240 (training on tcgen05; predict / eval_loss on the fp32 kernels)
+bool tcx_supported(const int* dims, int n_layers);
+size_t tcx_workspace_bytes(const int* dims, int n_layers);
+int tcx_grad(const int* dims, int n_layers, int loss, const float* params, const float* X, const float* y, size_t n_rows,
+             float* grad_sum, void* workspace, size_t workspace_bytes, cudaStream_t st, size_t ldx);
+int tcx_fit_step(const int* dims, int n_layers, int loss, const dlas_opt_cfg* cfg, float* params, float* m, float* v, const float* X,
+                 const float* y, size_t n_rows, uint64_t iteration, float* loss_out, void* workspace, size_t workspace_bytes,
+                 cudaStream_t st, bool chained, size_t ldx, bool more_follow);
+inline bool tc_any(const int* dims, int n_layers) {
+  return tc_supported(dims, n_layers) || tc64_supported(dims, n_layers) || tcx_supported(dims, n_layers);
+}
 size_t tc_dp_recv_words(int world);
 int tc_dp_step(const int* dims, int n_layers, int loss, const dlas_opt_cfg* cfg, float* params, float* m, float* v,
                const float* X_base, const float* y_base, size_t batch_rows, dlas_step_state* state,
@@ -86,6 +96,7 @@ extern "C" size_t dlas_mlp_workspace_bytes(const int* dims, int n_layers, int mo
     size_t a = tc64_workspace_bytes(dims), b = simt_workspace_bytes(dims, n_layers);
     return a > b ? a : b;
   }
+  if (mode == DLAS_MODE_TC && tcx_supported(dims, n_layers)) return tcx_workspace_bytes(dims, n_layers);
   if (mode == DLAS_MODE_TC) return tc_supported(dims, n_layers) ? tc_workspace_bytes(dims, n_layers) : 0;
   return simt_workspace_bytes(dims, n_layers);
 }
@@ -110,6 +121,8 @@ extern "C" int dlas_mlp_grad_strided(const int* dims, int n_layers, int loss, in
   if (rc != DLAS_OK) return rc;
   if (mode == DLAS_MODE_TC && tc64_supported(dims, n_layers))
     return tc64_grad(dims, loss, params, X, y, n_rows, grad_sum, workspace, workspace_bytes, (cudaStream_t)stream, nullptr, 0, x_row_stride);
+  if (mode == DLAS_MODE_TC && tcx_supported(dims, n_layers))
+    return tcx_grad(dims, n_layers, loss, params, X, y, n_rows, grad_sum, workspace, workspace_bytes, (cudaStream_t)stream, x_row_stride);
   if (mode == DLAS_MODE_TC)
     return tc_grad(dims, n_layers, loss, params, X, y, n_rows, grad_sum, workspace, workspace_bytes,
                    (cudaStream_t)stream, nullptr, 0, x_row_stride);
@@ -138,6 +151,10 @@ extern "C" int dlas_mlp_grad_at(const int* dims, int n_layers, int loss, int mod
   if (mode == DLAS_MODE_TC && tc64_supported(dims, n_layers))
     return tc64_grad(dims, loss, params, X_base, y_base, batch_rows, grad_sum, workspace, workspace_bytes, (cudaStream_t)stream, cursor,
                      parity_stride, 0);
+  if (mode == DLAS_MODE_TC && tcx_supported(dims, n_layers)) {
+    set_error("dlas_mlp_grad_at: the tensor-core path of %d-256-256-1 has no device-cursor flavour (use DLAS_MODE_FP32)", dims[0]);
+    return DLAS_ERR_UNSUPPORTED_SHAPE;
+  }
   if (mode == DLAS_MODE_TC)
     return tc_grad(dims, n_layers, loss, params, X_base, y_base, batch_rows, grad_sum, workspace, workspace_bytes,
                    (cudaStream_t)stream, cursor, parity_stride);
@@ -189,6 +206,13 @@ extern "C" int dlas_mlp_fit_steps_strided(const int* dims, int n_layers, int los
       if (rc != DLAS_OK) return rc;
       continue;
     }
+    if (mode == DLAS_MODE_TC && tcx_supported(dims, n_layers)) {
+      rc = tcx_fit_step(dims, n_layers, loss, cfg, params, m, v, Xb, yb, batch, iteration0 + (uint64_t)s,
+                        step_losses ? step_losses + s : nullptr, workspace, workspace_bytes, st, /*chained=*/s > 0, x_row_stride,
+                        /*more_follow=*/s + 1 < n_steps);
+      if (rc != DLAS_OK) return rc;
+      continue;
+    }
     if (mode == DLAS_MODE_TC) {   // gradient kernel + (reduction fused with the update): two launches per step
       rc = tc_fit_step(dims, n_layers, loss, cfg, params, m, v, Xb, yb, batch, iteration0 + (uint64_t)s,
                        step_losses ? step_losses + s : nullptr, workspace, workspace_bytes, st, /*chained=*/s > 0, x_row_stride,
@@ -222,6 +246,7 @@ extern "C" int dlas_mlp_predict_strided(const int* dims, int n_layers, int mode,
   if (rc != DLAS_OK) return rc;
   if (mode == DLAS_MODE_TC) {   // forward-only kind of the tcgen05 kernel
     if (tc64_supported(dims, n_layers)) return tc64_predict(dims, params, X, n_rows, yhat, (cudaStream_t)stream, x_row_stride);
+    if (tcx_supported(dims, n_layers)) return simt_predict(dims, n_layers, params, X, n_rows, yhat, (cudaStream_t)stream, x_row_stride);
     if (!tc_supported(dims, n_layers)) { set_error("dlas_mlp_predict: DLAS_MODE_TC does not support these layer widths"); return DLAS_ERR_UNSUPPORTED_SHAPE; }
     return tc_predict(dims, n_layers, params, X, n_rows, yhat, (cudaStream_t)stream, x_row_stride);
   }
@@ -249,6 +274,8 @@ extern "C" int dlas_mlp_eval_loss_strided(const int* dims, int n_layers, int los
   if (mode == DLAS_MODE_TC) {
     if (tc64_supported(dims, n_layers))
       return tc64_eval_loss(dims, loss, params, X, y, n_rows, loss_sum, workspace, workspace_bytes, (cudaStream_t)stream, x_row_stride);
+    if (tcx_supported(dims, n_layers))
+      return simt_eval_loss(dims, n_layers, loss, params, X, y, n_rows, loss_sum, workspace, workspace_bytes, (cudaStream_t)stream, x_row_stride);
     if (!tc_supported(dims, n_layers)) { set_error("dlas_mlp_eval_loss: DLAS_MODE_TC does not support these layer widths"); return DLAS_ERR_UNSUPPORTED_SHAPE; }
     return tc_eval_loss(dims, n_layers, loss, params, X, y, n_rows, loss_sum, workspace, workspace_bytes, (cudaStream_t)stream, x_row_stride);
   }

@@ -68,12 +68,21 @@ constexpr uint32_t S_W1 = 0, S_W2 = S_W1 + K1 * 4 * 128, S_X = S_W2 + 65536, S_H
 constexpr int F_B2 = 0, F_W3 = 128, F_Y = 256 /*[2][128]*/, F_PART = 512 /*[2][128]*/, F_RP = 768 /*[CSPLIT][128]*/,
               F_RED = F_RP + CSPLIT * 128 /*[4][128]*/, F_END = F_RED + 512;
 constexpr uint32_t S_BAR = S_F32 + F_END * 4;
-enum { B_DONE = 0, B_FREE, B_X0, B_X1, B_H1A, B_H1, B_DZ2, B_DW2A, B_DW2B, B_DZ1A, B_DZ1, B_DW1, B_ALL, B_XC0, B_XC1, B_WIMG, N_BARS };
+enum { B_DONE = 0, B_FREE, B_X0, B_X1, B_H1A, B_H1, B_DZ2, B_DW2A, B_DW2B, B_DZ1A, B_DZ1, B_DW1, B_ALL, B_XC0, B_XC1, B_WIMG, B_H1L, N_BARS };
 // fp16 image of the weights in the kernel's own tile layout, kept in the workspace by the finishing kernel of a step loop
 // (tc_reduce_kernel writes every updated parameter into it), so that the next step's set-up is three bulk copies instead of
 // a 160 KB fp32 read + convert per CTA:  [sW1 tile 24 KB: W1 rows, b1 row, zero rows][sW2 tile of rank 0 64 KB][rank 1 64 KB]
 constexpr uint32_t IMG_W1_BYTES = K1 * 4 * 128, IMG_W2_BYTES = 65536, IMG_BYTES = IMG_W1_BYTES + 2 * IMG_W2_BYTES;
-enum { K_TRAIN = 0, K_EVAL = 1, K_PREDICT = 2 };
+enum { K_TRAIN = 0, K_EVAL = 1, K_PREDICT = 2, K_TRAIN_EXT = 3 };
+// K_TRAIN_EXT: layers 2 and 3 of the wide-input network d0-256-256-1 (mlp_tc_l1.cu holds layer 1): H1 arrives as a 64 KB
+// tile image per 128 rows (one bulk copy instead of Z1 / E1) and each CTA's partial dZ1 tile leaves as an image (one bulk
+// copy instead of the dW1 MMAs); `params` points (d0 - 32) * 256 floats into the real vector, so the W2.. offsets hold.
+constexpr uint32_t IMG_TILE_BYTES = 65536;
+struct ExtIo {
+  const uint8_t* h1_img;   // [tile][64 KB], written by l1_fwd_tc_kernel
+  uint8_t* dz1_img;        // [2 CTA ranks][img_stride bytes], read by l1_dw_tc_kernel
+  size_t img_stride;
+};
 constexpr uint32_t S_TMEM = S_BAR + N_BARS * 8;
 constexpr uint32_t SMEM_BYTES = S_TMEM + 16;
 
@@ -140,8 +149,9 @@ mlp_tc_kernel(const int loss_kind, const float* __restrict__ params, const float
               const float* __restrict__ y_base, const size_t n_rows, float* __restrict__ partials,
               unsigned* __restrict__ err_flag, const unsigned call_id, long long* __restrict__ trace,
               const long long* __restrict__ cursor, const int rows_ready, const size_t ldx,
-              const uint8_t* __restrict__ w_image, float* __restrict__ yhat_out) {
-  constexpr bool TRAIN = (KIND == K_TRAIN);
+              const uint8_t* __restrict__ w_image, float* __restrict__ yhat_out, const ExtIo ext) {
+  constexpr bool EXT = (KIND == K_TRAIN_EXT);
+  constexpr bool TRAIN = (KIND == K_TRAIN) || EXT;
   // ldx: floats between consecutive rows of X (32 for a dense matrix; smaller for lag windows laid over a raw series)
   // device-resident batch cursor (replayable steps): this launch works on rows [cursor*n_rows, (cursor+1)*n_rows)
   extern __shared__ __align__(1024) uint8_t smem[];
@@ -174,6 +184,7 @@ mlp_tc_kernel(const int loss_kind, const float* __restrict__ params, const float
     mbar_init(&bars[B_ALL], 1); mbar_init(&bars[B_DW1], 1); mbar_init(&bars[B_DW2A], 1); mbar_init(&bars[B_DW2B], 1);
     mbar_init(&bars[B_XC0], 1); mbar_init(&bars[B_XC1], 1);   // exchange of the partial output dots: 1 arrival + 512 tx bytes
     mbar_init(&bars[B_WIMG], 1);                               // weight image: 1 arrival + 88 KB of bulk-copy bytes
+    mbar_init(&bars[B_H1L], 1);                                // K_TRAIN_EXT: H1 tile image, 1 arrival + 64 KB
     mbar_fence_init();
   }
   if (warp == ISSUER_WARP) tmem_alloc(tmem_slot, TM_COLS);
@@ -187,7 +198,7 @@ mlp_tc_kernel(const int loss_kind, const float* __restrict__ params, const float
     const bool in = row0 + xr < n_rows;
     const float* src = X + (row0 + xr) * ldx + xh * XF;
 #pragma unroll
-    for (int i = 0; i < XF / 4; ++i) xv[i] = in ? __ldcs(reinterpret_cast<const float4*>(src + i * 4)) : make_float4(0.f, 0.f, 0.f, 0.f);
+    for (int i = 0; i < XF / 4; ++i) xv[i] = (in && !EXT) ? __ldcs(reinterpret_cast<const float4*>(src + i * 4)) : make_float4(0.f, 0.f, 0.f, 0.f);
     if (KIND != K_PREDICT && tid < TILE) yv = (row0 + tid < n_rows) ? __ldcs(y + row0 + tid) : 0.f;
   };
   // rows_ready: the host states that X / y were NOT written by the kernel that precedes this one in the stream (the
@@ -207,8 +218,8 @@ mlp_tc_kernel(const int loss_kind, const float* __restrict__ params, const float
   if (w_image != nullptr) {
     // the finishing kernel of the previous step left the updated weights as fp16 tiles: fetch them with the copy engine
     if (tid == 0) {
-      mbar_arrive_expect_tx(&bars[B_WIMG], IMG_W1_BYTES + IMG_W2_BYTES);
-      bulk_g2s(sW1, w_image, IMG_W1_BYTES, &bars[B_WIMG]);
+      mbar_arrive_expect_tx(&bars[B_WIMG], (EXT ? 0u : IMG_W1_BYTES) + IMG_W2_BYTES);
+      if (!EXT) bulk_g2s(sW1, w_image, IMG_W1_BYTES, &bars[B_WIMG]);
 #pragma unroll
       for (int c = 0; c < 4; ++c)
         bulk_g2s(sW2 + c * 16384, w_image + IMG_W1_BYTES + rank * IMG_W2_BYTES + c * 16384, 16384, &bars[B_WIMG]);
@@ -216,7 +227,7 @@ mlp_tc_kernel(const int loss_kind, const float* __restrict__ params, const float
   } else {
     // sW1 = [W1 ; b1 ; 0]: rows 0..31 weights, row 32 the bias (it multiplies the ones column of [x | 1 | 0]),
     // rows 33..47 zero -> Z1 comes out of the MMA with the bias already added
-    for (int idx = tid; idx < K1 * (D1 / 8); idx += NT) {
+    for (int idx = tid; idx < (EXT ? 0 : K1 * (D1 / 8)); idx += NT) {
       const int r = idx / (D1 / 8), c = (idx % (D1 / 8)) * 8;
       float4 a = make_float4(0.f, 0.f, 0.f, 0.f), b = a;
       if (r <= D0) {
@@ -318,7 +329,13 @@ mlp_tc_kernel(const int loss_kind, const float* __restrict__ params, const float
       ++n;
     };
     if (w_image != nullptr) ok = mbar_wait(&bars[B_WIMG], 0) && ok;   // bulk copies of the weight tiles have landed
-    if (my_tiles > 0) {
+    if (EXT) {
+      if (my_tiles > 0 && leader) {   // H1 of the first tile: one bulk copy of the image l1_fwd_tc_kernel left
+        mbar_arrive_expect_tx(&bars[B_H1L], IMG_TILE_BYTES);
+        bulk_g2s(sH1, ext.h1_img + (size_t)pair * IMG_TILE_BYTES, IMG_TILE_BYTES, &bars[B_H1L]);
+      }
+      __syncwarp();
+    } else if (my_tiles > 0) {
       ok = mbar_wait(&bars[B_X0], 0) && ok;
       issue_z1(0, 0);
     }
@@ -327,12 +344,12 @@ mlp_tc_kernel(const int loss_kind, const float* __restrict__ params, const float
       const bool first = (it == 0);
       pin_descs();
       TRACE_M(10);
-      issue_z1(xb, 1);
+      if (!EXT) issue_z1(xb, 1);
       // Z2h = H1 W2h: one N=128 chain, K = 256; its first half only needs H1 columns 0..127, which are in place
       // while the epilogue is still converting columns 128..255
       TRACE_M(12);
       wait_free();
-      ok = mbar_wait(&bars[B_H1A], it & 1) && ok;
+      ok = mbar_wait(&bars[EXT ? B_H1L : B_H1A], it & 1) && ok;
       fence_after();
       if (leader) {
 #pragma unroll
@@ -340,9 +357,11 @@ mlp_tc_kernel(const int loss_kind, const float* __restrict__ params, const float
           mma_f16(tm + TM_W0, dH1_km + koff_kmajor(TILE, i), dW2_mn + koff_mnmajor(i), ID_KM_MN_128, i > 0);
       }
       __syncwarp();
-      ok = mbar_wait(&bars[B_H1], it & 1) && ok;
-      TRACE_M(13);
-      fence_after();
+      if (!EXT) {
+        ok = mbar_wait(&bars[B_H1], it & 1) && ok;
+        TRACE_M(13);
+        fence_after();
+      }
       if (leader) {
 #pragma unroll
         for (int i = D1 / 32; i < D1 / 16; ++i)
@@ -413,6 +432,24 @@ mlp_tc_kernel(const int loss_kind, const float* __restrict__ params, const float
       }
       __syncwarp();
       TRACE_M(17);
+      if (EXT) {
+        // layer 1 lives in mlp_tc_l1.cu: the partial dZ1 tile leaves as an image; then the next tile's H1 image comes in
+        if (leader) mma_commit(&bars[B_DW1]);   // sDZ2 is free once this arrives (dW2, db2 were its last readers)
+        __syncwarp();
+        ok = mbar_wait(&bars[B_DZ1], it & 1) && ok;   // both halves of dZ1 are in place (the writers fenced for the async proxy)
+        if (leader) {
+          const size_t tile = (size_t)pair + (size_t)it * n_pairs;
+          bulk_s2g(ext.dz1_img + (size_t)rank * ext.img_stride + tile * IMG_TILE_BYTES, sH1, IMG_TILE_BYTES);
+          bulk_commit();
+          bulk_wait_read0();                    // the copy engine has read the tile: it may be overwritten
+          if (it + 1 < my_tiles) {
+            mbar_arrive_expect_tx(&bars[B_H1L], IMG_TILE_BYTES);
+            bulk_g2s(sH1, ext.h1_img + (tile + n_pairs) * IMG_TILE_BYTES, IMG_TILE_BYTES, &bars[B_H1L]);
+          }
+        }
+        __syncwarp();
+        continue;
+      }
       ok = mbar_wait(&bars[B_DZ1A], it & 1) && ok;    // dZ1 columns 0..127 are in place
       fence_after();
       issue_dw1(0);
@@ -428,7 +465,10 @@ mlp_tc_kernel(const int loss_kind, const float* __restrict__ params, const float
       if (leader) mma_commit(&bars[B_DW1]);   // sH1 (dZ1), sDZ2 and sX[xb] are free once this arrives
       __syncwarp();
     }
-    if (leader) mma_commit(&bars[B_ALL]);
+    if (leader) {
+      mma_commit(&bars[B_ALL]);
+      if (EXT) bulk_wait0();   // every dZ1 image has reached memory before the kernel ends
+    }
     __syncwarp();
   } else {
     // =========================== epilogue warps ===========================
@@ -461,7 +501,7 @@ mlp_tc_kernel(const int loss_kind, const float* __restrict__ params, const float
 #pragma unroll
       for (int i = 0; i < XF / 4; ++i) asm volatile("" : "+f"(xv[i].x), "+f"(xv[i].y), "+f"(xv[i].z), "+f"(xv[i].w));
 #pragma unroll
-      for (int i = 0; i < XF / 8; ++i)
+      for (int i = 0; i < (EXT ? 0 : XF / 8); ++i)
         sts128(sX + j * 16384 + tile_chunk_off(TILE, xr, xh * XF + i * 8), pack8(xv[2 * i], xv[2 * i + 1]));
       if (tid < TILE) f32[F_Y + j * 128 + tid] = yv;
       fence_async_smem();
@@ -477,8 +517,9 @@ mlp_tc_kernel(const int loss_kind, const float* __restrict__ params, const float
       const bool row_valid = row0 + row < n_rows;
       TRACE_E(20);
       // ---- (b) H1 = relu(Z1 + b1) -> sH1, two halves of 128 columns (the bias is already in the accumulator) ----
+      if (EXT && it > 0) ok = mbar_wait(&bars[B_DW1], (it - 1) & 1) && ok;   // dW2 / db2 of the previous tile still read sDZ2
 #pragma unroll 1
-      for (int h = 0; h < 2; ++h) {
+      for (int h = 0; h < (EXT ? 0 : 2); ++h) {
         uint32_t v[CW];
         TRACE_E(40);
         take(v);
@@ -661,7 +702,9 @@ mlp_tc_kernel(const int loss_kind, const float* __restrict__ params, const float
         }
         // dW1p^T: lane = h1 unit, column = input feature; column 32 = db1
         const int h1 = mh * 128 + row;
-        if (hh == 0) {
+        if (EXT) {
+          // dW1 / db1 come from l1_dw_tc_kernel
+        } else if (hh == 0) {
           uint32_t v[32];
           tmem_ld32(tm + TM_DW1 + mh * 64 + lane_base, v);
           tmem_ld_wait();
@@ -791,7 +834,10 @@ __global__ void __launch_bounds__(64 * RG, 8)   // 8 blocks per SM: the whole gr
 tc_reduce_kernel(const float* __restrict__ partials, int n_active_pairs, unsigned* __restrict__ err_flag,
                  unsigned call_id, float* __restrict__ out, OptScalars opt, float grad_scale, float* __restrict__ params,
                  float* __restrict__ m, float* __restrict__ v, float* __restrict__ loss_out,
-                 const long long* __restrict__ state, size_t parity_stride, const FinDp dp, uint8_t* __restrict__ img_out) {
+                 const long long* __restrict__ state, size_t parity_stride, const FinDp dp, uint8_t* __restrict__ img_out,
+                 const int pshift) {
+  // pshift != 0: the wide-input network d0-256-256-1 (K_TRAIN_EXT partials).  Entries below W2_OFF belong to layer 1, which
+  // l1_reduce_kernel finishes; entry i >= W2_OFF is parameter i + pshift of the real vector (params / m / v / out are its base)
   // 64 consecutive entries per block; the list of contributing CTAs is cut into RG contiguous parts summed by RG
   // thread groups (more loads in flight: the pass is latency-bound), then added in quarter order -> still deterministic
   __shared__ float red[RG - 1][64];
@@ -800,6 +846,8 @@ tc_reduce_kernel(const float* __restrict__ partials, int n_active_pairs, unsigne
   asm volatile("griddepcontrol.launch_dependents;" ::: "memory");   // next gradient kernel: set-up may overlap this pass
   asm volatile("griddepcontrol.wait;" ::: "memory");   // the gradient kernel has completed; its partials are visible
   const int i = blockIdx.x * 64 + (threadIdx.x & 63), grp = threadIdx.x >> 6;
+  if (pshift != 0 && i < W2_OFF) return;     // whole blocks: W2_OFF is a multiple of 64
+  const int pi = i + pshift;
   const bool live = i <= N_PARAMS;
   long long it = 0, cur = 0;
   if (MODE == FIN_EXCHANGE && dp.state == nullptr) {
@@ -848,15 +896,15 @@ tc_reduce_kernel(const float* __restrict__ partials, int n_active_pairs, unsigne
   if (MODE != FIN_EXCHANGE) {
     if (grp > 0 || !live) return;
     if (MODE == FIN_GRAD) {
-      out[(state && (state[1] & 1)) ? parity_stride + i : i] = s;   // state[1] = iteration: double-buffered bucket
+      out[(state && (state[1] & 1)) ? parity_stride + pi : pi] = s;   // state[1] = iteration: double-buffered bucket
     } else if (i == N_PARAMS) {
       if (loss_out) *loss_out = s * grad_scale;
     } else {
-      float p = params[i], mi = m[i], vi = (opt.kind == 0) ? 0.f : v[i];
+      float p = params[pi], mi = m[pi], vi = (opt.kind == 0) ? 0.f : v[pi];
       opt_update(opt, s * grad_scale, p, mi, vi);
-      params[i] = p;
-      m[i] = mi;
-      if (opt.kind != 0) v[i] = vi;
+      params[pi] = p;
+      m[pi] = mi;
+      if (opt.kind != 0) v[pi] = vi;
       if (img_out) {
         img_store(img_out, i, p);
         if (i < (K1 - D0 - 1) * D1)      // rows 33..47 of the [W1 ; b1 ; 0] tile are zero (the workspace is not initialised)
@@ -957,7 +1005,7 @@ template <int KIND = K_TRAIN>
 int launch_main(int loss, const float* params, const float* X, const float* y, size_t n_rows, void* workspace,
                 size_t workspace_bytes, cudaStream_t st, float** partials_out, unsigned** err_out, int* n_active_pairs,
                 const long long* cursor = nullptr, bool rows_ready = false, size_t ldx = 0, const uint8_t* w_image = nullptr,
-                float* yhat = nullptr) {
+                float* yhat = nullptr, const ExtIo& ext = ExtIo{}) {
   if (ldx == 0) ldx = D0;
   DLAS_REQUIRE(ldx % 4 == 0, "mlp (tc): the row stride of X must be a multiple of 4 floats (16-byte row loads), got %zu", ldx);
   size_t need = ws_need();
@@ -998,7 +1046,7 @@ int launch_main(int loss, const float* params, const float* X, const float* y, s
     cfg.attrs = at;
     cfg.numAttrs = 1;
     DLAS_CUDA(cudaLaunchKernelEx(&cfg, mlp_tc_kernel<KIND>, loss, params, X, y, n_rows, partials, err_flag, g_call_id, trace, cursor,
-                                 rows_ready ? 1 : 0, ldx, w_image, yhat));
+                                 rows_ready ? 1 : 0, ldx, w_image, yhat, ext));
   }
   prof_end(pi, st);
   DLAS_LAUNCH_CHECK();
@@ -1026,7 +1074,7 @@ int launch_main(int loss, const float* params, const float* X, const float* y, s
 template <int MODE>
 int launch_reduce(cudaStream_t st, const float* partials, int nap, unsigned* err, float* out, OptScalars o,
                   float grad_scale, float* params, float* m, float* v, float* loss_out, const long long* state = nullptr,
-                  size_t parity_stride = 0, const FinDp& dp = FinDp{}, uint8_t* img_out = nullptr) {
+                  size_t parity_stride = 0, const FinDp& dp = FinDp{}, uint8_t* img_out = nullptr, int pshift = 0) {
   cudaLaunchConfig_t cfg = {};
   cfg.gridDim = dim3((N_PARAMS + 1 + 63) / 64);
   cfg.blockDim = dim3(64 * RG);
@@ -1037,7 +1085,7 @@ int launch_reduce(cudaStream_t st, const float* partials, int nap, unsigned* err
   cfg.attrs = at;
   cfg.numAttrs = 1;
   DLAS_CUDA(cudaLaunchKernelEx(&cfg, tc_reduce_kernel<MODE>, partials, nap, err, g_call_id, out, o, grad_scale, params, m, v,
-                               loss_out, state, parity_stride, dp, img_out));
+                               loss_out, state, parity_stride, dp, img_out, pshift));
   return DLAS_OK;
 }
 
@@ -1167,6 +1215,105 @@ int tc_fit_step(const int* dims, int n_layers, int loss, const dlas_opt_cfg* cfg
   return DLAS_OK;
 }
 
+
+// ---- d0-256-256-1 (64 <= d0 <= 240, d0 % 8 == 0: the dynamic ANN's 24 x 8 lag window is d0 = 192) --------------------
+// Five launches per step, chained by programmatic dependent launch:
+//   l1_fwd (H1 tile images) -> mlp_tc_kernel<K_TRAIN_EXT> (layers 2, 3; partial dZ1 images) -> tc_reduce (W2.. [update])
+//   -> l1_dw (dW1, db1 partials) -> l1_reduce ([update of] W1, b1)
+// Workspace: [pair partials | status words | weight image] as for 32-256-256-1, then the H1 images, the two partial dZ1
+// image sets and layer 1's partials.  The images bound the rows of one call (TCX_MAX_ROWS).
+int l1_fwd(int d0, const float* params, const float* X, size_t ldx, size_t n_rows, uint8_t* h1_img, unsigned* err_flag, unsigned call_id,
+           cudaStream_t st);
+int l1_dw(int d0, const float* X, size_t ldx, size_t n_rows, const uint8_t* dz1_img, size_t img_stride, float* partials,
+          unsigned* err_flag, unsigned call_id, int mode, float* grad_sum, const OptScalars& opt, float grad_scale, float* params,
+          float* m, float* v, cudaStream_t st);
+size_t l1_partial_bytes(int d0);
+
+constexpr size_t TCX_MAX_ROWS = 65536;
+namespace {
+size_t tcx_base() { return (ws_need() + 1023) & ~(size_t)1023; }
+size_t tcx_img_bytes() { return (TCX_MAX_ROWS / TILE) * (size_t)IMG_TILE_BYTES; }
+}  // namespace
+
+bool tcx_supported(const int* dims, int n_layers) {
+  return n_layers == 3 && dims[1] == D1 && dims[2] == D2 && dims[3] == 1 && dims[0] >= 64 && dims[0] <= 240 && dims[0] % 8 == 0;
+}
+
+size_t tcx_workspace_bytes(const int* dims, int n_layers) {
+  size_t tc = tcx_base() + 3 * tcx_img_bytes() + l1_partial_bytes(dims[0]);
+  size_t simt = simt_workspace_bytes(dims, n_layers);             // eval / predict run on the fp32 kernels
+  return tc > simt ? tc : simt;
+}
+
+// mode 0: gradient sums -> grad_sum (dlas_mlp_grad);  mode 1: one whole step (update fused into the two reductions)
+static int tcx_run(const int* dims, int loss, int mode, const float* params_c, float* params, float* m, float* v, const OptScalars& o,
+                   float grad_scale, const float* X, size_t ldx, const float* y, size_t n_rows, float* grad_sum, float* loss_out,
+                   void* workspace, size_t workspace_bytes, cudaStream_t st, bool chained, bool more_follow) {
+  const int d0 = dims[0];
+  const size_t need = tcx_base() + 3 * tcx_img_bytes() + l1_partial_bytes(d0);
+  if (workspace == nullptr || workspace_bytes < need) {
+    set_error("mlp (tc, %d-256-256-1): workspace of %zu bytes given, %zu needed", d0, workspace_bytes, need);
+    return DLAS_ERR_WORKSPACE;
+  }
+  if (n_rows > TCX_MAX_ROWS) {
+    set_error("mlp (tc, %d-256-256-1): %zu rows in one call; the tensor-core path of this shape takes at most %zu (its "
+              "workspace holds the layer-1 tiles of one call) -- split the batch or use DLAS_MODE_FP32", d0, n_rows, TCX_MAX_ROWS);
+    return DLAS_ERR_UNSUPPORTED_SHAPE;
+  }
+  DLAS_REQUIRE(ldx % 4 == 0, "mlp (tc): the row stride of X must be a multiple of 4 floats (16-byte row loads), got %zu", ldx);
+  DLAS_REQUIRE((((uintptr_t)X) & 15) == 0, "mlp (tc): X must be 16-byte aligned");
+  uint8_t* base = (uint8_t*)workspace + tcx_base();
+  ExtIo ext;
+  ext.h1_img = base;
+  ext.dz1_img = base + tcx_img_bytes();
+  ext.img_stride = tcx_img_bytes();
+  float* l1_part = (float*)(base + 3 * tcx_img_bytes());
+  unsigned* err = (unsigned*)((char*)workspace + ws_partials_bytes());
+  const int pshift = (d0 - D0) * D1;
+  int rc = l1_fwd(d0, params_c, X, ldx, n_rows, base, err, g_call_id + 1, st);   // launch_main gives the step its id
+  if (rc != DLAS_OK) return rc;
+  float* partials; int nap;
+  rc = launch_main<K_TRAIN_EXT>(loss, params_c + pshift, X, y, n_rows, workspace, workspace_bytes, st, &partials, &err, &nap, nullptr, false,
+                                ldx, chained ? ws_image(workspace) : nullptr, nullptr, ext);
+  if (rc != DLAS_OK) return rc;
+  if (mode == 0)
+    rc = launch_reduce<FIN_GRAD>(st, partials, nap, err, grad_sum, OptScalars{}, 0.f, nullptr, nullptr, nullptr, nullptr, nullptr, 0,
+                                 FinDp{}, nullptr, pshift);
+  else
+    rc = launch_reduce<FIN_UPDATE>(st, partials, nap, err, nullptr, o, grad_scale, params, m, v, loss_out, nullptr, 0, FinDp{},
+                                   more_follow ? ws_image(workspace) : nullptr, pshift);
+  if (rc != DLAS_OK) return rc;
+  return l1_dw(d0, X, ldx, n_rows, ext.dz1_img, ext.img_stride, l1_part, err, g_call_id, mode, grad_sum, o, grad_scale, params, m, v, st);
+}
+
+int tcx_grad(const int* dims, int n_layers, int loss, const float* params, const float* X, const float* y, size_t n_rows,
+             float* grad_sum, void* workspace, size_t workspace_bytes, cudaStream_t st, size_t ldx) {
+  if (!tcx_supported(dims, n_layers)) {
+    set_error("DLAS_MODE_TC: not a d0-256-256-1 network");
+    return DLAS_ERR_UNSUPPORTED_SHAPE;
+  }
+  if (n_rows == 0) {
+    DLAS_CUDA(cudaMemsetAsync(grad_sum, 0, ((size_t)N_PARAMS + (size_t)(dims[0] - D0) * D1 + 1) * sizeof(float), st));
+    return DLAS_OK;
+  }
+  return tcx_run(dims, loss, 0, params, nullptr, nullptr, nullptr, OptScalars{}, 0.f, X, ldx, y, n_rows, grad_sum, nullptr, workspace,
+                 workspace_bytes, st, false, false);
+}
+
+int tcx_fit_step(const int* dims, int n_layers, int loss, const dlas_opt_cfg* cfg, float* params, float* m, float* v, const float* X,
+                 const float* y, size_t n_rows, uint64_t iteration, float* loss_out, void* workspace, size_t workspace_bytes,
+                 cudaStream_t st, bool chained, size_t ldx, bool more_follow) {
+  if (!tcx_supported(dims, n_layers)) {
+    set_error("DLAS_MODE_TC: not a d0-256-256-1 network");
+    return DLAS_ERR_UNSUPPORTED_SHAPE;
+  }
+  OptScalars o;
+  int rc = make_opt_scalars(cfg, iteration, o);
+  if (rc != DLAS_OK) return rc;
+  DLAS_REQUIRE(o.kind == DLAS_OPT_SGD || v != nullptr, "Adam needs the second-moment buffer v");
+  return tcx_run(dims, loss, 1, params, params, m, v, o, 1.0f / (float)n_rows, X, ldx, y, n_rows, nullptr, loss_out, workspace,
+                 workspace_bytes, st, chained, more_follow);
+}
 
 // one whole data-parallel step in two launches (forward/backward, then reduce + exchange + update + advance)
 size_t tc_dp_recv_words(int world) { return 2 * (size_t)world * (((size_t)N_PARAMS + 1 + 63) & ~(size_t)63); }

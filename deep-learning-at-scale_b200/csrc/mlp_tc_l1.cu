@@ -33,10 +33,11 @@ __device__ __forceinline__ void load_x_tile(uint32_t sXw, const float* __restric
   const bool in = row0 + r < n_rows;
   const float* src = X + (row0 + r) * ldx;
   const int n_chunks = k1 >> 3;
-  for (int c0 = half; c0 < n_chunks; c0 += 8) {          // 4 chunks (8 loads) in flight per round
-    float4 a[4], e[4];
+  constexpr int U = 7;                                     // chunks (2 loads each) in flight per round: d0 = 192 -> 2 rounds
+  for (int c0 = half; c0 < n_chunks; c0 += 2 * U) {
+    float4 a[U], e[U];
 #pragma unroll
-    for (int u = 0; u < 4; ++u) {
+    for (int u = 0; u < U; ++u) {
       const int c = c0 + 2 * u;
       a[u] = make_float4(0.f, 0.f, 0.f, 0.f); e[u] = a[u];
       if (c < n_chunks) {
@@ -48,7 +49,7 @@ __device__ __forceinline__ void load_x_tile(uint32_t sXw, const float* __restric
       }
     }
 #pragma unroll
-    for (int u = 0; u < 4; ++u) {
+    for (int u = 0; u < U; ++u) {
       const int c = c0 + 2 * u;
       if (c < n_chunks)
         sts128(sXw + tile_chunk_off(TILE, r, c * 8), make_uint4(pack_half2(a[u].x, a[u].y), pack_half2(a[u].z, a[u].w), pack_half2(e[u].x, e[u].y), pack_half2(e[u].z, e[u].w)));
@@ -83,15 +84,25 @@ l1_fwd_tc_kernel(const int d0, const float* __restrict__ params, const float* __
   if (warp == ISSUER_WARP) tmem_alloc(tmem_slot, TM_COLS);
   asm volatile("griddepcontrol.wait;" ::: "memory");           // params come from the previous step's update
   // [W1 ; b1 ; 0] -> fp16 tile: rows = k (features, bias row, zero rows), columns = units
-  for (int idx = tid; idx < k1 * 32; idx += NT) {
-    const int n = idx >> 5, c = (idx & 31) * 8;
-    float4 a = make_float4(0.f, 0.f, 0.f, 0.f), e = a;
-    if (n <= d0) {
-      const float* src = (n < d0) ? params + (size_t)n * D1 + c : params + (size_t)d0 * D1 + c;
-      a = __ldg(reinterpret_cast<const float4*>(src));
-      e = __ldg(reinterpret_cast<const float4*>(src + 4));
+  for (int i0 = 0; i0 < k1 * 32; i0 += NT * 4) {          // 4 chunks (8 loads) in flight per thread
+    float4 a[4], e[4];
+#pragma unroll
+    for (int u = 0; u < 4; ++u) {
+      const int idx = i0 + u * NT + tid, n = idx >> 5, c = (idx & 31) * 8;
+      a[u] = make_float4(0.f, 0.f, 0.f, 0.f); e[u] = a[u];
+      if (idx < k1 * 32 && n <= d0) {                      // rows 0..d0-1 weights, row d0 the bias (b1 follows W1), then zero rows
+        const float* src = params + (size_t)n * D1 + c;
+        a[u] = __ldg(reinterpret_cast<const float4*>(src));
+        e[u] = __ldg(reinterpret_cast<const float4*>(src + 4));
+      }
     }
-    sts128(sW1 + tile_chunk_off(256, n, c), make_uint4(pack_half2(a.x, a.y), pack_half2(a.z, a.w), pack_half2(e.x, e.y), pack_half2(e.z, e.w)));
+#pragma unroll
+    for (int u = 0; u < 4; ++u) {
+      const int idx = i0 + u * NT + tid;
+      if (idx < k1 * 32)
+        sts128(sW1 + tile_chunk_off(256, idx >> 5, (idx & 31) * 8),
+               make_uint4(pack_half2(a[u].x, a[u].y), pack_half2(a[u].z, a[u].w), pack_half2(e[u].x, e[u].y), pack_half2(e[u].z, e[u].w)));
+    }
   }
   fence_async_smem();
   fence_before();
@@ -219,26 +230,30 @@ l1_dw_tc_kernel(const int d0, const float* __restrict__ X, const size_t ldx, con
       __syncwarp();
     }
   } else {
+    // dZ1 of this CTA's 128 units: column blocks 2jc, 2jc+1 of the two partial tile images, added as packed halves.  An
+    // image is byte-identical to the shared-memory tile, so the copy keeps every 16-byte chunk in place.  The chunks of
+    // tile c+1 are requested before tile c's rows are converted, so their latency hides under that work.
+    uint4 a[8], e[8];
+    auto dz_issue = [&](int c) {
+      const size_t tile = (size_t)slice + (size_t)c * n_slices;
+      const uint8_t* g0 = dz1_img + tile * (size_t)IMG_TILE_BYTES + (size_t)jc * 32768;
+      const uint8_t* g1 = g0 + img_stride;
+#pragma unroll
+      for (int u = 0; u < 8; ++u) {
+        a[u] = __ldcs(reinterpret_cast<const uint4*>(g0 + (size_t)(tid + u * N_WORK) * 16));
+        e[u] = __ldcs(reinterpret_cast<const uint4*>(g1 + (size_t)(tid + u * N_WORK) * 16));
+      }
+    };
+    if (my_tiles > 0) dz_issue(0);
     for (int c = 0; c < my_tiles; ++c) {
       const int b = c & 1;
       const size_t tile = (size_t)slice + (size_t)c * n_slices;
       if (c >= 2) ok = mbar_wait(&bars[B_FREE0 + b], ((c >> 1) - 1) & 1) && ok;
-      // dZ1 of this CTA's 128 units: column blocks 2jc, 2jc+1 of the two partial tile images, added as packed halves.  An
-      // image is byte-identical to the shared-memory tile, so the copy keeps every 16-byte chunk in place.
-      {
-        const uint8_t* g0 = dz1_img + tile * (size_t)IMG_TILE_BYTES + (size_t)jc * 32768;
-        const uint8_t* g1 = g0 + img_stride;
-        uint4 a[8], e[8];
 #pragma unroll
-        for (int u = 0; u < 8; ++u) {
-          a[u] = __ldcs(reinterpret_cast<const uint4*>(g0 + (size_t)(tid + u * N_WORK) * 16));
-          e[u] = __ldcs(reinterpret_cast<const uint4*>(g1 + (size_t)(tid + u * N_WORK) * 16));
-        }
-#pragma unroll
-        for (int u = 0; u < 8; ++u)
-          sts128(sDZ + b * 32768 + (uint32_t)(tid + u * N_WORK) * 16,
-                 make_uint4(add_h2(a[u].x, e[u].x), add_h2(a[u].y, e[u].y), add_h2(a[u].z, e[u].z), add_h2(a[u].w, e[u].w)));
-      }
+      for (int u = 0; u < 8; ++u)
+        sts128(sDZ + b * 32768 + (uint32_t)(tid + u * N_WORK) * 16,
+               make_uint4(add_h2(a[u].x, e[u].x), add_h2(a[u].y, e[u].y), add_h2(a[u].z, e[u].z), add_h2(a[u].w, e[u].w)));
+      if (c + 1 < my_tiles) dz_issue(c + 1);
       load_x_tile(sX + b * 65536, X, ldx, tile * TILE, n_rows, d0, k1, tid);
       fence_async_smem();
       __syncwarp();
@@ -279,12 +294,20 @@ l1_reduce_kernel(const int d0, const float* __restrict__ partials, const int n_c
                  float* __restrict__ params, float* __restrict__ m, float* __restrict__ v) {
   asm volatile("griddepcontrol.launch_dependents;" ::: "memory");
   asm volatile("griddepcontrol.wait;" ::: "memory");
-  const int i = blockIdx.x * 256 + threadIdx.x;          // index into [W1 (d0 x 256) ; b1 (256)]
-  if (i >= (d0 + 1) * D1) return;
+  // 64 consecutive entries of [W1 (d0 x 256) ; b1 (256)] per block; the slices are cut into 4 contiguous parts summed by 4
+  // thread groups (more loads in flight), then added in part order -> deterministic
+  __shared__ float red[3][64];
+  const int i = blockIdx.x * 64 + (threadIdx.x & 63), grp = threadIdx.x >> 6;   // (d0 + 1) * 256 is a multiple of 64
   const int k = i / D1, unit = i - k * D1, jc = unit >> 7, j = unit & 127;
   const size_t pf = l1_part_floats(d0);
+  const int n_src = n_ctas >> 1, per = (n_src + 3) / 4, s0 = grp * per, s1 = min(n_src, s0 + per);
   float s = 0.f;
-  for (int b = jc; b < n_ctas; b += 2) s += partials[(size_t)b * pf + (size_t)k * 128 + j];
+#pragma unroll 8
+  for (int q = s0; q < s1; ++q) s += partials[(size_t)(2 * q + jc) * pf + (size_t)k * 128 + j];
+  if (grp > 0) red[grp - 1][threadIdx.x & 63] = s;
+  __syncthreads();
+  if (grp > 0) return;
+  s += red[0][threadIdx.x]; s += red[1][threadIdx.x]; s += red[2][threadIdx.x];
   if (*err_flag == call_id) s = __int_as_float(0x7fc00000);
   if (!(fabsf(s) <= 3.0e38f)) err_flag[1] = call_id;     // status words: see tc_reduce_kernel
   if (MODE == 0) {
@@ -345,7 +368,7 @@ int l1_dw(int d0, const float* X, size_t ldx, size_t n_rows, const uint8_t* dz1_
   cfg.attrs = at;
   cfg.numAttrs = 1;
   DLAS_CUDA(cudaLaunchKernelEx(&cfg, l1_dw_tc_kernel, d0, X, ldx, n_rows, dz1_img, img_stride, partials, err_flag, call_id));
-  cfg.gridDim = dim3((unsigned)(((d0 + 1) * D1 + 255) / 256));
+  cfg.gridDim = dim3((unsigned)(((d0 + 1) * D1) / 64));
   cfg.blockDim = dim3(256);
   cfg.dynamicSmemBytes = 0;
   if (mode == 0)

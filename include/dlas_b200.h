@@ -40,7 +40,9 @@ extern "C" {
 /* arithmetic mode of the MLP kernels */
 #define DLAS_MODE_FP32 0   /* CUDA-core fp32, any layer widths                                   */
 #define DLAS_MODE_TC 1     /* tcgen05 tensor cores: fp16 operands, fp32 accumulation in TMEM; fixed shapes,
-                              see dlas_mlp_mode_supported.  A REDUCED-RANGE mode: rows, hidden activations
+                              see dlas_mlp_mode_supported (32-256-256-1; d0-64-64-1 with d0 <= 15;
+                              d0-256-256-1 with 64 <= d0 <= 240, d0 % 8 == 0: training entry points, at most
+                              65,536 rows per call, predict / eval_loss on the fp32 kernels).  A REDUCED-RANGE mode: rows, hidden activations
                               and back-propagated terms are rounded to fp16 -- TF32's 11-bit significand but
                               a 5-bit exponent: |value| <= 65504, full precision down to 6.1e-5, flushed to
                               zero below 6e-8.  Feed it standardised columns (raw wellhead pressures of a

@@ -285,7 +285,7 @@ extern "C" int dlas_mlp_eval_loss_strided(const int* dims, int n_layers, int los
 
 extern "C" size_t dlas_mlp_dp_recv_bytes(const int* dims, int n_layers, int mode, int world) {
   if (!dims || mode != DLAS_MODE_TC || !tc_supported(dims, n_layers) || world < 1 || world > 8) return 0;
-  return tc_dp_recv_words(world) * 8;
+  return tc_dp_recv_words(world) * 4;
 }
 
 extern "C" int dlas_mlp_dp_step_at(const int* dims, int n_layers, int loss, int mode, const dlas_opt_cfg* cfg, float* params,

@@ -766,13 +766,17 @@ mlp_tc_kernel(const int loss_kind, const float* __restrict__ params, const float
 // FIN_UPDATE:   the optimiser update of entry i is applied in the same pass (single-GPU step: no all-reduce sits
 //               between the gradient and the update), and the batch-mean loss goes to *loss_out.
 // FIN_EXCHANGE: data-parallel step over NVLink peer memory.  Every block PUSHES its 64 sums into every peer's receive
-//               buffer as 8-byte {value, epoch} words (epoch = iteration + 1; an aligned 8-byte store arrives whole), then
-//               polls ITS OWN receive buffer -- local memory -- until the peers' words of this epoch are there, adds the
-//               `world` values in rank order (same bits on every rank), applies the update, and the last block to finish
-//               advances the device-resident cursor and iteration.  One NVLink one-way latency per step, no flags, no
-//               separate all-reduce / update / advance kernels.  Receive buffer of a rank: [2 parities][world sources]
-//               [recv_stride words]; parity = iteration & 1, so a rank one step ahead never overwrites words still being
-//               read (it cannot get two steps ahead: it needs this rank's next words first).
+//               buffer as plain 4-byte floats, then polls ITS OWN receive buffer -- local memory -- until the peers' words
+//               are there, adds the `world` values in rank order (same bits on every rank), applies the update, and the
+//               last block to finish advances the device-resident cursor and iteration.  A word is its own flag: the
+//               buffer starts as zeros, +0.0 travels as -0.0 (and is read back as +0.0), so "non-zero bits" means
+//               "arrived"; the reader clears every word it has consumed.  100 % of the NVLink bytes are payload (the
+//               {value, epoch} pairs of the first version spent half of them on the epoch, and at 8 ranks the poll was
+//               bound by the 4.2 MB each rank receives per step), and no access wider than a 4-byte word has to arrive
+//               whole.  One NVLink one-way latency per step, no flags, no separate all-reduce / update / advance
+//               kernels.  Receive buffer of a rank: [2 parities][world sources][recv_stride words]; parity =
+//               iteration & 1: a rank one step ahead writes the other parity, and it cannot get two steps ahead -- it
+//               needs this rank's next words first, which leave after this step's kernel (and its clearing) has ended.
 enum { FIN_GRAD = 0, FIN_UPDATE = 1, FIN_EXCHANGE = 2 };
 struct FinDp {
   const unsigned long long* recv_bases;   // device array: address of every rank's receive buffer as mapped HERE
@@ -796,17 +800,19 @@ __device__ __forceinline__ unsigned long long gtime() { unsigned long long t; as
 #endif
 __device__ unsigned g_fin_done = 0;       // blocks of the current FIN_EXCHANGE launch that have finished (reset by the last)
 
-// {value, epoch} travels as ONE 8-byte scalar access (low word = value bits, high word = epoch): an aligned .b64 access is
-// single-copy atomic, so a reader never sees the new epoch beside the old value (a .v2.b32 access is formally two scalar
-// accesses in unspecified order).
-__device__ __forceinline__ void st_push(unsigned long long addr, float v, unsigned epoch) {
-  const unsigned long long w = ((unsigned long long)epoch << 32) | (unsigned long long)__float_as_uint(v);
-  asm volatile("st.relaxed.sys.global.b64 [%0], %1;" ::"l"(addr), "l"(w) : "memory");
+// One 4-byte word per value; all-zero bits = "not arrived".  +0.0 is sent as -0.0 and every zero is read as +0.0.
+__device__ __forceinline__ void st_push(unsigned long long addr, float v) {
+  unsigned w = __float_as_uint(v);
+  if (w == 0u) w = 0x80000000u;
+  asm volatile("st.relaxed.sys.global.b32 [%0], %1;" ::"l"(addr), "r"(w) : "memory");
 }
-__device__ __forceinline__ uint2 ld_poll(unsigned long long addr) {
-  unsigned long long w;
-  asm volatile("ld.relaxed.sys.global.b64 %0, [%1];" : "=l"(w) : "l"(addr) : "memory");
-  return make_uint2((unsigned)(w & 0xffffffffull), (unsigned)(w >> 32));
+__device__ __forceinline__ unsigned ld_poll(unsigned long long addr) {
+  unsigned w;
+  asm volatile("ld.relaxed.sys.global.b32 %0, [%1];" : "=r"(w) : "l"(addr) : "memory");
+  return w;
+}
+__device__ __forceinline__ void st_clear(unsigned long long addr) {
+  asm volatile("st.relaxed.sys.global.b32 [%0], %1;" ::"l"(addr), "r"(0u) : "memory");
 }
 
 // the updated parameter i as fp16 at its place in the weight image (see IMG_*); b2, w3, b3 are not part of the operand tiles
@@ -915,11 +921,10 @@ tc_reduce_kernel(const float* __restrict__ partials, int n_active_pairs, unsigne
   }
   // ---- FIN_EXCHANGE -------------------------------------------------------------------------------------------
   if (grp == 0 && live) {
-    const unsigned epoch = (unsigned)(it + 1);
     const size_t slot = (size_t)(it & 1) * dp.world * dp.recv_stride + (size_t)i;   // + source * recv_stride
-    // push my sum into every peer's buffer, at source index = my rank (64 threads x 8 bytes: one 512-byte row per peer)
+    // push my sum into every peer's buffer, at source index = my rank (64 threads x 4 bytes: one 256-byte row per peer)
     for (int r = 0; r < dp.world; ++r)
-      if (r != dp.rank) st_push(dp.recv_bases[r] + (slot + (size_t)dp.rank * dp.recv_stride) * 8, s, epoch);
+      if (r != dp.rank) st_push(dp.recv_bases[r] + (slot + (size_t)dp.rank * dp.recv_stride) * 4, s);
     FIN_STAMP(1);
     // collect the peers' sums from my own buffer; every load first, spinning only on words that have not arrived
     float q[FIN_MAXW];
@@ -929,16 +934,17 @@ tc_reduce_kernel(const float* __restrict__ partials, int n_active_pairs, unsigne
     for (int r = 0; r < FIN_MAXW; ++r) {
       q[r] = 0.f;
       if (r < dp.world && r != dp.rank) {
-        const unsigned long long a = mine + (slot + (size_t)r * dp.recv_stride) * 8;
-        uint2 w = ld_poll(a);
-        for (unsigned spin = 0; w.y != epoch && spin < (1u << 21); ++spin) {
+        const unsigned long long a = mine + (slot + (size_t)r * dp.recv_stride) * 4;
+        unsigned w = ld_poll(a);
+        for (unsigned spin = 0; w == 0u && spin < (1u << 21); ++spin) {
           __nanosleep(20);
           w = ld_poll(a);
         }
-        if (w.y != epoch) ok = false;
-        q[r] = __uint_as_float(w.x);
+        if (w == 0u) ok = false;
+        else st_clear(a);                                   // consumed: the slot is free for iteration it + 2
+        q[r] = (w == 0x80000000u) ? 0.f : __uint_as_float(w);
       } else if (r == dp.rank) {
-        q[r] = s;
+        q[r] = (s == 0.f) ? 0.f : s;                        // the same canonical zero the peers read
       }
     }
     FIN_STAMP(2);

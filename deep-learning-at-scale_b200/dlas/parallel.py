@@ -72,7 +72,8 @@ class PeerBucket:
 
 class PeerRecvBuffer:
     """This rank's RECEIVE buffer for dlas_mlp_dp_step_at, in memory every peer GPU of the box can store to (torch
-    symmetric memory): [2 parities][world sources][words] of 8-byte {value, epoch} words, zeroed once.  PyTorch only
+    symmetric memory): [2 parities][world sources][words] of 4-byte floats, zeroed once (zero bits = not arrived; the
+    kernel clears what it has consumed).  PyTorch only
     allocates and maps it; the pushes over NVLink, the polling, the sum and the update are the library's kernel."""
 
     def __init__(self, n_bytes, device):
@@ -80,7 +81,7 @@ class PeerRecvBuffer:
         self.rank, self.world = world_info()
         self.buf = symm_mem.empty(n_bytes // 4, dtype=torch.float32, device=device)
         self.handle = symm_mem.rendezvous(self.buf, dist.group.WORLD)
-        self.buf.zero_()                      # epochs start at 1: a zeroed word has never been written
+        self.buf.zero_()                      # all-zero bits: a word that has not arrived
         torch.cuda.synchronize(device)
         dist.barrier()                        # nobody pushes before everybody has cleared
         self.bases = torch.tensor([int(p) for p in self.handle.buffer_ptrs], dtype=torch.int64, device=device)

@@ -182,8 +182,9 @@ int dlas_dp_allreduce_update(const dlas_opt_cfg* cfg, float* params, float* m, f
 
 /* n_steps whole data-parallel steps of DLAS_MODE_TC, TWO launches each (no reference counterpart; same averaging semantics as
  * dlas_dp_allreduce_update): the forward/backward kernel on rows [cursor*batch_rows, ...) of this rank's shard, then ONE
- * kernel that sums the per-CTA partials, PUSHES the sums into every peer's receive buffer as 8-byte {value, epoch}
- * words (epoch = iteration + 1), polls its own receive buffer until the peers' words of this epoch have arrived, adds
+ * kernel that sums the per-CTA partials, PUSHES the sums into every peer's receive buffer as 4-byte floats (all-zero bits
+ * mean "not arrived": +0.0 travels as -0.0, the reader clears what it has consumed), polls its own receive buffer until the
+ * peers' words have arrived, adds
  * the `world` values in rank order (bit-identical on every rank), applies the optimiser update with
  * g = sum * grad_scale, writes the batch-mean loss to loss_ring[iteration % ring_len] and advances the state
  * (cursor = (cursor + 1) % n_batches, iteration += 1).  One NVLink one-way latency per step; no flags, no NCCL call,
@@ -193,7 +194,8 @@ int dlas_dp_allreduce_update(const dlas_opt_cfg* cfg, float* params, float* m, f
  * shuffled epoch order, n_steps entries) or, with batch_order_host == NULL, on batch (cursor0 + s) % n_batches, with the
  * schedule of iteration iteration0 + s (from the second step of a call on, the forward/backward kernel loads its first
  * rows before the previous step has finished).  world == 1 is allowed (no peer, same two launches).  Every rank owns a receive buffer of dlas_mlp_dp_recv_bytes(...) bytes,
- * ZEROED once by the caller, in memory its peers can store to (CUDA IPC / VMM / symmetric memory);
+ * ZEROED once by the caller BEFORE any rank's first step (synchronise the ranks after clearing), in memory its peers can
+ * store to (CUDA IPC / VMM / symmetric memory);
  * recv_bases_dev[r] = the address under which THIS process reaches rank r's buffer.  A rank whose peers' words do not
  * arrive within a bounded spin writes NaN into its parameters and loss ring instead of hanging. */
 size_t dlas_mlp_dp_recv_bytes(const int* dims, int n_layers, int mode, int world);   /* 0: not supported */

@@ -22,9 +22,9 @@ namespace dlas {
 bool lstm_tc_supported(const lstm::LstmDesc& d);
 size_t lstm_tc_dw_partial_floats(const lstm::LstmDesc& d);
 int lstm_tc_fwd(const lstm::LstmDesc& d, const float* params, const float* X, size_t n_seq, float* stash, float* yhat,
-                unsigned* err_flag, cudaStream_t st);
+                unsigned* err_flag, unsigned* prog, cudaStream_t st);
 int lstm_tc_bwd(const lstm::LstmDesc& d, int loss, const float* params, const float* y, float* yhat_dy, size_t n_seq,
-                float* stash, float* dseqP, float* partials, int n_blocks, unsigned* err_flag, cudaStream_t st);
+                float* stash, float* dseqP, float* partials, int n_blocks, unsigned* err_flag, unsigned* prog, cudaStream_t st);
 int lstm_tc_dw(const lstm::LstmDesc& d, const float* X, const float* stash, size_t n_seq, float* grad_sum, float* tc_partials,
                unsigned* err_flag, cudaStream_t st);
 
@@ -277,7 +277,7 @@ lstm_reduce_kernel(const float* __restrict__ partials, size_t stride, int n_acti
   out[i0 + i] = s;
 }
 
-struct Ws { float *stash, *dseq, *KT, *partials, *yhat, *tcp, *dseqP; unsigned* status; size_t bytes; };
+struct Ws { float *stash, *dseq, *KT, *partials, *yhat, *tcp, *dseqP; unsigned *status, *prog; size_t bytes; };
 Ws carve_ws(const LstmDesc& d, size_t n_seq, void* base) {
   Ws w;
   size_t o = 0;
@@ -292,6 +292,8 @@ Ws carve_ws(const LstmDesc& d, size_t n_seq, void* base) {
   // tensor-core BPTT: the two CTAs of a pair write partial dx of a layer into separate buffers (x 2 sets from 3 layers up)
   w.dseqP = take(lstm_tc_supported(d) && d.L > 1 ? (size_t)(d.L >= 3 ? 4 : 2) * n_pad * d.T * (size_t)d.H : 0);
   w.status = reinterpret_cast<unsigned*>(take(64));                              // status words of the tensor-core kernels
+  // layer pipeline of the tensor-core recurrences: one progress counter per (128-sequence tile, layer)
+  w.prog = reinterpret_cast<unsigned*>(take(lstm_tc_supported(d) ? ((n_seq + 127) / 128) * (size_t)d.L : 0));
   w.bytes = o * sizeof(float);
   return w;
 }
@@ -366,7 +368,7 @@ extern "C" int dlas_lstm_predict_mode(int mode, int d_in, int hidden, int n_laye
   size_t smem = rec_smem_bytes(d);
   rc = set_smem(lstm_fwd_kernel, smem);
   if (rc != DLAS_OK) return rc;
-  if (bits & TC_FWD) return lstm_tc_fwd(d, params, X, n_seq, w.stash, yhat, w.status, st);
+  if (bits & TC_FWD) return lstm_tc_fwd(d, params, X, n_seq, w.stash, yhat, w.status, w.prog, st);
   lstm_fwd_kernel<<<sm_count(), NT, smem, st>>>(d, params, X, n_seq, w.stash, yhat);
   DLAS_LAUNCH_CHECK();
   return DLAS_OK;
@@ -422,14 +424,14 @@ extern "C" int dlas_lstm_grad_mode(int mode, int d_in, int hidden, int n_layers,
   transpose_kernel<<<64, 256, 0, st>>>(d, params, w.KT);
   DLAS_LAUNCH_CHECK();
   if (bits & TC_FWD) {   // persistent recurrence on the tensor cores
-    rc = lstm_tc_fwd(d, params, X, n_seq, w.stash, w.yhat, w.status, st);
+    rc = lstm_tc_fwd(d, params, X, n_seq, w.stash, w.yhat, w.status, w.prog, st);
     if (rc != DLAS_OK) return rc;
   } else {
     lstm_fwd_kernel<<<grid, NT, smem, st>>>(d, params, X, n_seq, w.stash, w.yhat);
     DLAS_LAUNCH_CHECK();
   }
   if (bits & TC_BWD) {   // loss + head gradient, then the backward recurrence on the tensor cores
-    rc = lstm_tc_bwd(d, loss, params, y, w.yhat, n_seq, w.stash, w.dseqP, w.partials, grid, w.status, st);
+    rc = lstm_tc_bwd(d, loss, params, y, w.yhat, n_seq, w.stash, w.dseqP, w.partials, grid, w.status, w.prog, st);
     if (rc != DLAS_OK) return rc;
   } else {
     lstm_bwd_kernel<<<grid, NT, smem, st>>>(d, loss, params, w.KT, y, w.yhat, n_seq, w.stash, w.dseq, w.partials);

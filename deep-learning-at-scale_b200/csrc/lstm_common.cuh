@@ -76,5 +76,21 @@ __device__ __forceinline__ size_t didx(const LstmDesc& d, size_t seq, int t, int
   return slab + (((seq >> 5) * 4 + ((unit >> 2) & 3)) * 32 + (seq & 31)) * 4 + (unit & 3);
 }
 
+// Layer pipeline of the tensor-core recurrences: the CTA pair of layer l publishes how far it is (one arrival per epilogue
+// warp and step, release at gpu scope after the warp's stores), the pair of the layer that consumes its sequence polls the
+// counter (acquire) a round before it needs the data.  Producers have the lower block indices, so a waiting CTA's producer
+// has always been scheduled; the poll is bounded all the same (false = timed out, the caller raises the error word).
+__device__ __forceinline__ void prog_arrive(unsigned* p) { asm volatile("red.release.gpu.global.add.u32 [%0], 1;" ::"l"(p) : "memory"); }
+__device__ __forceinline__ bool prog_wait(const unsigned* p, unsigned target) {
+  for (unsigned spin = 0; spin < (1u << 23); ++spin) {
+    unsigned v;
+    asm volatile("ld.acquire.gpu.global.u32 %0, [%1];" : "=r"(v) : "l"(p) : "memory");
+    if (v >= target) return true;
+    __nanosleep(64);
+  }
+  return false;
+}
+constexpr unsigned PROG_WARPS = 32;   // epilogue warps of a pair = arrivals per step
+
 }  // namespace lstm
 }  // namespace dlas

@@ -64,7 +64,10 @@ lstm_head_grad_kernel(const LstmDesc d, const int loss, const float* __restrict_
 template <bool FAST>
 __global__ void __cluster_dims__(2, 1, 1) __launch_bounds__(NT, 1)
 lstm_bwd_tc_kernel(const LstmDesc d, const float* __restrict__ params, float* __restrict__ stash, const float* __restrict__ dy,
-                   float* __restrict__ dseqP, const size_t n_seq, unsigned* __restrict__ err_flag, const unsigned call_id) {
+                   float* __restrict__ dseqP, const size_t n_seq, unsigned* __restrict__ err_flag, const unsigned call_id,
+                   unsigned* __restrict__ prog) {
+  // Layer pipeline (as in lstm_tc_fwd.cu, top layer first): pair p works on layer L-1 - p / n_lanes of the tiles lane,
+  // lane + n_lanes, ...; a layer reads the dx partials of the layer above as soon as that pair has published the step.
   extern __shared__ __align__(1024) uint8_t smem[];
   uint64_t* bars = reinterpret_cast<uint64_t*>(smem + S_BAR);
   uint32_t* tmem_slot = reinterpret_cast<uint32_t*>(smem + S_TMEM);
@@ -100,12 +103,15 @@ lstm_bwd_tc_kernel(const LstmDesc d, const float* __restrict__ params, float* __
   const uint32_t lane_base = (uint32_t)(q4 * 32) << 16;
   const int u0 = UH * (int)rank + hh * UT;                // first of this thread's 16 units
 
-  for (size_t tile = pair; tile < n_tiles; tile += n_pairs) {
+  const int n_lanes = n_pairs / d.L, my_layer = d.L - 1 - pair / n_lanes;
+  for (size_t tile = pair % n_lanes; tile < n_tiles; tile += n_lanes) {
     const size_t seq = tile * TS + row;
     const bool valid = (warp < ISSUER_WARP) && seq < n_seq;
     const size_t sq = valid ? seq : 0;
     const StashPos sp = stash_pos(d, sq);
-    for (int l = d.L - 1; l >= 0; --l) {
+    unsigned* const prog_mine = prog + tile * d.L + my_layer;                           // dx steps this pair has published
+    const unsigned* const prog_above = prog_mine + (my_layer + 1 < d.L ? 1 : 0);        // ... and the layer above
+    for (int l = my_layer; l == my_layer; --l) {
       const int dl = d.d_l[l], xw = xw_of(l), nk = xw + HT;
       float* dsW = dseqP + (size_t)(n_sets == 2 ? (l & 1) : 0) * 2 * pstr;              // this layer's dx partials
       const float* dsR = dseqP + (size_t)(n_sets == 2 ? ((l + 1) & 1) : 0) * 2 * pstr;  // the layer above's
@@ -154,6 +160,10 @@ lstm_bwd_tc_kernel(const LstmDesc d, const float* __restrict__ params, float* __
             for (int c = 0; c < 5; ++c) prefetch_l2(stash + sidx<FAST>(d, sp, sq, l, t - 1, c, u0));
             if (t > 1) prefetch_l2(stash + sidx<FAST>(d, sp, sq, l, t - 2, 4, u0));
             if (l < d.L - 1) { prefetch_l2(dsR + didx<FAST>(d, sp, sq, t - 1, u0)); prefetch_l2(dsR + pstr + didx<FAST>(d, sp, sq, t - 1, u0)); }
+          }
+          if (l < d.L - 1) {     // dx of step t from the layer above (read below, after the exchange): polled here, under the MMA
+            if (lane == 0) ok = prog_wait(prog_above, PROG_WARPS * (unsigned)(T - t)) && ok;
+            __syncwarp();
           }
           // ---- what the previous round's MMA (step t+1) produced: dx partial, my units' dh partial, the peer's units'
           if (!first) {
@@ -269,6 +279,9 @@ lstm_bwd_tc_kernel(const LstmDesc d, const float* __restrict__ params, float* __
           fence_async_smem();
           __syncwarp();
           if (lane == 0) mbar_arrive(&bars[B_A]);
+          if (l > 0 && !first) {   // dx of step t+1 (stored at the top of this round) -> the pair of the layer below
+            if (lane == 0) prog_arrive(prog_mine);
+          }
         }
         // ---- the layer's last MMA (step 0): only its dx columns are needed (layers above 0) ----
         ok = mbar_wait(&bars[B_Z], (q - 1) & 1) && ok;
@@ -285,6 +298,8 @@ lstm_bwd_tc_kernel(const LstmDesc d, const float* __restrict__ params, float* __
               if (valid) *reinterpret_cast<float4*>(dst + didx<FAST>(d, sp, sq, 0, hh * 32 + j4 * 4)) = make_float4(__uint_as_float(v[j4 * 4]), __uint_as_float(v[j4 * 4 + 1]),
                                                                              __uint_as_float(v[j4 * 4 + 2]), __uint_as_float(v[j4 * 4 + 3]));
           }
+          __syncwarp();
+          if (lane == 0) prog_arrive(prog_mine);       // dx of step 0: T arrivals per warp in all
         }
         fence_before();
       }
@@ -306,7 +321,7 @@ extern unsigned g_lstm_call_id;   // lstm_tc.cu
 
 // loss, head gradient and full BPTT: dz into the stash (comps 0..3), head entries + loss sum into the per-block partials
 int lstm_tc_bwd(const lstm::LstmDesc& d, int loss, const float* params, const float* y, float* yhat_dy, size_t n_seq,
-                float* stash, float* dseqP, float* partials, int n_blocks, unsigned* err_flag, cudaStream_t st) {
+                float* stash, float* dseqP, float* partials, int n_blocks, unsigned* err_flag, unsigned* prog, cudaStream_t st) {
   static bool attr_set[64] = {};
   int dev = 0;
   DLAS_CUDA(cudaGetDevice(&dev));
@@ -319,10 +334,12 @@ int lstm_tc_bwd(const lstm::LstmDesc& d, int loss, const float* params, const fl
   lstm_head_grad_kernel<<<n_blocks, 256, 0, st>>>(d, loss, y, yhat_dy, stash, n_seq, partials);
   DLAS_LAUNCH_CHECK();
   const size_t n_tiles = (n_seq + TS - 1) / TS;
-  const int max_pairs = sm_count() / 2;
-  const int pairs = (int)(n_tiles < (size_t)max_pairs ? n_tiles : (size_t)max_pairs);
-  if (d.fast) lstm_bwd_tc_kernel<true><<<2 * pairs, NT, SMEM_BYTES, st>>>(d, params, stash, yhat_dy, dseqP, n_seq, err_flag, g_lstm_call_id);
-  else lstm_bwd_tc_kernel<false><<<2 * pairs, NT, SMEM_BYTES, st>>>(d, params, stash, yhat_dy, dseqP, n_seq, err_flag, g_lstm_call_id);
+  const int max_lanes = (sm_count() / 2) / d.L;
+  if (max_lanes < 1) { set_error("lstm (tc): %d layers need more SM pairs than this GPU has", d.L); return DLAS_ERR_UNSUPPORTED_SHAPE; }
+  const int pairs = (int)(n_tiles < (size_t)max_lanes ? n_tiles : (size_t)max_lanes) * d.L;
+  DLAS_CUDA(cudaMemsetAsync(prog, 0, n_tiles * d.L * sizeof(unsigned), st));
+  if (d.fast) lstm_bwd_tc_kernel<true><<<2 * pairs, NT, SMEM_BYTES, st>>>(d, params, stash, yhat_dy, dseqP, n_seq, err_flag, g_lstm_call_id, prog);
+  else lstm_bwd_tc_kernel<false><<<2 * pairs, NT, SMEM_BYTES, st>>>(d, params, stash, yhat_dy, dseqP, n_seq, err_flag, g_lstm_call_id, prog);
   DLAS_LAUNCH_CHECK();
   return DLAS_OK;
 }

@@ -35,7 +35,10 @@ __device__ __forceinline__ float tanh_(float x) { return 2.0f * sigm(2.0f * x) -
 template <bool FAST>
 __global__ void __cluster_dims__(2, 1, 1) __launch_bounds__(NT, 1)
 lstm_fwd_tc_kernel(const LstmDesc d, const float* __restrict__ params, const float* __restrict__ X, const size_t n_seq,
-                   float* __restrict__ stash, unsigned* __restrict__ err_flag, const unsigned call_id) {
+                   float* __restrict__ stash, unsigned* __restrict__ err_flag, const unsigned call_id, unsigned* __restrict__ prog) {
+  // Layer pipeline: the grid is n_lanes x L pairs; pair p works on layer p / n_lanes of the tiles lane, lane + n_lanes, ...
+  // Layer l reads h of layer l-1 from the stash as soon as that pair has published the step (prog[tile * L + l - 1]), so the
+  // layers of one tile run one step apart on different SM pairs instead of one after the other on the same pair.
   extern __shared__ __align__(1024) uint8_t smem[];
   float* bias = reinterpret_cast<float*>(smem + S_F32);
   uint64_t* bars = reinterpret_cast<uint64_t*>(smem + S_BAR);
@@ -68,11 +71,14 @@ lstm_fwd_tc_kernel(const LstmDesc d, const float* __restrict__ params, const flo
   const int row = q4 * 32 + lane;
   const uint32_t lane_base = (uint32_t)(q4 * 32) << 16;
 
-  for (size_t tile = pair; tile < n_tiles; tile += n_pairs) {
+  const int n_lanes = n_pairs / d.L, my_layer = pair / n_lanes;
+  for (size_t tile = pair % n_lanes; tile < n_tiles; tile += n_lanes) {
     const size_t seq = tile * TS + row;
     const bool valid = (warp < ISSUER_WARP) && seq < n_seq;
     const StashPos sp = stash_pos(d, valid ? seq : 0);
-    for (int l = 0; l < d.L; ++l) {
+    unsigned* const prog_mine = prog + tile * d.L + my_layer;          // published by this pair (layers below the top)
+    const unsigned* const prog_below = prog_mine - (my_layer > 0 ? 1 : 0);                   // polled by layers above the first
+    for (int l = my_layer; l == my_layer; ++l) {
       const int dl = d.d_l[l], xw = xw_of(l), nk = xw + HT;
       // ---- this layer's weights -> fp16 tile: row n of [x | h] (n < xw: input row n, zero beyond d_l; else recurrent row),
       // column g*64 + u = gate g of this CTA's unit u.  Everybody is past the previous layer here (barrier below).
@@ -121,6 +127,10 @@ lstm_fwd_tc_kernel(const LstmDesc d, const float* __restrict__ params, const flo
         for (int j = 0; j < UT; ++j) c_state[j] = 0.f;
 #pragma unroll
         for (int c8 = 0; c8 < 4; ++c8) sts128(sA + tile_chunk_off(TS, row, xw + hh * 32 + c8 * 8), make_uint4(0u, 0u, 0u, 0u));
+        if (l > 0) {                       // step 0 of the layer below has been published
+          if (lane == 0) ok = prog_wait(prog_below, PROG_WARPS) && ok;
+          __syncwarp();
+        }
         x_store(0);
       }
       fence_async_smem();
@@ -154,6 +164,10 @@ lstm_fwd_tc_kernel(const LstmDesc d, const float* __restrict__ params, const flo
           if (l > 0 && valid && t + 2 < T) {
             prefetch_l2(stash + sidx<FAST>(d, sp, seq, l - 1, t + 2, 5, hh * 32));
             if (FAST) prefetch_l2(stash + sidx<FAST>(d, sp, seq, l - 1, t + 2, 5, hh * 32 + 16));
+          }
+          if (l > 0 && t + 1 < T) {        // step t+1 of the layer below (read at the end of this round): polled here, under the MMA
+            if (lane == 0) ok = prog_wait(prog_below, PROG_WARPS * (unsigned)(t + 2)) && ok;
+            __syncwarp();
           }
           ok = mbar_wait(&bars[B_Z], q & 1) && ok;
           fence_after();
@@ -215,6 +229,10 @@ lstm_fwd_tc_kernel(const LstmDesc d, const float* __restrict__ params, const flo
             __syncwarp();
             if (lane == 0) { mbar_arrive(&bars[B_A]); mbar_arrive_remote(peer_PH); }
           }
+          if (l + 1 < d.L) {               // publish h_t to the pair of the layer above; the release waits for this warp's stash
+            __syncwarp();                  // stores, after the recurrence's own hand-over so that it does not sit in its way
+            if (lane == 0) prog_arrive(prog_mine);
+          }
         }
       }
       // everybody of this CTA is past the layer's last round before the weights / A tile are rewritten
@@ -251,7 +269,7 @@ extern unsigned g_lstm_call_id;   // lstm_tc.cu
 
 // forward over all layers and steps: fills the stash (i, f, g, o, c, h per sequence, layer, step) and yhat
 int lstm_tc_fwd(const lstm::LstmDesc& d, const float* params, const float* X, size_t n_seq, float* stash, float* yhat,
-                unsigned* err_flag, cudaStream_t st) {
+                unsigned* err_flag, unsigned* prog, cudaStream_t st) {
   static bool attr_set[64] = {};
   int dev = 0;
   DLAS_CUDA(cudaGetDevice(&dev));
@@ -262,10 +280,12 @@ int lstm_tc_fwd(const lstm::LstmDesc& d, const float* params, const float* X, si
   }
   ++g_lstm_call_id;
   const size_t n_tiles = (n_seq + TS - 1) / TS;
-  const int max_pairs = sm_count() / 2;
-  const int pairs = (int)(n_tiles < (size_t)max_pairs ? n_tiles : (size_t)max_pairs);
-  if (d.fast) lstm_fwd_tc_kernel<true><<<2 * pairs, NT, SMEM_BYTES, st>>>(d, params, X, n_seq, stash, err_flag, g_lstm_call_id);
-  else lstm_fwd_tc_kernel<false><<<2 * pairs, NT, SMEM_BYTES, st>>>(d, params, X, n_seq, stash, err_flag, g_lstm_call_id);
+  const int max_lanes = (sm_count() / 2) / d.L;          // a lane = the L pairs (one per layer) that share a tile
+  if (max_lanes < 1) { set_error("lstm (tc): %d layers need more SM pairs than this GPU has", d.L); return DLAS_ERR_UNSUPPORTED_SHAPE; }
+  const int pairs = (int)(n_tiles < (size_t)max_lanes ? n_tiles : (size_t)max_lanes) * d.L;
+  DLAS_CUDA(cudaMemsetAsync(prog, 0, n_tiles * d.L * sizeof(unsigned), st));
+  if (d.fast) lstm_fwd_tc_kernel<true><<<2 * pairs, NT, SMEM_BYTES, st>>>(d, params, X, n_seq, stash, err_flag, g_lstm_call_id, prog);
+  else lstm_fwd_tc_kernel<false><<<2 * pairs, NT, SMEM_BYTES, st>>>(d, params, X, n_seq, stash, err_flag, g_lstm_call_id, prog);
   DLAS_LAUNCH_CHECK();
   lstm_head_kernel<<<(unsigned)((n_seq + 7) / 8), 256, 0, st>>>(d, params, stash, n_seq, err_flag, g_lstm_call_id, yhat);
   DLAS_LAUNCH_CHECK();

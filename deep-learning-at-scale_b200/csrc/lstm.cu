@@ -22,11 +22,11 @@ namespace dlas {
 bool lstm_tc_supported(const lstm::LstmDesc& d);
 size_t lstm_tc_dw_partial_floats(const lstm::LstmDesc& d);
 int lstm_tc_fwd(const lstm::LstmDesc& d, const float* params, const float* X, size_t n_seq, float* stash, float* yhat,
-                unsigned* err_flag, unsigned* prog, cudaStream_t st);
+                unsigned* err_flag, unsigned* prog, uint16_t* h16, cudaStream_t st);
 int lstm_tc_bwd(const lstm::LstmDesc& d, int loss, const float* params, const float* y, float* yhat_dy, size_t n_seq,
-                float* stash, float* dseqP, float* partials, int n_blocks, unsigned* err_flag, unsigned* prog, cudaStream_t st);
+                float* stash, float* dseqP, float* partials, int n_blocks, unsigned* err_flag, unsigned* prog, uint16_t* dz16, cudaStream_t st);
 int lstm_tc_dw(const lstm::LstmDesc& d, const float* X, const float* stash, size_t n_seq, float* grad_sum, float* tc_partials,
-               unsigned* err_flag, cudaStream_t st);
+               unsigned* err_flag, const uint16_t* h16, const uint16_t* dz16, cudaStream_t st);
 
 namespace {
 using namespace lstm;
@@ -277,7 +277,7 @@ lstm_reduce_kernel(const float* __restrict__ partials, size_t stride, int n_acti
   out[i0 + i] = s;
 }
 
-struct Ws { float *stash, *dseq, *KT, *partials, *yhat, *tcp, *dseqP; unsigned *status, *prog; size_t bytes; };
+struct Ws { float *stash, *dseq, *KT, *partials, *yhat, *tcp, *dseqP; unsigned *status, *prog; uint16_t *h16, *dz16; size_t bytes; };
 Ws carve_ws(const LstmDesc& d, size_t n_seq, void* base) {
   Ws w;
   size_t o = 0;
@@ -294,6 +294,9 @@ Ws carve_ws(const LstmDesc& d, size_t n_seq, void* base) {
   w.status = reinterpret_cast<unsigned*>(take(64));                              // status words of the tensor-core kernels
   // layer pipeline of the tensor-core recurrences: one progress counter per (128-sequence tile, layer)
   w.prog = reinterpret_cast<unsigned*>(take(lstm_tc_supported(d) ? ((n_seq + 127) / 128) * (size_t)d.L : 0));
+  // all-tensor-core step: h and dz as fp16 operands (lstm_common.cuh idx16), halves counted as half floats
+  w.h16 = reinterpret_cast<uint16_t*>(take(lstm_tc_supported(d) ? n_pad * d.L * d.T * (size_t)d.H / 2 : 0));
+  w.dz16 = reinterpret_cast<uint16_t*>(take(lstm_tc_supported(d) ? n_pad * d.L * d.T * 4 * (size_t)d.H / 2 : 0));
   w.bytes = o * sizeof(float);
   return w;
 }
@@ -368,7 +371,7 @@ extern "C" int dlas_lstm_predict_mode(int mode, int d_in, int hidden, int n_laye
   size_t smem = rec_smem_bytes(d);
   rc = set_smem(lstm_fwd_kernel, smem);
   if (rc != DLAS_OK) return rc;
-  if (bits & TC_FWD) return lstm_tc_fwd(d, params, X, n_seq, w.stash, yhat, w.status, w.prog, st);
+  if (bits & TC_FWD) return lstm_tc_fwd(d, params, X, n_seq, w.stash, yhat, w.status, w.prog, w.h16, st);
   lstm_fwd_kernel<<<sm_count(), NT, smem, st>>>(d, params, X, n_seq, w.stash, yhat);
   DLAS_LAUNCH_CHECK();
   return DLAS_OK;
@@ -421,17 +424,19 @@ extern "C" int dlas_lstm_grad_mode(int mode, int d_in, int hidden, int n_layers,
   size_t smem_dw = (size_t)((dmax + d.H) + 4 * d.H) * DRS * sizeof(float);
   rc = set_smem(lstm_dw_kernel, smem_dw);
   if (rc != DLAS_OK) return rc;
-  transpose_kernel<<<64, 256, 0, st>>>(d, params, w.KT);
-  DLAS_LAUNCH_CHECK();
+  if (!(bits & TC_BWD)) {       // K^T for the fp32 backward recurrence
+    transpose_kernel<<<64, 256, 0, st>>>(d, params, w.KT);
+    DLAS_LAUNCH_CHECK();
+  }
   if (bits & TC_FWD) {   // persistent recurrence on the tensor cores
-    rc = lstm_tc_fwd(d, params, X, n_seq, w.stash, w.yhat, w.status, w.prog, st);
+    rc = lstm_tc_fwd(d, params, X, n_seq, w.stash, w.yhat, w.status, w.prog, w.h16, st);
     if (rc != DLAS_OK) return rc;
   } else {
     lstm_fwd_kernel<<<grid, NT, smem, st>>>(d, params, X, n_seq, w.stash, w.yhat);
     DLAS_LAUNCH_CHECK();
   }
   if (bits & TC_BWD) {   // loss + head gradient, then the backward recurrence on the tensor cores
-    rc = lstm_tc_bwd(d, loss, params, y, w.yhat, n_seq, w.stash, w.dseqP, w.partials, grid, w.status, w.prog, st);
+    rc = lstm_tc_bwd(d, loss, params, y, w.yhat, n_seq, w.stash, w.dseqP, w.partials, grid, w.status, w.prog, w.dz16, st);
     if (rc != DLAS_OK) return rc;
   } else {
     lstm_bwd_kernel<<<grid, NT, smem, st>>>(d, loss, params, w.KT, y, w.yhat, n_seq, w.stash, w.dseq, w.partials);
@@ -439,7 +444,7 @@ extern "C" int dlas_lstm_grad_mode(int mode, int d_in, int hidden, int n_layers,
   }
   size_t n_layer_params = (size_t)d.hw_off;
   if (bits & TC_DW) {   // weight gradient as a tcgen05 GEMM over all (sequence, t) rows
-    rc = lstm_tc_dw(d, X, w.stash, n_seq, grad_sum, w.tcp, w.status, st);
+    rc = lstm_tc_dw(d, X, w.stash, n_seq, grad_sum, w.tcp, w.status, w.h16, w.dz16, st);
     if (rc != DLAS_OK) return rc;
   } else {
     lstm_dw_kernel<<<grid, NT, smem_dw, st>>>(d, X, w.stash, n_seq, w.partials);

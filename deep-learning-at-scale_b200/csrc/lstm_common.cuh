@@ -46,13 +46,21 @@ __device__ __forceinline__ size_t stash_idx(const LstmDesc& d, size_t seq, int l
 // step runs on the tensor cores) is [l][t][comp][16-unit group][sequence block of 32][4 x float4][32 sequences][4]: the
 // warp's lanes then read / write 512 contiguous bytes per instruction.  `unit` is a multiple of 4 for the float4 form.
 struct StashPos {     // the per-sequence part of a fast-layout address, computed once per thread and tile / chunk
-  size_t inner, ugs;
+  size_t inner, ugs, inner16;
 };
 __device__ __forceinline__ StashPos stash_pos(const LstmDesc& d, size_t seq) {
   StashPos p;
   p.inner = (((seq >> 5) * 4) * 32 + (seq & 31)) * 4;
   p.ugs = d.n_pad * 16;
+  p.inner16 = (seq >> 5) * 512 + (seq & 31) * 8;
   return p;
+}
+// fp16 side arrays of the all-tensor-core step (fast layout only): h of every (layer, step) and dz of every (layer, step,
+// gate) as the operands the next consumer needs -- the layer above's A tile, the weight-gradient GEMM -- so that nobody
+// re-reads fp32 to round it again.  Slab (one (l, t[, gate])) = [16-unit group][sequence block of 32][2 x 16 B][32 sequences]
+// [8 halves]: a warp's lanes touch 512 contiguous bytes per 16-byte access.  Index in halves; `unit` a multiple of 8.
+__device__ __forceinline__ size_t idx16(const StashPos& p, size_t slab, int unit) {
+  return (slab * 8 + (size_t)(unit >> 4)) * p.ugs + p.inner16 + (size_t)((((unit >> 3) & 1) << 8) + (unit & 7));
 }
 template <bool FAST>
 __device__ __forceinline__ size_t sidx(const LstmDesc& d, const StashPos& p, size_t seq, int l, int t, int comp, int unit) {

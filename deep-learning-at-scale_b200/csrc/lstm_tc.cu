@@ -37,7 +37,10 @@ constexpr int PART = 256 * 128 + 128;   // floats per (layer, CTA) partial: [k 0
 template <bool FAST>
 __global__ void __launch_bounds__(dw::NT, 1)
 lstm_dw_tc_kernel(const LstmDesc d, const float* __restrict__ X, const float* __restrict__ stash, const size_t n_seq,
-                  float* __restrict__ partials, unsigned* __restrict__ err_flag, const unsigned call_id) {
+                  float* __restrict__ partials, unsigned* __restrict__ err_flag, const unsigned call_id,
+                  const uint16_t* __restrict__ h16, const uint16_t* __restrict__ dz16) {
+  // FAST: both operands come as fp16 from the side arrays the recurrences wrote (h16, dz16: lstm_common.cuh), 16-byte
+  // chunks copied into the swizzled tiles as they are.
   using namespace dw;
   extern __shared__ __align__(1024) uint8_t smem[];
   uint64_t* bars = reinterpret_cast<uint64_t*>(smem + S_BAR);
@@ -117,7 +120,14 @@ lstm_dw_tc_kernel(const LstmDesc d, const float* __restrict__ X, const float* __
         const StashPos sp = stash_pos(d, seq);
         if (u >= 2) ok = mbar_wait(&bars[B_FREE0 + b], ((u >> 1) - 1) & 1) && ok;   // the MMAs of use u-2 have read this buffer
         const uint32_t tDZ = sDZ + b * 32768, tA = sA + b * 65536;
-        {  // dz: 64 floats of gate jc
+        if (FAST) {   // dz: 64 halves of gate jc
+          uint4 v[8];
+#pragma unroll
+          for (int q = 0; q < 8; ++q)
+            v[q] = in ? __ldcs(reinterpret_cast<const uint4*>(dz16 + idx16(sp, ((size_t)l * T + t) * 4 + jc, half * 64 + q * 8))) : make_uint4(0u, 0u, 0u, 0u);
+#pragma unroll
+          for (int q = 0; q < 8; ++q) sts128(tDZ + tile_chunk_off(CH, r, half * 64 + q * 8), v[q]);
+        } else {      // dz: 64 floats of gate jc
 #pragma unroll
           for (int q = 0; q < 8; ++q) {
             float4 a = make_float4(0.f, 0.f, 0.f, 0.f), e = a;
@@ -140,15 +150,27 @@ lstm_dw_tc_kernel(const LstmDesc d, const float* __restrict__ X, const float* __
           const bool have = in && (half == 0 || t > 0);
           const int sl = (half == 0) ? l - 1 : l, stt = (half == 0) ? t : (t > 0 ? t - 1 : 0);
           const int c0 = (half == 0) ? 0 : xw;
+          if (FAST) {
 #pragma unroll
-          for (int q = 0; q < 16; ++q) {
-            float4 a = make_float4(0.f, 0.f, 0.f, 0.f), e = a;
-            if (have) {
-              a = __ldg(reinterpret_cast<const float4*>(stash + sidx<FAST>(d, sp, seq, sl, stt, 5, q * 8)));
-              e = __ldg(reinterpret_cast<const float4*>(stash + sidx<FAST>(d, sp, seq, sl, stt, 5, q * 8 + 4)));
+            for (int q0 = 0; q0 < 16; q0 += 8) {
+              uint4 v[8];
+#pragma unroll
+              for (int q = 0; q < 8; ++q)
+                v[q] = have ? __ldg(reinterpret_cast<const uint4*>(h16 + idx16(sp, (size_t)sl * T + stt, (q0 + q) * 8))) : make_uint4(0u, 0u, 0u, 0u);
+#pragma unroll
+              for (int q = 0; q < 8; ++q) sts128(tA + tile_chunk_off(CH, r, c0 + (q0 + q) * 8), v[q]);
             }
-            sts128(tA + tile_chunk_off(CH, r, c0 + q * 8),
-                   make_uint4(pack_half2(a.x, a.y), pack_half2(a.z, a.w), pack_half2(e.x, e.y), pack_half2(e.z, e.w)));
+          } else {
+#pragma unroll
+            for (int q = 0; q < 16; ++q) {
+              float4 a = make_float4(0.f, 0.f, 0.f, 0.f), e = a;
+              if (have) {
+                a = __ldg(reinterpret_cast<const float4*>(stash + sidx<FAST>(d, sp, seq, sl, stt, 5, q * 8)));
+                e = __ldg(reinterpret_cast<const float4*>(stash + sidx<FAST>(d, sp, seq, sl, stt, 5, q * 8 + 4)));
+              }
+              sts128(tA + tile_chunk_off(CH, r, c0 + q * 8),
+                     make_uint4(pack_half2(a.x, a.y), pack_half2(a.z, a.w), pack_half2(e.x, e.y), pack_half2(e.z, e.w)));
+            }
           }
         }
         fence_async_smem();
@@ -225,7 +247,7 @@ unsigned g_lstm_call_id = 0x5eed0000u;
 
 // dK_l, db_l of every layer from X and the stash (h in comp 5, dz in comps 0..3) into grad_sum[0 .. hw_off)
 int lstm_tc_dw(const lstm::LstmDesc& d, const float* X, const float* stash, size_t n_seq, float* grad_sum, float* tc_partials,
-               unsigned* err_flag, cudaStream_t st) {
+               unsigned* err_flag, const uint16_t* h16, const uint16_t* dz16, cudaStream_t st) {
   static bool attr_set[64] = {};
   int dev = 0;
   DLAS_CUDA(cudaGetDevice(&dev));
@@ -236,8 +258,8 @@ int lstm_tc_dw(const lstm::LstmDesc& d, const float* X, const float* stash, size
   }
   ++g_lstm_call_id;
   const int grid = lstm_tc_ctas();
-  if (d.fast) lstm_dw_tc_kernel<true><<<grid, dw::NT, dw::SMEM_BYTES, st>>>(d, X, stash, n_seq, tc_partials, err_flag, g_lstm_call_id);
-  else lstm_dw_tc_kernel<false><<<grid, dw::NT, dw::SMEM_BYTES, st>>>(d, X, stash, n_seq, tc_partials, err_flag, g_lstm_call_id);
+  if (d.fast) lstm_dw_tc_kernel<true><<<grid, dw::NT, dw::SMEM_BYTES, st>>>(d, X, stash, n_seq, tc_partials, err_flag, g_lstm_call_id, h16, dz16);
+  else lstm_dw_tc_kernel<false><<<grid, dw::NT, dw::SMEM_BYTES, st>>>(d, X, stash, n_seq, tc_partials, err_flag, g_lstm_call_id, h16, dz16);
   DLAS_LAUNCH_CHECK();
   const int max_rows = 2 * HT + 1;
   dim3 rg((unsigned)((max_rows * 4 * HT + 255) / 256), (unsigned)d.L);

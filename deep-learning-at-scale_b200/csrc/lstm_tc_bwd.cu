@@ -44,17 +44,32 @@ lstm_head_grad_kernel(const LstmDesc d, const int loss, const float* __restrict_
                       const float* __restrict__ stash, const size_t n_seq, float* __restrict__ partials) {
   float* my = partials + (size_t)blockIdx.x * pstride(d.n_params);
   const int u = threadIdx.x;
+  __shared__ float g_sh[256], lo_sh[256];
   float acc = 0.f;
-  for (size_t s = blockIdx.x; s < n_seq; s += gridDim.x) {
-    const float dd = yhat_dy[s] - y[s];
-    float g, lo;
-    if (loss == DLAS_LOSS_MSE) { lo = dd * dd; g = 2.0f * dd; }
-    else { const float a = fabsf(dd); lo = fminf(a, 6.0f); g = (a <= 6.0f) ? (dd > 0.0f ? 1.0f : (dd < 0.0f ? -1.0f : 0.0f)) : 0.0f; }
-    if (u < d.H) acc += stash[sidx(d, s, d.L - 1, d.T - 1, 5, u)] * g;
-    else if (u == d.H) acc += g;
-    else if (u == d.H + 1) acc += lo;
-    __syncthreads();                    // every thread has read yhat[s] before it becomes dy[s]
-    if (u == 0) yhat_dy[s] = g;
+  // the block's sequences in order, 256 at a time: thread j first turns yhat of sequence j into dy (and keeps g, the loss
+  // term), then thread u < H adds h[u] * g over them -- loads that do not depend on each other
+  for (size_t base = blockIdx.x; base < n_seq; base += (size_t)gridDim.x * 256) {
+    const size_t s = base + (size_t)u * gridDim.x;
+    float g = 0.f, lo = 0.f;
+    if (s < n_seq) {
+      const float dd = yhat_dy[s] - y[s];
+      if (loss == DLAS_LOSS_MSE) { lo = dd * dd; g = 2.0f * dd; }
+      else { const float a = fabsf(dd); lo = fminf(a, 6.0f); g = (a <= 6.0f) ? (dd > 0.0f ? 1.0f : (dd < 0.0f ? -1.0f : 0.0f)) : 0.0f; }
+      yhat_dy[s] = g;
+    }
+    g_sh[u] = g; lo_sh[u] = lo;
+    __syncthreads();
+    const size_t left = (n_seq - base + gridDim.x - 1) / gridDim.x;
+    const int cnt = (int)(left < 256 ? left : 256);
+    if (u < d.H) {
+#pragma unroll 4
+      for (int j = 0; j < cnt; ++j) acc += stash[sidx(d, base + (size_t)j * gridDim.x, d.L - 1, d.T - 1, 5, u)] * g_sh[j];
+    } else if (u == d.H) {
+      for (int j = 0; j < cnt; ++j) acc += g_sh[j];
+    } else if (u == d.H + 1) {
+      for (int j = 0; j < cnt; ++j) acc += lo_sh[j];
+    }
+    __syncthreads();
   }
   if (u < d.H) my[d.hw_off + u] = acc;
   else if (u == d.H) my[d.hb_off] = acc;
@@ -65,7 +80,9 @@ template <bool FAST>
 __global__ void __cluster_dims__(2, 1, 1) __launch_bounds__(NT, 1)
 lstm_bwd_tc_kernel(const LstmDesc d, const float* __restrict__ params, float* __restrict__ stash, const float* __restrict__ dy,
                    float* __restrict__ dseqP, const size_t n_seq, unsigned* __restrict__ err_flag, const unsigned call_id,
-                   unsigned* __restrict__ prog) {
+                   unsigned* __restrict__ prog, uint16_t* __restrict__ dz16) {
+  // FAST: dz leaves as fp16 (dz16, lstm_common.cuh) -- the operand the weight-gradient GEMM takes -- instead of overwriting
+  // the fp32 gates of the stash.
   // Layer pipeline (as in lstm_tc_fwd.cu, top layer first): pair p works on layer L-1 - p / n_lanes of the tiles lane,
   // lane + n_lanes, ...; a layer reads the dx partials of the layer above as soon as that pair has published the step.
   extern __shared__ __align__(1024) uint8_t smem[];
@@ -259,7 +276,7 @@ lstm_bwd_tc_kernel(const LstmDesc d, const float* __restrict__ params, float* __
               zo[e] = dh * tc_ * go[e] * (1.0f - go[e]);
               dc_next[j] = dc * gf[e];
             }
-            if (valid) {   // dz overwrites the gates in the stash (fp32): the weight-gradient pass reads it
+            if (valid && !FAST) {   // dz overwrites the gates in the stash (fp32): the weight-gradient pass reads it
 #pragma unroll
               for (int h4 = 0; h4 < 2; ++h4) {
                 const int o = b8 * 8 + h4 * 4, e = h4 * 4;
@@ -271,10 +288,15 @@ lstm_bwd_tc_kernel(const LstmDesc d, const float* __restrict__ params, float* __
             }
             // fp16 A tile of the next MMA: column g*64 + (unit within this CTA)
             const int cu = hh * UT + b8 * 8;
-            sts128(sDZ + tile_chunk_off(TS, row, 0 * 64 + cu), make_uint4(pack_half2(zi[0], zi[1]), pack_half2(zi[2], zi[3]), pack_half2(zi[4], zi[5]), pack_half2(zi[6], zi[7])));
-            sts128(sDZ + tile_chunk_off(TS, row, 1 * 64 + cu), make_uint4(pack_half2(zf[0], zf[1]), pack_half2(zf[2], zf[3]), pack_half2(zf[4], zf[5]), pack_half2(zf[6], zf[7])));
-            sts128(sDZ + tile_chunk_off(TS, row, 2 * 64 + cu), make_uint4(pack_half2(zg[0], zg[1]), pack_half2(zg[2], zg[3]), pack_half2(zg[4], zg[5]), pack_half2(zg[6], zg[7])));
-            sts128(sDZ + tile_chunk_off(TS, row, 3 * 64 + cu), make_uint4(pack_half2(zo[0], zo[1]), pack_half2(zo[2], zo[3]), pack_half2(zo[4], zo[5]), pack_half2(zo[6], zo[7])));
+            const uint4 pz[4] = {make_uint4(pack_half2(zi[0], zi[1]), pack_half2(zi[2], zi[3]), pack_half2(zi[4], zi[5]), pack_half2(zi[6], zi[7])),
+                                 make_uint4(pack_half2(zf[0], zf[1]), pack_half2(zf[2], zf[3]), pack_half2(zf[4], zf[5]), pack_half2(zf[6], zf[7])),
+                                 make_uint4(pack_half2(zg[0], zg[1]), pack_half2(zg[2], zg[3]), pack_half2(zg[4], zg[5]), pack_half2(zg[6], zg[7])),
+                                 make_uint4(pack_half2(zo[0], zo[1]), pack_half2(zo[2], zo[3]), pack_half2(zo[4], zo[5]), pack_half2(zo[6], zo[7]))};
+#pragma unroll
+            for (int g = 0; g < 4; ++g) {
+              sts128(sDZ + tile_chunk_off(TS, row, g * 64 + cu), pz[g]);
+              if (FAST && valid) *reinterpret_cast<uint4*>(dz16 + idx16(sp, ((size_t)l * T + t) * 4 + g, u0 + b8 * 8)) = pz[g];
+            }
           }
           fence_async_smem();
           __syncwarp();
@@ -321,7 +343,7 @@ extern unsigned g_lstm_call_id;   // lstm_tc.cu
 
 // loss, head gradient and full BPTT: dz into the stash (comps 0..3), head entries + loss sum into the per-block partials
 int lstm_tc_bwd(const lstm::LstmDesc& d, int loss, const float* params, const float* y, float* yhat_dy, size_t n_seq,
-                float* stash, float* dseqP, float* partials, int n_blocks, unsigned* err_flag, unsigned* prog, cudaStream_t st) {
+                float* stash, float* dseqP, float* partials, int n_blocks, unsigned* err_flag, unsigned* prog, uint16_t* dz16, cudaStream_t st) {
   static bool attr_set[64] = {};
   int dev = 0;
   DLAS_CUDA(cudaGetDevice(&dev));
@@ -338,8 +360,8 @@ int lstm_tc_bwd(const lstm::LstmDesc& d, int loss, const float* params, const fl
   if (max_lanes < 1) { set_error("lstm (tc): %d layers need more SM pairs than this GPU has", d.L); return DLAS_ERR_UNSUPPORTED_SHAPE; }
   const int pairs = (int)(n_tiles < (size_t)max_lanes ? n_tiles : (size_t)max_lanes) * d.L;
   DLAS_CUDA(cudaMemsetAsync(prog, 0, n_tiles * d.L * sizeof(unsigned), st));
-  if (d.fast) lstm_bwd_tc_kernel<true><<<2 * pairs, NT, SMEM_BYTES, st>>>(d, params, stash, yhat_dy, dseqP, n_seq, err_flag, g_lstm_call_id, prog);
-  else lstm_bwd_tc_kernel<false><<<2 * pairs, NT, SMEM_BYTES, st>>>(d, params, stash, yhat_dy, dseqP, n_seq, err_flag, g_lstm_call_id, prog);
+  if (d.fast) lstm_bwd_tc_kernel<true><<<2 * pairs, NT, SMEM_BYTES, st>>>(d, params, stash, yhat_dy, dseqP, n_seq, err_flag, g_lstm_call_id, prog, dz16);
+  else lstm_bwd_tc_kernel<false><<<2 * pairs, NT, SMEM_BYTES, st>>>(d, params, stash, yhat_dy, dseqP, n_seq, err_flag, g_lstm_call_id, prog, dz16);
   DLAS_LAUNCH_CHECK();
   return DLAS_OK;
 }

@@ -35,7 +35,10 @@ __device__ __forceinline__ float tanh_(float x) { return 2.0f * sigm(2.0f * x) -
 template <bool FAST>
 __global__ void __cluster_dims__(2, 1, 1) __launch_bounds__(NT, 1)
 lstm_fwd_tc_kernel(const LstmDesc d, const float* __restrict__ params, const float* __restrict__ X, const size_t n_seq,
-                   float* __restrict__ stash, unsigned* __restrict__ err_flag, const unsigned call_id, unsigned* __restrict__ prog) {
+                   float* __restrict__ stash, unsigned* __restrict__ err_flag, const unsigned call_id, unsigned* __restrict__ prog,
+                   uint16_t* __restrict__ h16) {
+  // FAST (every stage of the step on the tensor cores): h goes out as fp16 (h16, lstm_common.cuh) for the layer above and the
+  // weight-gradient GEMM; the fp32 h of the stash is written for the head only (top layer, last step).
   // Layer pipeline: the grid is n_lanes x L pairs; pair p works on layer p / n_lanes of the tiles lane, lane + n_lanes, ...
   // Layer l reads h of layer l-1 from the stash as soon as that pair has published the step (prog[tile * L + l - 1]), so the
   // layers of one tile run one step apart on different SM pairs instead of one after the other on the same pair.
@@ -108,6 +111,13 @@ lstm_fwd_tc_kernel(const LstmDesc d, const float* __restrict__ params, const flo
             sts128(sA + tile_chunk_off(TS, row, 0), make_uint4(pack_half2(xv[0], xv[1]), pack_half2(xv[2], xv[3]), pack_half2(xv[4], xv[5]), pack_half2(xv[6], xv[7])));
             sts128(sA + tile_chunk_off(TS, row, 8), make_uint4(pack_half2(xv[8], xv[9]), pack_half2(xv[10], xv[11]), pack_half2(xv[12], xv[13]), pack_half2(xv[14], xv[15])));
           }
+        } else if (FAST) {
+#pragma unroll
+          for (int c8 = 0; c8 < 4; ++c8) {
+            uint4 o = make_uint4(0u, 0u, 0u, 0u);
+            if (valid) o = __ldcg(reinterpret_cast<const uint4*>(h16 + idx16(sp, (size_t)(l - 1) * T + t, hh * 32 + c8 * 8)));
+            sts128(sA + tile_chunk_off(TS, row, hh * 32 + c8 * 8), o);
+          }
         } else {
 #pragma unroll
           for (int c8 = 0; c8 < 4; ++c8) {
@@ -162,8 +172,12 @@ lstm_fwd_tc_kernel(const LstmDesc d, const float* __restrict__ params, const flo
         for (int t = 0; t < T; ++t, ++q) {
           // the layer below's h two steps ahead: into L2 now, read at the end of the next round
           if (l > 0 && valid && t + 2 < T) {
-            prefetch_l2(stash + sidx<FAST>(d, sp, seq, l - 1, t + 2, 5, hh * 32));
-            if (FAST) prefetch_l2(stash + sidx<FAST>(d, sp, seq, l - 1, t + 2, 5, hh * 32 + 16));
+            if (FAST) {
+              prefetch_l2(h16 + idx16(sp, (size_t)(l - 1) * T + t + 2, hh * 32));
+              prefetch_l2(h16 + idx16(sp, (size_t)(l - 1) * T + t + 2, hh * 32 + 16));
+            } else {
+              prefetch_l2(stash + sidx<FAST>(d, sp, seq, l - 1, t + 2, 5, hh * 32));
+            }
           }
           if (l > 0 && t + 1 < T) {        // step t+1 of the layer below (read at the end of this round): polled here, under the MMA
             if (lane == 0) ok = prog_wait(prog_below, PROG_WARPS * (unsigned)(t + 2)) && ok;
@@ -211,15 +225,27 @@ lstm_fwd_tc_kernel(const LstmDesc d, const float* __restrict__ params, const flo
           put(3, ig);
 #pragma unroll
           for (int j = 0; j < UT; ++j) hout[j] = ig[j] * tanh_(c_state[j]);
-          put(5, hout);
+          uint4 hp[UT / 8];               // h_t as packed halves: the A tiles' recurrent part and (FAST) the h16 array
+#pragma unroll
+          for (int c8 = 0; c8 < UT / 8; ++c8)
+            hp[c8] = make_uint4(pack_half2(hout[c8 * 8], hout[c8 * 8 + 1]), pack_half2(hout[c8 * 8 + 2], hout[c8 * 8 + 3]),
+                                pack_half2(hout[c8 * 8 + 4], hout[c8 * 8 + 5]), pack_half2(hout[c8 * 8 + 6], hout[c8 * 8 + 7]));
+          if (FAST) {
+            if (valid) {
+#pragma unroll
+              for (int c8 = 0; c8 < UT / 8; ++c8) *reinterpret_cast<uint4*>(h16 + idx16(sp, (size_t)l * T + t, ub + c8 * 8)) = hp[c8];
+            }
+            if (l == d.L - 1 && t == T - 1) put(5, hout);     // the head reads fp32
+          } else {
+            put(5, hout);
+          }
           // the peer's MMA of this step has completed (waited every round so that no phase is ever skipped)
           ok = mbar_wait_cluster(&bars[B_PZ], q & 1) && ok;
           if (t + 1 < T) {
             // h_t -> recurrent part of both A tiles (fp16), then the next step's input part
 #pragma unroll
             for (int c8 = 0; c8 < UT / 8; ++c8) {
-              const uint4 o = make_uint4(pack_half2(hout[c8 * 8], hout[c8 * 8 + 1]), pack_half2(hout[c8 * 8 + 2], hout[c8 * 8 + 3]),
-                                         pack_half2(hout[c8 * 8 + 4], hout[c8 * 8 + 5]), pack_half2(hout[c8 * 8 + 6], hout[c8 * 8 + 7]));
+              const uint4 o = hp[c8];
               const uint32_t off = tile_chunk_off(TS, row, xw + UH * rank + hh * UT + c8 * 8);
               sts128(sA + off, o);
               st_cluster_v4(peerA + off, o);
@@ -269,7 +295,7 @@ extern unsigned g_lstm_call_id;   // lstm_tc.cu
 
 // forward over all layers and steps: fills the stash (i, f, g, o, c, h per sequence, layer, step) and yhat
 int lstm_tc_fwd(const lstm::LstmDesc& d, const float* params, const float* X, size_t n_seq, float* stash, float* yhat,
-                unsigned* err_flag, unsigned* prog, cudaStream_t st) {
+                unsigned* err_flag, unsigned* prog, uint16_t* h16, cudaStream_t st) {
   static bool attr_set[64] = {};
   int dev = 0;
   DLAS_CUDA(cudaGetDevice(&dev));
@@ -284,8 +310,8 @@ int lstm_tc_fwd(const lstm::LstmDesc& d, const float* params, const float* X, si
   if (max_lanes < 1) { set_error("lstm (tc): %d layers need more SM pairs than this GPU has", d.L); return DLAS_ERR_UNSUPPORTED_SHAPE; }
   const int pairs = (int)(n_tiles < (size_t)max_lanes ? n_tiles : (size_t)max_lanes) * d.L;
   DLAS_CUDA(cudaMemsetAsync(prog, 0, n_tiles * d.L * sizeof(unsigned), st));
-  if (d.fast) lstm_fwd_tc_kernel<true><<<2 * pairs, NT, SMEM_BYTES, st>>>(d, params, X, n_seq, stash, err_flag, g_lstm_call_id, prog);
-  else lstm_fwd_tc_kernel<false><<<2 * pairs, NT, SMEM_BYTES, st>>>(d, params, X, n_seq, stash, err_flag, g_lstm_call_id, prog);
+  if (d.fast) lstm_fwd_tc_kernel<true><<<2 * pairs, NT, SMEM_BYTES, st>>>(d, params, X, n_seq, stash, err_flag, g_lstm_call_id, prog, h16);
+  else lstm_fwd_tc_kernel<false><<<2 * pairs, NT, SMEM_BYTES, st>>>(d, params, X, n_seq, stash, err_flag, g_lstm_call_id, prog, h16);
   DLAS_LAUNCH_CHECK();
   lstm_head_kernel<<<(unsigned)((n_seq + 7) / 8), 256, 0, st>>>(d, params, stash, n_seq, err_flag, g_lstm_call_id, yhat);
   DLAS_LAUNCH_CHECK();

@@ -135,7 +135,8 @@ def test_backward_recurrence_stage_vs_fp32(dl, shape, loss):
     assert np.array_equal(got, again)
 
 
-@pytest.mark.parametrize("shape", [(8, 128, 2, 48, 300), (16, 128, 3, 6, 77), (3, 128, 1, 9, 1), (8, 128, 2, 4, 9472 + 128 + 45)])
+# the last two shapes hold more 128-sequence tiles than the layer pipeline has lanes (74 SM pairs / layers): tiles queue up per lane
+@pytest.mark.parametrize("shape", [(8, 128, 2, 48, 300), (16, 128, 3, 6, 77), (3, 128, 1, 9, 1), (8, 128, 2, 4, 9472 + 128 + 45), (8, 128, 3, 3, 3072 + 300)])
 def test_whole_mode_on_ragged_batches_vs_fp32(dl, shape):
     """DLAS_MODE_TC end to end (all three stages, the tensor-core kernels' own stash layout) against the fp32 path on
     batches that are no multiple of the 128-sequence tile / the 32-sequence layout block."""

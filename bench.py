@@ -275,7 +275,10 @@ def main():
     from dlas import ops
 
     torch.cuda.set_device(local_rank)
+    host_cpus = 0
     if world > 1:
+        from dlas import parallel as _par
+        host_cpus = _par.bind_host_to_gpu(local_rank)     # pinned batch buffers on the GPU's own NUMA node (e2e)
         os.environ.setdefault("MASTER_ADDR", "127.0.0.1")
         if os.environ.get("NCCL_DEBUG", "").upper() in ("", "VERSION"):
             os.environ["NCCL_DEBUG"] = "WARN"   # keep NCCL's version banner off stdout: rank 0 prints ONE JSON line
@@ -651,7 +654,7 @@ def main():
                        "rows_resident_per_gpu": rows_rank, "l2": "inputs (%.1f GB per GPU) larger than L2; every step reads new rows"
                        % (rows_rank * BYTES_PER_SAMPLE / 1e9), "parallelism": "dp%d" % N, "final_loss": final_loss,
                        "dp_path": getattr(model, "dp_path", None) or ("single" if N == 1 else None),
-                       "dp_path_e2e": dp_path_e2e},
+                       "dp_path_e2e": dp_path_e2e, "host_cpus_bound_to_gpu_numa_node": host_cpus},
             # the K timed steps are a burst of about a millisecond: quoted against the BURST peak; `sustained` below carries
             # the >= 2 s figure against the sustained peak
             "roofline": {"bound": "tensor", "achieved": tfs, "peak": pk["tf_burst"], "unit": "TFLOP/s", "frac": tfs / pk["tf_burst"],

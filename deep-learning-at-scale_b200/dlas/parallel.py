@@ -6,6 +6,8 @@ slices, each rank computes gradient SUMS over its slice, one all-reduce of ONE f
 grad_scale = 1/global_batch.  The path has no other collective."""
 from __future__ import annotations
 
+import os
+
 import torch
 import torch.distributed as dist
 
@@ -108,3 +110,29 @@ def average_(tensors):
         else:
             dist.all_reduce(t, op=dist.ReduceOp.SUM)
             t /= world
+
+
+def bind_host_to_gpu(local_rank):
+    """One process per GPU on a multi-socket host: restrict this process to the CPUs the driver reports as local to its GPU
+    (NVML ideal CPU affinity), BEFORE any pinned host buffer is allocated, so that the buffers it streams batches from are
+    first-touched on the GPU's own NUMA node and the host->device copies do not cross the socket link.  Returns the number
+    of CPUs kept, or 0 when nothing was changed (no NVML, single node, or an affinity mask set by the launcher already)."""
+    try:
+        import pynvml
+        all_cpus = os.sched_getaffinity(0)
+        if len(all_cpus) < (os.cpu_count() or 0):
+            return 0                                  # the launcher has bound us already: keep its choice
+        pynvml.nvmlInit()
+        try:
+            h = pynvml.nvmlDeviceGetHandleByIndex(int(local_rank))
+            n_words = ((os.cpu_count() or 64) + 63) // 64
+            words = pynvml.nvmlDeviceGetCpuAffinity(h, n_words)
+        finally:
+            pynvml.nvmlShutdown()
+        cpus = {w * 64 + b for w, word in enumerate(words) for b in range(64) if (int(word) >> b) & 1} & all_cpus
+        if not cpus or cpus == all_cpus:
+            return 0
+        os.sched_setaffinity(0, cpus)
+        return len(cpus)
+    except Exception:
+        return 0

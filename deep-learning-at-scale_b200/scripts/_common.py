@@ -64,6 +64,8 @@ def init_distributed(args):
     import torch.distributed as dist
     rank, local = int(os.environ["RANK"]), int(os.environ.get("LOCAL_RANK", "0"))
     torch.cuda.set_device(local)
+    from dlas import parallel
+    parallel.bind_host_to_gpu(local)           # host buffers first-touched on the GPU's own NUMA node
     os.environ.setdefault("MASTER_ADDR", "127.0.0.1")
     dist.init_process_group("nccl", device_id=torch.device("cuda", local))
     if rank != 0:

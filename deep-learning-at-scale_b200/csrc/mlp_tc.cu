@@ -68,7 +68,7 @@ constexpr uint32_t S_W1 = 0, S_W2 = S_W1 + K1 * 4 * 128, S_X = S_W2 + 65536, S_H
 constexpr int F_B2 = 0, F_W3 = 128, F_Y = 256 /*[2][128]*/, F_PART = 512 /*[2][128]*/, F_RP = 768 /*[CSPLIT][128]*/,
               F_RED = F_RP + CSPLIT * 128 /*[4][128]*/, F_END = F_RED + 512;
 constexpr uint32_t S_BAR = S_F32 + F_END * 4;
-enum { B_DONE = 0, B_FREE, B_X0, B_X1, B_H1A, B_H1, B_DZ2, B_DW2A, B_DW2B, B_DZ1A, B_DZ1, B_DW1, B_ALL, B_XC0, B_XC1, B_WIMG, B_H1L, N_BARS };
+enum { B_DONE = 0, B_FREE, B_X0, B_X1, B_H1A, B_H1, B_DZ2, B_DW2A, B_DW2B, B_DZ1A, B_DZ1, B_DW1, B_ALL, B_XC0, B_XC1, B_WIMG, B_H1L, B_DW1A, N_BARS };
 // fp16 image of the weights in the kernel's own tile layout, kept in the workspace by the finishing kernel of a step loop
 // (tc_reduce_kernel writes every updated parameter into it), so that the next step's set-up is three bulk copies instead of
 // a 160 KB fp32 read + convert per CTA:  [sW1 tile 24 KB: W1 rows, b1 row, zero rows][sW2 tile of rank 0 64 KB][rank 1 64 KB]
@@ -181,7 +181,7 @@ mlp_tc_kernel(const int loss_kind, const float* __restrict__ params, const float
     mbar_init(&bars[B_X0], N_EPI / 32); mbar_init(&bars[B_X1], N_EPI / 32);
     mbar_init(&bars[B_H1A], N_EPI / 32); mbar_init(&bars[B_H1], N_EPI / 32); mbar_init(&bars[B_DZ2], N_EPI / 32); mbar_init(&bars[B_DZ1A], N_EPI / 32);
     mbar_init(&bars[B_DZ1], N_EPI / 32);
-    mbar_init(&bars[B_ALL], 1); mbar_init(&bars[B_DW1], 1); mbar_init(&bars[B_DW2A], 1); mbar_init(&bars[B_DW2B], 1);
+    mbar_init(&bars[B_ALL], 1); mbar_init(&bars[B_DW1], 1); mbar_init(&bars[B_DW1A], 1); mbar_init(&bars[B_DW2A], 1); mbar_init(&bars[B_DW2B], 1);
     mbar_init(&bars[B_XC0], 1); mbar_init(&bars[B_XC1], 1);   // exchange of the partial output dots: 1 arrival + 512 tx bytes
     mbar_init(&bars[B_WIMG], 1);                               // weight image: 1 arrival + 88 KB of bulk-copy bytes
     mbar_init(&bars[B_H1L], 1);                                // K_TRAIN_EXT: H1 tile image, 1 arrival + 64 KB
@@ -453,6 +453,8 @@ mlp_tc_kernel(const int loss_kind, const float* __restrict__ params, const float
       ok = mbar_wait(&bars[B_DZ1A], it & 1) && ok;    // dZ1 columns 0..127 are in place
       fence_after();
       issue_dw1(0);
+      if (leader) mma_commit(&bars[B_DW1A]);   // H1 / dZ1 columns 0..127 (and sDZ2) are free once this arrives: the next tile's
+      __syncwarp();                            // first H1 half does not have to wait for dW1 rows 128..255
       // next tile's Z1 half 0 (the work buffer is free as soon as the second dH1p half has been read)
       if (it + 1 < my_tiles) {
         ok = mbar_wait(&bars[B_X0 + (xb ^ 1)], ((it + 1) >> 1) & 1) && ok;
@@ -524,7 +526,8 @@ mlp_tc_kernel(const int loss_kind, const float* __restrict__ params, const float
         TRACE_E(40);
         take(v);
         TRACE_E(43);
-        if (TRAIN && h == 0 && it > 0) ok = mbar_wait(&bars[B_DW1], (it - 1) & 1) && ok;   // dW1 of the previous tile still reads sH1
+        // dW1 of the previous tile still reads sH1 (as dZ1): its rows 0..127 read columns 0..127, its rows 128..255 the rest
+        if (TRAIN && it > 0) ok = mbar_wait(&bars[h == 0 ? B_DW1A : B_DW1], (it - 1) & 1) && ok;
         // (forward only: sH1 was last read by the previous tile's Z2h, whose completion this thread has already seen)
         const int c0 = h * 128 + hh * CW;
 #pragma unroll

@@ -423,16 +423,19 @@ mlp_tc_kernel(const int loss_kind, const float* __restrict__ params, const float
       __syncwarp();
       issue_dh1(1);
       issue_dw2(1);
-      if (leader) {
-        mma_commit(&bars[B_DW2B]);             // ... and columns 128..255 after this one
-        // db2h += dZ2h^T 1
-#pragma unroll
-        for (int i = 0; i < TILE / 16; ++i)
-          mma_f16(tm + TM_DB2, dDZ2_mn + koff_mnmajor(i), dONES, ID_MN_KM_16, !(first && i == 0));
-      }
+      if (leader) mma_commit(&bars[B_DW2B]);   // ... and columns 128..255 after this one
       __syncwarp();
+      auto issue_db2 = [&]() {                 // db2h += dZ2h^T 1
+        if (leader) {
+#pragma unroll
+          for (int i = 0; i < TILE / 16; ++i)
+            mma_f16(tm + TM_DB2, dDZ2_mn + koff_mnmajor(i), dONES, ID_MN_KM_16, !(first && i == 0));
+        }
+        __syncwarp();
+      };
       TRACE_M(17);
       if (EXT) {
+        issue_db2();
         // layer 1 lives in mlp_tc_l1.cu: the partial dZ1 tile leaves as an image; then the next tile's H1 image comes in
         if (leader) mma_commit(&bars[B_DW1]);   // sDZ2 is free once this arrives (dW2, db2 were its last readers)
         __syncwarp();
@@ -460,6 +463,9 @@ mlp_tc_kernel(const int loss_kind, const float* __restrict__ params, const float
         ok = mbar_wait(&bars[B_X0 + (xb ^ 1)], ((it + 1) >> 1) & 1) && ok;
         issue_z1(xb ^ 1, 0);
       }
+      // db2 only after the MMAs the next tile's first epilogue pass waits for (dW1 rows 0..127 free sH1's first half, Z1 half 0
+      // is its input): on the tensor pipe's queue it would delay both by its 8 MMAs
+      issue_db2();
       ok = mbar_wait(&bars[B_DZ1], it & 1) && ok;
       TRACE_M(18);
       fence_after();

@@ -146,3 +146,20 @@ def test_static_ann_tc_mode_on_wellhead_scale_columns(tmp_path):
     r = subprocess.run([sys.executable, os.path.join(SCRIPTS, "static_ann.py"), names, types, "q", str(tmp_path) + "/big32/"] + common
                        + ["--mode", "fp32", "--epochs", "1", "--standardize"], capture_output=True, text=True, timeout=600)
     assert r.returncode == 0, r.stdout[-1500:] + r.stderr[-1500:]
+
+
+@pytest.mark.gpu
+def test_dynamic_ann_tc_mode_matches_fp32(tmp_path):
+    """The dynamic-ANN script (24 lags x 8 features = 192-256-256-1, Readme.md:17-19) in the tensor-core mode: layer 1 in
+    mlp_tc_l1.cu around the CTA-pair kernel (the script materialises the windows: its random row split breaks the series); the run
+    ends where the fp32 run does."""
+    names = ",".join("f%d" % i for i in range(8)) + ",q"
+    types = ",".join(["float"] * 9)
+    losses = {}
+    for mode in ("fp32", "tc"):
+        r = subprocess.run([sys.executable, os.path.join(SCRIPTS, "dynamic_ann.py"), names, types, "q", str(tmp_path) + "/" + mode + "/",
+                            "--synthetic", "40000", "--lags", "24", "--hidden", "256,256", "--batch-size", "2048", "--epochs", "4",
+                            "--loss", "mse", "--mode", mode], capture_output=True, text=True, timeout=600)
+        assert r.returncode == 0, r.stdout[-1500:] + r.stderr[-1500:]
+        losses[mode] = float(r.stdout.split("Testing set loss:")[1].split()[0])
+    assert np.isfinite(losses["tc"]) and losses["tc"] == pytest.approx(losses["fp32"], rel=1e-2), losses

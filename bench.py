@@ -533,8 +533,10 @@ def main():
             tf = timed(lambda: ops.mlp_fit_steps(dd, mdl.loss, mdl.mode, mdl.cfg, mdl.params, mdl.m, mdl.v, Wd, yd, 65536, 4, 0, ls4,
                                                  mdl.grad_sum, mdl.workspace, batch_order=np.zeros(4, dtype=np.int64)), 3) / 4
             ops.mlp_status(dd, mdl.mode, mdl.workspace)
+            tp = timed(lambda: mdl.predict(Wd), 5)
             extras["dynamic_ann_192_256_256_1" + ("" if dm == "tc" or mode != "tc" else "_fp32")] = {
                 "samples_per_s": 65536 / tf, "us_per_step": tf * 1e6, "train_on_batch_samples_per_s": 65536 / t, "mode": dm,
+                "predict_rows_per_s": 65536 / tp,
                 "rows_per_step": 65536,
                 "input": "24-lag windows gathered from the raw (n, 8) series inside the kernels "
                          "(dlas_mlp_fit_steps_strided): 36 algorithmic bytes per sample, no materialised copy",

@@ -41,7 +41,7 @@ int tc64_fit_step(const int* dims, int loss, const dlas_opt_cfg* cfg, float* par
 int tc64_predict(const int* dims, const float* params, const float* X, size_t n_rows, float* yhat, cudaStream_t st, size_t ldx);
 int tc64_eval_loss(const int* dims, int loss, const float* params, const float* X, const float* y, size_t n_rows, float* loss_sum,
                    void* workspace, size_t workspace_bytes, cudaStream_t st, size_t ldx);
-// mlp_tc.cu + mlp_tc_l1.cu: d0-256-256-1 with 64 <= d0 <= 240 (training on tcgen05; predict / eval_loss on the fp32 kernels)
+// mlp_tc.cu + mlp_tc_l1.cu: d0-256-256-1 with 64 <= d0 <= 240 (the forward-only kinds need a workspace: dlas_mlp_predict_ws)
 bool tcx_supported(const int* dims, int n_layers);
 size_t tcx_workspace_bytes(const int* dims, int n_layers);
 int tcx_grad(const int* dims, int n_layers, int loss, const float* params, const float* X, const float* y, size_t n_rows,
@@ -49,6 +49,10 @@ int tcx_grad(const int* dims, int n_layers, int loss, const float* params, const
 int tcx_fit_step(const int* dims, int n_layers, int loss, const dlas_opt_cfg* cfg, float* params, float* m, float* v, const float* X,
                  const float* y, size_t n_rows, uint64_t iteration, float* loss_out, void* workspace, size_t workspace_bytes,
                  cudaStream_t st, bool chained, size_t ldx, bool more_follow);
+int tcx_predict(const int* dims, int n_layers, const float* params, const float* X, size_t n_rows, float* yhat, void* workspace,
+                size_t workspace_bytes, cudaStream_t st, size_t ldx);
+int tcx_eval_loss(const int* dims, int n_layers, int loss, const float* params, const float* X, const float* y, size_t n_rows,
+                  float* loss_sum, void* workspace, size_t workspace_bytes, cudaStream_t st, size_t ldx);
 inline bool tc_any(const int* dims, int n_layers) {
   return tc_supported(dims, n_layers) || tc64_supported(dims, n_layers) || tcx_supported(dims, n_layers);
 }
@@ -253,6 +257,26 @@ extern "C" int dlas_mlp_predict_strided(const int* dims, int n_layers, int mode,
   return simt_predict(dims, n_layers, params, X, n_rows, yhat, (cudaStream_t)stream, x_row_stride);
 }
 
+extern "C" int dlas_mlp_predict_ws(const int* dims, int n_layers, int mode, const float* params, const float* X, size_t n_rows,
+                                   float* yhat, void* workspace, size_t workspace_bytes, void* stream) {
+  if (!dims) { set_error("dlas_mlp_predict_ws: dims is null"); return DLAS_ERR_INVALID; }
+  return dlas_mlp_predict_ws_strided(dims, n_layers, mode, params, X, (size_t)dims[0], n_rows, yhat, workspace, workspace_bytes, stream);
+}
+
+extern "C" int dlas_mlp_predict_ws_strided(const int* dims, int n_layers, int mode, const float* params, const float* X,
+                                           size_t x_row_stride, size_t n_rows, float* yhat, void* workspace, size_t workspace_bytes,
+                                           void* stream) {
+  DLAS_CHECK_DEVICE();
+  if (dims && n_layers >= 1 && n_layers <= 8 && mode == DLAS_MODE_TC && tcx_supported(dims, n_layers)) {
+    DLAS_REQUIRE(params && (n_rows == 0 || (X && yhat)), "dlas_mlp_predict_ws: null pointer");
+    int rc = check_stride("dlas_mlp_predict_ws_strided", dims, x_row_stride);
+    if (rc != DLAS_OK) return rc;
+    if (n_rows == 0) return DLAS_OK;
+    return tcx_predict(dims, n_layers, params, X, n_rows, yhat, workspace, workspace_bytes, (cudaStream_t)stream, x_row_stride);
+  }
+  return dlas_mlp_predict_strided(dims, n_layers, mode, params, X, x_row_stride, n_rows, yhat, stream);   // no scratch needed
+}
+
 extern "C" int dlas_mlp_eval_loss(const int* dims, int n_layers, int loss, int mode, const float* params,
                                   const float* X, const float* y, size_t n_rows, float* loss_sum,
                                   void* workspace, size_t workspace_bytes, void* stream) {
@@ -275,7 +299,7 @@ extern "C" int dlas_mlp_eval_loss_strided(const int* dims, int n_layers, int los
     if (tc64_supported(dims, n_layers))
       return tc64_eval_loss(dims, loss, params, X, y, n_rows, loss_sum, workspace, workspace_bytes, (cudaStream_t)stream, x_row_stride);
     if (tcx_supported(dims, n_layers))
-      return simt_eval_loss(dims, n_layers, loss, params, X, y, n_rows, loss_sum, workspace, workspace_bytes, (cudaStream_t)stream, x_row_stride);
+      return tcx_eval_loss(dims, n_layers, loss, params, X, y, n_rows, loss_sum, workspace, workspace_bytes, (cudaStream_t)stream, x_row_stride);
     if (!tc_supported(dims, n_layers)) { set_error("dlas_mlp_eval_loss: DLAS_MODE_TC does not support these layer widths"); return DLAS_ERR_UNSUPPORTED_SHAPE; }
     return tc_eval_loss(dims, n_layers, loss, params, X, y, n_rows, loss_sum, workspace, workspace_bytes, (cudaStream_t)stream, x_row_stride);
   }

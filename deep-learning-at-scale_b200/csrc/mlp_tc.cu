@@ -73,7 +73,7 @@ enum { B_DONE = 0, B_FREE, B_X0, B_X1, B_H1A, B_H1, B_DZ2, B_DW2A, B_DW2B, B_DZ1
 // (tc_reduce_kernel writes every updated parameter into it), so that the next step's set-up is three bulk copies instead of
 // a 160 KB fp32 read + convert per CTA:  [sW1 tile 24 KB: W1 rows, b1 row, zero rows][sW2 tile of rank 0 64 KB][rank 1 64 KB]
 constexpr uint32_t IMG_W1_BYTES = K1 * 4 * 128, IMG_W2_BYTES = 65536, IMG_BYTES = IMG_W1_BYTES + 2 * IMG_W2_BYTES;
-enum { K_TRAIN = 0, K_EVAL = 1, K_PREDICT = 2, K_TRAIN_EXT = 3 };
+enum { K_TRAIN = 0, K_EVAL = 1, K_PREDICT = 2, K_TRAIN_EXT = 3, K_EVAL_EXT = 4, K_PREDICT_EXT = 5 };
 // K_TRAIN_EXT: layers 2 and 3 of the wide-input network d0-256-256-1 (mlp_tc_l1.cu holds layer 1): H1 arrives as a 64 KB
 // tile image per 128 rows (one bulk copy instead of Z1 / E1) and each CTA's partial dZ1 tile leaves as an image (one bulk
 // copy instead of the dW1 MMAs); `params` points (d0 - 32) * 256 floats into the real vector, so the W2.. offsets hold.
@@ -150,8 +150,9 @@ mlp_tc_kernel(const int loss_kind, const float* __restrict__ params, const float
               unsigned* __restrict__ err_flag, const unsigned call_id, long long* __restrict__ trace,
               const long long* __restrict__ cursor, const int rows_ready, const size_t ldx,
               const uint8_t* __restrict__ w_image, float* __restrict__ yhat_out, const ExtIo ext) {
-  constexpr bool EXT = (KIND == K_TRAIN_EXT);
-  constexpr bool TRAIN = (KIND == K_TRAIN) || EXT;
+  constexpr bool EXT = (KIND >= K_TRAIN_EXT);           // layer 1 lives in mlp_tc_l1.cu (H1 tile images in)
+  constexpr int BK = EXT ? KIND - K_TRAIN_EXT : KIND;   // what the kernel computes: K_TRAIN / K_EVAL / K_PREDICT
+  constexpr bool TRAIN = (BK == K_TRAIN);
   // ldx: floats between consecutive rows of X (32 for a dense matrix; smaller for lag windows laid over a raw series)
   // device-resident batch cursor (replayable steps): this launch works on rows [cursor*n_rows, (cursor+1)*n_rows)
   extern __shared__ __align__(1024) uint8_t smem[];
@@ -199,7 +200,7 @@ mlp_tc_kernel(const int loss_kind, const float* __restrict__ params, const float
     const float* src = X + (row0 + xr) * ldx + xh * XF;
 #pragma unroll
     for (int i = 0; i < XF / 4; ++i) xv[i] = (in && !EXT) ? __ldcs(reinterpret_cast<const float4*>(src + i * 4)) : make_float4(0.f, 0.f, 0.f, 0.f);
-    if (KIND != K_PREDICT && tid < TILE) yv = (row0 + tid < n_rows) ? __ldcs(y + row0 + tid) : 0.f;
+    if (BK != K_PREDICT && tid < TILE) yv = (row0 + tid < n_rows) ? __ldcs(y + row0 + tid) : 0.f;
   };
   // rows_ready: the host states that X / y were NOT written by the kernel that precedes this one in the stream (the
   // library's own step loops: the predecessor is the previous step's finishing kernel).  Only then, and with a host-side
@@ -213,8 +214,10 @@ mlp_tc_kernel(const int loss_kind, const float* __restrict__ params, const float
   // (the optimiser update that produced `params`); from here on its writes are visible.
   asm volatile("griddepcontrol.wait;" ::: "memory");
   const size_t batch0 = cursor ? (size_t)__ldcg(cursor) * n_rows : 0;   // the cursor is written by the previous step's kernels
+  // forward-only with layer 1 outside: a timed-out wait in l1_fwd_tc_kernel (same call id) poisons the predictions too
+  if (EXT && BK == K_PREDICT && err_flag != nullptr && __ldcg(err_flag) == call_id) ok = false;
   const float* __restrict__ X = X_base + batch0 * ldx;
-  const float* __restrict__ y = (KIND == K_PREDICT) ? nullptr : y_base + batch0;
+  const float* __restrict__ y = (BK == K_PREDICT) ? nullptr : y_base + batch0;
   if (w_image != nullptr) {
     // the finishing kernel of the previous step left the updated weights as fp16 tiles: fetch them with the copy engine
     if (tid == 0) {
@@ -371,6 +374,17 @@ mlp_tc_kernel(const int loss_kind, const float* __restrict__ params, const float
       __syncwarp();
       ++n;
       TRACE_M(14);
+      if (!TRAIN && EXT) {   // forward only, layer 1 outside: the next H1 image may land once Z2h has read this one
+        if (it + 1 < my_tiles) {
+          ok = mbar_wait(&bars[B_DONE], (n - 1) & 1) && ok;
+          if (leader) {
+            mbar_arrive_expect_tx(&bars[B_H1L], IMG_TILE_BYTES);
+            bulk_g2s(sH1, ext.h1_img + ((size_t)pair + (size_t)(it + 1) * n_pairs) * IMG_TILE_BYTES, IMG_TILE_BYTES, &bars[B_H1L]);
+          }
+          __syncwarp();
+        }
+        continue;
+      }
       if (!TRAIN) {   // forward only: the next tile's first Z1 half follows at once (work buffer free after the partial-dot pass)
         if (it + 1 < my_tiles) {
           ok = mbar_wait(&bars[B_X0 + (xb ^ 1)], ((it + 1) >> 1) & 1) && ok;
@@ -525,7 +539,7 @@ mlp_tc_kernel(const int loss_kind, const float* __restrict__ params, const float
       const bool row_valid = row0 + row < n_rows;
       TRACE_E(20);
       // ---- (b) H1 = relu(Z1 + b1) -> sH1, two halves of 128 columns (the bias is already in the accumulator) ----
-      if (EXT && it > 0) ok = mbar_wait(&bars[B_DW1], (it - 1) & 1) && ok;   // dW2 / db2 of the previous tile still read sDZ2
+      if (EXT && TRAIN && it > 0) ok = mbar_wait(&bars[B_DW1], (it - 1) & 1) && ok;   // dW2 / db2 of the previous tile still read sDZ2
 #pragma unroll 1
       for (int h = 0; h < (EXT ? 0 : 2); ++h) {
         uint32_t v[CW];
@@ -602,7 +616,7 @@ mlp_tc_kernel(const int loss_kind, const float* __restrict__ params, const float
       TRACE_E(25);
       const float other = f32[F_PART + buf * 128 + row];
       const float yhat = (rank == 0 ? mine + other : other + mine) + b3;   // same value on both CTAs
-      if (KIND == K_PREDICT) {
+      if (BK == K_PREDICT) {
         // a timed-out wait in this thread poisons its rows (the predict entry point has no status words)
         if (rank == 0 && hh == 0 && row_valid) yhat_out[row0 + row] = ok ? yhat : __int_as_float(0x7fc00000);
         continue;
@@ -621,7 +635,7 @@ mlp_tc_kernel(const int loss_kind, const float* __restrict__ params, const float
         }
         if (hh == 0) { acc_loss += lo; acc_b3 += g; }
       }
-      if (KIND == K_EVAL) continue;
+      if (BK == K_EVAL) continue;
       {
         float4 cw[2][2];
         auto fetch = [&](int blk, int s) {
@@ -682,7 +696,7 @@ mlp_tc_kernel(const int loss_kind, const float* __restrict__ params, const float
 
     // ---- drain the accumulators into this CTA's partial vector -----------------------------------------
     float* my = partials + (size_t)blockIdx.x * PSTRIDE;
-    if (KIND == K_EVAL && my_tiles > 0) {   // loss sum of this pair's rows: fixed-order sum over the 128 rows
+    if (BK == K_EVAL && my_tiles > 0) {   // loss sum of this pair's rows: fixed-order sum over the 128 rows
       if (hh == 0) f32[F_RED + row] = acc_loss;
       named_bar_sync(1, N_EPI);
       if (rank == 0 && tid == 0) {
@@ -996,7 +1010,7 @@ tc_reduce_kernel(const float* __restrict__ partials, int n_active_pairs, unsigne
 // validation / test loss (K_EVAL launches): sum of the rank-0 CTAs' loss partials in CTA order
 __global__ void __launch_bounds__(32)
 tc_loss_reduce_kernel(const float* __restrict__ partials, int n_active_pairs, unsigned* __restrict__ err_flag, unsigned call_id,
-                      float* __restrict__ loss_sum) {
+                      float* __restrict__ loss_sum, int accumulate) {
   asm volatile("griddepcontrol.launch_dependents;" ::: "memory");
   asm volatile("griddepcontrol.wait;" ::: "memory");
   if (threadIdx.x == 0) {
@@ -1005,7 +1019,7 @@ tc_loss_reduce_kernel(const float* __restrict__ partials, int n_active_pairs, un
     if (*err_flag == call_id) s = __int_as_float(0x7fc00000);
     if (!(fabsf(s) <= 3.0e38f)) err_flag[1] = call_id;
     err_flag[2] = call_id;
-    *loss_sum = s;
+    *loss_sum = accumulate ? *loss_sum + s : s;   // accumulate: a later 65,536-row part of the same call
   }
 }
 
@@ -1024,13 +1038,14 @@ int launch_main(int loss, const float* params, const float* X, const float* y, s
   if (ldx == 0) ldx = D0;
   DLAS_REQUIRE(ldx % 4 == 0, "mlp (tc): the row stride of X must be a multiple of 4 floats (16-byte row loads), got %zu", ldx);
   size_t need = ws_need();
-  if (KIND != K_PREDICT && (workspace == nullptr || workspace_bytes < need)) {
+  constexpr int BK = KIND >= K_TRAIN_EXT ? KIND - K_TRAIN_EXT : KIND;
+  if (BK != K_PREDICT && (workspace == nullptr || workspace_bytes < need)) {
     set_error("mlp (tc): workspace of %zu bytes given, %zu needed", workspace_bytes, need);
     return DLAS_ERR_WORKSPACE;
   }
   DLAS_REQUIRE((((uintptr_t)X) & 15) == 0, "mlp (tc): X must be 16-byte aligned");
-  float* partials = (KIND == K_PREDICT) ? nullptr : (float*)workspace;
-  unsigned* err_flag = (KIND == K_PREDICT) ? nullptr : (unsigned*)((char*)workspace + ws_partials_bytes());
+  float* partials = (BK == K_PREDICT) ? nullptr : (float*)workspace;
+  unsigned* err_flag = (BK == K_PREDICT && workspace == nullptr) ? nullptr : (unsigned*)((char*)workspace + ws_partials_bytes());
   static bool attr_set[64] = {};   // the attribute is per device
   int dev = 0;
   DLAS_CUDA(cudaGetDevice(&dev));
@@ -1202,7 +1217,7 @@ int tc_eval_loss(const int* dims, int n_layers, int loss, const float* params, c
   at[0].val.programmaticStreamSerializationAllowed = 1;
   cfg.attrs = at;
   cfg.numAttrs = 1;
-  DLAS_CUDA(cudaLaunchKernelEx(&cfg, tc_loss_reduce_kernel, (const float*)partials, nap, err, g_call_id, loss_sum));
+  DLAS_CUDA(cudaLaunchKernelEx(&cfg, tc_loss_reduce_kernel, (const float*)partials, nap, err, g_call_id, loss_sum, 0));
   return DLAS_OK;
 }
 
@@ -1328,6 +1343,81 @@ int tcx_fit_step(const int* dims, int n_layers, int loss, const dlas_opt_cfg* cf
   DLAS_REQUIRE(o.kind == DLAS_OPT_SGD || v != nullptr, "Adam needs the second-moment buffer v");
   return tcx_run(dims, loss, 1, params, params, m, v, o, 1.0f / (float)n_rows, X, ldx, y, n_rows, nullptr, loss_out, workspace,
                  workspace_bytes, st, chained, more_follow);
+}
+
+// model.predict / validation loss of d0-256-256-1 on the tensor cores: per 65,536-row part l1_fwd (H1 images) and the
+// forward-only kinds of the pair kernel; the workspace holds the images, so these take one (dlas_mlp_predict_ws)
+int tcx_predict(const int* dims, int n_layers, const float* params, const float* X, size_t n_rows, float* yhat, void* workspace,
+                size_t workspace_bytes, cudaStream_t st, size_t ldx) {
+  if (!tcx_supported(dims, n_layers)) {
+    set_error("DLAS_MODE_TC: not a d0-256-256-1 network");
+    return DLAS_ERR_UNSUPPORTED_SHAPE;
+  }
+  const int d0 = dims[0];
+  const size_t need = tcx_base() + tcx_img_bytes();
+  if (workspace == nullptr || workspace_bytes < need) {
+    set_error("mlp predict (tc, %d-256-256-1): workspace of %zu bytes given, %zu needed", d0, workspace_bytes, need);
+    return DLAS_ERR_WORKSPACE;
+  }
+  DLAS_REQUIRE(ldx % 4 == 0, "mlp (tc): the row stride of X must be a multiple of 4 floats (16-byte row loads), got %zu", ldx);
+  ExtIo ext;
+  ext.h1_img = (uint8_t*)workspace + tcx_base();
+  ext.dz1_img = nullptr;
+  ext.img_stride = 0;
+  unsigned* err = (unsigned*)((char*)workspace + ws_partials_bytes());
+  for (size_t r0 = 0; r0 < n_rows; r0 += TCX_MAX_ROWS) {
+    const size_t n = n_rows - r0 < TCX_MAX_ROWS ? n_rows - r0 : TCX_MAX_ROWS;
+    int rc = l1_fwd(d0, params, X + r0 * ldx, ldx, n, (uint8_t*)workspace + tcx_base(), err, g_call_id + 1, st);
+    if (rc != DLAS_OK) return rc;
+    rc = launch_main<K_PREDICT_EXT>(DLAS_LOSS_MSE, params + (size_t)(d0 - D0) * D1, X + r0 * ldx, nullptr, n, workspace, workspace_bytes, st,
+                                    nullptr, nullptr, nullptr, nullptr, false, ldx, nullptr, yhat + r0, ext);
+    if (rc != DLAS_OK) return rc;
+  }
+  return DLAS_OK;
+}
+
+int tcx_eval_loss(const int* dims, int n_layers, int loss, const float* params, const float* X, const float* y, size_t n_rows,
+                  float* loss_sum, void* workspace, size_t workspace_bytes, cudaStream_t st, size_t ldx) {
+  if (!tcx_supported(dims, n_layers)) {
+    set_error("DLAS_MODE_TC: not a d0-256-256-1 network");
+    return DLAS_ERR_UNSUPPORTED_SHAPE;
+  }
+  if (n_rows == 0) {
+    DLAS_CUDA(cudaMemsetAsync(loss_sum, 0, sizeof(float), st));
+    return DLAS_OK;
+  }
+  const int d0 = dims[0];
+  const size_t need = tcx_base() + tcx_img_bytes();
+  if (workspace == nullptr || workspace_bytes < need) {
+    set_error("mlp eval_loss (tc, %d-256-256-1): workspace of %zu bytes given, %zu needed", d0, workspace_bytes, need);
+    return DLAS_ERR_WORKSPACE;
+  }
+  DLAS_REQUIRE(ldx % 4 == 0, "mlp (tc): the row stride of X must be a multiple of 4 floats (16-byte row loads), got %zu", ldx);
+  ExtIo ext;
+  ext.h1_img = (uint8_t*)workspace + tcx_base();
+  ext.dz1_img = nullptr;
+  ext.img_stride = 0;
+  for (size_t r0 = 0; r0 < n_rows; r0 += TCX_MAX_ROWS) {
+    const size_t n = n_rows - r0 < TCX_MAX_ROWS ? n_rows - r0 : TCX_MAX_ROWS;
+    unsigned* err = (unsigned*)((char*)workspace + ws_partials_bytes());
+    int rc = l1_fwd(d0, params, X + r0 * ldx, ldx, n, (uint8_t*)workspace + tcx_base(), err, g_call_id + 1, st);
+    if (rc != DLAS_OK) return rc;
+    float* partials; int nap;
+    rc = launch_main<K_EVAL_EXT>(loss, params + (size_t)(d0 - D0) * D1, X + r0 * ldx, y + r0, n, workspace, workspace_bytes, st, &partials, &err,
+                                 &nap, nullptr, false, ldx, nullptr, nullptr, ext);
+    if (rc != DLAS_OK) return rc;
+    cudaLaunchConfig_t cfg = {};
+    cfg.gridDim = dim3(1);
+    cfg.blockDim = dim3(32);
+    cfg.stream = st;
+    cudaLaunchAttribute at[1];
+    at[0].id = cudaLaunchAttributeProgrammaticStreamSerialization;
+    at[0].val.programmaticStreamSerializationAllowed = 1;
+    cfg.attrs = at;
+    cfg.numAttrs = 1;
+    DLAS_CUDA(cudaLaunchKernelEx(&cfg, tc_loss_reduce_kernel, (const float*)partials, nap, err, g_call_id, loss_sum, r0 > 0 ? 1 : 0));
+  }
+  return DLAS_OK;
 }
 
 // one whole data-parallel step in two launches (forward/backward, then reduce + exchange + update + advance)

@@ -61,6 +61,8 @@ SIGNATURES = {
     "dlas_mlp_fit_steps_strided": (_i, [_ip, _i, _i, _i, C.POINTER(OptCfg), _p, _p, _p, _p, _sz, _p, _sz, _i,
                                         C.POINTER(C.c_int64), C.c_int64, _i, _u64, _p, _p, _p, _sz, _p]),
     "dlas_mlp_predict_strided": (_i, [_ip, _i, _i, _p, _p, _sz, _sz, _p, _p]),
+    "dlas_mlp_predict_ws": (_i, [_ip, _i, _i, _p, _p, _sz, _p, _p, _sz, _p]),
+    "dlas_mlp_predict_ws_strided": (_i, [_ip, _i, _i, _p, _p, _sz, _sz, _p, _p, _sz, _p]),
     "dlas_mlp_eval_loss_strided": (_i, [_ip, _i, _i, _i, _p, _p, _sz, _p, _sz, _p, _p, _sz, _p]),
     "dlas_mlp_predict": (_i, [_ip, _i, _i, _p, _p, _sz, _p, _p]),
     "dlas_mlp_eval_loss": (_i, [_ip, _i, _i, _i, _p, _p, _p, _sz, _p, _p, _sz, _p]),

@@ -591,7 +591,7 @@ class Sequential:
     # -- inference (cnn.py:132)
     def predict(self, x):
         X = self._to_dev(x, self.dims[0])
-        return ops.mlp_predict(self.dims, self.mode, self.params, X)
+        return ops.mlp_predict(self.dims, self.mode, self.params, X, workspace=self.workspace)
 
     def evaluate(self, x, y):
         """Mean loss over (x, y); with torch.distributed the mean is over all ranks' rows."""

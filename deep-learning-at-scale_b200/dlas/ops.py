@@ -159,11 +159,17 @@ def mlp_fit_steps(dims, loss, mode, cfg, params, m, v, X, y, batch, n_steps, ite
                                          stream_ptr()))
 
 
-def mlp_predict(dims, mode, params, X, out=None):
+def mlp_predict(dims, mode, params, X, out=None, workspace=None):
+    """yhat of every row.  With the model's workspace the call is dlas_mlp_predict_ws: the shapes whose tensor-core forward pass
+    needs scratch (d0-256-256-1) then run on the tensor cores too."""
     if not isinstance(X, LagWindows):
         _dev_f32(X, "X")
     if out is None:
         out = torch.empty((X.shape[0], dims[-1]), dtype=torch.float32, device=X.device)
+    if workspace is not None:
+        check(_lib.load().dlas_mlp_predict_ws_strided(int_array(dims), len(dims) - 1, int(mode), ptr(params), ptr(X), _x_stride(X, dims),
+                                                      X.shape[0], ptr(out), ptr(workspace), workspace.numel(), stream_ptr()))
+        return out
     check(_lib.load().dlas_mlp_predict_strided(int_array(dims), len(dims) - 1, int(mode), ptr(params), ptr(X), _x_stride(X, dims),
                                                X.shape[0], ptr(out), stream_ptr()))
     return out

@@ -41,8 +41,8 @@ extern "C" {
 #define DLAS_MODE_FP32 0   /* CUDA-core fp32, any layer widths                                   */
 #define DLAS_MODE_TC 1     /* tcgen05 tensor cores: fp16 operands, fp32 accumulation in TMEM; fixed shapes,
                               see dlas_mlp_mode_supported (32-256-256-1; d0-64-64-1 with d0 <= 15;
-                              d0-256-256-1 with 64 <= d0 <= 240, d0 % 8 == 0: training entry points, at most
-                              65,536 rows per call, predict / eval_loss on the fp32 kernels).  A REDUCED-RANGE mode: rows, hidden activations
+                              d0-256-256-1 with 64 <= d0 <= 240, d0 % 8 == 0: at most 65,536 rows per training
+                              call; inference through dlas_mlp_predict_ws).  A REDUCED-RANGE mode: rows, hidden activations
                               and back-propagated terms are rounded to fp16 -- TF32's 11-bit significand but
                               a 5-bit exponent: |value| <= 65504, full precision down to 6.1e-5, flushed to
                               zero below 6e-8.  Feed it standardised columns (raw wellhead pressures of a
@@ -240,6 +240,14 @@ int dlas_mlp_eval_loss_strided(const int* dims, int n_layers, int loss, int mode
 /* Inference (model.predict / test_on_batch, cnn.py:132): yhat (n_rows, dims[n_layers]). */
 int dlas_mlp_predict(const int* dims, int n_layers, int mode, const float* params, const float* X,
                      size_t n_rows, float* yhat, void* stream);
+/* The same with the workspace of dlas_mlp_workspace_bytes: DLAS_MODE_TC on d0-256-256-1 needs scratch for its forward
+ * pass (layer 1 runs in its own kernel and hands 64 KB tile images to the pair kernel); without one, dlas_mlp_predict
+ * serves that shape from the fp32 kernels.  Any number of rows (65,536 per pass).  Other shapes ignore the workspace. */
+int dlas_mlp_predict_ws(const int* dims, int n_layers, int mode, const float* params, const float* X,
+                        size_t n_rows, float* yhat, void* workspace, size_t workspace_bytes, void* stream);
+int dlas_mlp_predict_ws_strided(const int* dims, int n_layers, int mode, const float* params, const float* X,
+                                size_t x_row_stride, size_t n_rows, float* yhat, void* workspace,
+                                size_t workspace_bytes, void* stream);
 /* loss_sum[0] = SUM of per-row losses (validation / test loss numerator, cnn.py:121,:132) */
 int dlas_mlp_eval_loss(const int* dims, int n_layers, int loss, int mode, const float* params,
                        const float* X, const float* y, size_t n_rows, float* loss_sum,

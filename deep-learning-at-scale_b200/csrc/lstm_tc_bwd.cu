@@ -9,9 +9,12 @@
 //                own units' columns are read back from TMEM at step t-1; the dx columns (layers above 0) go to one of two
 //                partial dseq buffers in global memory, which the layer below adds when it reads dh_t.
 // The weight tile is the forward kernel's ([x | h] rows x own gate columns): tcgen05 reads it K-major here, MN-major there.
-// mbarriers: B_A (sDZ of this step in place), B_Z (tcgen05.commit), B_RFULL (the peer's partial for my units has arrived),
+// mbarriers: B_A (sDZ of this step in place), B_Z (tcgen05.commit), B_RFULL (the peer's partial for my units has arrived:
+// st.async stores that complete their bytes on the receiver's barrier, so no releasing arrive has to wait for the sender's
+// global stores; plus one relaxed arrival per peer warp and round, which keeps the two CTAs within one round of each other),
 // B_RFREE (the peer has read what I sent last: its receive buffer may be overwritten).  Every barrier completes exactly one
-// phase per round (dummy arrivals where a round has nothing to send), so no waiter ever skips a phase.
+// phase per round (arrivals without data where a round has nothing to send), so no waiter ever skips a phase and no barrier
+// gets two phases ahead of one.
 #include "common.cuh"
 #include "lstm_common.cuh"
 #include "tc_common.cuh"
@@ -102,7 +105,7 @@ lstm_bwd_tc_kernel(const LstmDesc d, const float* __restrict__ params, float* __
   bool ok = (sbase & 1023u) == 0;
   if (tid == 0) {
     mbar_init(&bars[B_A], N_EPI / 32); mbar_init(&bars[B_Z], 1);
-    mbar_init(&bars[B_RFULL], N_EPI / 32); mbar_init(&bars[B_RFREE], N_EPI / 32);
+    mbar_init(&bars[B_RFULL], 1 + N_EPI / 32); mbar_init(&bars[B_RFREE], N_EPI / 32);   // B_RFULL: 1 local arrival (expect_tx) + the peer's 16 warps + 32 KB of st.async bytes
     mbar_fence_init();
   }
   if (warp == ISSUER_WARP) tmem_alloc(tmem_slot, TM_COLS);
@@ -186,26 +189,14 @@ lstm_bwd_tc_kernel(const LstmDesc d, const float* __restrict__ params, float* __
           if (!first) {
             ok = mbar_wait(&bars[B_Z], (q - 1) & 1) && ok;
             fence_after();
-            uint32_t v[32];
-            if (l > 0) {   // (warp-uniform: tcgen05.ld is warp-collective; only the stores depend on the row being valid)
-              float* dst = dsW + (size_t)rank * pstr;
-#pragma unroll
-              for (int c = 0; c < 1; ++c) {
-                tmem_ld32(tm + lane_base + hh * 32 + c * 32, v);
-                tmem_ld_wait();
-#pragma unroll
-                for (int j4 = 0; j4 < 8; ++j4)
-                  if (valid) *reinterpret_cast<float4*>(dst + didx<FAST>(d, sp, sq, t + 1, hh * 32 + j4 * 4)) = make_float4(__uint_as_float(v[j4 * 4]), __uint_as_float(v[j4 * 4 + 1]),
-                                                                                 __uint_as_float(v[j4 * 4 + 2]), __uint_as_float(v[j4 * 4 + 3]));
-              }
-            }
-            tmem_ld16(tm + lane_base + xw + UH * (rank ^ 1u) + hh * UT, *reinterpret_cast<uint32_t(*)[16]>(&v[0]));   // the peer's units: send
+            uint32_t v[16];
+            tmem_ld16(tm + lane_base + xw + UH * (rank ^ 1u) + hh * UT, v);   // the peer's units: send
             tmem_ld_wait();
             if (q >= 1) ok = mbar_wait_cluster(&bars[B_RFREE], (q - 1) & 1) && ok;   // the peer has read what I sent last round
 #pragma unroll
             for (int j4 = 0; j4 < UT / 4; ++j4)
-              st_cluster_v4(peerRecv + recv_off(row, hh * 4 + j4), make_uint4(v[j4 * 4], v[j4 * 4 + 1], v[j4 * 4 + 2], v[j4 * 4 + 3]));
-            tmem_ld16(tm + lane_base + xw + u0, *reinterpret_cast<uint32_t(*)[16]>(&v[0]));                    // my units: keep
+              st_async_v4(peerRecv + recv_off(row, hh * 4 + j4), make_uint4(v[j4 * 4], v[j4 * 4 + 1], v[j4 * 4 + 2], v[j4 * 4 + 3]), peer_RFULL);
+            tmem_ld16(tm + lane_base + xw + u0, v);                    // my units: keep
             tmem_ld_wait();
             fence_before();
 #pragma unroll
@@ -215,8 +206,12 @@ lstm_bwd_tc_kernel(const LstmDesc d, const float* __restrict__ params, float* __
 #pragma unroll
             for (int j = 0; j < UT; ++j) dh_rec[j] = 0.f;
           }
+          // the peer's partial for my units: 32 KB of asynchronous stores that complete their bytes on this barrier (none in a
+          // layer's first round).  Every warp also arrives on the peer's barrier (relaxed: the bytes carry their own completion):
+          // that keeps the pair in step, so that no barrier ever gets two phases ahead of a waiter
           __syncwarp();
-          if (lane == 0) mbar_arrive_remote(peer_RFULL);
+          if (lane == 0) mbar_arrive_remote_relaxed(peer_RFULL);
+          if (tid == 0) mbar_arrive_expect_tx(&bars[B_RFULL], first ? 0u : (uint32_t)(TS * UH * 4));
           ok = mbar_wait_cluster(&bars[B_RFULL], q & 1) && ok;
           if (!first) {
 #pragma unroll
@@ -226,7 +221,21 @@ lstm_bwd_tc_kernel(const LstmDesc d, const float* __restrict__ params, float* __
             }
           }
           __syncwarp();
-          if (lane == 0) mbar_arrive_remote(peer_RFREE);
+          if (lane == 0) mbar_arrive_remote_relaxed(peer_RFREE);
+          // ---- the dx columns of step t+1 (layers above 0) -> this CTA's partial buffer.  Here, not before the exchange: no
+          // fence of the recurrence ever waits for these stores (warp-uniform: tcgen05.ld is warp-collective; only the stores
+          // depend on the row being valid)
+          if (!first && l > 0) {
+            uint32_t w[32];
+            float* dst = dsW + (size_t)rank * pstr;
+            tmem_ld32(tm + lane_base + hh * 32, w);
+            tmem_ld_wait();
+            fence_before();
+#pragma unroll
+            for (int j4 = 0; j4 < 8; ++j4)
+              if (valid) *reinterpret_cast<float4*>(dst + didx<FAST>(d, sp, sq, t + 1, hh * 32 + j4 * 4)) = make_float4(__uint_as_float(w[j4 * 4]), __uint_as_float(w[j4 * 4 + 1]),
+                                                                             __uint_as_float(w[j4 * 4 + 2]), __uint_as_float(w[j4 * 4 + 3]));
+          }
           // ---- gate gradients of step t for this row's 16 units, 8 units at a time ----
 
           const float dyr = (l == d.L - 1 && first && valid) ? __ldg(dy + sq) : 0.f;

@@ -8,8 +8,9 @@
 //     stash (fp32, the layout of lstm.cu, so the fp32 BPTT can consume it) and store h_t as fp16 into BOTH CTAs' A tiles
 //     (own half locally, the other through distributed shared memory) -- the only exchange of the recurrence.
 //   * hand-over by mbarriers only: B_A (own rows of the next step are in place), B_PH (the peer's half of h has arrived:
-//     remote arrive, cluster-scope release/acquire), B_Z (tcgen05.commit), B_PZ (the peer's MMA of this step has completed,
-//     so its A tile may be overwritten).
+//     st.async stores that complete their bytes on the receiver's barrier -- a releasing arrive would first wait for the
+//     sender's stash stores), B_Z (tcgen05.commit), B_PZ (the peer's MMA of this step has completed, so its A tile may be
+//     overwritten).
 #include "common.cuh"
 #include "lstm_common.cuh"
 #include "tc_common.cuh"
@@ -55,7 +56,7 @@ lstm_fwd_tc_kernel(const LstmDesc d, const float* __restrict__ params, const flo
   const size_t n_tiles = (n_seq + TS - 1) / TS;
   bool ok = (sbase & 1023u) == 0;
   if (tid == 0) {
-    mbar_init(&bars[B_A], N_EPI / 32); mbar_init(&bars[B_PH], N_EPI / 32);
+    mbar_init(&bars[B_A], N_EPI / 32); mbar_init(&bars[B_PH], 1 + N_EPI / 32);   // B_PH: 1 local arrival (expect_tx) + the peer's 16 warps + its 16 KB of st.async bytes
     mbar_init(&bars[B_Z], 1); mbar_init(&bars[B_PZ], 1);
     mbar_fence_init();
   }
@@ -146,7 +147,8 @@ lstm_fwd_tc_kernel(const LstmDesc d, const float* __restrict__ params, const flo
       fence_async_smem();
       __syncthreads();          // weights, bias, A tile of step 0 complete in this CTA
       if (warp < ISSUER_WARP) {
-        if (lane == 0) { mbar_arrive(&bars[B_A]); mbar_arrive_remote(peer_PH); }   // nothing to send for step 0: phases stay in step
+        // (the remote arrival carries no data: it keeps the pair in step, so that no barrier ever gets two phases ahead of a waiter)
+        if (lane == 0) { mbar_arrive(&bars[B_A]); mbar_arrive_remote_relaxed(peer_PH); }
       }
       if (warp == ISSUER_WARP) {
         // =========================== MMA issuer ===========================
@@ -155,7 +157,10 @@ lstm_fwd_tc_kernel(const LstmDesc d, const float* __restrict__ params, const flo
         const uint64_t dA = desc_kmajor(sA, TS, 0, 0), dW = desc_mnmajor(sW, 256, 0, 0);
         for (int t = 0; t < T; ++t, ++q) {
           ok = mbar_wait(&bars[B_A], q & 1) && ok;
-          ok = mbar_wait_cluster(&bars[B_PH], q & 1) && ok;        // the peer's half of h_{t-1} is in my A tile
+          // the peer's half of h_{t-1}: 128 rows x 64 units as asynchronous stores that complete their bytes on this barrier
+          // (nothing at step 0: the phase still completes, so every barrier stays in step)
+          if (leader) mbar_arrive_expect_tx(&bars[B_PH], t == 0 ? 0u : (uint32_t)(TS * UH * 2));
+          ok = mbar_wait_cluster(&bars[B_PH], q & 1) && ok;
           fence_after();
           if (leader) {
             for (int i = 0; i < nk / 16; ++i)
@@ -248,12 +253,12 @@ lstm_fwd_tc_kernel(const LstmDesc d, const float* __restrict__ params, const flo
               const uint4 o = hp[c8];
               const uint32_t off = tile_chunk_off(TS, row, xw + UH * rank + hh * UT + c8 * 8);
               sts128(sA + off, o);
-              st_cluster_v4(peerA + off, o);
+              st_async_v4(peerA + off, o, peer_PH);
             }
             x_store(t + 1);
             fence_async_all();
             __syncwarp();
-            if (lane == 0) { mbar_arrive(&bars[B_A]); mbar_arrive_remote(peer_PH); }
+            if (lane == 0) { mbar_arrive(&bars[B_A]); mbar_arrive_remote_relaxed(peer_PH); }
           }
           if (l + 1 < d.L) {               // publish h_t to the pair of the layer above; the release waits for this warp's stash
             __syncwarp();                  // stores, after the recurrence's own hand-over so that it does not sit in its way

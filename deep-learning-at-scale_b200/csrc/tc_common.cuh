@@ -197,6 +197,19 @@ __device__ __forceinline__ void bulk_g2s(uint32_t sdst, const void* gsrc, uint32
 __device__ __forceinline__ void st_cluster_v4(uint32_t caddr, uint4 v) {
   asm volatile("st.shared::cluster.v4.b32 [%0], {%1,%2,%3,%4};" ::"r"(caddr), "r"(v.x), "r"(v.y), "r"(v.z), "r"(v.w) : "memory");
 }
+// 16 bytes into a peer CTA's shared memory as an asynchronous store that completes 16 transaction bytes on the PEER's
+// mbarrier when the data has landed: no release fence on the sender's side (a releasing arrive would first wait for every
+// global store the thread still has in flight)
+__device__ __forceinline__ void st_async_v4(uint32_t caddr, uint4 v, uint32_t cbar) {
+  asm volatile("st.async.weak.shared::cluster.mbarrier::complete_tx::bytes.v4.b32 [%0], {%1,%2,%3,%4}, [%5];" ::"r"(caddr), "r"(v.x),
+               "r"(v.y), "r"(v.z), "r"(v.w), "r"(cbar)
+               : "memory");
+}
+// arrive on a peer's mbarrier without ordering this thread's earlier writes (a buffer has been READ and may be overwritten;
+// the reads' results have been consumed by earlier instructions of the arriving warp)
+__device__ __forceinline__ void mbar_arrive_remote_relaxed(uint32_t cbar) {
+  asm volatile("mbarrier.arrive.relaxed.cluster.shared::cluster.b64 _, [%0];" ::"r"(cbar) : "memory");
+}
 // generic-proxy writes (own or peer shared memory) -> visible to async-proxy readers (tcgen05.mma operand fetch)
 __device__ __forceinline__ void fence_async_all() { asm volatile("fence.proxy.async;" ::: "memory"); }
 // arrive on a mbarrier of a peer CTA (address from map_to_cta), releasing this thread's earlier writes at cluster scope

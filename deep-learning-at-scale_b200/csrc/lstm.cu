@@ -22,7 +22,7 @@ namespace dlas {
 bool lstm_tc_supported(const lstm::LstmDesc& d);
 size_t lstm_tc_dw_partial_floats(const lstm::LstmDesc& d);
 int lstm_tc_fwd(const lstm::LstmDesc& d, const float* params, const float* X, size_t n_seq, float* stash, float* yhat,
-                unsigned* err_flag, unsigned* prog, uint16_t* h16, cudaStream_t st);
+                unsigned* err_flag, unsigned* prog, uint16_t* h16, uint16_t* g16, cudaStream_t st);
 int lstm_tc_bwd(const lstm::LstmDesc& d, int loss, const float* params, const float* y, float* yhat_dy, size_t n_seq,
                 float* stash, float* dseqP, float* partials, int n_blocks, unsigned* err_flag, unsigned* prog, uint16_t* dz16, cudaStream_t st);
 int lstm_tc_dw(const lstm::LstmDesc& d, const float* X, const float* stash, size_t n_seq, float* grad_sum, float* tc_partials,
@@ -371,7 +371,7 @@ extern "C" int dlas_lstm_predict_mode(int mode, int d_in, int hidden, int n_laye
   size_t smem = rec_smem_bytes(d);
   rc = set_smem(lstm_fwd_kernel, smem);
   if (rc != DLAS_OK) return rc;
-  if (bits & TC_FWD) return lstm_tc_fwd(d, params, X, n_seq, w.stash, yhat, w.status, w.prog, w.h16, st);
+  if (bits & TC_FWD) return lstm_tc_fwd(d, params, X, n_seq, w.stash, yhat, w.status, w.prog, w.h16, w.dz16, st);
   lstm_fwd_kernel<<<sm_count(), NT, smem, st>>>(d, params, X, n_seq, w.stash, yhat);
   DLAS_LAUNCH_CHECK();
   return DLAS_OK;
@@ -429,7 +429,7 @@ extern "C" int dlas_lstm_grad_mode(int mode, int d_in, int hidden, int n_layers,
     DLAS_LAUNCH_CHECK();
   }
   if (bits & TC_FWD) {   // persistent recurrence on the tensor cores
-    rc = lstm_tc_fwd(d, params, X, n_seq, w.stash, w.yhat, w.status, w.prog, w.h16, st);
+    rc = lstm_tc_fwd(d, params, X, n_seq, w.stash, w.yhat, w.status, w.prog, w.h16, w.dz16, st);
     if (rc != DLAS_OK) return rc;
   } else {
     lstm_fwd_kernel<<<grid, NT, smem, st>>>(d, params, X, n_seq, w.stash, w.yhat);

@@ -176,8 +176,17 @@ lstm_bwd_tc_kernel(const LstmDesc d, const float* __restrict__ params, float* __
         for (int t = T - 1; t >= 0; --t, ++q) {
           const bool first = (t == T - 1);
           if (valid && t > 0) {   // step t-1's stash lines (and the layer above's dx): into L2 a round ahead
+            if (FAST) {
 #pragma unroll
-            for (int c = 0; c < 5; ++c) prefetch_l2(stash + sidx<FAST>(d, sp, sq, l, t - 1, c, u0));
+              for (int g = 0; g < 4; ++g) {
+                prefetch_l2(dz16 + idx16(sp, ((size_t)l * T + t - 1) * 4 + g, u0));
+                prefetch_l2(dz16 + idx16(sp, ((size_t)l * T + t - 1) * 4 + g, u0 + 8));
+              }
+              prefetch_l2(stash + sidx<FAST>(d, sp, sq, l, t - 1, 4, u0));
+            } else {
+#pragma unroll
+              for (int c = 0; c < 5; ++c) prefetch_l2(stash + sidx<FAST>(d, sp, sq, l, t - 1, c, u0));
+            }
             if (t > 1) prefetch_l2(stash + sidx<FAST>(d, sp, sq, l, t - 2, 4, u0));
             if (l < d.L - 1) { prefetch_l2(dsR + didx<FAST>(d, sp, sq, t - 1, u0)); prefetch_l2(dsR + pstr + didx<FAST>(d, sp, sq, t - 1, u0)); }
           }
@@ -248,10 +257,23 @@ lstm_bwd_tc_kernel(const LstmDesc d, const float* __restrict__ params, float* __
               const int o = b8 * 8 + h4 * 4;
               float4 a = make_float4(0.f, 0.f, 0.f, 0.f), f4 = a, g4 = a, o4 = a, c4 = a, p4 = a, d4 = a;
               if (valid) {
-                a = __ldg(reinterpret_cast<const float4*>(stash + sidx<FAST>(d, sp, sq, l, t, 0, u0 + o)));
-                f4 = __ldg(reinterpret_cast<const float4*>(stash + sidx<FAST>(d, sp, sq, l, t, 1, u0 + o)));
-                g4 = __ldg(reinterpret_cast<const float4*>(stash + sidx<FAST>(d, sp, sq, l, t, 2, u0 + o)));
-                o4 = __ldg(reinterpret_cast<const float4*>(stash + sidx<FAST>(d, sp, sq, l, t, 3, u0 + o)));
+                if (FAST) {   // gates as packed halves (written by the forward kernel into the dz array): 4 of them per 8-byte word pair
+                  const size_t sl4 = ((size_t)l * T + t) * 4;
+                  const uint2 pi = __ldcg(reinterpret_cast<const uint2*>(dz16 + idx16(sp, sl4 + 0, u0 + b8 * 8) + h4 * 4));
+                  const uint2 pf = __ldcg(reinterpret_cast<const uint2*>(dz16 + idx16(sp, sl4 + 1, u0 + b8 * 8) + h4 * 4));
+                  const uint2 pg = __ldcg(reinterpret_cast<const uint2*>(dz16 + idx16(sp, sl4 + 2, u0 + b8 * 8) + h4 * 4));
+                  const uint2 po = __ldcg(reinterpret_cast<const uint2*>(dz16 + idx16(sp, sl4 + 3, u0 + b8 * 8) + h4 * 4));
+                  auto un = [](uint2 p) {
+                    const float2 lo = __half22float2(*reinterpret_cast<const __half2*>(&p.x)), hi = __half22float2(*reinterpret_cast<const __half2*>(&p.y));
+                    return make_float4(lo.x, lo.y, hi.x, hi.y);
+                  };
+                  a = un(pi); f4 = un(pf); g4 = un(pg); o4 = un(po);
+                } else {
+                  a = __ldg(reinterpret_cast<const float4*>(stash + sidx<FAST>(d, sp, sq, l, t, 0, u0 + o)));
+                  f4 = __ldg(reinterpret_cast<const float4*>(stash + sidx<FAST>(d, sp, sq, l, t, 1, u0 + o)));
+                  g4 = __ldg(reinterpret_cast<const float4*>(stash + sidx<FAST>(d, sp, sq, l, t, 2, u0 + o)));
+                  o4 = __ldg(reinterpret_cast<const float4*>(stash + sidx<FAST>(d, sp, sq, l, t, 3, u0 + o)));
+                }
                 c4 = __ldg(reinterpret_cast<const float4*>(stash + sidx<FAST>(d, sp, sq, l, t, 4, u0 + o)));
                 if (t > 0) p4 = __ldg(reinterpret_cast<const float4*>(stash + sidx<FAST>(d, sp, sq, l, t - 1, 4, u0 + o)));
                 if (l < d.L - 1) {

@@ -37,7 +37,7 @@ template <bool FAST>
 __global__ void __cluster_dims__(2, 1, 1) __launch_bounds__(NT, 1)
 lstm_fwd_tc_kernel(const LstmDesc d, const float* __restrict__ params, const float* __restrict__ X, const size_t n_seq,
                    float* __restrict__ stash, unsigned* __restrict__ err_flag, const unsigned call_id, unsigned* __restrict__ prog,
-                   uint16_t* __restrict__ h16) {
+                   uint16_t* __restrict__ h16, uint16_t* __restrict__ g16) {
   // FAST (every stage of the step on the tensor cores): h goes out as fp16 (h16, lstm_common.cuh) for the layer above and the
   // weight-gradient GEMM; the fp32 h of the stash is written for the head only (top layer, last step).
   // Layer pipeline: the grid is n_lanes x L pairs; pair p works on layer p / n_lanes of the tiles lane, lane + n_lanes, ...
@@ -195,7 +195,17 @@ lstm_fwd_tc_kernel(const LstmDesc d, const float* __restrict__ params, const flo
           float ig[UT], hout[UT];
           const int ub = UH * (int)rank + hh * UT;
           auto put = [&](int comp, const float (&a)[UT]) {
-            if (valid) {
+            if (FAST && comp < 4) {
+              // all-tensor-core step: the gates go out as packed halves into the array the BPTT later overwrites with dz (same
+              // thread owns the same (sequence, units) there); 11 bits on values in (-1, 1), the precision dz travels with anyway
+              if (valid) {
+#pragma unroll
+                for (int c8 = 0; c8 < UT / 8; ++c8)
+                  *reinterpret_cast<uint4*>(g16 + idx16(sp, ((size_t)l * T + t) * 4 + comp, ub + c8 * 8)) =
+                      make_uint4(pack_half2(a[c8 * 8], a[c8 * 8 + 1]), pack_half2(a[c8 * 8 + 2], a[c8 * 8 + 3]),
+                                 pack_half2(a[c8 * 8 + 4], a[c8 * 8 + 5]), pack_half2(a[c8 * 8 + 6], a[c8 * 8 + 7]));
+              }
+            } else if (valid) {
 #pragma unroll
               for (int j4 = 0; j4 < UT / 4; ++j4)
                 *reinterpret_cast<float4*>(stash + sidx<FAST>(d, sp, seq, l, t, comp, ub + j4 * 4)) = make_float4(a[j4 * 4], a[j4 * 4 + 1], a[j4 * 4 + 2], a[j4 * 4 + 3]);
@@ -300,7 +310,7 @@ extern unsigned g_lstm_call_id;   // lstm_tc.cu
 
 // forward over all layers and steps: fills the stash (i, f, g, o, c, h per sequence, layer, step) and yhat
 int lstm_tc_fwd(const lstm::LstmDesc& d, const float* params, const float* X, size_t n_seq, float* stash, float* yhat,
-                unsigned* err_flag, unsigned* prog, uint16_t* h16, cudaStream_t st) {
+                unsigned* err_flag, unsigned* prog, uint16_t* h16, uint16_t* g16, cudaStream_t st) {
   static bool attr_set[64] = {};
   int dev = 0;
   DLAS_CUDA(cudaGetDevice(&dev));
@@ -315,8 +325,8 @@ int lstm_tc_fwd(const lstm::LstmDesc& d, const float* params, const float* X, si
   if (max_lanes < 1) { set_error("lstm (tc): %d layers need more SM pairs than this GPU has", d.L); return DLAS_ERR_UNSUPPORTED_SHAPE; }
   const int pairs = (int)(n_tiles < (size_t)max_lanes ? n_tiles : (size_t)max_lanes) * d.L;
   DLAS_CUDA(cudaMemsetAsync(prog, 0, n_tiles * d.L * sizeof(unsigned), st));
-  if (d.fast) lstm_fwd_tc_kernel<true><<<2 * pairs, NT, SMEM_BYTES, st>>>(d, params, X, n_seq, stash, err_flag, g_lstm_call_id, prog, h16);
-  else lstm_fwd_tc_kernel<false><<<2 * pairs, NT, SMEM_BYTES, st>>>(d, params, X, n_seq, stash, err_flag, g_lstm_call_id, prog, h16);
+  if (d.fast) lstm_fwd_tc_kernel<true><<<2 * pairs, NT, SMEM_BYTES, st>>>(d, params, X, n_seq, stash, err_flag, g_lstm_call_id, prog, h16, g16);
+  else lstm_fwd_tc_kernel<false><<<2 * pairs, NT, SMEM_BYTES, st>>>(d, params, X, n_seq, stash, err_flag, g_lstm_call_id, prog, h16, g16);
   DLAS_LAUNCH_CHECK();
   lstm_head_kernel<<<(unsigned)((n_seq + 7) / 8), 256, 0, st>>>(d, params, stash, n_seq, err_flag, g_lstm_call_id, yhat);
   DLAS_LAUNCH_CHECK();

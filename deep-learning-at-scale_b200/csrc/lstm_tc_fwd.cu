@@ -161,6 +161,7 @@ lstm_fwd_tc_kernel(const LstmDesc d, const float* __restrict__ params, const flo
           // (nothing at step 0: the phase still completes, so every barrier stays in step)
           if (leader) mbar_arrive_expect_tx(&bars[B_PH], t == 0 ? 0u : (uint32_t)(TS * UH * 2));
           ok = mbar_wait_cluster(&bars[B_PH], q & 1) && ok;
+          fence_async_all();   // the peer's st.async bytes (observed through the barrier) before this thread's async-proxy reads
           fence_after();
           if (leader) {
             for (int i = 0; i < nk / 16; ++i)
@@ -266,7 +267,7 @@ lstm_fwd_tc_kernel(const LstmDesc d, const float* __restrict__ params, const flo
               st_async_v4(peerA + off, o, peer_PH);
             }
             x_store(t + 1);
-            fence_async_all();
+            fence_async_smem();   // own sts128 -> the MMA's operand reads (the remote half goes by st.async)
             __syncwarp();
             if (lane == 0) { mbar_arrive(&bars[B_A]); mbar_arrive_remote_relaxed(peer_PH); }
           }

@@ -54,6 +54,21 @@ def test_host_only_queries(lib):
     assert lib.dlas_mlp_n_params(dims, 3) == 4801
 
 
+def test_mode_table_is_a_host_only_query(lib):
+    """Which layer widths the tensor-core mode takes (no device needed): 32-256-256-1, d0-64-64-1 with d0 <= 15, d0-256-256-1 with
+    64 <= d0 <= 240 and d0 % 8 == 0 (the dynamic ANN's 24 x 8 = 192 inputs); LSTM: hidden 128, d_in <= 16."""
+    from dlas import _lib
+    tc = lambda d: lib.dlas_mlp_mode_supported(_lib.int_array(d), len(d) - 1, _lib.MODE_TC)
+    for d in ([32, 256, 256, 1], [8, 64, 64, 1], [1, 64, 64, 1], [15, 64, 64, 1], [192, 256, 256, 1], [64, 256, 256, 1], [240, 256, 256, 1]):
+        assert tc(d) == 1, d
+    for d in ([16, 64, 64, 1], [32, 256, 256, 2], [32, 256, 1], [100, 256, 256, 1], [248, 256, 256, 1], [48, 256, 256, 1],
+              [192, 256, 128, 1], [32, 128, 256, 1]):
+        assert tc(d) == 0, d
+    assert lib.dlas_lstm_mode_supported(8, 128, 2, _lib.MODE_TC) == 1 and lib.dlas_lstm_mode_supported(16, 128, 4, _lib.MODE_TC) == 1
+    assert lib.dlas_lstm_mode_supported(8, 64, 2, _lib.MODE_TC) == 0 and lib.dlas_lstm_mode_supported(17, 128, 2, _lib.MODE_TC) == 0
+    assert lib.dlas_lstm_mode_supported(8, 64, 2, _lib.MODE_FP32) == 1
+
+
 def test_no_cpu_fallback_without_gpu(lib):
     import torch
     if torch.cuda.is_available():

@@ -25,7 +25,7 @@
 // halves through ONE 128-column TMEM work buffer (mbarrier waits cost ~140 cycles each whatever their state --
 // tools/mbar_lat.cu -- so fewer, larger hand-overs win over double-buffered N=64 chunks); the issuer interleaves
 //   Z1 half 1 | Z2h (first K half as soon as H1 columns 0..127 are stored) | dH1p half 0 | dW2^T half 0 | dH1p half 1 |
-//   dW2^T half 1 | db2 | dW1 half 0 | next tile's Z1 half 0 | dW1 half 1
+//   dW2^T half 1 | dW1 half 0 | next tile's Z1 half 0 | dW1 half 1      (db2 = column sums of dZ2: two sibling warps of the issuer)
 // so that the epilogue of one piece runs under the MMAs of the next.  dW2^T / db2 / dW1^T accumulate in their own TMEM
 // columns for the whole launch (dW2 transposed: lane = layer-2 unit, so the drain stores 128 contiguous bytes per
 // instruction).  X tiles are double-buffered; their loads are issued where the epilogue warps are about to wait.
@@ -36,7 +36,7 @@
 // Shared memory (fp16 tiles in the column-blocked SWIZZLE_128B layout of tc_common.cuh):
 //   sW1 [48][256] 24 KB ([W1; b1; 0]) | sW2 [256][128] 64 KB | sX[2] [128][64] 2x16 KB ([x | 1 | 0]) |
 //   sH1 [128][256] 64 KB (dZ1 overwrites it in place) | sDZ2 [128][128] 32 KB | ones [16][64] 2 KB | fp32 vectors
-// TMEM columns: [0,128) work | [128,384) dW2^T half | [384,432) [448,496) dW1^T halves | [496,512) db2
+// TMEM columns: [0,128) work | [128,384) dW2^T half | [384,432) [448,496) dW1^T halves
 #include "common.cuh"
 #include "optim_math.cuh"
 #include "tc_common.cuh"
@@ -68,7 +68,7 @@ constexpr uint32_t S_W1 = 0, S_W2 = S_W1 + K1 * 4 * 128, S_X = S_W2 + 65536, S_H
 constexpr int F_B2 = 0, F_W3 = 128, F_Y = 256 /*[2][128]*/, F_PART = 512 /*[2][128]*/, F_RP = 768 /*[CSPLIT][128]*/,
               F_RED = F_RP + CSPLIT * 128 /*[4][128]*/, F_END = F_RED + 512;
 constexpr uint32_t S_BAR = S_F32 + F_END * 4;
-enum { B_DONE = 0, B_FREE, B_X0, B_X1, B_H1A, B_H1, B_DZ2, B_DW2A, B_DW2B, B_DZ1A, B_DZ1, B_DW1, B_ALL, B_XC0, B_XC1, B_WIMG, B_H1L, B_DW1A, N_BARS };
+enum { B_DONE = 0, B_FREE, B_X0, B_X1, B_H1A, B_H1, B_DZ2, B_DW2A, B_DW2B, B_DZ1A, B_DZ1, B_DW1, B_ALL, B_XC0, B_XC1, B_WIMG, B_H1L, B_DW1A, B_DB2, N_BARS };
 // fp16 image of the weights in the kernel's own tile layout, kept in the workspace by the finishing kernel of a step loop
 // (tc_reduce_kernel writes every updated parameter into it), so that the next step's set-up is three bulk copies instead of
 // a 160 KB fp32 read + convert per CTA:  [sW1 tile 24 KB: W1 rows, b1 row, zero rows][sW2 tile of rank 0 64 KB][rank 1 64 KB]
@@ -86,7 +86,7 @@ struct ExtIo {
 constexpr uint32_t S_TMEM = S_BAR + N_BARS * 8;
 constexpr uint32_t SMEM_BYTES = S_TMEM + 16;
 
-constexpr uint32_t TM_W0 = 0, TM_DW2 = 128, TM_DW1 = 384, TM_DB2 = 496, TM_COLS = 512;
+constexpr uint32_t TM_W0 = 0, TM_DW2 = 128, TM_DW1 = 384, TM_COLS = 512;
 
 // v[0..W) per lane -> lane l (< W) returns the sum over the warp's 32 lanes of v[l]  (W = 32 or 16)
 template <int W>
@@ -182,6 +182,7 @@ mlp_tc_kernel(const int loss_kind, const float* __restrict__ params, const float
     mbar_init(&bars[B_X0], N_EPI / 32); mbar_init(&bars[B_X1], N_EPI / 32);
     mbar_init(&bars[B_H1A], N_EPI / 32); mbar_init(&bars[B_H1], N_EPI / 32); mbar_init(&bars[B_DZ2], N_EPI / 32); mbar_init(&bars[B_DZ1A], N_EPI / 32);
     mbar_init(&bars[B_DZ1], N_EPI / 32);
+    mbar_init(&bars[B_DB2], 2);                                // the two db2 warps have read sDZ2
     mbar_init(&bars[B_ALL], 1); mbar_init(&bars[B_DW1], 1); mbar_init(&bars[B_DW1A], 1); mbar_init(&bars[B_DW2A], 1); mbar_init(&bars[B_DW2B], 1);
     mbar_init(&bars[B_XC0], 1); mbar_init(&bars[B_XC1], 1);   // exchange of the partial output dots: 1 arrival + 512 tx bytes
     mbar_init(&bars[B_WIMG], 1);                               // weight image: 1 arrival + 88 KB of bulk-copy bytes
@@ -288,7 +289,29 @@ mlp_tc_kernel(const int loss_kind, const float* __restrict__ params, const float
     asm volatile("setmaxnreg.dec.sync.aligned.u32 %0;" ::"n"(ISSUER_REGS));
   }
   if (warp > ISSUER_WARP) {
-    // idle siblings of the issuer warp
+    // Siblings of the issuer warp.  Two of them compute db2h = dZ2h^T 1 on the CUDA cores: thread j sums columns 2j, 2j+1 of
+    // every dZ2 tile over its 128 rows (one conflict-free 4-byte read per row).  As eight N = 16 MMAs the same sums cost the
+    // tensor pipe ~410 cycles per tile in the half of the tile where it is the bottleneck.
+    if (TRAIN && warp <= ISSUER_WARP + 2) {
+      const int j = (warp - ISSUER_WARP - 1) * 32 + lane;     // 0..63
+      float s0 = 0.f, s1 = 0.f;
+      for (int it = 0; it < my_tiles; ++it) {
+        ok = mbar_wait(&bars[B_DZ2], it & 1) && ok;
+#pragma unroll 8
+        for (int r = 0; r < TILE; ++r) {
+          const uint32_t w = lds32(sDZ2 + tile_chunk_off(TILE, r, (2 * j) & ~7) + (uint32_t)((2 * j) & 7) * 2);
+          const float2 f = __half22float2(*reinterpret_cast<const __half2*>(&w));
+          s0 += f.x; s1 += f.y;
+        }
+        __syncwarp();
+        if (lane == 0) mbar_arrive(&bars[B_DB2]);
+      }
+      if (my_tiles > 0) {
+        float* my = partials + (size_t)blockIdx.x * PSTRIDE;
+        my[B2_OFF + rank * 128 + 2 * j] = s0;
+        my[B2_OFF + rank * 128 + 2 * j + 1] = s1;
+      }
+    }
   } else if (warp == ISSUER_WARP) {
     // =========================== MMA issuer ===========================
     // The whole warp runs the control flow (so descriptor arithmetic stays warp-uniform); one elected
@@ -297,7 +320,6 @@ mlp_tc_kernel(const int loss_kind, const float* __restrict__ params, const float
     constexpr uint32_t ID_KM_KM_128 = make_idesc(128, 128, false, false);
     constexpr uint32_t ID_MN_MN_128 = make_idesc(128, 128, true, true);
     constexpr uint32_t ID_MN_MN_48 = make_idesc(128, 48, true, true);
-    constexpr uint32_t ID_MN_KM_16 = make_idesc(128, 16, true, false);
     const bool leader = elect_one();
     // the second X buffer is 16 KB further: +1024 in the descriptor's (address >> 4) field
     uint64_t dX_km0 = desc_kmajor(sX, TILE, 0, 0), dX_mn0 = desc_mnmajor(sX, TILE, 0, 0);
@@ -395,7 +417,7 @@ mlp_tc_kernel(const int loss_kind, const float* __restrict__ params, const float
       ok = mbar_wait(&bars[B_DZ2], it & 1) && ok;
       TRACE_M(16);
       fence_after();
-      // Order: dH1p half 0 | dW2 rows 0..127 | dH1p half 1 | dW2 rows 128..255 | db2 | dW1 rows 0..127 | next tile's
+      // Order: dH1p half 0 | dW2 rows 0..127 | dH1p half 1 | dW2 rows 128..255 | dW1 rows 0..127 | next tile's
       // Z1 half 0 | dW1 rows 128..255.  The epilogue overwrites H1 with dZ1 in place, half by half: half h (H1 columns
       // 128h..128h+127) may be written once the dW2 half that reads those columns as its M rows has completed
       // (B_DW2A / B_DW2B), so the epilogue fetches dH1p half h and the ReLU mask while that dW2 half still runs.
@@ -439,17 +461,8 @@ mlp_tc_kernel(const int loss_kind, const float* __restrict__ params, const float
       issue_dw2(1);
       if (leader) mma_commit(&bars[B_DW2B]);   // ... and columns 128..255 after this one
       __syncwarp();
-      auto issue_db2 = [&]() {                 // db2h += dZ2h^T 1
-        if (leader) {
-#pragma unroll
-          for (int i = 0; i < TILE / 16; ++i)
-            mma_f16(tm + TM_DB2, dDZ2_mn + koff_mnmajor(i), dONES, ID_MN_KM_16, !(first && i == 0));
-        }
-        __syncwarp();
-      };
       TRACE_M(17);
       if (EXT) {
-        issue_db2();
         // layer 1 lives in mlp_tc_l1.cu: the partial dZ1 tile leaves as an image; then the next tile's H1 image comes in
         if (leader) mma_commit(&bars[B_DW1]);   // sDZ2 is free once this arrives (dW2, db2 were its last readers)
         __syncwarp();
@@ -477,9 +490,6 @@ mlp_tc_kernel(const int loss_kind, const float* __restrict__ params, const float
         ok = mbar_wait(&bars[B_X0 + (xb ^ 1)], ((it + 1) >> 1) & 1) && ok;
         issue_z1(xb ^ 1, 0);
       }
-      // db2 only after the MMAs the next tile's first epilogue pass waits for (dW1 rows 0..127 free sH1's first half, Z1 half 0
-      // is its input): on the tensor pipe's queue it would delay both by its 8 MMAs
-      issue_db2();
       ok = mbar_wait(&bars[B_DZ1], it & 1) && ok;
       TRACE_M(18);
       fence_after();
@@ -539,7 +549,7 @@ mlp_tc_kernel(const int loss_kind, const float* __restrict__ params, const float
       const bool row_valid = row0 + row < n_rows;
       TRACE_E(20);
       // ---- (b) H1 = relu(Z1 + b1) -> sH1, two halves of 128 columns (the bias is already in the accumulator) ----
-      if (EXT && TRAIN && it > 0) ok = mbar_wait(&bars[B_DW1], (it - 1) & 1) && ok;   // dW2 / db2 of the previous tile still read sDZ2
+      if (EXT && TRAIN && it > 0) { ok = mbar_wait(&bars[B_DW1], (it - 1) & 1) && ok; ok = mbar_wait(&bars[B_DB2], (it - 1) & 1) && ok; }   // dW2 / db2 of the previous tile still read sDZ2
 #pragma unroll 1
       for (int h = 0; h < (EXT ? 0 : 2); ++h) {
         uint32_t v[CW];
@@ -548,6 +558,7 @@ mlp_tc_kernel(const int loss_kind, const float* __restrict__ params, const float
         TRACE_E(43);
         // dW1 of the previous tile still reads sH1 (as dZ1): its rows 0..127 read columns 0..127, its rows 128..255 the rest
         if (TRAIN && it > 0) ok = mbar_wait(&bars[h == 0 ? B_DW1A : B_DW1], (it - 1) & 1) && ok;
+        if (TRAIN && it > 0 && h == 1) ok = mbar_wait(&bars[B_DB2], (it - 1) & 1) && ok;   // ... and the db2 warps the previous dZ2 tile
         // (forward only: sH1 was last read by the previous tile's Z2h, whose completion this thread has already seen)
         const int c0 = h * 128 + hh * CW;
 #pragma unroll
@@ -740,12 +751,7 @@ mlp_tc_kernel(const int loss_kind, const float* __restrict__ params, const float
           my[B1_OFF + h1] = __uint_as_float(w[0]);
         }
       }
-      if (hh == CSPLIT - 1) {  // db2h: lane = out column, every accumulator column holds the same sum
-        uint32_t w[16];
-        tmem_ld16(tm + TM_DB2 + lane_base, w);
-        tmem_ld_wait();
-        my[B2_OFF + rank * 128 + row] = __uint_as_float(w[0]);
-      }
+      // (db2h is written by the db2 warps)
       // dw3h: per-warp column sums (lanes 0..CW-1 hold them) -> add the four row quarters in order
 #pragma unroll
       for (int c = 0; c < CW / 32; ++c) {

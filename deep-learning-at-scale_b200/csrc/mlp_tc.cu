@@ -168,7 +168,7 @@ mlp_tc_kernel(const int loss_kind, const float* __restrict__ params, const float
   const int pair = blockIdx.x >> 1, n_pairs = gridDim.x >> 1;
   const size_t n_tiles = (n_rows + TILE - 1) / TILE;
   bool ok = (sbase & 1023u) == 0;   // the swizzled tile layout needs a 1024-byte aligned base
-  int te = 0, tmm = 0;
+  [[maybe_unused]] int te = 0, tmm = 0;   // trace slots (DLAS_TC_TRACE builds)
   TRACE_E(1);
   const bool clk_owner = (blockIdx.x == 0 && tid == 0);
   const long long clk_c0 = clk_owner ? clock64() : 0;

@@ -141,3 +141,13 @@ def test_parameter_average_gloo_world2(tmp_path):
     r = np.load(out)
     np.testing.assert_allclose(r["a"], 1.5)
     np.testing.assert_allclose(r["b"], np.arange(3) * 1.5)
+
+
+def test_bind_host_to_gpu_is_a_no_op_without_nvml_or_on_one_node():
+    """dlas.parallel.bind_host_to_gpu narrows the CPU affinity to the GPU's NUMA node before pinned buffers are allocated; with
+    no NVML device (this container) or a single-node host it must change nothing and say so."""
+    import os
+    from dlas import parallel
+    before = os.sched_getaffinity(0)
+    assert parallel.bind_host_to_gpu(0) == 0
+    assert os.sched_getaffinity(0) == before

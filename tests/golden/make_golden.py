@@ -49,6 +49,26 @@ def mlp_steps(dims, batch, n_steps, tag):
     np.savez_compressed(os.path.join(HERE, "mlp_%s_steps.npz" % tag), **out)
 
 
+def dynamic_ann_steps(lags, batch, n_steps):
+    """configs[3] shape: an (n + lags - 1, 8) raw series, sample i = rows i .. i + lags - 1 flattened lag-major (Readme.md:17-19),
+    192-256-256-1.  The series is stored, not the windows: consumers build them (oracle) or read them in place (kernels)."""
+    n = batch * n_steps
+    series, ys = O.synth_rows(SEED, 5000, n + lags - 1, 8)
+    y = ys[lags - 1:]
+    dims = [lags * 8, 256, 256, 1]
+    W = O.lag_windows(series.astype(np.float64), lags)
+    p0 = O.glorot_init(dims, SEED + 3)
+    out = dict(dims=np.array(dims), lags=lags, batch=batch, n_steps=n_steps, series=series, y=y, params0=p0)
+    for name, cfg in (("sgd_mse", O.sgd_config()), ("adam_mse", O.adam_config())):
+        p = p0.astype(np.float64)
+        out[name + "_losses"] = O.mlp_fit_steps(p, dims, W, y.astype(np.float64), batch, n_steps, O.LOSS_MSE, cfg, O.opt_state(p.size))
+        out[name + "_final"] = p.astype(np.float32)          # 115,457 parameters: stored as fp32 (tolerances are 1e-4)
+    ls, g = O.mlp_loss_grad_sums(p0.astype(np.float64), dims, W[:batch], y[:batch].astype(np.float64), O.LOSS_MSE)
+    out["grad0_loss_sum"] = ls
+    out["grad0"] = g.astype(np.float32)
+    np.savez_compressed(os.path.join(HERE, "dynamic_ann_192_256_256_1_steps.npz"), **out)
+
+
 def lstm_vectors():
     out = {}
     for tag, (d, h, nl, T, B) in (("small", (3, 8, 2, 5, 6)), ("h128", (8, 128, 2, 48, 4))):
@@ -81,6 +101,7 @@ if __name__ == "__main__":
     gilbert_kat()
     mlp_steps([8, 64, 64, 1], 32, 8, "8_64_64_1")
     mlp_steps([32, 256, 256, 1], 64, 4, "32_256_256_1")
+    dynamic_ann_steps(24, 128, 4)
     lstm_vectors()
     dp_equivalence()
     for f in sorted(os.listdir(HERE)):

@@ -202,3 +202,35 @@ def test_rows_per_call_limit(dl):
         ops.mlp_grad(dims, 0, dl.MODE_TC, torch.zeros(gs.numel() - 1, device="cuda"), torch.zeros(n, 192, device="cuda"),
                      torch.zeros(n, device="cuda"), gs, ws)
     assert "at most" in str(e.value)
+
+
+@pytest.mark.parametrize("mode", ["fp32", "tc"])
+@pytest.mark.parametrize("name", ["sgd_mse", "adam_mse"])
+def test_dynamic_ann_golden(dl, golden_dir, mode, name):
+    """The committed configs[3] fixture (tests/golden/make_golden.py: raw (n + 23, 8) series, 24-lag windows, 4 steps of 128):
+    windows read in place from the series through dlas_mlp_fit_steps_strided.  fp32 mode: loss and weights within 1e-4;
+    tensor-core mode at this batch of 128: loss 1e-2 (single rows' operand rounding is not averaged away below 4096 rows),
+    weights 1e-4 (SGD) / 3e-3 (Adam)."""
+    import os
+    from dlas import ops
+    g = np.load(os.path.join(golden_dir, "dynamic_ann_192_256_256_1_steps.npz"))
+    dims, lags, b, ns = g["dims"].tolist(), int(g["lags"]), int(g["batch"]), int(g["n_steps"])
+    md = dl.MODE_TC if mode == "tc" else dl.MODE_FP32
+    opt = dl.Adam() if name.startswith("adam") else dl.SGD(lr=0.001, momentum=0.99, decay=1e-6, nesterov=True)
+    V = dl.LagWindows(_cuda(g["series"]), lags)
+    p = _cuda(g["params0"])
+    m, v = torch.zeros_like(p), torch.zeros_like(p)
+    gs = torch.zeros(p.numel() + 1, device="cuda")
+    losses = torch.zeros(ns, device="cuda")
+    ws = ops.mlp_workspace(dims, md)
+    ops.mlp_fit_steps(dims, dl.LOSS_MSE, md, opt.cfg(), p, m, v, V, _cuda(g["y"]), b, ns, 0, losses, gs, ws)
+    ops.mlp_status(dims, md, ws)
+    ltol, wtol = (1e-4, 1e-4) if mode == "fp32" else (1e-2, 3e-3 if name.startswith("adam") else 1e-4)
+    np.testing.assert_allclose(losses.cpu().numpy(), g[name + "_losses"], rtol=ltol)
+    assert _relerr(p.cpu().numpy(), g[name + "_final"].astype(np.float64)) < wtol
+    # first-batch gradient of the fixture
+    ops.mlp_grad(dims, dl.LOSS_MSE, md, _cuda(g["params0"]), dl.LagWindows(_cuda(g["series"][:b + lags - 1]), lags), _cuda(g["y"][:b]), gs, ws)
+    gg = gs.cpu().numpy()
+    assert gg[-1] == pytest.approx(float(g["grad0_loss_sum"]), rel=ltol)
+    # a raw gradient of 128 rows in tensor-core mode: 1 / sqrt(rows) from the 1.0e-2 measured at 1000 rows (module docstring)
+    assert _relerr(gg[:-1], g["grad0"].astype(np.float64)) < (1e-4 if mode == "fp32" else 3e-2)

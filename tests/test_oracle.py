@@ -262,6 +262,25 @@ def test_torch_cpu_port_matches_oracle(golden_dir):
     assert np.abs(q / O.gilbert(P, S, R) - 1).max() < 1e-6
 
 
+def test_dynamic_ann_golden_reproduces(golden_dir):
+    """configs[3] fixture (raw series + lag windows, 192-256-256-1): the oracle reproduces its committed losses / weights, and
+    the torch-CPU port (the timed CPU baseline) lands on them within the fp32 tolerance."""
+    import torch_cpu as T
+    g = _g(golden_dir, "dynamic_ann_192_256_256_1_steps.npz")
+    dims, lags, b, ns = g["dims"].tolist(), int(g["lags"]), int(g["batch"]), int(g["n_steps"])
+    W = O.lag_windows(g["series"].astype(np.float64), lags)
+    assert W.shape == (b * ns, dims[0]) and dims[0] == lags * 8
+    p = g["params0"].astype(np.float64)
+    losses = O.mlp_fit_steps(p, dims, W, g["y"].astype(np.float64), b, ns, O.LOSS_MSE, O.sgd_config(), O.opt_state(p.size))
+    np.testing.assert_allclose(losses, g["sgd_mse_losses"], rtol=1e-12)
+    assert np.linalg.norm(p - g["sgd_mse_final"]) / np.linalg.norm(p) < 1e-6          # stored as fp32
+    m = T.TorchCpuMlp(dims, g["params0"], loss="mse")
+    X, y = torch.from_numpy(W.astype(np.float32)), torch.from_numpy(g["y"]).reshape(-1, 1)
+    tl = [m.step(X[s * b:(s + 1) * b], y[s * b:(s + 1) * b]) for s in range(ns)]
+    np.testing.assert_allclose(tl, g["sgd_mse_losses"], rtol=1e-4)
+    assert np.linalg.norm(m.flat() - g["sgd_mse_final"]) / np.linalg.norm(g["sgd_mse_final"]) < 1e-5
+
+
 def test_parameter_averaging_reduces_to_gradient_averaging_for_plain_sgd():
     """every=1, no momentum: averaging parameters after one local step == one step on the mean gradient."""
     dims, batch, steps = [5, 7, 1], 32, 5

@@ -120,13 +120,26 @@ lstm_dw_tc_kernel(const LstmDesc d, const float* __restrict__ X, const float* __
         const StashPos sp = stash_pos(d, seq);
         if (u >= 2) ok = mbar_wait(&bars[B_FREE0 + b], ((u >> 1) - 1) & 1) && ok;   // the MMAs of use u-2 have read this buffer
         const uint32_t tDZ = sDZ + b * 32768, tA = sA + b * 65536;
-        if (FAST) {   // dz: 64 halves of gate jc
-          uint4 v[8];
+        if (FAST) {
+          // every 16-byte chunk of the row -- 8 of dz (gate jc, this thread's unit half), 16 of [x | h_prev] -- is requested before
+          // the first one is stored: one trip to L2 per chunk of rows instead of three
+          uint4 vz[8], va[16];
 #pragma unroll
           for (int q = 0; q < 8; ++q)
-            v[q] = in ? __ldcs(reinterpret_cast<const uint4*>(dz16 + idx16(sp, ((size_t)l * T + t) * 4 + jc, half * 64 + q * 8))) : make_uint4(0u, 0u, 0u, 0u);
+            vz[q] = in ? __ldcs(reinterpret_cast<const uint4*>(dz16 + idx16(sp, ((size_t)l * T + t) * 4 + jc, half * 64 + q * 8))) : make_uint4(0u, 0u, 0u, 0u);
+          const bool hx = (half == 0 && l == 0);            // x_t comes from X (fp32), below
+          const bool have = in && !hx && (half == 0 || t > 0);
+          const int sl = (half == 0) ? l - 1 : l, stt = (half == 0) ? t : (t > 0 ? t - 1 : 0);
 #pragma unroll
-          for (int q = 0; q < 8; ++q) sts128(tDZ + tile_chunk_off(CH, r, half * 64 + q * 8), v[q]);
+          for (int q = 0; q < 16; ++q)
+            va[q] = have ? __ldg(reinterpret_cast<const uint4*>(h16 + idx16(sp, (size_t)(hx ? 0 : sl) * T + stt, q * 8))) : make_uint4(0u, 0u, 0u, 0u);
+#pragma unroll
+          for (int q = 0; q < 8; ++q) sts128(tDZ + tile_chunk_off(CH, r, half * 64 + q * 8), vz[q]);
+          if (!hx) {
+            const int c0 = (half == 0) ? 0 : xw;
+#pragma unroll
+            for (int q = 0; q < 16; ++q) sts128(tA + tile_chunk_off(CH, r, c0 + q * 8), va[q]);
+          }
         } else {      // dz: 64 floats of gate jc
 #pragma unroll
           for (int q = 0; q < 8; ++q) {
@@ -151,15 +164,7 @@ lstm_dw_tc_kernel(const LstmDesc d, const float* __restrict__ X, const float* __
           const int sl = (half == 0) ? l - 1 : l, stt = (half == 0) ? t : (t > 0 ? t - 1 : 0);
           const int c0 = (half == 0) ? 0 : xw;
           if (FAST) {
-#pragma unroll
-            for (int q0 = 0; q0 < 16; q0 += 8) {
-              uint4 v[8];
-#pragma unroll
-              for (int q = 0; q < 8; ++q)
-                v[q] = have ? __ldg(reinterpret_cast<const uint4*>(h16 + idx16(sp, (size_t)sl * T + stt, (q0 + q) * 8))) : make_uint4(0u, 0u, 0u, 0u);
-#pragma unroll
-              for (int q = 0; q < 8; ++q) sts128(tA + tile_chunk_off(CH, r, c0 + (q0 + q) * 8), v[q]);
-            }
+            // (copied above, together with dz)
           } else {
 #pragma unroll
             for (int q = 0; q < 16; ++q) {

@@ -68,7 +68,7 @@ constexpr uint32_t S_W1 = 0, S_W2 = S_W1 + K1 * 4 * 128, S_X = S_W2 + 65536, S_H
 constexpr int F_B2 = 0, F_W3 = 128, F_Y = 256 /*[2][128]*/, F_PART = 512 /*[2][128]*/, F_RP = 768 /*[CSPLIT][128]*/,
               F_RED = F_RP + CSPLIT * 128 /*[4][128]*/, F_END = F_RED + 512;
 constexpr uint32_t S_BAR = S_F32 + F_END * 4;
-enum { B_DONE = 0, B_FREE, B_X0, B_X1, B_H1A, B_H1, B_DZ2, B_DW2A, B_DW2B, B_DZ1A, B_DZ1, B_DW1, B_ALL, B_XC0, B_XC1, B_WIMG, B_H1L, B_DW1A, B_DB2, N_BARS };
+enum { B_DONE = 0, B_FREE, B_X0, B_X1, B_H1A, B_H1, B_DZ2, B_DW2A, B_DW2B, B_DZ1A, B_DZ1, B_DW1, B_ALL, B_XC0, B_XC1, B_WIMG, B_H1L, B_H1M, B_DW1A, B_DB2, N_BARS };
 // fp16 image of the weights in the kernel's own tile layout, kept in the workspace by the finishing kernel of a step loop
 // (tc_reduce_kernel writes every updated parameter into it), so that the next step's set-up is three bulk copies instead of
 // a 160 KB fp32 read + convert per CTA:  [sW1 tile 24 KB: W1 rows, b1 row, zero rows][sW2 tile of rank 0 64 KB][rank 1 64 KB]
@@ -186,7 +186,7 @@ mlp_tc_kernel(const int loss_kind, const float* __restrict__ params, const float
     mbar_init(&bars[B_ALL], 1); mbar_init(&bars[B_DW1], 1); mbar_init(&bars[B_DW1A], 1); mbar_init(&bars[B_DW2A], 1); mbar_init(&bars[B_DW2B], 1);
     mbar_init(&bars[B_XC0], 1); mbar_init(&bars[B_XC1], 1);   // exchange of the partial output dots: 1 arrival + 512 tx bytes
     mbar_init(&bars[B_WIMG], 1);                               // weight image: 1 arrival + 88 KB of bulk-copy bytes
-    mbar_init(&bars[B_H1L], 1);                                // K_TRAIN_EXT: H1 tile image, 1 arrival + 64 KB
+    mbar_init(&bars[B_H1L], 1); mbar_init(&bars[B_H1M], 1);   // layer 1 outside: H1 tile image, columns 0..127 / 128..255: 1 arrival + 32 KB each
     mbar_fence_init();
   }
   if (warp == ISSUER_WARP) tmem_alloc(tmem_slot, TM_COLS);
@@ -355,9 +355,12 @@ mlp_tc_kernel(const int loss_kind, const float* __restrict__ params, const float
     };
     if (w_image != nullptr) ok = mbar_wait(&bars[B_WIMG], 0) && ok;   // bulk copies of the weight tiles have landed
     if (EXT) {
-      if (my_tiles > 0 && leader) {   // H1 of the first tile: one bulk copy of the image l1_fwd_tc_kernel left
-        mbar_arrive_expect_tx(&bars[B_H1L], IMG_TILE_BYTES);
-        bulk_g2s(sH1, ext.h1_img + (size_t)pair * IMG_TILE_BYTES, IMG_TILE_BYTES, &bars[B_H1L]);
+      if (my_tiles > 0 && leader) {   // H1 of the first tile: the image l1_fwd_tc_kernel left, as two bulk copies (K halves of Z2h)
+        const uint8_t* src = ext.h1_img + (size_t)pair * IMG_TILE_BYTES;
+        mbar_arrive_expect_tx(&bars[B_H1L], IMG_TILE_BYTES / 2);
+        bulk_g2s(sH1, src, IMG_TILE_BYTES / 2, &bars[B_H1L]);
+        mbar_arrive_expect_tx(&bars[B_H1M], IMG_TILE_BYTES / 2);
+        bulk_g2s(sH1 + IMG_TILE_BYTES / 2, src + IMG_TILE_BYTES / 2, IMG_TILE_BYTES / 2, &bars[B_H1M]);
       }
       __syncwarp();
     } else if (my_tiles > 0) {
@@ -382,11 +385,9 @@ mlp_tc_kernel(const int loss_kind, const float* __restrict__ params, const float
           mma_f16(tm + TM_W0, dH1_km + koff_kmajor(TILE, i), dW2_mn + koff_mnmajor(i), ID_KM_MN_128, i > 0);
       }
       __syncwarp();
-      if (!EXT) {
-        ok = mbar_wait(&bars[B_H1], it & 1) && ok;
-        TRACE_M(13);
-        fence_after();
-      }
+      ok = mbar_wait(&bars[EXT ? B_H1M : B_H1], it & 1) && ok;
+      TRACE_M(13);
+      fence_after();
       if (leader) {
 #pragma unroll
         for (int i = D1 / 32; i < D1 / 16; ++i)
@@ -400,8 +401,11 @@ mlp_tc_kernel(const int loss_kind, const float* __restrict__ params, const float
         if (it + 1 < my_tiles) {
           ok = mbar_wait(&bars[B_DONE], (n - 1) & 1) && ok;
           if (leader) {
-            mbar_arrive_expect_tx(&bars[B_H1L], IMG_TILE_BYTES);
-            bulk_g2s(sH1, ext.h1_img + ((size_t)pair + (size_t)(it + 1) * n_pairs) * IMG_TILE_BYTES, IMG_TILE_BYTES, &bars[B_H1L]);
+            const uint8_t* src = ext.h1_img + ((size_t)pair + (size_t)(it + 1) * n_pairs) * IMG_TILE_BYTES;
+            mbar_arrive_expect_tx(&bars[B_H1L], IMG_TILE_BYTES / 2);
+            bulk_g2s(sH1, src, IMG_TILE_BYTES / 2, &bars[B_H1L]);
+            mbar_arrive_expect_tx(&bars[B_H1M], IMG_TILE_BYTES / 2);
+            bulk_g2s(sH1 + IMG_TILE_BYTES / 2, src + IMG_TILE_BYTES / 2, IMG_TILE_BYTES / 2, &bars[B_H1M]);
           }
           __syncwarp();
         }
@@ -466,15 +470,31 @@ mlp_tc_kernel(const int loss_kind, const float* __restrict__ params, const float
         // layer 1 lives in mlp_tc_l1.cu: the partial dZ1 tile leaves as an image; then the next tile's H1 image comes in
         if (leader) mma_commit(&bars[B_DW1]);   // sDZ2 is free once this arrives (dW2, db2 were its last readers)
         __syncwarp();
-        ok = mbar_wait(&bars[B_DZ1], it & 1) && ok;   // both halves of dZ1 are in place (the writers fenced for the async proxy)
+        // half by half (columns 0..127, then 128..255): the partial dZ1 leaves as soon as the epilogue has written it, and the
+        // next tile's H1 half comes in as soon as the copy engine has read that half (the writers fenced for the async proxy)
+        const size_t tile = (size_t)pair + (size_t)it * n_pairs;
+        uint8_t* dzo = ext.dz1_img + (size_t)rank * ext.img_stride + tile * IMG_TILE_BYTES;
+        const uint8_t* nxt = ext.h1_img + (tile + n_pairs) * IMG_TILE_BYTES;
+        const bool more = it + 1 < my_tiles;
+        ok = mbar_wait(&bars[B_DZ1A], it & 1) && ok;
         if (leader) {
-          const size_t tile = (size_t)pair + (size_t)it * n_pairs;
-          bulk_s2g(ext.dz1_img + (size_t)rank * ext.img_stride + tile * IMG_TILE_BYTES, sH1, IMG_TILE_BYTES);
+          bulk_s2g(dzo, sH1, IMG_TILE_BYTES / 2);
           bulk_commit();
-          bulk_wait_read0();                    // the copy engine has read the tile: it may be overwritten
-          if (it + 1 < my_tiles) {
-            mbar_arrive_expect_tx(&bars[B_H1L], IMG_TILE_BYTES);
-            bulk_g2s(sH1, ext.h1_img + (tile + n_pairs) * IMG_TILE_BYTES, IMG_TILE_BYTES, &bars[B_H1L]);
+          bulk_wait_read0();                    // the copy engine has read the half: it may be overwritten
+          if (more) {                           // ... by the next tile's H1 columns 0..127, under the epilogue's second dZ1 half
+            mbar_arrive_expect_tx(&bars[B_H1L], IMG_TILE_BYTES / 2);
+            bulk_g2s(sH1, nxt, IMG_TILE_BYTES / 2, &bars[B_H1L]);
+          }
+        }
+        __syncwarp();
+        ok = mbar_wait(&bars[B_DZ1], it & 1) && ok;
+        if (leader) {
+          bulk_s2g(dzo + IMG_TILE_BYTES / 2, sH1 + IMG_TILE_BYTES / 2, IMG_TILE_BYTES / 2);
+          bulk_commit();
+          bulk_wait_read0();
+          if (more) {
+            mbar_arrive_expect_tx(&bars[B_H1M], IMG_TILE_BYTES / 2);
+            bulk_g2s(sH1 + IMG_TILE_BYTES / 2, nxt + IMG_TILE_BYTES / 2, IMG_TILE_BYTES / 2, &bars[B_H1M]);
           }
         }
         __syncwarp();
